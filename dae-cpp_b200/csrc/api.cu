@@ -1,0 +1,423 @@
+// C ABI of libdaecpp_b200.so (see include/daecpp_b200.h for the contract and the reference
+// regions each entry point replaces).
+#include <cmath>
+#include <cstring>
+#include <new>
+
+#include "ctx.hpp"
+
+using namespace daecpp_b200;
+
+static thread_local std::string g_create_error;
+
+namespace
+{
+
+int fail(daecpp_b200_ctx *c, int code, const char *msg)
+{
+    c->err = msg;
+    return code;
+}
+
+// Variable-step BDF-1..4 weights.  The association of every product/quotient follows the
+// expressions at dae-cpp/solver.hpp:160,168-173,178-184,190-199 so that alpha and the weights
+// are bit-identical to the reference's (C++ evaluates * and / left to right).
+bool bdf_weights(int order, const double *dt, double *w)
+{
+    const double h0 = dt[0], h1 = dt[1], h2 = dt[2], h3 = dt[3];
+    const double s01 = h0 + h1, s12 = h1 + h2, s23 = h2 + h3;
+    const double s012 = h0 + h1 + h2, s123 = h1 + h2 + h3, s0123 = h0 + h1 + h2 + h3;
+    w[0] = w[1] = w[2] = w[3] = w[4] = 0.0;
+    if (order == 1)
+    {
+        w[0] = 1.0 / h0;
+        w[1] = w[0];
+    }
+    else if (order == 2)
+    {
+        w[0] = (2.0 * h0 + h1) / (h0 * s01);
+        w[1] = s01 / (h0 * h1);
+        w[2] = h0 / (h1 * s01);
+    }
+    else if (order == 3)
+    {
+        w[0] = (3.0 * h0 * h0 + h1 * s12 + 2.0 * h0 * (2.0 * h1 + h2)) / (h0 * s01 * s012);
+        w[1] = s01 * s012 / (h0 * h1 * s12);
+        w[2] = h0 * s012 / (h1 * h2 * s01);
+        w[3] = h0 * s01 / (h2 * s12 * s012);
+    }
+    else if (order == 4)
+    {
+        w[0] = (4.0 * h0 * h0 * h0 + h1 * s12 * s123 + 3.0 * h0 * h0 * (3.0 * h1 + 2.0 * h2 + h3) +
+                2.0 * h0 * (3.0 * h1 * h1 + h2 * s23 + 2.0 * h1 * (2.0 * h2 + h3))) /
+               (h0 * s01 * s012 * s0123);
+        w[1] = s01 * s012 * s0123 / (h0 * h1 * s12 * s123);
+        w[2] = h0 * s012 * s0123 / (h1 * s01 * h2 * s23);
+        w[3] = h0 * s01 * s0123 / (h2 * s12 * s012 * h3);
+        w[4] = h0 * s01 * s012 / (h3 * s23 * s123 * s0123);
+    }
+    else
+        return false;
+    return true;
+}
+
+int ensure_stage(daecpp_b200_ctx *c, size_t count)
+{
+    if (count <= c->h_stage_cap) return DAECPP_B200_OK;
+    if (c->h_stage) cudaFreeHost(c->h_stage);
+    c->h_stage = nullptr; c->h_stage_cap = 0;
+    DAECPP_CUDA_TRY(c, cudaMallocHost((void **)&c->h_stage, sizeof(double) * count));
+    c->h_stage_cap = count;
+    return DAECPP_B200_OK;
+}
+
+int upload_vector(daecpp_b200_ctx *c, double *dst, const double *src_host)
+{
+    // through the pinned stage so the copy is one DMA regardless of how the caller allocated
+    int rc = ensure_stage(c, c->n);
+    if (rc) return rc;
+    std::memcpy(c->h_stage, src_host, sizeof(double) * c->n);
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(dst, c->h_stage, sizeof(double) * c->n, cudaMemcpyHostToDevice, c->stream));
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return DAECPP_B200_OK;
+}
+
+int download_vector(daecpp_b200_ctx *c, double *dst_host, const double *src)
+{
+    int rc = ensure_stage(c, c->n);
+    if (rc) return rc;
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_stage, src, sizeof(double) * c->n, cudaMemcpyDeviceToHost, c->stream));
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    std::memcpy(dst_host, c->h_stage, sizeof(double) * c->n);
+    return DAECPP_B200_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *daecpp_b200_version(void) { return "daecpp_b200 0.1 (sm_100a)"; }
+
+int daecpp_b200_create(int32_t n, int device, daecpp_b200_ctx **out)
+{
+    if (!out) return DAECPP_B200_EINVAL;
+    *out = nullptr;
+    if (n <= 0) { g_create_error = "system size must be positive"; return DAECPP_B200_EINVAL; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+    {
+        g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (this library has no CPU fallback)";
+        return DAECPP_B200_ECUDA;
+    }
+    if (device < 0 || device >= ndev) { g_create_error = "device index out of range"; return DAECPP_B200_EINVAL; }
+    daecpp_b200_ctx *c = new (std::nothrow) daecpp_b200_ctx();
+    if (!c) return DAECPP_B200_ENOMEM;
+    c->n = n;
+    c->device = device;
+    auto bail = [&](cudaError_t err, const char *what) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
+        daecpp_b200_destroy(c);
+        return err == cudaErrorMemoryAllocation ? DAECPP_B200_ENOMEM : DAECPP_B200_ECUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+    if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    double *slab = nullptr;
+    const size_t nv = 10; // xk, x[0..3], f, b, dx, work, dxdt
+    if ((e = cudaMalloc((void **)&slab, sizeof(double) * nv * (size_t)n)) != cudaSuccess) return bail(e, "cudaMalloc(state)");
+    c->xk = slab;
+    for (int k = 0; k < 4; ++k) c->xh[k] = slab + (size_t)(k + 1) * n;
+    c->f = slab + 5 * (size_t)n; c->b = slab + 6 * (size_t)n; c->dx = slab + 7 * (size_t)n;
+    c->work = slab + 8 * (size_t)n; c->dxdt = slab + 9 * (size_t)n;
+    if ((e = cudaMemsetAsync(slab, 0, sizeof(double) * nv * (size_t)n, c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
+    if ((e = cudaMalloc((void **)&c->d_flags, sizeof(int32_t) * 8)) != cudaSuccess) return bail(e, "cudaMalloc(flags)");
+    if ((e = cudaMalloc((void **)&c->d_scalars, sizeof(double) * 8)) != cudaSuccess) return bail(e, "cudaMalloc(scalars)");
+    if ((e = cudaMallocHost((void **)&c->h_flags, sizeof(int32_t) * 8)) != cudaSuccess) return bail(e, "cudaMallocHost");
+    if ((e = cudaMallocHost((void **)&c->h_scalars, sizeof(double) * 8)) != cudaSuccess) return bail(e, "cudaMallocHost");
+    if ((e = cudaMemsetAsync(c->d_flags, 0, sizeof(int32_t) * 8, c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
+    if ((e = cudaMemsetAsync(c->d_scalars, 0, sizeof(double) * 8, c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
+    if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
+    *out = c;
+    return DAECPP_B200_OK;
+}
+
+void daecpp_b200_destroy(daecpp_b200_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    c->M.release(); c->J.release(); c->dS.release();
+    c->m_rowptr.release(); c->m_rowslot.release(); c->m_rowcol.release();
+    c->u_outer.release(); c->u_inner.release(); c->u_J.release(); c->u_M.release(); c->u_vals.release();
+    c->LU.release(); c->CB.release(); c->upd.release();
+    c->keys_a.release(); c->keys_b.release(); c->pay_a.release(); c->pay_b.release(); c->scan.release(); c->cub_tmp.release();
+    if (c->xk) cudaFree(c->xk);
+    if (c->d_flags) cudaFree(c->d_flags);
+    if (c->d_scalars) cudaFree(c->d_scalars);
+    if (c->h_flags) cudaFreeHost(c->h_flags);
+    if (c->h_scalars) cudaFreeHost(c->h_scalars);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char *daecpp_b200_last_error(const daecpp_b200_ctx *c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+void *daecpp_b200_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+    return p;
+}
+void daecpp_b200_host_free(void *p)
+{
+    if (p) cudaFreeHost(p);
+}
+
+int daecpp_b200_set_state(daecpp_b200_ctx *c, const double *x0)
+{
+    if (!c || !x0) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    int rc = upload_vector(c, c->xk, x0);
+    if (rc) return rc;
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->xh[0], c->xk, sizeof(double) * c->n, cudaMemcpyDeviceToDevice, c->stream));
+    for (int k = 1; k < 4; ++k) DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->xh[k], 0, sizeof(double) * c->n, c->stream));
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_get_xk(daecpp_b200_ctx *c, double *xk_host)
+{
+    if (!c || !xk_host) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    return download_vector(c, xk_host, c->xk);
+}
+
+int daecpp_b200_rollback(daecpp_b200_ctx *c)
+{
+    if (!c) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->xk, c->xh[0], sizeof(double) * c->n, cudaMemcpyDeviceToDevice, c->stream));
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_set_mass(daecpp_b200_ctx *c, const double *A, const int32_t *i, const int32_t *j, int64_t nT)
+{
+    if (!c) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    int rc = assemble_triplets(c, c->M, A, i, j, nT);
+    if (rc) return rc;
+    return build_mass_csr(c);
+}
+
+int daecpp_b200_set_jacobian(daecpp_b200_ctx *c, const double *A, const int32_t *i, const int32_t *j, int64_t nT)
+{
+    if (!c) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    c->direct_csc = false;
+    return assemble_triplets(c, c->J, A, i, j, nT);
+}
+
+int daecpp_b200_residual(daecpp_b200_ctx *c, const double *f_host, int32_t order, const double dt[4], double *alpha_out)
+{
+    if (!c || !f_host || !dt) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->M.have_pattern) return fail(c, DAECPP_B200_EINVAL, "set_mass must precede residual");
+    double w[5];
+    if (!bdf_weights(order, dt, w)) return fail(c, DAECPP_B200_EINVAL, "unsupported time integration order");
+    if (alpha_out) *alpha_out = w[0];
+    int rc = ensure_stage(c, c->n);
+    if (rc) return rc;
+    std::memcpy(c->h_stage, f_host, sizeof(double) * c->n);
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->f, c->h_stage, sizeof(double) * c->n, cudaMemcpyHostToDevice, c->stream));
+    rc = launch_residual(c, order, w);
+    if (rc) return rc;
+    // the stage buffer is reused by the next call
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    std::memcpy(c->h_scalars + 2, w, sizeof(w)); // remembered for get_vector(dxdt)
+    c->h_flags[6] = order;
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_refactor(daecpp_b200_ctx *c, double alpha)
+{
+    if (!c) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    int rc = build_union(c);
+    if (rc) return rc;
+    if (!c->have_symbolic && (rc = upload_symbolic(c))) return rc;
+    return numeric_refactor(c, alpha);
+}
+
+int daecpp_b200_solve_update(daecpp_b200_ctx *c, double atol, double rtol, double max_err_abs, int32_t *flags)
+{
+    if (!c || !flags) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_factor) return fail(c, DAECPP_B200_EINVAL, "no valid factorisation");
+    DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev0, c->stream));
+    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, sizeof(int32_t), c->stream));
+    int rc = numeric_solve(c);
+    if (rc) return rc;
+    rc = launch_update(c, atol, rtol, max_err_abs);
+    if (rc) return rc;
+    DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev1, c->stream));
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->ms_last_solve = ms;
+    *flags = c->h_flags[2];
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_accept_step(daecpp_b200_ctx *c, int32_t variability_on, double tol, double *variability_out)
+{
+    if (!c) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    if (variability_on) DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_scalars, 0, sizeof(double), c->stream));
+    int rc = launch_accept(c, variability_on, tol);
+    if (rc) return rc;
+    double v = 0.0;
+    if (variability_on)
+    {
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_scalars, c->d_scalars, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        v = c->h_scalars[0];
+    }
+    if (variability_out) *variability_out = v;
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_set_rhs(daecpp_b200_ctx *c, const double *b_host)
+{
+    if (!c || !b_host) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    return upload_vector(c, c->b, b_host);
+}
+
+int daecpp_b200_solve(daecpp_b200_ctx *c, double *dx_host)
+{
+    if (!c) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_factor) return fail(c, DAECPP_B200_EINVAL, "no valid factorisation");
+    DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev0, c->stream));
+    int rc = numeric_solve(c);
+    if (rc) return rc;
+    DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev1, c->stream));
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->ms_last_solve = ms;
+    if (dx_host) return download_vector(c, dx_host, c->dx);
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_get_csc(daecpp_b200_ctx *c, int32_t which, int32_t *outer, int32_t *inner, double *vals, int64_t cap,
+                        int64_t *nnz_out)
+{
+    if (!c) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    const int32_t *d_outer, *d_inner; const double *d_vals; int64_t nnz;
+    if (which == 0 || which == 1)
+    {
+        TripletSet &T = which == 0 ? c->M : c->J;
+        if (!T.have_pattern) return fail(c, DAECPP_B200_EINVAL, "matrix not set");
+        d_outer = T.outer.p; d_inner = T.inner.p; d_vals = T.vals.p; nnz = T.nnz;
+    }
+    else if (which == 2)
+    {
+        if (c->n_refactor == 0) return fail(c, DAECPP_B200_EINVAL, "refactor has not run");
+        d_outer = c->u_outer.p; d_inner = c->u_inner.p; d_vals = c->u_vals.p; nnz = c->nnzU;
+    }
+    else
+        return fail(c, DAECPP_B200_EINVAL, "unknown matrix selector");
+    if (nnz_out) *nnz_out = nnz;
+    if (outer) DAECPP_CUDA_TRY(c, cudaMemcpyAsync(outer, d_outer, sizeof(int32_t) * ((size_t)c->n + 1), cudaMemcpyDeviceToHost, c->stream));
+    const int64_t m = nnz < cap ? nnz : cap;
+    if (inner && m > 0) DAECPP_CUDA_TRY(c, cudaMemcpyAsync(inner, d_inner, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, c->stream));
+    if (vals && m > 0) DAECPP_CUDA_TRY(c, cudaMemcpyAsync(vals, d_vals, sizeof(double) * m, cudaMemcpyDeviceToHost, c->stream));
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_get_vector(daecpp_b200_ctx *c, int32_t which, double *host)
+{
+    if (!c || !host) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    const double *src = nullptr;
+    switch (which)
+    {
+    case 0: src = c->b; break;
+    case 1: src = c->dx; break;
+    case 2:
+    {
+        int rc = launch_dxdt(c, c->h_flags[6] ? c->h_flags[6] : 1, c->h_scalars + 2);
+        if (rc) return rc;
+        src = c->dxdt;
+        break;
+    }
+    case 3: src = c->xk; break;
+    case 4: case 5: case 6: case 7: src = c->xh[which - 4]; break;
+    default: return fail(c, DAECPP_B200_EINVAL, "unknown vector selector");
+    }
+    return download_vector(c, host, src);
+}
+
+int daecpp_b200_set_vector(daecpp_b200_ctx *c, int32_t which, const double *host)
+{
+    if (!c || !host) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    double *dst = nullptr;
+    switch (which)
+    {
+    case 0: dst = c->b; break;
+    case 1: dst = c->dx; break;
+    case 3: dst = c->xk; break;
+    case 4: case 5: case 6: case 7: dst = c->xh[which - 4]; break;
+    default: return fail(c, DAECPP_B200_EINVAL, "unknown vector selector");
+    }
+    return upload_vector(c, dst, host);
+}
+
+int daecpp_b200_get_stat(daecpp_b200_ctx *c, const char *key, double *value)
+{
+    if (!c || !key || !value) return DAECPP_B200_EINVAL;
+    const std::string k(key);
+    if (k == "n_symbolic") *value = c->n_symbolic;
+    else if (k == "n_refactor") *value = c->n_refactor;
+    else if (k == "n_solve") *value = c->n_solve;
+    else if (k == "n_cold_assembly") *value = c->n_cold;
+    else if (k == "kernels_launched") *value = c->kernels;
+    else if (k == "ms_symbolic") *value = c->ms_symbolic;
+    else if (k == "ms_last_refactor") *value = c->ms_last_refactor;
+    else if (k == "ms_last_solve") *value = c->ms_last_solve;
+    else if (k == "n_fronts") *value = c->S.nsn;
+    else if (k == "n_levels") *value = c->S.nlevels;
+    else if (k == "nnz_factor") *value = (double)c->S.nnz_factor;
+    else if (k == "factor_flops") *value = c->S.flops;
+    else if (k == "max_front") *value = c->S.max_front;
+    else if (k == "lu_doubles") *value = (double)c->S.lu_size;
+    else if (k == "cb_doubles") *value = (double)c->S.cb_size;
+    else if (k == "nnz_jb") *value = (double)c->nnzU;
+    else if (k == "n_missing_diag") *value = c->S.n_missing_diag;
+    else return fail(c, DAECPP_B200_EINVAL, "unknown stat key");
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
+{
+    if (!c || !key) return DAECPP_B200_EINVAL;
+    const std::string k(key);
+    if (k == "refine_steps") c->refine_steps = (int)value;
+    else if (k == "pivot_tol") c->pivot_tol = value;
+    else if (k == "leaf_size") { c->sopt.leaf_size = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "max_super") { c->sopt.max_super = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else return fail(c, DAECPP_B200_EINVAL, "unknown option key");
+    return DAECPP_B200_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,162 @@
+// Internal context layout shared by the .cu translation units of libdaecpp_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/daecpp_b200.h"
+#include "symbolic.hpp"
+
+namespace daecpp_b200
+{
+
+// Grow-only device buffer.
+template <class T>
+struct DevBuf
+{
+    T *p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t count)
+    {
+        if (count <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = count + count / 8 + 16;
+        cudaError_t e = cudaMalloc((void **)&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+// One triplet stream (mass matrix or Jacobian) and its compressed-column form on the device.
+struct TripletSet
+{
+    // staging of the latest upload
+    DevBuf<double> A;
+    DevBuf<int32_t> ti, tj;
+    int64_t nT = 0;
+    // cached pattern (valid while the (i,j) stream repeats)
+    bool have_pattern = false;
+    int64_t nT_cached = -1;
+    DevBuf<int32_t> ti_cached, tj_cached;
+    DevBuf<int32_t> src;     // [nT]  triplet indices ordered by (col,row,input order)
+    DevBuf<int32_t> src_ptr; // [nnz+1] first position in src of every slot
+    DevBuf<int32_t> outer;   // [n+1]
+    DevBuf<int32_t> inner;   // [nnz]
+    DevBuf<double> vals;     // [nnz]
+    int64_t nnz = 0;
+    bool no_duplicates = false;
+    uint64_t pattern_version = 0;
+    void release()
+    {
+        A.release(); ti.release(); tj.release(); ti_cached.release(); tj_cached.release();
+        src.release(); src_ptr.release(); outer.release(); inner.release(); vals.release();
+    }
+};
+
+struct DeviceSymbolic
+{
+    DevBuf<int32_t> perm, iperm, sn_first, sn_rows, sn_rel, child_ptr, child_idx, level_sn;
+    DevBuf<int64_t> sn_rowptr, sn_lu, sn_cb;
+    DevBuf<uint32_t> a_dest;
+    void release()
+    {
+        perm.release(); iperm.release(); sn_first.release(); sn_rows.release(); sn_rel.release();
+        child_ptr.release(); child_idx.release(); level_sn.release(); sn_rowptr.release(); sn_lu.release();
+        sn_cb.release(); a_dest.release();
+    }
+};
+
+struct LevelLaunch
+{
+    int32_t begin = 0, count = 0; // range in level_sn
+    int32_t group = 32;           // threads cooperating on one front
+    int32_t max_dim = 0;
+};
+
+} // namespace daecpp_b200
+
+struct daecpp_b200_ctx
+{
+    int32_t n = 0;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    // state vectors (solver.hpp:301-337 equivalents), all length n, resident in HBM
+    double *xk = nullptr, *xh[4] = {nullptr, nullptr, nullptr, nullptr};
+    double *f = nullptr, *b = nullptr, *dx = nullptr, *work = nullptr, *dxdt = nullptr;
+    int32_t *d_flags = nullptr; // [8] device flag words
+    int32_t *h_flags = nullptr; // pinned mirror
+    double *d_scalars = nullptr, *h_scalars = nullptr; // [8]
+    double *h_stage = nullptr;  // pinned staging for n doubles
+    size_t h_stage_cap = 0;
+
+    daecpp_b200::TripletSet M, J;
+    // CSR view of M for the residual (row-wise accumulation in column order)
+    daecpp_b200::DevBuf<int32_t> m_rowptr, m_rowslot, m_rowcol;
+    uint64_t m_csr_version = ~0ull;
+
+    // union pattern of J and M = pattern of Jb
+    uint64_t union_J_version = ~0ull, union_M_version = ~0ull;
+    int64_t nnzU = 0;
+    daecpp_b200::DevBuf<int32_t> u_outer, u_inner, u_J, u_M;
+    daecpp_b200::DevBuf<double> u_vals;
+    bool direct_csc = false; // matrix given through the linear-solver-only entry
+
+    // symbolic + numeric factor
+    bool have_symbolic = false, have_factor = false;
+    daecpp_b200::SymbolicOptions sopt;
+    daecpp_b200::Symbolic S;
+    daecpp_b200::DeviceSymbolic dS;
+    std::vector<daecpp_b200::LevelLaunch> levels;
+    daecpp_b200::DevBuf<double> LU, CB, upd;
+    double last_alpha = 0.0;
+
+    // scratch for the cold (sorting) path
+    daecpp_b200::DevBuf<uint64_t> keys_a, keys_b;
+    daecpp_b200::DevBuf<int32_t> pay_a, pay_b, scan;
+    daecpp_b200::DevBuf<char> cub_tmp;
+
+    // options
+    int refine_steps = 0;
+    double pivot_tol = 0.0;
+
+    // statistics
+    double n_symbolic = 0, n_refactor = 0, n_solve = 0, n_cold = 0, kernels = 0;
+    double ms_symbolic = 0, ms_last_refactor = 0, ms_last_solve = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+#define DAECPP_CUDA_TRY(ctx, call)                                                                        \
+    do                                                                                                    \
+    {                                                                                                     \
+        cudaError_t e__ = (call);                                                                         \
+        if (e__ != cudaSuccess)                                                                           \
+        {                                                                                                 \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);                             \
+            return (e__ == cudaErrorMemoryAllocation) ? DAECPP_B200_ENOMEM : DAECPP_B200_ECUDA;           \
+        }                                                                                                 \
+    } while (0)
+
+namespace daecpp_b200
+{
+// assembly.cu
+int assemble_triplets(daecpp_b200_ctx *c, TripletSet &T, const double *A, const int32_t *i, const int32_t *j,
+                      int64_t nT);
+int build_union(daecpp_b200_ctx *c);
+int build_mass_csr(daecpp_b200_ctx *c);
+// numeric.cu
+int upload_symbolic(daecpp_b200_ctx *c);
+int numeric_refactor(daecpp_b200_ctx *c, double alpha);
+int numeric_solve(daecpp_b200_ctx *c); // b -> dx
+// vector_ops.cu
+int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
+int launch_dxdt(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
+int launch_update(daecpp_b200_ctx *c, double atol, double rtol, double max_err_abs);
+int launch_accept(daecpp_b200_ctx *c, int32_t variability_on, double tol);
+} // namespace daecpp_b200

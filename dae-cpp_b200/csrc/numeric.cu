@@ -1,0 +1,396 @@
+// Numeric multifrontal LU refactorisation and triangular solves on the device.
+//
+// Role replaced: Eigen::SparseLU::factorize / _solve_impl as called from
+// dae-cpp/solver.hpp:537,558 (Eigen/src/SparseLU/SparseLU.h:611-814, 338-358).  The algorithm
+// is different by design: the reference interleaves symbolic and numeric work column by column
+// with partial pivoting and is strictly sequential; here the pattern-only analysis
+// (symbolic.cpp) fixes a shallow assembly tree once, and every refactorisation is a sweep over
+// its levels in which all fronts of a level are processed concurrently:
+//
+//   scatter   Jb = J - (M*alpha) (bit-exact, solver.hpp:523) written straight into front storage
+//   level l   for every front: extend-add the children's contribution blocks, dense LU of the
+//             pivot block (static pivoting), panel solves, Schur complement -> own contribution
+//   solve     forward sweep up the tree with per-front update vectors (deterministic, no
+//             atomics), backward sweep down the tree
+//
+// A front is worked on by a cooperative group of G threads (4/8/32 lanes of a warp, or a whole
+// CTA); G is picked per level from the largest front in it.
+#include <chrono>
+
+#include "ctx.hpp"
+
+namespace daecpp_b200
+{
+namespace
+{
+
+struct FrontTables
+{
+    const int32_t *sn_first, *sn_rows, *sn_rel, *child_ptr, *child_idx, *level_sn;
+    const int64_t *sn_rowptr, *sn_lu, *sn_cb;
+};
+
+template <int G>
+struct Grp
+{
+    static constexpr int FRONTS_PER_CTA = (G <= 32) ? (128 / G) : 1;
+    static constexpr int THREADS = (G <= 32) ? 128 : G;
+    __device__ static __forceinline__ int lane() { return (G <= 32) ? (threadIdx.x % G) : threadIdx.x; }
+    __device__ static __forceinline__ int slot() { return (G <= 32) ? (threadIdx.x / G) : 0; }
+    __device__ static __forceinline__ void sync()
+    {
+        if (G > 32) __syncthreads();
+        else if (G == 32) __syncwarp();
+        else
+        {
+            const unsigned base = ((threadIdx.x & 31) / G) * G;
+            __syncwarp((((1u << G) - 1u)) << base);
+        }
+    }
+};
+
+// Jb slot values (bit-exact) and their scatter into the zeroed front storage.
+__global__ void k_scatter(int64_t nnzU, const int32_t *__restrict__ uJ, const int32_t *__restrict__ uM,
+                          const double *__restrict__ jv, const double *__restrict__ mv, double alpha,
+                          double *__restrict__ uvals, const uint32_t *__restrict__ dest, double *__restrict__ LU)
+{
+    int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= nnzU) return;
+    double v;
+    if (uJ)
+    {
+        const int32_t a = uJ[u], b = uM[u];
+        const double m = (b >= 0) ? __dmul_rn(mv[b], alpha) : 0.0;
+        const double j = (a >= 0) ? jv[a] : 0.0;
+        v = __dsub_rn(j, m);
+        uvals[u] = v;
+    }
+    else
+        v = uvals[u];
+    LU[dest[u]] = v;
+}
+
+template <int G>
+__global__ void __launch_bounds__(Grp<G>::THREADS) k_factor_level(FrontTables T, int32_t begin, int32_t count,
+                                                                  double *__restrict__ LU, double *__restrict__ CB,
+                                                                  double pivot_tol, int32_t *__restrict__ flags)
+{
+    const int32_t idx = blockIdx.x * Grp<G>::FRONTS_PER_CTA + Grp<G>::slot();
+    if (idx >= count) return;
+    const int t = Grp<G>::lane();
+    const int32_t f = T.level_sn[begin + idx];
+    const int32_t s = T.sn_first[f + 1] - T.sn_first[f];
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - T.sn_rowptr[f]);
+    const int32_t ld = s + r;
+    double *Lp = LU + T.sn_lu[f];
+    double *Ut = Lp + (int64_t)ld * s;
+    double *C = CB + T.sn_cb[f];
+    const int32_t rr = r * r;
+
+    for (int32_t e = t; e < rr; e += G) C[e] = 0.0;
+    Grp<G>::sync();
+
+    for (int32_t ci = T.child_ptr[f]; ci < T.child_ptr[f + 1]; ++ci)
+    {
+        const int32_t c = T.child_idx[ci];
+        const int64_t rp = T.sn_rowptr[c];
+        const int32_t rc = (int32_t)(T.sn_rowptr[c + 1] - rp);
+        const double *Cc = CB + T.sn_cb[c];
+        const int32_t *rel = T.sn_rel + rp;
+        for (int32_t e = t; e < rc * rc; e += G)
+        {
+            const int32_t a = e % rc, bc = e / rc;
+            const int32_t ra = rel[a], rb = rel[bc];
+            const double v = Cc[e];
+            if (rb < s) Lp[(int64_t)rb * ld + ra] += v;
+            else if (ra < s) Ut[(int64_t)ra * r + (rb - s)] += v;
+            else C[(int64_t)(rb - s) * r + (ra - s)] += v;
+        }
+        Grp<G>::sync();
+    }
+
+    for (int32_t k = 0; k < s; ++k)
+    {
+        double *colk = Lp + (int64_t)k * ld;
+        const double d = colk[k];
+        if (t == 0 && (!(fabs(d) > pivot_tol) || isinf(d))) atomicOr(&flags[3], 1);
+        const double inv = 1.0 / d;
+        for (int32_t i = k + 1 + t; i < ld; i += G) colk[i] *= inv;
+        Grp<G>::sync();
+        const int32_t ncol = s - k - 1, nrow = ld - k - 1;
+        for (int32_t e = t; e < ncol * nrow; e += G)
+        {
+            const int32_t j = k + 1 + e / nrow, i = k + 1 + e % nrow;
+            Lp[(int64_t)j * ld + i] -= colk[i] * Lp[(int64_t)j * ld + k];
+        }
+        const double *utk = Ut + (int64_t)k * r;
+        for (int32_t e = t; e < ncol * r; e += G)
+        {
+            const int32_t j = k + 1 + e / r, i = e % r;
+            Ut[(int64_t)j * r + i] -= utk[i] * colk[j];
+        }
+        Grp<G>::sync();
+    }
+
+    for (int32_t e = t; e < rr; e += G)
+    {
+        const int32_t a = e % r, bc = e / r;
+        double acc = C[e];
+        for (int32_t k = 0; k < s; ++k) acc -= Lp[(int64_t)k * ld + s + a] * Ut[(int64_t)k * r + bc];
+        C[e] = acc;
+    }
+}
+
+__global__ void k_permute_in(int32_t n, const int32_t *__restrict__ perm, const double *__restrict__ b, double *__restrict__ y)
+{
+    int32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) y[k] = b[perm[k]];
+}
+__global__ void k_permute_out(int32_t n, const int32_t *__restrict__ perm, const double *__restrict__ y, double *__restrict__ dx)
+{
+    int32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) dx[perm[k]] = y[k];
+}
+
+template <int G>
+__global__ void __launch_bounds__(Grp<G>::THREADS) k_forward_level(FrontTables T, int32_t begin, int32_t count,
+                                                                   const double *__restrict__ LU, double *__restrict__ upd,
+                                                                   double *__restrict__ y)
+{
+    const int32_t idx = blockIdx.x * Grp<G>::FRONTS_PER_CTA + Grp<G>::slot();
+    if (idx >= count) return;
+    const int t = Grp<G>::lane();
+    const int32_t f = T.level_sn[begin + idx];
+    const int32_t first = T.sn_first[f];
+    const int32_t s = T.sn_first[f + 1] - first;
+    const int64_t rp0 = T.sn_rowptr[f];
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - rp0);
+    const int32_t ld = s + r;
+    const double *Lp = LU + T.sn_lu[f];
+    double *u = upd + rp0;
+    double *y1 = y + first;
+    for (int32_t a = t; a < r; a += G) u[a] = 0.0;
+    Grp<G>::sync();
+    for (int32_t ci = T.child_ptr[f]; ci < T.child_ptr[f + 1]; ++ci)
+    {
+        const int32_t c = T.child_idx[ci];
+        const int64_t rp = T.sn_rowptr[c];
+        const int32_t rc = (int32_t)(T.sn_rowptr[c + 1] - rp);
+        const double *uc = upd + rp;
+        const int32_t *rel = T.sn_rel + rp;
+        for (int32_t a = t; a < rc; a += G)
+        {
+            const int32_t ra = rel[a];
+            if (ra < s) y1[ra] += uc[a]; else u[ra - s] += uc[a];
+        }
+        Grp<G>::sync();
+    }
+    for (int32_t k = 0; k < s; ++k)
+    {
+        const double yk = y1[k];
+        const double *colk = Lp + (int64_t)k * ld;
+        for (int32_t i = k + 1 + t; i < ld; i += G)
+        {
+            const double v = colk[i] * yk;
+            if (i < s) y1[i] -= v; else u[i - s] -= v;
+        }
+        Grp<G>::sync();
+    }
+}
+
+template <int G>
+__global__ void __launch_bounds__(Grp<G>::THREADS) k_backward_level(FrontTables T, int32_t begin, int32_t count,
+                                                                    const double *__restrict__ LU, double *__restrict__ y)
+{
+    const int32_t idx = blockIdx.x * Grp<G>::FRONTS_PER_CTA + Grp<G>::slot();
+    if (idx >= count) return;
+    const int t = Grp<G>::lane();
+    const int32_t f = T.level_sn[begin + idx];
+    const int32_t first = T.sn_first[f];
+    const int32_t s = T.sn_first[f + 1] - first;
+    const int64_t rp0 = T.sn_rowptr[f];
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - rp0);
+    const int32_t ld = s + r;
+    const double *Lp = LU + T.sn_lu[f];
+    const double *Ut = Lp + (int64_t)ld * s;
+    const int32_t *rows = T.sn_rows + rp0;
+    double *y1 = y + first;
+    for (int32_t k = t; k < s; k += G)
+    {
+        double acc = y1[k];
+        const double *utk = Ut + (int64_t)k * r;
+        for (int32_t a = 0; a < r; ++a) acc -= utk[a] * y[rows[a]];
+        y1[k] = acc;
+    }
+    Grp<G>::sync();
+    for (int32_t j = s - 1; j >= 0; --j)
+    {
+        const double *colj = Lp + (int64_t)j * ld;
+        if (t == 0) y1[j] = y1[j] / colj[j];
+        Grp<G>::sync();
+        const double xj = y1[j];
+        for (int32_t i = t; i < j; i += G) y1[i] -= colj[i] * xj;
+        Grp<G>::sync();
+    }
+}
+
+FrontTables tables(daecpp_b200_ctx *c)
+{
+    FrontTables T;
+    T.sn_first = c->dS.sn_first.p; T.sn_rows = c->dS.sn_rows.p; T.sn_rel = c->dS.sn_rel.p;
+    T.child_ptr = c->dS.child_ptr.p; T.child_idx = c->dS.child_idx.p; T.level_sn = c->dS.level_sn.p;
+    T.sn_rowptr = c->dS.sn_rowptr.p; T.sn_lu = c->dS.sn_lu.p; T.sn_cb = c->dS.sn_cb.p;
+    return T;
+}
+
+template <class T>
+int upload(daecpp_b200_ctx *c, DevBuf<T> &d, const std::vector<T> &h)
+{
+    DAECPP_CUDA_TRY(c, d.reserve(h.size() ? h.size() : 1));
+    if (!h.empty())
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(d.p, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, c->stream));
+    return DAECPP_B200_OK;
+}
+
+int pick_group(int32_t max_dim)
+{
+    if (max_dim <= 4) return 4;
+    if (max_dim <= 8) return 8;
+    if (max_dim <= 48) return 32;
+    return 256;
+}
+
+#define DISPATCH_GROUP(G, KERNEL, count, ...)                                                                     \
+    switch (G)                                                                                                    \
+    {                                                                                                             \
+    case 4: KERNEL<4><<<((count) + Grp<4>::FRONTS_PER_CTA - 1) / Grp<4>::FRONTS_PER_CTA, Grp<4>::THREADS, 0, st>>>(__VA_ARGS__); break;       \
+    case 8: KERNEL<8><<<((count) + Grp<8>::FRONTS_PER_CTA - 1) / Grp<8>::FRONTS_PER_CTA, Grp<8>::THREADS, 0, st>>>(__VA_ARGS__); break;       \
+    case 32: KERNEL<32><<<((count) + Grp<32>::FRONTS_PER_CTA - 1) / Grp<32>::FRONTS_PER_CTA, Grp<32>::THREADS, 0, st>>>(__VA_ARGS__); break;  \
+    default: KERNEL<256><<<(count), Grp<256>::THREADS, 0, st>>>(__VA_ARGS__); break;                             \
+    }
+
+} // namespace
+
+// Download the pattern of Jb, analyse it on the host, ship the tables back.
+int upload_symbolic(daecpp_b200_ctx *c)
+{
+    const int32_t n = c->n;
+    cudaStream_t st = c->stream;
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<int32_t> outer((size_t)n + 1), inner((size_t)(c->nnzU ? c->nnzU : 1));
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(outer.data(), c->u_outer.p, sizeof(int32_t) * ((size_t)n + 1), cudaMemcpyDeviceToHost, st));
+    if (c->nnzU)
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(inner.data(), c->u_inner.p, sizeof(int32_t) * c->nnzU, cudaMemcpyDeviceToHost, st));
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
+    const char *err = nullptr;
+    if (!analyse_pattern(n, outer.data(), inner.data(), c->sopt, c->S, &err))
+    {
+        c->err = err ? err : "symbolic analysis failed";
+        return DAECPP_B200_ENOMEM;
+    }
+    Symbolic &S = c->S;
+    int rc;
+    if ((rc = upload(c, c->dS.perm, S.perm))) return rc;
+    if ((rc = upload(c, c->dS.iperm, S.iperm))) return rc;
+    if ((rc = upload(c, c->dS.sn_first, S.sn_first))) return rc;
+    if ((rc = upload(c, c->dS.sn_rows, S.sn_rows))) return rc;
+    if ((rc = upload(c, c->dS.sn_rel, S.sn_rel))) return rc;
+    if ((rc = upload(c, c->dS.child_ptr, S.child_ptr))) return rc;
+    if ((rc = upload(c, c->dS.child_idx, S.child_idx))) return rc;
+    if ((rc = upload(c, c->dS.level_sn, S.level_sn))) return rc;
+    if ((rc = upload(c, c->dS.sn_rowptr, S.sn_rowptr))) return rc;
+    if ((rc = upload(c, c->dS.sn_lu, S.sn_lu))) return rc;
+    if ((rc = upload(c, c->dS.sn_cb, S.sn_cb))) return rc;
+    if ((rc = upload(c, c->dS.a_dest, S.a_dest))) return rc;
+    DAECPP_CUDA_TRY(c, c->LU.reserve((size_t)S.lu_size + 1));
+    DAECPP_CUDA_TRY(c, c->CB.reserve((size_t)S.cb_size + 1));
+    DAECPP_CUDA_TRY(c, c->upd.reserve((size_t)S.upd_size + 1));
+    c->levels.clear();
+    for (int32_t l = 0; l < S.nlevels; ++l)
+    {
+        LevelLaunch L;
+        L.begin = S.level_ptr[l];
+        L.count = S.level_ptr[l + 1] - S.level_ptr[l];
+        for (int32_t q = L.begin; q < L.begin + L.count; ++q)
+        {
+            const int32_t f = S.level_sn[q];
+            const int32_t d = S.s_of(f) + S.r_of(f);
+            if (d > L.max_dim) L.max_dim = d;
+        }
+        L.group = pick_group(L.max_dim);
+        c->levels.push_back(L);
+    }
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
+    c->have_symbolic = true;
+    c->have_factor = false;
+    c->n_symbolic += 1;
+    c->ms_symbolic = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return DAECPP_B200_OK;
+}
+
+int numeric_refactor(daecpp_b200_ctx *c, double alpha)
+{
+    cudaStream_t st = c->stream;
+    Symbolic &S = c->S;
+    FrontTables T = tables(c);
+    DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev0, st));
+    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->LU.p, 0, sizeof(double) * (size_t)S.lu_size, st));
+    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 3, 0, sizeof(int32_t), st));
+    if (c->nnzU)
+    {
+        const int blocks = (int)((c->nnzU + 255) / 256);
+        if (c->direct_csc)
+            k_scatter<<<blocks, 256, 0, st>>>(c->nnzU, nullptr, nullptr, nullptr, nullptr, 0.0, c->u_vals.p, c->dS.a_dest.p, c->LU.p);
+        else
+            k_scatter<<<blocks, 256, 0, st>>>(c->nnzU, c->u_J.p, c->u_M.p, c->J.vals.p, c->M.vals.p, alpha, c->u_vals.p,
+                                              c->dS.a_dest.p, c->LU.p);
+        c->kernels += 1;
+    }
+    for (const LevelLaunch &L : c->levels)
+    {
+        DISPATCH_GROUP(L.group, k_factor_level, L.count, T, L.begin, L.count, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+        c->kernels += 1;
+    }
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev1, st));
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 3, c->d_flags + 3, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->ms_last_refactor = ms;
+    c->n_refactor += 1;
+    c->last_alpha = alpha;
+    if (c->h_flags[3])
+    {
+        c->have_factor = false;
+        return DAECPP_B200_EDECOMP;
+    }
+    c->have_factor = true;
+    return DAECPP_B200_OK;
+}
+
+// dx = Jb^-1 b, all on the stream, no synchronisation
+int numeric_solve(daecpp_b200_ctx *c)
+{
+    cudaStream_t st = c->stream;
+    const int32_t n = c->n;
+    FrontTables T = tables(c);
+    k_permute_in<<<(n + 255) / 256, 256, 0, st>>>(n, c->dS.perm.p, c->b, c->work);
+    for (size_t l = 0; l < c->levels.size(); ++l)
+    {
+        const LevelLaunch &L = c->levels[l];
+        DISPATCH_GROUP(L.group, k_forward_level, L.count, T, L.begin, L.count, c->LU.p, c->upd.p, c->work);
+    }
+    for (size_t l = c->levels.size(); l-- > 0;)
+    {
+        const LevelLaunch &L = c->levels[l];
+        DISPATCH_GROUP(L.group, k_backward_level, L.count, T, L.begin, L.count, c->LU.p, c->work);
+    }
+    k_permute_out<<<(n + 255) / 256, 256, 0, st>>>(n, c->dS.perm.p, c->work, c->dx);
+    c->kernels += 2 + 2 * (double)c->levels.size();
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    c->n_solve += 1;
+    return DAECPP_B200_OK;
+}
+
+} // namespace daecpp_b200

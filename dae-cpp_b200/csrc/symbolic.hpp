@@ -1,0 +1,71 @@
+// Once-per-pattern symbolic analysis for the multifrontal sparse LU (host side).
+//
+// Plays the role Eigen::SparseLU::analyzePattern plays in the reference
+// (Eigen/src/SparseLU/SparseLU.h:528-587: COLAMD + column etree + postorder), but is built
+// for a GPU numeric phase: a nested-dissection ordering that keeps the elimination tree
+// shallow (O(log n) levels on chains and grids), a static (pivot-free) symbolic factorisation
+// of pattern(A + A^T), supernodes = frontal matrices, a level schedule of the assembly tree
+// and the scatter map from assembled-matrix slots into frontal storage.  It is computed once
+// and reused by every numeric refactorisation until the sparsity pattern changes -- the
+// reference redoes its analysis at every factorisation (dae-cpp/solver.hpp:537).
+#pragma once
+#include <cstdint>
+#include <vector>
+
+namespace daecpp_b200
+{
+
+struct SymbolicOptions
+{
+    int leaf_size = 8;      // stop dissecting below this many vertices
+    int relax_zeros = 0;    // reserved: relaxed amalgamation budget
+    int max_super = 256;    // widest supernode (pivot block) allowed
+};
+
+struct Symbolic
+{
+    int32_t n = 0;
+    std::vector<int32_t> perm;  // perm[k]  = original index eliminated k-th
+    std::vector<int32_t> iperm; // iperm[v] = elimination position of original index v
+
+    // supernodes / fronts, numbered in elimination order
+    int32_t nsn = 0;
+    std::vector<int32_t> sn_first;  // [nsn+1] first pivot column (permuted numbering)
+    std::vector<int64_t> sn_rowptr; // [nsn+1] offsets into sn_rows (also offsets of update vectors)
+    std::vector<int32_t> sn_rows;   // permuted indices below the pivot block, ascending
+    std::vector<int32_t> sn_rel;    // same indexing: position of that row in the PARENT's index list
+    std::vector<int32_t> sn_parent; // parent front or -1
+    std::vector<int64_t> sn_lu;     // [nsn] offset of the front's factor storage:
+                                    //   L panel  (s+r) x s, column major, ld = s+r  (F11 over F21)
+                                    //   Ut panel  r x s,    column major, ld = r    (F12 transposed)
+    std::vector<int64_t> sn_cb;     // [nsn] offset of the r x r contribution block (ld = r)
+    std::vector<int32_t> child_ptr; // [nsn+1]
+    std::vector<int32_t> child_idx; // children of each front, ascending
+
+    // level schedule: fronts of level l are independent; children live in lower levels
+    int32_t nlevels = 0;
+    std::vector<int32_t> level_ptr; // [nlevels+1]
+    std::vector<int32_t> level_sn;  // fronts ordered by (level, size class, id)
+
+    // matrix slot -> factor storage.  a_dest[u] is the offset (in doubles) inside the LU storage
+    // of slot u of the compressed-column pattern the analysis was given.
+    std::vector<uint32_t> a_dest;
+
+    int64_t lu_size = 0;  // doubles
+    int64_t cb_size = 0;  // doubles
+    int64_t upd_size = 0; // doubles (= sn_rows.size())
+    int64_t nnz_factor = 0; // structural nonzeros of L+U (unit diagonal not counted twice)
+    double flops = 0.0;
+    int32_t max_front = 0, max_pivot_block = 0;
+    int32_t n_missing_diag = 0; // structurally absent diagonal entries (become explicit zeros)
+
+    int32_t s_of(int32_t f) const { return sn_first[f + 1] - sn_first[f]; }
+    int32_t r_of(int32_t f) const { return (int32_t)(sn_rowptr[f + 1] - sn_rowptr[f]); }
+};
+
+// Analyse an n x n compressed-column pattern (outer[n+1], inner[nnz], rows ascending per
+// column).  Returns false (and fills err) if the factor would not fit the 32-bit slot map.
+bool analyse_pattern(int32_t n, const int32_t *outer, const int32_t *inner, const SymbolicOptions &opt,
+                     Symbolic &S, const char **err);
+
+} // namespace daecpp_b200

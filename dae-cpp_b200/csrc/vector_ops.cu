@@ -1,0 +1,151 @@
+// Fused, HBM-resident vector kernels of the Newton iteration.
+//
+//   k_residual : dxdt = BDF(xk, x[0..3]) (dae-cpp/solver.hpp:141-217) fused with
+//                b = M*dxdt - f            (dae-cpp/solver.hpp:516-518)
+//   k_update   : error checks and xk += dx (dae-cpp/solver.hpp:590-619)
+//   k_accept   : history shift + max relative variability (dae-cpp/solver.hpp:698-721)
+//
+// Arithmetic is written with __dmul_rn/__dadd_rn/__dsub_rn so that nvcc cannot contract to
+// FMA: the reference's default build has none, and b / xk are compared bit for bit.
+#include "ctx.hpp"
+
+namespace daecpp_b200
+{
+namespace
+{
+constexpr int TPB = 256;
+
+struct Bdf
+{
+    double c[5];
+    const double *xk, *x0, *x1, *x2, *x3;
+    int order;
+};
+
+__device__ __forceinline__ double bdf_at(const Bdf &s, int64_t i)
+{
+    if (s.order == 1) return __dmul_rn(__dsub_rn(s.xk[i], s.x0[i]), s.c[0]);
+    double r = __dmul_rn(s.c[0], s.xk[i]);
+    r = __dsub_rn(r, __dmul_rn(s.c[1], s.x0[i]));
+    r = __dadd_rn(r, __dmul_rn(s.c[2], s.x1[i]));
+    if (s.order >= 3) r = __dsub_rn(r, __dmul_rn(s.c[3], s.x2[i]));
+    if (s.order >= 4) r = __dadd_rn(r, __dmul_rn(s.c[4], s.x3[i]));
+    return r;
+}
+
+__global__ void k_dxdt(Bdf s, int32_t n, double *__restrict__ out)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = bdf_at(s, i);
+}
+
+// One thread per row; the row's mass entries are visited in increasing column order.
+__global__ void k_residual(Bdf s, int32_t n, const int32_t *__restrict__ rowptr, const int32_t *__restrict__ rowslot,
+                           const int32_t *__restrict__ rowcol, const double *__restrict__ mvals,
+                           const double *__restrict__ f, double *__restrict__ b)
+{
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    double acc = 0.0;
+    const int32_t e = rowptr[r + 1];
+    for (int32_t p = rowptr[r]; p < e; ++p)
+        acc = __dadd_rn(acc, __dmul_rn(mvals[rowslot[p]], bdf_at(s, rowcol[p])));
+    b[r] = __dsub_rn(acc, f[r]);
+}
+
+__global__ void k_update(int32_t n, const double *__restrict__ dx, const double *__restrict__ x0, double *__restrict__ xk,
+                         double atol, double rtol, double max_err_abs, int32_t *__restrict__ flags)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int f = 0;
+    if (i < n)
+    {
+        const double d = dx[i];
+        const double e = fabs(d);
+        if (e > max_err_abs || isnan(d)) f |= DAECPP_B200_DIVERGED;
+        const double xa = fabs(x0[i]);
+        if (xa > 1e-14 && __ddiv_rn(e, xa) > rtol) f |= DAECPP_B200_NOT_CONVERGED;
+        if (e > atol) f |= DAECPP_B200_NOT_CONVERGED;
+        xk[i] = __dadd_rn(xk[i], d);
+    }
+    // one atomic per warp that has something to report
+    const unsigned any = __reduce_or_sync(0xffffffffu, (unsigned)f);
+    if (any && (threadIdx.x & 31) == 0) atomicOr(&flags[2], (int32_t)any);
+}
+
+__global__ void k_accept(int32_t n, const double *__restrict__ xk, const double *__restrict__ x0_old,
+                         double *__restrict__ x0_new, int variability_on, double tol,
+                         unsigned long long *__restrict__ vmax_bits)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    double v = 0.0;
+    if (i < n)
+    {
+        const double a = xk[i];
+        x0_new[i] = a;
+        if (variability_on)
+        {
+            const double p = x0_old[i];
+            if (fabs(p) > tol && fabs(a) > tol) v = fabs(__ddiv_rn(__dsub_rn(p, a), p));
+        }
+    }
+    if (!variability_on) return;
+    // non-negative doubles order like their bit patterns; NaN (sign clear) compares above inf
+    unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        unsigned long long other = __shfl_xor_sync(0xffffffffu, bits, o);
+        bits = other > bits ? other : bits;
+    }
+    if ((threadIdx.x & 31) == 0 && bits) atomicMax(vmax_bits, bits);
+}
+
+Bdf make_bdf(daecpp_b200_ctx *c, int32_t order, const double coef[5])
+{
+    Bdf s;
+    for (int k = 0; k < 5; ++k) s.c[k] = coef[k];
+    s.xk = c->xk; s.x0 = c->xh[0]; s.x1 = c->xh[1]; s.x2 = c->xh[2]; s.x3 = c->xh[3];
+    s.order = order;
+    return s;
+}
+} // namespace
+
+int launch_dxdt(daecpp_b200_ctx *c, int32_t order, const double coef[5])
+{
+    k_dxdt<<<(c->n + TPB - 1) / TPB, TPB, 0, c->stream>>>(make_bdf(c, order, coef), c->n, c->dxdt);
+    c->kernels += 1;
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    return DAECPP_B200_OK;
+}
+
+int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5])
+{
+    k_residual<<<(c->n + TPB - 1) / TPB, TPB, 0, c->stream>>>(make_bdf(c, order, coef), c->n, c->m_rowptr.p, c->m_rowslot.p,
+                                                             c->m_rowcol.p, c->M.vals.p, c->f, c->b);
+    c->kernels += 1;
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    return DAECPP_B200_OK;
+}
+
+int launch_update(daecpp_b200_ctx *c, double atol, double rtol, double max_err_abs)
+{
+    k_update<<<(c->n + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->n, c->dx, c->xh[0], c->xk, atol, rtol, max_err_abs, c->d_flags);
+    c->kernels += 1;
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    return DAECPP_B200_OK;
+}
+
+int launch_accept(daecpp_b200_ctx *c, int32_t variability_on, double tol)
+{
+    // rotate the history by pointer: the oldest buffer becomes the new x[0]
+    double *oldest = c->xh[3];
+    const double *x0_old = c->xh[0];
+    c->xh[3] = c->xh[2]; c->xh[2] = c->xh[1]; c->xh[1] = c->xh[0]; c->xh[0] = oldest;
+    k_accept<<<(c->n + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->n, c->xk, x0_old, oldest, variability_on, tol,
+                                                           (unsigned long long *)c->d_scalars);
+    c->kernels += 1;
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    return DAECPP_B200_OK;
+}
+
+} // namespace daecpp_b200

@@ -1,0 +1,123 @@
+/*
+ * daecpp_b200 -- C ABI of the B200-native Newton linear-solve hot path for dae-cpp.
+ *
+ * This is the drop-in boundary.  The reference (dae-cpp 2.2.0) has no FFI: its integrator
+ * `core::detail::solve` owns an `Eigen::SparseLU<eimat> linsolver`, `eimat M_, Jb` and
+ * `eivec f_, b, dx, dxdt` as locals (dae-cpp/solver.hpp:325-337) and works on them inline.
+ * Each entry point below replaces one of those inline regions; the citation names it
+ * (paths relative to the reference tree).  The overlay header dae-cpp_b200/dae-cpp/solver.hpp
+ * is the only caller a user needs; INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *   - plain pointers and sizes; host arrays are owned by the caller and are only read/written
+ *     during the call (all calls return after the stream work they need has completed, unless
+ *     noted "async");
+ *   - one context = one DAE system on one GPU, used by one host thread at a time; no globals,
+ *     so an ensemble may own many contexts;
+ *   - return value: DAECPP_B200_OK (0) or a DAECPP_B200_E* code; numerical failures use the
+ *     codes that map onto the reference's exit_code values 2 and 3 (dae-cpp/typedefs.hpp:47-54);
+ *   - all values FP64, all indices int32 (the reference's default int_type / float_type,
+ *     dae-cpp/typedefs.hpp:57-69).
+ *   - there is NO CPU fallback: without a CUDA device every call fails with
+ *     DAECPP_B200_ECUDA.
+ */
+#ifndef DAECPP_B200_H
+#define DAECPP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct daecpp_b200_ctx daecpp_b200_ctx;
+
+enum
+{
+    DAECPP_B200_OK = 0,
+    DAECPP_B200_EDECOMP = 2,  /* factorisation failed (zero / non-finite pivot): solver.hpp:541-551 */
+    DAECPP_B200_ESOLVE = 3,   /* solution not finite:                            solver.hpp:562-572 */
+    DAECPP_B200_EINDEX = 20,  /* triplet index out of range: sparse-matrix.hpp:135-136 ASSERTs      */
+    DAECPP_B200_EINVAL = 21,  /* bad argument / call order                                            */
+    DAECPP_B200_ECUDA = 22,   /* CUDA runtime error or no device                                      */
+    DAECPP_B200_ENOMEM = 23
+};
+
+/* flags written by daecpp_b200_solve_update */
+enum
+{
+    DAECPP_B200_DIVERGED = 1,     /* |dx_i| > max_err_abs or NaN   (solver.hpp:596-601) */
+    DAECPP_B200_NOT_CONVERGED = 2 /* rel/abs tests failed somewhere (solver.hpp:603-614) */
+};
+
+/* ---- life cycle ---------------------------------------------------------------------- */
+/* Replaces the locals at solver.hpp:301-337 (SolverState history, xk, M_, Jb, f_, b, dx). */
+int daecpp_b200_create(int32_t n, int device, daecpp_b200_ctx **out);
+void daecpp_b200_destroy(daecpp_b200_ctx *ctx);
+const char *daecpp_b200_last_error(const daecpp_b200_ctx *ctx); /* NULL ctx: last create() error */
+const char *daecpp_b200_version(void);
+
+/* Pinned host memory for sparse_matrix::A/i/j (sparse-matrix.hpp:36-40) so that the triplet
+ * upload is a true async DMA.  Falls back to nothing: returns NULL on failure. */
+void *daecpp_b200_host_alloc(size_t bytes);
+void daecpp_b200_host_free(void *p);
+
+/* ---- state --------------------------------------------------------------------------- */
+/* xk = x[0] = x0, order/dt history cleared       (solver.hpp:310-313) */
+int daecpp_b200_set_state(daecpp_b200_ctx *ctx, const double *x0);
+/* download the Newton iterate xk for the host functors / Solution Manager (solver.hpp:455,500,659) */
+int daecpp_b200_get_xk(daecpp_b200_ctx *ctx, double *xk_host);
+/* xk = x[0]  (roll back after a failed step, solver.hpp:643,671) */
+int daecpp_b200_rollback(daecpp_b200_ctx *ctx);
+
+/* ---- triplet hand-off (replaces sparse_matrix::convert, sparse-matrix.hpp:124-152) ---- */
+/* M_ = M.convert(n)   (solver.hpp:481).  nT may be 0 (MassMatrixZero). */
+int daecpp_b200_set_mass(daecpp_b200_ctx *ctx, const double *A, const int32_t *i, const int32_t *j, int64_t nT);
+/* Jb = J.convert(n)   (solver.hpp:502).  A pattern equal to the previous call's takes the
+ * cached path (no sort); a new pattern triggers sort + symbolic analysis at the next refactor. */
+int daecpp_b200_set_jacobian(daecpp_b200_ctx *ctx, const double *A, const int32_t *i, const int32_t *j, int64_t nT);
+
+/* ---- per-iteration path -------------------------------------------------------------- */
+/* dxdt = BDF(order, dt[0..3]) of (xk, x[0..3]);  b = M*dxdt - f   (solver.hpp:439,516-518).
+ * f_host: the RHS values (f__[k].val(), solver.hpp:461-464).  *alpha_out receives the BDF
+ * derivative d(dxdt)/d(xk) that solver.hpp:439 returns. */
+int daecpp_b200_residual(daecpp_b200_ctx *ctx, const double *f_host, int32_t order, const double dt[4],
+                         double *alpha_out);
+/* Jb -= M_*alpha; linsolver.compute(Jb)   (solver.hpp:523,537).  Symbolic analysis runs only
+ * when the union pattern changed.  Returns OK or DAECPP_B200_EDECOMP. */
+int daecpp_b200_refactor(daecpp_b200_ctx *ctx, double alpha);
+/* dx = linsolver.solve(b); error checks; xk += dx   (solver.hpp:558,590-619).
+ * *flags = DIVERGED | NOT_CONVERGED bits.  Returns OK or DAECPP_B200_ESOLVE. */
+int daecpp_b200_solve_update(daecpp_b200_ctx *ctx, double atol, double rtol, double max_err_abs, int32_t *flags);
+/* x[3]<-x[2]<-x[1]<-x[0]<-xk and max relative variability   (solver.hpp:698-721) */
+int daecpp_b200_accept_step(daecpp_b200_ctx *ctx, int32_t variability_on, double variability_tolerance,
+                            double *variability_out);
+
+/* ---- linear-solver-only entry points (what Eigen::SparseLU::compute/solve expose,
+ *      Eigen/src/SparseLU/SparseLU.h:210-215,338-358; used by tests/test_linear-solver.cpp) ---- */
+int daecpp_b200_set_rhs(daecpp_b200_ctx *ctx, const double *b_host); /* b (device) = b_host */
+int daecpp_b200_solve(daecpp_b200_ctx *ctx, double *dx_host);        /* dx = Jb^-1 b; dx_host may be NULL */
+
+/* ---- parity / debug exports ---------------------------------------------------------- */
+/* Compressed-column copy of the mass matrix (which=0), the Jacobian (1) or Jb = J - alpha*M as
+ * last refactored (2).  outer has n+1 entries; inner/vals are filled up to cap entries.
+ * *nnz_out receives the true count. */
+int daecpp_b200_get_csc(daecpp_b200_ctx *ctx, int32_t which, int32_t *outer, int32_t *inner, double *vals,
+                        int64_t cap, int64_t *nnz_out);
+/* which: 0 = b, 1 = dx, 2 = dxdt, 3 = xk, 4..7 = x[0..3] */
+int daecpp_b200_get_vector(daecpp_b200_ctx *ctx, int32_t which, double *host);
+/* Overwrite a device vector (same selectors except dxdt); lets tests plant a BDF history
+ * (SolverState::x, solver.hpp:45) without integrating. */
+int daecpp_b200_set_vector(daecpp_b200_ctx *ctx, int32_t which, const double *host);
+/* Counters and timings.  Keys: "n_symbolic", "n_refactor", "n_solve", "n_fronts", "n_levels",
+ * "nnz_factor", "factor_flops", "max_front", "ms_symbolic", "ms_last_refactor", "ms_last_solve",
+ * "kernels_launched", "n_cold_assembly" ... returns EINVAL for an unknown key. */
+int daecpp_b200_get_stat(daecpp_b200_ctx *ctx, const char *key, double *value);
+/* Tunables, by name ("refine_steps", "pivot_tol", "leaf_size", "use_graph" ...). */
+int daecpp_b200_set_option(daecpp_b200_ctx *ctx, const char *key, double value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DAECPP_B200_H */

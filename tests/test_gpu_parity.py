@@ -1,0 +1,285 @@
+"""GPU parity tests: the CUDA path behind the C ABI against the oracle on the same inputs.
+
+Bars:
+  assembly / residual / update / history : bit-exact (bytes compared)
+  linear solve : normwise backward error <= 1e-12 and ||r||_2 <= 10 ||r_eigen||_2 + 1e-12 ||b||_2
+"""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import problems as P
+from gpu_lib import binding as B
+
+pytestmark = pytest.mark.gpu
+
+EMPTY = (np.zeros(0), np.zeros(0, np.int32), np.zeros(0, np.int32))
+
+
+def same(a, b):
+    return all(u.tobytes() == v.tobytes() for u, v in zip(a, b))
+
+
+def checker():
+    return O.ref if O.ref is not None else O.port
+
+
+# ---------------------------------------------------------------- assembly (a3, a6)
+@pytest.mark.parametrize("seed,n", [(0, 1), (1, 7), (2, 100), (3, 1000), (4, 20000), (5, 200000)])
+def test_assembly_random_duplicates_bit_exact(seed, n):
+    J = P.random_triplets(n, 6 * n + 3, seed)
+    M = P.random_triplets(n, n // 2 + 1, 100 + seed)
+    alpha = 123.456 / (seed + 1)
+    c = B.Context(n)
+    c.set_mass(M); c.set_jacobian(J)
+    assert same(c.get_csc(0), O.convert(O.port, n, M))
+    assert same(c.get_csc(1), O.convert(O.port, n, J))
+    # symbolic+numeric run too; a random matrix may be singular for static pivoting -> only the
+    # assembled Jb is compared here
+    c.refactor(alpha, allow=(B.EDECOMP,))
+    assert same(c.get_csc(2), O.assemble_jb(checker(), n, J, M, alpha))
+    c.close()
+
+
+def test_assembly_edge_cases_bit_exact():
+    n = 5
+    J = (np.array([1.0, 0.0, -3.0, 3.0, -0.0]), np.array([1, 4, 2, 2, 3], np.int32), np.array([0, 4, 2, 2, 3], np.int32))
+    M = P.identity_mass(n)
+    for jj, mm in [(J, M), (EMPTY, M), (J, EMPTY), (M, M), (EMPTY, EMPTY)]:
+        c = B.Context(n)
+        c.set_mass(mm); c.set_jacobian(jj)
+        c.refactor(7.0, allow=(B.EDECOMP,))
+        assert same(c.get_csc(2), O.assemble_jb(checker(), n, jj, mm, 7.0))
+        c.close()
+
+
+def test_assembly_cached_pattern_hot_path():
+    N = 400
+    c = B.Context(2 * N)
+    M = P.perovskite_mass(N)
+    c.set_mass(M)
+    for k in range(4):
+        x = P.perovskite_state(N, seed=k)
+        J = P.perovskite_jacobian(x, N)
+        c.set_jacobian(J)
+        c.refactor(10.0 * (k + 1))
+        assert same(c.get_csc(2), O.assemble_jb(checker(), 2 * N, J, M, 10.0 * (k + 1)))
+    assert c.stat("n_cold_assembly") == 2  # one for M, one for J; later calls reuse the pattern
+    assert c.stat("n_symbolic") == 1
+    # a different pattern of the same length must be detected and re-sorted
+    A, i, j = P.perovskite_jacobian(x, N)
+    i = i.copy(); j = j.copy(); i[5], j[5] = 7, 300
+    c.set_jacobian((A, i, j))
+    c.refactor(3.0, allow=(B.EDECOMP,))
+    assert c.stat("n_cold_assembly") == 3 and c.stat("n_symbolic") == 2
+    assert same(c.get_csc(2), O.assemble_jb(checker(), 2 * N, (A, i, j), M, 3.0))
+    c.close()
+
+
+def test_index_out_of_range_is_reported():
+    c = B.Context(4)
+    T = (np.ones(3), np.array([0, 4, 1], np.int32), np.array([0, 1, 1], np.int32))
+    assert c.set_jacobian(T, allow=(B.EINDEX,)) == B.EINDEX
+    T = (np.ones(3), np.array([0, 3, 1], np.int32), np.array([0, -1, 1], np.int32))
+    assert c.set_mass(T, allow=(B.EINDEX,)) == B.EINDEX
+    c.close()
+
+
+# ---------------------------------------------------------------- residual (a4, a5)
+@pytest.mark.parametrize("order", [1, 2, 3, 4])
+def test_residual_bit_exact(order):
+    r = np.random.default_rng(order)
+    n = 5000
+    M = P.random_triplets(n, 3 * n, 7)
+    c = B.Context(n)
+    c.set_mass(M)
+    hist = [r.standard_normal(n) for _ in range(5)]  # xk, x[0..3]
+    c.set_vector("xk", hist[0])
+    for k in range(4):
+        c.set_vector("x%d" % k, hist[k + 1])
+    dt = r.uniform(0.01, 0.3, 4)
+    f = r.standard_normal(n)
+    alpha = c.residual(f, order, dt)
+    xh = np.concatenate([hist[1], hist[2], hist[3], hist[4]])
+    d = np.zeros(n); b = np.zeros(n)
+    alpha_ref = O.port.oracle_time_derivative(n, order, dt, hist[0], xh, d)
+    O.port.oracle_residual(n, *O.convert(O.port, n, M), d, f, b)
+    assert alpha == alpha_ref
+    assert c.get_vector("dxdt").tobytes() == d.tobytes()
+    assert c.get_vector("b").tobytes() == b.tobytes()
+    c.close()
+
+
+
+
+# ---------------------------------------------------------------- linear solve (a7-a9)
+def _solve_and_check(n, J, M, alpha, b=None):
+    csc = O.assemble_jb(O.port, n, J, M, alpha)
+    b = np.full(n, 1.24) if b is None else b
+    c = B.Context(n)
+    c.set_mass(M); c.set_jacobian(J)
+    c.refactor(alpha)
+    c.set_rhs(b)
+    x = c.solve()
+    stats = {k: c.stat(k) for k in ("n_fronts", "n_levels", "nnz_factor", "max_front", "ms_last_refactor", "ms_last_solve")}
+    c.close()
+    eta, r2 = O.backward_error(n, csc, x, b)
+    assert eta <= 1e-12, (eta, stats)
+    if O.ref is not None and n <= 300000:
+        rc, x_ref, _, _ = O.ref_sparselu(n, csc, b)
+        assert rc == 0
+        _, r2_ref = O.backward_error(n, csc, x_ref, b)
+        assert r2 <= 10.0 * r2_ref + 1e-12 * np.linalg.norm(b), (r2, r2_ref)
+    return x, stats
+
+
+def test_linear_solve_3x3_kat():
+    # /root/reference/tests/test_linear-solver.cpp:26-61 style: per-entry residual <= 1e-15
+    A = np.array([[2.0, -1.0, 0.0], [-1.0, 2.0, -1.0], [0.0, -1.0, 2.0]])
+    ii, jj = np.nonzero(A)
+    b = np.array([1.0, 0.0, 1.0])
+    x, _ = _solve_and_check(3, (A[ii, jj], ii.astype(np.int32), jj.astype(np.int32)), EMPTY, 0.0, b)
+    assert np.max(np.abs(A @ x - b)) <= 1e-15
+
+
+def test_linear_solve_scalar_system():
+    # C1: flame_propagation as shipped is N = 1
+    x, _ = _solve_and_check(1, (np.array([-3.0]), np.zeros(1, np.int32), np.zeros(1, np.int32)),
+                            P.identity_mass(1), 100.0, np.array([2.0]))
+    assert x[0] == 2.0 / (-3.0 - 100.0)
+
+
+@pytest.mark.parametrize("N,alpha", [(500, 100.0), (4000, 100.0), (4000, 1.0), (10000, 1.0)])
+def test_linear_solve_perovskite(N, alpha):
+    # N=10000 mirrors LinearSolver.BigSystem (/root/reference/tests/test_linear-solver.cpp:138-181):
+    # b == 1.24 and per-entry |b - A x| <= 1e-7
+    xs = P.perovskite_state(N)
+    J = P.perovskite_jacobian(xs, N); M = P.perovskite_mass(N)
+    x, stats = _solve_and_check(2 * N, J, M, alpha)
+    csc = O.assemble_jb(O.port, 2 * N, J, M, alpha)
+    _, r2 = O.backward_error(2 * N, csc, x, np.full(2 * N, 1.24))
+    assert r2 / np.sqrt(2 * N) <= 1e-7
+
+
+@pytest.mark.parametrize("n", [2, 3, 10, 1000, 100000])
+def test_linear_solve_flame1d(n):
+    u = P.flame1d_state(n)
+    _solve_and_check(n, P.flame1d_jacobian(u), P.identity_mass(n), 50.0)
+
+
+@pytest.mark.parametrize("m", [4, 33, 128])
+def test_linear_solve_grid2d(m):
+    _solve_and_check(m * m, P.grid2d_probe_matrix(m), EMPTY, 0.0)
+
+
+def test_linear_solve_dense_block_and_disconnected():
+    # two disconnected dense 40x40 blocks plus 20 isolated unknowns
+    r = np.random.default_rng(3)
+    n = 100
+    A = np.zeros((n, n))
+    A[:40, :40] = r.standard_normal((40, 40)) + 40 * np.eye(40)
+    A[40:80, 40:80] = r.standard_normal((40, 40)) + 40 * np.eye(40)
+    A[80:, 80:] = np.diag(r.uniform(1, 2, 20))
+    ii, jj = np.nonzero(A)
+    _solve_and_check(n, (A[ii, jj], ii.astype(np.int32), jj.astype(np.int32)), EMPTY, 0.0, r.standard_normal(n))
+
+
+def test_singular_matrix_reports_decomposition_failure():
+    n = 4
+    T = (np.array([1.0, 1.0, 1.0]), np.array([0, 1, 2], np.int32), np.array([0, 1, 2], np.int32))  # row/col 3 empty
+    c = B.Context(n)
+    c.set_mass(EMPTY); c.set_jacobian(T)
+    assert c.refactor(0.0, allow=(B.EDECOMP,)) == B.EDECOMP
+    c.close()
+
+
+# ---------------------------------------------------------------- update / history (a11, a12)
+def test_update_and_accept_bit_exact():
+    r = np.random.default_rng(0)
+    n = 100003
+    x0 = r.standard_normal(n); x0[::7] = 0.0
+    xk = x0 + 1e-3 * r.standard_normal(n)
+    dx = 1e-7 * r.standard_normal(n) * 10.0 ** r.integers(-3, 3, n)
+    # plant dx as the solution of I * dx = b
+    c = B.Context(n)
+    c.set_mass(EMPTY); c.set_jacobian(P.identity_mass(n)); c.refactor(0.0)
+    for atol, rtol in [(1e-6, 1e-6), (1e-3, 1e-1), (1.0, 1e9)]:
+        c.set_vector("xk", xk); c.set_vector("x0", x0); c.set_vector("b", dx)
+        rc, flags = c.solve_update(atol, rtol)
+        xk_ref = xk.copy()
+        f_ref = O.port.oracle_error_check_update(n, dx, x0, xk_ref, atol, rtol, 1e100)
+        assert rc == 0 and flags == f_ref
+        assert c.get_xk().tobytes() == xk_ref.tobytes()
+    dx2 = dx.copy(); dx2[n // 2] = np.nan
+    c.set_vector("xk", xk); c.set_vector("b", dx2)
+    rc, flags = c.solve_update(1e-6, 1e-6)
+    assert flags & B.DIVERGED
+    dx2[n // 2] = 1e101
+    c.set_vector("xk", xk); c.set_vector("b", dx2)
+    assert c.solve_update(1e-6, 1e-6)[1] & B.DIVERGED
+    # rollback restores xk = x[0]
+    c.rollback()
+    assert c.get_xk().tobytes() == x0.tobytes()
+    # history shift + variability
+    hist = [r.standard_normal(n) for _ in range(4)]
+    for k in range(4):
+        c.set_vector("x%d" % k, hist[k])
+    c.set_vector("xk", xk)
+    v = c.accept_step(True, 1e-4)
+    xh = np.concatenate(hist)
+    v_ref = O.port.oracle_accept_step(n, xk, xh, 1, 1e-4)
+    assert v == v_ref
+    for k in range(4):
+        assert c.get_vector("x%d" % k).tobytes() == xh[k * n:(k + 1) * n].tobytes()
+    assert c.accept_step(False, 1e-4) == 0.0
+    c.close()
+
+
+# ---------------------------------------------------------------- one BDF step end to end
+def test_newton_iterations_perovskite_vs_oracle():
+    """Three quasi-Newton iterations of the first BDF-1 step of C2 (N reduced): the device
+    pipeline (set_jacobian -> residual -> refactor -> solve_update) against the same sequence
+    done with the oracle; b is bit-exact, dx within the linear-solve bar."""
+    N = 300; n = 2 * N
+    x0 = np.concatenate([np.ones(N), np.zeros(N)])
+    M = P.perovskite_mass(N)
+    dt = np.array([0.01, 0, 0, 0.0]); t = 0.01
+
+    def rhs(x):
+        h = 1.0 / (N - 1); invh2 = 1.0 / (h * h)
+        f = np.zeros(n); Pc = x[:N]; Ph = x[N:]
+        f[1:N - 1] = (Pc[2:] - 2 * Pc[1:-1] + Pc[:-2] + 0.5 * ((Pc[2:] + Pc[1:-1]) * (Ph[2:] - Ph[1:-1]) -
+                      (Pc[1:-1] + Pc[:-2]) * (Ph[1:-1] - Ph[:-2]))) * invh2
+        f[0] = (Pc[1] - Pc[0] + 0.5 * (Pc[1] + Pc[0]) * (Ph[1] - Ph[0])) * invh2
+        f[N - 1] = -(Pc[-1] - Pc[-2] + 0.5 * (Pc[-1] + Pc[-2]) * (Ph[-1] - Ph[-2])) * invh2
+        f[N + 1:n - 1] = (Ph[2:] - 2 * Ph[1:-1] + Ph[:-2]) * invh2 - (1.0 - Pc[1:-1])
+        f[N] = Ph[0] + t; f[n - 1] = Ph[-1] - t
+        return f
+
+    c = B.Context(n)
+    c.set_state(x0); c.set_mass(M)
+    xk_ref = x0.copy(); xh = np.concatenate([x0, np.zeros(3 * n)])
+    mcsc = O.convert(O.port, n, M)
+    for it in range(3):
+        xk = c.get_xk()
+        assert np.max(np.abs(xk - xk_ref)) <= 1e-9 * max(1.0, np.max(np.abs(xk_ref)))
+        f = rhs(xk)
+        alpha = c.residual(f, 1, dt)
+        d = np.zeros(n); b_ref = np.zeros(n)
+        assert alpha == O.port.oracle_time_derivative(n, 1, dt, xk, xh, d)
+        O.port.oracle_residual(n, *mcsc, d, f, b_ref)
+        assert c.get_vector("b").tobytes() == b_ref.tobytes()
+        J = P.perovskite_jacobian(xk, N)
+        c.set_jacobian(J); c.refactor(alpha)
+        csc = O.assemble_jb(O.port, n, J, M, alpha)
+        assert same(c.get_csc(2), csc)
+        rc, flags = c.solve_update(1e-6, 1e-6)
+        dx = c.get_vector("dx")
+        eta, _ = O.backward_error(n, csc, dx, b_ref)
+        assert rc == 0 and eta <= 1e-12
+        dx_ref = np.zeros(n)
+        assert O.port.oracle_lu_solve(n, *csc, b_ref, dx_ref) == 0
+        assert np.max(np.abs(dx - dx_ref)) <= 1e-8 * max(np.max(np.abs(dx_ref)), 1e-300)
+        xk_ref = xk.copy()
+        O.port.oracle_error_check_update(n, dx, x0, xk_ref, 1e-6, 1e-6, 1e100)
+    c.close()

@@ -15,7 +15,15 @@ def test_port_loaded():
 
 # --- literals from /root/reference/tests/test_sparse-matrix.cpp:183-229 (convert, duplicates)
 def test_convert_kat_duplicates_summed():
-    # M(0,1,1.0) M(1,0,2.5) M(1,0,2.5)?  The reference test sums 2.5+2.5 = 5.0 in one slot.
+    # M2 of the reference test: (0,0,-5.0) (1,1,2.5) (1,1,2.5) -> dense [[-5,0],[0,5]]
+    A = np.array([-5.0, 2.5, 2.5]); i = np.array([0, 1, 1], np.int32); j = np.array([0, 1, 1], np.int32)
+    outer, inner, vals = O.convert(O.port, 2, (A, i, j))
+    assert outer.tolist() == [0, 1, 2] and inner.tolist() == [0, 1] and vals.tolist() == [-5.0, 5.0]
+    # M1 of the reference test: full 2x2 given row by row -> column-major storage
+    A = np.array([1.0, 2.0, 3.0, 4.0]); i = np.array([0, 0, 1, 1], np.int32); j = np.array([0, 1, 0, 1], np.int32)
+    outer, inner, vals = O.convert(O.port, 2, (A, i, j))
+    assert outer.tolist() == [0, 2, 4] and inner.tolist() == [0, 1, 0, 1] and vals.tolist() == [1.0, 3.0, 2.0, 4.0]
+    # out-of-order + duplicate mix
     A = np.array([1.0, 2.0, 2.5, 2.5, 4.0]); i = np.array([0, 1, 2, 2, 0], np.int32); j = np.array([0, 1, 2, 2, 2], np.int32)
     outer, inner, vals = O.convert(O.port, 3, (A, i, j))
     assert outer.tolist() == [0, 1, 2, 4]
