@@ -249,6 +249,7 @@ int daecpp_b200_refactor(daecpp_b200_ctx *c, double alpha)
     cudaSetDevice(c->device);
     int rc = build_union(c);
     if (rc) return rc;
+    if (c->assemble_only) return assemble_values_only(c, alpha);
     if (!c->have_symbolic && (rc = upload_symbolic(c))) return rc;
     return numeric_refactor(c, alpha);
 }
@@ -414,6 +415,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     const std::string k(key);
     if (k == "refine_steps") c->refine_steps = (int)value;
     else if (k == "pivot_tol") c->pivot_tol = value;
+    else if (k == "assemble_only") c->assemble_only = value != 0.0;
     else if (k == "leaf_size") { c->sopt.leaf_size = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "max_super") { c->sopt.max_super = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else return fail(c, DAECPP_B200_EINVAL, "unknown option key");

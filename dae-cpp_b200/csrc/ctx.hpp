@@ -124,6 +124,7 @@ struct daecpp_b200_ctx
 
     // options
     int refine_steps = 0;
+    bool assemble_only = false;
     double pivot_tol = 0.0;
 
     // statistics
@@ -153,6 +154,7 @@ int build_mass_csr(daecpp_b200_ctx *c);
 // numeric.cu
 int upload_symbolic(daecpp_b200_ctx *c);
 int numeric_refactor(daecpp_b200_ctx *c, double alpha);
+int assemble_values_only(daecpp_b200_ctx *c, double alpha);
 int numeric_solve(daecpp_b200_ctx *c); // b -> dx
 // vector_ops.cu
 int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5]);

@@ -67,7 +67,7 @@ __global__ void k_scatter(int64_t nnzU, const int32_t *__restrict__ uJ, const in
     }
     else
         v = uvals[u];
-    LU[dest[u]] = v;
+    if (LU) LU[dest[u]] = v;
 }
 
 template <int G>
@@ -325,6 +325,21 @@ int upload_symbolic(daecpp_b200_ctx *c)
     c->have_factor = false;
     c->n_symbolic += 1;
     c->ms_symbolic = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return DAECPP_B200_OK;
+}
+
+// Only the values of Jb = J - (M*alpha) on the union pattern (parity export, no factorisation).
+int assemble_values_only(daecpp_b200_ctx *c, double alpha)
+{
+    if (c->nnzU && !c->direct_csc)
+    {
+        k_scatter<<<(int)((c->nnzU + 255) / 256), 256, 0, c->stream>>>(c->nnzU, c->u_J.p, c->u_M.p, c->J.vals.p, c->M.vals.p,
+                                                                      alpha, c->u_vals.p, nullptr, nullptr);
+        c->kernels += 1;
+        DAECPP_CUDA_TRY(c, cudaGetLastError());
+    }
+    c->n_refactor += 1;
+    c->have_factor = false;
     return DAECPP_B200_OK;
 }
 

@@ -87,6 +87,7 @@ __global__ void k_accept(int32_t n, const double *__restrict__ xk, const double 
         {
             const double p = x0_old[i];
             if (fabs(p) > tol && fabs(a) > tol) v = fabs(__ddiv_rn(__dsub_rn(p, a), p));
+            if (!(v == v)) v = 0.0; // the reference's `rel_change > variability` ignores NaN
         }
     }
     if (!variability_on) return;

@@ -34,9 +34,10 @@ def test_assembly_random_duplicates_bit_exact(seed, n):
     c.set_mass(M); c.set_jacobian(J)
     assert same(c.get_csc(0), O.convert(O.port, n, M))
     assert same(c.get_csc(1), O.convert(O.port, n, J))
-    # symbolic+numeric run too; a random matrix may be singular for static pivoting -> only the
-    # assembled Jb is compared here
-    c.refactor(alpha, allow=(B.EDECOMP,))
+    # a random sparsity pattern has no small separators (catastrophic fill for any direct
+    # solver), so only the assembly stage of refactor runs here
+    c.set_option("assemble_only", 1)
+    c.refactor(alpha)
     assert same(c.get_csc(2), O.assemble_jb(checker(), n, J, M, alpha))
     c.close()
 
