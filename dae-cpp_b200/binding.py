@@ -23,7 +23,7 @@ SYMBOLS = [
     "daecpp_b200_rollback", "daecpp_b200_set_mass", "daecpp_b200_set_jacobian", "daecpp_b200_residual",
     "daecpp_b200_refactor", "daecpp_b200_solve_update", "daecpp_b200_accept_step", "daecpp_b200_set_rhs",
     "daecpp_b200_solve", "daecpp_b200_get_csc", "daecpp_b200_get_vector", "daecpp_b200_set_vector", "daecpp_b200_get_stat",
-    "daecpp_b200_set_option",
+    "daecpp_b200_set_option", "daecpp_b200_iteration_resident", "daecpp_b200_event_mark", "daecpp_b200_event_elapsed_ms",
 ]
 
 
@@ -57,6 +57,10 @@ def load():
     lib.daecpp_b200_set_vector.argtypes = [_vp, C.c_int32, _f64]
     lib.daecpp_b200_get_stat.argtypes = [_vp, C.c_char_p, C.POINTER(C.c_double)]
     lib.daecpp_b200_set_option.argtypes = [_vp, C.c_char_p, C.c_double]
+    lib.daecpp_b200_iteration_resident.argtypes = [_vp, C.c_int32, C.c_int32, _f64, C.c_double, C.c_double, C.c_double,
+                                                   C.POINTER(C.c_int32)]
+    lib.daecpp_b200_event_mark.argtypes = [_vp]
+    lib.daecpp_b200_event_elapsed_ms.argtypes = [_vp, C.POINTER(C.c_double)]
     return lib
 
 
@@ -156,6 +160,21 @@ class Context:
         flags = C.c_int32(0)
         rc = self._ck(self.lib.daecpp_b200_solve_update(self.h, atol, rtol, max_err_abs, C.byref(flags)), allow)
         return rc, flags.value
+
+    def iteration_resident(self, do_refactor, order, dt4, atol, rtol, max_err_abs=1e100, allow=()):
+        flags = C.c_int32(0)
+        rc = self._ck(self.lib.daecpp_b200_iteration_resident(self.h, int(do_refactor), order,
+                                                              np.ascontiguousarray(dt4, np.float64), atol, rtol,
+                                                              max_err_abs, C.byref(flags)), allow)
+        return rc, flags.value
+
+    def event_mark(self):
+        self._ck(self.lib.daecpp_b200_event_mark(self.h))
+
+    def event_elapsed_ms(self):
+        ms = C.c_double(0)
+        self._ck(self.lib.daecpp_b200_event_elapsed_ms(self.h, C.byref(ms)))
+        return ms.value
 
     def accept_step(self, variability_on=True, tol=1e-4):
         v = C.c_double(0)

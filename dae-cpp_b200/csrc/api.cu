@@ -124,6 +124,9 @@ int daecpp_b200_create(int32_t n, int device, daecpp_b200_ctx **out)
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreate(&c->ev_mark)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    for (int k = 0; k < 6; ++k)
+        if ((e = cudaEventCreate(&c->pev[k])) != cudaSuccess) return bail(e, "cudaEventCreate");
     double *slab = nullptr;
     const size_t nv = 10; // xk, x[0..3], f, b, dx, work, dxdt
     if ((e = cudaMalloc((void **)&slab, sizeof(double) * nv * (size_t)n)) != cudaSuccess) return bail(e, "cudaMalloc(state)");
@@ -161,6 +164,8 @@ void daecpp_b200_destroy(daecpp_b200_ctx *c)
     if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ev_mark) cudaEventDestroy(c->ev_mark);
+    for (int k = 0; k < 6; ++k) if (c->pev[k]) cudaEventDestroy(c->pev[k]);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -293,6 +298,73 @@ int daecpp_b200_accept_step(daecpp_b200_ctx *c, int32_t variability_on, double t
     return DAECPP_B200_OK;
 }
 
+int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int32_t order, const double dt[4],
+                                   double atol, double rtol, double max_err_abs, int32_t *flags)
+{
+    if (!c || !dt || !flags) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->M.have_pattern || !c->J.have_pattern) return fail(c, DAECPP_B200_EINVAL, "set_mass/set_jacobian must precede");
+    double w[5];
+    if (!bdf_weights(order, dt, w)) return fail(c, DAECPP_B200_EINVAL, "unsupported time integration order");
+    int rc = build_union(c);
+    if (rc) return rc;
+    if (!c->have_symbolic && (rc = upload_symbolic(c))) return rc;
+    if (!do_refactor && !c->have_factor) return fail(c, DAECPP_B200_EINVAL, "no valid factorisation");
+    cudaStream_t st = c->stream;
+    const bool pt = c->phase_timing;
+    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, sizeof(int32_t), st));
+    if (pt) cudaEventRecord(c->pev[0], st);
+    if (do_refactor && (rc = regather_values(c, c->J))) return rc;
+    if (pt) cudaEventRecord(c->pev[1], st);
+    if ((rc = launch_residual(c, order, w))) return rc;
+    if (pt) cudaEventRecord(c->pev[2], st);
+    if (do_refactor && (rc = numeric_refactor_async(c, w[0]))) return rc;
+    if (pt) cudaEventRecord(c->pev[3], st);
+    if ((rc = numeric_solve(c))) return rc;
+    if (pt) cudaEventRecord(c->pev[4], st);
+    if ((rc = launch_update(c, atol, rtol, max_err_abs))) return rc;
+    if (pt) cudaEventRecord(c->pev[5], st);
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
+    if (pt)
+    {
+        for (int k = 0; k < 5; ++k)
+        {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, c->pev[k], c->pev[k + 1]);
+            c->ms_phase[k] += ms;
+        }
+        c->n_phase_samples += 1;
+    }
+    *flags = c->h_flags[2];
+    if (do_refactor)
+    {
+        c->have_factor = c->h_flags[3] == 0;
+        if (!c->have_factor) return DAECPP_B200_EDECOMP;
+    }
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_event_mark(daecpp_b200_ctx *c)
+{
+    if (!c) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev_mark, c->stream));
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_event_elapsed_ms(daecpp_b200_ctx *c, double *ms_out)
+{
+    if (!c || !ms_out) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev1, c->stream));
+    DAECPP_CUDA_TRY(c, cudaEventSynchronize(c->ev1));
+    float ms = 0;
+    DAECPP_CUDA_TRY(c, cudaEventElapsedTime(&ms, c->ev_mark, c->ev1));
+    *ms_out = ms;
+    return DAECPP_B200_OK;
+}
+
 int daecpp_b200_set_rhs(daecpp_b200_ctx *c, const double *b_host)
 {
     if (!c || !b_host) return DAECPP_B200_EINVAL;
@@ -405,6 +477,13 @@ int daecpp_b200_get_stat(daecpp_b200_ctx *c, const char *key, double *value)
     else if (k == "cb_doubles") *value = (double)c->S.cb_size;
     else if (k == "nnz_jb") *value = (double)c->nnzU;
     else if (k == "n_missing_diag") *value = c->S.n_missing_diag;
+    else if (k == "ms_phase_assembly") *value = c->n_phase_samples ? c->ms_phase[0] / c->n_phase_samples : 0;
+    else if (k == "ms_phase_residual") *value = c->n_phase_samples ? c->ms_phase[1] / c->n_phase_samples : 0;
+    else if (k == "ms_phase_refactor") *value = c->n_phase_samples ? c->ms_phase[2] / c->n_phase_samples : 0;
+    else if (k == "ms_phase_solve") *value = c->n_phase_samples ? c->ms_phase[3] / c->n_phase_samples : 0;
+    else if (k == "ms_phase_update") *value = c->n_phase_samples ? c->ms_phase[4] / c->n_phase_samples : 0;
+    else if (k == "n_phase_samples") *value = c->n_phase_samples;
+    else if (k == "upd_doubles") *value = (double)c->S.upd_size;
     else return fail(c, DAECPP_B200_EINVAL, "unknown stat key");
     return DAECPP_B200_OK;
 }
@@ -416,6 +495,12 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     if (k == "refine_steps") c->refine_steps = (int)value;
     else if (k == "pivot_tol") c->pivot_tol = value;
     else if (k == "assemble_only") c->assemble_only = value != 0.0;
+    else if (k == "phase_timing")
+    {
+        c->phase_timing = value != 0.0;
+        for (int q = 0; q < 5; ++q) c->ms_phase[q] = 0;
+        c->n_phase_samples = 0;
+    }
     else if (k == "leaf_size") { c->sopt.leaf_size = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "max_super") { c->sopt.max_super = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else return fail(c, DAECPP_B200_EINVAL, "unknown option key");

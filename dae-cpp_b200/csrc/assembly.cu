@@ -246,6 +246,17 @@ int assemble_triplets(daecpp_b200_ctx *c, TripletSet &T, const double *A, const 
     return DAECPP_B200_OK;
 }
 
+int regather_values(daecpp_b200_ctx *c, TripletSet &T)
+{
+    if (!T.have_pattern) { c->err = "no cached pattern to re-gather"; return DAECPP_B200_EINVAL; }
+    if (T.nnz == 0) return DAECPP_B200_OK;
+    if (T.no_duplicates) k_gather_nodup<<<blocks_for(T.nnz), TPB, 0, c->stream>>>(T.A.p, T.src.p, T.nnz, T.vals.p);
+    else k_gather_sum<<<blocks_for(T.nnz), TPB, 0, c->stream>>>(T.A.p, T.src.p, T.src_ptr.p, T.nnz, T.vals.p);
+    c->kernels += 1;
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    return DAECPP_B200_OK;
+}
+
 // Pattern of Jb = pattern(J) U pattern(M), slot maps u_J / u_M (-1 where absent).
 int build_union(daecpp_b200_ctx *c)
 {

@@ -130,7 +130,13 @@ struct daecpp_b200_ctx
     // statistics
     double n_symbolic = 0, n_refactor = 0, n_solve = 0, n_cold = 0, kernels = 0;
     double ms_symbolic = 0, ms_last_refactor = 0, ms_last_solve = 0;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mark = nullptr;
+    // per-phase device times of iteration_resident (option "phase_timing"):
+    // 0 assembly, 1 residual, 2 refactor, 3 solve, 4 update
+    bool phase_timing = false;
+    cudaEvent_t pev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    double ms_phase[5] = {0, 0, 0, 0, 0};
+    double n_phase_samples = 0;
 };
 
 #define DAECPP_CUDA_TRY(ctx, call)                                                                        \
@@ -151,9 +157,11 @@ int assemble_triplets(daecpp_b200_ctx *c, TripletSet &T, const double *A, const 
                       int64_t nT);
 int build_union(daecpp_b200_ctx *c);
 int build_mass_csr(daecpp_b200_ctx *c);
+int regather_values(daecpp_b200_ctx *c, TripletSet &T); // hot path on the resident staging values, async
 // numeric.cu
 int upload_symbolic(daecpp_b200_ctx *c);
 int numeric_refactor(daecpp_b200_ctx *c, double alpha);
+int numeric_refactor_async(daecpp_b200_ctx *c, double alpha); // enqueue only; pivot flag left in d_flags[3]
 int assemble_values_only(daecpp_b200_ctx *c, double alpha);
 int numeric_solve(daecpp_b200_ctx *c); // b -> dx
 // vector_ops.cu

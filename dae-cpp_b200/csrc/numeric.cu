@@ -343,12 +343,11 @@ int assemble_values_only(daecpp_b200_ctx *c, double alpha)
     return DAECPP_B200_OK;
 }
 
-int numeric_refactor(daecpp_b200_ctx *c, double alpha)
+int numeric_refactor_async(daecpp_b200_ctx *c, double alpha)
 {
     cudaStream_t st = c->stream;
     Symbolic &S = c->S;
     FrontTables T = tables(c);
-    DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev0, st));
     DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->LU.p, 0, sizeof(double) * (size_t)S.lu_size, st));
     DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 3, 0, sizeof(int32_t), st));
     if (c->nnzU)
@@ -367,14 +366,23 @@ int numeric_refactor(daecpp_b200_ctx *c, double alpha)
         c->kernels += 1;
     }
     DAECPP_CUDA_TRY(c, cudaGetLastError());
+    c->n_refactor += 1;
+    c->last_alpha = alpha;
+    return DAECPP_B200_OK;
+}
+
+int numeric_refactor(daecpp_b200_ctx *c, double alpha)
+{
+    cudaStream_t st = c->stream;
+    DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev0, st));
+    int rc = numeric_refactor_async(c, alpha);
+    if (rc) return rc;
     DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev1, st));
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 3, c->d_flags + 3, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     c->ms_last_refactor = ms;
-    c->n_refactor += 1;
-    c->last_alpha = alpha;
     if (c->h_flags[3])
     {
         c->have_factor = false;

@@ -94,6 +94,19 @@ int daecpp_b200_solve_update(daecpp_b200_ctx *ctx, double atol, double rtol, dou
 int daecpp_b200_accept_step(daecpp_b200_ctx *ctx, int32_t variability_on, double variability_tolerance,
                             double *variability_out);
 
+/* ---- one whole Newton iteration on data already resident in HBM -------------------------
+ * The device part of solver.hpp:431-627 in one submission, with no host<->device copy except
+ * the flag word: re-assemble J from the triplet VALUES of the last set_jacobian upload (cached
+ * pattern), b = M*dxdt - f from the f of the last residual upload, then (do_refactor != 0)
+ * Jb = J - alpha*M and the numeric refactorisation, the triangular solves, error checks and
+ * xk += dx.  This is the quantity SURVEY.md 8(d) times ("triplet values resident in HBM" ->
+ * "dx applied, flags ready"); bench.py's `value` is measured through it. */
+int daecpp_b200_iteration_resident(daecpp_b200_ctx *ctx, int32_t do_refactor, int32_t order, const double dt[4],
+                                   double atol, double rtol, double max_err_abs, int32_t *flags);
+/* CUDA-event stopwatch on the context's stream (torch.cuda.Event cannot see this stream). */
+int daecpp_b200_event_mark(daecpp_b200_ctx *ctx);
+int daecpp_b200_event_elapsed_ms(daecpp_b200_ctx *ctx, double *ms); /* synchronises the stream */
+
 /* ---- linear-solver-only entry points (what Eigen::SparseLU::compute/solve expose,
  *      Eigen/src/SparseLU/SparseLU.h:210-215,338-358; used by tests/test_linear-solver.cpp) ---- */
 int daecpp_b200_set_rhs(daecpp_b200_ctx *ctx, const double *b_host); /* b (device) = b_host */
