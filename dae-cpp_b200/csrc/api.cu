@@ -214,7 +214,7 @@ int daecpp_b200_set_mass(daecpp_b200_ctx *c, const double *A, const int32_t *i, 
 {
     if (!c) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
-    int rc = assemble_triplets(c, c->M, A, i, j, nT);
+    int rc = assemble_triplets(c, c->M, A, i, j, nT, false);
     if (rc) return rc;
     return build_mass_csr(c);
 }
@@ -224,7 +224,7 @@ int daecpp_b200_set_jacobian(daecpp_b200_ctx *c, const double *A, const int32_t 
     if (!c) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
     c->direct_csc = false;
-    return assemble_triplets(c, c->J, A, i, j, nT);
+    return assemble_triplets(c, c->J, A, i, j, nT, true);
 }
 
 int daecpp_b200_residual(daecpp_b200_ctx *c, const double *f_host, int32_t order, const double dt[4], double *alpha_out)
@@ -266,17 +266,17 @@ int daecpp_b200_solve_update(daecpp_b200_ctx *c, double atol, double rtol, doubl
     if (!c->have_factor) return fail(c, DAECPP_B200_EINVAL, "no valid factorisation");
     DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev0, c->stream));
     DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, sizeof(int32_t), c->stream));
-    int rc = numeric_solve(c);
-    if (rc) return rc;
-    rc = launch_update(c, atol, rtol, max_err_abs);
+    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 4, 0, sizeof(int32_t), c->stream));
+    int rc = numeric_solve(c, true, atol, rtol, max_err_abs);
     if (rc) return rc;
     DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev1, c->stream));
-    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     c->ms_last_solve = ms;
     *flags = c->h_flags[2];
+    if (c->h_flags[4]) return fail(c, DAECPP_B200_ECUDA, "unit dependency wait timed out");
     return DAECPP_B200_OK;
 }
 
@@ -313,18 +313,21 @@ int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int3
     cudaStream_t st = c->stream;
     const bool pt = c->phase_timing;
     DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, sizeof(int32_t), st));
+    // the triplet values are resident: the Jacobian's compressed-column values (if anything
+    // still needs them) are stale from here on
+    if (do_refactor) c->J.vals_valid = false;
     if (pt) cudaEventRecord(c->pev[0], st);
-    if (do_refactor && (rc = regather_values(c, c->J))) return rc;
+    if (do_refactor && !c->jvals_from_triplets && (rc = ensure_csc_values(c, c->J))) return rc; // duplicate-summing path
     if (pt) cudaEventRecord(c->pev[1], st);
     if ((rc = launch_residual(c, order, w))) return rc;
     if (pt) cudaEventRecord(c->pev[2], st);
     if (do_refactor && (rc = numeric_refactor_async(c, w[0]))) return rc;
+    if (!do_refactor) DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 3, 0, 2 * sizeof(int32_t), st));
     if (pt) cudaEventRecord(c->pev[3], st);
-    if ((rc = numeric_solve(c))) return rc;
+    if ((rc = numeric_solve(c, true, atol, rtol, max_err_abs))) return rc;
     if (pt) cudaEventRecord(c->pev[4], st);
-    if ((rc = launch_update(c, atol, rtol, max_err_abs))) return rc;
     if (pt) cudaEventRecord(c->pev[5], st);
-    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
     if (pt)
     {
@@ -337,6 +340,7 @@ int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int3
         c->n_phase_samples += 1;
     }
     *flags = c->h_flags[2];
+    if (c->h_flags[4]) return fail(c, DAECPP_B200_ECUDA, "unit dependency wait timed out");
     if (do_refactor)
     {
         c->have_factor = c->h_flags[3] == 0;
@@ -399,11 +403,15 @@ int daecpp_b200_get_csc(daecpp_b200_ctx *c, int32_t which, int32_t *outer, int32
     {
         TripletSet &T = which == 0 ? c->M : c->J;
         if (!T.have_pattern) return fail(c, DAECPP_B200_EINVAL, "matrix not set");
+        int rc = ensure_csc_values(c, T);
+        if (rc) return rc;
         d_outer = T.outer.p; d_inner = T.inner.p; d_vals = T.vals.p; nnz = T.nnz;
     }
     else if (which == 2)
     {
         if (c->n_refactor == 0) return fail(c, DAECPP_B200_EINVAL, "refactor has not run");
+        int rc = jb_values(c, c->last_alpha); // computed on demand: the factorisation assembles straight into the fronts
+        if (rc) return rc;
         d_outer = c->u_outer.p; d_inner = c->u_inner.p; d_vals = c->u_vals.p; nnz = c->nnzU;
     }
     else
@@ -484,6 +492,14 @@ int daecpp_b200_get_stat(daecpp_b200_ctx *c, const char *key, double *value)
     else if (k == "ms_phase_update") *value = c->n_phase_samples ? c->ms_phase[4] / c->n_phase_samples : 0;
     else if (k == "n_phase_samples") *value = c->n_phase_samples;
     else if (k == "upd_doubles") *value = (double)c->S.upd_size;
+    else if (k == "n_units") *value = c->S.nunit;
+    else if (k == "n_big_fronts") *value = c->S.nbig;
+    else if (k == "n_launch_groups") *value = (double)c->S.groups.size();
+    else if (k == "factor_smem_bytes") *value = c->S.factor_smem_bytes;
+    else if (k == "solve_smem_bytes") *value = c->S.solve_smem_bytes;
+    else if (k == "unit_grid_factor") *value = c->unit_grid_factor;
+    else if (k == "unit_grid_solve") *value = c->unit_grid_solve;
+    else if (k == "schedule_bytes") *value = 4.0 * (double)(c->S.blob.size() + 3 * c->S.ent_u.size());
     else return fail(c, DAECPP_B200_EINVAL, "unknown stat key");
     return DAECPP_B200_OK;
 }
@@ -502,6 +518,9 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
         c->n_phase_samples = 0;
     }
     else if (k == "leaf_size") { c->sopt.leaf_size = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "unit_smem_bytes") { c->sopt.unit_smem_bytes = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "serial_dim") { c->sopt.serial_dim = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "unit_threads") { c->unit_threads = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "max_super") { c->sopt.max_super = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else return fail(c, DAECPP_B200_EINVAL, "unknown option key");
     return DAECPP_B200_OK;

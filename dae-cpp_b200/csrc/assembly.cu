@@ -172,7 +172,7 @@ int sort_and_scan(daecpp_b200_ctx *c, int64_t count, int32_t n, int32_t *nseg)
 } // namespace
 
 int assemble_triplets(daecpp_b200_ctx *c, TripletSet &T, const double *A, const int32_t *ti, const int32_t *tj,
-                      int64_t nT)
+                      int64_t nT, bool lazy_vals)
 {
     const int32_t n = c->n;
     cudaStream_t st = c->stream;
@@ -201,9 +201,14 @@ int assemble_triplets(daecpp_b200_ctx *c, TripletSet &T, const double *A, const 
     if (T.have_pattern && T.nT_cached == nT)
     { // optimistic hot path: verify the pattern and gather in the same submission
         k_compare_pattern<<<blocks_for(nT), TPB, 0, st>>>(T.ti.p, T.tj.p, T.ti_cached.p, T.tj_cached.p, nT, c->d_flags);
-        if (T.no_duplicates) k_gather_nodup<<<blocks_for(T.nnz), TPB, 0, st>>>(T.A.p, T.src.p, T.nnz, T.vals.p);
-        else k_gather_sum<<<blocks_for(T.nnz), TPB, 0, st>>>(T.A.p, T.src.p, T.src_ptr.p, T.nnz, T.vals.p);
-        c->kernels += 2;
+        c->kernels += 1;
+        T.vals_valid = false;
+        if (!lazy_vals)
+        { // compressed-column values wanted now (mass matrix: the residual kernel reads them)
+            int rc = regather_values(c, T);
+            if (rc) return rc;
+            T.vals_valid = true;
+        }
         DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags, c->d_flags, sizeof(int32_t) * 4, cudaMemcpyDeviceToHost, st));
         DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
         if (c->h_flags[1] == 0) return DAECPP_B200_OK;
@@ -241,6 +246,7 @@ int assemble_triplets(daecpp_b200_ctx *c, TripletSet &T, const double *A, const 
     c->kernels += 3;
     DAECPP_CUDA_TRY(c, cudaGetLastError());
     T.have_pattern = true;
+    T.vals_valid = true;
     T.nT_cached = nT;
     T.pattern_version++;
     return DAECPP_B200_OK;

@@ -50,6 +50,7 @@ struct TripletSet
     DevBuf<double> vals;     // [nnz]
     int64_t nnz = 0;
     bool no_duplicates = false;
+    bool vals_valid = false; // vals[] reflects the latest upload
     uint64_t pattern_version = 0;
     void release()
     {
@@ -60,22 +61,28 @@ struct TripletSet
 
 struct DeviceSymbolic
 {
-    DevBuf<int32_t> perm, iperm, sn_first, sn_rows, sn_rel, child_ptr, child_idx, level_sn;
+    // global front tables (used by the per-level kernels that handle big fronts)
+    DevBuf<int32_t> perm, iperm, sn_first, sn_rows, sn_rel, child_ptr, child_idx, big_sn;
     DevBuf<int64_t> sn_rowptr, sn_lu, sn_cb;
-    DevBuf<uint32_t> a_dest;
+    // subtree-unit schedule (schedule.hpp)
+    DevBuf<int32_t> blob, unit_blob, ent_u, ent_dst, ent_sj, ent_sm, big_u, big_sj, big_sm;
+    DevBuf<uint32_t> big_dst;
+    DevBuf<int32_t> sync_words; // [0] ticket, [1..nunit] dep counters, [1+nunit..] backward done epochs
     void release()
     {
         perm.release(); iperm.release(); sn_first.release(); sn_rows.release(); sn_rel.release();
-        child_ptr.release(); child_idx.release(); level_sn.release(); sn_rowptr.release(); sn_lu.release();
-        sn_cb.release(); a_dest.release();
+        child_ptr.release(); child_idx.release(); big_sn.release(); sn_rowptr.release(); sn_lu.release();
+        sn_cb.release(); blob.release(); unit_blob.release(); ent_u.release(); ent_dst.release();
+        ent_sj.release(); ent_sm.release(); big_u.release(); big_sj.release(); big_sm.release(); big_dst.release();
+        sync_words.release();
     }
 };
 
-struct LevelLaunch
+struct GroupLaunch
 {
-    int32_t begin = 0, count = 0; // range in level_sn
-    int32_t group = 32;           // threads cooperating on one front
-    int32_t max_dim = 0;
+    int32_t kind = 0, begin = 0, count = 0;
+    int32_t group = 32, max_dim = 0; // kind 1: threads cooperating on one front
+    int32_t grid = 0;                // kind 0: persistent blocks
 };
 
 } // namespace daecpp_b200
@@ -113,7 +120,12 @@ struct daecpp_b200_ctx
     daecpp_b200::SymbolicOptions sopt;
     daecpp_b200::Symbolic S;
     daecpp_b200::DeviceSymbolic dS;
-    std::vector<daecpp_b200::LevelLaunch> levels;
+    std::vector<daecpp_b200::GroupLaunch> groups;
+    uint32_t ticket_base = 0; // value of the ticket word before the next unit launch
+    int32_t solve_epoch = 0;
+    int unit_threads = 128;
+    int unit_grid_factor = 0, unit_grid_solve = 0; // resident blocks (SMs x occupancy)
+    bool jvals_from_triplets = false; // fused assembly reads the staged triplet values directly
     daecpp_b200::DevBuf<double> LU, CB, upd;
     double last_alpha = 0.0;
 
@@ -154,7 +166,7 @@ namespace daecpp_b200
 {
 // assembly.cu
 int assemble_triplets(daecpp_b200_ctx *c, TripletSet &T, const double *A, const int32_t *i, const int32_t *j,
-                      int64_t nT);
+                      int64_t nT, bool lazy_vals);
 int build_union(daecpp_b200_ctx *c);
 int build_mass_csr(daecpp_b200_ctx *c);
 int regather_values(daecpp_b200_ctx *c, TripletSet &T); // hot path on the resident staging values, async
@@ -163,7 +175,18 @@ int upload_symbolic(daecpp_b200_ctx *c);
 int numeric_refactor(daecpp_b200_ctx *c, double alpha);
 int numeric_refactor_async(daecpp_b200_ctx *c, double alpha); // enqueue only; pivot flag left in d_flags[3]
 int assemble_values_only(daecpp_b200_ctx *c, double alpha);
-int numeric_solve(daecpp_b200_ctx *c); // b -> dx
+int numeric_solve(daecpp_b200_ctx *c, bool fuse_update = false, double atol = 0, double rtol = 0,
+                  double max_err_abs = 0); // b -> dx (and, fused, the error checks and xk += dx)
+int ensure_csc_values(daecpp_b200_ctx *c, TripletSet &T); // J.vals / M.vals up to date (parity exports)
+int jb_values(daecpp_b200_ctx *c, double alpha);          // u_vals = J - alpha*M on the union pattern
+// subtree.cu
+int unit_setup(daecpp_b200_ctx *c);
+int compose_entries(daecpp_b200_ctx *c);
+int launch_scatter_big(daecpp_b200_ctx *c, double alpha);
+int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha);
+int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct);
+int launch_unit_backward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, bool update, double atol, double rtol,
+                         double max_err_abs);
 // vector_ops.cu
 int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
 int launch_dxdt(daecpp_b200_ctx *c, int32_t order, const double coef[5]);

@@ -49,25 +49,17 @@ struct Grp
     }
 };
 
-// Jb slot values (bit-exact) and their scatter into the zeroed front storage.
-__global__ void k_scatter(int64_t nnzU, const int32_t *__restrict__ uJ, const int32_t *__restrict__ uM,
-                          const double *__restrict__ jv, const double *__restrict__ mv, double alpha,
-                          double *__restrict__ uvals, const uint32_t *__restrict__ dest, double *__restrict__ LU)
+// Jb slot values on the union pattern, bit-exact with `Jb -= M_*alpha` (solver.hpp:523): parity export.
+__global__ void k_jb_values(int64_t nnzU, const int32_t *__restrict__ uJ, const int32_t *__restrict__ uM,
+                            const double *__restrict__ jv, const double *__restrict__ mv, double alpha,
+                            double *__restrict__ uvals)
 {
     int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (u >= nnzU) return;
-    double v;
-    if (uJ)
-    {
-        const int32_t a = uJ[u], b = uM[u];
-        const double m = (b >= 0) ? __dmul_rn(mv[b], alpha) : 0.0;
-        const double j = (a >= 0) ? jv[a] : 0.0;
-        v = __dsub_rn(j, m);
-        uvals[u] = v;
-    }
-    else
-        v = uvals[u];
-    if (LU) LU[dest[u]] = v;
+    const int32_t a = uJ[u], b = uM[u];
+    const double m = (b >= 0) ? __dmul_rn(mv[b], alpha) : 0.0;
+    const double j = (a >= 0) ? jv[a] : 0.0;
+    uvals[u] = __dsub_rn(j, m);
 }
 
 template <int G>
@@ -238,7 +230,7 @@ FrontTables tables(daecpp_b200_ctx *c)
 {
     FrontTables T;
     T.sn_first = c->dS.sn_first.p; T.sn_rows = c->dS.sn_rows.p; T.sn_rel = c->dS.sn_rel.p;
-    T.child_ptr = c->dS.child_ptr.p; T.child_idx = c->dS.child_idx.p; T.level_sn = c->dS.level_sn.p;
+    T.child_ptr = c->dS.child_ptr.p; T.child_idx = c->dS.child_idx.p; T.level_sn = c->dS.big_sn.p;
     T.sn_rowptr = c->dS.sn_rowptr.p; T.sn_lu = c->dS.sn_lu.p; T.sn_cb = c->dS.sn_cb.p;
     return T;
 }
@@ -271,7 +263,7 @@ int pick_group(int32_t max_dim)
 
 } // namespace
 
-// Download the pattern of Jb, analyse it on the host, ship the tables back.
+// Download the pattern of Jb, analyse it on the host, ship the schedule back.
 int upload_symbolic(daecpp_b200_ctx *c)
 {
     const int32_t n = c->n;
@@ -292,34 +284,48 @@ int upload_symbolic(daecpp_b200_ctx *c)
     int rc;
     if ((rc = upload(c, c->dS.perm, S.perm))) return rc;
     if ((rc = upload(c, c->dS.iperm, S.iperm))) return rc;
-    if ((rc = upload(c, c->dS.sn_first, S.sn_first))) return rc;
-    if ((rc = upload(c, c->dS.sn_rows, S.sn_rows))) return rc;
-    if ((rc = upload(c, c->dS.sn_rel, S.sn_rel))) return rc;
-    if ((rc = upload(c, c->dS.child_ptr, S.child_ptr))) return rc;
-    if ((rc = upload(c, c->dS.child_idx, S.child_idx))) return rc;
-    if ((rc = upload(c, c->dS.level_sn, S.level_sn))) return rc;
-    if ((rc = upload(c, c->dS.sn_rowptr, S.sn_rowptr))) return rc;
-    if ((rc = upload(c, c->dS.sn_lu, S.sn_lu))) return rc;
-    if ((rc = upload(c, c->dS.sn_cb, S.sn_cb))) return rc;
-    if ((rc = upload(c, c->dS.a_dest, S.a_dest))) return rc;
+    if (S.nbig)
+    { // the global front tables are only read by the per-level kernels of big fronts
+        if ((rc = upload(c, c->dS.sn_first, S.sn_first))) return rc;
+        if ((rc = upload(c, c->dS.sn_rows, S.sn_rows))) return rc;
+        if ((rc = upload(c, c->dS.sn_rel, S.sn_rel))) return rc;
+        if ((rc = upload(c, c->dS.child_ptr, S.child_ptr))) return rc;
+        if ((rc = upload(c, c->dS.child_idx, S.child_idx))) return rc;
+        if ((rc = upload(c, c->dS.big_sn, S.big_sn))) return rc;
+        if ((rc = upload(c, c->dS.sn_rowptr, S.sn_rowptr))) return rc;
+        if ((rc = upload(c, c->dS.sn_lu, S.sn_lu))) return rc;
+        if ((rc = upload(c, c->dS.sn_cb, S.sn_cb))) return rc;
+        if ((rc = upload(c, c->dS.big_u, S.big_u))) return rc;
+        if ((rc = upload(c, c->dS.big_dst, S.big_dst))) return rc;
+        DAECPP_CUDA_TRY(c, c->dS.big_sj.reserve(S.big_u.size() + 1));
+        DAECPP_CUDA_TRY(c, c->dS.big_sm.reserve(S.big_u.size() + 1));
+    }
+    if ((rc = upload(c, c->dS.blob, S.blob))) return rc;
+    if ((rc = upload(c, c->dS.unit_blob, S.unit_blob))) return rc;
+    if ((rc = upload(c, c->dS.ent_u, S.ent_u))) return rc;
+    if ((rc = upload(c, c->dS.ent_dst, S.ent_dst))) return rc;
+    DAECPP_CUDA_TRY(c, c->dS.ent_sj.reserve(S.ent_u.size() + 1));
+    DAECPP_CUDA_TRY(c, c->dS.ent_sm.reserve(S.ent_u.size() + 1));
+    const size_t nsync = 1 + 2 * (size_t)S.nunit + 1;
+    DAECPP_CUDA_TRY(c, c->dS.sync_words.reserve(nsync));
+    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->dS.sync_words.p, 0, sizeof(int32_t) * nsync, st));
+    c->ticket_base = 0;
+    c->solve_epoch = 0;
     DAECPP_CUDA_TRY(c, c->LU.reserve((size_t)S.lu_size + 1));
     DAECPP_CUDA_TRY(c, c->CB.reserve((size_t)S.cb_size + 1));
     DAECPP_CUDA_TRY(c, c->upd.reserve((size_t)S.upd_size + 1));
-    c->levels.clear();
-    for (int32_t l = 0; l < S.nlevels; ++l)
+    c->groups.clear();
+    for (const LaunchGroup &g : S.groups)
     {
-        LevelLaunch L;
-        L.begin = S.level_ptr[l];
-        L.count = S.level_ptr[l + 1] - S.level_ptr[l];
-        for (int32_t q = L.begin; q < L.begin + L.count; ++q)
-        {
-            const int32_t f = S.level_sn[q];
-            const int32_t d = S.s_of(f) + S.r_of(f);
-            if (d > L.max_dim) L.max_dim = d;
-        }
-        L.group = pick_group(L.max_dim);
-        c->levels.push_back(L);
+        GroupLaunch L;
+        L.kind = g.kind; L.begin = g.begin; L.count = g.end - g.begin; L.max_dim = g.max_dim;
+        L.group = pick_group(g.max_dim);
+        c->groups.push_back(L);
     }
+    // the fused assembly reads the staged triplet values when every slot has exactly one triplet
+    c->jvals_from_triplets = !c->direct_csc && c->J.no_duplicates && c->J.nnz > 0;
+    if ((rc = unit_setup(c))) return rc;
+    if ((rc = compose_entries(c))) return rc;
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
     c->have_symbolic = true;
     c->have_factor = false;
@@ -328,17 +334,37 @@ int upload_symbolic(daecpp_b200_ctx *c)
     return DAECPP_B200_OK;
 }
 
+// vals[] of a triplet set (compressed-column values) -- only the parity exports and the
+// duplicate-summing path need them; the fused assembly reads the triplet values directly.
+int ensure_csc_values(daecpp_b200_ctx *c, TripletSet &T)
+{
+    if (T.vals_valid || !T.have_pattern) return DAECPP_B200_OK;
+    int rc = regather_values(c, T);
+    if (rc) return rc;
+    T.vals_valid = true;
+    return DAECPP_B200_OK;
+}
+
+int jb_values(daecpp_b200_ctx *c, double alpha)
+{
+    if (c->direct_csc || !c->nnzU) return DAECPP_B200_OK;
+    int rc = ensure_csc_values(c, c->J);
+    if (rc) return rc;
+    if ((rc = ensure_csc_values(c, c->M))) return rc;
+    k_jb_values<<<(int)((c->nnzU + 255) / 256), 256, 0, c->stream>>>(c->nnzU, c->u_J.p, c->u_M.p, c->J.vals.p, c->M.vals.p,
+                                                                  alpha, c->u_vals.p);
+    c->kernels += 1;
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    return DAECPP_B200_OK;
+}
+
 // Only the values of Jb = J - (M*alpha) on the union pattern (parity export, no factorisation).
 int assemble_values_only(daecpp_b200_ctx *c, double alpha)
 {
-    if (c->nnzU && !c->direct_csc)
-    {
-        k_scatter<<<(int)((c->nnzU + 255) / 256), 256, 0, c->stream>>>(c->nnzU, c->u_J.p, c->u_M.p, c->J.vals.p, c->M.vals.p,
-                                                                      alpha, c->u_vals.p, nullptr, nullptr);
-        c->kernels += 1;
-        DAECPP_CUDA_TRY(c, cudaGetLastError());
-    }
+    int rc = jb_values(c, alpha);
+    if (rc) return rc;
     c->n_refactor += 1;
+    c->last_alpha = alpha;
     c->have_factor = false;
     return DAECPP_B200_OK;
 }
@@ -347,23 +373,26 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha)
 {
     cudaStream_t st = c->stream;
     Symbolic &S = c->S;
-    FrontTables T = tables(c);
-    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->LU.p, 0, sizeof(double) * (size_t)S.lu_size, st));
-    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 3, 0, sizeof(int32_t), st));
-    if (c->nnzU)
+    int rc;
+    if (!c->jvals_from_triplets && !c->direct_csc && (rc = ensure_csc_values(c, c->J))) return rc;
+    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 3, 0, 2 * sizeof(int32_t), st));
+    if (S.nbig)
     {
-        const int blocks = (int)((c->nnzU + 255) / 256);
-        if (c->direct_csc)
-            k_scatter<<<blocks, 256, 0, st>>>(c->nnzU, nullptr, nullptr, nullptr, nullptr, 0.0, c->u_vals.p, c->dS.a_dest.p, c->LU.p);
-        else
-            k_scatter<<<blocks, 256, 0, st>>>(c->nnzU, c->u_J.p, c->u_M.p, c->J.vals.p, c->M.vals.p, alpha, c->u_vals.p,
-                                              c->dS.a_dest.p, c->LU.p);
-        c->kernels += 1;
+        DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->LU.p + S.lu_big_begin, 0, sizeof(double) * (size_t)(S.lu_size - S.lu_big_begin), st));
+        if ((rc = launch_scatter_big(c, alpha))) return rc;
     }
-    for (const LevelLaunch &L : c->levels)
+    FrontTables T = tables(c);
+    for (const GroupLaunch &L : c->groups)
     {
-        DISPATCH_GROUP(L.group, k_factor_level, L.count, T, L.begin, L.count, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
-        c->kernels += 1;
+        if (L.kind == 0)
+        {
+            if ((rc = launch_unit_factor(c, L, alpha))) return rc;
+        }
+        else
+        {
+            DISPATCH_GROUP(L.group, k_factor_level, L.count, T, L.begin, L.count, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+            c->kernels += 1;
+        }
     }
     DAECPP_CUDA_TRY(c, cudaGetLastError());
     c->n_refactor += 1;
@@ -378,11 +407,12 @@ int numeric_refactor(daecpp_b200_ctx *c, double alpha)
     int rc = numeric_refactor_async(c, alpha);
     if (rc) return rc;
     DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev1, st));
-    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 3, c->d_flags + 3, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 3, c->d_flags + 3, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     c->ms_last_refactor = ms;
+    if (c->h_flags[4]) { c->err = "unit dependency wait timed out"; c->have_factor = false; return DAECPP_B200_ECUDA; }
     if (c->h_flags[3])
     {
         c->have_factor = false;
@@ -392,25 +422,47 @@ int numeric_refactor(daecpp_b200_ctx *c, double alpha)
     return DAECPP_B200_OK;
 }
 
-// dx = Jb^-1 b, all on the stream, no synchronisation
-int numeric_solve(daecpp_b200_ctx *c)
+// dx = Jb^-1 b, all on the stream, no synchronisation.  With no big fronts the permutations (and,
+// if asked, the error checks and xk += dx) are fused into the unit kernels.
+int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, double max_err_abs)
 {
     cudaStream_t st = c->stream;
     const int32_t n = c->n;
     FrontTables T = tables(c);
-    k_permute_in<<<(n + 255) / 256, 256, 0, st>>>(n, c->dS.perm.p, c->b, c->work);
-    for (size_t l = 0; l < c->levels.size(); ++l)
+    const bool direct = c->S.nbig == 0;
+    int rc;
+    c->solve_epoch += 1;
+    if (!direct)
     {
-        const LevelLaunch &L = c->levels[l];
-        DISPATCH_GROUP(L.group, k_forward_level, L.count, T, L.begin, L.count, c->LU.p, c->upd.p, c->work);
+        k_permute_in<<<(n + 255) / 256, 256, 0, st>>>(n, c->dS.perm.p, c->b, c->work);
+        c->kernels += 1;
     }
-    for (size_t l = c->levels.size(); l-- > 0;)
+    for (size_t l = 0; l < c->groups.size(); ++l)
     {
-        const LevelLaunch &L = c->levels[l];
-        DISPATCH_GROUP(L.group, k_backward_level, L.count, T, L.begin, L.count, c->LU.p, c->work);
+        const GroupLaunch &L = c->groups[l];
+        if (L.kind == 0) { if ((rc = launch_unit_forward(c, L, direct))) return rc; }
+        else
+        {
+            DISPATCH_GROUP(L.group, k_forward_level, L.count, T, L.begin, L.count, c->LU.p, c->upd.p, c->work);
+            c->kernels += 1;
+        }
     }
-    k_permute_out<<<(n + 255) / 256, 256, 0, st>>>(n, c->dS.perm.p, c->work, c->dx);
-    c->kernels += 2 + 2 * (double)c->levels.size();
+    for (size_t l = c->groups.size(); l-- > 0;)
+    {
+        const GroupLaunch &L = c->groups[l];
+        if (L.kind == 0) { if ((rc = launch_unit_backward(c, L, direct, fuse_update, atol, rtol, max_err_abs))) return rc; }
+        else
+        {
+            DISPATCH_GROUP(L.group, k_backward_level, L.count, T, L.begin, L.count, c->LU.p, c->work);
+            c->kernels += 1;
+        }
+    }
+    if (!direct)
+    {
+        k_permute_out<<<(n + 255) / 256, 256, 0, st>>>(n, c->dS.perm.p, c->work, c->dx);
+        c->kernels += 1;
+        if (fuse_update && (rc = launch_update(c, atol, rtol, max_err_abs))) return rc;
+    }
     DAECPP_CUDA_TRY(c, cudaGetLastError());
     c->n_solve += 1;
     return DAECPP_B200_OK;

@@ -3,7 +3,10 @@
 // factorisation (Eigen/src/SparseLU/SparseLU.h:528-814), which cannot be level-scheduled.
 #include "symbolic.hpp"
 
+#include "schedule.hpp"
+
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
@@ -136,13 +139,17 @@ struct Dissector
             for (int32_t k = 0; k < count; ++k) lev_count[level[queue[k]]]++;
             // separator = the thinnest level whose prefix holds 40..60 % of the vertices,
             // falling back to the median level
-            int32_t best = -1; int64_t acc = 0;
+            int32_t best = -1; int64_t acc = 0, best_skew = 0;
             for (int32_t l = 0; l < nlev; ++l)
             {
                 int64_t before = acc; acc += lev_count[l];
                 if (l == 0 || l == nlev - 1) continue;
                 bool in_window = before * 10 >= (int64_t)size * 4 && before * 10 <= (int64_t)size * 6;
-                if (in_window && (best < 0 || lev_count[l] < lev_count[best])) best = l;
+                if (!in_window) continue;
+                // thinnest level wins; among equally thin ones the most balanced split (shallower tree)
+                const int64_t skew = std::llabs(2 * before + lev_count[l] - (int64_t)size);
+                if (best < 0 || lev_count[l] < lev_count[best] || (lev_count[l] == lev_count[best] && skew < best_skew))
+                { best = l; best_skew = skew; }
             }
             if (best < 0)
             {
@@ -211,6 +218,9 @@ struct Dissector
 };
 
 } // namespace
+
+static bool build_schedule(int32_t n, const int32_t *outer, const int32_t *inner, const SymbolicOptions &opt, Symbolic &S,
+                           const std::vector<int32_t> &sn_of_col, const char **err);
 
 bool analyse_pattern(int32_t n, const int32_t *outer, const int32_t *inner, const SymbolicOptions &opt,
                      Symbolic &S, const char **err)
@@ -332,35 +342,25 @@ bool analyse_pattern(int32_t n, const int32_t *outer, const int32_t *inner, cons
         if (p >= 0 && lvl[p] < lvl[f] + 1) { lvl[p] = lvl[f] + 1; }
         if (lvl[f] + 1 > nlev) nlev = lvl[f] + 1;
     }
-    S.nlevels = nlev;
-    S.level_ptr.assign((size_t)nlev + 1, 0);
-    for (int32_t f = 0; f < nsn; ++f) S.level_ptr[lvl[f] + 1]++;
-    for (int32_t l = 0; l < nlev; ++l) S.level_ptr[l + 1] += S.level_ptr[l];
-    S.level_sn.resize(nsn);
-    {
-        std::vector<int32_t> fillp(S.level_ptr.begin(), S.level_ptr.end() - 1);
-        for (int32_t f = 0; f < nsn; ++f) S.level_sn[fillp[lvl[f]]++] = f;
-    }
+    S.nlevels = nlev; // height of the assembly tree (statistics only)
 
-    // storage offsets, relative indices, statistics
-    S.sn_lu.assign(nsn, 0); S.sn_cb.assign(nsn, 0);
-    int64_t lu = 0, cb = 0; double flops = 0; int64_t nnzf = 0;
+    double flops = 0; int64_t nnzf = 0;
     for (int32_t f = 0; f < nsn; ++f)
     {
         const int64_t s = S.s_of(f), r = S.r_of(f);
-        S.sn_lu[f] = lu; lu += (s + r) * s + r * s;
-        S.sn_cb[f] = cb; cb += r * r;
         flops += 2.0 / 3.0 * (double)s * s * s + 2.0 * (double)s * s * r + 2.0 * (double)s * r * r;
         nnzf += s * s + 2 * s * r;
         if (s + r > S.max_front) S.max_front = (int32_t)(s + r);
         if (s > S.max_pivot_block) S.max_pivot_block = (int32_t)s;
     }
-    S.lu_size = lu; S.cb_size = cb; S.upd_size = (int64_t)S.sn_rows.size(); S.flops = flops; S.nnz_factor = nnzf;
-    if (lu >= (int64_t)0xFFFFFFF0u)
+    S.flops = flops; S.nnz_factor = nnzf; S.upd_size = (int64_t)S.sn_rows.size();
+    if (S.upd_size >= 0x7ffffff0ll)
     {
-        if (err) *err = "factor storage exceeds the 32-bit slot map";
+        if (err) *err = "front row lists exceed the 32-bit schedule";
         return false;
     }
+
+    // relative indices: position of every row of a front inside its parent's index list
     S.sn_rel.assign(S.sn_rows.size(), -1);
     {
         std::vector<int32_t> pos((size_t)n, -1);
@@ -381,9 +381,337 @@ bool analyse_pattern(int32_t n, const int32_t *outer, const int32_t *inner, cons
         }
     }
 
-    // matrix slot -> factor storage
+    if (!build_schedule(n, outer, inner, opt, S, sn_of_col, err)) return false;
+    return true;
+}
+
+// --------------------------------------------------------------------------------------------
+// Partition the assembly tree into shared-memory units and big fronts, order them children
+// first, lay the factor storage out in that order and emit the per-unit blobs (schedule.hpp).
+static bool build_schedule(int32_t n, const int32_t *outer, const int32_t *inner, const SymbolicOptions &opt, Symbolic &S,
+                           const std::vector<int32_t> &sn_of_col, const char **err)
+{
+    using namespace sched;
+    const int32_t nsn = S.nsn;
+    int64_t budget = opt.unit_smem_bytes;
+    auto dim = [&](int32_t f) { return (int64_t)S.s_of(f) + S.r_of(f); };
+    auto wsz = [&](int32_t f) { int64_t d = dim(f); return (d * d) | 1; };           // odd: no bank aliasing
+    auto lusz = [&](int32_t f) { int64_t s = S.s_of(f), r = S.r_of(f); return (s + r) * s + r * s; };
+    auto own_bytes = [&](int32_t f) {
+        const int64_t s = S.s_of(f), r = S.r_of(f);
+        const int64_t ints = F_SIZE + (S.child_ptr[f + 1] - S.child_ptr[f]) + 2 * r + 2;
+        const int64_t fac = wsz(f), sol = s + 2 * r + lusz(f);
+        return 4 * ints + 8 * (fac > sol ? fac : sol);
+    };
+
+    if (budget < 0)
+    { // auto: enough units to occupy every SM a few times over, each as large as that allows
+        int64_t total = 0;
+        for (int32_t f = 0; f < nsn; ++f) total += own_bytes(f);
+        budget = total / (4 * 148);
+        if (budget < 6 * 1024) budget = 6 * 1024;
+        if (budget > 64 * 1024) budget = 64 * 1024;
+    }
+
+    // ---- 1. cuts ---------------------------------------------------------------------------
+    std::vector<char> cut((size_t)nsn, 0), big((size_t)nsn, 0);
+    std::vector<int64_t> acc((size_t)nsn, 0);
+    const int64_t header_bytes = 4 * (H_SIZE + 4);
+    std::vector<std::pair<int64_t, int32_t>> kids;
+    for (int32_t f = 0; f < nsn; ++f)
+    {
+        int64_t own = own_bytes(f);
+        const int32_t cb = S.child_ptr[f], ce = S.child_ptr[f + 1];
+        int64_t all_cut = own;
+        for (int32_t ci = cb; ci < ce; ++ci) all_cut += 4 * (X_SIZE + (int64_t)S.r_of(S.child_idx[ci]));
+        if (budget <= 0 || all_cut + header_bytes > budget)
+        {
+            big[f] = 1; cut[f] = 1;
+            for (int32_t ci = cb; ci < ce; ++ci) cut[S.child_idx[ci]] = 1;
+            acc[f] = 0;
+            continue;
+        }
+        int64_t a = own;
+        kids.clear();
+        for (int32_t ci = cb; ci < ce; ++ci)
+        {
+            const int32_t c = S.child_idx[ci];
+            if (cut[c]) a += 4 * (X_SIZE + (int64_t)S.r_of(c));
+            else { a += acc[c]; kids.push_back({acc[c], c}); }
+        }
+        if (a + header_bytes > budget)
+        {
+            std::sort(kids.begin(), kids.end());
+            while (a + header_bytes > budget && !kids.empty())
+            {
+                const int32_t c = kids.back().second;
+                a -= kids.back().first;
+                a += 4 * (X_SIZE + (int64_t)S.r_of(c));
+                cut[c] = 1;
+                kids.pop_back();
+            }
+        }
+        acc[f] = a;
+        if (S.sn_parent[f] < 0) cut[f] = 1;
+    }
+
+    // ---- 2. units = bins of cut, non-big siblings ---------------------------------------------
+    std::vector<int32_t> unit_of((size_t)nsn, -1), root_of((size_t)nsn, -1);
+    int32_t nunit = 0;
+    {
+        // cut children of the same parent are contiguous in child_idx; parentless roots are
+        // visited in id order
+        int64_t fill = 0; int32_t cur_parent = -2;
+        auto place = [&](int32_t c, int32_t parent) {
+            if (big[c]) return;
+            if (parent != cur_parent || fill + acc[c] + header_bytes > budget) { nunit++; fill = 0; cur_parent = parent; }
+            fill += acc[c];
+            unit_of[c] = nunit - 1;
+        };
+        for (int32_t f = 0; f < nsn; ++f) if (S.sn_parent[f] < 0) place(f, -1);
+        for (int32_t p = 0; p < nsn; ++p)
+            for (int32_t ci = S.child_ptr[p]; ci < S.child_ptr[p + 1]; ++ci)
+                if (cut[S.child_idx[ci]]) place(S.child_idx[ci], p);
+    }
+    for (int32_t f = nsn - 1; f >= 0; --f)
+    {
+        if (cut[f]) { root_of[f] = f; continue; }
+        unit_of[f] = unit_of[S.sn_parent[f]];
+        root_of[f] = root_of[S.sn_parent[f]];
+    }
+
+    // ---- 3. stages (units and big fronts are the nodes), ticket order, launch groups -----------
+    // node id: unit u -> u ; big front f -> nunit + f
+    auto node_of = [&](int32_t f) { return big[f] ? nunit + f : unit_of[f]; };
+    std::vector<int32_t> stage((size_t)nunit + nsn, 0), ndep((size_t)nunit, 0), unit_parent((size_t)nunit, -1);
+    {
+        std::vector<int32_t> last_child_unit((size_t)nunit + nsn, -1);
+        for (int32_t f = 0; f < nsn; ++f)
+        {
+            const int32_t me = node_of(f);
+            for (int32_t ci = S.child_ptr[f]; ci < S.child_ptr[f + 1]; ++ci)
+            {
+                const int32_t c = S.child_idx[ci];
+                if (!cut[c]) continue;
+                const int32_t cn = node_of(c);
+                if (stage[me] < stage[cn] + 1) stage[me] = stage[cn] + 1;
+                if (cn < nunit)
+                {
+                    unit_parent[cn] = me < nunit ? me : -2;
+                    if (me < nunit && last_child_unit[me] != cn) { ndep[me]++; last_child_unit[me] = cn; }
+                }
+            }
+        }
+    }
+    int32_t nstage = 0;
+    for (int32_t u = 0; u < nunit; ++u) if (stage[u] + 1 > nstage) nstage = stage[u] + 1;
+    S.nbig = 0;
+    for (int32_t f = 0; f < nsn; ++f) if (big[f]) { S.nbig++; if (stage[nunit + f] + 1 > nstage) nstage = stage[nunit + f] + 1; }
+    std::vector<int32_t> order((size_t)nunit), rank((size_t)nunit);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return stage[a] < stage[b]; });
+    for (int32_t t = 0; t < nunit; ++t) rank[order[t]] = t;
+    S.big_sn.clear();
+    {
+        std::vector<int32_t> bigs;
+        for (int32_t f = 0; f < nsn; ++f) if (big[f]) bigs.push_back(f);
+        std::stable_sort(bigs.begin(), bigs.end(), [&](int32_t a, int32_t b) { return stage[nunit + a] < stage[nunit + b]; });
+        S.big_sn = bigs;
+    }
+    S.groups.clear();
+    {
+        int32_t tu = 0, tb = 0, open_begin = 0;
+        for (int32_t st = 0; st < nstage; ++st)
+        {
+            while (tu < nunit && stage[order[tu]] == st) ++tu;
+            const int32_t b0 = tb;
+            int32_t md = 0;
+            while (tb < S.nbig && stage[nunit + S.big_sn[tb]] == st) { md = std::max<int32_t>(md, (int32_t)dim(S.big_sn[tb])); ++tb; }
+            if (tb > b0)
+            {
+                if (tu > open_begin) S.groups.push_back({0, open_begin, tu, 0});
+                open_begin = tu;
+                S.groups.push_back({1, b0, tb, md});
+            }
+        }
+        if (nunit > open_begin) S.groups.push_back({0, open_begin, nunit, 0});
+    }
+    S.nunit = nunit;
+
+    // ---- 4. fronts of every unit in (local level, id) order -------------------------------------
+    std::vector<int32_t> llev((size_t)nsn, 0);
+    for (int32_t f = 0; f < nsn; ++f)
+    {
+        if (big[f]) continue;
+        const int32_t p = S.sn_parent[f];
+        if (!cut[f] && llev[p] < llev[f] + 1) llev[p] = llev[f] + 1;
+    }
+    std::vector<int32_t> ucount((size_t)nunit + 1, 0);
+    for (int32_t f = 0; f < nsn; ++f) if (!big[f]) ucount[rank[unit_of[f]] + 1]++;
+    for (int32_t t = 0; t < nunit; ++t) ucount[t + 1] += ucount[t];
+    std::vector<int32_t> ufront((size_t)ucount[nunit]);
+    {
+        std::vector<int32_t> fillp(ucount.begin(), ucount.end() - 1);
+        for (int32_t f = 0; f < nsn; ++f) if (!big[f]) ufront[fillp[rank[unit_of[f]]]++] = f;
+        for (int32_t t = 0; t < nunit; ++t)
+            std::stable_sort(ufront.begin() + ucount[t], ufront.begin() + ucount[t + 1],
+                             [&](int32_t a, int32_t b) { return llev[a] < llev[b]; });
+    }
+
+    // ---- 5. factor storage in schedule order: units first, big fronts last ----------------------
+    S.sn_lu.assign(nsn, 0); S.sn_cb.assign(nsn, -1);
+    int64_t lu = 0, cbsz = 0;
+    for (int32_t q = 0; q < ucount[nunit]; ++q) { const int32_t f = ufront[q]; S.sn_lu[f] = lu; lu += lusz(f); }
+    S.lu_big_begin = lu;
+    for (int32_t f : S.big_sn) { S.sn_lu[f] = lu; lu += lusz(f); }
+    for (int32_t f = 0; f < nsn; ++f)
+        if (cut[f] && S.r_of(f) > 0) { S.sn_cb[f] = cbsz; cbsz += (int64_t)S.r_of(f) * S.r_of(f); }
+    S.lu_size = lu; S.cb_size = cbsz;
+    if (lu >= (int64_t)0xFFFFFFF0u || cbsz >= (int64_t)0xFFFFFFF0u)
+    {
+        if (err) *err = "factor storage exceeds the 32-bit slot map";
+        return false;
+    }
+
+    // ---- 6. blobs ------------------------------------------------------------------------------
+    S.blob.clear(); S.unit_blob.assign((size_t)nunit + 1, 0);
+    std::vector<int32_t> local_idx((size_t)nsn, -1), woff((size_t)nsn, 0), yoff((size_t)nsn, 0), xroff((size_t)nsn, 0);
+    int64_t max_fac = 0, max_sol = 0;
+    S.n_serial_fronts = 0;
+    for (int32_t t = 0; t < nunit; ++t)
+    {
+        const int32_t u = order[t];
+        const int32_t fb = ucount[t], fe = ucount[t + 1], nf = fe - fb;
+        const size_t base = S.blob.size();
+        if (base + 64 >= (size_t)0x7fffff00)
+        {
+            if (err) *err = "unit schedule exceeds 32-bit offsets";
+            return false;
+        }
+        S.unit_blob[t] = (int32_t)base;
+        S.blob.resize(base + H_SIZE, 0);
+        int32_t nl = 0;
+        for (int32_t q = fb; q < fe; ++q) nl = std::max(nl, llev[ufront[q]] + 1);
+        // level table
+        const int32_t lev_off = (int32_t)(S.blob.size() - base);
+        S.blob.resize(S.blob.size() + 2 * (size_t)nl + 1, 0);
+        {
+            int32_t *lp = S.blob.data() + base + lev_off;
+            int32_t *lg = lp + nl + 1;
+            std::vector<int32_t> maxd((size_t)nl, 0);
+            for (int32_t q = fb; q < fe; ++q)
+            {
+                const int32_t f = ufront[q];
+                lp[llev[f] + 1]++;
+                maxd[llev[f]] = std::max<int32_t>(maxd[llev[f]], (int32_t)dim(f));
+            }
+            for (int32_t l = 0; l < nl; ++l) lp[l + 1] += lp[l];
+            for (int32_t l = 0; l < nl; ++l)
+            {
+                const int32_t d = maxd[l];
+                lg[l] = d <= opt.serial_dim ? 1 : (d <= 12 ? 8 : (d <= 40 ? 32 : 0));
+                if (lg[l] == 1) S.n_serial_fronts += lp[l + 1] - lp[l];
+            }
+        }
+        // arenas
+        int64_t w = 0, y = 0, ud = 0, xr = 0, lucount = 0;
+        for (int32_t q = fb; q < fe; ++q)
+        {
+            const int32_t f = ufront[q];
+            local_idx[f] = q - fb;
+            woff[f] = (int32_t)w; w += wsz(f);
+            yoff[f] = (int32_t)y; y += S.s_of(f);
+            ud += S.r_of(f);
+            lucount += lusz(f);
+            if (cut[f]) { xroff[f] = (int32_t)xr; xr += S.r_of(f); }
+        }
+        // front records
+        const int32_t fr_off = (int32_t)(S.blob.size() - base);
+        S.blob.resize(S.blob.size() + (size_t)nf * F_SIZE, 0);
+        int64_t uacc = 0;
+        for (int32_t q = fb; q < fe; ++q)
+        {
+            const int32_t f = ufront[q];
+            const int32_t s = S.s_of(f), r = S.r_of(f);
+            const int32_t nch = S.child_ptr[f + 1] - S.child_ptr[f];
+            const int64_t rp = S.sn_rowptr[f];
+            // rows: rel[r], rowsrc[r]
+            const int32_t rows_off = (int32_t)(S.blob.size() - base);
+            S.blob.resize(S.blob.size() + 2 * (size_t)r);
+            {
+                int32_t *rel = S.blob.data() + base + rows_off, *src = rel + r;
+                const int32_t root = root_of[f];
+                const int32_t *rr = S.sn_rows.data() + S.sn_rowptr[root];
+                const int32_t nrr = S.r_of(root);
+                for (int32_t a = 0; a < r; ++a)
+                {
+                    const int32_t wcol = S.sn_rows[rp + a];
+                    rel[a] = S.sn_rel[rp + a];
+                    const int32_t g = sn_of_col[wcol];
+                    if (!big[g] && unit_of[g] == u && local_idx[g] >= 0 && g > f && root_of[g] == root)
+                        src[a] = yoff[g] + (wcol - S.sn_first[g]);
+                    else
+                        src[a] = (int32_t)y + xroff[root] + (int32_t)(std::lower_bound(rr, rr + nrr, wcol) - rr);
+                }
+            }
+            // children
+            const int32_t child_off = (int32_t)(S.blob.size() - base);
+            S.blob.resize(S.blob.size() + (size_t)nch);
+            for (int32_t k = 0; k < nch; ++k)
+            {
+                const int32_t c = S.child_idx[S.child_ptr[f] + k];
+                if (!cut[c]) { S.blob[base + child_off + k] = local_idx[c]; continue; }
+                const int32_t rc = S.r_of(c);
+                const int32_t xo = (int32_t)(S.blob.size() - base);
+                S.blob.resize(S.blob.size() + X_SIZE + (size_t)rc);
+                int32_t *x = S.blob.data() + base + xo;
+                x[X_CB] = (int32_t)(uint32_t)(rc > 0 ? S.sn_cb[c] : 0);
+                x[X_R] = rc;
+                x[X_REL] = xo + X_SIZE;
+                x[X_UPD] = (int32_t)S.sn_rowptr[c];
+                for (int32_t a = 0; a < rc; ++a) x[X_SIZE + a] = S.sn_rel[S.sn_rowptr[c] + a];
+                S.blob[base + child_off + k] = -xo;
+            }
+            int32_t *F = S.blob.data() + base + fr_off + (size_t)(q - fb) * F_SIZE;
+            F[F_COL0] = S.sn_first[f]; F[F_S] = s; F[F_R] = r; F[F_WOFF] = woff[f];
+            F[F_LUOFF] = (int32_t)(S.sn_lu[f] - S.sn_lu[ufront[fb]]);
+            F[F_ROWS] = rows_off; F[F_CHILD] = child_off; F[F_NCHILD] = nch;
+            F[F_YOFF] = yoff[f]; F[F_UOFF] = (int32_t)uacc;
+            F[F_EXTCB] = (cut[f] && r > 0) ? (int32_t)(uint32_t)S.sn_cb[f] : -1;
+            F[F_EXTUPD] = (cut[f] && r > 0) ? (int32_t)rp : -1;
+            uacc += r;
+        }
+        // external rows of the roots (global permuted indices)
+        const int32_t xr_off = (int32_t)(S.blob.size() - base);
+        S.blob.resize(S.blob.size() + (size_t)xr);
+        for (int32_t q = fb; q < fe; ++q)
+        {
+            const int32_t f = ufront[q];
+            if (!cut[f]) continue;
+            for (int32_t a = 0; a < S.r_of(f); ++a) S.blob[base + xr_off + xroff[f] + a] = S.sn_rows[S.sn_rowptr[f] + a];
+        }
+        while ((S.blob.size() - base) % 4) S.blob.push_back(0); // 16-byte granules for vector loads
+        int32_t *H = S.blob.data() + base;
+        H[H_NF] = nf; H[H_NLEV] = nl; H[H_WDOUBLES] = (int32_t)w;
+        H[H_LU0] = (int32_t)(uint32_t)S.sn_lu[ufront[fb]]; H[H_LUCOUNT] = (int32_t)lucount;
+        H[H_YDOUBLES] = (int32_t)y; H[H_UDOUBLES] = (int32_t)ud; H[H_NXR] = (int32_t)xr;
+        H[H_NDEP] = ndep[u]; H[H_PARENT] = unit_parent[u] >= 0 ? rank[unit_parent[u]] : unit_parent[u];
+        H[H_LEVELS] = lev_off; H[H_FRONTS] = fr_off; H[H_XR] = xr_off;
+        H[H_NINTS] = (int32_t)(S.blob.size() - base);
+        const int64_t ints_b = 4 * (int64_t)H[H_NINTS];
+        max_fac = std::max(max_fac, ints_b + 8 * w);
+        max_sol = std::max(max_sol, ints_b + 8 * (y + xr + ud + lucount));
+    }
+    S.unit_blob[nunit] = (int32_t)S.blob.size();
+    S.factor_smem_bytes = (int32_t)max_fac + 64;
+    S.solve_smem_bytes = (int32_t)max_sol + 64;
+
+    // ---- 7. matrix slots -> frontal positions -----------------------------------------------------
     const int64_t nnz = outer[n];
-    S.a_dest.resize((size_t)nnz);
+    std::vector<int32_t> ecount((size_t)nunit + 1, 0);
+    std::vector<int32_t> slot_front((size_t)nnz);
+    std::vector<int32_t> slot_pos((size_t)nnz); // unit fronts: index inside the frontal matrix; big: unused
+    S.big_u.clear(); S.big_dst.clear();
     for (int32_t c = 0; c < n; ++c)
     {
         const int32_t pj = S.iperm[c];
@@ -393,24 +721,51 @@ bool analyse_pattern(int32_t n, const int32_t *outer, const int32_t *inner, cons
             const int32_t k = pi < pj ? pi : pj;
             const int32_t f = sn_of_col[k];
             const int32_t first = S.sn_first[f], last = S.sn_first[f + 1] - 1;
-            const int64_t s = last - first + 1, r = S.r_of(f);
+            const int64_t s = last - first + 1, r = S.r_of(f), d = s + r;
             const int32_t *rb = S.sn_rows.data() + S.sn_rowptr[f];
-            int64_t off;
+            int64_t ii, jj;
             if (pj <= last)
-            { // column inside the pivot block: L panel
-                int64_t rowpos;
-                if (pi <= last) rowpos = pi - first;
-                else rowpos = s + (std::lower_bound(rb, rb + r, pi) - rb);
-                off = S.sn_lu[f] + (int64_t)(pj - first) * (s + r) + rowpos;
+            {
+                jj = pj - first;
+                ii = (pi <= last) ? (pi - first) : s + (std::lower_bound(rb, rb + r, pi) - rb);
             }
             else
-            { // row inside the pivot block, column beyond it: Ut panel (transposed)
-                int64_t colpos = std::lower_bound(rb, rb + r, pj) - rb;
-                off = S.sn_lu[f] + (s + r) * s + (int64_t)(pi - first) * r + colpos;
+            {
+                ii = pi - first;
+                jj = s + (std::lower_bound(rb, rb + r, pj) - rb);
             }
-            S.a_dest[p] = (uint32_t)off;
+            slot_front[p] = f;
+            if (big[f])
+            {
+                const int64_t off = (jj < s) ? S.sn_lu[f] + jj * d + ii : S.sn_lu[f] + d * s + ii * r + (jj - s);
+                S.big_u.push_back(p);
+                S.big_dst.push_back((uint32_t)off);
+            }
+            else
+            {
+                slot_pos[p] = (int32_t)(woff[f] + jj * d + ii);
+                ecount[rank[unit_of[f]] + 1]++;
+            }
         }
     }
+    for (int32_t t = 0; t < nunit; ++t) ecount[t + 1] += ecount[t];
+    S.ent_u.assign((size_t)ecount[nunit], 0); S.ent_dst.assign((size_t)ecount[nunit], 0);
+    {
+        std::vector<int32_t> fillp(ecount.begin(), ecount.end() - 1);
+        for (int64_t p = 0; p < nnz; ++p)
+        {
+            const int32_t f = slot_front[p];
+            if (big[f]) continue;
+            const int32_t q = fillp[rank[unit_of[f]]]++;
+            S.ent_u[q] = (int32_t)p; S.ent_dst[q] = slot_pos[p];
+        }
+    }
+    for (int32_t t = 0; t < nunit; ++t)
+    {
+        int32_t *H = S.blob.data() + S.unit_blob[t];
+        H[H_ENT0] = ecount[t]; H[H_ENTCOUNT] = ecount[t + 1] - ecount[t];
+    }
+    S.a_dest.clear();
     return true;
 }
 

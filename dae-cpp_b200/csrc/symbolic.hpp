@@ -20,6 +20,16 @@ struct SymbolicOptions
     int leaf_size = 8;      // stop dissecting below this many vertices
     int relax_zeros = 0;    // reserved: relaxed amalgamation budget
     int max_super = 256;    // widest supernode (pivot block) allowed
+    int unit_smem_bytes = -1; // shared-memory budget of one subtree unit (-1: chosen from the problem
+                              // size; 0: no units, every front goes through the per-level kernels)
+    int serial_dim = 4;     // fronts up to this order are factored by one thread each
+};
+
+struct LaunchGroup
+{
+    int32_t kind = 0;           // 0: subtree units [begin,end) handed out by ticket; 1: big fronts big_sn[begin,end)
+    int32_t begin = 0, end = 0;
+    int32_t max_dim = 0;        // kind 1: largest front order in the group
 };
 
 struct Symbolic
@@ -50,6 +60,20 @@ struct Symbolic
     // matrix slot -> factor storage.  a_dest[u] is the offset (in doubles) inside the LU storage
     // of slot u of the compressed-column pattern the analysis was given.
     std::vector<uint32_t> a_dest;
+
+    // ---- subtree-unit schedule (schedule.hpp) ----------------------------------------------
+    int32_t nunit = 0, nbig = 0;
+    std::vector<int32_t> blob;      // all unit blobs, concatenated
+    std::vector<int32_t> unit_blob; // [nunit+1] word offsets into blob, ticket order
+    std::vector<int32_t> ent_u;     // matrix slot (index into the pattern the analysis was given) ...
+    std::vector<int32_t> ent_dst;   // ... and its position inside the owning unit's frontal arena
+    std::vector<int32_t> big_u;     // matrix slots that belong to big fronts ...
+    std::vector<uint32_t> big_dst;  // ... and their offset in the global factor storage
+    std::vector<int32_t> big_sn;    // big fronts ordered by stage
+    std::vector<LaunchGroup> groups;
+    int64_t lu_big_begin = 0;       // factor storage of big fronts starts here (needs zeroing)
+    int32_t factor_smem_bytes = 0, solve_smem_bytes = 0;
+    int32_t n_serial_fronts = 0;
 
     int64_t lu_size = 0;  // doubles
     int64_t cb_size = 0;  // doubles

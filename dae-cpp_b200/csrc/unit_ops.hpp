@@ -1,0 +1,188 @@
+// Per-front work of a subtree unit (schedule.hpp), written once for the CUDA kernels
+// (subtree.cu: a front is handled by G cooperating lanes, G = 1, 8, 32 or the whole block) and for
+// the scalar walk used by the GPU-less tests (tests/emu/: G = 1).  `P` is a policy type with
+//   int lane() const, int width() const, void sync() const
+// All pointers except LUg / CBg / UPDg point into the unit's (shared-memory) arenas.
+//
+// Role in the reference: this is what Eigen::SparseLU::factorize and _solve_impl do column by
+// column (Eigen/src/SparseLU/SparseLU.h:611-814, 338-358), restated as a multifrontal sweep.
+#pragma once
+#include <cmath>
+#include <cstdint>
+
+#include "schedule.hpp"
+
+#if defined(__CUDACC__)
+#define DAE_HD __host__ __device__ __forceinline__
+#else
+#define DAE_HD inline
+#endif
+// Data written by OTHER thread blocks of the same launch (contribution blocks, update vectors,
+// finished unknowns) must bypass the non-coherent L1.
+#if defined(__CUDA_ARCH__)
+#define DAE_LDCG(p) __ldcg(p)
+#else
+#define DAE_LDCG(p) (*(p))
+#endif
+
+namespace daecpp_b200
+{
+namespace unit_ops
+{
+using namespace sched;
+
+// Extend-add the children's contribution blocks, eliminate the s pivots (right-looking, static
+// pivoting), store the L and transposed-U panels, and leave / export the contribution block.
+template <class P>
+DAE_HD void factor_front(const P &p, const int32_t *B, const int32_t *F, double *W, double *LUunit, double *CBg,
+                         double pivot_tol, int *fail)
+{
+    const int lane = p.lane(), G = p.width();
+    const int32_t s = F[F_S], r = F[F_R], d = s + r;
+    double *A = W + F[F_WOFF];
+    const int32_t *fronts = B + B[H_FRONTS];
+    for (int32_t k = 0; k < F[F_NCHILD]; ++k)
+    {
+        const int32_t v = B[F[F_CHILD] + k];
+        const double *Cc; const int32_t *rel; int32_t rc, ldc;
+        if (v >= 0)
+        {
+            const int32_t *Fc = fronts + (int64_t)v * F_SIZE;
+            const int32_t sc = Fc[F_S];
+            rc = Fc[F_R]; ldc = sc + rc;
+            Cc = W + Fc[F_WOFF] + (int64_t)sc * ldc + sc;
+            rel = B + Fc[F_ROWS];
+        }
+        else
+        {
+            const int32_t *X = B - v;
+            rc = X[X_R]; ldc = rc;
+            Cc = CBg + (uint32_t)X[X_CB];
+            rel = B + X[X_REL];
+        }
+        for (int32_t e = lane; e < rc * rc; e += G)
+        {
+            const int32_t a = e % rc, b = e / rc;
+            const double cv = (v >= 0) ? Cc[(int64_t)b * ldc + a] : DAE_LDCG(Cc + (int64_t)b * ldc + a);
+            A[(int64_t)rel[b] * d + rel[a]] += cv;
+        }
+        p.sync();
+    }
+    for (int32_t k = 0; k < s; ++k)
+    {
+        double *colk = A + (int64_t)k * d;
+        const double piv = colk[k];
+        if (lane == 0 && (!(fabs(piv) > pivot_tol) || std::isinf(piv))) *fail = 1;
+        const double inv = 1.0 / piv;
+        p.sync(); // everybody has read the pivot before the column is scaled
+        for (int32_t i = k + 1 + lane; i < d; i += G) colk[i] *= inv;
+        p.sync();
+        const int32_t m = d - k - 1;
+        for (int32_t e = lane; e < m * m; e += G)
+        {
+            const int32_t j = k + 1 + e / m, i = k + 1 + e % m;
+            A[(int64_t)j * d + i] -= colk[i] * A[(int64_t)j * d + k];
+        }
+        p.sync();
+    }
+    double *Lp = LUunit + (uint32_t)F[F_LUOFF];
+    for (int32_t e = lane; e < d * s; e += G) Lp[e] = A[e];
+    double *Ut = Lp + (int64_t)d * s;
+    for (int32_t e = lane; e < r * s; e += G)
+    {
+        const int32_t a = e % r, k = e / r;
+        Ut[e] = A[(int64_t)(s + a) * d + k];
+    }
+    if (F[F_EXTCB] != -1)
+    {
+        double *C = CBg + (uint32_t)F[F_EXTCB];
+        for (int32_t e = lane; e < r * r; e += G)
+        {
+            const int32_t a = e % r, b = e / r;
+            C[e] = A[(int64_t)(s + b) * d + s + a];
+        }
+    }
+}
+
+// Forward substitution of one front: gather the children's update vectors, solve with the unit
+// lower triangle of the pivot block, push the remainder into this front's update vector.
+// Y: pivot unknowns of the unit, U: update-vector arena, LUs: the unit's factor storage.
+template <class P>
+DAE_HD void forward_front(const P &p, const int32_t *B, const int32_t *F, double *Y, double *U, const double *LUs,
+                          double *UPDg)
+{
+    const int lane = p.lane(), G = p.width();
+    const int32_t s = F[F_S], r = F[F_R], d = s + r;
+    double *y1 = Y + F[F_YOFF];
+    double *u = U + F[F_UOFF];
+    const int32_t *fronts = B + B[H_FRONTS];
+    for (int32_t k = 0; k < F[F_NCHILD]; ++k)
+    {
+        const int32_t v = B[F[F_CHILD] + k];
+        const double *uc; const int32_t *rel; int32_t rc;
+        if (v >= 0)
+        {
+            const int32_t *Fc = fronts + (int64_t)v * F_SIZE;
+            rc = Fc[F_R]; uc = U + Fc[F_UOFF]; rel = B + Fc[F_ROWS];
+        }
+        else
+        {
+            const int32_t *X = B - v;
+            rc = X[X_R]; uc = UPDg + X[X_UPD]; rel = B + X[X_REL];
+        }
+        for (int32_t a = lane; a < rc; a += G)
+        {
+            const int32_t ra = rel[a];
+            const double uv = (v >= 0) ? uc[a] : DAE_LDCG(uc + a);
+            if (ra < s) y1[ra] += uv; else u[ra - s] += uv;
+        }
+        p.sync();
+    }
+    const double *Lp = LUs + (uint32_t)F[F_LUOFF];
+    for (int32_t k = 0; k < s; ++k)
+    {
+        const double yk = y1[k];
+        const double *colk = Lp + (int64_t)k * d;
+        for (int32_t i = k + 1 + lane; i < d; i += G)
+        {
+            const double v = colk[i] * yk;
+            if (i < s) y1[i] -= v; else u[i - s] -= v;
+        }
+        p.sync();
+    }
+    if (F[F_EXTUPD] != -1)
+        for (int32_t a = lane; a < r; a += G) UPDg[F[F_EXTUPD] + a] = u[a];
+}
+
+// Backward substitution of one front.  X = [Y | xr]: the unit's pivot unknowns followed by the
+// (already final) unknowns of the rows that lie above the unit.
+template <class P>
+DAE_HD void backward_front(const P &p, const int32_t *B, const int32_t *F, double *X, const double *LUs)
+{
+    const int lane = p.lane(), G = p.width();
+    const int32_t s = F[F_S], r = F[F_R], d = s + r;
+    double *y1 = X + F[F_YOFF];
+    const double *Lp = LUs + (uint32_t)F[F_LUOFF];
+    const double *Ut = Lp + (int64_t)d * s;
+    const int32_t *src = B + F[F_ROWS] + r;
+    for (int32_t k = lane; k < s; k += G)
+    {
+        double acc = y1[k];
+        const double *utk = Ut + (int64_t)k * r;
+        for (int32_t a = 0; a < r; ++a) acc -= utk[a] * X[src[a]];
+        y1[k] = acc;
+    }
+    p.sync();
+    for (int32_t j = s - 1; j >= 0; --j)
+    {
+        const double *colj = Lp + (int64_t)j * d;
+        if (lane == 0) y1[j] = y1[j] / colj[j];
+        p.sync();
+        const double xj = y1[j];
+        for (int32_t i = lane; i < j; i += G) y1[i] -= colj[i] * xj;
+        p.sync();
+    }
+}
+
+} // namespace unit_ops
+} // namespace daecpp_b200

@@ -114,15 +114,18 @@ def test_residual_bit_exact(order):
 
 
 # ---------------------------------------------------------------- linear solve (a7-a9)
-def _solve_and_check(n, J, M, alpha, b=None):
+def _solve_and_check(n, J, M, alpha, b=None, options=None):
     csc = O.assemble_jb(O.port, n, J, M, alpha)
     b = np.full(n, 1.24) if b is None else b
     c = B.Context(n)
+    for k, v in (options or {}).items():
+        c.set_option(k, v)
     c.set_mass(M); c.set_jacobian(J)
     c.refactor(alpha)
     c.set_rhs(b)
     x = c.solve()
-    stats = {k: c.stat(k) for k in ("n_fronts", "n_levels", "nnz_factor", "max_front", "ms_last_refactor", "ms_last_solve")}
+    stats = {k: c.stat(k) for k in ("n_fronts", "n_levels", "nnz_factor", "max_front", "ms_last_refactor", "ms_last_solve",
+                                    "n_units", "n_big_fronts", "n_launch_groups")}
     c.close()
     eta, r2 = O.backward_error(n, csc, x, b)
     assert eta <= 1e-12, (eta, stats)
@@ -171,6 +174,50 @@ def test_linear_solve_flame1d(n):
 @pytest.mark.parametrize("m", [4, 33, 128])
 def test_linear_solve_grid2d(m):
     _solve_and_check(m * m, P.grid2d_probe_matrix(m), EMPTY, 0.0)
+
+
+@pytest.mark.parametrize("budget", [0, 2048, 16 * 1024, 96 * 1024])
+@pytest.mark.parametrize("threads", [64, 256])
+def test_linear_solve_schedule_variants(budget, threads):
+    """Same answers whatever the partition into shared-memory units and per-level big fronts."""
+    opts = {"unit_smem_bytes": budget, "unit_threads": threads}
+    N = 700
+    xs = P.perovskite_state(N)
+    _, st = _solve_and_check(2 * N, P.perovskite_jacobian(xs, N), P.perovskite_mass(N), 100.0, options=opts)
+    assert (st["n_units"] == 0) == (budget == 0)
+    _, st = _solve_and_check(48 * 48, P.grid2d_probe_matrix(48), EMPTY, 0.0, options=opts)
+    if budget == 2048:
+        assert st["n_big_fronts"] > 0 and st["n_units"] > 0  # mixed schedule
+    n = 5000
+    _solve_and_check(n, P.flame1d_jacobian(P.flame1d_state(n)), P.identity_mass(n), 50.0, options=opts)
+
+
+def test_linear_solve_wide_groups():
+    """serial_dim = 0 forces every front through the cooperative (8 / 32 / block wide) code."""
+    N = 300
+    xs = P.perovskite_state(N)
+    _solve_and_check(2 * N, P.perovskite_jacobian(xs, N), P.perovskite_mass(N), 100.0, options={"serial_dim": 0})
+    _solve_and_check(40 * 40, P.grid2d_probe_matrix(40), EMPTY, 0.0, options={"serial_dim": 0, "unit_smem_bytes": 200 * 1024})
+
+
+def test_repeated_refactor_and_solve_reuse_schedule():
+    """Counters / tickets / epochs survive many launches on one context."""
+    n = 20000
+    u = P.flame1d_state(n)
+    J = P.flame1d_jacobian(u); M = P.identity_mass(n)
+    c = B.Context(n)
+    c.set_mass(M); c.set_jacobian(J)
+    b = np.linspace(-1, 1, n)
+    for k in range(12):
+        alpha = 10.0 + k
+        c.refactor(alpha)
+        for _ in range(2):
+            c.set_rhs(b)
+            x = c.solve()
+            eta, _ = O.backward_error(n, O.assemble_jb(O.port, n, J, M, alpha), x, b)
+            assert eta <= 1e-12
+    assert c.stat("n_symbolic") == 1
+    c.close()
 
 
 def test_linear_solve_dense_block_and_disconnected():
