@@ -23,7 +23,7 @@ SYMBOLS = [
     "daecpp_b200_rollback", "daecpp_b200_set_mass", "daecpp_b200_set_jacobian", "daecpp_b200_residual",
     "daecpp_b200_refactor", "daecpp_b200_solve_update", "daecpp_b200_accept_step", "daecpp_b200_set_rhs",
     "daecpp_b200_solve", "daecpp_b200_get_csc", "daecpp_b200_get_vector", "daecpp_b200_set_vector", "daecpp_b200_get_stat",
-    "daecpp_b200_set_option", "daecpp_b200_iteration_resident", "daecpp_b200_event_mark", "daecpp_b200_event_elapsed_ms",
+    "daecpp_b200_set_option", "daecpp_b200_iteration_resident", "daecpp_b200_event_mark", "daecpp_b200_event_elapsed_ms", "daecpp_b200_debug_unit_trace",
 ]
 
 
@@ -59,6 +59,7 @@ def load():
     lib.daecpp_b200_set_option.argtypes = [_vp, C.c_char_p, C.c_double]
     lib.daecpp_b200_iteration_resident.argtypes = [_vp, C.c_int32, C.c_int32, _f64, C.c_double, C.c_double, C.c_double,
                                                    C.POINTER(C.c_int32)]
+    lib.daecpp_b200_debug_unit_trace.argtypes = [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]
     lib.daecpp_b200_event_mark.argtypes = [_vp]
     lib.daecpp_b200_event_elapsed_ms.argtypes = [_vp, C.POINTER(C.c_double)]
     return lib
@@ -167,6 +168,13 @@ class Context:
                                                               np.ascontiguousarray(dt4, np.float64), atol, rtol,
                                                               max_err_abs, C.byref(flags)), allow)
         return rc, flags.value
+
+    def unit_trace(self):
+        cnt = C.c_int64(0)
+        self._ck(self.lib.daecpp_b200_debug_unit_trace(self.h, None, 0, C.byref(cnt)))
+        out = np.zeros(max(cnt.value, 1), np.int64)
+        self._ck(self.lib.daecpp_b200_debug_unit_trace(self.h, out.ctypes.data, cnt.value, C.byref(cnt)))
+        return out[:cnt.value].reshape(-1, 4)
 
     def event_mark(self):
         self._ck(self.lib.daecpp_b200_event_mark(self.h))

@@ -154,7 +154,7 @@ void daecpp_b200_destroy(daecpp_b200_ctx *c)
     c->M.release(); c->J.release(); c->dS.release();
     c->m_rowptr.release(); c->m_rowslot.release(); c->m_rowcol.release();
     c->u_outer.release(); c->u_inner.release(); c->u_J.release(); c->u_M.release(); c->u_vals.release();
-    c->LU.release(); c->CB.release(); c->upd.release();
+    c->LU.release(); c->CB.release(); c->upd.release(); c->trace.release();
     c->keys_a.release(); c->keys_b.release(); c->pay_a.release(); c->pay_b.release(); c->scan.release(); c->cub_tmp.release();
     if (c->xk) cudaFree(c->xk);
     if (c->d_flags) cudaFree(c->d_flags);
@@ -464,6 +464,18 @@ int daecpp_b200_set_vector(daecpp_b200_ctx *c, int32_t which, const double *host
     return upload_vector(c, dst, host);
 }
 
+int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *c, int64_t *out, int64_t cap, int64_t *count)
+{
+    if (!c || !count) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    const int64_t m = (int64_t)c->S.nunit * 12; // factor, forward, backward
+    *count = m;
+    if (!c->trace.p || !out) return DAECPP_B200_OK;
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    DAECPP_CUDA_TRY(c, cudaMemcpy(out, c->trace.p, sizeof(int64_t) * (m < cap ? m : cap), cudaMemcpyDeviceToHost));
+    return DAECPP_B200_OK;
+}
+
 int daecpp_b200_get_stat(daecpp_b200_ctx *c, const char *key, double *value)
 {
     if (!c || !key || !value) return DAECPP_B200_EINVAL;
@@ -493,6 +505,7 @@ int daecpp_b200_get_stat(daecpp_b200_ctx *c, const char *key, double *value)
     else if (k == "n_phase_samples") *value = c->n_phase_samples;
     else if (k == "upd_doubles") *value = (double)c->S.upd_size;
     else if (k == "n_units") *value = c->S.nunit;
+    else if (k == "n_stages") *value = c->S.nstages;
     else if (k == "n_big_fronts") *value = c->S.nbig;
     else if (k == "n_launch_groups") *value = (double)c->S.groups.size();
     else if (k == "factor_smem_bytes") *value = c->S.factor_smem_bytes;
@@ -521,6 +534,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "unit_smem_bytes") { c->sopt.unit_smem_bytes = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "serial_dim") { c->sopt.serial_dim = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "unit_threads") { c->unit_threads = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "trace_units") c->trace_units = value != 0.0;
     else if (k == "max_super") { c->sopt.max_super = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else return fail(c, DAECPP_B200_EINVAL, "unknown option key");
     return DAECPP_B200_OK;

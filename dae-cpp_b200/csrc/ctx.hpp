@@ -123,8 +123,10 @@ struct daecpp_b200_ctx
     std::vector<daecpp_b200::GroupLaunch> groups;
     uint32_t ticket_base = 0; // value of the ticket word before the next unit launch
     int32_t solve_epoch = 0;
-    int unit_threads = 128;
+    int unit_threads = 256;
     int unit_grid_factor = 0, unit_grid_solve = 0; // resident blocks (SMs x occupancy)
+    bool trace_units = false;          // debug: per-unit globaltimer stamps of the factor kernel
+    daecpp_b200::DevBuf<long long> trace;
     bool jvals_from_triplets = false; // fused assembly reads the staged triplet values directly
     daecpp_b200::DevBuf<double> LU, CB, upd;
     double last_alpha = 0.0;

@@ -56,10 +56,12 @@ struct UnitArgs
     int32_t *done;  // backward sweep: epoch at which a unit's unknowns became final
     int32_t epoch;
     int32_t *flags; // [3] pivot failure, [4] dependency wait timed out
+    long long *trace; // optional: 4 globaltimer stamps per unit (debug)
     // factor
     const int32_t *ent_sj, *ent_sm, *ent_dst;
     const double *jvals, *mvals;
     double alpha, pivot_tol;
+    int32_t serial_dim;
     double *LU, *CB;
     // solve
     const int32_t *perm; // nullptr: rhs / solution already in elimination order
@@ -73,6 +75,16 @@ struct UnitArgs
 
 constexpr int SPIN_LIMIT = 1 << 22;
 
+__device__ __forceinline__ void stamp(const UnitArgs &A, int32_t unit, int k)
+{
+    if (A.trace && threadIdx.x == 0)
+    {
+        long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        A.trace[(int64_t)unit * 4 + k] = t;
+    }
+}
+
 __device__ __forceinline__ int32_t ld_volatile(const int32_t *p) { return *(const volatile int32_t *)p; }
 
 // Take the next unit.  Returns false when the launch's units are exhausted.
@@ -85,12 +97,16 @@ __device__ __forceinline__ bool next_ticket(const UnitArgs &A, uint32_t *s_t, ui
     return t < (uint32_t)A.count;
 }
 
-__device__ __forceinline__ void load_blob(const int32_t *Bg, int32_t *B, int nints)
+// Asynchronous global -> shared copy of the unit's blob (LDGSTS, 16 bytes per request, L2 only):
+// the issuing warps go on to the next phase's loads instead of waiting on registers.
+__device__ __forceinline__ void load_blob_async(const int32_t *Bg, int32_t *B, int nints)
 {
-    const int4 *src = reinterpret_cast<const int4 *>(Bg);
-    int4 *dst = reinterpret_cast<int4 *>(B);
-    for (int i = threadIdx.x; i < nints / 4; i += blockDim.x) dst[i] = __ldg(src + i);
+    const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(B);
+    for (int i = threadIdx.x; i < nints / 4; i += blockDim.x)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + 16u * i), "l"(Bg + 4 * i) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
 }
+__device__ __forceinline__ void async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 __device__ __forceinline__ void wait_counter(const UnitArgs &A, const int32_t *word, int32_t target)
 {
@@ -141,11 +157,12 @@ __global__ void k_unit_factor(UnitArgs A)
         const int nw = __ldg(Bg + H_WDOUBLES);
         int32_t *B = reinterpret_cast<int32_t *>(smem);
         double *W = reinterpret_cast<double *>(smem + (size_t)nints * 4);
-        load_blob(Bg, B, nints);
+        stamp(A, unit, 0);
+        load_blob_async(Bg, B, nints);
         for (int i = threadIdx.x; i < nw; i += blockDim.x) W[i] = 0.0;
         __syncthreads();
         {   // Jb = J - (M*alpha) scattered into the frontal arena (two roundings, no FMA: solver.hpp:523)
-            const int32_t e0 = B[H_ENT0], ne = B[H_ENTCOUNT];
+            const int32_t e0 = __ldg(Bg + H_ENT0), ne = __ldg(Bg + H_ENTCOUNT);
             for (int32_t e = threadIdx.x; e < ne; e += blockDim.x)
             {
                 const int32_t sj = __ldg(A.ent_sj + e0 + e), sm = __ldg(A.ent_sm + e0 + e);
@@ -154,6 +171,9 @@ __global__ void k_unit_factor(UnitArgs A)
                 W[__ldg(A.ent_dst + e0 + e)] = __dsub_rn(j, m);
             }
         }
+        async_wait_all();
+        __syncthreads();
+        stamp(A, unit, 1);
         if (B[H_NDEP] > 0)
         {
             wait_counter(A, A.dep + unit, B[H_NDEP]);
@@ -161,6 +181,7 @@ __global__ void k_unit_factor(UnitArgs A)
         }
         else
             __syncthreads();
+        stamp(A, unit, 2);
         const int32_t nlev = B[H_NLEV];
         const int32_t *lp = B + B[H_LEVELS], *lg = lp + nlev + 1;
         const int32_t *fronts = B + B[H_FRONTS];
@@ -169,11 +190,20 @@ __global__ void k_unit_factor(UnitArgs A)
         for (int32_t l = 0; l < nlev; ++l)
         {
             const int32_t G = lg[l], fb = lp[l], fe = lp[l + 1];
-            FOR_LEVEL_FRONTS(G, fb, fe,
-                             unit_ops::factor_front(P, B, fronts + (int64_t)fi * F_SIZE, W, LUu, A.CB, A.pivot_tol, &fail));
+            if (G == 1 && A.serial_dim <= 4)
+            {
+                for (int32_t fi = fb + (int32_t)threadIdx.x; fi < fe; fi += (int32_t)blockDim.x)
+                    unit_ops::factor_front_small<4>(B, fronts + fi * F_SIZE, W, LUu, A.CB, A.pivot_tol, &fail);
+            }
+            else
+            {
+                FOR_LEVEL_FRONTS(G, fb, fe,
+                                 unit_ops::factor_front(P, B, fronts + (int64_t)fi * F_SIZE, W, LUu, A.CB, A.pivot_tol, &fail));
+            }
             __syncthreads();
         }
         if (fail) atomicOr(&A.flags[3], 1);
+        stamp(A, unit, 3);
         const int32_t parent = B[H_PARENT];
         if (parent >= 0)
         {
@@ -199,12 +229,14 @@ __global__ void k_unit_forward(UnitArgs A)
         double *Y = reinterpret_cast<double *>(smem + (size_t)nints * 4);
         double *U = Y + ny;
         double *LUs = U + nu;
-        load_blob(Bg, B, nints);
+        stamp(A, unit, 0);
+        load_blob_async(Bg, B, nints);
         for (int i = threadIdx.x; i < nu; i += blockDim.x) U[i] = 0.0;
         {
             const double *src = A.LU + (uint32_t)__ldg(Bg + H_LU0);
             for (int i = threadIdx.x; i < nlu; i += blockDim.x) LUs[i] = src[i];
         }
+        async_wait_all();
         __syncthreads();
         const int32_t nf = B[H_NF];
         const int32_t *fronts = B + B[H_FRONTS];
@@ -217,6 +249,7 @@ __global__ void k_unit_forward(UnitArgs A)
                 Y[F[F_YOFF] + k] = A.rhs[A.perm ? A.perm[col] : col];
             }
         }
+        stamp(A, unit, 1);
         if (B[H_NDEP] > 0)
         {
             wait_counter(A, A.dep + unit, B[H_NDEP]);
@@ -224,6 +257,7 @@ __global__ void k_unit_forward(UnitArgs A)
         }
         else
             __syncthreads();
+        stamp(A, unit, 2);
         const int32_t nlev = B[H_NLEV];
         const int32_t *lp = B + B[H_LEVELS], *lg = lp + nlev + 1;
         for (int32_t l = 0; l < nlev; ++l)
@@ -237,6 +271,7 @@ __global__ void k_unit_forward(UnitArgs A)
             const int32_t *F = fronts + (int64_t)fi * F_SIZE;
             for (int32_t k = 0; k < F[F_S]; ++k) A.y[F[F_COL0] + k] = Y[F[F_YOFF] + k];
         }
+        stamp(A, unit, 3);
         const int32_t parent = B[H_PARENT];
         if (parent >= 0)
         {
@@ -264,11 +299,13 @@ __global__ void k_unit_backward(UnitArgs A)
         int32_t *B = reinterpret_cast<int32_t *>(smem);
         double *X = reinterpret_cast<double *>(smem + (size_t)nints * 4);
         double *LUs = X + ny + nxr;
-        load_blob(Bg, B, nints);
+        stamp(A, unit, 0);
+        load_blob_async(Bg, B, nints);
         {
             const double *src = A.LU + (uint32_t)__ldg(Bg + H_LU0);
             for (int i = threadIdx.x; i < nlu; i += blockDim.x) LUs[i] = src[i];
         }
+        async_wait_all();
         __syncthreads();
         const int32_t nf = B[H_NF];
         const int32_t *fronts = B + B[H_FRONTS];
@@ -278,8 +315,10 @@ __global__ void k_unit_backward(UnitArgs A)
             for (int32_t k = 0; k < F[F_S]; ++k) X[F[F_YOFF] + k] = A.y[F[F_COL0] + k];
         }
         const int32_t parent = B[H_PARENT];
+        stamp(A, unit, 1);
         if (parent >= 0) wait_counter(A, A.done + parent, A.epoch);
         else __syncthreads();
+        stamp(A, unit, 2);
         {
             const int32_t *xr = B + B[H_XR];
             for (int32_t a = threadIdx.x; a < nxr; a += blockDim.x) X[ny + a] = __ldcg(A.y + xr[a]);
@@ -317,6 +356,7 @@ __global__ void k_unit_backward(UnitArgs A)
                 }
             }
         }
+        stamp(A, unit, 3);
         __threadfence();
         __syncthreads();
         if (threadIdx.x == 0) *(volatile int32_t *)(A.done + unit) = A.epoch;
@@ -361,6 +401,7 @@ UnitArgs base_args(daecpp_b200_ctx *c, const GroupLaunch &g)
     A.epoch = c->solve_epoch;
     A.flags = c->d_flags;
     A.LU = c->LU.p; A.CB = c->CB.p;
+    A.trace = nullptr;
     return A;
 }
 
@@ -431,6 +472,8 @@ int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha)
     A.ent_sj = c->dS.ent_sj.p; A.ent_sm = c->dS.ent_sm.p; A.ent_dst = c->dS.ent_dst.p;
     A.jvals = jvals_of(c); A.mvals = c->M.vals.p;
     A.alpha = alpha; A.pivot_tol = c->pivot_tol;
+    A.serial_dim = c->sopt.serial_dim;
+    if (c->trace_units && c->trace.reserve((size_t)c->S.nunit * 12 + 4) == cudaSuccess) A.trace = c->trace.p;
     const int grid = grid_for(g, c->unit_grid_factor);
     k_unit_factor<<<grid, c->unit_threads, c->S.factor_smem_bytes, c->stream>>>(A);
     c->ticket_base += (uint32_t)(g.count + grid);
@@ -444,6 +487,7 @@ int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct)
     A.perm = direct ? c->dS.perm.p : nullptr;
     A.rhs = direct ? c->b : c->work;
     A.y = c->work; A.upd = c->upd.p;
+    if (c->trace_units && c->trace.p) A.trace = c->trace.p + (size_t)c->S.nunit * 4;
     const int grid = grid_for(g, c->unit_grid_solve);
     k_unit_forward<<<grid, c->unit_threads, c->S.solve_smem_bytes, c->stream>>>(A);
     c->ticket_base += (uint32_t)(g.count + grid);
@@ -460,6 +504,7 @@ int launch_unit_backward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, 
     A.out = direct ? c->dx : nullptr;
     A.xk = c->xk; A.x0 = c->xh[0];
     A.atol = atol; A.rtol = rtol; A.max_err_abs = max_err_abs;
+    if (c->trace_units && c->trace.p) A.trace = c->trace.p + (size_t)c->S.nunit * 8;
     const int grid = grid_for(g, c->unit_grid_solve);
     if (direct && update) k_unit_backward<true><<<grid, c->unit_threads, c->S.solve_smem_bytes, c->stream>>>(A);
     else k_unit_backward<false><<<grid, c->unit_threads, c->S.solve_smem_bytes, c->stream>>>(A);

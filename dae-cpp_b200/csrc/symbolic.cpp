@@ -440,15 +440,14 @@ static bool build_schedule(int32_t n, const int32_t *outer, const int32_t *inner
             else { a += acc[c]; kids.push_back({acc[c], c}); }
         }
         if (a + header_bytes > budget)
-        {
-            std::sort(kids.begin(), kids.end());
-            while (a + header_bytes > budget && !kids.empty())
+        { // cut ALL children: units then come in layers of the tree and the chain of dependent
+          // units from a leaf to the root has length height / (levels per unit), not height
+            for (const auto &kc : kids)
             {
-                const int32_t c = kids.back().second;
-                a -= kids.back().first;
+                const int32_t c = kc.second;
+                a -= kc.first;
                 a += 4 * (X_SIZE + (int64_t)S.r_of(c));
                 cut[c] = 1;
-                kids.pop_back();
             }
         }
         acc[f] = a;
@@ -537,6 +536,7 @@ static bool build_schedule(int32_t n, const int32_t *outer, const int32_t *inner
         if (nunit > open_begin) S.groups.push_back({0, open_begin, nunit, 0});
     }
     S.nunit = nunit;
+    S.nstages = nstage;
 
     // ---- 4. fronts of every unit in (local level, id) order -------------------------------------
     std::vector<int32_t> llev((size_t)nsn, 0);

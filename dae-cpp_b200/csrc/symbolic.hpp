@@ -17,7 +17,7 @@ namespace daecpp_b200
 
 struct SymbolicOptions
 {
-    int leaf_size = 8;      // stop dissecting below this many vertices
+    int leaf_size = 2;      // stop dissecting below this many vertices
     int relax_zeros = 0;    // reserved: relaxed amalgamation budget
     int max_super = 256;    // widest supernode (pivot block) allowed
     int unit_smem_bytes = -1; // shared-memory budget of one subtree unit (-1: chosen from the problem
@@ -62,7 +62,7 @@ struct Symbolic
     std::vector<uint32_t> a_dest;
 
     // ---- subtree-unit schedule (schedule.hpp) ----------------------------------------------
-    int32_t nunit = 0, nbig = 0;
+    int32_t nunit = 0, nbig = 0, nstages = 0;
     std::vector<int32_t> blob;      // all unit blobs, concatenated
     std::vector<int32_t> unit_blob; // [nunit+1] word offsets into blob, ticket order
     std::vector<int32_t> ent_u;     // matrix slot (index into the pattern the analysis was given) ...

@@ -104,6 +104,115 @@ DAE_HD void factor_front(const P &p, const int32_t *B, const int32_t *F, double 
     }
 }
 
+#if defined(__CUDA_ARCH__)
+#define DAE_UNROLL _Pragma("unroll")
+#else
+#define DAE_UNROLL
+#endif
+
+// One-thread fast path for a front of order exactly D (compile-time strides): extend-add in the
+// arena, one load of the D x D block into registers, elimination fully unrolled, and the
+// factor panels / contribution block written straight from registers.
+template <int D>
+DAE_HD void factor_front_fixed(const int32_t *B, const int32_t *F, double *W, double *LUunit, double *CBg,
+                               double pivot_tol, int *fail)
+{
+    const int32_t s = F[F_S], r = D - s;
+    double *A = W + F[F_WOFF];
+    const int32_t *fronts = B + B[H_FRONTS];
+    const int32_t nch = F[F_NCHILD];
+    for (int32_t k = 0; k < nch; ++k)
+    {
+        const int32_t v = B[F[F_CHILD] + k];
+        if (v >= 0)
+        {
+            const int32_t *Fc = fronts + v * F_SIZE;
+            const int32_t sc = Fc[F_S], rc = Fc[F_R], ldc = sc + rc;
+            const double *Cc = W + Fc[F_WOFF] + sc * ldc + sc;
+            const int32_t *rel = B + Fc[F_ROWS];
+            for (int32_t b = 0; b < rc; ++b)
+            {
+                double *Ab = A + rel[b] * D;
+                for (int32_t a = 0; a < rc; ++a) Ab[rel[a]] += Cc[b * ldc + a];
+            }
+        }
+        else
+        {
+            const int32_t *X = B - v;
+            const int32_t rc = X[X_R];
+            const double *Cc = CBg + (uint32_t)X[X_CB];
+            const int32_t *rel = B + X[X_REL];
+            for (int32_t b = 0; b < rc; ++b)
+            {
+                double *Ab = A + rel[b] * D;
+                for (int32_t a = 0; a < rc; ++a) Ab[rel[a]] += DAE_LDCG(Cc + b * rc + a);
+            }
+        }
+    }
+    double a[D][D];
+    DAE_UNROLL
+    for (int j = 0; j < D; ++j)
+        DAE_UNROLL
+        for (int i = 0; i < D; ++i) a[j][i] = A[j * D + i];
+    bool bad = false;
+    DAE_UNROLL
+    for (int k = 0; k < D; ++k)
+    {
+        if (k < s)
+        {
+            const double piv = a[k][k];
+            bad |= !(fabs(piv) > pivot_tol) || std::isinf(piv);
+            const double inv = 1.0 / piv;
+            DAE_UNROLL
+            for (int i = k + 1; i < D; ++i) a[k][i] *= inv;
+            DAE_UNROLL
+            for (int j = k + 1; j < D; ++j)
+                DAE_UNROLL
+                for (int i = k + 1; i < D; ++i) a[j][i] -= a[k][i] * a[j][k];
+        }
+    }
+    if (bad) *fail = 1;
+    double *Lp = LUunit + (uint32_t)F[F_LUOFF];
+    double *Ut = Lp + D * s;
+    const bool ext = F[F_EXTCB] != -1;
+    double *C = CBg + (uint32_t)F[F_EXTCB];
+    DAE_UNROLL
+    for (int j = 0; j < D; ++j)
+    {
+        if (j < s)
+        {
+            DAE_UNROLL
+            for (int i = 0; i < D; ++i) Lp[j * D + i] = a[j][i];
+        }
+        else
+        {
+            DAE_UNROLL
+            for (int i = 0; i < D; ++i)
+            {
+                if (i < s) Ut[i * r + (j - s)] = a[j][i];
+                else
+                {
+                    A[j * D + i] = a[j][i]; // contribution block stays in the arena for the parent
+                    if (ext) C[(j - s) * r + (i - s)] = a[j][i];
+                }
+            }
+        }
+    }
+}
+
+template <int DMAX>
+DAE_HD void factor_front_small(const int32_t *B, const int32_t *F, double *W, double *LUunit, double *CBg,
+                               double pivot_tol, int *fail)
+{
+    switch (F[F_S] + F[F_R])
+    {
+    case 1: factor_front_fixed<1>(B, F, W, LUunit, CBg, pivot_tol, fail); break;
+    case 2: factor_front_fixed<2>(B, F, W, LUunit, CBg, pivot_tol, fail); break;
+    case 3: factor_front_fixed<3>(B, F, W, LUunit, CBg, pivot_tol, fail); break;
+    default: factor_front_fixed<4>(B, F, W, LUunit, CBg, pivot_tol, fail); break;
+    }
+}
+
 // Forward substitution of one front: gather the children's update vectors, solve with the unit
 // lower triangle of the pivot block, push the remainder into this front's update vector.
 // Y: pivot unknowns of the unit, U: update-vector arena, LUs: the unit's factor storage.

@@ -127,6 +127,10 @@ int daecpp_b200_set_vector(daecpp_b200_ctx *ctx, int32_t which, const double *ho
  * "nnz_factor", "factor_flops", "max_front", "ms_symbolic", "ms_last_refactor", "ms_last_solve",
  * "kernels_launched", "n_cold_assembly" ... returns EINVAL for an unknown key. */
 int daecpp_b200_get_stat(daecpp_b200_ctx *ctx, const char *key, double *value);
+/* Debug: with option "trace_units" = 1 the factor kernel stamps %globaltimer (ns) four times per
+ * subtree unit (start, staged, dependencies met, done), in ticket order, for the factor kernel and
+ * then for the forward and the backward solve kernels (3 x n_units x 4 values). */
+int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *ctx, int64_t *out, int64_t cap, int64_t *count);
 /* Tunables, by name ("refine_steps", "pivot_tol", "leaf_size", "use_graph" ...). */
 int daecpp_b200_set_option(daecpp_b200_ctx *ctx, const char *key, double value);
 

@@ -36,7 +36,7 @@ extern "C" int mfemu_solve(int32_t n, const int32_t *outer, const int32_t *inner
     if (!analyse_pattern(n, outer, inner, opt, S, &err)) return 21;
     if (stats)
     {
-        stats[0] = S.nsn; stats[1] = S.nlevels; stats[2] = (double)S.nnz_factor; stats[3] = S.flops;
+        stats[0] = S.nsn; stats[1] = S.nlevels * 1000 + S.nstages; stats[2] = (double)S.nnz_factor; stats[3] = S.flops;
         stats[4] = S.max_front; stats[5] = (double)S.lu_size; stats[6] = (double)S.cb_size; stats[7] = S.max_pivot_block;
         stats[8] = S.nunit; stats[9] = S.nbig; stats[10] = (double)S.groups.size(); stats[11] = S.factor_smem_bytes;
     }
@@ -59,10 +59,17 @@ extern "C" int mfemu_solve(int32_t n, const int32_t *outer, const int32_t *inner
                 W.assign((size_t)B[H_WDOUBLES] + 1, 0.0);
                 for (int32_t e = 0; e < B[H_ENTCOUNT]; ++e) W[S.ent_dst[B[H_ENT0] + e]] = vals[S.ent_u[B[H_ENT0] + e]];
                 const int32_t *lp = B + B[H_LEVELS];
+                const int32_t *lg = lp + B[H_NLEV] + 1;
                 for (int32_t l = 0; l < B[H_NLEV]; ++l)
                     for (int32_t fi = lp[l]; fi < lp[l + 1]; ++fi)
-                        unit_ops::factor_front(P, B, B + B[H_FRONTS] + (int64_t)fi * F_SIZE, W.data(),
-                                               LU.data() + (uint32_t)B[H_LU0], CB.data(), 0.0, &fail);
+                    {
+                        if (lg[l] == 1 && opt.serial_dim <= 4) // the kernels' register fast path
+                            unit_ops::factor_front_small<4>(B, B + B[H_FRONTS] + (int64_t)fi * F_SIZE, W.data(),
+                                                            LU.data() + (uint32_t)B[H_LU0], CB.data(), 0.0, &fail);
+                        else
+                            unit_ops::factor_front(P, B, B + B[H_FRONTS] + (int64_t)fi * F_SIZE, W.data(),
+                                                   LU.data() + (uint32_t)B[H_LU0], CB.data(), 0.0, &fail);
+                    }
             }
         }
         else
