@@ -23,7 +23,7 @@ SYMBOLS = [
     "daecpp_b200_rollback", "daecpp_b200_set_mass", "daecpp_b200_set_jacobian", "daecpp_b200_residual",
     "daecpp_b200_refactor", "daecpp_b200_solve_update", "daecpp_b200_accept_step", "daecpp_b200_set_rhs",
     "daecpp_b200_solve", "daecpp_b200_get_csc", "daecpp_b200_get_vector", "daecpp_b200_set_vector", "daecpp_b200_get_stat",
-    "daecpp_b200_set_option", "daecpp_b200_iteration_resident", "daecpp_b200_event_mark", "daecpp_b200_event_elapsed_ms", "daecpp_b200_debug_unit_trace",
+    "daecpp_b200_set_option", "daecpp_b200_iteration_resident", "daecpp_b200_event_mark", "daecpp_b200_event_elapsed_ms", "daecpp_b200_debug_unit_trace", "daecpp_b200_host_register", "daecpp_b200_host_unregister",
 ]
 
 
@@ -41,6 +41,8 @@ def load():
     lib.daecpp_b200_host_alloc.restype = _vp
     lib.daecpp_b200_host_free.argtypes = [_vp]
     lib.daecpp_b200_host_free.restype = None
+    lib.daecpp_b200_host_register.argtypes = [_vp, C.c_size_t]
+    lib.daecpp_b200_host_unregister.argtypes = [_vp]
     lib.daecpp_b200_set_state.argtypes = [_vp, _f64]
     lib.daecpp_b200_get_xk.argtypes = [_vp, _f64]
     lib.daecpp_b200_rollback.argtypes = [_vp]

@@ -73,6 +73,12 @@ int ensure_stage(daecpp_b200_ctx *c, size_t count)
 
 int upload_vector(daecpp_b200_ctx *c, double *dst, const double *src_host)
 {
+    if (c->pinned_io)
+    { // the caller guarantees page-locked buffers (overlay solver.hpp): one DMA, no staging copy
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(dst, src_host, sizeof(double) * c->n, cudaMemcpyHostToDevice, c->stream));
+        DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        return DAECPP_B200_OK;
+    }
     // through the pinned stage so the copy is one DMA regardless of how the caller allocated
     int rc = ensure_stage(c, c->n);
     if (rc) return rc;
@@ -84,6 +90,12 @@ int upload_vector(daecpp_b200_ctx *c, double *dst, const double *src_host)
 
 int download_vector(daecpp_b200_ctx *c, double *dst_host, const double *src)
 {
+    if (c->pinned_io)
+    {
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(dst_host, src, sizeof(double) * c->n, cudaMemcpyDeviceToHost, c->stream));
+        DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+        return DAECPP_B200_OK;
+    }
     int rc = ensure_stage(c, c->n);
     if (rc) return rc;
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_stage, src, sizeof(double) * c->n, cudaMemcpyDeviceToHost, c->stream));
@@ -183,6 +195,17 @@ void daecpp_b200_host_free(void *p)
     if (p) cudaFreeHost(p);
 }
 
+int daecpp_b200_host_register(void *p, size_t bytes)
+{
+    if (!p || !bytes) return DAECPP_B200_EINVAL;
+    return cudaHostRegister(p, bytes, cudaHostRegisterPortable) == cudaSuccess ? DAECPP_B200_OK : DAECPP_B200_ECUDA;
+}
+int daecpp_b200_host_unregister(void *p)
+{
+    if (!p) return DAECPP_B200_EINVAL;
+    return cudaHostUnregister(p) == cudaSuccess ? DAECPP_B200_OK : DAECPP_B200_ECUDA;
+}
+
 int daecpp_b200_set_state(daecpp_b200_ctx *c, const double *x0)
 {
     if (!c || !x0) return DAECPP_B200_EINVAL;
@@ -235,10 +258,15 @@ int daecpp_b200_residual(daecpp_b200_ctx *c, const double *f_host, int32_t order
     double w[5];
     if (!bdf_weights(order, dt, w)) return fail(c, DAECPP_B200_EINVAL, "unsupported time integration order");
     if (alpha_out) *alpha_out = w[0];
-    int rc = ensure_stage(c, c->n);
-    if (rc) return rc;
-    std::memcpy(c->h_stage, f_host, sizeof(double) * c->n);
-    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->f, c->h_stage, sizeof(double) * c->n, cudaMemcpyHostToDevice, c->stream));
+    int rc = DAECPP_B200_OK;
+    if (c->pinned_io)
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->f, f_host, sizeof(double) * c->n, cudaMemcpyHostToDevice, c->stream));
+    else
+    {
+        if ((rc = ensure_stage(c, c->n))) return rc;
+        std::memcpy(c->h_stage, f_host, sizeof(double) * c->n);
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->f, c->h_stage, sizeof(double) * c->n, cudaMemcpyHostToDevice, c->stream));
+    }
     rc = launch_residual(c, order, w);
     if (rc) return rc;
     // the stage buffer is reused by the next call
@@ -534,6 +562,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "unit_smem_bytes") { c->sopt.unit_smem_bytes = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "serial_dim") { c->sopt.serial_dim = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "unit_threads") { c->unit_threads = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "pinned_io") c->pinned_io = value != 0.0;
     else if (k == "trace_units") c->trace_units = value != 0.0;
     else if (k == "max_super") { c->sopt.max_super = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else return fail(c, DAECPP_B200_EINVAL, "unknown option key");

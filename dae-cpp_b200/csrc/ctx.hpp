@@ -139,6 +139,7 @@ struct daecpp_b200_ctx
     // options
     int refine_steps = 0;
     bool assemble_only = false;
+    bool pinned_io = false; // host vectors handed to the ABI are page-locked: no staging copies
     double pivot_tol = 0.0;
 
     // statistics

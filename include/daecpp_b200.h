@@ -63,6 +63,12 @@ const char *daecpp_b200_version(void);
 void *daecpp_b200_host_alloc(size_t bytes);
 void daecpp_b200_host_free(void *p);
 
+/* Page-lock an existing host range (the storage behind sparse_matrix::A/i/j keeps its
+ * std::vector type, sparse-matrix.hpp:36-40; the overlay solver registers it once it is large
+ * and stable).  Failure is not fatal: the copies then go through pageable memory. */
+int daecpp_b200_host_register(void *p, size_t bytes);
+int daecpp_b200_host_unregister(void *p);
+
 /* ---- state --------------------------------------------------------------------------- */
 /* xk = x[0] = x0, order/dt history cleared       (solver.hpp:310-313) */
 int daecpp_b200_set_state(daecpp_b200_ctx *ctx, const double *x0);
