@@ -1,0 +1,123 @@
+"""Golden vectors produced by the reference itself (tests/golden/make_golden.py, run in the build
+container where /root/reference exists).  CPU part: the oracle port against them.  GPU part: the
+CUDA path through the C ABI, and whole daecpp::solve() trajectories through the overlay header."""
+import glob
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+NEWTON = sorted(os.path.basename(p)[7:-4] for p in glob.glob(os.path.join(GOLD, "newton_*.npz")))
+TRAJ = sorted(os.path.basename(p)[5:-5] for p in glob.glob(os.path.join(GOLD, "traj_*.json")))
+
+
+def _load(name):
+    g = np.load(os.path.join(GOLD, f"newton_{name}.npz"))
+    return {k: g[k] for k in g.files}
+
+
+def test_fixtures_present():
+    assert len(NEWTON) >= 4 and len(TRAJ) >= 6
+
+
+@pytest.mark.parametrize("name", NEWTON)
+def test_oracle_port_matches_reference_golden(name):
+    g = _load(name)
+    n, order = int(g["n"]), int(g["order"])
+    J = (g["JA"], g["Ji"], g["Jj"]); M = (g["MA"], g["Mi"], g["Mj"])
+    d = np.zeros(n); b = np.zeros(n)
+    alpha = O.port.oracle_time_derivative(n, order, np.ascontiguousarray(g["dt"]), np.ascontiguousarray(g["xk"]),
+                                          np.ascontiguousarray(g["hist"].reshape(-1)), d)
+    assert alpha == float(g["alpha"])
+    assert d.tobytes() == g["dxdt"].tobytes()
+    outer, inner, vals = O.assemble_jb(O.port, n, J, M, alpha)
+    assert outer.tobytes() == g["outer"].tobytes() and inner.tobytes() == g["inner"].tobytes()
+    assert vals.tobytes() == g["vals"].tobytes()
+    O.port.oracle_residual(n, *O.convert(O.port, n, M), d, np.ascontiguousarray(g["f"]), b)
+    assert b.tobytes() == g["b"].tobytes()
+    dx = np.zeros(n)
+    assert O.port.oracle_lu_solve(n, outer, inner, vals, b, dx) == 0
+    eta, r2 = O.backward_error(n, (outer, inner, vals), dx, b)
+    eta_ref, r2_ref = O.backward_error(n, (outer, inner, vals), np.ascontiguousarray(g["dx"]), b)
+    assert eta <= 1e-12 and eta_ref <= 1e-12
+    assert np.max(np.abs(dx - g["dx"])) <= 1e-8 * np.max(np.abs(g["dx"]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", NEWTON)
+def test_cuda_newton_step_matches_reference_golden(name):
+    from gpu_lib import binding as B
+    g = _load(name)
+    n, order = int(g["n"]), int(g["order"])
+    c = B.Context(n)
+    c.set_state(g["xk"])
+    for k in range(4):
+        c.set_vector("x%d" % k, g["hist"][k])
+    c.set_mass((g["MA"], g["Mi"], g["Mj"]))
+    c.set_jacobian((g["JA"], g["Ji"], g["Jj"]))
+    alpha = c.residual(g["f"], order, g["dt"])
+    assert alpha == float(g["alpha"])
+    assert c.get_vector("dxdt").tobytes() == g["dxdt"].tobytes()
+    assert c.get_vector("b").tobytes() == g["b"].tobytes()
+    c.refactor(alpha)
+    outer, inner, vals = c.get_csc(2)
+    assert outer.tobytes() == g["outer"].tobytes() and inner.tobytes() == g["inner"].tobytes()
+    assert vals.tobytes() == g["vals"].tobytes()
+    rc, flags = c.solve_update(1e-6, 1e-6)
+    assert rc == 0
+    dx = c.get_vector("dx")
+    csc = (g["outer"], g["inner"], g["vals"])
+    eta, r2 = O.backward_error(n, csc, dx, g["b"])
+    _, r2_ref = O.backward_error(n, csc, np.ascontiguousarray(g["dx"]), g["b"])
+    assert eta <= 1e-12
+    assert r2 <= 10.0 * r2_ref + 1e-12 * np.linalg.norm(g["b"])
+    assert np.max(np.abs(dx - g["dx"])) <= 1e-8 * np.max(np.abs(g["dx"]))
+    assert c.get_xk().tobytes() == (g["xk"] + dx).tobytes()  # xk += dx (solver.hpp:617)
+    c.close()
+
+
+def _traj_exe():
+    exe = os.path.join(ROOT, "hostcpp", "_bin", "traj_dump")
+    if not os.path.exists(exe):
+        pytest.skip("hostcpp/_bin/traj_dump not built (needs /root/reference at build time)")
+    return exe
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", TRAJ)
+def test_trajectory_matches_reference_golden(name, tmp_path):
+    """daecpp::solve() through the overlay header + libdaecpp_b200.so vs the unmodified reference:
+    final state within 10 x (atol, rtol), accepted steps within 2 %, same exit code
+    (BASELINE.json north_star; SURVEY.md 8(c) definition 3)."""
+    meta = json.load(open(os.path.join(GOLD, f"traj_{name}.json")))
+    want = np.fromfile(os.path.join(GOLD, f"traj_{name}.f64"))
+    out = tmp_path / "x.f64"
+    p = subprocess.run([_traj_exe()] + meta["argv"] + [f"out={out}"], stdout=subprocess.PIPE, text=True, timeout=600)
+    got_meta = json.loads(p.stdout.strip().splitlines()[-1])
+    got = np.fromfile(out)
+    assert got_meta["impl"] == "b200"
+    assert got_meta["status"] == meta["status"] == p.returncode
+    assert abs(got_meta["steps"] - meta["steps"]) <= max(0.02 * meta["steps"], 0.5)
+    assert got_meta["t_final"] == meta["t_final"]
+    tol = 10.0 * meta["tol"]
+    assert got.shape == want.shape
+    assert np.all(np.abs(got - want) <= tol + tol * np.abs(want)), float(np.max(np.abs(got - want)))
+
+
+@pytest.mark.gpu
+def test_reference_gtest_suite_against_overlay():
+    """The reference's own 56 gtest cases (tests/test_*.cpp, compiled unmodified) with the overlay
+    solver.hpp first on the include path -- every daecpp::solve in them runs on the device."""
+    exe = os.path.join(ROOT, "hostcpp", "_bin", "dae-cpp-test")
+    if not os.path.exists(exe):
+        pytest.skip("hostcpp/_bin/dae-cpp-test not built (needs /root/reference at build time)")
+    p = subprocess.run([exe, "--gtest_brief=1"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    tail = p.stdout[-2000:]
+    assert p.returncode == 0, tail
+    assert "[  PASSED  ] 56 tests." in p.stdout, tail
