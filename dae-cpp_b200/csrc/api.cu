@@ -163,7 +163,7 @@ void daecpp_b200_destroy(daecpp_b200_ctx *c)
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    c->M.release(); c->J.release(); c->dS.release();
+    c->M.release(); c->J.release(); c->dS.release(); c->dC.release();
     c->m_rowptr.release(); c->m_rowslot.release(); c->m_rowcol.release();
     c->u_outer.release(); c->u_inner.release(); c->u_J.release(); c->u_M.release(); c->u_vals.release();
     c->LU.release(); c->CB.release(); c->upd.release(); c->trace.release();
@@ -516,9 +516,15 @@ int daecpp_b200_get_stat(daecpp_b200_ctx *c, const char *key, double *value)
     else if (k == "ms_symbolic") *value = c->ms_symbolic;
     else if (k == "ms_last_refactor") *value = c->ms_last_refactor;
     else if (k == "ms_last_solve") *value = c->ms_last_solve;
-    else if (k == "n_fronts") *value = c->S.nsn;
-    else if (k == "n_levels") *value = c->S.nlevels;
-    else if (k == "nnz_factor") *value = (double)c->S.nnz_factor;
+    else if (k == "chain_block") *value = c->CH.active ? c->CH.B : 0;
+    else if (k == "chain_levels") *value = c->CH.active ? (double)c->CH.levels.size() : 0;
+    else if (k == "chain_tiles") *value = c->CH.active ? c->CH.levels[0].ntiles : 0;
+    else if (k == "chain_identity_perm") *value = c->CH.active && c->CH.identity_perm ? 1 : 0;
+    else if (k == "n_fronts") *value = c->CH.active ? c->CH.m : c->S.nsn;
+    else if (k == "n_levels") *value = c->CH.active ? 3.0 * (double)c->CH.levels.size() : c->S.nlevels;
+    else if (k == "nnz_factor") *value = c->CH.active ? (double)c->CH.nnz_factor : (double)c->S.nnz_factor;
+    else if (k == "lu_doubles" && c->CH.active) *value = (double)c->CH.fac_doubles;
+    else if (k == "schedule_bytes" && c->CH.active) *value = 12.0 * (double)c->CH.ent_u.size();
     else if (k == "factor_flops") *value = c->S.flops;
     else if (k == "max_front") *value = c->S.max_front;
     else if (k == "lu_doubles") *value = (double)c->S.lu_size;
@@ -563,6 +569,9 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "serial_dim") { c->sopt.serial_dim = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "unit_threads") { c->unit_threads = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "pinned_io") c->pinned_io = value != 0.0;
+    else if (k == "chain") { c->chain_enabled = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "chain_min_n") { c->chain_min_n = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "chain_max_block") { c->chain_max_b = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "trace_units") c->trace_units = value != 0.0;
     else if (k == "max_super") { c->sopt.max_super = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else return fail(c, DAECPP_B200_EINVAL, "unknown option key");

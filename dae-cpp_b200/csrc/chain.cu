@@ -1,0 +1,370 @@
+// Block-chain numeric LU refactorisation and triangular solves (chain.hpp, chain_ops.hpp).
+//
+// Role replaced: Eigen::SparseLU::factorize / _solve_impl behind linsolver.compute(Jb) and
+// linsolver.solve(b) (dae-cpp/solver.hpp:537,558) for block-tridiagonal patterns, with the
+// assembly Jb = J - M*alpha (solver.hpp:523), the permutation and the error check / update loop
+// (solver.hpp:590-619) fused into the first and the last kernel.
+//
+// One CTA owns a tile of T*Q0 consecutive block rows.  The matrix values of the tile are gathered
+// through the slot map into shared memory with coalesced loads, each thread eliminates its own
+// chunk of Q0 rows out of shared memory and streams the factors to HBM in a [step][field][thread]
+// layout (every store and every later load of the solves is a full 256-byte warp transaction),
+// two more levels are swept inside the CTA, and one row of the grid-level reduced system leaves
+// the CTA.  That reduced system is factored by the same kernel run on it (one CTA for up to
+// T*Q0 tiles).  No index table other than the slot map is read: the hierarchy is implicit.
+// HBM traffic per refactorisation: slot map + matrix values in, 5*B*B doubles per block row out.
+#include "chain.hpp"
+#include "chain_ops.hpp"
+#include "ctx.hpp"
+
+namespace daecpp_b200
+{
+namespace
+{
+using namespace chain;
+
+struct ChainArgs
+{
+    int32_t rows, ntiles, n, is_top;
+    // factor
+    const int32_t *sj, *sm, *flags;
+    const double *jv, *mv;
+    double alpha, tol;
+    double *F, *Y;
+    const double *red_in;
+    double *red_out;
+    // solve
+    const double *rv_in;
+    double *rv_out;
+    const double *rhs;
+    const int32_t *perm;
+    double *xlev;      // solution of this level's rows (levels >= 1)
+    const double *xup; // solution of the level above = this level's separators
+    double *out, *xk;
+    const double *x0;
+    double atol, rtol, max_err_abs;
+    int32_t update;
+    int32_t *dflags;
+    // ensemble: member = blockIdx.y, strides in elements
+    const double *alpha_arr;
+    int64_t s_jv, s_mv, s_F, s_Y, s_red, s_rv, s_x, s_vec;
+};
+
+template <int B, bool FIRST>
+__global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
+{
+    using D = Dim<B>;
+    extern __shared__ __align__(16) unsigned char smem[];
+    FactorShared<B> &sh = *reinterpret_cast<FactorShared<B> *>(smem);
+    const int t = threadIdx.x, tile = blockIdx.x;
+    const int64_t mb = blockIdx.y;
+    double *Ft = a.F + mb * a.s_F + (size_t)tile * D::TILE_F;
+    const int nvalid = min(D::ROWS, a.rows - tile * D::ROWS);
+    if (FIRST)
+    {
+        const double alpha = a.alpha_arr ? a.alpha_arr[mb] : a.alpha;
+        stage_matrix_first<B>(t, D::T, tile, sh.S, a.sj, a.sm, a.flags, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
+    }
+    else
+        stage_matrix_reduced<B>(t, D::T, tile, a.rows, sh.S, a.red_in + mb * a.s_red);
+    __syncthreads();
+    int fail = 0;
+    {
+        Mat<B> G, Dk, SL, H;
+        factor_phase0<B>(t, nvalid, sh, Ft, a.tol, fail, G, Dk, SL, H);
+        __syncthreads();
+        factor_store1<B>(t, sh, G, Dk, SL, H);
+    }
+    __syncthreads();
+    factor_phase1<B>(t, nvalid, sh, Ft, a.tol, fail);
+    __syncthreads();
+    if (t == 0) factor_phase2<B>(tile, a.ntiles, a.is_top != 0, sh, Ft, a.red_out + mb * a.s_red, a.tol, fail);
+    if (fail) atomicOr(&a.dflags[3], 1);
+}
+
+// backward sweep of one tile and the write-out of its unknowns; sh.xR / sh.xL are set
+template <int B, bool FIRST>
+__device__ __forceinline__ void backward_tail(const ChainArgs &a, SolveShared<B> &sh, int t, int tile, int64_t mb, int nvalid,
+                                              double *Ft, double *Yt)
+{
+    using D = Dim<B>;
+    if (t == 0) backward_phase2<B>(sh, Ft, Yt);
+    __syncthreads();
+    backward_phase1<B>(t, nvalid, sh, Ft, Yt);
+    __syncthreads();
+    backward_phase0<B>(t, nvalid, sh, Ft, Yt);
+    __syncthreads();
+    if (FIRST)
+    {
+        if (!a.out) return;
+        double *out = a.out + mb * a.s_vec;
+        int flag = 0;
+        for (int q = 0; q < B; ++q)
+            for (int row = t; row < nvalid; row += D::T)
+            {
+                const int64_t k = ((int64_t)tile * D::ROWS + row) * B + q;
+                if (k >= a.n) continue;
+                const double v = sh.R[(size_t)q * D::RP + sidx<B>(row)];
+                const int64_t o = a.perm ? a.perm[k] : k;
+                out[o] = v;
+                if (a.update)
+                {   // dae-cpp/solver.hpp:590-619
+                    const double e = fabs(v);
+                    if (e > a.max_err_abs || isnan(v)) flag |= DAECPP_B200_DIVERGED;
+                    const double xa = fabs(a.x0[mb * a.s_vec + o]);
+                    if (xa > 1e-14 && __ddiv_rn(e, xa) > a.rtol) flag |= DAECPP_B200_NOT_CONVERGED;
+                    if (e > a.atol) flag |= DAECPP_B200_NOT_CONVERGED;
+                    double *xk = a.xk + mb * a.s_vec;
+                    xk[o] = __dadd_rn(xk[o], v);
+                }
+            }
+        if (flag) atomicOr(&a.dflags[2], flag);
+    }
+    else
+    {
+        double *xl = a.xlev + mb * a.s_x;
+        for (int q = 0; q < B; ++q)
+            for (int row = t; row < nvalid; row += D::T)
+                xl[((size_t)tile * D::ROWS + row) * B + q] = sh.R[(size_t)q * D::RP + sidx<B>(row)];
+    }
+}
+
+// forward sweep of one tile; the single tile of the top level carries on into the backward sweep
+template <int B, bool FIRST>
+__global__ void __launch_bounds__(Cfg<B>::T) k_chain_forward(ChainArgs a)
+{
+    using D = Dim<B>;
+    extern __shared__ __align__(16) unsigned char smem[];
+    SolveShared<B> &sh = *reinterpret_cast<SolveShared<B> *>(smem);
+    const int t = threadIdx.x, tile = blockIdx.x;
+    const int64_t mb = blockIdx.y;
+    double *Ft = a.F + mb * a.s_F + (size_t)tile * D::TILE_F;
+    double *Yt = a.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
+    const int nvalid = min(D::ROWS, a.rows - tile * D::ROWS);
+    if (FIRST) stage_rhs_first<B>(t, D::T, tile, a.n, sh.R, a.rhs + mb * a.s_vec, a.perm);
+    else stage_rhs_reduced<B>(t, D::T, tile, a.rows, sh.R, a.rv_in + mb * a.s_rv);
+    __syncthreads();
+    forward_phase0<B>(t, nvalid, sh, Ft, Yt);
+    __syncthreads();
+    forward_phase1<B>(t, nvalid, sh, Ft, Yt);
+    __syncthreads();
+    if (t == 0) forward_phase2<B>(tile, a.ntiles, a.is_top != 0, sh, Ft, Yt, a.rv_out + mb * a.s_rv);
+    if (!a.is_top) return;
+    __syncthreads();
+    backward_tail<B, FIRST>(a, sh, t, tile, mb, nvalid, Ft, Yt);
+}
+
+template <int B, bool FIRST>
+__global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
+{
+    using D = Dim<B>;
+    extern __shared__ __align__(16) unsigned char smem[];
+    SolveShared<B> &sh = *reinterpret_cast<SolveShared<B> *>(smem);
+    const int t = threadIdx.x, tile = blockIdx.x;
+    const int64_t mb = blockIdx.y;
+    double *Ft = a.F + mb * a.s_F + (size_t)tile * D::TILE_F;
+    double *Yt = a.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
+    const int nvalid = min(D::ROWS, a.rows - tile * D::ROWS);
+    if (t < B)
+    {
+        const double *xup = a.xup + mb * a.s_x;
+        sh.xR[t] = xup[(size_t)tile * B + t];
+        sh.xL[t] = tile > 0 ? xup[(size_t)(tile - 1) * B + t] : 0.0;
+    }
+    __syncthreads();
+    backward_tail<B, FIRST>(a, sh, t, tile, mb, nvalid, Ft, Yt);
+}
+
+// slot map -> sources of the values: sj = index into the staged triplet values (or J's
+// compressed values), sm = slot of M; negative codes (-1 absent, -2 one) pass through
+__global__ void k_chain_compose(int64_t ne, int32_t per_fe, const int32_t *__restrict__ ent_u, const int32_t *__restrict__ uJ,
+                                const int32_t *__restrict__ uM, const int32_t *__restrict__ srcJ, int32_t *__restrict__ sj,
+                                int32_t *__restrict__ sm, int32_t *__restrict__ flags)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= ne) return;
+    const int32_t u = ent_u[e];
+    int32_t j = u, m = -1;
+    if (u >= 0 && uJ)
+    {
+        const int32_t a = uJ[u];
+        j = a < 0 ? -1 : (srcJ ? srcJ[a] : a);
+        m = uM[u];
+    }
+    sj[e] = j;
+    sm[e] = m;
+    if (m >= 0) atomicOr(&flags[e / per_fe], TF_MASS);
+}
+
+} // namespace
+
+namespace
+{
+
+template <int B> constexpr size_t factor_smem() { return sizeof(FactorShared<B>); }
+template <int B> constexpr size_t solve_smem() { return sizeof(SolveShared<B>); }
+
+template <int B> int set_attributes(daecpp_b200_ctx *c)
+{
+    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_factor<B, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)factor_smem<B>()));
+    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_factor<B, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)factor_smem<B>()));
+    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_forward<B, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)solve_smem<B>()));
+    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_forward<B, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)solve_smem<B>()));
+    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_backward<B, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)solve_smem<B>()));
+    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_backward<B, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)solve_smem<B>()));
+    return DAECPP_B200_OK;
+}
+
+template <class T> int upload_vec(daecpp_b200_ctx *c, DevBuf<T> &d, const std::vector<T> &h)
+{
+    DAECPP_CUDA_TRY(c, d.reserve(h.size() ? h.size() : 1));
+    if (!h.empty())
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(d.p, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, c->stream));
+    return DAECPP_B200_OK;
+}
+
+ChainArgs level_args(daecpp_b200_ctx *c, int g)
+{
+    const Plan &P = c->CH;
+    const Level &L = P.levels[g];
+    ChainArgs a{};
+    a.rows = L.rows; a.ntiles = L.ntiles; a.n = P.n;
+    a.is_top = (g + 1 == (int)P.levels.size());
+    a.F = c->dC.F.p + L.fac0;
+    a.Y = c->dC.Y.p + L.y0;
+    a.red_out = c->dC.red.p + L.red0;
+    a.rv_out = c->dC.rv.p + L.rv0;
+    if (g > 0)
+    {
+        a.red_in = c->dC.red.p + P.levels[g - 1].red0;
+        a.rv_in = c->dC.rv.p + P.levels[g - 1].rv0;
+        a.xlev = c->dC.x.p + L.x0;
+    }
+    if (!a.is_top) a.xup = c->dC.x.p + P.levels[g + 1].x0;
+    a.dflags = c->d_flags;
+    a.tol = c->pivot_tol;
+    return a;
+}
+
+template <int B> void launch_factor(daecpp_b200_ctx *c, const ChainArgs &a, bool first)
+{
+    const dim3 grid(a.ntiles, 1);
+    if (first) k_chain_factor<B, true><<<grid, Cfg<B>::T, factor_smem<B>(), c->stream>>>(a);
+    else k_chain_factor<B, false><<<grid, Cfg<B>::T, factor_smem<B>(), c->stream>>>(a);
+}
+template <int B> void launch_forward(daecpp_b200_ctx *c, const ChainArgs &a, bool first)
+{
+    const dim3 grid(a.ntiles, 1);
+    if (first) k_chain_forward<B, true><<<grid, Cfg<B>::T, solve_smem<B>(), c->stream>>>(a);
+    else k_chain_forward<B, false><<<grid, Cfg<B>::T, solve_smem<B>(), c->stream>>>(a);
+}
+template <int B> void launch_backward(daecpp_b200_ctx *c, const ChainArgs &a, bool first)
+{
+    const dim3 grid(a.ntiles, 1);
+    if (first) k_chain_backward<B, true><<<grid, Cfg<B>::T, solve_smem<B>(), c->stream>>>(a);
+    else k_chain_backward<B, false><<<grid, Cfg<B>::T, solve_smem<B>(), c->stream>>>(a);
+}
+
+#define CHAIN_DISPATCH(B, CALL)              \
+    switch (B)                               \
+    {                                        \
+    case 1: CALL(1); break;                  \
+    case 2: CALL(2); break;                  \
+    default: CALL(3); break;                 \
+    }
+
+} // namespace
+
+// Recognise the pattern as a block chain; on success ship the plan and compose the slot map.
+// c->CH.active tells the caller whether the chain path took the pattern.
+int chain_try_setup(daecpp_b200_ctx *c, int32_t n, const int32_t *outer, const int32_t *inner)
+{
+    Plan &P = c->CH;
+    P.active = false;
+    if (!c->chain_enabled || n < c->chain_min_n) return DAECPP_B200_OK;
+    if (!detect(n, outer, inner, c->chain_max_b, P)) return DAECPP_B200_OK;
+    int rc;
+    if ((rc = upload_vec(c, c->dC.ent_u, P.ent_u))) return rc;
+    if ((rc = upload_vec(c, c->dC.flags, P.tile_flags))) return rc;
+    if (!P.identity_perm && (rc = upload_vec(c, c->dC.perm, P.perm))) return rc;
+    DAECPP_CUDA_TRY(c, c->dC.sj.reserve(P.ent_u.size() + 1));
+    DAECPP_CUDA_TRY(c, c->dC.sm.reserve(P.ent_u.size() + 1));
+    DAECPP_CUDA_TRY(c, c->dC.F.reserve((size_t)P.fac_doubles + 1));
+    DAECPP_CUDA_TRY(c, c->dC.Y.reserve((size_t)P.y_doubles + 1));
+    DAECPP_CUDA_TRY(c, c->dC.red.reserve((size_t)P.red_doubles + 1));
+    DAECPP_CUDA_TRY(c, c->dC.rv.reserve((size_t)P.rv_doubles + 1));
+    DAECPP_CUDA_TRY(c, c->dC.x.reserve((size_t)P.x_doubles + 1));
+#define SETATTR(B) rc = set_attributes<B>(c)
+    CHAIN_DISPATCH(P.B, SETATTR)
+#undef SETATTR
+    if (rc) return rc;
+    // sources of the matrix values (same rule as the general path: the staged triplet values when
+    // every slot has exactly one triplet, else J's duplicate-summed compressed values)
+    c->jvals_from_triplets = !c->direct_csc && c->J.no_duplicates && c->J.nnz > 0;
+    const int32_t *uJ = c->direct_csc ? nullptr : c->u_J.p;
+    const int32_t *srcJ = (!c->direct_csc && c->jvals_from_triplets) ? c->J.src.p : nullptr;
+    const int64_t ne = (int64_t)P.ent_u.size();
+    const int32_t per_fe = rows_per_tile(P.B) + 1;
+    k_chain_compose<<<(int)((ne + 255) / 256), 256, 0, c->stream>>>(ne, per_fe, c->dC.ent_u.p, uJ, c->u_M.p, srcJ, c->dC.sj.p,
+                                                                  c->dC.sm.p, c->dC.flags.p);
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    c->kernels += 1;
+    return DAECPP_B200_OK;
+}
+
+int chain_refactor_async(daecpp_b200_ctx *c, double alpha)
+{
+    const Plan &P = c->CH;
+    const double *jv = c->direct_csc ? c->u_vals.p : (c->jvals_from_triplets ? c->J.A.p : c->J.vals.p);
+    for (int g = 0; g < (int)P.levels.size(); ++g)
+    {
+        ChainArgs a = level_args(c, g);
+        if (g == 0)
+        {
+            a.sj = c->dC.sj.p; a.sm = c->dC.sm.p; a.flags = c->dC.flags.p;
+            a.jv = jv; a.mv = c->M.vals.p; a.alpha = alpha;
+        }
+#define LF(B) launch_factor<B>(c, a, g == 0)
+        CHAIN_DISPATCH(P.B, LF)
+#undef LF
+        c->kernels += 1;
+    }
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    return DAECPP_B200_OK;
+}
+
+// b -> dx (and, fused into the last kernel, the error checks and xk += dx)
+int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, double max_err_abs)
+{
+    const Plan &P = c->CH;
+    const int nlev = (int)P.levels.size();
+    auto first_args = [&](ChainArgs &a) {
+        a.rhs = c->b;
+        a.perm = P.identity_perm ? nullptr : c->dC.perm.p;
+        a.out = c->dx; a.xk = c->xk; a.x0 = c->xh[0];
+        a.atol = atol; a.rtol = rtol; a.max_err_abs = max_err_abs;
+        a.update = fuse_update ? 1 : 0;
+    };
+    for (int g = 0; g < nlev; ++g)
+    {
+        ChainArgs a = level_args(c, g);
+        if (g == 0) first_args(a);
+#define LW(B) launch_forward<B>(c, a, g == 0)
+        CHAIN_DISPATCH(P.B, LW)
+#undef LW
+        c->kernels += 1;
+    }
+    for (int g = nlev - 2; g >= 0; --g)
+    {
+        ChainArgs a = level_args(c, g);
+        if (g == 0) first_args(a);
+#define LB(B) launch_backward<B>(c, a, g == 0)
+        CHAIN_DISPATCH(P.B, LB)
+#undef LB
+        c->kernels += 1;
+    }
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    return DAECPP_B200_OK;
+}
+
+} // namespace daecpp_b200

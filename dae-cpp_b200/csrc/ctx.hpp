@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "../../include/daecpp_b200.h"
+#include "chain.hpp"
 #include "symbolic.hpp"
 
 namespace daecpp_b200
@@ -78,6 +79,18 @@ struct DeviceSymbolic
     }
 };
 
+// device side of the block-chain plan (chain.hpp)
+struct DeviceChain
+{
+    DevBuf<int32_t> ent_u, sj, sm, flags, perm;
+    DevBuf<double> F, Y, red, rv, x;
+    void release()
+    {
+        ent_u.release(); sj.release(); sm.release(); flags.release(); perm.release();
+        F.release(); Y.release(); red.release(); rv.release(); x.release();
+    }
+};
+
 struct GroupLaunch
 {
     int32_t kind = 0, begin = 0, count = 0;
@@ -121,6 +134,12 @@ struct daecpp_b200_ctx
     daecpp_b200::Symbolic S;
     daecpp_b200::DeviceSymbolic dS;
     std::vector<daecpp_b200::GroupLaunch> groups;
+    // block-chain path (banded patterns): taken instead of the multifrontal schedule when the
+    // pattern is recognised as a chain of blocks of order <= chain_max_b
+    daecpp_b200::chain::Plan CH;
+    daecpp_b200::DeviceChain dC;
+    bool chain_enabled = true;
+    int chain_min_n = 256, chain_max_b = 3;
     uint32_t ticket_base = 0; // value of the ticket word before the next unit launch
     int32_t solve_epoch = 0;
     int unit_threads = 256;
@@ -190,6 +209,10 @@ int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha);
 int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct);
 int launch_unit_backward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, bool update, double atol, double rtol,
                          double max_err_abs);
+// chain.cu
+int chain_try_setup(daecpp_b200_ctx *c, int32_t n, const int32_t *outer, const int32_t *inner);
+int chain_refactor_async(daecpp_b200_ctx *c, double alpha);
+int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, double max_err_abs);
 // vector_ops.cu
 int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
 int launch_dxdt(daecpp_b200_ctx *c, int32_t order, const double coef[5]);

@@ -274,6 +274,19 @@ int upload_symbolic(daecpp_b200_ctx *c)
     if (c->nnzU)
         DAECPP_CUDA_TRY(c, cudaMemcpyAsync(inner.data(), c->u_inner.p, sizeof(int32_t) * c->nnzU, cudaMemcpyDeviceToHost, st));
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
+    {   // banded patterns (1-D problems) take the block-chain path: no per-front tables at all
+        int rc = chain_try_setup(c, n, outer.data(), inner.data());
+        if (rc) return rc;
+        if (c->CH.active)
+        {
+            DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
+            c->have_symbolic = true;
+            c->have_factor = false;
+            c->n_symbolic += 1;
+            c->ms_symbolic = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+            return DAECPP_B200_OK;
+        }
+    }
     const char *err = nullptr;
     if (!analyse_pattern(n, outer.data(), inner.data(), c->sopt, c->S, &err))
     {
@@ -376,6 +389,13 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha)
     int rc;
     if (!c->jvals_from_triplets && !c->direct_csc && (rc = ensure_csc_values(c, c->J))) return rc;
     DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 3, 0, 2 * sizeof(int32_t), st));
+    if (c->CH.active)
+    {
+        if ((rc = chain_refactor_async(c, alpha))) return rc;
+        c->n_refactor += 1;
+        c->last_alpha = alpha;
+        return DAECPP_B200_OK;
+    }
     if (S.nbig)
     {
         DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->LU.p + S.lu_big_begin, 0, sizeof(double) * (size_t)(S.lu_size - S.lu_big_begin), st));
@@ -428,9 +448,15 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
 {
     cudaStream_t st = c->stream;
     const int32_t n = c->n;
+    int rc;
+    if (c->CH.active)
+    {
+        if ((rc = chain_solve(c, fuse_update, atol, rtol, max_err_abs))) return rc;
+        c->n_solve += 1;
+        return DAECPP_B200_OK;
+    }
     FrontTables T = tables(c);
     const bool direct = c->S.nbig == 0;
-    int rc;
     c->solve_epoch += 1;
     if (!direct)
     {

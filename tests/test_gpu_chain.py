@@ -1,0 +1,139 @@
+"""GPU parity tests of the block-chain path (dae-cpp_b200/csrc/chain.cu) through the C ABI: banded
+patterns (flame-1D, perovskite) are factored and solved with no per-front tables.  Same bars as
+test_gpu_parity.py: assembly bit-exact, linear solve eta <= 1e-12 and residual within 10x of
+Eigen::SparseLU's, update loop bit-exact given dx."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import problems as P
+from gpu_lib import binding as B
+
+pytestmark = pytest.mark.gpu
+
+EMPTY = (np.zeros(0), np.zeros(0, np.int32), np.zeros(0, np.int32))
+
+
+def solve_chain(n, J, M, alpha, b=None, expect_block=None, options=None):
+    csc = O.assemble_jb(O.port, n, J, M, alpha)
+    b = np.full(n, 1.24) if b is None else b
+    c = B.Context(n)
+    c.set_option("chain_min_n", 1)
+    for k, v in (options or {}).items():
+        c.set_option(k, v)
+    c.set_mass(M); c.set_jacobian(J)
+    c.refactor(alpha)
+    got = c.get_csc(2)
+    assert all(u.tobytes() == v.tobytes() for u, v in zip(got, csc)), "assembly not bit-exact"
+    c.set_rhs(b)
+    x = c.solve()
+    blk = int(c.stat("chain_block"))
+    stats = {k: c.stat(k) for k in ("chain_block", "chain_levels", "chain_tiles", "chain_identity_perm", "nnz_factor")}
+    c.close()
+    if expect_block is not None:
+        assert blk == expect_block, stats
+    eta, r2 = O.backward_error(n, csc, x, b)
+    assert eta <= 1e-12, (eta, stats)
+    if O.ref is not None and n <= 300000:
+        rc, x_ref, _, _ = O.ref_sparselu(n, csc, b)
+        assert rc == 0
+        _, r2_ref = O.backward_error(n, csc, x_ref, b)
+        assert r2 <= 10.0 * r2_ref + 1e-12 * np.linalg.norm(b), (r2, r2_ref)
+    return x, stats
+
+
+@pytest.mark.parametrize("n", [2, 3, 17, 1000, 2048, 2049, 100000, 1000000])
+def test_chain_flame1d(n):
+    u = P.flame1d_state(n)
+    _, st = solve_chain(n, P.flame1d_jacobian(u), P.identity_mass(n), 50.0, expect_block=1)
+    assert st["chain_identity_perm"] == 1
+    assert st["chain_levels"] == (1 if n <= 2048 else 2)
+
+
+def test_chain_three_grid_levels():
+    n = 2048 * 2048 + 77
+    u = P.flame1d_state(n)
+    _, st = solve_chain(n, P.flame1d_jacobian(u), P.identity_mass(n), 50.0, expect_block=1)
+    assert st["chain_levels"] == 3
+
+
+@pytest.mark.parametrize("N,alpha", [(5, 100.0), (300, 100.0), (4000, 100.0), (4000, 1.0), (10000, 1.0)])
+def test_chain_perovskite(N, alpha):
+    xs = P.perovskite_state(N)
+    _, st = solve_chain(2 * N, P.perovskite_jacobian(xs, N), P.perovskite_mass(N), alpha, expect_block=2)
+    assert st["chain_identity_perm"] == 0
+
+
+def test_chain_block3_random_band_with_duplicates():
+    n = 3001
+    rng = np.random.default_rng(5)
+    I, Jc, A = [], [], []
+    for i in range(n):
+        for j in range(max(0, i - 4), min(n, i + 5)):
+            if abs(i // 3 - j // 3) <= 1 and rng.random() < 0.6:
+                for _ in range(1 + (rng.random() < 0.3)):  # duplicates are summed in input order
+                    I.append(i); Jc.append(j); A.append(rng.standard_normal())
+        I.append(i); Jc.append(i); A.append(9.0 + rng.random())
+    p = rng.permutation(len(A))
+    J = (np.array(A)[p], np.array(I, np.int32)[p], np.array(Jc, np.int32)[p])
+    solve_chain(n, J, P.identity_mass(n), 2.0, b=rng.standard_normal(n), expect_block=3)
+
+
+def test_chain_matches_general_path():
+    N = 700
+    xs = P.perovskite_state(N)
+    J = P.perovskite_jacobian(xs, N); M = P.perovskite_mass(N)
+    b = np.random.default_rng(0).standard_normal(2 * N)
+    x1, _ = solve_chain(2 * N, J, M, 10.0, b=b, expect_block=2)
+    x0, _ = solve_chain(2 * N, J, M, 10.0, b=b, expect_block=0, options={"chain": 0})
+    assert np.max(np.abs(x1 - x0)) <= 1e-9 * np.max(np.abs(x0))
+
+
+def test_chain_singular_matrix_reports_decomposition_failure():
+    n = 1000
+    A = np.ones(3 * n - 2)
+    i = np.concatenate([np.arange(n), np.arange(1, n), np.arange(n - 1)]).astype(np.int32)
+    j = np.concatenate([np.arange(n), np.arange(n - 1), np.arange(1, n)]).astype(np.int32)
+    A[:n] = 2.0
+    A[500] = 0.0; A[n + 499] = 0.0; A[2 * n - 1 + 500] = 0.0  # row 500 is identically zero (entries kept in the pattern)
+    c = B.Context(n)
+    c.set_option("chain_min_n", 1)
+    c.set_mass(EMPTY); c.set_jacobian((A, i, j))
+    rc = c.refactor(0.0, allow=(B.EDECOMP,))
+    assert int(c.stat("chain_block")) == 1
+    assert rc == B.EDECOMP
+    c.close()
+
+
+def test_chain_newton_iterations_match_oracle():
+    # whole resident iterations on the chain path, checked like test_newton_iterations_perovskite_vs_oracle
+    N = 1500
+    n = 2 * N
+    M = P.perovskite_mass(N)
+    x = P.perovskite_state(N)
+    c = B.Context(n)
+    c.set_state(x)
+    c.set_mass(M)
+    dt4 = np.array([1e-3, 0.0, 0.0, 0.0])
+    for it in range(3):
+        xk = c.get_xk()
+        J = P.perovskite_jacobian(xk, N)
+        c.set_jacobian(J)
+        f = np.sin(np.arange(n) * 0.01) * 1e-3
+        alpha = c.residual(f, 1, dt4)
+        xk_before = c.get_vector("xk")
+        rc, flags = c.iteration_resident(1, 1, dt4, 1e-6, 1e-6)
+        assert rc == 0
+        assert int(c.stat("chain_block")) == 2
+        csc = O.assemble_jb(O.port, n, J, M, alpha)
+        dx = c.get_vector("dx"); b = c.get_vector("b")
+        eta, _ = O.backward_error(n, csc, dx, b)
+        assert eta <= 1e-12
+        assert (xk_before + dx).tobytes() == c.get_vector("xk").tobytes()
+        want = 0
+        e = np.abs(dx)
+        x0 = np.abs(c.get_vector("x0"))
+        if np.any(e > 1e100) or np.any(np.isnan(dx)): want |= 1
+        if np.any((x0 > 1e-14) & (e / np.where(x0 > 0, x0, 1.0) > 1e-6)) or np.any(e > 1e-6): want |= 2
+        assert flags == want
+    c.close()
