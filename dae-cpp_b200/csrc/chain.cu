@@ -82,50 +82,72 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
     if (fail) atomicOr(&a.dflags[3], 1);
 }
 
-// backward sweep of one tile and the write-out of its unknowns; sh.xR / sh.xL are set
+// backward sweep of one tile and the write-out of its unknowns; sh.xR / sh.xL, sh.F12 and sh.Y12 are set
 template <int B, bool FIRST>
 __device__ __forceinline__ void backward_tail(const ChainArgs &a, SolveShared<B> &sh, int t, int tile, int64_t mb, int nvalid,
                                               double *Ft, double *Yt)
 {
     using D = Dim<B>;
-    if (t == 0) backward_phase2<B>(sh, Ft, Yt);
+    if (t == 0) backward_phase2<B>(sh);
     __syncthreads();
-    backward_phase1<B>(t, nvalid, sh, Ft, Yt);
+    backward_phase1<B>(t, nvalid, sh);
     __syncthreads();
     backward_phase0<B>(t, nvalid, sh, Ft, Yt);
     __syncthreads();
+    constexpr int U = 4;
+    const int total = B * nvalid;
     if (FIRST)
     {
         if (!a.out) return;
-        double *out = a.out + mb * a.s_vec;
+        double *__restrict__ out = a.out + mb * a.s_vec;
+        double *__restrict__ xk = a.xk + mb * a.s_vec;
+        const double *__restrict__ x0 = a.x0 + mb * a.s_vec;
         int flag = 0;
-        for (int q = 0; q < B; ++q)
-            for (int row = t; row < nvalid; row += D::T)
+        for (int i0 = t; i0 < total; i0 += D::T * U)
+        {
+            int64_t o[U];
+            double v[U], xa[U], xo[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
             {
+                const int idx = i0 + u * D::T;
+                const int q = idx / nvalid, row = idx - q * nvalid;
                 const int64_t k = ((int64_t)tile * D::ROWS + row) * B + q;
-                if (k >= a.n) continue;
-                const double v = sh.R[(size_t)q * D::RP + sidx<B>(row)];
-                const int64_t o = a.perm ? a.perm[k] : k;
-                out[o] = v;
+                const bool ok = idx < total && k < a.n;
+                o[u] = ok ? (a.perm ? (int64_t)a.perm[k] : k) : -1;
+                v[u] = ok ? sh.R[(size_t)q * D::RP + sidx<B>(row)] : 0.0;
+            }
+            if (a.update)
+            {
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+                    if (o[u] >= 0) { xa[u] = x0[o[u]]; xo[u] = xk[o[u]]; }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+            {
+                if (o[u] < 0) continue;
+                out[o[u]] = v[u];
                 if (a.update)
                 {   // dae-cpp/solver.hpp:590-619
-                    const double e = fabs(v);
-                    if (e > a.max_err_abs || isnan(v)) flag |= DAECPP_B200_DIVERGED;
-                    const double xa = fabs(a.x0[mb * a.s_vec + o]);
-                    if (xa > 1e-14 && __ddiv_rn(e, xa) > a.rtol) flag |= DAECPP_B200_NOT_CONVERGED;
+                    const double e = fabs(v[u]), ax = fabs(xa[u]);
+                    if (e > a.max_err_abs || isnan(v[u])) flag |= DAECPP_B200_DIVERGED;
+                    if (ax > 1e-14 && __ddiv_rn(e, ax) > a.rtol) flag |= DAECPP_B200_NOT_CONVERGED;
                     if (e > a.atol) flag |= DAECPP_B200_NOT_CONVERGED;
-                    double *xk = a.xk + mb * a.s_vec;
-                    xk[o] = __dadd_rn(xk[o], v);
+                    xk[o[u]] = __dadd_rn(xo[u], v[u]);
                 }
             }
+        }
         if (flag) atomicOr(&a.dflags[2], flag);
     }
     else
     {
         double *xl = a.xlev + mb * a.s_x;
-        for (int q = 0; q < B; ++q)
-            for (int row = t; row < nvalid; row += D::T)
-                xl[((size_t)tile * D::ROWS + row) * B + q] = sh.R[(size_t)q * D::RP + sidx<B>(row)];
+        for (int idx = t; idx < total; idx += D::T)
+        {
+            const int q = idx / nvalid, row = idx - q * nvalid;
+            xl[((size_t)tile * D::ROWS + row) * B + q] = sh.R[(size_t)q * D::RP + sidx<B>(row)];
+        }
     }
 }
 
@@ -143,14 +165,19 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_forward(ChainArgs a)
     const int nvalid = min(D::ROWS, a.rows - tile * D::ROWS);
     if (FIRST) stage_rhs_first<B>(t, D::T, tile, a.n, sh.R, a.rhs + mb * a.s_vec, a.perm);
     else stage_rhs_reduced<B>(t, D::T, tile, a.rows, sh.R, a.rv_in + mb * a.s_rv);
+    load_small_factors<B>(t, D::T, sh, Ft);
     __syncthreads();
     forward_phase0<B>(t, nvalid, sh, Ft, Yt);
     __syncthreads();
-    forward_phase1<B>(t, nvalid, sh, Ft, Yt);
+    forward_phase1<B>(t, nvalid, sh);
     __syncthreads();
-    if (t == 0) forward_phase2<B>(tile, a.ntiles, a.is_top != 0, sh, Ft, Yt, a.rv_out + mb * a.s_rv);
-    if (!a.is_top) return;
+    if (t == 0) forward_phase2<B>(tile, a.ntiles, a.is_top != 0, sh, a.rv_out + mb * a.s_rv);
     __syncthreads();
+    if (!a.is_top)
+    {   // the level-1/2 forward results wait in HBM for the backward kernel
+        copy_small(t, D::T, Yt + D::Y0, sh.Y12, D::Y1 + D::Y2);
+        return;
+    }
     backward_tail<B, FIRST>(a, sh, t, tile, mb, nvalid, Ft, Yt);
 }
 
@@ -171,6 +198,8 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
         sh.xR[t] = xup[(size_t)tile * B + t];
         sh.xL[t] = tile > 0 ? xup[(size_t)(tile - 1) * B + t] : 0.0;
     }
+    load_small_factors<B>(t, D::T, sh, Ft);
+    copy_small(t, D::T, sh.Y12, Yt + D::Y0, D::Y1 + D::Y2);
     __syncthreads();
     backward_tail<B, FIRST>(a, sh, t, tile, mb, nvalid, Ft, Yt);
 }
