@@ -340,7 +340,9 @@ int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int3
     if (!do_refactor && !c->have_factor) return fail(c, DAECPP_B200_EINVAL, "no valid factorisation");
     cudaStream_t st = c->stream;
     const bool pt = c->phase_timing;
-    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, sizeof(int32_t), st));
+    // all flag words of the iteration are cleared up front so that its kernels follow each other
+    // on the stream with no other node in between (programmatic dependent launch, chain.cu)
+    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, 3 * sizeof(int32_t), st));
     // the triplet values are resident: the Jacobian's compressed-column values (if anything
     // still needs them) are stale from here on
     if (do_refactor) c->J.vals_valid = false;
@@ -349,8 +351,7 @@ int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int3
     if (pt) cudaEventRecord(c->pev[1], st);
     if ((rc = launch_residual(c, order, w))) return rc;
     if (pt) cudaEventRecord(c->pev[2], st);
-    if (do_refactor && (rc = numeric_refactor_async(c, w[0]))) return rc;
-    if (!do_refactor) DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 3, 0, 2 * sizeof(int32_t), st));
+    if (do_refactor && (rc = numeric_refactor_async(c, w[0], false))) return rc;
     if (pt) cudaEventRecord(c->pev[3], st);
     if ((rc = numeric_solve(c, true, atol, rtol, max_err_abs))) return rc;
     if (pt) cudaEventRecord(c->pev[4], st);

@@ -50,6 +50,12 @@ struct ChainArgs
     int64_t s_jv, s_mv, s_F, s_Y, s_red, s_rv, s_x, s_vec;
 };
 
+// Programmatic dependent launch: the chain kernels of one Newton iteration follow each other on the
+// stream with nothing in between, so each one lets its successor start launching as soon as its own
+// loads are issued, and waits for its predecessor's memory before touching global data.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 template <int B, bool FIRST>
 __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
 {
@@ -60,6 +66,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
     const int64_t mb = blockIdx.y;
     double *Ft = a.F + mb * a.s_F + (size_t)tile * D::TILE_F;
     const int nvalid = min(D::ROWS, a.rows - tile * D::ROWS);
+    pdl_wait();
     if (FIRST)
     {
         const double alpha = a.alpha_arr ? a.alpha_arr[mb] : a.alpha;
@@ -68,6 +75,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
     else
         stage_matrix_reduced<B>(t, D::T, tile, a.rows, sh.S, a.red_in + mb * a.s_red);
     __syncthreads();
+    pdl_trigger();
     int fail = 0;
     {
         Mat<B> G, Dk, SL, H;
@@ -163,10 +171,12 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_forward(ChainArgs a)
     double *Ft = a.F + mb * a.s_F + (size_t)tile * D::TILE_F;
     double *Yt = a.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
     const int nvalid = min(D::ROWS, a.rows - tile * D::ROWS);
+    pdl_wait();
     if (FIRST) stage_rhs_first<B>(t, D::T, tile, a.n, sh.R, a.rhs + mb * a.s_vec, a.perm);
     else stage_rhs_reduced<B>(t, D::T, tile, a.rows, sh.R, a.rv_in + mb * a.s_rv);
     load_small_factors<B>(t, D::T, sh, Ft);
     __syncthreads();
+    pdl_trigger();
     forward_phase0<B>(t, nvalid, sh, Ft, Yt);
     __syncthreads();
     forward_phase1<B>(t, nvalid, sh);
@@ -192,6 +202,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
     double *Ft = a.F + mb * a.s_F + (size_t)tile * D::TILE_F;
     double *Yt = a.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
     const int nvalid = min(D::ROWS, a.rows - tile * D::ROWS);
+    pdl_wait();
     if (t < B)
     {
         const double *xup = a.xup + mb * a.s_x;
@@ -201,6 +212,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
     load_small_factors<B>(t, D::T, sh, Ft);
     copy_small(t, D::T, sh.Y12, Yt + D::Y0, D::Y1 + D::Y2);
     __syncthreads();
+    pdl_trigger();
     backward_tail<B, FIRST>(a, sh, t, tile, mb, nvalid, Ft, Yt);
 }
 
@@ -275,23 +287,34 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g)
     return a;
 }
 
+template <class K> void launch_pdl(daecpp_b200_ctx *c, K kernel, const ChainArgs &a, int threads, size_t smem)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(a.ntiles, 1, 1);
+    cfg.blockDim = dim3(threads, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = c->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, kernel, a);
+}
 template <int B> void launch_factor(daecpp_b200_ctx *c, const ChainArgs &a, bool first)
 {
-    const dim3 grid(a.ntiles, 1);
-    if (first) k_chain_factor<B, true><<<grid, Cfg<B>::T, factor_smem<B>(), c->stream>>>(a);
-    else k_chain_factor<B, false><<<grid, Cfg<B>::T, factor_smem<B>(), c->stream>>>(a);
+    if (first) launch_pdl(c, k_chain_factor<B, true>, a, Cfg<B>::T, factor_smem<B>());
+    else launch_pdl(c, k_chain_factor<B, false>, a, Cfg<B>::T, factor_smem<B>());
 }
 template <int B> void launch_forward(daecpp_b200_ctx *c, const ChainArgs &a, bool first)
 {
-    const dim3 grid(a.ntiles, 1);
-    if (first) k_chain_forward<B, true><<<grid, Cfg<B>::T, solve_smem<B>(), c->stream>>>(a);
-    else k_chain_forward<B, false><<<grid, Cfg<B>::T, solve_smem<B>(), c->stream>>>(a);
+    if (first) launch_pdl(c, k_chain_forward<B, true>, a, Cfg<B>::T, solve_smem<B>());
+    else launch_pdl(c, k_chain_forward<B, false>, a, Cfg<B>::T, solve_smem<B>());
 }
 template <int B> void launch_backward(daecpp_b200_ctx *c, const ChainArgs &a, bool first)
 {
-    const dim3 grid(a.ntiles, 1);
-    if (first) k_chain_backward<B, true><<<grid, Cfg<B>::T, solve_smem<B>(), c->stream>>>(a);
-    else k_chain_backward<B, false><<<grid, Cfg<B>::T, solve_smem<B>(), c->stream>>>(a);
+    if (first) launch_pdl(c, k_chain_backward<B, true>, a, Cfg<B>::T, solve_smem<B>());
+    else launch_pdl(c, k_chain_backward<B, false>, a, Cfg<B>::T, solve_smem<B>());
 }
 
 #define CHAIN_DISPATCH(B, CALL)              \

@@ -96,6 +96,14 @@ template <int B> CH_HD Vec<B> mv(const Mat<B> &X, const Vec<B> &v)
 template <int B> CH_HD void vsub(Vec<B> &d, const Vec<B> &x) { for (int i = 0; i < B; ++i) d.a[i] -= x.a[i]; }
 template <int B> CH_HD void vadd(Vec<B> &d, const Vec<B> &x) { for (int i = 0; i < B; ++i) d.a[i] += x.a[i]; }
 
+CH_HD double rcp(double x)
+{
+#if defined(__CUDA_ARCH__)
+    return __drcp_rn(x);
+#else
+    return 1.0 / x;
+#endif
+}
 CH_HD bool bad_pivot(double p, double tol)
 {
     const double a = fabs(p);
@@ -110,7 +118,7 @@ template <int B> CH_HD Mat<B> minv(const Mat<B> &D, double tol, int &fail)
     {
         Mat<B> r;
         if (bad_pivot(D.a[0], tol)) fail = 1;
-        r.a[0] = 1.0 / D.a[0];
+        r.a[0] = rcp(D.a[0]);
         return r;
     }
     double w[B][2 * B];
@@ -134,7 +142,7 @@ template <int B> CH_HD Mat<B> minv(const Mat<B> &D, double tol, int &fail)
                 for (int j = 0; j < 2 * B; ++j) { const double tmp = w[k][j]; w[k][j] = w[i][j]; w[i][j] = tmp; }
             }
         if (bad_pivot(w[k][k], tol)) fail = 1;
-        const double inv = 1.0 / w[k][k];
+        const double inv = rcp(w[k][k]);
 #pragma unroll
         for (int j = 0; j < 2 * B; ++j) w[k][j] *= inv;
 #pragma unroll
@@ -154,81 +162,84 @@ template <int B> CH_HD Mat<B> minv(const Mat<B> &D, double tol, int &fail)
     return r;
 }
 
-// ---- factor storage of one chunk: element (k, field f, e) at base[((k*NF + f*BB + e)*stride + lane]
-template <int B> struct FacRef
+// ---- factor storage of one chunk: element (k, field f, e) at p[(k*NF + f*BB + e)*STRIDE]; p already
+// points at the chunk's lane, STRIDE is the number of chunks interleaved (T, Q2 or 1), so that with k
+// unrolled every access is base + immediate
+template <int B, int STRIDE> struct FacRef
 {
-    double *base;
-    int stride, lane;
+    double *p;
     CH_HD void put(int k, int f, const Mat<B> &X) const
     {
 #pragma unroll
-        for (int e = 0; e < B * B; ++e) base[(size_t)((k * Dim<B>::NF + f * B * B + e)) * stride + lane] = X.a[e];
+        for (int e = 0; e < B * B; ++e) p[(size_t)(k * Dim<B>::NF + f * B * B + e) * STRIDE] = X.a[e];
     }
     CH_HD Mat<B> get(int k, int f) const
     {
         Mat<B> X;
 #pragma unroll
-        for (int e = 0; e < B * B; ++e) X.a[e] = base[(size_t)((k * Dim<B>::NF + f * B * B + e)) * stride + lane];
+        for (int e = 0; e < B * B; ++e) X.a[e] = p[(size_t)(k * Dim<B>::NF + f * B * B + e) * STRIDE];
         return X;
     }
 };
-template <int B> struct YRef
+template <int B, int STRIDE> struct YRef
 {
-    double *base;
-    int stride, lane;
+    double *p;
     CH_HD void put(int k, const Vec<B> &v) const
     {
 #pragma unroll
-        for (int r = 0; r < B; ++r) base[(size_t)(k * B + r) * stride + lane] = v.a[r];
+        for (int r = 0; r < B; ++r) p[(size_t)(k * B + r) * STRIDE] = v.a[r];
     }
     CH_HD Vec<B> get(int k) const
     {
         Vec<B> v;
 #pragma unroll
-        for (int r = 0; r < B; ++r) v.a[r] = base[(size_t)(k * B + r) * stride + lane];
+        for (int r = 0; r < B; ++r) v.a[r] = p[(size_t)(k * B + r) * STRIDE];
         return v;
     }
 };
 
-// ---- row sources ---------------------------------------------------------------------------
+// ---- row sources: rows are addressed relative to the chunk (k = 0 first interior row, k = -1 the
+// row before the chunk, k = Q-1 the separator)
 // level 0: the staged tile S[fe][RP] (fe = f*BB + e; f = 0 sub, 1 diag, 2 super)
 template <int B> struct StagedRows
 {
-    const double *S;
-    CH_HD Mat<B> get(int f, int row) const
+    const double *Sb; // S + sidx(first row of the chunk) - 1
+    CH_HD Mat<B> get(int f, int k) const
     {
         Mat<B> X;
-        const int p = sidx<B>(row);
+        const int p = (k + 1) + (k + 1) / Dim<B>::Q0; // chunks start on a multiple of Q0
 #pragma unroll
-        for (int e = 0; e < B * B; ++e) X.a[e] = S[(size_t)(f * B * B + e) * Dim<B>::RP + p];
+        for (int e = 0; e < B * B; ++e) X.a[e] = Sb[(size_t)(f * B * B + e) * Dim<B>::RP + p];
         return X;
     }
-    CH_HD Mat<B> A(int row) const { return get(0, row); }
-    CH_HD Mat<B> D(int row) const { return get(1, row); }
-    CH_HD Mat<B> C(int row) const { return get(2, row); }
-    CH_HD Mat<B> Hinit(int row0) const { return get(2, row0 - 1); }
+    CH_HD Mat<B> A(int k) const { return get(0, k); }
+    CH_HD Mat<B> D(int k) const { return get(1, k); }
+    CH_HD Mat<B> C(int k) const { return get(2, k); }
+    CH_HD Mat<B> Hinit() const { return get(2, -1); }
 };
-// levels 1 and 2: the four per-chunk results of the level below, arrays [e][count]
-template <int B> struct ReducedRows
+template <int B> CH_HD StagedRows<B> staged_rows(const double *S, int chunk) { return StagedRows<B>{S + chunk * (Dim<B>::Q0 + 1)}; }
+
+// levels 1 and 2: the four per-chunk results of the level below, arrays [e][COUNT]
+template <int B, int COUNT> struct ReducedRows
 {
     const double *G, *Df, *SL, *Hf;
-    int count;
+    int i0; // first row of the chunk
     CH_HD Mat<B> ld(const double *p, int i) const
     {
         Mat<B> X;
 #pragma unroll
-        for (int e = 0; e < B * B; ++e) X.a[e] = p[e * count + i];
+        for (int e = 0; e < B * B; ++e) X.a[e] = p[e * COUNT + i];
         return X;
     }
-    CH_HD Mat<B> A(int i) const { return ld(G, i); }
-    CH_HD Mat<B> D(int i) const
+    CH_HD Mat<B> A(int k) const { return ld(G, i0 + k); }
+    CH_HD Mat<B> D(int k) const
     {
-        Mat<B> X = ld(Df, i);
-        if (i + 1 < count) msub<B>(X, ld(SL, i + 1));
+        Mat<B> X = ld(Df, i0 + k);
+        if (i0 + k + 1 < COUNT) msub<B>(X, ld(SL, i0 + k + 1));
         return X;
     }
-    CH_HD Mat<B> C(int i) const { return (i + 1 < count) ? ld(Hf, i + 1) : mzero<B>(); }
-    CH_HD Mat<B> Hinit(int row0) const { return ld(Hf, row0); } // = C(row0-1); chunk 0 carries the level below
+    CH_HD Mat<B> C(int k) const { return (i0 + k + 1 < COUNT) ? ld(Hf, i0 + k + 1) : mzero<B>(); }
+    CH_HD Mat<B> Hinit() const { return ld(Hf, i0); } // = C(-1); chunk 0 carries the level below
 };
 template <int B> CH_HD void st(double *p, int count, int i, const Mat<B> &X)
 {
@@ -248,78 +259,121 @@ template <int B> CH_HD Vec<B> ldv(const double *p, int count, int i)
     return v;
 }
 
-// ---- elimination of one chunk's interior ----------------------------------------------------
-template <int B, class Rows>
-CH_HD void chunk_factor(int q_int, const Rows &src, int row0, const FacRef<B> &dst, double tol, int &fail, Mat<B> &G,
-                        Mat<B> &Dk, Mat<B> &SL, Mat<B> &H)
+// ---- elimination of one chunk's interior (QI rows).  The rows of step k+1 are fetched before the
+// arithmetic of step k and the factor stores come last, so that the only thing a step waits for is
+// the previous pivot: reciprocal, one multiply, one fused multiply-add.
+template <int B, int QI, class Rows, class Fac>
+CH_HD void chunk_factor(const Rows &src, const Fac &dst, double tol, int &fail, Mat<B> &G, Mat<B> &Dk, Mat<B> &SL, Mat<B> &H)
 {
-    G = src.A(row0);
-    Dk = src.D(row0);
-    H = src.Hinit(row0);
+    G = src.A(0);
+    Dk = src.D(0);
+    H = src.Hinit();
     SL = mzero<B>();
-    for (int k = 0; k < q_int; ++k)
+    Mat<B> C = src.C(0), An = src.A(1), Dn = src.D(1);
+#pragma unroll
+    for (int k = 0; k < QI; ++k)
     {
-        const Mat<B> C = src.C(row0 + k);
+        Mat<B> C1, A2, D2;
+        if (k + 1 < QI) { C1 = src.C(k + 1); A2 = src.A(k + 2); D2 = src.D(k + 2); }
         const Mat<B> Dinv = minv<B>(Dk, tol, fail);
-        const Mat<B> L = mmul<B>(src.A(row0 + k + 1), Dinv);
+        const Mat<B> L = mmul<B>(An, Dinv);
         const Mat<B> LL = mmul<B>(H, Dinv);
+        Dk = Dn;
+        msub<B>(Dk, mmul<B>(L, C));
         dst.put(k, FL, L);
         dst.put(k, FLL, LL);
         dst.put(k, FDINV, Dinv);
         dst.put(k, FC, C);
         dst.put(k, FG, G);
-        Dk = src.D(row0 + k + 1);
-        msub<B>(Dk, mmul<B>(L, C));
         madd<B>(SL, mmul<B>(LL, G));
         G = mneg<B>(mmul<B>(L, G));
         H = mneg<B>(mmul<B>(LL, C));
+        if (k + 1 < QI) { C = C1; An = A2; Dn = D2; }
     }
 }
 
 // forward sweep of one chunk: y_k, the separator's partial rhs and the update tL of row L's rhs.
-// The multipliers are fetched up front (QI is a compile-time count): the sweep itself is a chain
-// of dependent FMAs that must not wait on memory at every step.
-template <int B, int QI, class Rhs>
-CH_HD void chunk_forward(const Rhs &rsrc, int row0, const FacRef<B> &fac, const YRef<B> &ydst, Vec<B> &ysep, Vec<B> &tL)
+// PRE: multipliers and right-hand sides are fetched up front (HBM operands: the sweep is a chain of
+// dependent FMAs that must not wait on memory at every step); otherwise they are read step by step
+// (shared-memory operands of the small levels, where registers are the scarcer resource).
+template <int B, int QI, bool PRE, class Rhs, class Fac, class YDst>
+CH_HD void chunk_forward(const Rhs &rsrc, const Fac &fac, const YDst &ydst, Vec<B> &ysep, Vec<B> &tL)
 {
-    Mat<B> L[QI], LL[QI];
-#pragma unroll
-    for (int k = 0; k < QI; ++k) { L[k] = fac.get(k, FL); LL[k] = fac.get(k, FLL); }
-    Vec<B> yk = rsrc.r(row0);
     tL = vzero<B>();
-#pragma unroll
-    for (int k = 0; k < QI; ++k)
+    if (PRE)
     {
-        ydst.put(k, yk);
-        vadd<B>(tL, mv<B>(LL[k], yk));
-        const Vec<B> ly = mv<B>(L[k], yk);
-        yk = rsrc.r(row0 + k + 1);
-        vsub<B>(yk, ly);
+        Mat<B> L[QI], LL[QI];
+        Vec<B> r[QI + 1];
+#pragma unroll
+        for (int k = 0; k < QI; ++k) { L[k] = fac.get(k, FL); LL[k] = fac.get(k, FLL); }
+#pragma unroll
+        for (int k = 0; k <= QI; ++k) r[k] = rsrc.r(k);
+        Vec<B> yk = r[0];
+#pragma unroll
+        for (int k = 0; k < QI; ++k)
+        {
+            ydst.put(k, yk);
+            vadd<B>(tL, mv<B>(LL[k], yk));
+            const Vec<B> ly = mv<B>(L[k], yk);
+            yk = r[k + 1];
+            vsub<B>(yk, ly);
+        }
+        ysep = yk;
     }
-    ysep = yk;
+    else
+    {
+        Vec<B> yk = rsrc.r(0);
+#pragma unroll
+        for (int k = 0; k < QI; ++k)
+        {
+            const Mat<B> L = fac.get(k, FL), LL = fac.get(k, FLL);
+            Vec<B> rn = rsrc.r(k + 1);
+            ydst.put(k, yk);
+            vadd<B>(tL, mv<B>(LL, yk));
+            vsub<B>(rn, mv<B>(L, yk));
+            yk = rn;
+        }
+        ysep = yk;
+    }
 }
 
 // backward sweep of one chunk; xdst(k, x) receives the interior unknowns, last row first
-template <int B, int QI, class XDst>
-CH_HD void chunk_backward(const FacRef<B> &fac, const YRef<B> &ysrc, const Vec<B> &xR, const Vec<B> &xL, XDst &xdst)
+template <int B, int QI, bool PRE, class Fac, class YSrc, class XDst>
+CH_HD void chunk_backward(const Fac &fac, const YSrc &ysrc, const Vec<B> &xR, const Vec<B> &xL, XDst &xdst)
 {
-    Mat<B> Di[QI], C[QI];
-    Vec<B> y[QI];
-#pragma unroll
-    for (int k = 0; k < QI; ++k)
-    {
-        Di[k] = fac.get(k, FDINV);
-        C[k] = fac.get(k, FC);
-        y[k] = ysrc.get(k);
-        vsub<B>(y[k], mv<B>(fac.get(k, FG), xL)); // the spike term does not depend on the sweep
-    }
     Vec<B> xn = xR;
-#pragma unroll
-    for (int k = QI - 1; k >= 0; --k)
+    if (PRE)
     {
-        vsub<B>(y[k], mv<B>(C[k], xn));
-        xn = mv<B>(Di[k], y[k]);
-        xdst.put(k, xn);
+        Mat<B> Di[QI], C[QI];
+        Vec<B> y[QI];
+#pragma unroll
+        for (int k = 0; k < QI; ++k)
+        {
+            Di[k] = fac.get(k, FDINV);
+            C[k] = fac.get(k, FC);
+            y[k] = ysrc.get(k);
+            vsub<B>(y[k], mv<B>(fac.get(k, FG), xL)); // the spike term does not depend on the sweep
+        }
+#pragma unroll
+        for (int k = QI - 1; k >= 0; --k)
+        {
+            vsub<B>(y[k], mv<B>(C[k], xn));
+            xn = mv<B>(Di[k], y[k]);
+            xdst.put(k, xn);
+        }
+    }
+    else
+    {
+#pragma unroll
+        for (int k = QI - 1; k >= 0; --k)
+        {
+            const Mat<B> Di = fac.get(k, FDINV), C = fac.get(k, FC);
+            Vec<B> y = ysrc.get(k);
+            vsub<B>(y, mv<B>(fac.get(k, FG), xL));
+            vsub<B>(y, mv<B>(C, xn));
+            xn = mv<B>(Di, y);
+            xdst.put(k, xn);
+        }
     }
 }
 
@@ -365,36 +419,35 @@ CH_HD void copy_small(int t, int nt, double *dst, const double *src, int count)
 }
 template <int B> struct StagedRhs
 {
-    const double *R;
-    CH_HD Vec<B> r(int row) const
+    const double *Rb; // R + sidx(first row of the chunk) - 1
+    CH_HD Vec<B> r(int k) const
     {
         Vec<B> v;
-        const int p = sidx<B>(row);
+        const int p = (k + 1) + (k + 1) / Dim<B>::Q0;
 #pragma unroll
-        for (int q = 0; q < B; ++q) v.a[q] = R[(size_t)q * Dim<B>::RP + p];
+        for (int q = 0; q < B; ++q) v.a[q] = Rb[(size_t)q * Dim<B>::RP + p];
         return v;
     }
 };
-template <int B> struct ReducedRhs
+template <int B, int COUNT> struct ReducedRhs
 {
     const double *Y, *Tl;
-    int count;
-    CH_HD Vec<B> r(int i) const
+    int i0;
+    CH_HD Vec<B> r(int k) const
     {
-        Vec<B> v = ldv<B>(Y, count, i);
-        if (i + 1 < count) vsub<B>(v, ldv<B>(Tl, count, i + 1));
+        Vec<B> v = ldv<B>(Y, COUNT, i0 + k);
+        if (i0 + k + 1 < COUNT) vsub<B>(v, ldv<B>(Tl, COUNT, i0 + k + 1));
         return v;
     }
 };
 template <int B> struct StagedX
 {
-    double *R;
-    int row0;
+    double *Rb;
     CH_HD void put(int k, const Vec<B> &x)
     {
-        const int p = sidx<B>(row0 + k);
+        const int p = (k + 1) + (k + 1) / Dim<B>::Q0;
 #pragma unroll
-        for (int q = 0; q < B; ++q) R[(size_t)q * Dim<B>::RP + p] = x.a[q];
+        for (int q = 0; q < B; ++q) Rb[(size_t)q * Dim<B>::RP + p] = x.a[q];
     }
 };
 template <int B> struct ArrayX
@@ -469,27 +522,37 @@ CH_HD void stage_matrix_first(int t, int nt, int tile, double *S, const int32_t 
 template <int B> CH_HD void stage_matrix_reduced(int t, int nt, int tile, int rows, double *S, const double *red)
 {
     using D = Dim<B>;
-    for (int rr = t; rr <= D::ROWS; rr += nt)
+    constexpr int U = (B == 1) ? 6 : 2;
+    for (int r0 = t; r0 <= D::ROWS; r0 += nt * U)
     {
-        const int i = tile * D::ROWS + rr - 1;
-        const int p = sidx<B>(rr - 1);
-        for (int e = 0; e < D::BB; ++e)
+        double a[U][D::BB], d[U][D::BB], d2[U][D::BB], c[U][D::BB];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
         {
-            double a = 0.0, d = 0.0, c = 0.0;
-            if (i >= rows) d = (e / B == e % B) ? 1.0 : 0.0;
-            else if (i >= 0)
+            const int i = tile * D::ROWS + r0 + u * nt - 1;
+            const bool in = i >= 0 && i < rows, nx = in && i + 1 < rows;
+#pragma unroll
+            for (int e = 0; e < D::BB; ++e)
             {
-                a = red[((size_t)0 * rows + i) * D::BB + e];
-                d = red[((size_t)1 * rows + i) * D::BB + e];
-                if (i + 1 < rows)
-                {
-                    d -= red[((size_t)2 * rows + i + 1) * D::BB + e];
-                    c = red[((size_t)3 * rows + i + 1) * D::BB + e];
-                }
+                a[u][e] = in ? red[((size_t)0 * rows + i) * D::BB + e] : 0.0;
+                d[u][e] = in ? red[((size_t)1 * rows + i) * D::BB + e] : ((i >= rows && e / B == e % B) ? 1.0 : 0.0);
+                d2[u][e] = nx ? red[((size_t)2 * rows + i + 1) * D::BB + e] : 0.0;
+                c[u][e] = nx ? red[((size_t)3 * rows + i + 1) * D::BB + e] : 0.0;
             }
-            S[(size_t)(0 * D::BB + e) * D::RP + p] = a;
-            S[(size_t)(1 * D::BB + e) * D::RP + p] = d;
-            S[(size_t)(2 * D::BB + e) * D::RP + p] = c;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+        {
+            const int rr = r0 + u * nt;
+            if (rr > D::ROWS) continue;
+            const int p = sidx<B>(rr - 1);
+#pragma unroll
+            for (int e = 0; e < D::BB; ++e)
+            {
+                S[(size_t)(0 * D::BB + e) * D::RP + p] = a[u][e];
+                S[(size_t)(1 * D::BB + e) * D::RP + p] = d[u][e] - d2[u][e];
+                S[(size_t)(2 * D::BB + e) * D::RP + p] = c[u][e];
+            }
         }
     }
 }
@@ -553,11 +616,7 @@ CH_HD void factor_phase0(int t, int nvalid, FactorShared<B> &sh, double *Ftile, 
     using D = Dim<B>;
     G = mzero<B>(); Dk = mident<B>(); SL = mzero<B>(); H = mzero<B>();
     if (t * D::Q0 < nvalid)
-    {
-        StagedRows<B> src{sh.S};
-        FacRef<B> dst{Ftile, D::T, t};
-        chunk_factor<B>(D::Q0 - 1, src, t * D::Q0, dst, tol, fail, G, Dk, SL, H);
-    }
+        chunk_factor<B, D::Q0 - 1>(staged_rows<B>(sh.S, t), FacRef<B, D::T>{Ftile + t}, tol, fail, G, Dk, SL, H);
 }
 // after a barrier: every thread is done reading the staged tile
 template <int B>
@@ -573,9 +632,8 @@ template <int B> CH_HD void factor_phase1(int c, int nvalid, FactorShared<B> &sh
     Mat<B> G = mzero<B>(), Dk = mident<B>(), SL = mzero<B>(), H = mzero<B>();
     if (c * D::Q1 * D::Q0 < nvalid)
     {
-        ReducedRows<B> src{sh.G1(), sh.D1(), sh.SL1(), sh.H1(), D::T};
-        FacRef<B> dst{Ftile + D::F0, D::Q2, c};
-        chunk_factor<B>(D::Q1 - 1, src, c * D::Q1, dst, tol, fail, G, Dk, SL, H);
+        ReducedRows<B, D::T> src{sh.G1(), sh.D1(), sh.SL1(), sh.H1(), c * D::Q1};
+        chunk_factor<B, D::Q1 - 1>(src, FacRef<B, D::Q2>{Ftile + D::F0 + c}, tol, fail, G, Dk, SL, H);
     }
     st<B>(sh.G2(), D::Q2, c, G); st<B>(sh.D2(), D::Q2, c, Dk); st<B>(sh.SL2(), D::Q2, c, SL); st<B>(sh.H2(), D::Q2, c, H);
 }
@@ -586,9 +644,8 @@ CH_HD void factor_phase2(int tile, int ntiles, bool is_top, FactorShared<B> &sh,
 {
     using D = Dim<B>;
     Mat<B> G, Dk, SL, H;
-    ReducedRows<B> src{sh.G2(), sh.D2(), sh.SL2(), sh.H2(), D::Q2};
-    FacRef<B> dst{Ftile + D::F0 + D::F1, 1, 0};
-    chunk_factor<B>(D::Q2 - 1, src, 0, dst, tol, fail, G, Dk, SL, H);
+    ReducedRows<B, D::Q2> src{sh.G2(), sh.D2(), sh.SL2(), sh.H2(), 0};
+    chunk_factor<B, D::Q2 - 1>(src, FacRef<B, 1>{Ftile + D::F0 + D::F1}, tol, fail, G, Dk, SL, H);
     // updates of the left tile's separator collected from the first chunk of every level
     for (int e = 0; e < B * B; ++e) SL.a[e] += sh.SL1()[e * D::T] + sh.SL2()[e * D::Q2];
     if (is_top)
@@ -619,10 +676,8 @@ template <int B> CH_HD void forward_phase0(int t, int nvalid, SolveShared<B> &sh
     using D = Dim<B>;
     Vec<B> ysep = vzero<B>(), tL = vzero<B>();
     if (t * D::Q0 < nvalid)
-    {
-        StagedRhs<B> rs{sh.R};
-        chunk_forward<B, D::Q0 - 1>(rs, t * D::Q0, FacRef<B>{Ftile, D::T, t}, YRef<B>{Ytile, D::T, t}, ysep, tL);
-    }
+        chunk_forward<B, D::Q0 - 1, true>(StagedRhs<B>{sh.R + t * (D::Q0 + 1)}, FacRef<B, D::T>{Ftile + t}, YRef<B, D::T>{Ytile + t}, ysep,
+                                    tL);
     stv<B>(sh.Y1, D::T, t, ysep); stv<B>(sh.T1, D::T, t, tL);
 }
 template <int B> CH_HD void forward_phase1(int c, int nvalid, SolveShared<B> &sh)
@@ -631,10 +686,8 @@ template <int B> CH_HD void forward_phase1(int c, int nvalid, SolveShared<B> &sh
     if (c >= D::Q2) return;
     Vec<B> ysep = vzero<B>(), tL = vzero<B>();
     if (c * D::Q1 * D::Q0 < nvalid)
-    {
-        ReducedRhs<B> rs{sh.Y1, sh.T1, D::T};
-        chunk_forward<B, D::Q1 - 1>(rs, c * D::Q1, FacRef<B>{sh.F12, D::Q2, c}, YRef<B>{sh.Y12, D::Q2, c}, ysep, tL);
-    }
+        chunk_forward<B, D::Q1 - 1, B == 1>(ReducedRhs<B, D::T>{sh.Y1, sh.T1, c * D::Q1}, FacRef<B, D::Q2>{sh.F12 + c},
+                                    YRef<B, D::Q2>{sh.Y12 + c}, ysep, tL);
     stv<B>(sh.Y2, D::Q2, c, ysep); stv<B>(sh.T2, D::Q2, c, tL);
 }
 // thread 0 only.  rv: this level's reduced rhs [2][ntiles][B] (separator rhs, update of the left tile's).
@@ -642,8 +695,8 @@ template <int B> CH_HD void forward_phase2(int tile, int ntiles, bool is_top, So
 {
     using D = Dim<B>;
     Vec<B> ysep, tL;
-    ReducedRhs<B> rs{sh.Y2, sh.T2, D::Q2};
-    chunk_forward<B, D::Q2 - 1>(rs, 0, FacRef<B>{sh.F12 + D::F1, 1, 0}, YRef<B>{sh.Y12 + D::Y1, 1, 0}, ysep, tL);
+    chunk_forward<B, D::Q2 - 1, B == 1>(ReducedRhs<B, D::Q2>{sh.Y2, sh.T2, 0}, FacRef<B, 1>{sh.F12 + D::F1}, YRef<B, 1>{sh.Y12 + D::Y1},
+                                ysep, tL);
     for (int q = 0; q < B; ++q) tL.a[q] += sh.T1[q * D::T] + sh.T2[q * D::Q2];
     for (int q = 0; q < B; ++q)
     {
@@ -667,7 +720,7 @@ template <int B> CH_HD void backward_phase2(SolveShared<B> &sh)
     for (int q = 0; q < B; ++q) { xR.a[q] = sh.xR[q]; xL.a[q] = sh.xL[q]; }
     stv<B>(sh.X2, D::Q2, D::Q2 - 1, xR);
     ArrayX<B> xd{sh.X2, D::Q2, 0};
-    chunk_backward<B, D::Q2 - 1>(FacRef<B>{sh.F12 + D::F1, 1, 0}, YRef<B>{sh.Y12 + D::Y1, 1, 0}, xR, xL, xd);
+    chunk_backward<B, D::Q2 - 1, B == 1>(FacRef<B, 1>{sh.F12 + D::F1}, YRef<B, 1>{sh.Y12 + D::Y1}, xR, xL, xd);
 }
 template <int B> CH_HD void backward_phase1(int c, int nvalid, SolveShared<B> &sh)
 {
@@ -680,7 +733,7 @@ template <int B> CH_HD void backward_phase1(int c, int nvalid, SolveShared<B> &s
     stv<B>(sh.X1, D::T, c * D::Q1 + D::Q1 - 1, xR);
     ArrayX<B> xd{sh.X1, D::T, c * D::Q1};
     if (c * D::Q1 * D::Q0 < nvalid)
-        chunk_backward<B, D::Q1 - 1>(FacRef<B>{sh.F12, D::Q2, c}, YRef<B>{sh.Y12, D::Q2, c}, xR, xL, xd);
+        chunk_backward<B, D::Q1 - 1, B == 1>(FacRef<B, D::Q2>{sh.F12 + c}, YRef<B, D::Q2>{sh.Y12 + c}, xR, xL, xd);
     else
         for (int k = 0; k < D::Q1 - 1; ++k) xd.put(k, vzero<B>());
 }
@@ -691,10 +744,10 @@ template <int B> CH_HD void backward_phase0(int t, int nvalid, SolveShared<B> &s
     Vec<B> xL;
     if (t > 0) xL = ldv<B>(sh.X1, D::T, t - 1);
     else for (int q = 0; q < B; ++q) xL.a[q] = sh.xL[q];
-    StagedX<B> xd{sh.R, t * D::Q0};
+    StagedX<B> xd{sh.R + t * (D::Q0 + 1)};
     xd.put(D::Q0 - 1, xR);
     if (t * D::Q0 < nvalid)
-        chunk_backward<B, D::Q0 - 1>(FacRef<B>{Ftile, D::T, t}, YRef<B>{Ytile, D::T, t}, xR, xL, xd);
+        chunk_backward<B, D::Q0 - 1, true>(FacRef<B, D::T>{Ftile + t}, YRef<B, D::T>{Ytile + t}, xR, xL, xd);
 }
 
 } // namespace chain

@@ -195,7 +195,7 @@ int regather_values(daecpp_b200_ctx *c, TripletSet &T); // hot path on the resid
 // numeric.cu
 int upload_symbolic(daecpp_b200_ctx *c);
 int numeric_refactor(daecpp_b200_ctx *c, double alpha);
-int numeric_refactor_async(daecpp_b200_ctx *c, double alpha); // enqueue only; pivot flag left in d_flags[3]
+int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags = true); // enqueue only; pivot flag left in d_flags[3]
 int assemble_values_only(daecpp_b200_ctx *c, double alpha);
 int numeric_solve(daecpp_b200_ctx *c, bool fuse_update = false, double atol = 0, double rtol = 0,
                   double max_err_abs = 0); // b -> dx (and, fused, the error checks and xk += dx)

@@ -382,13 +382,13 @@ int assemble_values_only(daecpp_b200_ctx *c, double alpha)
     return DAECPP_B200_OK;
 }
 
-int numeric_refactor_async(daecpp_b200_ctx *c, double alpha)
+int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
 {
     cudaStream_t st = c->stream;
     Symbolic &S = c->S;
     int rc;
     if (!c->jvals_from_triplets && !c->direct_csc && (rc = ensure_csc_values(c, c->J))) return rc;
-    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 3, 0, 2 * sizeof(int32_t), st));
+    if (clear_flags) DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 3, 0, 2 * sizeof(int32_t), st));
     if (c->CH.active)
     {
         if ((rc = chain_refactor_async(c, alpha))) return rc;
@@ -424,7 +424,7 @@ int numeric_refactor(daecpp_b200_ctx *c, double alpha)
 {
     cudaStream_t st = c->stream;
     DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev0, st));
-    int rc = numeric_refactor_async(c, alpha);
+    int rc = numeric_refactor_async(c, alpha, true);
     if (rc) return rc;
     DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev1, st));
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 3, c->d_flags + 3, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
