@@ -571,6 +571,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "unit_threads") { c->unit_threads = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "pinned_io") c->pinned_io = value != 0.0;
     else if (k == "chain") { c->chain_enabled = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "chain_affine") { c->chain_affine = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "chain_min_n") { c->chain_min_n = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "chain_max_block") { c->chain_max_b = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "trace_units") c->trace_units = value != 0.0;

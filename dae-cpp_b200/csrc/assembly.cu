@@ -340,7 +340,7 @@ int build_mass_csr(daecpp_b200_ctx *c)
         DAECPP_CUDA_TRY(c, cudaGetLastError());
     }
     c->m_csr_version = M.pattern_version;
-    return DAECPP_B200_OK;
+    return classify_mass(c);
 }
 
 } // namespace daecpp_b200

@@ -27,7 +27,7 @@ struct ChainArgs
 {
     int32_t rows, ntiles, n, is_top;
     // factor
-    const int32_t *sj, *sm, *flags;
+    const int32_t *sj, *sm, *flags, *desc;
     const double *jv, *mv;
     double alpha, tol;
     double *F, *Y;
@@ -70,7 +70,11 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
     if (FIRST)
     {
         const double alpha = a.alpha_arr ? a.alpha_arr[mb] : a.alpha;
-        stage_matrix_first<B>(t, D::T, tile, sh.S, a.sj, a.sm, a.flags, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
+        bool affine = true;
+#pragma unroll
+        for (int fe = 0; fe < 3 * D::BB; ++fe) affine = affine && (a.flags[tile * 3 * D::BB + fe] & TF_AFF);
+        if (affine) stage_matrix_affine<B>(t, D::T, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
+        else stage_matrix_first<B>(t, D::T, tile, sh.S, a.sj, a.sm, a.flags, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
     }
     else
         stage_matrix_reduced<B>(t, D::T, tile, a.rows, sh.S, a.red_in + mb * a.s_red);
@@ -237,6 +241,35 @@ __global__ void k_chain_compose(int64_t ne, int32_t per_fe, const int32_t *__res
     if (m >= 0) atomicOr(&flags[e / per_fe], TF_MASS);
 }
 
+// one block per (tile, field element): is the value source an arithmetic progression in the row?
+__global__ void k_chain_affine(int32_t per_fe, const int32_t *__restrict__ sj, const int32_t *__restrict__ sm,
+                               int32_t *__restrict__ flags, int32_t *__restrict__ desc)
+{
+    const size_t base = (size_t)blockIdx.x * per_fe;
+    const int32_t fl = flags[blockIdx.x];
+    const int32_t s0 = sj[base], sb = sj[base + 1] - s0;
+    const int32_t m0 = sm[base], mb = sm[base + 1] - m0;
+    const bool empty = !(fl & (TF_ANY | TF_ONE)), mass = (fl & TF_MASS) != 0;
+    int ok = 1;
+    for (int rr = threadIdx.x; rr < per_fe; rr += blockDim.x)
+    {
+        const int32_t s = sj[base + rr], m = sm[base + rr];
+        if (empty) ok &= (s == -1);
+        else ok &= (s >= 0 && s == s0 + sb * rr);
+        if (mass) ok &= (m >= 0 && m == m0 + mb * rr);
+        else ok &= (m < 0);
+    }
+    ok = __syncthreads_and(ok);
+    if (threadIdx.x == 0)
+    {
+        desc[(size_t)blockIdx.x * 4 + 0] = empty ? -1 : s0;
+        desc[(size_t)blockIdx.x * 4 + 1] = empty ? 0 : sb;
+        desc[(size_t)blockIdx.x * 4 + 2] = mass ? m0 : -1;
+        desc[(size_t)blockIdx.x * 4 + 3] = mass ? mb : 0;
+        flags[blockIdx.x] = ok ? (fl | TF_AFF) : (fl & ~TF_AFF);
+    }
+}
+
 } // namespace
 
 namespace
@@ -359,8 +392,11 @@ int chain_try_setup(daecpp_b200_ctx *c, int32_t n, const int32_t *outer, const i
     const int32_t per_fe = rows_per_tile(P.B) + 1;
     k_chain_compose<<<(int)((ne + 255) / 256), 256, 0, c->stream>>>(ne, per_fe, c->dC.ent_u.p, uJ, c->u_M.p, srcJ, c->dC.sj.p,
                                                                   c->dC.sm.p, c->dC.flags.p);
+    DAECPP_CUDA_TRY(c, c->dC.desc.reserve(P.tile_flags.size() * 4 + 4));
+    if (c->chain_affine)
+        k_chain_affine<<<(int)P.tile_flags.size(), 256, 0, c->stream>>>(per_fe, c->dC.sj.p, c->dC.sm.p, c->dC.flags.p, c->dC.desc.p);
     DAECPP_CUDA_TRY(c, cudaGetLastError());
-    c->kernels += 1;
+    c->kernels += 2;
     return DAECPP_B200_OK;
 }
 
@@ -373,7 +409,7 @@ int chain_refactor_async(daecpp_b200_ctx *c, double alpha)
         ChainArgs a = level_args(c, g);
         if (g == 0)
         {
-            a.sj = c->dC.sj.p; a.sm = c->dC.sm.p; a.flags = c->dC.flags.p;
+            a.sj = c->dC.sj.p; a.sm = c->dC.sm.p; a.flags = c->dC.flags.p; a.desc = c->dC.desc.p;
             a.jv = jv; a.mv = c->M.vals.p; a.alpha = alpha;
         }
 #define LF(B) launch_factor<B>(c, a, g == 0)

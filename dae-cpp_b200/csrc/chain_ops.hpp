@@ -475,7 +475,7 @@ CH_HD double sub_rn(double a, double b)
     return a - b;
 #endif
 }
-enum { TF_ANY = 1, TF_ONE = 2, TF_MASS = 4 };
+enum { TF_ANY = 1, TF_ONE = 2, TF_MASS = 4, TF_AFF = 8 };
 // level 0: Jb = J - (M*alpha) (two roundings, dae-cpp/solver.hpp:523) gathered through the slot map
 template <int B>
 CH_HD void stage_matrix_first(int t, int nt, int tile, double *S, const int32_t *sj, const int32_t *sm, const int32_t *flags,
@@ -515,6 +515,49 @@ CH_HD void stage_matrix_first(int t, int nt, int tile, double *S, const int32_t 
                 const int fe = idx / PER, rr = idx - fe * PER;
                 S[(size_t)fe * D::RP + sidx<B>(rr - 1)] = sub_rn(j[u], q[u] >= 0 ? mul_rn(m[u], alpha) : 0.0);
             }
+        }
+    }
+}
+// level 0, affine tiles: when the value source of every field of the tile is an arithmetic
+// progression in the row (the normal case: a functor that emits its triplets row by row, e.g.
+// JacobianMatrixShape) the slot map is not read at all.  desc[(tile*3*BB + fe)*4] = {first J index
+// (or -1: structurally empty field), J stride, first M slot (or -1: no mass entry), M stride}.
+// All loads of a batch are independent; the fields of one row are fetched back to back by the same
+// warp so that the strided accesses share their cache lines.
+template <int B>
+CH_HD void stage_matrix_affine(int t, int nt, int tile, double *S, const int32_t *desc, const double *jv, const double *mvals,
+                               double alpha)
+{
+    using D = Dim<B>;
+    constexpr int PER = D::ROWS + 1, NFE = 3 * D::BB, U = (B == 1) ? 4 : (B == 2 ? 2 : 1);
+    int32_t ja[NFE], jb[NFE], ma[NFE], mb[NFE];
+    const int32_t *d = desc + (size_t)tile * NFE * 4;
+#pragma unroll
+    for (int fe = 0; fe < NFE; ++fe) { ja[fe] = d[fe * 4]; jb[fe] = d[fe * 4 + 1]; ma[fe] = d[fe * 4 + 2]; mb[fe] = d[fe * 4 + 3]; }
+    for (int r0 = t; r0 < PER; r0 += nt * U)
+    {
+        double j[U][NFE], m[U][NFE];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+        {
+            const int rr = r0 + u * nt;
+            const bool ok = rr < PER;
+#pragma unroll
+            for (int fe = 0; fe < NFE; ++fe)
+            {
+                j[u][fe] = (ok && ja[fe] >= 0) ? jv[ja[fe] + jb[fe] * rr] : 0.0;
+                m[u][fe] = (ok && ma[fe] >= 0) ? mvals[ma[fe] + mb[fe] * rr] : 0.0;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+        {
+            const int rr = r0 + u * nt;
+            if (rr >= PER) continue;
+            const int p = sidx<B>(rr - 1);
+#pragma unroll
+            for (int fe = 0; fe < NFE; ++fe)
+                S[(size_t)fe * D::RP + p] = sub_rn(j[u][fe], ma[fe] >= 0 ? mul_rn(m[u][fe], alpha) : 0.0);
         }
     }
 }

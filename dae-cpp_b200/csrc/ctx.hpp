@@ -82,11 +82,11 @@ struct DeviceSymbolic
 // device side of the block-chain plan (chain.hpp)
 struct DeviceChain
 {
-    DevBuf<int32_t> ent_u, sj, sm, flags, perm;
+    DevBuf<int32_t> ent_u, sj, sm, flags, perm, desc;
     DevBuf<double> F, Y, red, rv, x;
     void release()
     {
-        ent_u.release(); sj.release(); sm.release(); flags.release(); perm.release();
+        ent_u.release(); sj.release(); sm.release(); flags.release(); perm.release(); desc.release();
         F.release(); Y.release(); red.release(); rv.release(); x.release();
     }
 };
@@ -120,6 +120,7 @@ struct daecpp_b200_ctx
     // CSR view of M for the residual (row-wise accumulation in column order)
     daecpp_b200::DevBuf<int32_t> m_rowptr, m_rowslot, m_rowcol;
     uint64_t m_csr_version = ~0ull;
+    bool m_diag = false; // M is diagonal with slots in row order: index-free residual kernel
 
     // union pattern of J and M = pattern of Jb
     uint64_t union_J_version = ~0ull, union_M_version = ~0ull;
@@ -138,7 +139,7 @@ struct daecpp_b200_ctx
     // pattern is recognised as a chain of blocks of order <= chain_max_b
     daecpp_b200::chain::Plan CH;
     daecpp_b200::DeviceChain dC;
-    bool chain_enabled = true;
+    bool chain_enabled = true, chain_affine = true;
     int chain_min_n = 256, chain_max_b = 3;
     uint32_t ticket_base = 0; // value of the ticket word before the next unit launch
     int32_t solve_epoch = 0;
@@ -215,6 +216,7 @@ int chain_refactor_async(daecpp_b200_ctx *c, double alpha);
 int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, double max_err_abs);
 // vector_ops.cu
 int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
+int classify_mass(daecpp_b200_ctx *c);
 int launch_dxdt(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
 int launch_update(daecpp_b200_ctx *c, double atol, double rtol, double max_err_abs);
 int launch_accept(daecpp_b200_ctx *c, int32_t variability_on, double tol);

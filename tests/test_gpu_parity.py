@@ -180,7 +180,7 @@ def test_linear_solve_grid2d(m):
 @pytest.mark.parametrize("threads", [64, 256])
 def test_linear_solve_schedule_variants(budget, threads):
     """Same answers whatever the partition into shared-memory units and per-level big fronts."""
-    opts = {"unit_smem_bytes": budget, "unit_threads": threads}
+    opts = {"unit_smem_bytes": budget, "unit_threads": threads, "chain": 0}  # the general multifrontal path
     N = 700
     xs = P.perovskite_state(N)
     _, st = _solve_and_check(2 * N, P.perovskite_jacobian(xs, N), P.perovskite_mass(N), 100.0, options=opts)
@@ -196,7 +196,7 @@ def test_linear_solve_wide_groups():
     """serial_dim = 0 forces every front through the cooperative (8 / 32 / block wide) code."""
     N = 300
     xs = P.perovskite_state(N)
-    _solve_and_check(2 * N, P.perovskite_jacobian(xs, N), P.perovskite_mass(N), 100.0, options={"serial_dim": 0})
+    _solve_and_check(2 * N, P.perovskite_jacobian(xs, N), P.perovskite_mass(N), 100.0, options={"serial_dim": 0, "chain": 0})
     _solve_and_check(40 * 40, P.grid2d_probe_matrix(40), EMPTY, 0.0, options={"serial_dim": 0, "unit_smem_bytes": 200 * 1024})
 
 
@@ -206,6 +206,7 @@ def test_repeated_refactor_and_solve_reuse_schedule():
     u = P.flame1d_state(n)
     J = P.flame1d_jacobian(u); M = P.identity_mass(n)
     c = B.Context(n)
+    c.set_option("chain", 0)  # the general path's tickets and epochs; the chain path has its own test file
     c.set_mass(M); c.set_jacobian(J)
     b = np.linspace(-1, 1, n)
     for k in range(12):
