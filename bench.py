@@ -40,8 +40,12 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="flame1d", choices=["flame1d", "perovskite", "grid2d"])
-    ap.add_argument("--n", type=int, default=0, help="flame1d: unknowns; perovskite: N (system 2N); grid2d: side")
+    ap.add_argument("--workload", default="flame1d", choices=["flame1d", "perovskite", "grid2d", "ensemble"])
+    ap.add_argument("--n", "--size", dest="n", type=int, default=0, help="flame1d: unknowns; perovskite: N (system 2N); grid2d: side")
+    ap.add_argument("--members", type=int, default=4096, help="ensemble: members of the whole sweep (C5)")
+    ap.add_argument("--threads", type=int, default=0, help="ensemble: members in flight per GPU (0: host cores / GPUs)")
+    ap.add_argument("--host-logic-check", action="store_true",
+                    help="ensemble: run the partition + gather logic on CPU (gloo, reference driver) -- used by tests/")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -211,6 +215,148 @@ def run_reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------------------ ensemble (C5)
+ENS_METRIC = "ensemble systems/s"
+
+
+def _driver(name):
+    exe = os.path.join(ROOT, "hostcpp", "_bin", name)
+    if not os.path.exists(exe):
+        raise SystemExit(f"bench.py: {exe} is not built (python -c 'import __graft_entry__ as g; g.build()')")
+    return exe
+
+
+def _run_driver(exe, env_device, **kv):
+    env = dict(os.environ)
+    if env_device is not None:
+        env["DAECPP_B200_DEVICE"] = str(env_device)
+    cmd = [exe, "ensemble"] + [f"{k}={v}" for k, v in kv.items()]
+    p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env)
+    if p.returncode not in (0, 1):
+        raise SystemExit(f"bench.py: {' '.join(cmd)} failed ({p.returncode}): {p.stderr[-2000:]}")
+    return json.loads(p.stdout.strip().splitlines()[-1])
+
+
+def run_ensemble_reference(args):
+    """The unmodified reference headers (Eigen::SparseLU) integrating a bounded sample of the sweep on
+    ALL host cores, one daecpp::solve per thread (SURVEY.md 8(d): not a single-core strawman)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cores = os.cpu_count() or 1
+    N = args.n or 4000
+    sample = min(args.members, max(2 * cores, 8))
+    vals = []
+    for _ in range(max(1, min(args.steps, 3))):
+        r = _run_driver(_driver("traj_dump_ref"), None, members=args.members, first=0, count=sample, threads=cores, n=N)
+        vals.append(r["systems_per_s"])
+    v = float(np.median(vals))
+    line = {"impl": "reference", "metric": ENS_METRIC, "value": v, "unit": "systems/s", "n_gpus": args.gpus,
+            "steps": len(vals), "warmup": 0, "ms_per_step": 1e3 * sample / v, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"C5 ensemble of perovskite N={N} (n={2 * N}) members, lambda log-spaced 0.5..2", "members": args.members},
+            "cpu_baseline": {"value": v, "unit": "systems/s", "cores": cores, "kind": "reference",
+                             "sample": f"{sample} of {args.members} members, one daecpp::solve per host thread, {cores} threads"},
+            "e2e": {"value": v, "unit": "systems/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_ensemble_b200(args):
+    """C5: 4096 independent perovskite solves partitioned across the ranks (contiguous blocks), every
+    member a complete daecpp::solve through the overlay header; one all_gather of the final states."""
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    check = args.host_logic_check  # tests only: same partition / gather code, CPU tensors, reference driver
+    dev = "cpu" if check else "cuda"
+    if not check:
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+        torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if check:
+            dist.init_process_group("gloo")
+        else:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if not check:
+            torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    N = args.n or 4000
+    n = 2 * N
+    cores = os.cpu_count() or 1
+    threads = args.threads or max(1, 2 * cores // world)  # waiting threads sleep (blocking sync): oversubscribe
+    per = (args.members + world - 1) // world
+    first = rank * per
+    count = max(0, min(per, args.members - first))
+    exe = _driver("traj_dump_ref" if check else "traj_dump")
+    out = os.path.join("/tmp", f"daecpp_ens_{os.getpid()}_{rank}.f64")
+    for _ in range(args.warmup):  # a small block: brings the device, the driver and the page cache up
+        _run_driver(exe, local, members=args.members, first=first, count=min(count, threads), threads=threads, n=N)
+    sampler = ClockSampler(local)
+    if not check:
+        sampler.start()
+    barrier()
+    t0 = time.perf_counter()
+    last = None
+    for _ in range(args.steps):
+        last = _run_driver(exe, local, members=args.members, first=first, count=count, threads=threads, n=N, out=out)
+    barrier()
+    el = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([el], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        el = float(t.item())
+    clocks = sampler.stop() if not check else None
+    # ---- the one collective of the path: gather {status, steps, final state} of every member
+    mine = torch.from_numpy(np.fromfile(out, dtype=np.float64).reshape(count, n + 2)).to(dev)
+    os.remove(out)
+    if count < per:
+        mine = torch.cat([mine, torch.zeros(per - count, n + 2, dtype=torch.float64, device=dev)])
+    if dist is not None:
+        allm = torch.empty(world * per, n + 2, dtype=torch.float64, device=dev)
+        tg = time.perf_counter()
+        if check:
+            parts = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(parts, mine)
+            allm = torch.cat(parts)
+        else:
+            dist.all_gather_into_tensor(allm, mine)
+            torch.cuda.synchronize()
+        gather_ms = (time.perf_counter() - tg) * 1e3
+    else:
+        allm, gather_ms = mine, 0.0
+    allm = allm[:args.members]
+    failed = int((allm[:, 0] != 0).sum().item())
+    steps_total = int(allm[:, 1].sum().item())
+    line = {"metric": ENS_METRIC, "value": args.members * args.steps / el, "unit": "systems/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * el / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"C5 ensemble of perovskite N={N} (n={n}) members, lambda log-spaced 0.5..2 (BASELINE configs[4])",
+                       "members": args.members, "members_per_gpu": per, "threads_per_gpu": threads, "host_cores": cores,
+                       "parallelism": f"members partitioned in contiguous blocks over {world} GPU(s); one context + stream per "
+                                      "in-flight member; no data-path collective, one final all_gather",
+                       "timing": "wall clock between barriers, max over ranks (host functors are part of a solve)"},
+            "clocks": clocks, "failed_members": failed, "accepted_steps_total": steps_total, "gather_ms": gather_ms,
+            "gather_bytes": int(allm.numel() * 8),
+            "state_checksum": float(allm[:, 2:].sum().item()),
+            "rank0_driver": {k: last[k] for k in ("steps", "rhs_calls", "jac_calls", "wall_ms", "systems_per_s", "checksum")},
+            "e2e": {"value": args.members * args.steps / el, "unit": "systems/s",
+                    "h2d_bytes_per_step": None, "d2h_bytes_per_step": None,
+                    "note": "every member is a whole daecpp::solve through host buffers: value is already end to end"},
+            "gpu_launches": None, "roofline": None}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 # ------------------------------------------------------------------------------ B200 arm
 def run_b200_arm(args):
     import torch  # device bring-up, barrier and the max-over-ranks reduction only
@@ -309,7 +455,9 @@ def run_b200_arm(args):
     roofline = None
     if "GBps" in phases["refactor"]:
         a = phases["refactor"]["GBps"]
-        roofline = {"bound": "hbm", "kernel": "numeric refactorisation phase (k_scatter + k_factor_level launches)",
+        roofline = {"bound": "hbm", "kernel": ("numeric refactorisation phase: k_chain_factor<B,1> (tiles) + k_chain_factor<B,0> (grid level)"
+                               if c.stat("chain_block") > 0 else
+                               "numeric refactorisation phase (k_scatter_big + k_unit_factor + k_factor_level launches)"),
                     "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak, "traffic": None,
                     "peak_source": peak_src, "algorithmic_bytes": abytes["refactor"],
                     "us": phases["refactor"]["us"]}
@@ -368,7 +516,9 @@ def run_b200_arm(args):
 
 if __name__ == "__main__":
     a = parse_args()
-    if a.impl == "reference":
+    if a.workload == "ensemble":
+        run_ensemble_reference(a) if a.impl == "reference" else run_ensemble_b200(a)
+    elif a.impl == "reference":
         run_reference_arm(a)
     else:
         run_b200_arm(a)

@@ -195,6 +195,13 @@ void daecpp_b200_host_free(void *p)
     if (p) cudaFreeHost(p);
 }
 
+int daecpp_b200_set_blocking_sync(int device, int on)
+{
+    if (cudaSetDevice(device) != cudaSuccess) return DAECPP_B200_ECUDA;
+    const cudaError_t e = cudaSetDeviceFlags(on ? cudaDeviceScheduleBlockingSync : cudaDeviceScheduleAuto);
+    return e == cudaSuccess ? DAECPP_B200_OK : DAECPP_B200_ECUDA;
+}
+
 int daecpp_b200_host_register(void *p, size_t bytes)
 {
     if (!p || !bytes) return DAECPP_B200_EINVAL;

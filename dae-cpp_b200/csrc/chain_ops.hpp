@@ -633,18 +633,29 @@ CH_HD void stage_rhs_first(int t, int nt, int tile, int n, double *R, const doub
 template <int B> CH_HD void stage_rhs_reduced(int t, int nt, int tile, int rows, double *R, const double *rv)
 {
     using D = Dim<B>;
-    for (int row = t; row < D::ROWS; row += nt)
+    constexpr int U = (B == 1) ? 8 : 4;
+    for (int r0 = t; r0 < D::ROWS; r0 += nt * U)
     {
-        const int i = tile * D::ROWS + row;
-        for (int q = 0; q < B; ++q)
+        double y[U][B], tl[U][B];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
         {
-            double v = 0.0;
-            if (i < rows)
+            const int i = tile * D::ROWS + r0 + u * nt;
+            const bool in = r0 + u * nt < D::ROWS && i < rows, nx = in && i + 1 < rows;
+#pragma unroll
+            for (int q = 0; q < B; ++q)
             {
-                v = rv[((size_t)0 * rows + i) * B + q];
-                if (i + 1 < rows) v -= rv[((size_t)1 * rows + i + 1) * B + q];
+                y[u][q] = in ? rv[((size_t)0 * rows + i) * B + q] : 0.0;
+                tl[u][q] = nx ? rv[((size_t)1 * rows + i + 1) * B + q] : 0.0;
             }
-            R[(size_t)q * D::RP + sidx<B>(row)] = v;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+        {
+            const int row = r0 + u * nt;
+            if (row >= D::ROWS) continue;
+#pragma unroll
+            for (int q = 0; q < B; ++q) R[(size_t)q * D::RP + sidx<B>(row)] = y[u][q] - tl[u][q];
         }
     }
 }

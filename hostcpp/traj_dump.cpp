@@ -6,10 +6,12 @@
 // so that step counts, final states and wall times can be compared run against run.
 //
 // Usage: traj_dump <workload> [key=value ...]
-//   workloads: flame | perovskite | flame1d | grid2d
+//   workloads: flame | perovskite | flame1d | grid2d | ensemble
+//   ensemble keys: members (size of the whole sweep), first, count (this process's block), threads, n
 //   keys: n, lambda, t_end, out=<file for the final state, raw f64>, shape=0|1, repeat
 // Prints one JSON line.
 #include <dae-cpp/solver.hpp>
+#include <dae-cpp/ensemble.hpp>
 
 #include <chrono>
 #include <cmath>
@@ -403,6 +405,65 @@ int main(int argc, char **argv)
         opt.is_mass_matrix_static = true;
         opt.solution_variability_control = arg(kv, "variability", 1) != 0;
         status = solve(MassMatrixIdentity(n), Grid2DRHS{p, &tally}, Grid2DJac{p, &tally}, u0, t_end, Observer{&tally}, opt);
+    }
+    else if (wl == "ensemble")
+    {
+        // C5: perovskite members with lambda_m = 0.5 * 4^(m/(members-1)), same pattern,
+        // different values and different adaptive step sequences; this process integrates the block
+        // [first, first+count) with `threads` members in flight.
+        const std::size_t members = (std::size_t)arg(kv, "members", 4096), first = (std::size_t)arg(kv, "first", 0);
+        const std::size_t count = (std::size_t)arg(kv, "count", (double)(members - first));
+        const unsigned threads = (unsigned)arg(kv, "threads", 0);
+        const int_type N = (int_type)arg(kv, "n", 4000);
+        n = 2 * (std::size_t)N;
+        t_end = arg(kv, "t_end", 10.0);
+        std::vector<Tally> tallies(count);
+        Stopwatch sw;
+        auto result = solve_ensemble(first, count, [&](std::size_t m) {
+            Tally &tl = tallies[m - first];
+            const double lam = 0.5 * std::pow(4.0, members > 1 ? double(m) / double(members - 1) : 0.0);
+            Perovskite p{N, 1.0, lam};
+            state_vector x0(n, 0.0);
+            for (int_type k = 0; k < N; ++k) x0[k] = 1.0;
+            SolverOptions o;
+            o.solution_variability_control = false;
+            ensemble_capture cap;
+            const int st = solve(PerovskiteMass{p, &tl}, PerovskiteRHS{p, &tl}, PerovskiteJac{p, &tl}, x0, t_end, cap.observer(), o);
+            return ensemble_member{st, cap.steps(), std::move(cap.x)};
+        }, threads);
+        const double ms_ens = sw.ms();
+        long steps = 0, rhs_calls = 0, jac_calls = 0;
+        double checksum = 0.0;
+        for (std::size_t k = 0; k < count; ++k)
+        {
+            steps += result.members[k].steps;
+            rhs_calls += tallies[k].rhs; jac_calls += tallies[k].jac;
+            for (double v : result.members[k].x) checksum += v;
+        }
+        auto it = kv.find("out");
+        if (it != kv.end())
+        {
+            FILE *fp = std::fopen(it->second.c_str(), "wb");
+            if (!fp) { std::perror("out"); return 65; }
+            for (std::size_t k = 0; k < count; ++k)
+            {
+                const double head[2] = {(double)result.members[k].status, (double)result.members[k].steps};
+                std::fwrite(head, sizeof(double), 2, fp);
+                std::fwrite(result.members[k].x.data(), sizeof(double), result.members[k].x.size(), fp);
+            }
+            std::fclose(fp);
+        }
+#ifdef TRAJ_REFERENCE
+        const char *impl_e = "reference";
+#else
+        const char *impl_e = "b200";
+#endif
+        std::printf("{\"impl\": \"%s\", \"workload\": \"ensemble\", \"n\": %zu, \"members\": %zu, \"first\": %zu, \"count\": %zu, "
+                    "\"threads\": %u, \"failed\": %d, \"steps\": %ld, \"rhs_calls\": %ld, \"jac_calls\": %ld, \"wall_ms\": %.3f, "
+                    "\"systems_per_s\": %.6f, \"checksum\": %.17g}\n",
+                    impl_e, n, members, first, count, threads ? threads : std::thread::hardware_concurrency(), result.failed, steps,
+                    rhs_calls, jac_calls, ms_ens, 1e3 * double(count) / ms_ens, checksum);
+        return result.failed ? 1 : 0;
     }
     else
     {

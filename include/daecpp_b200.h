@@ -69,6 +69,11 @@ void daecpp_b200_host_free(void *p);
 int daecpp_b200_host_register(void *p, size_t bytes);
 int daecpp_b200_host_unregister(void *p);
 
+/* Process-wide, per device: make host threads SLEEP while they wait for the device instead of
+ * spinning (cudaDeviceScheduleBlockingSync).  Meant for ensembles (dae-cpp/ensemble.hpp): with many
+ * contexts in flight the host cores are needed by the user functors of other members. */
+int daecpp_b200_set_blocking_sync(int device, int on);
+
 /* ---- state --------------------------------------------------------------------------- */
 /* xk = x[0] = x0, order/dt history cleared       (solver.hpp:310-313) */
 int daecpp_b200_set_state(daecpp_b200_ctx *ctx, const double *x0);
