@@ -24,6 +24,7 @@ SYMBOLS = [
     "daecpp_b200_refactor", "daecpp_b200_solve_update", "daecpp_b200_accept_step", "daecpp_b200_set_rhs",
     "daecpp_b200_solve", "daecpp_b200_get_csc", "daecpp_b200_get_vector", "daecpp_b200_set_vector", "daecpp_b200_get_stat",
     "daecpp_b200_set_option", "daecpp_b200_iteration_resident", "daecpp_b200_event_mark", "daecpp_b200_event_elapsed_ms", "daecpp_b200_debug_unit_trace", "daecpp_b200_host_register", "daecpp_b200_host_unregister",
+    "daecpp_b200_set_blocking_sync", "daecpp_b200_set_pooling",
 ]
 
 

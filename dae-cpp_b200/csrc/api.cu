@@ -2,13 +2,24 @@
 // regions each entry point replaces).
 #include <cmath>
 #include <cstring>
+#include <mutex>
 #include <new>
+#include <utility>
 
 #include "ctx.hpp"
 
 using namespace daecpp_b200;
 
 static thread_local std::string g_create_error;
+
+// Process-wide pools (ensembles): released contexts and page-locked buffers are kept for the next
+// member instead of going through cudaFree / cudaFreeHost, which synchronise the whole device and
+// serialise the host threads of the other members in flight.  A recycled context keeps its cached
+// sparsity patterns and its symbolic plan: a member with the same pattern starts on the hot path.
+static std::mutex g_pool_mu;
+static bool g_pool_on = false;
+static std::vector<daecpp_b200_ctx *> g_ctx_pool;
+static std::vector<std::pair<size_t, void *>> g_host_pool;
 
 namespace
 {
@@ -106,6 +117,31 @@ int download_vector(daecpp_b200_ctx *c, double *dst_host, const double *src)
 
 } // namespace
 
+// A pooled context handed to a new owner: numerical state and options back to their defaults, the
+// cached patterns (triplet streams, union, symbolic plan) stay -- they are revalidated against the new
+// owner's uploads exactly like between two calls of one owner.
+static void recycle(daecpp_b200_ctx *c)
+{
+    const daecpp_b200_ctx fresh;
+    c->err.clear();
+    c->have_factor = false;
+    c->direct_csc = false;
+    c->M.vals_valid = false; c->J.vals_valid = false;
+    if (c->chain_enabled != fresh.chain_enabled || c->chain_min_n != fresh.chain_min_n || c->chain_max_b != fresh.chain_max_b ||
+        c->chain_affine != fresh.chain_affine || c->unit_threads != fresh.unit_threads || c->sopt.leaf_size != fresh.sopt.leaf_size ||
+        c->sopt.unit_smem_bytes != fresh.sopt.unit_smem_bytes || c->sopt.serial_dim != fresh.sopt.serial_dim ||
+        c->sopt.max_super != fresh.sopt.max_super)
+        c->have_symbolic = false;
+    c->chain_enabled = fresh.chain_enabled; c->chain_min_n = fresh.chain_min_n; c->chain_max_b = fresh.chain_max_b;
+    c->chain_affine = fresh.chain_affine; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
+    c->refine_steps = 0; c->assemble_only = false; c->pinned_io = false; c->pivot_tol = 0.0;
+    c->phase_timing = false; c->trace_units = false;
+    c->n_symbolic = c->n_refactor = c->n_solve = c->n_cold = c->kernels = 0;
+    c->ms_symbolic = c->ms_last_refactor = c->ms_last_solve = 0;
+    c->last_alpha = 0.0;
+    for (int k = 0; k < 8; ++k) { c->h_flags[k] = 0; c->h_scalars[k] = 0.0; }
+}
+
 extern "C" {
 
 const char *daecpp_b200_version(void) { return "daecpp_b200 0.1 (sm_100a)"; }
@@ -123,6 +159,18 @@ int daecpp_b200_create(int32_t n, int device, daecpp_b200_ctx **out)
         return DAECPP_B200_ECUDA;
     }
     if (device < 0 || device >= ndev) { g_create_error = "device index out of range"; return DAECPP_B200_EINVAL; }
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        for (size_t k = 0; g_pool_on && k < g_ctx_pool.size(); ++k)
+            if (g_ctx_pool[k]->n == n && g_ctx_pool[k]->device == device)
+            {
+                daecpp_b200_ctx *r = g_ctx_pool[k];
+                g_ctx_pool.erase(g_ctx_pool.begin() + k);
+                recycle(r);
+                *out = r;
+                return DAECPP_B200_OK;
+            }
+    }
     daecpp_b200_ctx *c = new (std::nothrow) daecpp_b200_ctx();
     if (!c) return DAECPP_B200_ENOMEM;
     c->n = n;
@@ -158,9 +206,40 @@ int daecpp_b200_create(int32_t n, int device, daecpp_b200_ctx **out)
     return DAECPP_B200_OK;
 }
 
+static void destroy_now(daecpp_b200_ctx *c);
+
 void daecpp_b200_destroy(daecpp_b200_ctx *c)
 {
     if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        if (g_pool_on && c->stream && c->xk && c->h_scalars && g_ctx_pool.size() < 1024)
+        {
+            g_ctx_pool.push_back(c);
+            return;
+        }
+    }
+    destroy_now(c);
+}
+
+int daecpp_b200_set_pooling(int on)
+{
+    std::vector<daecpp_b200_ctx *> ctxs;
+    std::vector<std::pair<size_t, void *>> bufs;
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        g_pool_on = on != 0;
+        if (!g_pool_on) { ctxs.swap(g_ctx_pool); bufs.swap(g_host_pool); }
+    }
+    for (daecpp_b200_ctx *c : ctxs) destroy_now(c);
+    for (auto &b : bufs) cudaFreeHost(b.second);
+    return DAECPP_B200_OK;
+}
+
+static void destroy_now(daecpp_b200_ctx *c)
+{
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->M.release(); c->J.release(); c->dS.release(); c->dC.release();
@@ -184,15 +263,38 @@ void daecpp_b200_destroy(daecpp_b200_ctx *c)
 
 const char *daecpp_b200_last_error(const daecpp_b200_ctx *c) { return c ? c->err.c_str() : g_create_error.c_str(); }
 
+// page-locked blocks carry their size in a 64-byte header so that a freed block can be reused
 void *daecpp_b200_host_alloc(size_t bytes)
 {
+    if (!bytes) bytes = 1;
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        for (size_t k = 0; g_pool_on && k < g_host_pool.size(); ++k)
+            if (g_host_pool[k].first == bytes)
+            {
+                void *p = g_host_pool[k].second;
+                g_host_pool.erase(g_host_pool.begin() + k);
+                return static_cast<char *>(p) + 64;
+            }
+    }
     void *p = nullptr;
-    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
-    return p;
+    if (cudaMallocHost(&p, bytes + 64) != cudaSuccess) return nullptr;
+    *static_cast<size_t *>(p) = bytes;
+    return static_cast<char *>(p) + 64;
 }
-void daecpp_b200_host_free(void *p)
+void daecpp_b200_host_free(void *q)
 {
-    if (p) cudaFreeHost(p);
+    if (!q) return;
+    void *p = static_cast<char *>(q) - 64;
+    {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        if (g_pool_on && g_host_pool.size() < 4096)
+        {
+            g_host_pool.emplace_back(*static_cast<size_t *>(p), p);
+            return;
+        }
+    }
+    cudaFreeHost(p);
 }
 
 int daecpp_b200_set_blocking_sync(int device, int on)

@@ -81,7 +81,8 @@ ensemble_result solve_ensemble(std::size_t first, std::size_t count, MemberFn me
     {   // waiting threads sleep: the cores belong to the functors of the other members in flight
         int device = 0;
         if (const char *env = std::getenv("DAECPP_B200_DEVICE")) device = std::atoi(env);
-        if (threads > 1) daecpp_b200_set_blocking_sync(device, 1);
+        if (threads > 2 * std::thread::hardware_concurrency()) daecpp_b200_set_blocking_sync(device, 1);
+        daecpp_b200_set_pooling(1); // contexts and pinned buffers are recycled from member to member
     }
 #endif
     std::atomic<std::size_t> next{0};
@@ -99,6 +100,9 @@ ensemble_result solve_ensemble(std::size_t first, std::size_t count, MemberFn me
     for (unsigned t = 1; t < threads; ++t) pool.emplace_back(work);
     work();
     for (auto &th : pool) th.join();
+#ifdef DAECPP_B200_H
+    daecpp_b200_set_pooling(0);
+#endif
     R.failed = failed.load();
     return R;
 }

@@ -197,7 +197,7 @@ class DeviceNewton
         if (slot.p)
             daecpp_b200_host_unregister(const_cast<void *>(slot.p));
         slot = Pinned();
-        if (bytes >= (std::size_t(1) << 18) && daecpp_b200_host_register(const_cast<void *>(p), bytes) == DAECPP_B200_OK)
+        if (bytes >= (std::size_t(1) << 22) && daecpp_b200_host_register(const_cast<void *>(p), bytes) == DAECPP_B200_OK)
         {
             slot.p = p;
             slot.bytes = bytes;

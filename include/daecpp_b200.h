@@ -73,6 +73,11 @@ int daecpp_b200_host_unregister(void *p);
  * spinning (cudaDeviceScheduleBlockingSync).  Meant for ensembles (dae-cpp/ensemble.hpp): with many
  * contexts in flight the host cores are needed by the user functors of other members. */
 int daecpp_b200_set_blocking_sync(int device, int on);
+/* Process-wide: keep destroyed contexts and freed page-locked buffers for the next create / host_alloc
+ * of the same size (ensembles create and destroy one context per member; cudaFree would synchronise
+ * the device under the other members).  A recycled context keeps its pattern caches and symbolic plan.
+ * on = 0 switches pooling off and releases everything pooled. */
+int daecpp_b200_set_pooling(int on);
 
 /* ---- state --------------------------------------------------------------------------- */
 /* xk = x[0] = x0, order/dt history cleared       (solver.hpp:310-313) */
