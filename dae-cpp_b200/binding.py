@@ -24,7 +24,7 @@ SYMBOLS = [
     "daecpp_b200_refactor", "daecpp_b200_solve_update", "daecpp_b200_accept_step", "daecpp_b200_set_rhs",
     "daecpp_b200_solve", "daecpp_b200_get_csc", "daecpp_b200_get_vector", "daecpp_b200_set_vector", "daecpp_b200_get_stat",
     "daecpp_b200_set_option", "daecpp_b200_iteration_resident", "daecpp_b200_event_mark", "daecpp_b200_event_elapsed_ms", "daecpp_b200_debug_unit_trace", "daecpp_b200_host_register", "daecpp_b200_host_unregister",
-    "daecpp_b200_set_blocking_sync", "daecpp_b200_set_pooling",
+    "daecpp_b200_set_blocking_sync", "daecpp_b200_set_pooling", "daecpp_b200_set_jacobian_values", "daecpp_b200_iteration_host",
 ]
 
 
@@ -62,6 +62,11 @@ def load():
     lib.daecpp_b200_set_option.argtypes = [_vp, C.c_char_p, C.c_double]
     lib.daecpp_b200_iteration_resident.argtypes = [_vp, C.c_int32, C.c_int32, _f64, C.c_double, C.c_double, C.c_double,
                                                    C.POINTER(C.c_int32)]
+    lib.daecpp_b200_set_jacobian_values.argtypes = [_vp, _vp, C.c_int64]
+    lib.daecpp_b200_iteration_host.argtypes = [_vp, _vp, C.c_int32, C.c_int32, _f64, C.c_double, C.c_double, C.c_double, _vp,
+                                               C.POINTER(C.c_double), C.POINTER(C.c_int32)]
+    lib.daecpp_b200_set_blocking_sync.argtypes = [C.c_int, C.c_int]
+    lib.daecpp_b200_set_pooling.argtypes = [C.c_int]
     lib.daecpp_b200_debug_unit_trace.argtypes = [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]
     lib.daecpp_b200_event_mark.argtypes = [_vp]
     lib.daecpp_b200_event_elapsed_ms.argtypes = [_vp, C.POINTER(C.c_double)]
@@ -171,6 +176,19 @@ class Context:
                                                               np.ascontiguousarray(dt4, np.float64), atol, rtol,
                                                               max_err_abs, C.byref(flags)), allow)
         return rc, flags.value
+
+    def set_jacobian_values_raw(self, A, nT):
+        return self._ck(self.lib.daecpp_b200_set_jacobian_values(self.h, A.ctypes.data, nT))
+
+    def iteration_host(self, f, do_refactor, order, dt4, atol, rtol, xk_out, max_err_abs=1e100, allow=()):
+        """f and xk_out: contiguous float64 arrays (pinned when option pinned_io is set)."""
+        flags = C.c_int32(0)
+        alpha = C.c_double(0)
+        rc = self._ck(self.lib.daecpp_b200_iteration_host(self.h, f.ctypes.data, int(do_refactor), order,
+                                                          np.ascontiguousarray(dt4, np.float64), atol, rtol, max_err_abs,
+                                                          xk_out.ctypes.data if xk_out is not None else None,
+                                                          C.byref(alpha), C.byref(flags)), allow)
+        return rc, flags.value, alpha.value
 
     def unit_trace(self):
         cnt = C.c_int64(0)

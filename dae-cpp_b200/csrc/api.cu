@@ -435,18 +435,11 @@ int daecpp_b200_accept_step(daecpp_b200_ctx *c, int32_t variability_on, double t
     return DAECPP_B200_OK;
 }
 
-int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int32_t order, const double dt[4],
-                                   double atol, double rtol, double max_err_abs, int32_t *flags)
+// Device part of one Newton iteration, enqueued on the stream (no synchronisation).
+static int enqueue_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t order, const double w[5], double atol,
+                             double rtol, double max_err_abs)
 {
-    if (!c || !dt || !flags) return DAECPP_B200_EINVAL;
-    cudaSetDevice(c->device);
-    if (!c->M.have_pattern || !c->J.have_pattern) return fail(c, DAECPP_B200_EINVAL, "set_mass/set_jacobian must precede");
-    double w[5];
-    if (!bdf_weights(order, dt, w)) return fail(c, DAECPP_B200_EINVAL, "unsupported time integration order");
-    int rc = build_union(c);
-    if (rc) return rc;
-    if (!c->have_symbolic && (rc = upload_symbolic(c))) return rc;
-    if (!do_refactor && !c->have_factor) return fail(c, DAECPP_B200_EINVAL, "no valid factorisation");
+    int rc;
     cudaStream_t st = c->stream;
     const bool pt = c->phase_timing;
     // all flag words of the iteration are cleared up front so that its kernels follow each other
@@ -466,8 +459,13 @@ int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int3
     if (pt) cudaEventRecord(c->pev[4], st);
     if (pt) cudaEventRecord(c->pev[5], st);
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
-    if (pt)
+    return DAECPP_B200_OK;
+}
+
+// After the stream has been synchronised: phase timers, flags, status.
+static int finish_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t *flags)
+{
+    if (c->phase_timing)
     {
         for (int k = 0; k < 5; ++k)
         {
@@ -485,6 +483,78 @@ int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int3
         if (!c->have_factor) return DAECPP_B200_EDECOMP;
     }
     return DAECPP_B200_OK;
+}
+
+static int prepare_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t order, const double dt[4], double w[5])
+{
+    if (!c->M.have_pattern || !c->J.have_pattern) return fail(c, DAECPP_B200_EINVAL, "set_mass/set_jacobian must precede");
+    if (!bdf_weights(order, dt, w)) return fail(c, DAECPP_B200_EINVAL, "unsupported time integration order");
+    int rc = build_union(c);
+    if (rc) return rc;
+    if (!c->have_symbolic && (rc = upload_symbolic(c))) return rc;
+    if (!do_refactor && !c->have_factor) return fail(c, DAECPP_B200_EINVAL, "no valid factorisation");
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int32_t order, const double dt[4],
+                                   double atol, double rtol, double max_err_abs, int32_t *flags)
+{
+    if (!c || !dt || !flags) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    double w[5];
+    int rc = prepare_iteration(c, do_refactor, order, dt, w);
+    if (rc) return rc;
+    if ((rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs))) return rc;
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return finish_iteration(c, do_refactor, flags);
+}
+
+int daecpp_b200_set_jacobian_values(daecpp_b200_ctx *c, const double *A, int64_t nT)
+{
+    if (!c || (nT > 0 && !A)) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    TripletSet &J = c->J;
+    if (!J.have_pattern || J.nT_cached != nT) return fail(c, DAECPP_B200_EINVAL, "set_jacobian_values: no cached pattern of this length");
+    if (nT > 0) DAECPP_CUDA_TRY(c, cudaMemcpyAsync(J.A.p, A, sizeof(double) * nT, cudaMemcpyHostToDevice, c->stream));
+    J.nT = nT;
+    J.vals_valid = false;
+    c->have_factor = false;
+    return DAECPP_B200_OK;
+}
+
+int daecpp_b200_iteration_host(daecpp_b200_ctx *c, const double *f_host, int32_t do_refactor, int32_t order,
+                               const double dt[4], double atol, double rtol, double max_err_abs, double *xk_host,
+                               double *alpha_out, int32_t *flags)
+{
+    if (!c || !dt || !flags || !f_host) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    double w[5];
+    int rc = prepare_iteration(c, do_refactor, order, dt, w);
+    if (rc) return rc;
+    if (alpha_out) *alpha_out = w[0];
+    cudaStream_t st = c->stream;
+    const size_t bytes = sizeof(double) * (size_t)c->n;
+    if (c->pinned_io)
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->f, f_host, bytes, cudaMemcpyHostToDevice, st));
+    else
+    {
+        if ((rc = ensure_stage(c, c->n))) return rc;
+        std::memcpy(c->h_stage, f_host, bytes);
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->f, c->h_stage, bytes, cudaMemcpyHostToDevice, st));
+    }
+    if ((rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs))) return rc;
+    if (xk_host)
+    {
+        if (c->pinned_io)
+            DAECPP_CUDA_TRY(c, cudaMemcpyAsync(xk_host, c->xk, bytes, cudaMemcpyDeviceToHost, st));
+        else
+            DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_stage, c->xk, bytes, cudaMemcpyDeviceToHost, st));
+    }
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
+    if (xk_host && !c->pinned_io) std::memcpy(xk_host, c->h_stage, bytes);
+    std::memcpy(c->h_scalars + 2, w, sizeof(w));
+    c->h_flags[6] = order;
+    return finish_iteration(c, do_refactor, flags);
 }
 
 int daecpp_b200_event_mark(daecpp_b200_ctx *c)

@@ -32,6 +32,7 @@
 #include <iomanip>
 #include <sstream>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include <dae-cpp/jacobian-matrix.hpp>
@@ -167,6 +168,10 @@ inline double time_derivative_approx(eivec &dxdt, const rvec &xk, const SolverSt
  * numerical failures are returned to the integrator, which handles them the way the reference
  * handles `linsolver.info() != Eigen::Success`.
  */
+// Jacobian functors whose triplet (i, j) stream cannot change during a solve
+template <class T> struct is_jacobian_matrix_shape : std::false_type {};
+template <class R> struct is_jacobian_matrix_shape<JacobianMatrixShape<R>> : std::true_type {};
+
 class DeviceNewton
 {
     daecpp_b200_ctx *m_ctx{nullptr};
@@ -180,6 +185,7 @@ class DeviceNewton
         std::size_t bytes{0};
     };
     Pinned m_pin[6];
+    std::size_t m_nT_pattern{0}; // length of the (i, j) stream the device has cached for J
 
     void fatal(int rc, const char *what) const
     {
@@ -255,10 +261,21 @@ public:
         if (rc)
             fatal(rc, "set_mass");
     }
-    // Jb = J.convert(size)   (dae-cpp/solver.hpp:502)
-    void set_jacobian(const sparse_matrix &J)
+    // Jb = J.convert(size)   (dae-cpp/solver.hpp:502).  fixed_pattern: the functor is a
+    // JacobianMatrixShape, whose (i, j) stream is fixed at construction (jacobian-matrix.hpp:66-92):
+    // after the first hand-off only the values travel.
+    void set_jacobian(const sparse_matrix &J, bool fixed_pattern)
     {
-        pin(m_pin[3], J.A); pin(m_pin[4], J.i); pin(m_pin[5], J.j);
+        pin(m_pin[3], J.A);
+        if (fixed_pattern && m_nT_pattern == J.A.size() && m_nT_pattern > 0)
+        {
+            const int rc = daecpp_b200_set_jacobian_values(m_ctx, J.A.data(), static_cast<int64_t>(J.A.size()));
+            if (rc)
+                fatal(rc, "set_jacobian_values");
+            return;
+        }
+        pin(m_pin[4], J.i); pin(m_pin[5], J.j);
+        m_nT_pattern = J.A.size();
         const int rc = daecpp_b200_set_jacobian(m_ctx, J.A.data(), J.i.data(), J.j.data(), static_cast<int64_t>(J.A.size()));
         ASSERT(rc != DAECPP_B200_EINDEX, "Jacobian matrix: sparse matrix index is out of boundaries, matrix size is " << m_n << "x" << m_n);
         if (rc)
@@ -295,6 +312,26 @@ public:
         diverged = (flags & DAECPP_B200_DIVERGED) != 0;
         converged = (flags & DAECPP_B200_NOT_CONVERGED) == 0;
         return true;
+    }
+    // One whole Newton iteration in one submission and one synchronisation: f upload, b, (refactor,)
+    // solves, checks, xk += dx, download of xk   (dae-cpp/solver.hpp:439-619).
+    // Returns 0, or 1 when the decomposition failed (the caller rolls back like the reference, :541-551).
+    int iterate(const SolverState &state, const SolverOptions &opt, bool do_refactor, bool &diverged, bool &converged,
+                state_vector &xk)
+    {
+        int32_t flags = 0;
+        double alpha = 0.0;
+        const int rc = daecpp_b200_iteration_host(m_ctx, m_f, do_refactor ? 1 : 0, static_cast<int32_t>(state.order), state.dt,
+                                                  opt.atol, opt.rtol, opt.max_err_abs, m_xk, &alpha, &flags);
+        if (rc == DAECPP_B200_EDECOMP)
+            return 1;
+        if (rc)
+            fatal(rc, "iteration_host");
+        diverged = (flags & DAECPP_B200_DIVERGED) != 0;
+        converged = (flags & DAECPP_B200_NOT_CONVERGED) == 0;
+        if (!diverged)
+            std::copy(m_xk, m_xk + m_n, xk.begin());
+        return 0;
     }
     void fetch_xk(state_vector &xk)
     {
@@ -471,7 +508,7 @@ class Integrator
             m_J.clear();
             m_jac(m_J, m_xk, m_state.t);
             m_J.check();
-            m_dev.set_jacobian(m_J);
+            m_dev.set_jacobian(m_J, is_jacobian_matrix_shape<Jacobian>::value);
         }
         catch (const std::exception &e)
         {
@@ -498,18 +535,15 @@ class Integrator
             if (is_fact_enabled)
                 eval_jacobian();
 
-            double alpha = 0.0;
+            bool converged = true;
             {
-                Timer timer(&t[timer::linear_algebra]);
-                alpha = m_dev.residual(m_state); // dxdt, b = M*dxdt - f, alpha = d(dxdt)/d(xk)
-            }
-
-            if (is_fact_enabled)
-            {
-                Timer timer(&t[timer::factorization]);
-                const bool ok = m_dev.refactor(alpha); // Jb = J - alpha*M, numeric LU
-                m_count.n_fact_calls++;
-                if (!ok)
+                // residual, (refactorisation,) solves, error checks and the download of the new iterate
+                // are one device submission; its time goes to the bucket of its dominant part
+                Timer timer(&t[is_fact_enabled ? timer::factorization : timer::linear_solver]);
+                const int rc = m_dev.iterate(m_state, m_opt, is_fact_enabled, diverged, converged, m_xk);
+                if (is_fact_enabled)
+                    m_count.n_fact_calls++;
+                if (rc == 1)
                 {
                     PRINT(verbose(2), " <- decomposition failed");
                     if (m_opt.recover_from_linsolver_failure)
@@ -520,34 +554,12 @@ class Integrator
                     m_status = exit_code::linsolver_failed_decomposition;
                     return false;
                 }
-            }
-
-            bool converged = true;
-            {
-                Timer timer(&t[timer::linear_solver]);
-                const bool ok = m_dev.solve_update(m_opt, diverged, converged); // dx, checks, xk += dx
                 m_count.n_lin_calls++;
-                if (!ok)
-                {
-                    PRINT(verbose(2), " <- linear solver failed");
-                    if (m_opt.recover_from_linsolver_failure)
-                    {
-                        diverged = true;
-                        return true;
-                    }
-                    m_status = exit_code::linsolver_failed_solving;
-                    return false;
-                }
                 print_char(verbose(2), is_fact_enabled ? '#' : '*');
-            }
-            {
-                Timer timer(&t[timer::error_check]);
                 if (diverged)
                 {
                     PRINT(verbose(2), " <- diverged");
                 }
-                else
-                    m_dev.fetch_xk(m_xk); // the functors and the Solution Manager need the new iterate
             }
             if (converged || diverged)
                 return true;

@@ -119,6 +119,19 @@ int daecpp_b200_accept_step(daecpp_b200_ctx *ctx, int32_t variability_on, double
  * "dx applied, flags ready"); bench.py's `value` is measured through it. */
 int daecpp_b200_iteration_resident(daecpp_b200_ctx *ctx, int32_t do_refactor, int32_t order, const double dt[4],
                                    double atol, double rtol, double max_err_abs, int32_t *flags);
+/* Values-only Jacobian hand-off: the (i, j) stream is the one of the last
+ * set_jacobian call -- JacobianMatrixShape fixes it at construction (jacobian-matrix.hpp:66-92) -- so
+ * only the nT values travel.  Asynchronous: A must stay valid until the next synchronising call
+ * (iteration_host / refactor).  EINVAL when no pattern of this length is cached. */
+int daecpp_b200_set_jacobian_values(daecpp_b200_ctx *ctx, const double *A, int64_t nT);
+/* One whole Newton iteration from HOST buffers in one submission and one synchronisation:
+ * f upload, b = M*dxdt - f, (do_refactor) Jb = J - alpha*M + refactorisation, solves, error checks,
+ * xk += dx, download of the new xk into xk_host (may be NULL).  Same results and status codes as
+ * residual + refactor + solve_update + get_xk (solver.hpp:439-619); on DAECPP_B200_EDECOMP the
+ * iterate is not meaningful and the caller rolls back exactly as the reference does (:541-551). */
+int daecpp_b200_iteration_host(daecpp_b200_ctx *ctx, const double *f_host, int32_t do_refactor, int32_t order,
+                               const double dt[4], double atol, double rtol, double max_err_abs, double *xk_host,
+                               double *alpha_out, int32_t *flags);
 /* CUDA-event stopwatch on the context's stream (torch.cuda.Event cannot see this stream). */
 int daecpp_b200_event_mark(daecpp_b200_ctx *ctx);
 int daecpp_b200_event_elapsed_ms(daecpp_b200_ctx *ctx, double *ms); /* synchronises the stream */
