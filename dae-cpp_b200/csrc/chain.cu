@@ -23,23 +23,32 @@ namespace
 {
 using namespace chain;
 
+// one level of the hierarchy as a kernel sees it
+struct LevelView
+{
+    int32_t rows, ntiles, is_top;
+    double *F, *Y;
+    const double *red_in;
+    double *red_out;
+    const double *rv_in;
+    double *rv_out;
+    double *xlev;      // solution of this level's rows (levels >= 1)
+    const double *xup; // solution of the level above = this level's separators
+};
+
 struct ChainArgs
 {
-    int32_t rows, ntiles, n, is_top;
+    LevelView lv;  // the level this launch sweeps, one CTA per tile
+    LevelView top; // fuse_top: the single-tile top level, swept by the CTA that finishes last
+    int32_t fuse_top, n;
+    uint32_t *counter; // [2 * members] tiles finished (factor, forward)
     // factor
     const int32_t *sj, *sm, *flags, *desc;
     const double *jv, *mv;
     double alpha, tol;
-    double *F, *Y;
-    const double *red_in;
-    double *red_out;
     // solve
-    const double *rv_in;
-    double *rv_out;
     const double *rhs;
     const int32_t *perm;
-    double *xlev;      // solution of this level's rows (levels >= 1)
-    const double *xup; // solution of the level above = this level's separators
     double *out, *xk;
     const double *x0;
     double atol, rtol, max_err_abs;
@@ -56,17 +65,31 @@ struct ChainArgs
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// true in exactly one CTA per member: the one whose tile finished last (its view of the other
+// tiles' results is complete after the fence)
+__device__ __forceinline__ bool last_tile_done(uint32_t *counter, int ntiles, int t)
+{
+    __shared__ int s_last;
+    __threadfence();
+    __syncthreads();
+    if (t == 0)
+    {
+        const uint32_t ticket = atomicAdd(counter, 1u);
+        s_last = (ticket == (uint32_t)ntiles - 1u);
+        if (s_last) *counter = 0u;
+    }
+    __syncthreads();
+    if (s_last) __threadfence();
+    return s_last != 0;
+}
+
 template <int B, bool FIRST>
-__global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
+__device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView &lv, FactorShared<B> &sh, int t, int tile,
+                                            int64_t mb, bool trigger)
 {
     using D = Dim<B>;
-    extern __shared__ __align__(16) unsigned char smem[];
-    FactorShared<B> &sh = *reinterpret_cast<FactorShared<B> *>(smem);
-    const int t = threadIdx.x, tile = blockIdx.x;
-    const int64_t mb = blockIdx.y;
-    double *Ft = a.F + mb * a.s_F + (size_t)tile * D::TILE_F;
-    const int nvalid = min(D::ROWS, a.rows - tile * D::ROWS);
-    pdl_wait();
+    double *Ft = lv.F + mb * a.s_F + (size_t)tile * D::TILE_F;
+    const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
     if (FIRST)
     {
         const double alpha = a.alpha_arr ? a.alpha_arr[mb] : a.alpha;
@@ -77,9 +100,9 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
         else stage_matrix_first<B>(t, D::T, tile, sh.S, a.sj, a.sm, a.flags, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
     }
     else
-        stage_matrix_reduced<B>(t, D::T, tile, a.rows, sh.S, a.red_in + mb * a.s_red);
+        stage_matrix_reduced<B>(t, D::T, tile, lv.rows, sh.S, lv.red_in + mb * a.s_red);
     __syncthreads();
-    pdl_trigger();
+    if (trigger) pdl_trigger();
     int fail = 0;
     {
         Mat<B> G, Dk, SL, H;
@@ -90,14 +113,27 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
     __syncthreads();
     factor_phase1<B>(t, nvalid, sh, Ft, a.tol, fail);
     __syncthreads();
-    if (t == 0) factor_phase2<B>(tile, a.ntiles, a.is_top != 0, sh, Ft, a.red_out + mb * a.s_red, a.tol, fail);
+    if (t == 0) factor_phase2<B>(tile, lv.ntiles, lv.is_top != 0, sh, Ft, lv.red_out + mb * a.s_red, a.tol, fail);
     if (fail) atomicOr(&a.dflags[3], 1);
+}
+
+template <int B, bool FIRST>
+__global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    FactorShared<B> &sh = *reinterpret_cast<FactorShared<B> *>(smem);
+    const int t = threadIdx.x, tile = blockIdx.x;
+    const int64_t mb = blockIdx.y;
+    pdl_wait();
+    factor_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true);
+    if (a.fuse_top && last_tile_done(a.counter + 2 * mb, a.lv.ntiles, t))
+        factor_tile<B, false>(a, a.top, sh, t, 0, mb, false); // the grid-level reduced system, same CTA
 }
 
 // backward sweep of one tile and the write-out of its unknowns; sh.xR / sh.xL, sh.F12 and sh.Y12 are set
 template <int B, bool FIRST>
-__device__ __forceinline__ void backward_tail(const ChainArgs &a, SolveShared<B> &sh, int t, int tile, int64_t mb, int nvalid,
-                                              double *Ft, double *Yt)
+__device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelView &lv, SolveShared<B> &sh, int t, int tile,
+                                              int64_t mb, int nvalid, double *Ft, double *Yt)
 {
     using D = Dim<B>;
     if (t == 0) backward_phase2<B>(sh);
@@ -154,7 +190,7 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, SolveShared<B>
     }
     else
     {
-        double *xl = a.xlev + mb * a.s_x;
+        double *xl = lv.xlev + mb * a.s_x;
         for (int idx = t; idx < total; idx += D::T)
         {
             const int q = idx / nvalid, row = idx - q * nvalid;
@@ -165,34 +201,43 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, SolveShared<B>
 
 // forward sweep of one tile; the single tile of the top level carries on into the backward sweep
 template <int B, bool FIRST>
-__global__ void __launch_bounds__(Cfg<B>::T) k_chain_forward(ChainArgs a)
+__device__ __forceinline__ void forward_tile(const ChainArgs &a, const LevelView &lv, SolveShared<B> &sh, int t, int tile,
+                                             int64_t mb, bool trigger)
 {
     using D = Dim<B>;
-    extern __shared__ __align__(16) unsigned char smem[];
-    SolveShared<B> &sh = *reinterpret_cast<SolveShared<B> *>(smem);
-    const int t = threadIdx.x, tile = blockIdx.x;
-    const int64_t mb = blockIdx.y;
-    double *Ft = a.F + mb * a.s_F + (size_t)tile * D::TILE_F;
-    double *Yt = a.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
-    const int nvalid = min(D::ROWS, a.rows - tile * D::ROWS);
-    pdl_wait();
+    double *Ft = lv.F + mb * a.s_F + (size_t)tile * D::TILE_F;
+    double *Yt = lv.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
+    const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
     if (FIRST) stage_rhs_first<B>(t, D::T, tile, a.n, sh.R, a.rhs + mb * a.s_vec, a.perm);
-    else stage_rhs_reduced<B>(t, D::T, tile, a.rows, sh.R, a.rv_in + mb * a.s_rv);
+    else stage_rhs_reduced<B>(t, D::T, tile, lv.rows, sh.R, lv.rv_in + mb * a.s_rv);
     load_small_factors<B>(t, D::T, sh, Ft);
     __syncthreads();
-    pdl_trigger();
+    if (trigger) pdl_trigger();
     forward_phase0<B>(t, nvalid, sh, Ft, Yt);
     __syncthreads();
     forward_phase1<B>(t, nvalid, sh);
     __syncthreads();
-    if (t == 0) forward_phase2<B>(tile, a.ntiles, a.is_top != 0, sh, a.rv_out + mb * a.s_rv);
+    if (t == 0) forward_phase2<B>(tile, lv.ntiles, lv.is_top != 0, sh, lv.rv_out + mb * a.s_rv);
     __syncthreads();
-    if (!a.is_top)
+    if (!lv.is_top)
     {   // the level-1/2 forward results wait in HBM for the backward kernel
         copy_small(t, D::T, Yt + D::Y0, sh.Y12, D::Y1 + D::Y2);
         return;
     }
-    backward_tail<B, FIRST>(a, sh, t, tile, mb, nvalid, Ft, Yt);
+    backward_tail<B, FIRST>(a, lv, sh, t, tile, mb, nvalid, Ft, Yt);
+}
+
+template <int B, bool FIRST>
+__global__ void __launch_bounds__(Cfg<B>::T) k_chain_forward(ChainArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    SolveShared<B> &sh = *reinterpret_cast<SolveShared<B> *>(smem);
+    const int t = threadIdx.x, tile = blockIdx.x;
+    const int64_t mb = blockIdx.y;
+    pdl_wait();
+    forward_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true);
+    if (a.fuse_top && last_tile_done(a.counter + 2 * mb + 1, a.lv.ntiles, t))
+        forward_tile<B, false>(a, a.top, sh, t, 0, mb, false); // top level: forward, then its backward sweep
 }
 
 template <int B, bool FIRST>
@@ -203,13 +248,14 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
     SolveShared<B> &sh = *reinterpret_cast<SolveShared<B> *>(smem);
     const int t = threadIdx.x, tile = blockIdx.x;
     const int64_t mb = blockIdx.y;
-    double *Ft = a.F + mb * a.s_F + (size_t)tile * D::TILE_F;
-    double *Yt = a.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
-    const int nvalid = min(D::ROWS, a.rows - tile * D::ROWS);
+    const LevelView &lv = a.lv;
+    double *Ft = lv.F + mb * a.s_F + (size_t)tile * D::TILE_F;
+    double *Yt = lv.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
+    const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
     pdl_wait();
     if (t < B)
     {
-        const double *xup = a.xup + mb * a.s_x;
+        const double *xup = lv.xup + mb * a.s_x;
         sh.xR[t] = xup[(size_t)tile * B + t];
         sh.xL[t] = tile > 0 ? xup[(size_t)(tile - 1) * B + t] : 0.0;
     }
@@ -217,7 +263,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
     copy_small(t, D::T, sh.Y12, Yt + D::Y0, D::Y1 + D::Y2);
     __syncthreads();
     pdl_trigger();
-    backward_tail<B, FIRST>(a, sh, t, tile, mb, nvalid, Ft, Yt);
+    backward_tail<B, FIRST>(a, lv, sh, t, tile, mb, nvalid, Ft, Yt);
 }
 
 // slot map -> sources of the values: sj = index into the staged triplet values (or J's
@@ -297,24 +343,36 @@ template <class T> int upload_vec(daecpp_b200_ctx *c, DevBuf<T> &d, const std::v
     return DAECPP_B200_OK;
 }
 
-ChainArgs level_args(daecpp_b200_ctx *c, int g)
+LevelView level_view(daecpp_b200_ctx *c, int g)
 {
     const Plan &P = c->CH;
     const Level &L = P.levels[g];
-    ChainArgs a{};
-    a.rows = L.rows; a.ntiles = L.ntiles; a.n = P.n;
-    a.is_top = (g + 1 == (int)P.levels.size());
-    a.F = c->dC.F.p + L.fac0;
-    a.Y = c->dC.Y.p + L.y0;
-    a.red_out = c->dC.red.p + L.red0;
-    a.rv_out = c->dC.rv.p + L.rv0;
+    LevelView v{};
+    v.rows = L.rows; v.ntiles = L.ntiles;
+    v.is_top = (g + 1 == (int)P.levels.size());
+    v.F = c->dC.F.p + L.fac0;
+    v.Y = c->dC.Y.p + L.y0;
+    v.red_out = c->dC.red.p + L.red0;
+    v.rv_out = c->dC.rv.p + L.rv0;
     if (g > 0)
     {
-        a.red_in = c->dC.red.p + P.levels[g - 1].red0;
-        a.rv_in = c->dC.rv.p + P.levels[g - 1].rv0;
-        a.xlev = c->dC.x.p + L.x0;
+        v.red_in = c->dC.red.p + P.levels[g - 1].red0;
+        v.rv_in = c->dC.rv.p + P.levels[g - 1].rv0;
+        v.xlev = c->dC.x.p + L.x0;
     }
-    if (!a.is_top) a.xup = c->dC.x.p + P.levels[g + 1].x0;
+    if (!v.is_top) v.xup = c->dC.x.p + P.levels[g + 1].x0;
+    return v;
+}
+
+// fuse: the level above g is the single-tile top level and is swept by the last CTA of this launch
+ChainArgs level_args(daecpp_b200_ctx *c, int g, bool fuse)
+{
+    ChainArgs a{};
+    a.lv = level_view(c, g);
+    a.n = c->CH.n;
+    a.fuse_top = fuse ? 1 : 0;
+    if (fuse) a.top = level_view(c, g + 1);
+    a.counter = reinterpret_cast<uint32_t *>(c->dC.counter.p);
     a.dflags = c->d_flags;
     a.tol = c->pivot_tol;
     return a;
@@ -323,7 +381,7 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g)
 template <class K> void launch_pdl(daecpp_b200_ctx *c, K kernel, const ChainArgs &a, int threads, size_t smem)
 {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(a.ntiles, 1, 1);
+    cfg.gridDim = dim3(a.lv.ntiles, 1, 1);
     cfg.blockDim = dim3(threads, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = c->stream;
@@ -379,6 +437,8 @@ int chain_try_setup(daecpp_b200_ctx *c, int32_t n, const int32_t *outer, const i
     DAECPP_CUDA_TRY(c, c->dC.red.reserve((size_t)P.red_doubles + 1));
     DAECPP_CUDA_TRY(c, c->dC.rv.reserve((size_t)P.rv_doubles + 1));
     DAECPP_CUDA_TRY(c, c->dC.x.reserve((size_t)P.x_doubles + 1));
+    DAECPP_CUDA_TRY(c, c->dC.counter.reserve(8));
+    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->dC.counter.p, 0, 8 * sizeof(int32_t), c->stream));
 #define SETATTR(B) rc = set_attributes<B>(c)
     CHAIN_DISPATCH(P.B, SETATTR)
 #undef SETATTR
@@ -400,13 +460,21 @@ int chain_try_setup(daecpp_b200_ctx *c, int32_t n, const int32_t *outer, const i
     return DAECPP_B200_OK;
 }
 
+// With exactly two levels (n up to ROWS^2 block rows) the top level rides in the last CTA of the level-0
+// launches: one launch per refactorisation, two per solve.
+// chain_fuse_top bit 0: refactorisation, bit 1: solve.  Measured on B200 (C3): fusing the solve's top level
+// saves 3.6 us, fusing the factorisation's costs 5.6 us (profiles/r01_v6_*), hence the default 2.
+static bool fuse_two_levels(const daecpp_b200_ctx *c, int bit) { return (c->chain_fuse_top & bit) && c->CH.levels.size() == 2; }
+
 int chain_refactor_async(daecpp_b200_ctx *c, double alpha)
 {
     const Plan &P = c->CH;
     const double *jv = c->direct_csc ? c->u_vals.p : (c->jvals_from_triplets ? c->J.A.p : c->J.vals.p);
-    for (int g = 0; g < (int)P.levels.size(); ++g)
+    const bool fuse = fuse_two_levels(c, 1);
+    const int nlaunch = fuse ? 1 : (int)P.levels.size();
+    for (int g = 0; g < nlaunch; ++g)
     {
-        ChainArgs a = level_args(c, g);
+        ChainArgs a = level_args(c, g, fuse);
         if (g == 0)
         {
             a.sj = c->dC.sj.p; a.sm = c->dC.sm.p; a.flags = c->dC.flags.p; a.desc = c->dC.desc.p;
@@ -426,6 +494,7 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
 {
     const Plan &P = c->CH;
     const int nlev = (int)P.levels.size();
+    const bool fuse = fuse_two_levels(c, 2);
     auto first_args = [&](ChainArgs &a) {
         a.rhs = c->b;
         a.perm = P.identity_perm ? nullptr : c->dC.perm.p;
@@ -433,9 +502,9 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         a.atol = atol; a.rtol = rtol; a.max_err_abs = max_err_abs;
         a.update = fuse_update ? 1 : 0;
     };
-    for (int g = 0; g < nlev; ++g)
+    for (int g = 0; g < (fuse ? 1 : nlev); ++g)
     {
-        ChainArgs a = level_args(c, g);
+        ChainArgs a = level_args(c, g, fuse);
         if (g == 0) first_args(a);
 #define LW(B) launch_forward<B>(c, a, g == 0)
         CHAIN_DISPATCH(P.B, LW)
@@ -444,7 +513,7 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
     }
     for (int g = nlev - 2; g >= 0; --g)
     {
-        ChainArgs a = level_args(c, g);
+        ChainArgs a = level_args(c, g, false);
         if (g == 0) first_args(a);
 #define LB(B) launch_backward<B>(c, a, g == 0)
         CHAIN_DISPATCH(P.B, LB)

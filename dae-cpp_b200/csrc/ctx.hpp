@@ -82,11 +82,11 @@ struct DeviceSymbolic
 // device side of the block-chain plan (chain.hpp)
 struct DeviceChain
 {
-    DevBuf<int32_t> ent_u, sj, sm, flags, perm, desc;
+    DevBuf<int32_t> ent_u, sj, sm, flags, perm, desc, counter;
     DevBuf<double> F, Y, red, rv, x;
     void release()
     {
-        ent_u.release(); sj.release(); sm.release(); flags.release(); perm.release(); desc.release();
+        ent_u.release(); sj.release(); sm.release(); flags.release(); perm.release(); desc.release(); counter.release();
         F.release(); Y.release(); red.release(); rv.release(); x.release();
     }
 };
@@ -140,6 +140,7 @@ struct daecpp_b200_ctx
     daecpp_b200::chain::Plan CH;
     daecpp_b200::DeviceChain dC;
     bool chain_enabled = true, chain_affine = true;
+    int chain_fuse_top = 2; // bit 0: factor, bit 1: solve (top level swept by the last CTA of the level-0 launch)
     int chain_min_n = 256, chain_max_b = 3;
     uint32_t ticket_base = 0; // value of the ticket word before the next unit launch
     int32_t solve_epoch = 0;

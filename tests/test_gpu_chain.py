@@ -137,3 +137,34 @@ def test_chain_newton_iterations_match_oracle():
         if np.any((x0 > 1e-14) & (e / np.where(x0 > 0, x0, 1.0) > 1e-6)) or np.any(e > 1e-6): want |= 2
         assert flags == want
     c.close()
+
+
+@pytest.mark.parametrize("fuse", [0, 1, 2, 3])
+def test_chain_top_level_fused_into_last_cta(fuse):
+    # two levels: the top level rides in the last CTA of the level-0 launches (fuse) or has its own launches
+    n = 300000
+    u = P.flame1d_state(n)
+    x, st = solve_chain(n, P.flame1d_jacobian(u), P.identity_mass(n), 50.0, expect_block=1, options={"chain_fuse_top": fuse})
+    assert st["chain_levels"] == 2
+    N = 6000
+    xs = P.perovskite_state(N)
+    solve_chain(2 * N, P.perovskite_jacobian(xs, N), P.perovskite_mass(N), 10.0, expect_block=2, options={"chain_fuse_top": fuse})
+
+
+def test_chain_repeated_iterations_reuse_counters():
+    n = 50000
+    u = P.flame1d_state(n)
+    J = P.flame1d_jacobian(u); M = P.identity_mass(n)
+    c = B.Context(n)
+    c.set_mass(M); c.set_jacobian(J)
+    b = np.linspace(-1, 1, n)
+    for k in range(6):
+        alpha = 10.0 + k
+        c.refactor(alpha)
+        csc = O.assemble_jb(O.port, n, J, M, alpha)
+        for _ in range(2):
+            c.set_rhs(b)
+            x = c.solve()
+            eta, _ = O.backward_error(n, csc, x, b)
+            assert eta <= 1e-12
+    c.close()
