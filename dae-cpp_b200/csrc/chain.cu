@@ -83,6 +83,74 @@ __device__ __forceinline__ bool last_tile_done(uint32_t *counter, int ntiles, in
     return s_last != 0;
 }
 
+// Affine tiles whose only mass entries sit on the diagonal of the diagonal blocks (every identity-like
+// mass matrix): the J values of the whole tile are put in flight at once with LDGSTS (cp.async, 8 bytes,
+// global -> shared, no register staging), the few M values ride in registers meanwhile, and M*alpha is
+// subtracted in place by the thread that issued the copy.  One DRAM round trip for the whole tile.
+// Entries without a mass term are J's bits unchanged, which is what `J - 0.0` gives (solver.hpp:523).
+template <int B>
+__device__ __forceinline__ bool stage_matrix_affine_async(int t, int tile, double *S, const int32_t *desc, const double *jv,
+                                                          const double *mvals, double alpha)
+{
+    using D = Dim<B>;
+    constexpr int PER = D::ROWS + 1, NFE = 3 * D::BB, NT = D::T, IT = (PER + NT - 1) / NT;
+    int32_t ja[NFE], jb[NFE], ma[B], mb[B];
+    const int32_t *d = desc + (size_t)tile * NFE * 4;
+    bool simple = true;
+#pragma unroll
+    for (int fe = 0; fe < NFE; ++fe)
+    {
+        ja[fe] = d[fe * 4]; jb[fe] = d[fe * 4 + 1];
+        const bool diag = fe >= D::BB && fe < 2 * D::BB && ((fe - D::BB) / B == (fe - D::BB) % B);
+        if (!diag && d[fe * 4 + 2] >= 0) simple = false;
+    }
+    if (!simple) return false; // uniform over the CTA: the caller takes the register-staged path
+#pragma unroll
+    for (int r = 0; r < B; ++r) { ma[r] = d[(D::BB + r * B + r) * 4 + 2]; mb[r] = d[(D::BB + r * B + r) * 4 + 3]; }
+    const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(S);
+    double m[IT][B];
+#pragma unroll
+    for (int it = 0; it < IT; ++it)
+    {
+        const int rr = t + it * NT;
+        if (rr < PER)
+        {
+            const int p = sidx<B>(rr - 1);
+#pragma unroll
+            for (int fe = 0; fe < NFE; ++fe)
+            {
+                if (ja[fe] >= 0)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s0 + 8u * (uint32_t)(fe * D::RP + p)),
+                                 "l"(jv + (ja[fe] + jb[fe] * rr))
+                                 : "memory");
+                else
+                    S[(size_t)fe * D::RP + p] = 0.0;
+            }
+#pragma unroll
+            for (int r = 0; r < B; ++r) m[it][r] = ma[r] >= 0 ? mvals[ma[r] + mb[r] * rr] : 0.0;
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_all;" ::: "memory");
+#pragma unroll
+    for (int it = 0; it < IT; ++it)
+    {
+        const int rr = t + it * NT;
+        if (rr < PER)
+        {
+            const int p = sidx<B>(rr - 1);
+#pragma unroll
+            for (int r = 0; r < B; ++r)
+                if (ma[r] >= 0)
+                {
+                    double *q = S + (size_t)(D::BB + r * B + r) * D::RP + p;
+                    *q = __dsub_rn(*q, __dmul_rn(m[it][r], alpha));
+                }
+        }
+    }
+    return true;
+}
+
 template <int B, bool FIRST>
 __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView &lv, FactorShared<B> &sh, int t, int tile,
                                             int64_t mb, bool trigger)
@@ -96,7 +164,11 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
         bool affine = true;
 #pragma unroll
         for (int fe = 0; fe < 3 * D::BB; ++fe) affine = affine && (a.flags[tile * 3 * D::BB + fe] & TF_AFF);
-        if (affine) stage_matrix_affine<B>(t, D::T, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
+        if (affine)
+        {
+            if (!stage_matrix_affine_async<B>(t, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha))
+                stage_matrix_affine<B>(t, D::T, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
+        }
         else stage_matrix_first<B>(t, D::T, tile, sh.S, a.sj, a.sm, a.flags, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
     }
     else
@@ -142,7 +214,7 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
     __syncthreads();
     backward_phase0<B>(t, nvalid, sh, Ft, Yt);
     __syncthreads();
-    constexpr int U = 4;
+    constexpr int U = 8;
     const int total = B * nvalid;
     if (FIRST)
     {
