@@ -291,7 +291,7 @@ def run_ensemble_b200(args):
     N = args.n or 4000
     n = 2 * N
     cores = os.cpu_count() or 1
-    threads = args.threads or max(1, 2 * cores // world)  # waiting threads sleep (blocking sync): oversubscribe
+    threads = args.threads or max(1, cores // world)  # one in-flight member per host core (measured best: profiles/)
     per = (args.members + world - 1) // world
     first = rank * per
     count = max(0, min(per, args.members - first))

@@ -101,6 +101,11 @@ __global__ void __launch_bounds__(Grp<G>::THREADS) k_factor_level(FrontTables T,
         Grp<G>::sync();
     }
 
+    // right-looking elimination; the rank-1 updates walk columns by warp and rows by lane (coalesced,
+    // no integer division per element)
+    constexpr int LW = (G >= 32) ? 32 : G;          // lanes along a column
+    constexpr int NW = (G >= 32) ? G / 32 : 1;      // column groups
+    const int lane = t % LW, wid = t / LW;
     for (int32_t k = 0; k < s; ++k)
     {
         double *colk = Lp + (int64_t)k * ld;
@@ -109,28 +114,38 @@ __global__ void __launch_bounds__(Grp<G>::THREADS) k_factor_level(FrontTables T,
         const double inv = 1.0 / d;
         for (int32_t i = k + 1 + t; i < ld; i += G) colk[i] *= inv;
         Grp<G>::sync();
-        const int32_t ncol = s - k - 1, nrow = ld - k - 1;
-        for (int32_t e = t; e < ncol * nrow; e += G)
+        for (int32_t j = k + 1 + wid; j < s; j += NW)
         {
-            const int32_t j = k + 1 + e / nrow, i = k + 1 + e % nrow;
-            Lp[(int64_t)j * ld + i] -= colk[i] * Lp[(int64_t)j * ld + k];
+            double *colj = Lp + (int64_t)j * ld;
+            const double ukj = colj[k];
+            for (int32_t i = k + 1 + lane; i < ld; i += LW) colj[i] -= colk[i] * ukj;
         }
         const double *utk = Ut + (int64_t)k * r;
-        for (int32_t e = t; e < ncol * r; e += G)
+        for (int32_t j = k + 1 + wid; j < s; j += NW)
         {
-            const int32_t j = k + 1 + e / r, i = e % r;
-            Ut[(int64_t)j * r + i] -= utk[i] * colk[j];
+            double *utj = Ut + (int64_t)j * r;
+            const double ljk = colk[j];
+            for (int32_t i = lane; i < r; i += LW) utj[i] -= utk[i] * ljk;
         }
         Grp<G>::sync();
     }
 
-    for (int32_t e = t; e < rr; e += G)
-    {
-        const int32_t a = e % r, bc = e / r;
-        double acc = C[e];
-        for (int32_t k = 0; k < s; ++k) acc -= Lp[(int64_t)k * ld + s + a] * Ut[(int64_t)k * r + bc];
-        C[e] = acc;
-    }
+    // Schur complement C -= F21 * F12, 4 x 1 register blocking along the rows
+    for (int32_t bc = wid; bc < r; bc += NW)
+        for (int32_t a0 = lane * 4; a0 < r; a0 += LW * 4)
+        {
+            double acc[4] = {0.0, 0.0, 0.0, 0.0};
+            const int na = min(4, r - a0);
+            for (int32_t k = 0; k < s; ++k)
+            {
+                const double u = Ut[(int64_t)k * r + bc];
+                const double *l = Lp + (int64_t)k * ld + s + a0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (q < na) acc[q] += l[q] * u;
+            }
+            for (int q = 0; q < na; ++q) C[(int64_t)bc * r + a0 + q] -= acc[q];
+        }
 }
 
 __global__ void k_permute_in(int32_t n, const int32_t *__restrict__ perm, const double *__restrict__ b, double *__restrict__ y)
@@ -249,7 +264,8 @@ int pick_group(int32_t max_dim)
     if (max_dim <= 4) return 4;
     if (max_dim <= 8) return 8;
     if (max_dim <= 48) return 32;
-    return 256;
+    if (max_dim <= 384) return 256;
+    return 1024; // the few fronts at the top of the tree: one full-size CTA each
 }
 
 #define DISPATCH_GROUP(G, KERNEL, count, ...)                                                                     \
@@ -258,6 +274,7 @@ int pick_group(int32_t max_dim)
     case 4: KERNEL<4><<<((count) + Grp<4>::FRONTS_PER_CTA - 1) / Grp<4>::FRONTS_PER_CTA, Grp<4>::THREADS, 0, st>>>(__VA_ARGS__); break;       \
     case 8: KERNEL<8><<<((count) + Grp<8>::FRONTS_PER_CTA - 1) / Grp<8>::FRONTS_PER_CTA, Grp<8>::THREADS, 0, st>>>(__VA_ARGS__); break;       \
     case 32: KERNEL<32><<<((count) + Grp<32>::FRONTS_PER_CTA - 1) / Grp<32>::FRONTS_PER_CTA, Grp<32>::THREADS, 0, st>>>(__VA_ARGS__); break;  \
+    case 1024: KERNEL<1024><<<(count), Grp<1024>::THREADS, 0, st>>>(__VA_ARGS__); break;                         \
     default: KERNEL<256><<<(count), Grp<256>::THREADS, 0, st>>>(__VA_ARGS__); break;                             \
     }
 
