@@ -135,7 +135,7 @@ static void recycle(daecpp_b200_ctx *c)
     c->chain_enabled = fresh.chain_enabled; c->chain_min_n = fresh.chain_min_n; c->chain_max_b = fresh.chain_max_b;
     c->chain_affine = fresh.chain_affine; c->chain_fuse_top = fresh.chain_fuse_top; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
     c->refine_steps = 0; c->assemble_only = false; c->pinned_io = false; c->pivot_tol = 0.0;
-    c->phase_timing = false; c->trace_units = false;
+    c->phase_timing = false; c->trace_units = false; c->blocked_lu = fresh.blocked_lu; c->blocked_lu_min_dim = fresh.blocked_lu_min_dim;
     c->n_symbolic = c->n_refactor = c->n_solve = c->n_cold = c->kernels = 0;
     c->ms_symbolic = c->ms_last_refactor = c->ms_last_solve = 0;
     c->last_alpha = 0.0;
@@ -751,6 +751,8 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "pinned_io") c->pinned_io = value != 0.0;
     else if (k == "chain") { c->chain_enabled = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "chain_affine") { c->chain_affine = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "blocked_lu") c->blocked_lu = value != 0.0;
+    else if (k == "blocked_lu_min_dim") c->blocked_lu_min_dim = (int)value;
     else if (k == "chain_fuse_top") c->chain_fuse_top = (int)value;
     else if (k == "chain_min_n") { c->chain_min_n = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "chain_max_block") { c->chain_max_b = (int)value; c->have_symbolic = false; c->have_factor = false; }

@@ -151,6 +151,8 @@ struct daecpp_b200_ctx
     bool jvals_from_triplets = false; // fused assembly reads the staged triplet values directly
     daecpp_b200::DevBuf<double> LU, CB, upd;
     double last_alpha = 0.0;
+    bool blocked_lu = true;        // big fronts: blocked multi-CTA LU (numeric.cu) instead of one CTA per front
+    int blocked_lu_min_dim = 96;   // level groups whose largest front is at least this order
 
     // scratch for the cold (sorting) path
     daecpp_b200::DevBuf<uint64_t> keys_a, keys_b;

@@ -15,6 +15,7 @@
 //
 // A front is worked on by a cooperative group of G threads (4/8/32 lanes of a warp, or a whole
 // CTA); G is picked per level from the largest front in it.
+#include <algorithm>
 #include <chrono>
 
 #include "ctx.hpp"
@@ -146,6 +147,189 @@ __global__ void __launch_bounds__(Grp<G>::THREADS) k_factor_level(FrontTables T,
             }
             for (int q = 0; q < na; ++q) C[(int64_t)bc * r + a0 + q] -= acc[q];
         }
+}
+
+// ---- blocked LU of big fronts -----------------------------------------------------------------
+// The fronts at the top of the assembly tree (orders of several hundred to ~1500 on a 1024^2 grid)
+// carry almost all the flops of the factorisation.  They are factored level by level, all fronts of
+// a level in the same launches, by a right-looking blocked LU with panels of NB columns:
+//     panel   one CTA per front: unblocked elimination of columns [k0, k1), rows [k0, ld)
+//     trsm    one thread per trailing column: U12 = L11^-1 * A12 (unit lower L11 from shared memory)
+//     gemm    64 x 64 tiles over the whole trailing matrix (F11/F21 remainder, F12 remainder and the
+//             contribution block): F -= L[:, k0:k1) * U[k0:k1, :), 4 x 4 register blocking, FP64 FMA
+// The frontal matrix lives in three pieces (symbolic.hpp): L panel (ld x s, column major), transposed
+// U panel (r x s) and contribution block (r x r); fr_at() maps (i, j) of the front onto them.
+constexpr int NB = 32;
+
+struct FrontRef
+{
+    double *Lp, *Ut, *C;
+    int32_t s, r, ld;
+};
+__device__ __forceinline__ FrontRef front_ref(const FrontTables &T, int32_t f, double *LU, double *CB)
+{
+    FrontRef F;
+    F.s = T.sn_first[f + 1] - T.sn_first[f];
+    F.r = (int32_t)(T.sn_rowptr[f + 1] - T.sn_rowptr[f]);
+    F.ld = F.s + F.r;
+    F.Lp = LU + T.sn_lu[f];
+    F.Ut = F.Lp + (int64_t)F.ld * F.s;
+    F.C = CB + T.sn_cb[f];
+    return F;
+}
+__device__ __forceinline__ double *fr_at(const FrontRef &F, int32_t i, int32_t j)
+{
+    if (j < F.s) return F.Lp + (int64_t)j * F.ld + i;
+    if (i < F.s) return F.Ut + (int64_t)i * F.r + (j - F.s);
+    return F.C + (int64_t)(j - F.s) * F.r + (i - F.s);
+}
+
+// zero the contribution block and extend-add the children (one CTA per front)
+__global__ void __launch_bounds__(1024) k_bf_assemble(FrontTables T, int32_t begin, double *__restrict__ LU,
+                                                      double *__restrict__ CB)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.x];
+    const FrontRef F = front_ref(T, f, LU, CB);
+    const int t = threadIdx.x, G = blockDim.x;
+    const int32_t s = F.s, r = F.r, ld = F.ld;
+    for (int64_t e = t; e < (int64_t)r * r; e += G) F.C[e] = 0.0;
+    __syncthreads();
+    for (int32_t ci = T.child_ptr[f]; ci < T.child_ptr[f + 1]; ++ci)
+    {
+        const int32_t c = T.child_idx[ci];
+        const int64_t rp = T.sn_rowptr[c];
+        const int32_t rc = (int32_t)(T.sn_rowptr[c + 1] - rp);
+        const double *Cc = CB + T.sn_cb[c];
+        const int32_t *rel = T.sn_rel + rp;
+        for (int32_t bc = t / 32; bc < rc; bc += G / 32)
+        {
+            const int32_t rb = rel[bc];
+            for (int32_t a = t % 32; a < rc; a += 32)
+            {
+                const int32_t ra = rel[a];
+                const double v = Cc[(int64_t)bc * rc + a];
+                if (rb < s) F.Lp[(int64_t)rb * ld + ra] += v;
+                else if (ra < s) F.Ut[(int64_t)ra * r + (rb - s)] += v;
+                else F.C[(int64_t)(rb - s) * r + (ra - s)] += v;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_bf_panel(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
+                                                  double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.x];
+    const FrontRef F = front_ref(T, f, LU, CB);
+    if (k0 >= F.s) return;
+    const int32_t k1 = min(k0 + NB, F.s), ld = F.ld;
+    const int t = threadIdx.x, lane = t % 32, wid = t / 32, NW = blockDim.x / 32;
+    for (int32_t k = k0; k < k1; ++k)
+    {
+        double *colk = F.Lp + (int64_t)k * ld;
+        const double d = colk[k];
+        if (t == 0 && (!(fabs(d) > pivot_tol) || isinf(d))) atomicOr(&flags[3], 1);
+        const double inv = 1.0 / d;
+        for (int32_t i = k + 1 + t; i < ld; i += blockDim.x) colk[i] *= inv;
+        __syncthreads();
+        for (int32_t j = k + 1 + wid; j < k1; j += NW)
+        {
+            double *colj = F.Lp + (int64_t)j * ld;
+            const double ukj = colj[k];
+            for (int32_t i = k + 1 + lane; i < ld; i += 32) colj[i] -= colk[i] * ukj;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(128) k_bf_trsm(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
+                                                 double *__restrict__ CB)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.y];
+    const FrontRef F = front_ref(T, f, LU, CB);
+    if (k0 >= F.s) return;
+    const int32_t k1 = min(k0 + NB, F.s), nb = k1 - k0;
+    if ((int64_t)blockIdx.x * blockDim.x + k1 >= F.ld) return;
+    __shared__ double L11[NB][NB + 1];
+    for (int e = threadIdx.x; e < NB * NB; e += blockDim.x)
+    {
+        const int kk = e / NB, k = e % NB; // L11[k][kk] = multiplier of row k0+k, column k0+kk
+        L11[k][kk] = (k < nb && kk < k) ? F.Lp[(int64_t)(k0 + kk) * F.ld + (k0 + k)] : 0.0;
+    }
+    __syncthreads();
+    const int32_t j = k1 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= F.ld) return;
+    double x[NB];
+#pragma unroll
+    for (int k = 0; k < NB; ++k) x[k] = k < nb ? *fr_at(F, k0 + k, j) : 0.0;
+#pragma unroll
+    for (int k = 1; k < NB; ++k)
+    {
+        double acc = x[k];
+#pragma unroll
+        for (int kk = 0; kk < k; ++kk) acc -= L11[k][kk] * x[kk];
+        x[k] = acc;
+    }
+#pragma unroll
+    for (int k = 0; k < NB; ++k)
+        if (k < nb) *fr_at(F, k0 + k, j) = x[k];
+}
+
+__global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
+                                                 double *__restrict__ CB)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.z];
+    const FrontRef F = front_ref(T, f, LU, CB);
+    if (k0 >= F.s) return;
+    const int32_t k1 = min(k0 + NB, F.s), nb = k1 - k0;
+    const int32_t i0 = k1 + blockIdx.x * 64, j0 = k1 + blockIdx.y * 64;
+    if (i0 >= F.ld || j0 >= F.ld) return;
+    __shared__ double A[NB][64 + 1], Bm[NB][64 + 1];
+    const int t = threadIdx.x;
+    for (int e = t; e < NB * 64; e += 256)
+    {
+        const int k = e / 64, q = e % 64;
+        // A[k][q] = L(i0+q, k0+k): consecutive q are consecutive addresses of column k0+k
+        A[k][q] = (k < nb && i0 + q < F.ld) ? F.Lp[(int64_t)(k0 + k) * F.ld + (i0 + q)] : 0.0;
+    }
+    for (int e = t; e < NB * 64; e += 256)
+    {
+        // U(k0+k, j0+q): column major in the L panel (k fast), row major in the U panel (q fast)
+        int k, q;
+        if (j0 + 63 < F.s) { k = e % NB; q = e / NB; } else { k = e / 64; q = e % 64; }
+        Bm[k][q] = (k < nb && j0 + q < F.ld) ? *fr_at(F, k0 + k, j0 + q) : 0.0;
+    }
+    __syncthreads();
+    const int ti = (t % 16) * 4, tj = (t / 16) * 4;
+    double acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+#pragma unroll 8
+    for (int k = 0; k < NB; ++k)
+    {
+        double av[4], bv[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { av[a] = A[k][ti + a]; bv[a] = Bm[k][tj + a]; }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] += av[a] * bv[b];
+    }
+#pragma unroll
+    for (int b = 0; b < 4; ++b)
+    {
+        const int32_t j = j0 + tj + b;
+        if (j >= F.ld) continue;
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+        {
+            const int32_t i = i0 + ti + a;
+            if (i < F.ld) *fr_at(F, i, j) -= acc[a][b];
+        }
+    }
 }
 
 __global__ void k_permute_in(int32_t n, const int32_t *__restrict__ perm, const double *__restrict__ b, double *__restrict__ y)
@@ -424,6 +608,29 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
         if (L.kind == 0)
         {
             if ((rc = launch_unit_factor(c, L, alpha))) return rc;
+        }
+        else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
+        {   // blocked right-looking LU, all fronts of the level in the same launches
+            int32_t max_s = 0, max_ld = 0;
+            for (int32_t q = 0; q < L.count; ++q)
+            {
+                const int32_t f = S.big_sn[L.begin + q];
+                max_s = std::max(max_s, S.s_of(f));
+                max_ld = std::max(max_ld, S.s_of(f) + S.r_of(f));
+            }
+            k_bf_assemble<<<L.count, 1024, 0, st>>>(T, L.begin, c->LU.p, c->CB.p);
+            c->kernels += 1;
+            for (int32_t k0 = 0; k0 < max_s; k0 += NB)
+            {
+                const int32_t rest = max_ld - std::min(k0 + NB, max_s);
+                k_bf_panel<<<L.count, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                c->kernels += 1;
+                if (rest <= 0) continue;
+                k_bf_trsm<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
+                const int tiles = (rest + 63) / 64;
+                k_bf_gemm<<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
+                c->kernels += 2;
+            }
         }
         else
         {

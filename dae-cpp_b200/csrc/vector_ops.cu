@@ -44,6 +44,7 @@ __global__ void k_residual(Bdf s, int32_t n, const int32_t *__restrict__ rowptr,
                            const int32_t *__restrict__ rowcol, const double *__restrict__ mvals,
                            const double *__restrict__ f, double *__restrict__ b)
 {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n) return;
     double acc = 0.0;
@@ -69,6 +70,9 @@ __device__ __forceinline__ double bdf_one(const Bdf &s, double xk, double x0, do
 __global__ void k_residual_diag(Bdf s, int32_t n, const double *__restrict__ mvals, const double *__restrict__ f,
                                 double *__restrict__ b)
 {
+    // the factor kernel that follows on the stream is launched programmatically dependent (chain.cu):
+    // let it start launching now; it waits for this grid's memory before touching global data
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (i + 1 < n)
     {
