@@ -332,3 +332,18 @@ def test_newton_iterations_perovskite_vs_oracle():
         xk_ref = xk.copy()
         O.port.oracle_error_check_update(n, dx, x0, xk_ref, 1e-6, 1e-6, 1e100)
     c.close()
+
+
+@pytest.mark.parametrize("m,budget", [(33, 2048), (48, 2048), (64, 4096), (128, -1), (200, -1)])
+def test_linear_solve_blocked_big_fronts(m, budget):
+    """Big fronts through the blocked multi-CTA LU (panel / trsm / gemm kernels of numeric.cu): pivot
+    blocks that are not multiples of the panel width, tiles that straddle the L panel / U panel /
+    contribution block boundary, many fronts per level."""
+    opts = {"blocked_lu": 1, "blocked_lu_min_dim": 8}
+    if budget >= 0:
+        opts["unit_smem_bytes"] = budget
+    x1, st = _solve_and_check(m * m, P.grid2d_probe_matrix(m), EMPTY, 0.0, options=opts)
+    assert st["n_big_fronts"] > 0
+    opts["blocked_lu"] = 0
+    x0, _ = _solve_and_check(m * m, P.grid2d_probe_matrix(m), EMPTY, 0.0, options=opts)
+    assert np.max(np.abs(x1 - x0)) <= 1e-10 * np.max(np.abs(x0))
