@@ -184,63 +184,101 @@ __device__ __forceinline__ double *fr_at(const FrontRef &F, int32_t i, int32_t j
     return F.C + (int64_t)(j - F.s) * F.r + (i - F.s);
 }
 
-// zero the contribution block and extend-add the children (one CTA per front)
-__global__ void __launch_bounds__(1024) k_bf_assemble(FrontTables T, int32_t begin, double *__restrict__ LU,
-                                                      double *__restrict__ CB)
+// zero the contribution blocks of a level (grid.y = front)
+__global__ void k_bf_zero(FrontTables T, int32_t begin, double *__restrict__ CB)
 {
-    const int32_t f = T.level_sn[begin + blockIdx.x];
+    const int32_t f = T.level_sn[begin + blockIdx.y];
+    const int64_t r = T.sn_rowptr[f + 1] - T.sn_rowptr[f];
+    double *C = CB + T.sn_cb[f];
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < r * r; e += (int64_t)gridDim.x * blockDim.x) C[e] = 0.0;
+}
+// extend-add of the `ord`-th child of every front of the level (grid.y = front).  Children are added
+// one launch after the other: two children may hit the same entry, and the sum must not depend on timing.
+__global__ void __launch_bounds__(256) k_bf_extend(FrontTables T, int32_t begin, int32_t ord, double *__restrict__ LU,
+                                                   double *__restrict__ CB)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.y];
+    const int32_t ci = T.child_ptr[f] + ord;
+    if (ci >= T.child_ptr[f + 1]) return;
     const FrontRef F = front_ref(T, f, LU, CB);
-    const int t = threadIdx.x, G = blockDim.x;
     const int32_t s = F.s, r = F.r, ld = F.ld;
-    for (int64_t e = t; e < (int64_t)r * r; e += G) F.C[e] = 0.0;
-    __syncthreads();
-    for (int32_t ci = T.child_ptr[f]; ci < T.child_ptr[f + 1]; ++ci)
+    const int32_t c = T.child_idx[ci];
+    const int64_t rp = T.sn_rowptr[c];
+    const int32_t rc = (int32_t)(T.sn_rowptr[c + 1] - rp);
+    const double *Cc = CB + T.sn_cb[c];
+    const int32_t *rel = T.sn_rel + rp;
+    const int lane = threadIdx.x % 32, wid = threadIdx.x / 32, NW = blockDim.x / 32;
+    for (int32_t bc = blockIdx.x * NW + wid; bc < rc; bc += gridDim.x * NW)
     {
-        const int32_t c = T.child_idx[ci];
-        const int64_t rp = T.sn_rowptr[c];
-        const int32_t rc = (int32_t)(T.sn_rowptr[c + 1] - rp);
-        const double *Cc = CB + T.sn_cb[c];
-        const int32_t *rel = T.sn_rel + rp;
-        for (int32_t bc = t / 32; bc < rc; bc += G / 32)
+        const int32_t rb = rel[bc];
+        for (int32_t a = lane; a < rc; a += 32)
         {
-            const int32_t rb = rel[bc];
-            for (int32_t a = t % 32; a < rc; a += 32)
-            {
-                const int32_t ra = rel[a];
-                const double v = Cc[(int64_t)bc * rc + a];
-                if (rb < s) F.Lp[(int64_t)rb * ld + ra] += v;
-                else if (ra < s) F.Ut[(int64_t)ra * r + (rb - s)] += v;
-                else F.C[(int64_t)(rb - s) * r + (ra - s)] += v;
-            }
+            const int32_t ra = rel[a];
+            const double v = Cc[(int64_t)bc * rc + a];
+            if (rb < s) F.Lp[(int64_t)rb * ld + ra] += v;
+            else if (ra < s) F.Ut[(int64_t)ra * r + (rb - s)] += v;
+            else F.C[(int64_t)(rb - s) * r + (ra - s)] += v;
         }
-        __syncthreads();
     }
 }
 
-__global__ void __launch_bounds__(256) k_bf_panel(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
-                                                  double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags)
+// panel, step 1: LU of the NB x NB diagonal block in shared memory (one CTA of NB x NB threads per front)
+__global__ void __launch_bounds__(NB * NB) k_bf_diag(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
+                                                     double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags)
 {
     const int32_t f = T.level_sn[begin + blockIdx.x];
     const FrontRef F = front_ref(T, f, LU, CB);
     if (k0 >= F.s) return;
-    const int32_t k1 = min(k0 + NB, F.s), ld = F.ld;
-    const int t = threadIdx.x, lane = t % 32, wid = t / 32, NW = blockDim.x / 32;
-    for (int32_t k = k0; k < k1; ++k)
+    const int32_t nb = min(k0 + NB, F.s) - k0;
+    __shared__ double A[NB][NB + 1];
+    const int i = threadIdx.x % NB, j = threadIdx.x / NB; // A[i][j] = F(k0+i, k0+j), column j contiguous in i
+    A[i][j] = (i < nb && j < nb) ? F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] : (i == j ? 1.0 : 0.0);
+    __syncthreads();
+    for (int k = 0; k < nb; ++k)
     {
-        double *colk = F.Lp + (int64_t)k * ld;
-        const double d = colk[k];
-        if (t == 0 && (!(fabs(d) > pivot_tol) || isinf(d))) atomicOr(&flags[3], 1);
-        const double inv = 1.0 / d;
-        for (int32_t i = k + 1 + t; i < ld; i += blockDim.x) colk[i] *= inv;
+        const double d = A[k][k];
+        if (threadIdx.x == 0 && (!(fabs(d) > pivot_tol) || isinf(d))) atomicOr(&flags[3], 1);
         __syncthreads();
-        for (int32_t j = k + 1 + wid; j < k1; j += NW)
-        {
-            double *colj = F.Lp + (int64_t)j * ld;
-            const double ukj = colj[k];
-            for (int32_t i = k + 1 + lane; i < ld; i += 32) colj[i] -= colk[i] * ukj;
-        }
+        if (j == k && i > k) A[i][k] = A[i][k] / d;
+        __syncthreads();
+        if (i > k && j > k) A[i][j] -= A[i][k] * A[k][j];
         __syncthreads();
     }
+    if (i < nb && j < nb) F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] = A[i][j];
+}
+
+// panel, step 2 (rows below the diagonal block): one thread per row, L21 = A21 * U11^-1 in registers
+__global__ void __launch_bounds__(128) k_bf_rows(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
+                                                 double *__restrict__ CB)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.y];
+    const FrontRef F = front_ref(T, f, LU, CB);
+    if (k0 >= F.s) return;
+    const int32_t k1 = min(k0 + NB, F.s), nb = k1 - k0;
+    if ((int64_t)blockIdx.x * blockDim.x + k1 >= F.ld) return;
+    __shared__ double U11[NB][NB + 1]; // U11[kk][k] = U(k0+kk, k0+k), kk <= k
+    for (int e = threadIdx.x; e < NB * NB; e += blockDim.x)
+    {
+        const int kk = e % NB, k = e / NB;
+        U11[kk][k] = (k < nb && kk <= k) ? F.Lp[(int64_t)(k0 + k) * F.ld + (k0 + kk)] : (kk == k ? 1.0 : 0.0);
+    }
+    __syncthreads();
+    const int32_t i = k1 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= F.ld) return;
+    double x[NB];
+#pragma unroll
+    for (int k = 0; k < NB; ++k) x[k] = k < nb ? F.Lp[(int64_t)(k0 + k) * F.ld + i] : 0.0;
+#pragma unroll
+    for (int k = 0; k < NB; ++k)
+    {
+        double acc = x[k];
+#pragma unroll
+        for (int kk = 0; kk < k; ++kk) acc -= x[kk] * U11[kk][k];
+        x[k] = acc / U11[k][k];
+    }
+#pragma unroll
+    for (int k = 0; k < NB; ++k)
+        if (k < nb) F.Lp[(int64_t)(k0 + k) * F.ld + i] = x[k];
 }
 
 __global__ void __launch_bounds__(128) k_bf_trsm(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
@@ -422,6 +460,117 @@ __global__ void __launch_bounds__(Grp<G>::THREADS) k_backward_level(FrontTables 
         const double xj = y1[j];
         for (int32_t i = t; i < j; i += G) y1[i] -= colj[i] * xj;
         Grp<G>::sync();
+    }
+}
+
+// ---- triangular solves of big fronts, blocked like the factorisation --------------------------------
+// One CTA per front.  A block of NB pivots is solved by one warp (lanes over rows, __syncwarp between
+// pivots); the rest of the CTA then applies the block to all remaining rows at once, one thread per
+// row, reading the factor columns contiguously.  Two block-wide barriers per NB pivots instead of two
+// per pivot.
+__global__ void __launch_bounds__(512) k_bf_forward(FrontTables T, int32_t begin, const double *__restrict__ LU,
+                                                    double *__restrict__ upd, double *__restrict__ y)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.x];
+    const int t = threadIdx.x, G = blockDim.x;
+    const int32_t first = T.sn_first[f];
+    const int32_t s = T.sn_first[f + 1] - first;
+    const int64_t rp0 = T.sn_rowptr[f];
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - rp0);
+    const int32_t ld = s + r;
+    const double *Lp = LU + T.sn_lu[f];
+    double *u = upd + rp0;
+    double *y1 = y + first;
+    __shared__ double yb[NB];
+    for (int32_t a = t; a < r; a += G) u[a] = 0.0;
+    __syncthreads();
+    for (int32_t ci = T.child_ptr[f]; ci < T.child_ptr[f + 1]; ++ci)
+    {
+        const int32_t c = T.child_idx[ci];
+        const int64_t rp = T.sn_rowptr[c];
+        const int32_t rc = (int32_t)(T.sn_rowptr[c + 1] - rp);
+        const double *uc = upd + rp;
+        const int32_t *rel = T.sn_rel + rp;
+        for (int32_t a = t; a < rc; a += G)
+        {
+            const int32_t ra = rel[a];
+            if (ra < s) y1[ra] += uc[a]; else u[ra - s] += uc[a];
+        }
+        __syncthreads();
+    }
+    for (int32_t k0 = 0; k0 < s; k0 += NB)
+    {
+        const int32_t k1 = min(k0 + NB, s);
+        if (t < 32)
+        {   // unit lower triangular block: lane i owns row k0 + i
+            double yi = (k0 + t < k1) ? y1[k0 + t] : 0.0;
+            for (int32_t k = k0; k < k1; ++k)
+            {
+                const double yk = __shfl_sync(0xffffffffu, yi, k - k0);
+                if (k0 + t > k && k0 + t < k1) yi -= Lp[(int64_t)k * ld + (k0 + t)] * yk;
+            }
+            if (k0 + t < k1) { y1[k0 + t] = yi; yb[t] = yi; }
+        }
+        __syncthreads();
+        for (int32_t i = k1 + t; i < ld; i += G)
+        {
+            double acc = 0.0;
+            for (int32_t k = k0; k < k1; ++k) acc += Lp[(int64_t)k * ld + i] * yb[k - k0];
+            if (i < s) y1[i] -= acc; else u[i - s] -= acc;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(512) k_bf_backward(FrontTables T, int32_t begin, const double *__restrict__ LU,
+                                                     double *__restrict__ y)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.x];
+    const int t = threadIdx.x, G = blockDim.x, lane = t % 32, wid = t / 32, NW = G / 32;
+    const int32_t first = T.sn_first[f];
+    const int32_t s = T.sn_first[f + 1] - first;
+    const int64_t rp0 = T.sn_rowptr[f];
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - rp0);
+    const int32_t ld = s + r;
+    const double *Lp = LU + T.sn_lu[f];
+    const double *Ut = Lp + (int64_t)ld * s;
+    const int32_t *rows = T.sn_rows + rp0;
+    double *y1 = y + first;
+    __shared__ double xb[NB];
+    // y1 -= F12 * x_ext: one warp per pivot row, lanes along the (contiguous) row of the U panel
+    for (int32_t k = wid; k < s; k += NW)
+    {
+        const double *utk = Ut + (int64_t)k * r;
+        double acc = 0.0;
+        for (int32_t a = lane; a < r; a += 32) acc += utk[a] * y[rows[a]];
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) y1[k] -= acc;
+    }
+    __syncthreads();
+    for (int32_t k1 = s; k1 > 0; k1 -= NB)
+    {
+        const int32_t k0 = max(k1 - NB, 0);
+        if (t < 32)
+        {   // upper triangular block (diagonal of U in place): lane i owns row k0 + i
+            double yi = (k0 + t < k1) ? y1[k0 + t] : 0.0;
+            for (int32_t j = k1 - 1; j >= k0; --j)
+            {
+                const double *colj = Lp + (int64_t)j * ld;
+                double xj = 0.0;
+                if (k0 + t == j) { xj = yi / colj[j]; yi = xj; }
+                xj = __shfl_sync(0xffffffffu, xj, j - k0);
+                if (k0 + t < j) yi -= colj[k0 + t] * xj;
+            }
+            if (k0 + t < k1) { y1[k0 + t] = yi; xb[t] = yi; }
+        }
+        __syncthreads();
+        for (int32_t i = t; i < k0; i += G)
+        {
+            double acc = 0.0;
+            for (int32_t j = k0; j < k1; ++j) acc += Lp[(int64_t)j * ld + i] * xb[j - k0];
+            y1[i] -= acc;
+        }
+        __syncthreads();
     }
 }
 
@@ -618,18 +767,27 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
                 max_s = std::max(max_s, S.s_of(f));
                 max_ld = std::max(max_ld, S.s_of(f) + S.r_of(f));
             }
-            k_bf_assemble<<<L.count, 1024, 0, st>>>(T, L.begin, c->LU.p, c->CB.p);
-            c->kernels += 1;
+            int32_t max_children = 0;
+            for (int32_t q = 0; q < L.count; ++q)
+            {
+                const int32_t f = S.big_sn[L.begin + q];
+                max_children = std::max(max_children, S.child_ptr[f + 1] - S.child_ptr[f]);
+            }
+            k_bf_zero<<<dim3(64, L.count), 256, 0, st>>>(T, L.begin, c->CB.p);
+            for (int32_t ord = 0; ord < max_children; ++ord)
+                k_bf_extend<<<dim3(64, L.count), 256, 0, st>>>(T, L.begin, ord, c->LU.p, c->CB.p);
+            c->kernels += 1 + max_children;
             for (int32_t k0 = 0; k0 < max_s; k0 += NB)
             {
                 const int32_t rest = max_ld - std::min(k0 + NB, max_s);
-                k_bf_panel<<<L.count, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                k_bf_diag<<<L.count, NB * NB, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
                 c->kernels += 1;
                 if (rest <= 0) continue;
+                k_bf_rows<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                 k_bf_trsm<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                 const int tiles = (rest + 63) / 64;
                 k_bf_gemm<<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
-                c->kernels += 2;
+                c->kernels += 3;
             }
         }
         else
@@ -691,6 +849,11 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
     {
         const GroupLaunch &L = c->groups[l];
         if (L.kind == 0) { if ((rc = launch_unit_forward(c, L, direct))) return rc; }
+        else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
+        {
+            k_bf_forward<<<L.count, 512, 0, st>>>(T, L.begin, c->LU.p, c->upd.p, c->work);
+            c->kernels += 1;
+        }
         else
         {
             DISPATCH_GROUP(L.group, k_forward_level, L.count, T, L.begin, L.count, c->LU.p, c->upd.p, c->work);
@@ -701,6 +864,11 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
     {
         const GroupLaunch &L = c->groups[l];
         if (L.kind == 0) { if ((rc = launch_unit_backward(c, L, direct, fuse_update, atol, rtol, max_err_abs))) return rc; }
+        else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
+        {
+            k_bf_backward<<<L.count, 512, 0, st>>>(T, L.begin, c->LU.p, c->work);
+            c->kernels += 1;
+        }
         else
         {
             DISPATCH_GROUP(L.group, k_backward_level, L.count, T, L.begin, L.count, c->LU.p, c->work);
