@@ -717,6 +717,7 @@ int daecpp_b200_get_stat(daecpp_b200_ctx *c, const char *key, double *value)
     else if (k == "ms_phase_solve") *value = c->n_phase_samples ? c->ms_phase[3] / c->n_phase_samples : 0;
     else if (k == "ms_phase_update") *value = c->n_phase_samples ? c->ms_phase[4] / c->n_phase_samples : 0;
     else if (k == "n_phase_samples") *value = c->n_phase_samples;
+    else if (k == "jvals_from_triplets") *value = c->jvals_from_triplets ? 1 : 0;
     else if (k == "upd_doubles") *value = (double)c->S.upd_size;
     else if (k == "n_units") *value = c->S.nunit;
     else if (k == "n_stages") *value = c->S.nstages;

@@ -464,12 +464,16 @@ __global__ void __launch_bounds__(Grp<G>::THREADS) k_backward_level(FrontTables 
 }
 
 // ---- triangular solves of big fronts, blocked like the factorisation --------------------------------
-// One CTA per front.  A block of NB pivots is solved by one warp (lanes over rows, __syncwarp between
-// pivots); the rest of the CTA then applies the block to all remaining rows at once, one thread per
-// row, reading the factor columns contiguously.  Two block-wide barriers per NB pivots instead of two
-// per pivot.
-__global__ void __launch_bounds__(512) k_bf_forward(FrontTables T, int32_t begin, const double *__restrict__ LU,
-                                                    double *__restrict__ upd, double *__restrict__ y)
+// Per level two launches each way.  The triangular part (pivot rows only) runs one CTA per front: a
+// block of NB pivots is solved by one warp out of registers (the NB x NB diagonal block is loaded with
+// independent loads first, the dependent chain is shuffles only), then the whole CTA applies the block
+// to the remaining pivot rows, one thread per row, factor columns read contiguously.  The rectangular
+// part (L21 forward, U12 backward) is a dense matrix-vector product spread over many CTAs per front --
+// near the root there are only one or two fronts per level and a single SM cannot stream their panels.
+constexpr int GV_ROWS = 64, GV_SEG = 4;
+
+__global__ void __launch_bounds__(512) k_bf_forward_tri(FrontTables T, int32_t begin, const double *__restrict__ LU,
+                                                        double *__restrict__ upd, double *__restrict__ y)
 {
     const int32_t f = T.level_sn[begin + blockIdx.x];
     const int t = threadIdx.x, G = blockDim.x;
@@ -503,65 +507,132 @@ __global__ void __launch_bounds__(512) k_bf_forward(FrontTables T, int32_t begin
         const int32_t k1 = min(k0 + NB, s);
         if (t < 32)
         {   // unit lower triangular block: lane i owns row k0 + i
-            double yi = (k0 + t < k1) ? y1[k0 + t] : 0.0;
-            for (int32_t k = k0; k < k1; ++k)
+            const int32_t i = k0 + t;
+            double l[NB];
+#pragma unroll
+            for (int q = 0; q < NB; ++q) l[q] = (i < k1 && q < t) ? Lp[(int64_t)(k0 + q) * ld + i] : 0.0;
+            double yi = (i < k1) ? y1[i] : 0.0;
+#pragma unroll
+            for (int q = 0; q < NB; ++q)
             {
-                const double yk = __shfl_sync(0xffffffffu, yi, k - k0);
-                if (k0 + t > k && k0 + t < k1) yi -= Lp[(int64_t)k * ld + (k0 + t)] * yk;
+                const double yk = __shfl_sync(0xffffffffu, yi, q);
+                if (q < t) yi -= l[q] * yk;
             }
-            if (k0 + t < k1) { y1[k0 + t] = yi; yb[t] = yi; }
+            if (i < k1) { y1[i] = yi; yb[t] = yi; }
         }
         __syncthreads();
-        for (int32_t i = k1 + t; i < ld; i += G)
+        for (int32_t i = k1 + t; i < s; i += G)
         {
             double acc = 0.0;
             for (int32_t k = k0; k < k1; ++k) acc += Lp[(int64_t)k * ld + i] * yb[k - k0];
-            if (i < s) y1[i] -= acc; else u[i - s] -= acc;
+            y1[i] -= acc;
         }
         __syncthreads();
     }
 }
 
-__global__ void __launch_bounds__(512) k_bf_backward(FrontTables T, int32_t begin, const double *__restrict__ LU,
-                                                     double *__restrict__ y)
+// u -= L21 * y1.  CTA = GV_ROWS rows x GV_SEG interleaved pivot segments, partial sums folded in a fixed order.
+__global__ void __launch_bounds__(GV_ROWS *GV_SEG) k_bf_forward_gemv(FrontTables T, int32_t begin, const double *__restrict__ LU,
+                                                                     double *__restrict__ upd, const double *__restrict__ y)
 {
-    const int32_t f = T.level_sn[begin + blockIdx.x];
-    const int t = threadIdx.x, G = blockDim.x, lane = t % 32, wid = t / 32, NW = G / 32;
+    const int32_t f = T.level_sn[begin + blockIdx.y];
     const int32_t first = T.sn_first[f];
     const int32_t s = T.sn_first[f + 1] - first;
     const int64_t rp0 = T.sn_rowptr[f];
     const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - rp0);
+    const int32_t a0 = blockIdx.x * GV_ROWS;
+    if (a0 >= r) return;
     const int32_t ld = s + r;
     const double *Lp = LU + T.sn_lu[f];
-    const double *Ut = Lp + (int64_t)ld * s;
+    const double *y1 = y + first;
+    const int ri = threadIdx.x % GV_ROWS, seg = threadIdx.x / GV_ROWS;
+    const int32_t a = a0 + ri;
+    __shared__ double part[GV_SEG][GV_ROWS];
+    double acc0 = 0.0, acc1 = 0.0;
+    if (a < r)
+    {
+        const double *row = Lp + s + a;
+        int32_t k = seg;
+        for (; k + GV_SEG < s; k += 2 * GV_SEG)
+        {
+            acc0 += row[(int64_t)k * ld] * y1[k];
+            acc1 += row[(int64_t)(k + GV_SEG) * ld] * y1[k + GV_SEG];
+        }
+        if (k < s) acc0 += row[(int64_t)k * ld] * y1[k];
+    }
+    part[seg][ri] = acc0 + acc1;
+    __syncthreads();
+    if (seg == 0 && a < r)
+    {
+        double sum = part[0][ri];
+#pragma unroll
+        for (int q = 1; q < GV_SEG; ++q) sum += part[q][ri];
+        upd[rp0 + a] -= sum;
+    }
+}
+
+// y1 -= U12 * x_ext: one warp per pivot row, lanes along the (contiguous) row of the U panel
+__global__ void __launch_bounds__(256) k_bf_backward_gemv(FrontTables T, int32_t begin, const double *__restrict__ LU,
+                                                          double *__restrict__ y)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.y];
+    const int lane = threadIdx.x % 32, wid = threadIdx.x / 32;
+    const int32_t first = T.sn_first[f];
+    const int32_t s = T.sn_first[f + 1] - first;
+    const int32_t k = blockIdx.x * 8 + wid;
+    if (k >= s) return;
+    const int64_t rp0 = T.sn_rowptr[f];
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - rp0);
+    if (r == 0) return;
+    const int32_t ld = s + r;
+    const double *utk = LU + T.sn_lu[f] + (int64_t)ld * s + (int64_t)k * r;
     const int32_t *rows = T.sn_rows + rp0;
+    double acc0 = 0.0, acc1 = 0.0;
+    int32_t a = lane;
+    for (; a + 32 < r; a += 64)
+    {
+        acc0 += utk[a] * y[rows[a]];
+        acc1 += utk[a + 32] * y[rows[a + 32]];
+    }
+    if (a < r) acc0 += utk[a] * y[rows[a]];
+    double acc = acc0 + acc1;
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) y[first + k] -= acc;
+}
+
+__global__ void __launch_bounds__(512) k_bf_backward_tri(FrontTables T, int32_t begin, const double *__restrict__ LU,
+                                                         double *__restrict__ y)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.x];
+    const int t = threadIdx.x, G = blockDim.x;
+    const int32_t first = T.sn_first[f];
+    const int32_t s = T.sn_first[f + 1] - first;
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - T.sn_rowptr[f]);
+    const int32_t ld = s + r;
+    const double *Lp = LU + T.sn_lu[f];
     double *y1 = y + first;
     __shared__ double xb[NB];
-    // y1 -= F12 * x_ext: one warp per pivot row, lanes along the (contiguous) row of the U panel
-    for (int32_t k = wid; k < s; k += NW)
-    {
-        const double *utk = Ut + (int64_t)k * r;
-        double acc = 0.0;
-        for (int32_t a = lane; a < r; a += 32) acc += utk[a] * y[rows[a]];
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (lane == 0) y1[k] -= acc;
-    }
-    __syncthreads();
     for (int32_t k1 = s; k1 > 0; k1 -= NB)
     {
         const int32_t k0 = max(k1 - NB, 0);
         if (t < 32)
         {   // upper triangular block (diagonal of U in place): lane i owns row k0 + i
-            double yi = (k0 + t < k1) ? y1[k0 + t] : 0.0;
-            for (int32_t j = k1 - 1; j >= k0; --j)
+            const int32_t i = k0 + t, nb = k1 - k0;
+            double uu[NB];
+#pragma unroll
+            for (int q = 0; q < NB; ++q) uu[q] = (q < nb && t <= q) ? Lp[(int64_t)(k0 + q) * ld + i] : 1.0;
+            double yi = (i < k1) ? y1[i] : 0.0;
+#pragma unroll
+            for (int q = NB - 1; q >= 0; --q)
             {
-                const double *colj = Lp + (int64_t)j * ld;
-                double xj = 0.0;
-                if (k0 + t == j) { xj = yi / colj[j]; yi = xj; }
-                xj = __shfl_sync(0xffffffffu, xj, j - k0);
-                if (k0 + t < j) yi -= colj[k0 + t] * xj;
+                if (q < nb)
+                {
+                    if (t == q) yi = yi / uu[q];
+                    const double xj = __shfl_sync(0xffffffffu, yi, q);
+                    if (t < q) yi -= uu[q] * xj;
+                }
             }
-            if (k0 + t < k1) { y1[k0 + t] = yi; xb[t] = yi; }
+            if (i < k1) { y1[i] = yi; xb[t] = yi; }
         }
         __syncthreads();
         for (int32_t i = t; i < k0; i += G)
@@ -851,8 +922,10 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
         if (L.kind == 0) { if ((rc = launch_unit_forward(c, L, direct))) return rc; }
         else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
         {
-            k_bf_forward<<<L.count, 512, 0, st>>>(T, L.begin, c->LU.p, c->upd.p, c->work);
-            c->kernels += 1;
+            k_bf_forward_tri<<<L.count, 512, 0, st>>>(T, L.begin, c->LU.p, c->upd.p, c->work);
+            k_bf_forward_gemv<<<dim3((L.max_dim + GV_ROWS - 1) / GV_ROWS, L.count), GV_ROWS * GV_SEG, 0, st>>>(T, L.begin, c->LU.p, c->upd.p,
+                                                                                                            c->work);
+            c->kernels += 2;
         }
         else
         {
@@ -866,8 +939,9 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
         if (L.kind == 0) { if ((rc = launch_unit_backward(c, L, direct, fuse_update, atol, rtol, max_err_abs))) return rc; }
         else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
         {
-            k_bf_backward<<<L.count, 512, 0, st>>>(T, L.begin, c->LU.p, c->work);
-            c->kernels += 1;
+            k_bf_backward_gemv<<<dim3((L.max_dim + 7) / 8, L.count), 256, 0, st>>>(T, L.begin, c->LU.p, c->work);
+            k_bf_backward_tri<<<L.count, 512, 0, st>>>(T, L.begin, c->LU.p, c->work);
+            c->kernels += 2;
         }
         else
         {
