@@ -48,6 +48,8 @@ def parse_args():
                     help="ensemble: run the partition + gather logic on CPU (gloo, reference driver) -- used by tests/")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--option", action="append", default=[], metavar="KEY=VALUE",
+                    help="daecpp_b200_set_option before the first call (A/B runs of one kernel variant on one box)")
     return ap.parse_args()
 
 
@@ -392,6 +394,9 @@ def run_b200_arm(args):
     atol = rtol = 1e-6
     lib = B.load()
     c = B.Context(n, local, lib)
+    for kv in args.option:
+        k, v = kv.split("=", 1)
+        c.set_option(k, float(v))
 
     # pinned host buffers: what the overlay sparse_matrix / state vectors hand to the C ABI
     nT = len(w["J"][0])

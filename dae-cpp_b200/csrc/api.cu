@@ -133,7 +133,7 @@ static void recycle(daecpp_b200_ctx *c)
         c->sopt.max_super != fresh.sopt.max_super)
         c->have_symbolic = false;
     c->chain_enabled = fresh.chain_enabled; c->chain_min_n = fresh.chain_min_n; c->chain_max_b = fresh.chain_max_b;
-    c->chain_affine = fresh.chain_affine; c->chain_fuse_top = fresh.chain_fuse_top; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
+    c->chain_affine = fresh.chain_affine; c->chain_packed = fresh.chain_packed; c->chain_fuse_top = fresh.chain_fuse_top; c->chain_defer_top = fresh.chain_defer_top; c->chain_may_defer = false; c->chain_top_pending = false; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
     c->refine_steps = 0; c->assemble_only = false; c->pinned_io = false; c->pivot_tol = 0.0;
     c->phase_timing = false; c->trace_units = false; c->blocked_lu = fresh.blocked_lu; c->blocked_lu_min_dim = fresh.blocked_lu_min_dim;
     c->n_symbolic = c->n_refactor = c->n_solve = c->n_cold = c->kernels = 0;
@@ -453,7 +453,12 @@ static int enqueue_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t or
     if (pt) cudaEventRecord(c->pev[1], st);
     if ((rc = launch_residual(c, order, w))) return rc;
     if (pt) cudaEventRecord(c->pev[2], st);
-    if (do_refactor && (rc = numeric_refactor_async(c, w[0], false))) return rc;
+    // the solve follows on the same stream and the flags are read once at the end: a two-level chain
+    // may leave its (tiny) top-level factorisation to an extra CTA of the forward launch
+    c->chain_may_defer = true;
+    if (do_refactor) rc = numeric_refactor_async(c, w[0], false);
+    c->chain_may_defer = false;
+    if (do_refactor && rc) return rc;
     if (pt) cudaEventRecord(c->pev[3], st);
     if ((rc = numeric_solve(c, true, atol, rtol, max_err_abs))) return rc;
     if (pt) cudaEventRecord(c->pev[4], st);
@@ -676,7 +681,8 @@ int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *c, int64_t *out, int64_t cap, 
 {
     if (!c || !count) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
-    const int64_t m = (int64_t)c->S.nunit * 12; // factor, forward, backward
+    // subtree units: factor, forward, backward x 4 stamps; chain path: 5 kernels x tiles x 8 stamps (chain.cu)
+    const int64_t m = c->CH.active ? (int64_t)5 * c->CH.levels[0].ntiles * 8 : (int64_t)c->S.nunit * 12;
     *count = m;
     if (!c->trace.p || !out) return DAECPP_B200_OK;
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
@@ -751,10 +757,12 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "unit_threads") { c->unit_threads = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "pinned_io") c->pinned_io = value != 0.0;
     else if (k == "chain") { c->chain_enabled = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "chain_packed") c->chain_packed = value != 0.0 ? 1 : 0;
     else if (k == "chain_affine") { c->chain_affine = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "blocked_lu") c->blocked_lu = value != 0.0;
     else if (k == "blocked_lu_min_dim") c->blocked_lu_min_dim = (int)value;
     else if (k == "chain_fuse_top") c->chain_fuse_top = (int)value;
+    else if (k == "chain_defer_top") c->chain_defer_top = value != 0.0;
     else if (k == "chain_min_n") { c->chain_min_n = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "chain_max_block") { c->chain_max_b = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "trace_units") c->trace_units = value != 0.0;

@@ -40,7 +40,8 @@ struct ChainArgs
 {
     LevelView lv;  // the level this launch sweeps, one CTA per tile
     LevelView top; // fuse_top: the single-tile top level, swept by the CTA that finishes last
-    int32_t fuse_top, n;
+    int32_t fuse_top, n, trace_tiles, packed;
+    int32_t extra_factor; // forward launch: CTA number lv.ntiles factors the top level (deferred from the factor launch)
     uint32_t *counter; // [2 * members] tiles finished (factor, forward)
     // factor
     const int32_t *sj, *sm, *flags, *desc;
@@ -57,7 +58,19 @@ struct ChainArgs
     // ensemble: member = blockIdx.y, strides in elements
     const double *alpha_arr;
     int64_t s_jv, s_mv, s_F, s_Y, s_red, s_rv, s_x, s_vec;
+    long long *trace; // debug ("trace_units"): [kernel][tile][8] %globaltimer stamps, member 0
 };
+
+constexpr int TRACE_SLOTS = 8, TRACE_KERNELS = 5; // factor tiles, factor top, forward tiles, top solve, backward tiles
+__device__ __forceinline__ void stamp(const ChainArgs &a, int kernel, int tile, int slot)
+{
+    if (a.trace && threadIdx.x == 0 && blockIdx.y == 0)
+    {
+        long long ns;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns));
+        a.trace[((size_t)kernel * a.trace_tiles + tile) * TRACE_SLOTS + slot] = ns;
+    }
+}
 
 // Programmatic dependent launch: the chain kernels of one Newton iteration follow each other on the
 // stream with nothing in between, so each one lets its successor start launching as soon as its own
@@ -90,48 +103,79 @@ __device__ __forceinline__ bool last_tile_done(uint32_t *counter, int ntiles, in
 // Entries without a mass term are J's bits unchanged, which is what `J - 0.0` gives (solver.hpp:523).
 template <int B>
 __device__ __forceinline__ bool stage_matrix_affine_async(int t, int tile, double *S, const int32_t *desc, const double *jv,
-                                                          const double *mvals, double alpha)
+                                                          const double *mvals, double alpha, bool allow_packed)
 {
     using D = Dim<B>;
     constexpr int PER = D::ROWS + 1, NFE = 3 * D::BB, NT = D::T, IT = (PER + NT - 1) / NT;
-    int32_t ja[NFE], jb[NFE], ma[B], mb[B];
-    const int32_t *d = desc + (size_t)tile * NFE * 4;
-    bool simple = true;
+    __shared__ int32_t sd[NFE * DESC];
+    for (int k = t; k < NFE * DESC; k += NT) sd[k] = desc[(size_t)tile * NFE * DESC + k];
+    __syncthreads();
+    bool simple = true, packed = allow_packed && sd[DJLO] <= sd[DJHI];
 #pragma unroll
     for (int fe = 0; fe < NFE; ++fe)
     {
-        ja[fe] = d[fe * 4]; jb[fe] = d[fe * 4 + 1];
         const bool diag = fe >= D::BB && fe < 2 * D::BB && ((fe - D::BB) / B == (fe - D::BB) % B);
-        if (!diag && d[fe * 4 + 2] >= 0) simple = false;
+        if (!diag && sd[fe * DESC + DMLO] <= sd[fe * DESC + DMHI]) simple = false;
+        // one contiguous run: field fe of row rr sits at j0 + NFE*rr + fe
+        packed = packed && sd[fe * DESC + DJLO] <= sd[fe * DESC + DJHI] && sd[fe * DESC + DJ0] == sd[DJ0] + fe && sd[fe * DESC + DJS] == NFE;
     }
     if (!simple) return false; // uniform over the CTA: the caller takes the register-staged path
-#pragma unroll
-    for (int r = 0; r < B; ++r) { ma[r] = d[(D::BB + r * B + r) * 4 + 2]; mb[r] = d[(D::BB + r * B + r) * 4 + 3]; }
     const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(S);
     double m[IT][B];
+    if (packed)
+    {   // row-major triplet streams (flame-1D: (i,i-1),(i,i),(i,i+1) per row): consecutive lanes copy
+        // consecutive doubles (every sector requested once, fully used), the scatter is on the
+        // shared-memory side
+        const double *src = jv + sd[DJ0];
+        for (int idx = t; idx < NFE * PER; idx += NT)
+        {
+            const int rr = idx / NFE, fe = idx - rr * NFE;
+            const int32_t *e = sd + fe * DESC;
+            const int q = fe * D::RP + sidx<B>(rr - 1);
+            if (rr >= e[DJLO] && rr <= e[DJHI])
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s0 + 8u * (uint32_t)q), "l"(src + idx) : "memory");
+            else
+                S[q] = rr >= e[DONE] ? 1.0 : 0.0;
+        }
+    }
+    else
+    {
+#pragma unroll
+        for (int it = 0; it < IT; ++it)
+        {
+            const int rr = t + it * NT;
+            if (rr < PER)
+            {
+                const int p = sidx<B>(rr - 1);
+#pragma unroll
+                for (int fe = 0; fe < NFE; ++fe)
+                {
+                    const int32_t *e = sd + fe * DESC;
+                    if (rr >= e[DJLO] && rr <= e[DJHI])
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s0 + 8u * (uint32_t)(fe * D::RP + p)),
+                                     "l"(jv + (e[DJ0] + e[DJS] * rr))
+                                     : "memory");
+                    else
+                        S[(size_t)fe * D::RP + p] = rr >= e[DONE] ? 1.0 : 0.0;
+                }
+            }
+        }
+    }
+    // the few M values (diagonal of the diagonal blocks) ride in registers meanwhile
 #pragma unroll
     for (int it = 0; it < IT; ++it)
     {
         const int rr = t + it * NT;
-        if (rr < PER)
+#pragma unroll
+        for (int r = 0; r < B; ++r)
         {
-            const int p = sidx<B>(rr - 1);
-#pragma unroll
-            for (int fe = 0; fe < NFE; ++fe)
-            {
-                if (ja[fe] >= 0)
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s0 + 8u * (uint32_t)(fe * D::RP + p)),
-                                 "l"(jv + (ja[fe] + jb[fe] * rr))
-                                 : "memory");
-                else
-                    S[(size_t)fe * D::RP + p] = 0.0;
-            }
-#pragma unroll
-            for (int r = 0; r < B; ++r) m[it][r] = ma[r] >= 0 ? mvals[ma[r] + mb[r] * rr] : 0.0;
+            const int32_t *e = sd + (D::BB + r * B + r) * DESC;
+            m[it][r] = (rr >= e[DMLO] && rr <= e[DMHI]) ? mvals[e[DM0] + e[DMS] * rr] : 0.0;
         }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_all;" ::: "memory");
+    if (packed) __syncthreads(); // there the copy of an element and its mass correction belong to different threads
 #pragma unroll
     for (int it = 0; it < IT; ++it)
     {
@@ -141,11 +185,14 @@ __device__ __forceinline__ bool stage_matrix_affine_async(int t, int tile, doubl
             const int p = sidx<B>(rr - 1);
 #pragma unroll
             for (int r = 0; r < B; ++r)
-                if (ma[r] >= 0)
+            {
+                const int32_t *e = sd + (D::BB + r * B + r) * DESC;
+                if (rr >= e[DMLO] && rr <= e[DMHI])
                 {
                     double *q = S + (size_t)(D::BB + r * B + r) * D::RP + p;
                     *q = __dsub_rn(*q, __dmul_rn(m[it][r], alpha));
                 }
+            }
         }
     }
     return true;
@@ -158,6 +205,8 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
     using D = Dim<B>;
     double *Ft = lv.F + mb * a.s_F + (size_t)tile * D::TILE_F;
     const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
+    const int tk = FIRST ? 0 : 1;
+    stamp(a, tk, tile, 0);
     if (FIRST)
     {
         const double alpha = a.alpha_arr ? a.alpha_arr[mb] : a.alpha;
@@ -166,7 +215,7 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
         for (int fe = 0; fe < 3 * D::BB; ++fe) affine = affine && (a.flags[tile * 3 * D::BB + fe] & TF_AFF);
         if (affine)
         {
-            if (!stage_matrix_affine_async<B>(t, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha))
+            if (!stage_matrix_affine_async<B>(t, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha, a.packed != 0))
                 stage_matrix_affine<B>(t, D::T, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
         }
         else stage_matrix_first<B>(t, D::T, tile, sh.S, a.sj, a.sm, a.flags, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
@@ -174,6 +223,7 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
     else
         stage_matrix_reduced<B>(t, D::T, tile, lv.rows, sh.S, lv.red_in + mb * a.s_red);
     __syncthreads();
+    stamp(a, tk, tile, 1);
     if (trigger) pdl_trigger();
     int fail = 0;
     {
@@ -183,10 +233,13 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
         factor_store1<B>(t, sh, G, Dk, SL, H);
     }
     __syncthreads();
+    stamp(a, tk, tile, 2);
     factor_phase1<B>(t, nvalid, sh, Ft, a.tol, fail);
     __syncthreads();
+    stamp(a, tk, tile, 3);
     if (t == 0) factor_phase2<B>(tile, lv.ntiles, lv.is_top != 0, sh, Ft, lv.red_out + mb * a.s_red, a.tol, fail);
     if (fail) atomicOr(&a.dflags[3], 1);
+    stamp(a, tk, tile, 4);
 }
 
 template <int B, bool FIRST>
@@ -196,6 +249,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
     FactorShared<B> &sh = *reinterpret_cast<FactorShared<B> *>(smem);
     const int t = threadIdx.x, tile = blockIdx.x;
     const int64_t mb = blockIdx.y;
+    stamp(a, FIRST ? 0 : 1, tile, 5);
     pdl_wait();
     factor_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true);
     if (a.fuse_top && last_tile_done(a.counter + 2 * mb, a.lv.ntiles, t))
@@ -280,23 +334,30 @@ __device__ __forceinline__ void forward_tile(const ChainArgs &a, const LevelView
     double *Ft = lv.F + mb * a.s_F + (size_t)tile * D::TILE_F;
     double *Yt = lv.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
     const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
+    const int tk = FIRST ? 2 : 3;
+    stamp(a, tk, tile, 0);
     if (FIRST) stage_rhs_first<B>(t, D::T, tile, a.n, sh.R, a.rhs + mb * a.s_vec, a.perm);
     else stage_rhs_reduced<B>(t, D::T, tile, lv.rows, sh.R, lv.rv_in + mb * a.s_rv);
     load_small_factors<B>(t, D::T, sh, Ft);
     __syncthreads();
+    stamp(a, tk, tile, 1);
     if (trigger) pdl_trigger();
     forward_phase0<B>(t, nvalid, sh, Ft, Yt);
     __syncthreads();
+    stamp(a, tk, tile, 2);
     forward_phase1<B>(t, nvalid, sh);
     __syncthreads();
     if (t == 0) forward_phase2<B>(tile, lv.ntiles, lv.is_top != 0, sh, lv.rv_out + mb * a.s_rv);
     __syncthreads();
+    stamp(a, tk, tile, 3);
     if (!lv.is_top)
     {   // the level-1/2 forward results wait in HBM for the backward kernel
         copy_small(t, D::T, Yt + D::Y0, sh.Y12, D::Y1 + D::Y2);
+        stamp(a, tk, tile, 4);
         return;
     }
     backward_tail<B, FIRST>(a, lv, sh, t, tile, mb, nvalid, Ft, Yt);
+    stamp(a, tk, tile, 4);
 }
 
 template <int B, bool FIRST>
@@ -306,9 +367,15 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_forward(ChainArgs a)
     SolveShared<B> &sh = *reinterpret_cast<SolveShared<B> *>(smem);
     const int t = threadIdx.x, tile = blockIdx.x;
     const int64_t mb = blockIdx.y;
+    stamp(a, FIRST ? 2 : 3, tile, 5);
     pdl_wait();
-    forward_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true);
-    if (a.fuse_top && last_tile_done(a.counter + 2 * mb + 1, a.lv.ntiles, t))
+    if (a.extra_factor && tile == a.lv.ntiles)
+    {   // uniform over the CTA: the grid-level reduced system is factored here while the other CTAs sweep forward
+        factor_tile<B, false>(a, a.top, *reinterpret_cast<FactorShared<B> *>(smem), t, 0, mb, true);
+    }
+    else
+        forward_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true);
+    if (a.fuse_top && last_tile_done(a.counter + 2 * mb + 1, a.lv.ntiles + a.extra_factor, t))
         forward_tile<B, false>(a, a.top, sh, t, 0, mb, false); // top level: forward, then its backward sweep
 }
 
@@ -324,7 +391,9 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
     double *Ft = lv.F + mb * a.s_F + (size_t)tile * D::TILE_F;
     double *Yt = lv.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
     const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
+    stamp(a, 4, tile, 0);
     pdl_wait();
+    stamp(a, 4, tile, 1);
     if (t < B)
     {
         const double *xup = lv.xup + mb * a.s_x;
@@ -334,8 +403,10 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
     load_small_factors<B>(t, D::T, sh, Ft);
     copy_small(t, D::T, sh.Y12, Yt + D::Y0, D::Y1 + D::Y2);
     __syncthreads();
+    stamp(a, 4, tile, 2);
     pdl_trigger();
     backward_tail<B, FIRST>(a, lv, sh, t, tile, mb, nvalid, Ft, Yt);
+    stamp(a, 4, tile, 3);
 }
 
 // slot map -> sources of the values: sj = index into the staged triplet values (or J's
@@ -359,31 +430,44 @@ __global__ void k_chain_compose(int64_t ne, int32_t per_fe, const int32_t *__res
     if (m >= 0) atomicOr(&flags[e / per_fe], TF_MASS);
 }
 
-// one block per (tile, field element): is the value source an arithmetic progression in the row?
+// one block per (tile, field element): is the value source an arithmetic progression over a range of
+// rows, structural zeros before it and zeros / identity padding behind it?  (chain_ops.hpp, DESC)
 __global__ void k_chain_affine(int32_t per_fe, const int32_t *__restrict__ sj, const int32_t *__restrict__ sm,
                                int32_t *__restrict__ flags, int32_t *__restrict__ desc)
 {
     const size_t base = (size_t)blockIdx.x * per_fe;
     const int32_t fl = flags[blockIdx.x];
-    const int32_t s0 = sj[base], sb = sj[base + 1] - s0;
-    const int32_t m0 = sm[base], mb = sm[base + 1] - m0;
-    const bool empty = !(fl & (TF_ANY | TF_ONE)), mass = (fl & TF_MASS) != 0;
+    __shared__ int32_t r[5]; // jlo, jhi, mlo, mhi, one
+    if (threadIdx.x == 0) { r[0] = per_fe; r[1] = -1; r[2] = per_fe; r[3] = -1; r[4] = per_fe; }
+    __syncthreads();
+    for (int rr = threadIdx.x; rr < per_fe; rr += blockDim.x)
+    {
+        const int32_t s = sj[base + rr], m = sm[base + rr];
+        if (s >= 0) { atomicMin(&r[0], rr); atomicMax(&r[1], rr); }
+        if (m >= 0) { atomicMin(&r[2], rr); atomicMax(&r[3], rr); }
+        if (s == -2) atomicMin(&r[4], rr);
+    }
+    __syncthreads();
+    const int32_t jlo = r[0], jhi = r[1], mlo = r[2], mhi = r[3], one = r[4];
+    const int32_t sb = jhi > jlo ? sj[base + jlo + 1] - sj[base + jlo] : 0;
+    const int32_t s0 = jhi >= jlo ? sj[base + jlo] - sb * jlo : 0;
+    const int32_t mb = mhi > mlo ? sm[base + mlo + 1] - sm[base + mlo] : 0;
+    const int32_t m0 = mhi >= mlo ? sm[base + mlo] - mb * mlo : 0;
     int ok = 1;
     for (int rr = threadIdx.x; rr < per_fe; rr += blockDim.x)
     {
         const int32_t s = sj[base + rr], m = sm[base + rr];
-        if (empty) ok &= (s == -1);
-        else ok &= (s >= 0 && s == s0 + sb * rr);
-        if (mass) ok &= (m >= 0 && m == m0 + mb * rr);
+        if (rr >= jlo && rr <= jhi) ok &= (s == s0 + sb * rr);
+        else ok &= (s == (rr >= one ? -2 : -1));
+        if (rr >= mlo && rr <= mhi) ok &= (m == m0 + mb * rr);
         else ok &= (m < 0);
     }
     ok = __syncthreads_and(ok);
     if (threadIdx.x == 0)
     {
-        desc[(size_t)blockIdx.x * 4 + 0] = empty ? -1 : s0;
-        desc[(size_t)blockIdx.x * 4 + 1] = empty ? 0 : sb;
-        desc[(size_t)blockIdx.x * 4 + 2] = mass ? m0 : -1;
-        desc[(size_t)blockIdx.x * 4 + 3] = mass ? mb : 0;
+        int32_t *d = desc + (size_t)blockIdx.x * DESC;
+        d[DJ0] = s0; d[DJS] = sb; d[DM0] = m0; d[DMS] = mb;
+        d[DJLO] = jlo; d[DJHI] = jhi; d[DMLO] = mlo; d[DMHI] = mhi; d[DONE] = one; d[9] = 0;
         flags[blockIdx.x] = ok ? (fl | TF_AFF) : (fl & ~TF_AFF);
     }
 }
@@ -400,7 +484,9 @@ template <int B> int set_attributes(daecpp_b200_ctx *c)
 {
     DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_factor<B, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)factor_smem<B>()));
     DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_factor<B, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)factor_smem<B>()));
-    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_forward<B, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)solve_smem<B>()));
+    // the level-0 forward launch may carry the deferred top-level factorisation in one extra CTA
+    const size_t fwd = factor_smem<B>() > solve_smem<B>() ? factor_smem<B>() : solve_smem<B>();
+    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_forward<B, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fwd));
     DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_forward<B, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)solve_smem<B>()));
     DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_backward<B, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)solve_smem<B>()));
     DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_chain_backward<B, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)solve_smem<B>()));
@@ -447,13 +533,24 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g, bool fuse)
     a.counter = reinterpret_cast<uint32_t *>(c->dC.counter.p);
     a.dflags = c->d_flags;
     a.tol = c->pivot_tol;
+    a.packed = c->chain_packed;
+    if (c->trace_units && c->CH.levels.size() == 2)
+    {   // debug stamps, two-level hierarchies only (kernel ids would collide otherwise)
+        const size_t m = (size_t)TRACE_KERNELS * c->CH.levels[0].ntiles * TRACE_SLOTS;
+        if (c->trace.cap < m)
+        {
+            if (c->trace.reserve(m) == cudaSuccess) cudaMemsetAsync(c->trace.p, 0, sizeof(long long) * m, c->stream);
+        }
+        a.trace = c->trace.p;
+        a.trace_tiles = c->CH.levels[0].ntiles;
+    }
     return a;
 }
 
 template <class K> void launch_pdl(daecpp_b200_ctx *c, K kernel, const ChainArgs &a, int threads, size_t smem)
 {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(a.lv.ntiles, 1, 1);
+    cfg.gridDim = dim3(a.lv.ntiles + a.extra_factor, 1, 1);
     cfg.blockDim = dim3(threads, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = c->stream;
@@ -471,8 +568,9 @@ template <int B> void launch_factor(daecpp_b200_ctx *c, const ChainArgs &a, bool
 }
 template <int B> void launch_forward(daecpp_b200_ctx *c, const ChainArgs &a, bool first)
 {
-    if (first) launch_pdl(c, k_chain_forward<B, true>, a, Cfg<B>::T, solve_smem<B>());
-    else launch_pdl(c, k_chain_forward<B, false>, a, Cfg<B>::T, solve_smem<B>());
+    const size_t smem = a.extra_factor ? (factor_smem<B>() > solve_smem<B>() ? factor_smem<B>() : solve_smem<B>()) : solve_smem<B>();
+    if (first) launch_pdl(c, k_chain_forward<B, true>, a, Cfg<B>::T, smem);
+    else launch_pdl(c, k_chain_forward<B, false>, a, Cfg<B>::T, smem);
 }
 template <int B> void launch_backward(daecpp_b200_ctx *c, const ChainArgs &a, bool first)
 {
@@ -524,7 +622,7 @@ int chain_try_setup(daecpp_b200_ctx *c, int32_t n, const int32_t *outer, const i
     const int32_t per_fe = rows_per_tile(P.B) + 1;
     k_chain_compose<<<(int)((ne + 255) / 256), 256, 0, c->stream>>>(ne, per_fe, c->dC.ent_u.p, uJ, c->u_M.p, srcJ, c->dC.sj.p,
                                                                   c->dC.sm.p, c->dC.flags.p);
-    DAECPP_CUDA_TRY(c, c->dC.desc.reserve(P.tile_flags.size() * 4 + 4));
+    DAECPP_CUDA_TRY(c, c->dC.desc.reserve(P.tile_flags.size() * DESC + 4));
     if (c->chain_affine)
         k_chain_affine<<<(int)P.tile_flags.size(), 256, 0, c->stream>>>(per_fe, c->dC.sj.p, c->dC.sm.p, c->dC.flags.p, c->dC.desc.p);
     DAECPP_CUDA_TRY(c, cudaGetLastError());
@@ -543,7 +641,11 @@ int chain_refactor_async(daecpp_b200_ctx *c, double alpha)
     const Plan &P = c->CH;
     const double *jv = c->direct_csc ? c->u_vals.p : (c->jvals_from_triplets ? c->J.A.p : c->J.vals.p);
     const bool fuse = fuse_two_levels(c, 1);
-    const int nlaunch = fuse ? 1 : (int)P.levels.size();
+    if (c->sm_count == 0) cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, c->device);
+    // at most 4 CTAs per SM with the factor kernel's shared memory: the forward launch must stay one wave
+    const bool defer = !fuse && c->chain_may_defer && c->chain_defer_top && fuse_two_levels(c, 2) && P.levels[0].ntiles + 1 <= 4 * c->sm_count;
+    c->chain_top_pending = defer;
+    const int nlaunch = (fuse || defer) ? 1 : (int)P.levels.size();
     for (int g = 0; g < nlaunch; ++g)
     {
         ChainArgs a = level_args(c, g, fuse);
@@ -574,10 +676,20 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         a.atol = atol; a.rtol = rtol; a.max_err_abs = max_err_abs;
         a.update = fuse_update ? 1 : 0;
     };
+    if (c->chain_top_pending && !fuse)
+    {   // (options changed in between) factor the top level on its own
+        ChainArgs a = level_args(c, 1, false);
+#define LF(B) launch_factor<B>(c, a, false)
+        CHAIN_DISPATCH(P.B, LF)
+#undef LF
+        c->kernels += 1;
+        c->chain_top_pending = false;
+    }
     for (int g = 0; g < (fuse ? 1 : nlev); ++g)
     {
         ChainArgs a = level_args(c, g, fuse);
         if (g == 0) first_args(a);
+        if (g == 0 && c->chain_top_pending) { a.extra_factor = 1; c->chain_top_pending = false; }
 #define LW(B) launch_forward<B>(c, a, g == 0)
         CHAIN_DISPATCH(P.B, LW)
 #undef LW

@@ -520,20 +520,22 @@ CH_HD void stage_matrix_first(int t, int nt, int tile, double *S, const int32_t 
 }
 // level 0, affine tiles: when the value source of every field of the tile is an arithmetic
 // progression in the row (the normal case: a functor that emits its triplets row by row, e.g.
-// JacobianMatrixShape) the slot map is not read at all.  desc[(tile*3*BB + fe)*4] = {first J index
-// (or -1: structurally empty field), J stride, first M slot (or -1: no mass entry), M stride}.
-// All loads of a batch are independent; the fields of one row are fetched back to back by the same
-// warp so that the strided accesses share their cache lines.
+// JacobianMatrixShape) the slot map is not read at all.  Per (tile, field element) a descriptor of
+// DESC ints: {J index extrapolated to row 0 of the tile, J stride, M slot extrapolated, M stride,
+// first / last row with a J entry, first / last row with an M entry, first row of the identity
+// padding behind the end of the matrix}.  Rows outside the ranges are structural zeros (the matrix
+// edge: no sub-diagonal in the first row, no super-diagonal in the last), so the boundary tiles are
+// affine too.  All loads of a batch are independent.
+constexpr int DESC = 10;
+enum { DJ0 = 0, DJS = 1, DM0 = 2, DMS = 3, DJLO = 4, DJHI = 5, DMLO = 6, DMHI = 7, DONE = 8 };
+
 template <int B>
 CH_HD void stage_matrix_affine(int t, int nt, int tile, double *S, const int32_t *desc, const double *jv, const double *mvals,
                                double alpha)
 {
     using D = Dim<B>;
     constexpr int PER = D::ROWS + 1, NFE = 3 * D::BB, U = (B == 1) ? 4 : (B == 2 ? 2 : 1);
-    int32_t ja[NFE], jb[NFE], ma[NFE], mb[NFE];
-    const int32_t *d = desc + (size_t)tile * NFE * 4;
-#pragma unroll
-    for (int fe = 0; fe < NFE; ++fe) { ja[fe] = d[fe * 4]; jb[fe] = d[fe * 4 + 1]; ma[fe] = d[fe * 4 + 2]; mb[fe] = d[fe * 4 + 3]; }
+    const int32_t *d = desc + (size_t)tile * NFE * DESC;
     for (int r0 = t; r0 < PER; r0 += nt * U)
     {
         double j[U][NFE], m[U][NFE];
@@ -541,12 +543,12 @@ CH_HD void stage_matrix_affine(int t, int nt, int tile, double *S, const int32_t
         for (int u = 0; u < U; ++u)
         {
             const int rr = r0 + u * nt;
-            const bool ok = rr < PER;
 #pragma unroll
             for (int fe = 0; fe < NFE; ++fe)
             {
-                j[u][fe] = (ok && ja[fe] >= 0) ? jv[ja[fe] + jb[fe] * rr] : 0.0;
-                m[u][fe] = (ok && ma[fe] >= 0) ? mvals[ma[fe] + mb[fe] * rr] : 0.0;
+                const int32_t *e = d + fe * DESC;
+                j[u][fe] = (rr >= e[DJLO] && rr <= e[DJHI]) ? jv[e[DJ0] + e[DJS] * rr] : ((rr >= e[DONE] && rr < PER) ? 1.0 : 0.0);
+                m[u][fe] = (rr >= e[DMLO] && rr <= e[DMHI]) ? mvals[e[DM0] + e[DMS] * rr] : 0.0;
             }
         }
 #pragma unroll
@@ -557,7 +559,10 @@ CH_HD void stage_matrix_affine(int t, int nt, int tile, double *S, const int32_t
             const int p = sidx<B>(rr - 1);
 #pragma unroll
             for (int fe = 0; fe < NFE; ++fe)
-                S[(size_t)fe * D::RP + p] = sub_rn(j[u][fe], ma[fe] >= 0 ? mul_rn(m[u][fe], alpha) : 0.0);
+            {
+                const int32_t *e = d + fe * DESC;
+                S[(size_t)fe * D::RP + p] = sub_rn(j[u][fe], (rr >= e[DMLO] && rr <= e[DMHI]) ? mul_rn(m[u][fe], alpha) : 0.0);
+            }
         }
     }
 }

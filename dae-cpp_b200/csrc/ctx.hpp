@@ -140,6 +140,12 @@ struct daecpp_b200_ctx
     daecpp_b200::chain::Plan CH;
     daecpp_b200::DeviceChain dC;
     bool chain_enabled = true, chain_affine = true;
+    int chain_packed = 1;              // contiguous-run staging of affine tiles (chain.cu), 0 = per-field strided copies
+    bool chain_defer_top = true;       // two-level chains inside a fused iteration: the top level is factored by one
+                                       // extra CTA of the forward launch, concurrently with the tiles' forward sweeps
+    int sm_count = 0;
+    bool chain_may_defer = false;      // set by the fused iteration around its refactor + solve pair
+    bool chain_top_pending = false;    // level-0 factors are current, the top level's are not yet
     int chain_fuse_top = 2; // bit 0: factor, bit 1: solve (top level swept by the last CTA of the level-0 launch)
     int chain_min_n = 256, chain_max_b = 3;
     uint32_t ticket_base = 0; // value of the ticket word before the next unit launch
