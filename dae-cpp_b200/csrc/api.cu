@@ -133,7 +133,7 @@ static void recycle(daecpp_b200_ctx *c)
         c->sopt.max_super != fresh.sopt.max_super)
         c->have_symbolic = false;
     c->chain_enabled = fresh.chain_enabled; c->chain_min_n = fresh.chain_min_n; c->chain_max_b = fresh.chain_max_b;
-    c->chain_affine = fresh.chain_affine; c->chain_packed = fresh.chain_packed; c->chain_fuse_top = fresh.chain_fuse_top; c->chain_defer_top = fresh.chain_defer_top; c->chain_may_defer = false; c->chain_top_pending = false; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
+    c->chain_affine = fresh.chain_affine; c->chain_packed = fresh.chain_packed; c->lean_flags = fresh.lean_flags; c->publish_flags = false; c->chain_prefetch = fresh.chain_prefetch; c->chain_fuse_top = fresh.chain_fuse_top; c->chain_defer_top = fresh.chain_defer_top; c->chain_may_defer = false; c->chain_top_pending = false; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
     c->refine_steps = 0; c->assemble_only = false; c->pinned_io = false; c->pivot_tol = 0.0;
     c->phase_timing = false; c->trace_units = false; c->blocked_lu = fresh.blocked_lu; c->blocked_lu_min_dim = fresh.blocked_lu_min_dim;
     c->n_symbolic = c->n_refactor = c->n_solve = c->n_cold = c->kernels = 0;
@@ -197,7 +197,8 @@ int daecpp_b200_create(int32_t n, int device, daecpp_b200_ctx **out)
     if ((e = cudaMemsetAsync(slab, 0, sizeof(double) * nv * (size_t)n, c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
     if ((e = cudaMalloc((void **)&c->d_flags, sizeof(int32_t) * 8)) != cudaSuccess) return bail(e, "cudaMalloc(flags)");
     if ((e = cudaMalloc((void **)&c->d_scalars, sizeof(double) * 8)) != cudaSuccess) return bail(e, "cudaMalloc(scalars)");
-    if ((e = cudaMallocHost((void **)&c->h_flags, sizeof(int32_t) * 8)) != cudaSuccess) return bail(e, "cudaMallocHost");
+    if ((e = cudaHostAlloc((void **)&c->h_flags, sizeof(int32_t) * 8, cudaHostAllocMapped)) != cudaSuccess) return bail(e, "cudaHostAlloc");
+    if ((e = cudaHostGetDevicePointer((void **)&c->h_flags_dev, c->h_flags, 0)) != cudaSuccess) return bail(e, "cudaHostGetDevicePointer");
     if ((e = cudaMallocHost((void **)&c->h_scalars, sizeof(double) * 8)) != cudaSuccess) return bail(e, "cudaMallocHost");
     if ((e = cudaMemsetAsync(c->d_flags, 0, sizeof(int32_t) * 8, c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
     if ((e = cudaMemsetAsync(c->d_scalars, 0, sizeof(double) * 8, c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
@@ -444,14 +445,17 @@ static int enqueue_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t or
     const bool pt = c->phase_timing;
     // all flag words of the iteration are cleared up front so that its kernels follow each other
     // on the stream with no other node in between (programmatic dependent launch, chain.cu)
-    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, 3 * sizeof(int32_t), st));
+    // chain path: the residual kernel clears them and the last CTA of the last kernel writes them to the
+    // mapped host mirror -- no memset and no copy node around the kernels
+    const bool lean = c->lean_flags && c->CH.active && c->have_symbolic;
+    if (!lean) DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, 3 * sizeof(int32_t), st));
     // the triplet values are resident: the Jacobian's compressed-column values (if anything
     // still needs them) are stale from here on
     if (do_refactor) c->J.vals_valid = false;
     if (pt) cudaEventRecord(c->pev[0], st);
     if (do_refactor && !c->jvals_from_triplets && (rc = ensure_csc_values(c, c->J))) return rc; // duplicate-summing path
     if (pt) cudaEventRecord(c->pev[1], st);
-    if ((rc = launch_residual(c, order, w))) return rc;
+    if ((rc = launch_residual(c, order, w, lean))) return rc;
     if (pt) cudaEventRecord(c->pev[2], st);
     // the solve follows on the same stream and the flags are read once at the end: a two-level chain
     // may leave its (tiny) top-level factorisation to an extra CTA of the forward launch
@@ -460,10 +464,14 @@ static int enqueue_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t or
     c->chain_may_defer = false;
     if (do_refactor && rc) return rc;
     if (pt) cudaEventRecord(c->pev[3], st);
-    if ((rc = numeric_solve(c, true, atol, rtol, max_err_abs))) return rc;
+    c->publish_flags = lean; // (a pattern change inside the refactorisation may have left the chain path: then nothing is published)
+    c->flags_published = false;
+    rc = numeric_solve(c, true, atol, rtol, max_err_abs);
+    c->publish_flags = false;
+    if (rc) return rc;
     if (pt) cudaEventRecord(c->pev[4], st);
     if (pt) cudaEventRecord(c->pev[5], st);
-    DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    if (!c->flags_published) DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     return DAECPP_B200_OK;
 }
 
@@ -757,6 +765,8 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "unit_threads") { c->unit_threads = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "pinned_io") c->pinned_io = value != 0.0;
     else if (k == "chain") { c->chain_enabled = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "lean_flags") c->lean_flags = value != 0.0;
+    else if (k == "chain_prefetch") c->chain_prefetch = value != 0.0 ? 1 : 0;
     else if (k == "chain_packed") c->chain_packed = value != 0.0 ? 1 : 0;
     else if (k == "chain_affine") { c->chain_affine = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "blocked_lu") c->blocked_lu = value != 0.0;

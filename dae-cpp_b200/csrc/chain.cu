@@ -40,7 +40,7 @@ struct ChainArgs
 {
     LevelView lv;  // the level this launch sweeps, one CTA per tile
     LevelView top; // fuse_top: the single-tile top level, swept by the CTA that finishes last
-    int32_t fuse_top, n, trace_tiles, packed;
+    int32_t fuse_top, n, trace_tiles, packed, prefetch;
     int32_t extra_factor; // forward launch: CTA number lv.ntiles factors the top level (deferred from the factor launch)
     uint32_t *counter; // [2 * members] tiles finished (factor, forward)
     // factor
@@ -55,6 +55,7 @@ struct ChainArgs
     double atol, rtol, max_err_abs;
     int32_t update;
     int32_t *dflags;
+    int32_t *host_flags; // mapped host mirror of dflags[2..4], written by the CTA that finishes the iteration last
     // ensemble: member = blockIdx.y, strides in elements
     const double *alpha_arr;
     int64_t s_jv, s_mv, s_F, s_Y, s_red, s_rv, s_x, s_vec;
@@ -266,8 +267,10 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
     __syncthreads();
     backward_phase1<B>(t, nvalid, sh);
     __syncthreads();
+    stamp(a, FIRST ? 4 : 3, tile, 6);
     backward_phase0<B>(t, nvalid, sh, Ft, Yt);
     __syncthreads();
+    stamp(a, FIRST ? 4 : 3, tile, 7);
     constexpr int U = 8;
     const int total = B * nvalid;
     if (FIRST)
@@ -313,6 +316,10 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
             }
         }
         if (flag) atomicOr(&a.dflags[2], flag);
+        if (a.host_flags && last_tile_done(a.counter + 4, lv.ntiles, t))
+        {
+            if (t < 3) a.host_flags[t] = atomicOr(&a.dflags[2 + t], 0); // visible to the host once the grid has completed
+        }
     }
     else
     {
@@ -392,6 +399,17 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
     double *Yt = lv.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
     const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
     stamp(a, 4, tile, 0);
+    // The factors are two launches old (the forward kernel waited for the factor kernel before it let
+    // this one start), so they may be touched before the dependency wait: while the top level is being
+    // solved by the last CTA of the forward launch, pull this tile's factors into L2 and the small
+    // levels into shared memory.
+    if (a.prefetch)
+    {
+        const char *f0 = reinterpret_cast<const char *>(Ft);
+        for (int off = t * 128; off < (int)(D::TILE_F * sizeof(double)); off += D::T * 128)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(f0 + off));
+    }
+    load_small_factors<B>(t, D::T, sh, Ft);
     pdl_wait();
     stamp(a, 4, tile, 1);
     if (t < B)
@@ -400,7 +418,6 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
         sh.xR[t] = xup[(size_t)tile * B + t];
         sh.xL[t] = tile > 0 ? xup[(size_t)(tile - 1) * B + t] : 0.0;
     }
-    load_small_factors<B>(t, D::T, sh, Ft);
     copy_small(t, D::T, sh.Y12, Yt + D::Y0, D::Y1 + D::Y2);
     __syncthreads();
     stamp(a, 4, tile, 2);
@@ -534,6 +551,7 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g, bool fuse)
     a.dflags = c->d_flags;
     a.tol = c->pivot_tol;
     a.packed = c->chain_packed;
+    a.prefetch = c->chain_prefetch;
     if (c->trace_units && c->CH.levels.size() == 2)
     {   // debug stamps, two-level hierarchies only (kernel ids would collide otherwise)
         const size_t m = (size_t)TRACE_KERNELS * c->CH.levels[0].ntiles * TRACE_SLOTS;
@@ -675,6 +693,8 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         a.out = c->dx; a.xk = c->xk; a.x0 = c->xh[0];
         a.atol = atol; a.rtol = rtol; a.max_err_abs = max_err_abs;
         a.update = fuse_update ? 1 : 0;
+        a.host_flags = c->publish_flags ? c->h_flags_dev + 2 : nullptr;
+        if (a.host_flags) c->flags_published = true;
     };
     if (c->chain_top_pending && !fuse)
     {   // (options changed in between) factor the top level on its own

@@ -111,7 +111,9 @@ struct daecpp_b200_ctx
     double *xk = nullptr, *xh[4] = {nullptr, nullptr, nullptr, nullptr};
     double *f = nullptr, *b = nullptr, *dx = nullptr, *work = nullptr, *dxdt = nullptr;
     int32_t *d_flags = nullptr; // [8] device flag words
-    int32_t *h_flags = nullptr; // pinned mirror
+    int32_t *h_flags = nullptr; // pinned mirror (mapped: the last kernel of a fused chain iteration writes it directly)
+    int32_t *h_flags_dev = nullptr;
+    bool lean_flags = true, publish_flags = false, flags_published = false;
     double *d_scalars = nullptr, *h_scalars = nullptr; // [8]
     double *h_stage = nullptr;  // pinned staging for n doubles
     size_t h_stage_cap = 0;
@@ -140,6 +142,7 @@ struct daecpp_b200_ctx
     daecpp_b200::chain::Plan CH;
     daecpp_b200::DeviceChain dC;
     bool chain_enabled = true, chain_affine = true;
+    int chain_prefetch = 1;            // backward kernel: L2 prefetch of the tile's factors before the dependency wait
     int chain_packed = 1;              // contiguous-run staging of affine tiles (chain.cu), 0 = per-field strided copies
     bool chain_defer_top = true;       // two-level chains inside a fused iteration: the top level is factored by one
                                        // extra CTA of the forward launch, concurrently with the tiles' forward sweeps
@@ -224,7 +227,7 @@ int chain_try_setup(daecpp_b200_ctx *c, int32_t n, const int32_t *outer, const i
 int chain_refactor_async(daecpp_b200_ctx *c, double alpha);
 int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, double max_err_abs);
 // vector_ops.cu
-int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
+int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5], bool clear_flags = false);
 int classify_mass(daecpp_b200_ctx *c);
 int launch_dxdt(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
 int launch_update(daecpp_b200_ctx *c, double atol, double rtol, double max_err_abs);

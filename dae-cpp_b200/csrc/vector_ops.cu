@@ -42,8 +42,9 @@ __global__ void k_dxdt(Bdf s, int32_t n, double *__restrict__ out)
 // One thread per row; the row's mass entries are visited in increasing column order.
 __global__ void k_residual(Bdf s, int32_t n, const int32_t *__restrict__ rowptr, const int32_t *__restrict__ rowslot,
                            const int32_t *__restrict__ rowcol, const double *__restrict__ mvals,
-                           const double *__restrict__ f, double *__restrict__ b)
+                           const double *__restrict__ f, double *__restrict__ b, int32_t *__restrict__ clear)
 {
+    if (clear && blockIdx.x == 0 && threadIdx.x < 3) clear[threadIdx.x] = 0;
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n) return;
@@ -68,8 +69,11 @@ __device__ __forceinline__ double bdf_one(const Bdf &s, double xk, double x0, do
     return r;
 }
 __global__ void k_residual_diag(Bdf s, int32_t n, const double *__restrict__ mvals, const double *__restrict__ f,
-                                double *__restrict__ b)
+                                double *__restrict__ b, int32_t *__restrict__ clear)
 {
+    // first kernel of a fused iteration: the iteration's flag words are cleared here (every later
+    // kernel waits for this grid before it can raise one), which saves a memset node on the stream
+    if (clear && blockIdx.x == 0 && threadIdx.x < 3) clear[threadIdx.x] = 0;
     // the factor kernel that follows on the stream is launched programmatically dependent (chain.cu):
     // let it start launching now; it waits for this grid's memory before touching global data
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -178,18 +182,18 @@ int classify_mass(daecpp_b200_ctx *c)
     return DAECPP_B200_OK;
 }
 
-int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5])
+int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5], bool clear_flags)
 {
     if (c->m_diag)
     {
         const int pairs = (c->n + 1) / 2;
-        k_residual_diag<<<(pairs + TPB - 1) / TPB, TPB, 0, c->stream>>>(make_bdf(c, order, coef), c->n, c->M.vals.p, c->f, c->b);
+        k_residual_diag<<<(pairs + TPB - 1) / TPB, TPB, 0, c->stream>>>(make_bdf(c, order, coef), c->n, c->M.vals.p, c->f, c->b, clear_flags ? c->d_flags + 2 : nullptr);
         c->kernels += 1;
         DAECPP_CUDA_TRY(c, cudaGetLastError());
         return DAECPP_B200_OK;
     }
     k_residual<<<(c->n + TPB - 1) / TPB, TPB, 0, c->stream>>>(make_bdf(c, order, coef), c->n, c->m_rowptr.p, c->m_rowslot.p,
-                                                             c->m_rowcol.p, c->M.vals.p, c->f, c->b);
+                                                             c->m_rowcol.p, c->M.vals.p, c->f, c->b, clear_flags ? c->d_flags + 2 : nullptr);
     c->kernels += 1;
     DAECPP_CUDA_TRY(c, cudaGetLastError());
     return DAECPP_B200_OK;

@@ -45,3 +45,9 @@ for k, nm in ((2, "forward"), (4, "backward")):
     a = tr[k]; rel = (a - t0) / 1e3; last = 4 if k == 2 else 3
     o = np.argsort(rel[:, last])
     print(nm, "latest 6 (tile, done):", [(int(i), round(float(rel[i, last]), 1)) for i in o[-6:]], "percentiles 50/90/99/100", np.percentile(rel[:, last], [50, 90, 99, 100]).round(1))
+
+for k, nm in ((3, "top solve"), (4, "backward tiles")):
+    a = tr[k]; live = a[:, 0] > 0; a = a[live]
+    end = 4 if k == 3 else 3; st = 3 if k == 3 else 2
+    print(nm, "backward part (median us): levels 2+1 %.2f, level 0 sweep %.2f, write-out %.2f" % (
+        np.median(a[:, 6] - a[:, st]) / 1e3, np.median(a[:, 7] - a[:, 6]) / 1e3, np.median(a[:, end] - a[:, 7]) / 1e3))
