@@ -40,8 +40,10 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="flame1d", choices=["flame1d", "perovskite", "grid2d", "ensemble"])
+    ap.add_argument("--workload", default="flame1d", choices=["flame1d", "perovskite", "grid2d", "ensemble", "trajectory"])
     ap.add_argument("--n", "--size", dest="n", type=int, default=0, help="flame1d: unknowns; perovskite: N (system 2N); grid2d: side")
+    ap.add_argument("--problem", default="perovskite", choices=["flame", "perovskite", "flame1d", "grid2d"],
+                    help="trajectory: which daecpp::solve run (C1 flame, C2 perovskite as shipped; flame1d / grid2d take --size)")
     ap.add_argument("--members", type=int, default=4096, help="ensemble: members of the whole sweep (C5)")
     ap.add_argument("--threads", type=int, default=0, help="ensemble: members in flight per GPU (0: host cores / GPUs)")
     ap.add_argument("--host-logic-check", action="store_true",
@@ -214,6 +216,64 @@ def run_reference_arm(args):
         "e2e": {"value": us, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------ whole trajectories (C1, C2): BDF steps/s
+TRAJ_METRIC = "BDF steps/s"
+
+
+def run_trajectory(args, reference):
+    """One whole daecpp::solve (host functors, autodiff, observer, step control) through the overlay
+    header + libdaecpp_b200.so, or -- reference arm -- through the unmodified reference headers; accepted
+    BDF steps per second of wall time, host functor time reported apart."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    exe = _driver("traj_dump_ref" if reference else "traj_dump")
+    kv = [f"n={args.n}"] if args.n else []
+    kv.append("repeat=2")  # the second solve of the process is reported: CUDA context creation and module load are one-off
+    clocks = None
+    sampler = None
+    if not reference:
+        import torch
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+        sampler = ClockSampler(0)
+
+    def once():
+        p = subprocess.run([exe, args.problem] + kv, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        if p.returncode != 0:
+            raise SystemExit(f"bench.py: {exe} {args.problem} failed ({p.returncode}): {p.stderr[-2000:]}")
+        return json.loads(p.stdout.strip().splitlines()[-1])
+
+    warm = 0 if reference else max(1, min(args.warmup, 3))
+    for _ in range(warm):
+        once()
+    if sampler:
+        sampler.start()
+    runs = [once() for _ in range(1 if reference else max(1, min(args.steps, 5)))]
+    if sampler:
+        clocks = sampler.stop()
+    r = sorted(runs, key=lambda q: q["wall_ms"])[len(runs) // 2]
+    v = r["steps"] / (r["wall_ms"] * 1e-3)
+    line = {"metric": TRAJ_METRIC, "value": v, "unit": "steps/s", "n_gpus": 1, "steps": len(runs), "warmup": warm,
+            "ms_per_step": r["wall_ms"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": f"whole daecpp::solve of {args.problem} (n={r['n']}), one process, functors on the host",
+                       "timing": "wall clock of the second daecpp::solve of a process (the first, with the one-off process start-up, is "
+                                 "reported apart), median run; a step is one accepted BDF time step"},
+            "trajectory": {"accepted_steps": r["steps"], "exit_code": r["status"], "rhs_calls": r["rhs_calls"],
+                           "jac_calls": r["jac_calls"], "wall_ms": r["wall_ms"], "first_solve_of_process_ms": r["first_wall_ms"],
+                           "host_functor_ms": r["ms_rhs_functor"] + r["ms_jac_functor"], "t_final": r["t_final"]},
+            "e2e": {"value": v, "unit": "steps/s", "h2d_bytes_per_step": None, "d2h_bytes_per_step": None,
+                    "note": "the run is the public API end to end (host buffers, functors, observer)"},
+            "roofline": None}
+    if reference:
+        line.update({"impl": "reference", "gpu_launches": 0,
+                     "cpu_baseline": {"value": v, "unit": "steps/s", "cores": 1, "kind": "reference",
+                                      "sample": "one whole run of the unmodified reference (Eigen::SparseLU), 1 host core"}})
+    else:
+        line.update({"clocks": clocks, "gpu_launches": None})
     print(json.dumps(line), flush=True)
 
 
@@ -466,21 +526,22 @@ def run_b200_arm(args):
     # DRAM traffic of the refactorisation kernels from the committed `ncu --set full` capture of this
     # very command (profiles/: dram__bytes_read.sum + dram__bytes_write.sum, MB per launch), C3 only
     traffic = None
-    cap = os.path.join(ROOT, "profiles", "r01_v6_ncu_full_chain_kernels.csv")
+    cap = os.path.join(ROOT, "profiles", "r01_v9_ncu_full_chain_kernels.csv")
     if args.workload == "flame1d" and n == 1_000_000 and os.path.exists(cap):
         import csv
         rows = list(csv.reader(open(cap)))
         hd = rows[0]
         kn, rd, wr = hd.index("Kernel Name"), hd.index("dram__bytes_read.sum"), hd.index("dram__bytes_write.sum")
-        mb = [float(r[rd]) + float(r[wr]) for r in rows[2:] if "k_chain_factor" in r[kn]]
+        mb = [float(r[rd]) + float(r[wr]) for r in rows[2:] if "k_chain_factor<1, 1>" in r[kn]]
         if mb:
-            traffic = {"bytes_per_launch": sum(mb) * 1e6, "source": os.path.relpath(cap, ROOT),
-                       "note": "tile-level factor kernel; the 40 MB of factor stores stay in the 126 MB L2 (write-back) "
-                               "and are re-read from there by the forward sweep, so DRAM traffic is below the algorithmic bytes"}
+            traffic = {"bytes_per_launch": sum(mb) / len(mb) * 1e6, "launches_averaged": len(mb), "source": os.path.relpath(cap, ROOT),
+                       "note": "tile-level factor kernel (the 489-row top level is factored by one extra CTA of the forward launch); "
+                               "the 40 MB of factor stores stay in the 126 MB write-back L2 and are re-read from there by the forward "
+                               "sweep, so DRAM traffic is below the algorithmic bytes"}
     roofline = None
     if "GBps" in phases["refactor"]:
         a = phases["refactor"]["GBps"]
-        roofline = {"bound": "hbm", "kernel": ("numeric refactorisation phase: k_chain_factor<B,1> (tiles) + k_chain_factor<B,0> (grid level)"
+        roofline = {"bound": "hbm", "kernel": ("numeric refactorisation phase: k_chain_factor<B,1> (tiles; the grid-level system is factored inside the forward launch)"
                                if c.stat("chain_block") > 0 else
                                "numeric refactorisation phase (k_scatter_big + k_unit_factor + k_factor_level launches)"),
                     "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak, "traffic": traffic,
@@ -550,7 +611,9 @@ def run_b200_arm(args):
 
 if __name__ == "__main__":
     a = parse_args()
-    if a.workload == "ensemble":
+    if a.workload == "trajectory":
+        run_trajectory(a, a.impl == "reference")
+    elif a.workload == "ensemble":
         run_ensemble_reference(a) if a.impl == "reference" else run_ensemble_b200(a)
     elif a.impl == "reference":
         run_reference_arm(a)

@@ -766,7 +766,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "pinned_io") c->pinned_io = value != 0.0;
     else if (k == "chain") { c->chain_enabled = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "lean_flags") c->lean_flags = value != 0.0;
-    else if (k == "chain_prefetch") c->chain_prefetch = value != 0.0 ? 1 : 0;
+    else if (k == "chain_prefetch") c->chain_prefetch = (int)value;
     else if (k == "chain_packed") c->chain_packed = value != 0.0 ? 1 : 0;
     else if (k == "chain_affine") { c->chain_affine = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "blocked_lu") c->blocked_lu = value != 0.0;

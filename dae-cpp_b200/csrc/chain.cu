@@ -408,6 +408,18 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
         const char *f0 = reinterpret_cast<const char *>(Ft);
         for (int off = t * 128; off < (int)(D::TILE_F * sizeof(double)); off += D::T * 128)
             asm volatile("prefetch.global.L2 [%0];" ::"l"(f0 + off));
+        if (FIRST && a.update && !a.perm && a.prefetch > 1)
+        {   // operands of the fused update (solver.hpp:590-619): x[0] and xk of this tile's rows
+            const int64_t k0 = (int64_t)tile * D::ROWS * B;
+            const int bytes = (int)(min((int64_t)D::ROWS * B, (int64_t)a.n - k0) * sizeof(double));
+            const char *p0 = reinterpret_cast<const char *>(a.x0 + mb * a.s_vec + k0);
+            const char *p1 = reinterpret_cast<const char *>(a.xk + mb * a.s_vec + k0);
+            for (int off = t * 128; off < bytes; off += D::T * 128)
+            {
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(p0 + off));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(p1 + off));
+            }
+        }
     }
     load_small_factors<B>(t, D::T, sh, Ft);
     pdl_wait();

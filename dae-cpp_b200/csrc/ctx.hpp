@@ -142,7 +142,7 @@ struct daecpp_b200_ctx
     daecpp_b200::chain::Plan CH;
     daecpp_b200::DeviceChain dC;
     bool chain_enabled = true, chain_affine = true;
-    int chain_prefetch = 1;            // backward kernel: L2 prefetch of the tile's factors before the dependency wait
+    int chain_prefetch = 0;            // backward kernel: L2 prefetch of the tile's factors before the dependency wait
     int chain_packed = 1;              // contiguous-run staging of affine tiles (chain.cu), 0 = per-field strided copies
     bool chain_defer_top = true;       // two-level chains inside a fused iteration: the top level is factored by one
                                        // extra CTA of the forward launch, concurrently with the tiles' forward sweeps
