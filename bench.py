@@ -510,6 +510,12 @@ def run_b200_arm(args):
         if ph == "assembly" and c.stat("jvals_from_triplets") > 0:
             phases[ph]["note"] = "fused: Jb = J - M*alpha is formed from the triplet values inside the refactorisation kernels"
             continue
+        if ph == "residual" and c.stat("residual_fused") > 0:
+            phases[ph]["note"] = "fused: b = M*dxdt - f is formed while the forward kernel stages its right-hand side (diagonal mass)"
+            continue
+        if ph == "solve" and c.stat("residual_fused") > 0:
+            abytes = dict(abytes); abytes["solve"] = abytes["solve"] + abytes["residual"]
+            phases[ph]["note"] = "algorithmic bytes = triangular solves + residual (fused into this phase); also holds the top-level factorisation"
         if ph == "update":
             phases[ph]["note"] = "fused: error check and xk += dx are the write-out of the last backward kernel"
             continue

@@ -133,7 +133,7 @@ static void recycle(daecpp_b200_ctx *c)
         c->sopt.max_super != fresh.sopt.max_super)
         c->have_symbolic = false;
     c->chain_enabled = fresh.chain_enabled; c->chain_min_n = fresh.chain_min_n; c->chain_max_b = fresh.chain_max_b;
-    c->chain_affine = fresh.chain_affine; c->chain_packed = fresh.chain_packed; c->lean_flags = fresh.lean_flags; c->publish_flags = false; c->chain_prefetch = fresh.chain_prefetch; c->chain_fuse_top = fresh.chain_fuse_top; c->chain_defer_top = fresh.chain_defer_top; c->chain_may_defer = false; c->chain_top_pending = false; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
+    c->chain_affine = fresh.chain_affine; c->chain_packed = fresh.chain_packed; c->lean_flags = fresh.lean_flags; c->publish_flags = false; c->flags_clean = false; c->chain_fuse_residual = fresh.chain_fuse_residual; c->keep_b = fresh.keep_b; c->fuse_residual_now = false; c->chain_prefetch = fresh.chain_prefetch; c->chain_fuse_top = fresh.chain_fuse_top; c->chain_defer_top = fresh.chain_defer_top; c->chain_may_defer = false; c->chain_top_pending = false; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
     c->refine_steps = 0; c->assemble_only = false; c->pinned_io = false; c->pivot_tol = 0.0;
     c->phase_timing = false; c->trace_units = false; c->blocked_lu = fresh.blocked_lu; c->blocked_lu_min_dim = fresh.blocked_lu_min_dim;
     c->n_symbolic = c->n_refactor = c->n_solve = c->n_cold = c->kernels = 0;
@@ -403,6 +403,7 @@ int daecpp_b200_solve_update(daecpp_b200_ctx *c, double atol, double rtol, doubl
     cudaSetDevice(c->device);
     if (!c->have_factor) return fail(c, DAECPP_B200_EINVAL, "no valid factorisation");
     DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev0, c->stream));
+    c->flags_clean = false;
     DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, sizeof(int32_t), c->stream));
     DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 4, 0, sizeof(int32_t), c->stream));
     int rc = numeric_solve(c, true, atol, rtol, max_err_abs);
@@ -445,17 +446,22 @@ static int enqueue_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t or
     const bool pt = c->phase_timing;
     // all flag words of the iteration are cleared up front so that its kernels follow each other
     // on the stream with no other node in between (programmatic dependent launch, chain.cu)
-    // chain path: the residual kernel clears them and the last CTA of the last kernel writes them to the
-    // mapped host mirror -- no memset and no copy node around the kernels
+    // chain path: the CTA that finishes the iteration writes the flag words to the mapped host mirror and
+    // resets them -- no memset and no copy node around the kernels
     const bool lean = c->lean_flags && c->CH.active && c->have_symbolic;
-    if (!lean) DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, 3 * sizeof(int32_t), st));
+    if (!lean || !c->flags_clean) DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, 3 * sizeof(int32_t), st));
+    c->flags_clean = false;
     // the triplet values are resident: the Jacobian's compressed-column values (if anything
     // still needs them) are stale from here on
     if (do_refactor) c->J.vals_valid = false;
     if (pt) cudaEventRecord(c->pev[0], st);
     if (do_refactor && !c->jvals_from_triplets && (rc = ensure_csc_values(c, c->J))) return rc; // duplicate-summing path
     if (pt) cudaEventRecord(c->pev[1], st);
-    if ((rc = launch_residual(c, order, w, lean))) return rc;
+    // diagonal mass on the chain path: b = M*dxdt - f is formed by the forward kernel while it stages its
+    // right-hand side (same roundings), the residual kernel and the round trip of b through HBM go away
+    const bool fuse_res = lean && c->m_diag && c->chain_fuse_residual;
+    if (fuse_res) c->bdf_pending = make_bdf(c, order, w);
+    else if ((rc = launch_residual(c, order, w, false))) return rc;
     if (pt) cudaEventRecord(c->pev[2], st);
     // the solve follows on the same stream and the flags are read once at the end: a two-level chain
     // may leave its (tiny) top-level factorisation to an extra CTA of the forward launch
@@ -464,11 +470,14 @@ static int enqueue_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t or
     c->chain_may_defer = false;
     if (do_refactor && rc) return rc;
     if (pt) cudaEventRecord(c->pev[3], st);
+    c->fuse_residual_now = fuse_res;
     c->publish_flags = lean; // (a pattern change inside the refactorisation may have left the chain path: then nothing is published)
     c->flags_published = false;
     rc = numeric_solve(c, true, atol, rtol, max_err_abs);
     c->publish_flags = false;
+    c->fuse_residual_now = false;
     if (rc) return rc;
+    c->flags_clean = c->flags_published;
     if (pt) cudaEventRecord(c->pev[4], st);
     if (pt) cudaEventRecord(c->pev[5], st);
     if (!c->flags_published) DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
@@ -731,6 +740,7 @@ int daecpp_b200_get_stat(daecpp_b200_ctx *c, const char *key, double *value)
     else if (k == "ms_phase_solve") *value = c->n_phase_samples ? c->ms_phase[3] / c->n_phase_samples : 0;
     else if (k == "ms_phase_update") *value = c->n_phase_samples ? c->ms_phase[4] / c->n_phase_samples : 0;
     else if (k == "n_phase_samples") *value = c->n_phase_samples;
+    else if (k == "residual_fused") *value = (c->lean_flags && c->CH.active && c->m_diag && c->chain_fuse_residual) ? 1 : 0;
     else if (k == "jvals_from_triplets") *value = c->jvals_from_triplets ? 1 : 0;
     else if (k == "upd_doubles") *value = (double)c->S.upd_size;
     else if (k == "n_units") *value = c->S.nunit;
@@ -766,6 +776,8 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "pinned_io") c->pinned_io = value != 0.0;
     else if (k == "chain") { c->chain_enabled = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "lean_flags") c->lean_flags = value != 0.0;
+    else if (k == "chain_fuse_residual") c->chain_fuse_residual = value != 0.0;
+    else if (k == "keep_b") c->keep_b = value != 0.0;
     else if (k == "chain_prefetch") c->chain_prefetch = (int)value;
     else if (k == "chain_packed") c->chain_packed = value != 0.0 ? 1 : 0;
     else if (k == "chain_affine") { c->chain_affine = value != 0.0; c->have_symbolic = false; c->have_factor = false; }

@@ -196,6 +196,7 @@ int assemble_triplets(daecpp_b200_ctx *c, TripletSet &T, const double *A, const 
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(T.ti.p, ti, sizeof(int32_t) * nT, cudaMemcpyHostToDevice, st));
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(T.tj.p, tj, sizeof(int32_t) * nT, cudaMemcpyHostToDevice, st));
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(T.A.p, A, sizeof(double) * nT, cudaMemcpyHostToDevice, st));
+    c->flags_clean = false;
     DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags, 0, sizeof(int32_t) * 4, st));
 
     if (T.have_pattern && T.nT_cached == nT)
@@ -212,6 +213,7 @@ int assemble_triplets(daecpp_b200_ctx *c, TripletSet &T, const double *A, const 
         DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags, c->d_flags, sizeof(int32_t) * 4, cudaMemcpyDeviceToHost, st));
         DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
         if (c->h_flags[1] == 0) return DAECPP_B200_OK;
+        c->flags_clean = false;
         DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags, 0, sizeof(int32_t) * 4, st));
     }
 

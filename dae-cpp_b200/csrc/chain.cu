@@ -13,6 +13,7 @@
 // the CTA.  That reduced system is factored by the same kernel run on it (one CTA for up to
 // T*Q0 tiles).  No index table other than the slot map is read: the hierarchy is implicit.
 // HBM traffic per refactorisation: slot map + matrix values in, 5*B*B doubles per block row out.
+#include "bdf.hpp"
 #include "chain.hpp"
 #include "chain_ops.hpp"
 #include "ctx.hpp"
@@ -55,6 +56,11 @@ struct ChainArgs
     double atol, rtol, max_err_abs;
     int32_t update;
     int32_t *dflags;
+    // fused residual (diagonal mass): rhs = M*dxdt - f formed while staging (vector_ops.cu: k_residual_diag)
+    int32_t fuse_res;
+    Bdf bdf;
+    const double *mdiag, *fvec;
+    double *b_out; // optional copy of b to HBM
     int32_t *host_flags; // mapped host mirror of dflags[2..4], written by the CTA that finishes the iteration last
     // ensemble: member = blockIdx.y, strides in elements
     const double *alpha_arr;
@@ -318,7 +324,7 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
         if (flag) atomicOr(&a.dflags[2], flag);
         if (a.host_flags && last_tile_done(a.counter + 4, lv.ntiles, t))
         {
-            if (t < 3) a.host_flags[t] = atomicOr(&a.dflags[2 + t], 0); // visible to the host once the grid has completed
+            if (t < 3) a.host_flags[t] = atomicExch(&a.dflags[2 + t], 0); // published and reset for the next iteration
         }
     }
     else
@@ -328,6 +334,54 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
         {
             const int q = idx / nvalid, row = idx - q * nvalid;
             xl[((size_t)tile * D::ROWS + row) * B + q] = sh.R[(size_t)q * D::RP + sidx<B>(row)];
+        }
+    }
+}
+
+// stage_rhs_first with the residual formed on the fly: b_o = (0 + M_oo * dxdt_o) - f_o, the roundings of
+// k_residual_diag (dae-cpp/solver.hpp:516-518 for a diagonal mass matrix).  All loads of a batch first.
+template <int B>
+__device__ __forceinline__ void stage_rhs_residual(int t, int tile, int n, double *R, const ChainArgs &a, int64_t mb)
+{
+    using D = Dim<B>;
+    constexpr int TOTAL = B * D::ROWS, U = 4, NT = D::T;
+    const Bdf &s = a.bdf;
+    const int64_t sv = mb * a.s_vec;
+    for (int i0 = t; i0 < TOTAL; i0 += NT * U)
+    {
+        int64_t o[U];
+        double xk[U], x0[U], x1[U], x2[U], x3[U], m[U], f[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+        {
+            const int idx = i0 + u * NT;
+            const int q = idx / D::ROWS, row = idx - q * D::ROWS;
+            const int64_t k = ((int64_t)tile * D::ROWS + row) * B + q;
+            o[u] = (idx < TOTAL && k < n) ? (a.perm ? (int64_t)a.perm[k] : k) : -1;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+        {
+            const bool ok = o[u] >= 0;
+            const int64_t j = ok ? o[u] + sv : 0;
+            xk[u] = ok ? s.xk[j] : 0.0; x0[u] = ok ? s.x0[j] : 0.0;
+            x1[u] = (ok && s.order >= 2) ? s.x1[j] : 0.0;
+            x2[u] = (ok && s.order >= 3) ? s.x2[j] : 0.0;
+            x3[u] = (ok && s.order >= 4) ? s.x3[j] : 0.0;
+            m[u] = ok ? a.mdiag[o[u] + mb * a.s_mv] : 0.0;
+            f[u] = ok ? a.fvec[j] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+        {
+            const int idx = i0 + u * NT;
+            if (idx < TOTAL)
+            {
+                const int q = idx / D::ROWS, row = idx - q * D::ROWS;
+                const double v = o[u] >= 0 ? __dsub_rn(__dadd_rn(0.0, __dmul_rn(m[u], bdf_one(s, xk[u], x0[u], x1[u], x2[u], x3[u]))), f[u]) : 0.0;
+                R[(size_t)q * D::RP + sidx<B>(row)] = v;
+                if (a.b_out && o[u] >= 0) a.b_out[o[u] + sv] = v;
+            }
         }
     }
 }
@@ -343,7 +397,8 @@ __device__ __forceinline__ void forward_tile(const ChainArgs &a, const LevelView
     const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
     const int tk = FIRST ? 2 : 3;
     stamp(a, tk, tile, 0);
-    if (FIRST) stage_rhs_first<B>(t, D::T, tile, a.n, sh.R, a.rhs + mb * a.s_vec, a.perm);
+    if (FIRST && a.fuse_res) stage_rhs_residual<B>(t, tile, a.n, sh.R, a, mb);
+    else if (FIRST) stage_rhs_first<B>(t, D::T, tile, a.n, sh.R, a.rhs + mb * a.s_vec, a.perm);
     else stage_rhs_reduced<B>(t, D::T, tile, lv.rows, sh.R, lv.rv_in + mb * a.s_rv);
     load_small_factors<B>(t, D::T, sh, Ft);
     __syncthreads();
@@ -705,6 +760,11 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         a.out = c->dx; a.xk = c->xk; a.x0 = c->xh[0];
         a.atol = atol; a.rtol = rtol; a.max_err_abs = max_err_abs;
         a.update = fuse_update ? 1 : 0;
+        if (c->fuse_residual_now)
+        {
+            a.fuse_res = 1; a.bdf = c->bdf_pending; a.mdiag = c->M.vals.p; a.fvec = c->f;
+            a.b_out = c->keep_b ? c->b : nullptr;
+        }
         a.host_flags = c->publish_flags ? c->h_flags_dev + 2 : nullptr;
         if (a.host_flags) c->flags_published = true;
     };

@@ -1,5 +1,6 @@
 // Internal context layout shared by the .cu translation units of libdaecpp_b200.so.
 #pragma once
+#include "bdf.hpp"
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -114,6 +115,11 @@ struct daecpp_b200_ctx
     int32_t *h_flags = nullptr; // pinned mirror (mapped: the last kernel of a fused chain iteration writes it directly)
     int32_t *h_flags_dev = nullptr;
     bool lean_flags = true, publish_flags = false, flags_published = false;
+    bool flags_clean = false;          // d_flags[2..4] are zero (the publishing CTA of a fused chain iteration resets them)
+    bool chain_fuse_residual = true;   // diagonal mass: b = M*dxdt - f is formed while the forward kernel stages its right-hand side
+    bool fuse_residual_now = false;    // set by the fused iteration for the solve that follows
+    bool keep_b = false;               // fused residual: also write b to HBM (get_vector(b) after a fused iteration)
+    daecpp_b200::Bdf bdf_pending{};
     double *d_scalars = nullptr, *h_scalars = nullptr; // [8]
     double *h_stage = nullptr;  // pinned staging for n doubles
     size_t h_stage_cap = 0;
@@ -228,6 +234,7 @@ int chain_refactor_async(daecpp_b200_ctx *c, double alpha);
 int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, double max_err_abs);
 // vector_ops.cu
 int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5], bool clear_flags = false);
+Bdf make_bdf(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
 int classify_mass(daecpp_b200_ctx *c);
 int launch_dxdt(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
 int launch_update(daecpp_b200_ctx *c, double atol, double rtol, double max_err_abs);

@@ -809,6 +809,7 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
     Symbolic &S = c->S;
     int rc;
     if (!c->jvals_from_triplets && !c->direct_csc && (rc = ensure_csc_values(c, c->J))) return rc;
+    c->flags_clean = false;
     if (clear_flags) DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 3, 0, 2 * sizeof(int32_t), st));
     if (c->CH.active)
     {

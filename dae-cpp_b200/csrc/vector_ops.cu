@@ -7,6 +7,7 @@
 //
 // Arithmetic is written with __dmul_rn/__dadd_rn/__dsub_rn so that nvcc cannot contract to
 // FMA: the reference's default build has none, and b / xk are compared bit for bit.
+#include "bdf.hpp"
 #include "ctx.hpp"
 
 namespace daecpp_b200
@@ -14,24 +15,6 @@ namespace daecpp_b200
 namespace
 {
 constexpr int TPB = 256;
-
-struct Bdf
-{
-    double c[5];
-    const double *xk, *x0, *x1, *x2, *x3;
-    int order;
-};
-
-__device__ __forceinline__ double bdf_at(const Bdf &s, int64_t i)
-{
-    if (s.order == 1) return __dmul_rn(__dsub_rn(s.xk[i], s.x0[i]), s.c[0]);
-    double r = __dmul_rn(s.c[0], s.xk[i]);
-    r = __dsub_rn(r, __dmul_rn(s.c[1], s.x0[i]));
-    r = __dadd_rn(r, __dmul_rn(s.c[2], s.x1[i]));
-    if (s.order >= 3) r = __dsub_rn(r, __dmul_rn(s.c[3], s.x2[i]));
-    if (s.order >= 4) r = __dadd_rn(r, __dmul_rn(s.c[4], s.x3[i]));
-    return r;
-}
 
 __global__ void k_dxdt(Bdf s, int32_t n, double *__restrict__ out)
 {
@@ -58,16 +41,6 @@ __global__ void k_residual(Bdf s, int32_t n, const int32_t *__restrict__ rowptr,
 // M with exactly one entry per row on the diagonal and slots in row order (MassMatrixIdentity, any
 // diagonal mass): no index is read, two rows per thread with 16-byte accesses.  The sum still
 // starts from +0.0 like the general row loop, so b is bit-identical.
-__device__ __forceinline__ double bdf_one(const Bdf &s, double xk, double x0, double x1, double x2, double x3)
-{
-    if (s.order == 1) return __dmul_rn(__dsub_rn(xk, x0), s.c[0]);
-    double r = __dmul_rn(s.c[0], xk);
-    r = __dsub_rn(r, __dmul_rn(s.c[1], x0));
-    r = __dadd_rn(r, __dmul_rn(s.c[2], x1));
-    if (s.order >= 3) r = __dsub_rn(r, __dmul_rn(s.c[3], x2));
-    if (s.order >= 4) r = __dadd_rn(r, __dmul_rn(s.c[4], x3));
-    return r;
-}
 __global__ void k_residual_diag(Bdf s, int32_t n, const double *__restrict__ mvals, const double *__restrict__ f,
                                 double *__restrict__ b, int32_t *__restrict__ clear)
 {
@@ -150,6 +123,8 @@ __global__ void k_accept(int32_t n, const double *__restrict__ xk, const double 
     if ((threadIdx.x & 31) == 0 && bits) atomicMax(vmax_bits, bits);
 }
 
+} // namespace
+
 Bdf make_bdf(daecpp_b200_ctx *c, int32_t order, const double coef[5])
 {
     Bdf s;
@@ -158,7 +133,6 @@ Bdf make_bdf(daecpp_b200_ctx *c, int32_t order, const double coef[5])
     s.order = order;
     return s;
 }
-} // namespace
 
 int launch_dxdt(daecpp_b200_ctx *c, int32_t order, const double coef[5])
 {
