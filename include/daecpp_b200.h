@@ -158,9 +158,20 @@ int daecpp_b200_set_vector(daecpp_b200_ctx *ctx, int32_t which, const double *ho
 int daecpp_b200_get_stat(daecpp_b200_ctx *ctx, const char *key, double *value);
 /* Debug: with option "trace_units" = 1 the factor kernel stamps %globaltimer (ns) four times per
  * subtree unit (start, staged, dependencies met, done), in ticket order, for the factor kernel and
- * then for the forward and the backward solve kernels (3 x n_units x 4 values). */
+ * then for the forward and the backward solve kernels (3 x n_units x 4 values).  On the block-chain
+ * path (two-level hierarchies) the layout is 5 kernels x tiles x 8 stamps instead
+ * (profiles/tools/chain_trace.py reads it). */
 int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *ctx, int64_t *out, int64_t cap, int64_t *count);
-/* Tunables, by name ("refine_steps", "pivot_tol", "leaf_size", "use_graph" ...). */
+/* Tunables, by name ("refine_steps", "pivot_tol", "leaf_size", "use_graph" ...).  Block-chain path
+ * (banded patterns; every variant computes the same factors, the switches exist for A/B measurements):
+ * "chain" (0: always the general multifrontal path), "chain_min_n", "chain_max_block", "chain_affine"
+ * (descriptor instead of slot map for tiles whose value sources are arithmetic progressions),
+ * "chain_packed" (contiguous-run LDGSTS staging), "chain_fuse_top" (bit 0: factor, bit 1: solve -- top
+ * level swept by the CTA that finishes last), "chain_defer_top" (top level factored by an extra CTA of the
+ * forward launch inside daecpp_b200_iteration_*), "chain_fuse_residual" (diagonal mass: b formed inside the
+ * forward kernel; "keep_b" = 1 also writes it to HBM for daecpp_b200_get_vector), "lean_flags" (flag words
+ * delivered through a mapped host word instead of memset + copy nodes).  General path: "blocked_lu",
+ * "blocked_lu_min_dim".  Debug: "trace_units", "phase_timing", "pinned_io". */
 int daecpp_b200_set_option(daecpp_b200_ctx *ctx, const char *key, double value);
 
 #ifdef __cplusplus
