@@ -189,12 +189,13 @@ int daecpp_b200_create(int32_t n, int device, daecpp_b200_ctx **out)
         if ((e = cudaEventCreate(&c->pev[k])) != cudaSuccess) return bail(e, "cudaEventCreate");
     double *slab = nullptr;
     const size_t nv = 10; // xk, x[0..3], f, b, dx, work, dxdt
-    if ((e = cudaMalloc((void **)&slab, sizeof(double) * nv * (size_t)n)) != cudaSuccess) return bail(e, "cudaMalloc(state)");
+    const size_t ns = ((size_t)n + 31) / 32 * 32; // every vector starts on a 256-byte boundary (16-byte vector accesses, odd n)
+    if ((e = cudaMalloc((void **)&slab, sizeof(double) * nv * ns)) != cudaSuccess) return bail(e, "cudaMalloc(state)");
     c->xk = slab;
-    for (int k = 0; k < 4; ++k) c->xh[k] = slab + (size_t)(k + 1) * n;
-    c->f = slab + 5 * (size_t)n; c->b = slab + 6 * (size_t)n; c->dx = slab + 7 * (size_t)n;
-    c->work = slab + 8 * (size_t)n; c->dxdt = slab + 9 * (size_t)n;
-    if ((e = cudaMemsetAsync(slab, 0, sizeof(double) * nv * (size_t)n, c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
+    for (int k = 0; k < 4; ++k) c->xh[k] = slab + (size_t)(k + 1) * ns;
+    c->f = slab + 5 * ns; c->b = slab + 6 * ns; c->dx = slab + 7 * ns;
+    c->work = slab + 8 * ns; c->dxdt = slab + 9 * ns;
+    if ((e = cudaMemsetAsync(slab, 0, sizeof(double) * nv * ns, c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
     if ((e = cudaMalloc((void **)&c->d_flags, sizeof(int32_t) * 8)) != cudaSuccess) return bail(e, "cudaMalloc(flags)");
     if ((e = cudaMalloc((void **)&c->d_scalars, sizeof(double) * 8)) != cudaSuccess) return bail(e, "cudaMalloc(scalars)");
     if ((e = cudaHostAlloc((void **)&c->h_flags, sizeof(int32_t) * 8, cudaHostAllocMapped)) != cudaSuccess) return bail(e, "cudaHostAlloc");

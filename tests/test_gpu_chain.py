@@ -168,3 +168,79 @@ def test_chain_repeated_iterations_reuse_counters():
             eta, _ = O.backward_error(n, csc, x, b)
             assert eta <= 1e-12
     c.close()
+
+
+VARIANTS = [
+    {},  # defaults: edge tiles affine, packed staging, top level deferred into the forward launch, fused residual, lean flags
+    {"chain_defer_top": 0},
+    {"chain_fuse_residual": 0},
+    {"chain_fuse_residual": 1, "keep_b": 1},
+    {"lean_flags": 0},
+    {"chain_packed": 0},
+    {"chain_affine": 0},
+    {"chain_fuse_top": 0},
+    {"chain_fuse_top": 3},
+    {"chain_defer_top": 0, "chain_fuse_residual": 0, "lean_flags": 0, "chain_packed": 0, "chain_affine": 0, "chain_fuse_top": 0},
+]
+
+
+def _fused_iterations(problem, n, options, iters=3):
+    """Three fused Newton iterations (daecpp_b200_iteration_resident) and everything they leave behind."""
+    if problem == "flame1d":
+        x = P.flame1d_state(n); M = P.identity_mass(n); J = P.flame1d_jacobian(x); f = P.flame1d_rhs(x)
+    else:
+        N = n // 2
+        x = P.perovskite_state(N); M = P.perovskite_mass(N); J = P.perovskite_jacobian(x, N)
+        f = np.sin(np.arange(n) * 0.01) * 1e-3
+    c = B.Context(n)
+    for k, v in options.items():
+        c.set_option(k, v)
+    c.set_state(x); c.set_mass(M); c.set_jacobian(J)
+    dt4 = np.array([1e-3, 0.0, 0.0, 0.0])
+    c.residual(f, 1, dt4)  # uploads f (and leaves b behind for the variants that do not rewrite it)
+    out = []
+    for it in range(iters):
+        rc, flags = c.iteration_resident(0 if it == 1 else 1, 1, dt4, 1e-6, 1e-6)  # iteration 1 reuses the factors
+        out.append((rc, flags, c.get_vector("dx").tobytes(), c.get_vector("xk").tobytes()))
+    b = c.get_vector("b").tobytes()
+    c.close()
+    return out, b
+
+
+@pytest.mark.parametrize("problem,n", [("flame1d", 50000), ("flame1d", 2048 * 3 + 5), ("perovskite", 8000)])
+def test_fused_iteration_variants_are_bit_identical(problem, n):
+    """Staging variants, the deferred top-level factorisation, the fused residual and the flag delivery
+    change how the iteration is scheduled, never what it computes."""
+    ref, _ = _fused_iterations(problem, n, VARIANTS[0])
+    assert all(r[0] == 0 for r in ref)
+    for opt in VARIANTS[1:]:
+        got, _ = _fused_iterations(problem, n, opt)
+        for it, (a, g) in enumerate(zip(ref, got)):
+            assert a[0] == g[0] and a[1] == g[1], (opt, it, a[:2], g[:2])
+            assert a[2] == g[2], (opt, it, "dx differs")
+            assert a[3] == g[3], (opt, it, "xk differs")
+
+
+def test_fused_residual_keep_b_matches_residual_kernel():
+    n = 30000
+    _, b_kernel = _fused_iterations("flame1d", n, {"chain_fuse_residual": 0}, iters=2)
+    _, b_fused = _fused_iterations("flame1d", n, {"chain_fuse_residual": 1, "keep_b": 1}, iters=2)
+    assert b_kernel == b_fused
+
+
+def test_chain_trace_layout():
+    n = 2048 * 5
+    x = P.flame1d_state(n)
+    c = B.Context(n)
+    c.set_state(x); c.set_mass(P.identity_mass(n)); c.set_jacobian(P.flame1d_jacobian(x))
+    dt4 = np.array([1e-3, 0.0, 0.0, 0.0])
+    c.residual(P.flame1d_rhs(x), 1, dt4)
+    c.iteration_resident(1, 1, dt4, 1e-6, 1e-6)
+    c.set_option("trace_units", 1)
+    c.iteration_resident(1, 1, dt4, 1e-6, 1e-6)
+    tiles = int(c.stat("chain_tiles"))
+    tr = c.unit_trace().ravel().reshape(5, tiles, 8)
+    c.close()
+    assert tiles == 5
+    assert np.all(tr[0, :, 0] > 0) and np.all(tr[0, :, 4] >= tr[0, :, 0])      # factor tiles: start <= done
+    assert np.all(tr[2, :, 0] >= tr[0, :, 4].min()) and np.all(tr[4, :, 3] >= tr[2, :, 4].max())  # factor -> forward -> backward

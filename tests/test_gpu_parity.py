@@ -347,3 +347,22 @@ def test_linear_solve_blocked_big_fronts(m, budget):
     opts["blocked_lu"] = 0
     x0, _ = _solve_and_check(m * m, P.grid2d_probe_matrix(m), EMPTY, 0.0, options=opts)
     assert np.max(np.abs(x1 - x0)) <= 1e-10 * np.max(np.abs(x0))
+
+
+@pytest.mark.parametrize("n", [1, 3, 255, 6149])
+def test_residual_diagonal_mass_odd_sizes(n):
+    """k_residual_diag works on 16-byte pairs: vectors of odd length must still start aligned."""
+    rng = np.random.default_rng(n)
+    x = rng.standard_normal(n); f = rng.standard_normal(n)
+    M = (rng.uniform(0.5, 2.0, n), np.arange(n, dtype=np.int32), np.arange(n, dtype=np.int32))
+    c = B.Context(n)
+    c.set_state(x); c.set_mass(M)
+    c.set_vector("xk", x + 1e-3 * rng.standard_normal(n))
+    dt = np.array([1e-2, 0.0, 0.0, 0.0])
+    alpha = c.residual(f, 1, dt)
+    xk = c.get_vector("xk"); xh = np.concatenate([x, np.zeros(3 * n)])
+    d = np.zeros(n); b_ref = np.zeros(n)
+    assert alpha == O.port.oracle_time_derivative(n, 1, dt, xk, xh, d)
+    O.port.oracle_residual(n, *O.convert(O.port, n, M), d, f, b_ref)
+    assert c.get_vector("b").tobytes() == b_ref.tobytes()
+    c.close()
