@@ -476,8 +476,10 @@ def run_b200_arm(args):
     abytes = algorithmic_bytes(w, nnz_jb)
 
     def resident(k_iters, refactor=1):
-        for _ in range(k_iters):
-            c.iteration_resident(refactor, order, dt, atol, rtol)
+        # k complete Newton iterations, each with its flags on the host before the next is enqueued; the
+        # loop itself runs behind the C ABI (what a C++ caller does) rather than through ctypes
+        if k_iters > 0:
+            c.iterations_resident(k_iters, refactor, order, dt, atol, rtol)
 
     # ---- value: K iterations, data resident in HBM
     resident(args.warmup)

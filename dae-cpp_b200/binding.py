@@ -23,7 +23,7 @@ SYMBOLS = [
     "daecpp_b200_rollback", "daecpp_b200_set_mass", "daecpp_b200_set_jacobian", "daecpp_b200_residual",
     "daecpp_b200_refactor", "daecpp_b200_solve_update", "daecpp_b200_accept_step", "daecpp_b200_set_rhs",
     "daecpp_b200_solve", "daecpp_b200_get_csc", "daecpp_b200_get_vector", "daecpp_b200_set_vector", "daecpp_b200_get_stat",
-    "daecpp_b200_set_option", "daecpp_b200_iteration_resident", "daecpp_b200_event_mark", "daecpp_b200_event_elapsed_ms", "daecpp_b200_debug_unit_trace", "daecpp_b200_host_register", "daecpp_b200_host_unregister",
+    "daecpp_b200_set_option", "daecpp_b200_iteration_resident", "daecpp_b200_iterations_resident", "daecpp_b200_event_mark", "daecpp_b200_event_elapsed_ms", "daecpp_b200_debug_unit_trace", "daecpp_b200_host_register", "daecpp_b200_host_unregister",
     "daecpp_b200_set_blocking_sync", "daecpp_b200_set_pooling", "daecpp_b200_set_jacobian_values", "daecpp_b200_iteration_host",
 ]
 
@@ -62,6 +62,8 @@ def load():
     lib.daecpp_b200_set_option.argtypes = [_vp, C.c_char_p, C.c_double]
     lib.daecpp_b200_iteration_resident.argtypes = [_vp, C.c_int32, C.c_int32, _f64, C.c_double, C.c_double, C.c_double,
                                                    C.POINTER(C.c_int32)]
+    lib.daecpp_b200_iterations_resident.argtypes = [_vp, C.c_int32, C.c_int32, C.c_int32, _f64, C.c_double, C.c_double, C.c_double,
+                                                    C.POINTER(C.c_int32)]
     lib.daecpp_b200_set_jacobian_values.argtypes = [_vp, _vp, C.c_int64]
     lib.daecpp_b200_iteration_host.argtypes = [_vp, _vp, C.c_int32, C.c_int32, _f64, C.c_double, C.c_double, C.c_double, _vp,
                                                C.POINTER(C.c_double), C.POINTER(C.c_int32)]
@@ -175,6 +177,13 @@ class Context:
         rc = self._ck(self.lib.daecpp_b200_iteration_resident(self.h, int(do_refactor), order,
                                                               np.ascontiguousarray(dt4, np.float64), atol, rtol,
                                                               max_err_abs, C.byref(flags)), allow)
+        return rc, flags.value
+
+    def iterations_resident(self, count, do_refactor, order, dt4, atol, rtol, max_err_abs=1e100, allow=()):
+        flags = C.c_int32(0)
+        rc = self._ck(self.lib.daecpp_b200_iterations_resident(self.h, int(count), int(do_refactor), order,
+                                                               np.ascontiguousarray(dt4, np.float64), atol, rtol,
+                                                               max_err_abs, C.byref(flags)), allow)
         return rc, flags.value
 
     def set_jacobian_values_raw(self, A, nT):

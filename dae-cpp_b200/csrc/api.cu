@@ -2,6 +2,7 @@
 // regions each entry point replaces).
 #include <cmath>
 #include <cstring>
+#include <chrono>
 #include <mutex>
 #include <new>
 #include <utility>
@@ -133,7 +134,7 @@ static void recycle(daecpp_b200_ctx *c)
         c->sopt.max_super != fresh.sopt.max_super)
         c->have_symbolic = false;
     c->chain_enabled = fresh.chain_enabled; c->chain_min_n = fresh.chain_min_n; c->chain_max_b = fresh.chain_max_b;
-    c->chain_affine = fresh.chain_affine; c->chain_packed = fresh.chain_packed; c->lean_flags = fresh.lean_flags; c->publish_flags = false; c->flags_clean = false; c->chain_fuse_residual = fresh.chain_fuse_residual; c->keep_b = fresh.keep_b; c->fuse_residual_now = false; c->chain_prefetch = fresh.chain_prefetch; c->chain_fuse_top = fresh.chain_fuse_top; c->chain_defer_top = fresh.chain_defer_top; c->chain_may_defer = false; c->chain_top_pending = false; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
+    c->chain_affine = fresh.chain_affine; c->chain_packed = fresh.chain_packed; c->lean_flags = fresh.lean_flags; c->spin_flags = fresh.spin_flags; c->publish_flags = false; c->flags_clean = false; c->chain_fuse_residual = fresh.chain_fuse_residual; c->keep_b = fresh.keep_b; c->fuse_residual_now = false; c->chain_prefetch = fresh.chain_prefetch; c->chain_fuse_top = fresh.chain_fuse_top; c->chain_defer_top = fresh.chain_defer_top; c->chain_top_pcr = fresh.chain_top_pcr; c->chain_top_mode = 0; c->chain_may_defer = false; c->chain_top_pending = false; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
     c->refine_steps = 0; c->assemble_only = false; c->pinned_io = false; c->pivot_tol = 0.0;
     c->phase_timing = false; c->trace_units = false; c->blocked_lu = fresh.blocked_lu; c->blocked_lu_min_dim = fresh.blocked_lu_min_dim;
     c->n_symbolic = c->n_refactor = c->n_solve = c->n_cold = c->kernels = 0;
@@ -508,6 +509,26 @@ static int finish_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t *fl
     return DAECPP_B200_OK;
 }
 
+// The host side of "flags ready".  When the iteration's last CTA published the flags to the mapped mirror
+// (chain path) the host spins on the sequence word it wrote behind them -- a few hundred nanoseconds after
+// the write instead of a driver round trip; everything else (and a long wait) synchronises the stream.
+static int wait_iteration(daecpp_b200_ctx *c)
+{
+    if (c->flags_published && c->spin_flags && !c->phase_timing)
+    {
+        volatile int32_t *seq = c->h_flags + 5;
+        const auto t0 = std::chrono::steady_clock::now();
+        for (uint32_t spins = 0; *seq != (int32_t)c->flag_seq; ++spins)
+        {
+            __builtin_ia32_pause();
+            if ((spins & 1023u) == 1023u && std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(500)) break;
+        }
+        if (*seq == (int32_t)c->flag_seq) return DAECPP_B200_OK;
+    }
+    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    return DAECPP_B200_OK;
+}
+
 static int prepare_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t order, const double dt[4], double w[5])
 {
     if (!c->M.have_pattern || !c->J.have_pattern) return fail(c, DAECPP_B200_EINVAL, "set_mass/set_jacobian must precede");
@@ -528,8 +549,25 @@ int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int3
     int rc = prepare_iteration(c, do_refactor, order, dt, w);
     if (rc) return rc;
     if ((rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs))) return rc;
-    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    if ((rc = wait_iteration(c))) return rc;
     return finish_iteration(c, do_refactor, flags);
+}
+
+int daecpp_b200_iterations_resident(daecpp_b200_ctx *c, int32_t count, int32_t do_refactor, int32_t order, const double dt[4],
+                                    double atol, double rtol, double max_err_abs, int32_t *flags)
+{
+    if (!c || !dt || !flags || count < 1) return DAECPP_B200_EINVAL;
+    cudaSetDevice(c->device);
+    double w[5];
+    for (int32_t k = 0; k < count; ++k)
+    {
+        int rc = prepare_iteration(c, do_refactor, order, dt, w);
+        if (rc) return rc;
+        if ((rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs))) return rc;
+        if ((rc = wait_iteration(c))) return rc;
+        if ((rc = finish_iteration(c, do_refactor, flags))) return rc;
+    }
+    return DAECPP_B200_OK;
 }
 
 int daecpp_b200_set_jacobian_values(daecpp_b200_ctx *c, const double *A, int64_t nT)
@@ -777,6 +815,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "pinned_io") c->pinned_io = value != 0.0;
     else if (k == "chain") { c->chain_enabled = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "lean_flags") c->lean_flags = value != 0.0;
+    else if (k == "spin_flags") c->spin_flags = value != 0.0;
     else if (k == "chain_fuse_residual") c->chain_fuse_residual = value != 0.0;
     else if (k == "keep_b") c->keep_b = value != 0.0;
     else if (k == "chain_prefetch") c->chain_prefetch = (int)value;
@@ -786,6 +825,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "blocked_lu_min_dim") c->blocked_lu_min_dim = (int)value;
     else if (k == "chain_fuse_top") c->chain_fuse_top = (int)value;
     else if (k == "chain_defer_top") c->chain_defer_top = value != 0.0;
+    else if (k == "chain_top_pcr") c->chain_top_pcr = value != 0.0;
     else if (k == "chain_min_n") { c->chain_min_n = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "chain_max_block") { c->chain_max_b = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "trace_units") c->trace_units = value != 0.0;

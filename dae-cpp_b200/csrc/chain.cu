@@ -42,6 +42,7 @@ struct ChainArgs
     LevelView lv;  // the level this launch sweeps, one CTA per tile
     LevelView top; // fuse_top: the single-tile top level, swept by the CTA that finishes last
     int32_t fuse_top, n, trace_tiles, packed, prefetch;
+    int32_t top_pcr;      // the top level is solved by parallel cyclic reduction straight from the reduced system (no top factors)
     int32_t extra_factor; // forward launch: CTA number lv.ntiles factors the top level (deferred from the factor launch)
     uint32_t *counter; // [2 * members] tiles finished (factor, forward)
     // factor
@@ -61,6 +62,7 @@ struct ChainArgs
     Bdf bdf;
     const double *mdiag, *fvec;
     double *b_out; // optional copy of b to HBM
+    int32_t seq;
     int32_t *host_flags; // mapped host mirror of dflags[2..4], written by the CTA that finishes the iteration last
     // ensemble: member = blockIdx.y, strides in elements
     const double *alpha_arr;
@@ -256,6 +258,11 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
     FactorShared<B> &sh = *reinterpret_cast<FactorShared<B> *>(smem);
     const int t = threadIdx.x, tile = blockIdx.x;
     const int64_t mb = blockIdx.y;
+    if (FIRST && a.trace && t == 0 && tile == 0 && mb == 0)
+    {   // keep the previous iteration's first and last stamp of tile 0: the idle time between iterations
+        a.trace[6] = a.trace[5];
+        a.trace[7] = a.trace[((size_t)4 * a.trace_tiles) * TRACE_SLOTS + 3];
+    }
     stamp(a, FIRST ? 0 : 1, tile, 5);
     pdl_wait();
     factor_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true);
@@ -324,7 +331,12 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
         if (flag) atomicOr(&a.dflags[2], flag);
         if (a.host_flags && last_tile_done(a.counter + 4, lv.ntiles, t))
         {
-            if (t < 3) a.host_flags[t] = atomicExch(&a.dflags[2 + t], 0); // published and reset for the next iteration
+            if (t == 0)
+            {   // published, reset for the next iteration, then the sequence number the host may spin on
+                for (int k = 0; k < 3; ++k) a.host_flags[k] = atomicExch(&a.dflags[2 + k], 0);
+                __threadfence_system();
+                *reinterpret_cast<volatile int32_t *>(a.host_flags + 3) = a.seq;
+            }
         }
     }
     else
@@ -386,6 +398,134 @@ __device__ __forceinline__ void stage_rhs_residual(int t, int tile, int n, doubl
     }
 }
 
+// ---- top level by parallel cyclic reduction ----------------------------------------------------------
+// The grid-level system (one row per tile: C3 489 rows) is too small to occupy the GPU and too serial
+// for one CTA: the chunked LU sweeps it in three dependent levels, forward and backward, ~35 dependent
+// steps each way with a handful of threads busy.  Cyclic reduction takes log2(rows) steps with every
+// thread busy: at stride s row i eliminates its couplings to rows i-s and i+s
+//     al = -A_i D_{i-s}^-1,  ga = -C_i D_{i+s}^-1
+//     A_i' = al A_{i-s},  C_i' = ga C_{i+s},  D_i' = D_i + al C_{i-s} + ga A_{i+s},  r_i' = r_i + al r_{i-s} + ga r_{i+s}
+// and after the last step x_i = D_i^-1 r_i.  It works on the reduced rows the tiles left in HBM
+// (A = G, D = Df - SL(next), C = Hf(next), chain_ops.hpp), so no top-level factors exist in this mode;
+// pivot blocks are inverted with the same in-block partial pivoting and raise the same failure flag.
+template <int B> struct Pcr
+{
+    static constexpr int ROWS = (B == 1) ? 512 : (B == 2 ? 128 : 64);
+    static constexpr int NR = (ROWS + Cfg<B>::T - 1) / Cfg<B>::T;
+    static_assert(sizeof(double) * ROWS * (3 * B * B + B) <= sizeof(SolveShared<B>), "cyclic reduction works inside the solve kernel's shared memory");
+};
+template <int B> __device__ __forceinline__ Mat<B> pcr_ldm(const double *p, int i)
+{
+    Mat<B> X;
+#pragma unroll
+    for (int e = 0; e < B * B; ++e) X.a[e] = p[e * Pcr<B>::ROWS + i];
+    return X;
+}
+template <int B> __device__ __forceinline__ Vec<B> pcr_ldv(const double *p, int i)
+{
+    Vec<B> v;
+#pragma unroll
+    for (int q = 0; q < B; ++q) v.a[q] = p[q * Pcr<B>::ROWS + i];
+    return v;
+}
+// Pivot-block inverse of the cyclic reduction.  B = 1: hardware reciprocal seed + two Newton steps, no
+// special-case branch (the library reciprocal's slow-path call would serialise the independent chains);
+// a zero or non-finite pivot is caught by the explicit test.  B > 1: Gauss-Jordan with in-block pivoting.
+template <int B> __device__ __forceinline__ Mat<B> pcr_inv(const Mat<B> &X, double tol, int &fail)
+{
+    if constexpr (B == 1)
+    {
+        const double d = X.a[0];
+        fail |= bad_pivot(d, tol) ? 1 : 0;
+        double y;
+        asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+        y = fma(y, fma(-d, y, 1.0), y);
+        y = fma(y, fma(-d, y, 1.0), y);
+        Mat<B> r;
+        r.a[0] = y;
+        return r;
+    }
+    else
+        return minv<B>(X, tol, fail);
+}
+
+template <int B>
+__device__ __noinline__ void pcr_top(int R, const double *__restrict__ red, const double *__restrict__ rv, double *__restrict__ xl,
+                                     double tol, int32_t *fail_flag, double *__restrict__ W, int t, long long *trace)
+{
+    auto mark = [&](int slot) {
+        if (trace && t == 0) { long long ns; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns)); trace[slot] = ns; }
+    };
+    using D = Dim<B>;
+    constexpr int BB = D::BB, PR = Pcr<B>::ROWS, NR = Pcr<B>::NR, NT = D::T;
+    double *sA = W, *sD = W + BB * PR, *sC = W + 2 * BB * PR, *sr = W + 3 * BB * PR;
+    for (int i = t; i < R; i += NT)
+    {
+        const bool nx = i + 1 < R;
+#pragma unroll
+        for (int e = 0; e < BB; ++e)
+        {
+            sA[e * PR + i] = red[((size_t)0 * R + i) * BB + e];
+            sD[e * PR + i] = red[((size_t)1 * R + i) * BB + e] - (nx ? red[((size_t)2 * R + i + 1) * BB + e] : 0.0);
+            sC[e * PR + i] = nx ? red[((size_t)3 * R + i + 1) * BB + e] : 0.0;
+        }
+#pragma unroll
+        for (int q = 0; q < B; ++q) sr[q * PR + i] = rv[((size_t)0 * R + i) * B + q] - (nx ? rv[((size_t)1 * R + i + 1) * B + q] : 0.0);
+    }
+    __syncthreads();
+    mark(1);
+    int fail = 0;
+    for (int s = 1; s < R; s <<= 1)
+    {
+        if (s == 8) mark(2);
+        Mat<B> nA[NR], nD[NR], nC[NR];
+        Vec<B> nr[NR];
+        // Branch-free: a missing neighbour is the row itself with a zero multiplier, so the NR x 2
+        // eliminations of a thread are independent instruction streams the scheduler can interleave
+        // (one warp per scheduler here: there is no other latency hiding).
+#pragma unroll
+        for (int k = 0; k < NR; ++k)
+        {
+            const int i = min(t + k * NT, R - 1);
+            const int im = max(i - s, 0), ip = min(i + s, R - 1);
+            const double ml = (i - s >= 0) ? -1.0 : 0.0, mr = (i + s < R) ? -1.0 : 0.0;
+            Mat<B> al = mmul<B>(pcr_ldm<B>(sA, i), pcr_inv<B>(pcr_ldm<B>(sD, im), tol, fail));
+            Mat<B> ga = mmul<B>(pcr_ldm<B>(sC, i), pcr_inv<B>(pcr_ldm<B>(sD, ip), tol, fail));
+#pragma unroll
+            for (int e = 0; e < BB; ++e) { al.a[e] *= ml; ga.a[e] *= mr; }
+            Mat<B> Di = pcr_ldm<B>(sD, i);
+            Vec<B> ri = pcr_ldv<B>(sr, i);
+            madd<B>(Di, mmul<B>(al, pcr_ldm<B>(sC, im)));
+            madd<B>(Di, mmul<B>(ga, pcr_ldm<B>(sA, ip)));
+            vadd<B>(ri, mv<B>(al, pcr_ldv<B>(sr, im)));
+            vadd<B>(ri, mv<B>(ga, pcr_ldv<B>(sr, ip)));
+            nA[k] = mmul<B>(al, pcr_ldm<B>(sA, im));
+            nC[k] = mmul<B>(ga, pcr_ldm<B>(sC, ip));
+            nD[k] = Di; nr[k] = ri;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < NR; ++k)
+        {
+            const int i = t + k * NT;
+            if (i >= R) continue;
+#pragma unroll
+            for (int e = 0; e < BB; ++e) { sA[e * PR + i] = nA[k].a[e]; sD[e * PR + i] = nD[k].a[e]; sC[e * PR + i] = nC[k].a[e]; }
+#pragma unroll
+            for (int q = 0; q < B; ++q) sr[q * PR + i] = nr[k].a[q];
+        }
+        __syncthreads();
+    }
+    mark(3);
+    for (int i = t; i < R; i += NT)
+    {
+        const Vec<B> x = mv<B>(pcr_inv<B>(pcr_ldm<B>(sD, i), tol, fail), pcr_ldv<B>(sr, i));
+#pragma unroll
+        for (int q = 0; q < B; ++q) xl[(size_t)i * B + q] = x.a[q];
+    }
+    if (fail) atomicOr(fail_flag, 1);
+}
+
 // forward sweep of one tile; the single tile of the top level carries on into the backward sweep
 template <int B, bool FIRST>
 __device__ __forceinline__ void forward_tile(const ChainArgs &a, const LevelView &lv, SolveShared<B> &sh, int t, int tile,
@@ -423,7 +563,7 @@ __device__ __forceinline__ void forward_tile(const ChainArgs &a, const LevelView
 }
 
 template <int B, bool FIRST>
-__global__ void __launch_bounds__(Cfg<B>::T) k_chain_forward(ChainArgs a)
+__global__ void __launch_bounds__(Cfg<B>::T, (B <= 2 ? 4 : 1)) k_chain_forward(ChainArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     SolveShared<B> &sh = *reinterpret_cast<SolveShared<B> *>(smem);
@@ -438,7 +578,17 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_forward(ChainArgs a)
     else
         forward_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true);
     if (a.fuse_top && last_tile_done(a.counter + 2 * mb + 1, a.lv.ntiles + a.extra_factor, t))
-        forward_tile<B, false>(a, a.top, sh, t, 0, mb, false); // top level: forward, then its backward sweep
+    {
+        if (a.top_pcr)
+        {
+            stamp(a, 3, 0, 0);
+            pcr_top<B>(a.top.rows, a.top.red_in + mb * a.s_red, a.top.rv_in + mb * a.s_rv, a.top.xlev + mb * a.s_x, a.tol, &a.dflags[3],
+                       reinterpret_cast<double *>(smem), t, a.trace ? a.trace + (size_t)3 * a.trace_tiles * TRACE_SLOTS : nullptr);
+            stamp(a, 3, 0, 4);
+        }
+        else
+            forward_tile<B, false>(a, a.top, sh, t, 0, mb, false); // top level: forward, then its backward sweep
+    }
 }
 
 template <int B, bool FIRST>
@@ -729,8 +879,12 @@ int chain_refactor_async(daecpp_b200_ctx *c, double alpha)
     if (c->sm_count == 0) cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, c->device);
     // at most 4 CTAs per SM with the factor kernel's shared memory: the forward launch must stay one wave
     const bool defer = !fuse && c->chain_may_defer && c->chain_defer_top && fuse_two_levels(c, 2) && P.levels[0].ntiles + 1 <= 4 * c->sm_count;
-    c->chain_top_pending = defer;
-    const int nlaunch = (fuse || defer) ? 1 : (int)P.levels.size();
+    // ... or no top-level factorisation at all: the solve reduces the top system cyclically (pcr_top)
+    const int pcr_rows = P.B == 1 ? Pcr<1>::ROWS : (P.B == 2 ? Pcr<2>::ROWS : Pcr<3>::ROWS);
+    const bool pcr = !fuse && c->chain_may_defer && c->chain_top_pcr && fuse_two_levels(c, 2) && P.levels[1].rows <= pcr_rows;
+    c->chain_top_mode = pcr ? 1 : 0;
+    c->chain_top_pending = defer && !pcr;
+    const int nlaunch = (fuse || defer || pcr) ? 1 : (int)P.levels.size();
     for (int g = 0; g < nlaunch; ++g)
     {
         ChainArgs a = level_args(c, g, fuse);
@@ -766,10 +920,11 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
             a.b_out = c->keep_b ? c->b : nullptr;
         }
         a.host_flags = c->publish_flags ? c->h_flags_dev + 2 : nullptr;
-        if (a.host_flags) c->flags_published = true;
+        if (a.host_flags) { c->flags_published = true; a.seq = (int32_t)++c->flag_seq; }
     };
-    if (c->chain_top_pending && !fuse)
+    if ((c->chain_top_pending || c->chain_top_mode == 1) && !fuse)
     {   // (options changed in between) factor the top level on its own
+        c->chain_top_mode = 0;
         ChainArgs a = level_args(c, 1, false);
 #define LF(B) launch_factor<B>(c, a, false)
         CHAIN_DISPATCH(P.B, LF)
@@ -782,6 +937,7 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         ChainArgs a = level_args(c, g, fuse);
         if (g == 0) first_args(a);
         if (g == 0 && c->chain_top_pending) { a.extra_factor = 1; c->chain_top_pending = false; }
+        if (g == 0 && c->chain_top_mode == 1) a.top_pcr = 1;
 #define LW(B) launch_forward<B>(c, a, g == 0)
         CHAIN_DISPATCH(P.B, LW)
 #undef LW

@@ -115,6 +115,8 @@ struct daecpp_b200_ctx
     int32_t *h_flags = nullptr; // pinned mirror (mapped: the last kernel of a fused chain iteration writes it directly)
     int32_t *h_flags_dev = nullptr;
     bool lean_flags = true, publish_flags = false, flags_published = false;
+    uint32_t flag_seq = 0;             // sequence number written behind the published flags (h_flags[5])
+    bool spin_flags = true;            // resident iteration: spin on that word instead of cudaStreamSynchronize
     bool flags_clean = false;          // d_flags[2..4] are zero (the publishing CTA of a fused chain iteration resets them)
     bool chain_fuse_residual = true;   // diagonal mass: b = M*dxdt - f is formed while the forward kernel stages its right-hand side
     bool fuse_residual_now = false;    // set by the fused iteration for the solve that follows
@@ -154,6 +156,8 @@ struct daecpp_b200_ctx
                                        // extra CTA of the forward launch, concurrently with the tiles' forward sweeps
     int sm_count = 0;
     bool chain_may_defer = false;      // set by the fused iteration around its refactor + solve pair
+    bool chain_top_pcr = true;         // ... or solved by parallel cyclic reduction with no top-level factors at all (chain.cu: pcr_top)
+    int chain_top_mode = 0;            // 0: top-level LU factors are current, 1: there are none (cyclic reduction at solve time)
     bool chain_top_pending = false;    // level-0 factors are current, the top level's are not yet
     int chain_fuse_top = 2; // bit 0: factor, bit 1: solve (top level swept by the last CTA of the level-0 launch)
     int chain_min_n = 256, chain_max_b = 3;

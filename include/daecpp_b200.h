@@ -119,6 +119,11 @@ int daecpp_b200_accept_step(daecpp_b200_ctx *ctx, int32_t variability_on, double
  * "dx applied, flags ready"); bench.py's `value` is measured through it. */
 int daecpp_b200_iteration_resident(daecpp_b200_ctx *ctx, int32_t do_refactor, int32_t order, const double dt[4],
                                    double atol, double rtol, double max_err_abs, int32_t *flags);
+/* `count` such iterations back to back, each complete (flags on the host) before the next is
+ * enqueued; *flags receives the last iteration's.  What a C++ Newton loop over resident data costs,
+ * without a foreign-function call per iteration (bench.py's `value`). */
+int daecpp_b200_iterations_resident(daecpp_b200_ctx *ctx, int32_t count, int32_t do_refactor, int32_t order,
+                                    const double dt[4], double atol, double rtol, double max_err_abs, int32_t *flags);
 /* Values-only Jacobian hand-off: the (i, j) stream is the one of the last
  * set_jacobian call -- JacobianMatrixShape fixes it at construction (jacobian-matrix.hpp:66-92) -- so
  * only the nT values travel.  Asynchronous: A must stay valid until the next synchronising call

@@ -10,10 +10,10 @@ w = bench.make_workload("flame1d", 1_000_000)
 lib = B.load(); c = B.Context(w["n"], 0, lib)
 c.set_state(w["x0"]); c.set_mass(w["M"]); c.set_jacobian(w["J"])
 alpha = c.residual(w["f"], w["order"], w["dt"]); c.refactor(alpha); c.solve_update(1e-6, 1e-6)
-fuse = int(sys.argv[1]) if len(sys.argv) > 1 else 2
-c.set_option("chain_fuse_top", fuse)
-if len(sys.argv) > 2: c.set_option("chain_packed", int(sys.argv[2]))
-if len(sys.argv) > 3: c.set_option("chain_defer_top", int(sys.argv[3]))
+# usage: chain_trace.py [key=value ...]   (daecpp_b200_set_option before the first iteration)
+for kv in sys.argv[1:]:
+    k, v = kv.split("=", 1)
+    c.set_option(k, float(v))
 for _ in range(5): c.iteration_resident(1, w["order"], w["dt"], 1e-6, 1e-6)
 c.set_option("trace_units", 1)
 for _ in range(3): c.iteration_resident(1, w["order"], w["dt"], 1e-6, 1e-6)
@@ -51,3 +51,8 @@ for k, nm in ((3, "top solve"), (4, "backward tiles")):
     end = 4 if k == 3 else 3; st = 3 if k == 3 else 2
     print(nm, "backward part (median us): levels 2+1 %.2f, level 0 sweep %.2f, write-out %.2f" % (
         np.median(a[:, 6] - a[:, st]) / 1e3, np.median(a[:, 7] - a[:, 6]) / 1e3, np.median(a[:, end] - a[:, 7]) / 1e3))
+
+a0 = tr[0, 0]
+if a0[6] > 0 and a0[7] > 0:
+    print("tile 0: previous iteration factor entry -> backward done %.2f us; idle until this iteration's factor entry %.2f us; period %.2f us" % (
+        (a0[7] - a0[6]) / 1e3, (a0[5] - a0[7]) / 1e3, (a0[5] - a0[6]) / 1e3))

@@ -170,17 +170,20 @@ def test_chain_repeated_iterations_reuse_counters():
     c.close()
 
 
+# (options, top level solved by cyclic reduction?)  Within each group only the scheduling differs.
 VARIANTS = [
-    {},  # defaults: edge tiles affine, packed staging, top level deferred into the forward launch, fused residual, lean flags
-    {"chain_defer_top": 0},
-    {"chain_fuse_residual": 0},
-    {"chain_fuse_residual": 1, "keep_b": 1},
-    {"lean_flags": 0},
-    {"chain_packed": 0},
-    {"chain_affine": 0},
-    {"chain_fuse_top": 0},
-    {"chain_fuse_top": 3},
-    {"chain_defer_top": 0, "chain_fuse_residual": 0, "lean_flags": 0, "chain_packed": 0, "chain_affine": 0, "chain_fuse_top": 0},
+    ({}, True),  # defaults: edge tiles affine, packed staging, cyclic-reduction top level, fused residual, lean flags
+    ({"chain_fuse_residual": 0}, True),
+    ({"chain_fuse_residual": 1, "keep_b": 1}, True),
+    ({"lean_flags": 0}, True),
+    ({"chain_packed": 0}, True),
+    ({"chain_affine": 0}, True),
+    ({"chain_top_pcr": 0}, False),                        # top level by LU in an extra CTA of the forward launch
+    ({"chain_top_pcr": 0, "chain_defer_top": 0}, False),  # top level by LU in its own launch
+    ({"chain_fuse_top": 0}, False),
+    ({"chain_fuse_top": 3}, False),
+    ({"chain_top_pcr": 0, "chain_defer_top": 0, "chain_fuse_residual": 0, "lean_flags": 0, "chain_packed": 0, "chain_affine": 0,
+      "chain_fuse_top": 0}, False),
 ]
 
 
@@ -201,24 +204,34 @@ def _fused_iterations(problem, n, options, iters=3):
     out = []
     for it in range(iters):
         rc, flags = c.iteration_resident(0 if it == 1 else 1, 1, dt4, 1e-6, 1e-6)  # iteration 1 reuses the factors
-        out.append((rc, flags, c.get_vector("dx").tobytes(), c.get_vector("xk").tobytes()))
+        out.append((rc, flags, c.get_vector("dx"), c.get_vector("xk")))
     b = c.get_vector("b").tobytes()
     c.close()
     return out, b
 
 
-@pytest.mark.parametrize("problem,n", [("flame1d", 50000), ("flame1d", 2048 * 3 + 5), ("perovskite", 8000)])
-def test_fused_iteration_variants_are_bit_identical(problem, n):
-    """Staging variants, the deferred top-level factorisation, the fused residual and the flag delivery
-    change how the iteration is scheduled, never what it computes."""
-    ref, _ = _fused_iterations(problem, n, VARIANTS[0])
-    assert all(r[0] == 0 for r in ref)
-    for opt in VARIANTS[1:]:
+@pytest.mark.parametrize("problem,n", [("flame1d", 50000), ("flame1d", 2048 * 3 + 5), ("flame1d", 1000000), ("perovskite", 8000)])
+def test_fused_iteration_variants_agree(problem, n):
+    """Staging variants, where the top level is factored, the fused residual and the flag delivery change
+    how the iteration is scheduled, never what it computes: bit-identical.  The cyclic-reduction top level
+    is different arithmetic on the same reduced system: it agrees with the LU top level to rounding."""
+    ref = {}
+    for opt, pcr in VARIANTS:
+        if n == 1000000 and len(opt) > 1:
+            continue
         got, _ = _fused_iterations(problem, n, opt)
-        for it, (a, g) in enumerate(zip(ref, got)):
-            assert a[0] == g[0] and a[1] == g[1], (opt, it, a[:2], g[:2])
-            assert a[2] == g[2], (opt, it, "dx differs")
-            assert a[3] == g[3], (opt, it, "xk differs")
+        assert all(r[0] == 0 for r in got), opt
+        if pcr not in ref:
+            ref[pcr] = got
+            continue
+        for it, (a, g) in enumerate(zip(ref[pcr], got)):
+            assert a[1] == g[1], (opt, it, a[1], g[1])
+            assert a[2].tobytes() == g[2].tobytes(), (opt, it, "dx differs")
+            assert a[3].tobytes() == g[3].tobytes(), (opt, it, "xk differs")
+    for it, (a, g) in enumerate(zip(ref[True], ref[False])):
+        scale = np.max(np.abs(g[2]))
+        assert np.max(np.abs(a[2] - g[2])) <= 1e-10 * scale, (it, np.max(np.abs(a[2] - g[2])), scale)
+        assert a[1] == g[1]
 
 
 def test_fused_residual_keep_b_matches_residual_kernel():
@@ -244,3 +257,24 @@ def test_chain_trace_layout():
     assert tiles == 5
     assert np.all(tr[0, :, 0] > 0) and np.all(tr[0, :, 4] >= tr[0, :, 0])      # factor tiles: start <= done
     assert np.all(tr[2, :, 0] >= tr[0, :, 4].min()) and np.all(tr[4, :, 3] >= tr[2, :, 4].max())  # factor -> forward -> backward
+
+
+def test_iterations_resident_equals_single_iterations():
+    n = 40000
+    x = P.flame1d_state(n)
+    dt4 = np.array([1e-3, 0.0, 0.0, 0.0])
+    res = []
+    for batched in (False, True):
+        for spin in (1, 0):
+            c = B.Context(n)
+            c.set_option("spin_flags", spin)
+            c.set_state(x); c.set_mass(P.identity_mass(n)); c.set_jacobian(P.flame1d_jacobian(x))
+            c.residual(P.flame1d_rhs(x), 1, dt4)
+            if batched:
+                rc, flags = c.iterations_resident(4, 1, 1, dt4, 1e-6, 1e-6)
+            else:
+                for _ in range(4):
+                    rc, flags = c.iteration_resident(1, 1, dt4, 1e-6, 1e-6)
+            res.append((rc, flags, c.get_vector("xk").tobytes(), c.get_vector("dx").tobytes()))
+            c.close()
+    assert all(r == res[0] for r in res[1:])
