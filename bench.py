@@ -534,7 +534,7 @@ def run_b200_arm(args):
     # DRAM traffic of the refactorisation kernels from the committed `ncu --set full` capture of this
     # very command (profiles/: dram__bytes_read.sum + dram__bytes_write.sum, MB per launch), C3 only
     traffic = None
-    cap = os.path.join(ROOT, "profiles", "r01_v9_ncu_full_chain_kernels.csv")
+    cap = os.path.join(ROOT, "profiles", "r01_v10_ncu_full_chain_kernels.csv")
     if args.workload == "flame1d" and n == 1_000_000 and os.path.exists(cap):
         import csv
         rows = list(csv.reader(open(cap)))
