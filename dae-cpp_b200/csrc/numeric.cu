@@ -314,17 +314,112 @@ __global__ void __launch_bounds__(128) k_bf_trsm(FrontTables T, int32_t begin, i
         if (k < nb) *fr_at(F, k0 + k, j) = x[k];
 }
 
+// LU of the NB x NB diagonal block held in shared memory (identity padded), by all nt threads of the CTA:
+// the same operations in the same order as k_bf_diag, so every CTA that repeats it gets the same bits
+__device__ __forceinline__ void bf_block_lu(double (*A)[NB + 1], int nb, int t, int nt, double pivot_tol, int32_t *flags)
+{
+    for (int k = 0; k < nb; ++k)
+    {
+        const double d = A[k][k];
+        if (flags && t == 0 && (!(fabs(d) > pivot_tol) || isinf(d))) atomicOr(&flags[3], 1);
+        if (t < NB && t > k) A[t][k] = A[t][k] / d;
+        __syncthreads();
+        for (int e = t; e < NB * NB; e += nt)
+        {
+            const int i = e % NB, j = e / NB;
+            if (i > k && j > k) A[i][j] -= A[i][k] * A[k][j];
+        }
+        __syncthreads();
+    }
+}
+__device__ __forceinline__ void bf_load_diag(double (*A)[NB + 1], const FrontRef &F, int32_t k0, int nb, int t, int nt)
+{
+    for (int e = t; e < NB * NB; e += nt)
+    {
+        const int i = e % NB, j = e / NB; // column j contiguous in i
+        A[i][j] = (i < nb && j < nb) ? F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] : (i == j ? 1.0 : 0.0);
+    }
+    __syncthreads();
+}
+
+// panel in ONE launch: every CTA factors the (still unfactored) diagonal block for itself in shared memory
+// -- 2 us of redundant work instead of a dependent launch -- and then solves its 128 rows of L21
+// (even blockIdx.x) or its 128 columns of U12 (odd blockIdx.x) out of registers.  The factored
+// diagonal block is written back by the trailing update's first CTA (k_bf_gemm), when no CTA of this
+// launch can still be reading the unfactored one.
+__global__ void __launch_bounds__(128) k_bf_panel(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
+                                                  double *__restrict__ CB)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.y];
+    const FrontRef F = front_ref(T, f, LU, CB);
+    if (k0 >= F.s) return;
+    const int32_t k1 = min(k0 + NB, F.s), nb = k1 - k0;
+    const bool rows = (blockIdx.x & 1) == 0;
+    const int32_t blk = blockIdx.x >> 1;
+    if ((int64_t)blk * 128 + k1 >= F.ld) return;
+    __shared__ double A[NB][NB + 1];
+    const int t = threadIdx.x;
+    bf_load_diag(A, F, k0, nb, t, 128);
+    bf_block_lu(A, nb, t, 128, 0.0, nullptr);
+    const int32_t q = k1 + blk * 128 + t;
+    if (q >= F.ld) return;
+    double x[NB];
+    if (rows)
+    {   // L21 = A21 * U11^-1
+#pragma unroll
+        for (int k = 0; k < NB; ++k) x[k] = k < nb ? F.Lp[(int64_t)(k0 + k) * F.ld + q] : 0.0;
+#pragma unroll
+        for (int k = 0; k < NB; ++k)
+        {
+            double acc = x[k];
+#pragma unroll
+            for (int kk = 0; kk < k; ++kk) acc -= x[kk] * A[kk][k];
+            x[k] = acc / A[k][k];
+        }
+#pragma unroll
+        for (int k = 0; k < NB; ++k)
+            if (k < nb) F.Lp[(int64_t)(k0 + k) * F.ld + q] = x[k];
+    }
+    else
+    {   // U12 = L11^-1 * A12
+#pragma unroll
+        for (int k = 0; k < NB; ++k) x[k] = k < nb ? *fr_at(F, k0 + k, q) : 0.0;
+#pragma unroll
+        for (int k = 1; k < NB; ++k)
+        {
+            double acc = x[k];
+#pragma unroll
+            for (int kk = 0; kk < k; ++kk) acc -= A[k][kk] * x[kk];
+            x[k] = acc;
+        }
+#pragma unroll
+        for (int k = 0; k < NB; ++k)
+            if (k < nb) *fr_at(F, k0 + k, q) = x[k];
+    }
+}
+
 __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
-                                                 double *__restrict__ CB)
+                                                 double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags)
 {
     const int32_t f = T.level_sn[begin + blockIdx.z];
     const FrontRef F = front_ref(T, f, LU, CB);
     if (k0 >= F.s) return;
     const int32_t k1 = min(k0 + NB, F.s), nb = k1 - k0;
     const int32_t i0 = k1 + blockIdx.x * 64, j0 = k1 + blockIdx.y * 64;
+    const int t = threadIdx.x;
+    if (flags && blockIdx.x == 0 && blockIdx.y == 0)
+    {   // the panel launch is complete: nobody reads the unfactored diagonal block any more
+        __shared__ double Dg[NB][NB + 1];
+        bf_load_diag(Dg, F, k0, nb, t, 256);
+        bf_block_lu(Dg, nb, t, 256, pivot_tol, flags);
+        for (int e = t; e < NB * NB; e += 256)
+        {
+            const int i = e % NB, j = e / NB;
+            if (i < nb && j < nb) F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] = Dg[i][j];
+        }
+    }
     if (i0 >= F.ld || j0 >= F.ld) return;
     __shared__ double A[NB][64 + 1], Bm[NB][64 + 1];
-    const int t = threadIdx.x;
     for (int e = t; e < NB * 64; e += 256)
     {
         const int k = e / 64, q = e % 64;
@@ -852,14 +947,23 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
             for (int32_t k0 = 0; k0 < max_s; k0 += NB)
             {
                 const int32_t rest = max_ld - std::min(k0 + NB, max_s);
-                k_bf_diag<<<L.count, NB * NB, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
-                c->kernels += 1;
-                if (rest <= 0) continue;
-                k_bf_rows<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
-                k_bf_trsm<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
+                if (rest <= 0 || !c->bf_fused_panel)
+                {
+                    k_bf_diag<<<L.count, NB * NB, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                    c->kernels += 1;
+                    if (rest <= 0) continue;
+                    k_bf_rows<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
+                    k_bf_trsm<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
+                    const int tiles = (rest + 63) / 64;
+                    k_bf_gemm<<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr);
+                    c->kernels += 3;
+                    continue;
+                }
+                // two launches per block column: panel (diagonal block factored redundantly by every CTA), trailing update
+                k_bf_panel<<<dim3(2 * ((rest + 127) / 128), L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                 const int tiles = (rest + 63) / 64;
-                k_bf_gemm<<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
-                c->kernels += 3;
+                k_bf_gemm<<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                c->kernels += 2;
             }
         }
         else

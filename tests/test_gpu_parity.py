@@ -366,3 +366,24 @@ def test_residual_diagonal_mass_odd_sizes(n):
     O.port.oracle_residual(n, *O.convert(O.port, n, M), d, f, b_ref)
     assert c.get_vector("b").tobytes() == b_ref.tobytes()
     c.close()
+
+
+def test_big_front_fused_panel_is_bit_identical():
+    """One-launch panel (every CTA factors the diagonal block for itself) vs diag / rows / trsm launches."""
+    m = 160
+    n = m * m
+    u = P.grid2d_state(m)
+    J = P.grid2d_jacobian(u, m)
+    M = P.identity_mass(n)
+    b = np.full(n, 1.24)
+    out = []
+    for fused in (1, 0):
+        c = B.Context(n)
+        c.set_option("chain", 0); c.set_option("bf_fused_panel", fused)
+        c.set_mass(M); c.set_jacobian(J)
+        c.refactor(50.0)
+        c.set_rhs(b)
+        out.append(c.solve().tobytes())
+        assert c.stat("max_front") >= 96
+        c.close()
+    assert out[0] == out[1]
