@@ -134,7 +134,7 @@ static void recycle(daecpp_b200_ctx *c)
         c->sopt.max_super != fresh.sopt.max_super)
         c->have_symbolic = false;
     c->chain_enabled = fresh.chain_enabled; c->chain_min_n = fresh.chain_min_n; c->chain_max_b = fresh.chain_max_b;
-    c->chain_affine = fresh.chain_affine; c->chain_packed = fresh.chain_packed; c->lean_flags = fresh.lean_flags; c->spin_flags = fresh.spin_flags; c->publish_flags = false; c->flags_clean = false; c->chain_fuse_residual = fresh.chain_fuse_residual; c->keep_b = fresh.keep_b; c->fuse_residual_now = false; c->chain_prefetch = fresh.chain_prefetch; c->chain_fuse_top = fresh.chain_fuse_top; c->chain_defer_top = fresh.chain_defer_top; c->chain_top_pcr = fresh.chain_top_pcr; c->chain_top_mode = 0; c->chain_may_defer = false; c->chain_top_pending = false; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
+    c->chain_affine = fresh.chain_affine; c->chain_packed = fresh.chain_packed; c->lean_flags = fresh.lean_flags; c->spin_flags = fresh.spin_flags; c->host_xk_direct = fresh.host_xk_direct; c->host_xk_direct_max_n = fresh.host_xk_direct_max_n; c->xk_host_target = nullptr; c->xk_direct_used = false; c->publish_flags = false; c->flags_clean = false; c->chain_fuse_residual = fresh.chain_fuse_residual; c->keep_b = fresh.keep_b; c->fuse_residual_now = false; c->chain_prefetch = fresh.chain_prefetch; c->chain_fuse_top = fresh.chain_fuse_top; c->chain_defer_top = fresh.chain_defer_top; c->chain_top_pcr = fresh.chain_top_pcr; c->chain_top_mode = 0; c->chain_may_defer = false; c->chain_top_pending = false; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
     c->refine_steps = 0; c->assemble_only = false; c->pinned_io = false; c->pivot_tol = 0.0;
     c->phase_timing = false; c->trace_units = false; c->blocked_lu = fresh.blocked_lu; c->blocked_lu_min_dim = fresh.blocked_lu_min_dim;
     c->n_symbolic = c->n_refactor = c->n_solve = c->n_cold = c->kernels = 0;
@@ -603,15 +603,32 @@ int daecpp_b200_iteration_host(daecpp_b200_ctx *c, const double *f_host, int32_t
         std::memcpy(c->h_stage, f_host, bytes);
         DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->f, c->h_stage, bytes, cudaMemcpyHostToDevice, st));
     }
-    if ((rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs))) return rc;
-    if (xk_host)
+    // small systems handed over in pinned memory: the backward kernel stores xk into the caller's buffer itself
+    c->xk_host_target = nullptr;
+    c->xk_direct_used = false;
+    if (xk_host && c->pinned_io && c->host_xk_direct && c->n <= c->host_xk_direct_max_n && !c->phase_timing)
+    {
+        if (c->xk_host_cached != xk_host)
+        {
+            void *dp = nullptr;
+            if (cudaHostGetDevicePointer(&dp, xk_host, 0) == cudaSuccess) { c->xk_host_cached = xk_host; c->xk_host_dev_cached = static_cast<double *>(dp); }
+            else { cudaGetLastError(); c->xk_host_cached = nullptr; c->xk_host_dev_cached = nullptr; }
+        }
+        if (c->xk_host_cached == xk_host) c->xk_host_target = c->xk_host_dev_cached;
+    }
+    rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs);
+    c->xk_host_target = nullptr;
+    if (rc) return rc;
+    const bool direct = c->xk_direct_used && c->flags_published;
+    if (xk_host && !direct)
     {
         if (c->pinned_io)
             DAECPP_CUDA_TRY(c, cudaMemcpyAsync(xk_host, c->xk, bytes, cudaMemcpyDeviceToHost, st));
         else
             DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_stage, c->xk, bytes, cudaMemcpyDeviceToHost, st));
     }
-    DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
+    if (direct) { if ((rc = wait_iteration(c))) return rc; }
+    else DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
     if (xk_host && !c->pinned_io) std::memcpy(xk_host, c->h_stage, bytes);
     std::memcpy(c->h_scalars + 2, w, sizeof(w));
     c->h_flags[6] = order;
@@ -816,6 +833,8 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "chain") { c->chain_enabled = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "lean_flags") c->lean_flags = value != 0.0;
     else if (k == "spin_flags") c->spin_flags = value != 0.0;
+    else if (k == "host_xk_direct") c->host_xk_direct = value != 0.0;
+    else if (k == "host_xk_direct_max_n") c->host_xk_direct_max_n = (int64_t)value;
     else if (k == "chain_fuse_residual") c->chain_fuse_residual = value != 0.0;
     else if (k == "keep_b") c->keep_b = value != 0.0;
     else if (k == "chain_prefetch") c->chain_prefetch = (int)value;

@@ -63,6 +63,7 @@ struct ChainArgs
     const double *mdiag, *fvec;
     double *b_out; // optional copy of b to HBM
     int32_t seq;
+    double *xk_host;     // mapped pinned copy of xk for the host (small systems), written with the fused update
     int32_t *host_flags; // mapped host mirror of dflags[2..4], written by the CTA that finishes the iteration last
     // ensemble: member = blockIdx.y, strides in elements
     const double *alpha_arr;
@@ -89,10 +90,11 @@ __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.lau
 
 // true in exactly one CTA per member: the one whose tile finished last (its view of the other
 // tiles' results is complete after the fence)
-__device__ __forceinline__ bool last_tile_done(uint32_t *counter, int ntiles, int t)
+__device__ __forceinline__ bool last_tile_done(uint32_t *counter, int ntiles, int t, bool sys = false)
 {
     __shared__ int s_last;
-    __threadfence();
+    if (sys) __threadfence_system(); // this CTA stored to mapped host memory
+    else __threadfence();
     __syncthreads();
     if (t == 0)
     {
@@ -324,12 +326,14 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
                     if (e > a.max_err_abs || isnan(v[u])) flag |= DAECPP_B200_DIVERGED;
                     if (ax > 1e-14 && __ddiv_rn(e, ax) > a.rtol) flag |= DAECPP_B200_NOT_CONVERGED;
                     if (e > a.atol) flag |= DAECPP_B200_NOT_CONVERGED;
-                    xk[o[u]] = __dadd_rn(xo[u], v[u]);
+                    const double xn = __dadd_rn(xo[u], v[u]);
+                    xk[o[u]] = xn;
+                    if (a.xk_host) a.xk_host[o[u]] = xn;
                 }
             }
         }
         if (flag) atomicOr(&a.dflags[2], flag);
-        if (a.host_flags && last_tile_done(a.counter + 4, lv.ntiles, t))
+        if (a.host_flags && last_tile_done(a.counter + 4, lv.ntiles, t, a.xk_host != nullptr))
         {
             if (t == 0)
             {   // published, reset for the next iteration, then the sequence number the host may spin on
@@ -921,6 +925,7 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         }
         a.host_flags = c->publish_flags ? c->h_flags_dev + 2 : nullptr;
         if (a.host_flags) { c->flags_published = true; a.seq = (int32_t)++c->flag_seq; }
+        if (a.host_flags && fuse_update && c->xk_host_target) { a.xk_host = c->xk_host_target; c->xk_direct_used = true; }
     };
     if ((c->chain_top_pending || c->chain_top_mode == 1) && !fuse)
     {   // (options changed in between) factor the top level on its own

@@ -115,6 +115,13 @@ struct daecpp_b200_ctx
     int32_t *h_flags = nullptr; // pinned mirror (mapped: the last kernel of a fused chain iteration writes it directly)
     int32_t *h_flags_dev = nullptr;
     bool lean_flags = true, publish_flags = false, flags_published = false;
+    // small systems: the fused update also stores xk straight into the caller's pinned buffer (mapped), so a host
+    // iteration needs neither a device-to-host copy node nor a stream synchronisation
+    bool host_xk_direct = true;
+    int64_t host_xk_direct_max_n = 131072;
+    const double *xk_host_cached = nullptr;
+    double *xk_host_dev_cached = nullptr, *xk_host_target = nullptr;
+    bool xk_direct_used = false;
     uint32_t flag_seq = 0;             // sequence number written behind the published flags (h_flags[5])
     bool spin_flags = true;            // resident iteration: spin on that word instead of cudaStreamSynchronize
     bool flags_clean = false;          // d_flags[2..4] are zero (the publishing CTA of a fused chain iteration resets them)

@@ -278,3 +278,33 @@ def test_iterations_resident_equals_single_iterations():
             res.append((rc, flags, c.get_vector("xk").tobytes(), c.get_vector("dx").tobytes()))
             c.close()
     assert all(r == res[0] for r in res[1:])
+
+
+@pytest.mark.parametrize("problem,n", [("flame1d", 30001), ("perovskite", 8000)])
+def test_iteration_host_direct_xk_store(problem, n):
+    """Small systems: xk reaches the caller's pinned buffer by stores of the backward kernel (no copy node,
+    no stream synchronisation) -- same bits as the device vector and as the copy path."""
+    if problem == "flame1d":
+        x = P.flame1d_state(n); M = P.identity_mass(n); J = P.flame1d_jacobian(x); f = P.flame1d_rhs(x)
+    else:
+        N = n // 2
+        x = P.perovskite_state(N); M = P.perovskite_mass(N); J = P.perovskite_jacobian(x, N)
+        f = np.sin(np.arange(n) * 0.01) * 1e-3
+    lib = B.load()
+    dt4 = np.array([1e-3, 0.0, 0.0, 0.0])
+    res = []
+    for direct in (1, 0):
+        c = B.Context(n, 0, lib)
+        c.set_option("pinned_io", 1); c.set_option("host_xk_direct", direct)
+        pf = B.PinnedArray(lib, (n,), np.float64); px = B.PinnedArray(lib, (n,), np.float64)
+        pf.array[:] = f; px.array[:] = -7.0
+        c.set_state(x); c.set_mass(M); c.set_jacobian(J)
+        hist = []
+        for it in range(3):
+            rc, flags, alpha = c.iteration_host(pf.array, 0 if it == 1 else 1, 1, dt4, 1e-6, 1e-6, px.array)
+            assert rc == 0
+            assert px.array.tobytes() == c.get_vector("xk").tobytes()
+            hist.append((flags, alpha, px.array.tobytes()))
+        res.append(hist)
+        c.close(); pf.free(); px.free()
+    assert res[0] == res[1]
