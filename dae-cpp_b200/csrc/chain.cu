@@ -463,22 +463,43 @@ __device__ __noinline__ void pcr_top(int R, const double *__restrict__ red, cons
     using D = Dim<B>;
     constexpr int BB = D::BB, PR = Pcr<B>::ROWS, NR = Pcr<B>::NR, NT = D::T;
     double *sA = W, *sD = W + BB * PR, *sC = W + 2 * BB * PR, *sr = W + 3 * BB * PR;
-    for (int i = t; i < R; i += NT)
-    {
-        const bool nx = i + 1 < R;
+    {   // all global loads of the thread first (one L2 round trip), then the stores
+        double va[NR][BB], vd[NR][BB], vd2[NR][BB], vc[NR][BB], vy[NR][B], vt[NR][B];
 #pragma unroll
-        for (int e = 0; e < BB; ++e)
+        for (int k = 0; k < NR; ++k)
         {
-            sA[e * PR + i] = red[((size_t)0 * R + i) * BB + e];
-            sD[e * PR + i] = red[((size_t)1 * R + i) * BB + e] - (nx ? red[((size_t)2 * R + i + 1) * BB + e] : 0.0);
-            sC[e * PR + i] = nx ? red[((size_t)3 * R + i + 1) * BB + e] : 0.0;
+            const int i = t + k * NT;
+            const bool in = i < R, nx = i + 1 < R;
+#pragma unroll
+            for (int e = 0; e < BB; ++e)
+            {
+                va[k][e] = in ? red[((size_t)0 * R + i) * BB + e] : 0.0;
+                vd[k][e] = in ? red[((size_t)1 * R + i) * BB + e] : 0.0;
+                vd2[k][e] = nx ? red[((size_t)2 * R + i + 1) * BB + e] : 0.0;
+                vc[k][e] = nx ? red[((size_t)3 * R + i + 1) * BB + e] : 0.0;
+            }
+#pragma unroll
+            for (int q = 0; q < B; ++q)
+            {
+                vy[k][q] = in ? rv[((size_t)0 * R + i) * B + q] : 0.0;
+                vt[k][q] = nx ? rv[((size_t)1 * R + i + 1) * B + q] : 0.0;
+            }
         }
 #pragma unroll
-        for (int q = 0; q < B; ++q) sr[q * PR + i] = rv[((size_t)0 * R + i) * B + q] - (nx ? rv[((size_t)1 * R + i + 1) * B + q] : 0.0);
+        for (int k = 0; k < NR; ++k)
+        {
+            const int i = t + k * NT;
+            if (i >= R) continue;
+#pragma unroll
+            for (int e = 0; e < BB; ++e) { sA[e * PR + i] = va[k][e]; sD[e * PR + i] = vd[k][e] - vd2[k][e]; sC[e * PR + i] = vc[k][e]; }
+#pragma unroll
+            for (int q = 0; q < B; ++q) sr[q * PR + i] = vy[k][q] - vt[k][q];
+        }
     }
     __syncthreads();
     mark(1);
     int fail = 0;
+#pragma unroll 1 // one copy of the step: the code runs once per launch in one CTA, every copy is an instruction-cache miss
     for (int s = 1; s < R; s <<= 1)
     {
         if (s == 8) mark(2);
