@@ -211,40 +211,158 @@ __global__ void __launch_bounds__(256) k_bf_extend(FrontTables T, int32_t begin,
     for (int32_t bc = blockIdx.x * NW + wid; bc < rc; bc += gridDim.x * NW)
     {
         const int32_t rb = rel[bc];
-        for (int32_t a = lane; a < rc; a += 32)
+        constexpr int U = 4; // independent entries per lane: all loads of a batch first, then the stores
+        for (int32_t a0 = 0; a0 < rc; a0 += 32 * U)
         {
-            const int32_t ra = rel[a];
-            const double v = Cc[(int64_t)bc * rc + a];
-            if (rb < s) F.Lp[(int64_t)rb * ld + ra] += v;
-            else if (ra < s) F.Ut[(int64_t)ra * r + (rb - s)] += v;
-            else F.C[(int64_t)(rb - s) * r + (ra - s)] += v;
+            double *dst[U];
+            double v[U], old[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+            {
+                const int32_t a = a0 + u * 32 + lane;
+                dst[u] = nullptr;
+                if (a < rc)
+                {
+                    const int32_t ra = rel[a];
+                    v[u] = Cc[(int64_t)bc * rc + a];
+                    dst[u] = rb < s ? F.Lp + (int64_t)rb * ld + ra : ra < s ? F.Ut + (int64_t)ra * r + (rb - s) : F.C + (int64_t)(rb - s) * r + (ra - s);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (dst[u]) old[u] = *dst[u];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (dst[u]) *dst[u] = old[u] + v[u]; // distinct (a, bc) of one child hit distinct entries
         }
     }
 }
 
-// panel, step 1: LU of the NB x NB diagonal block in shared memory (one CTA of NB x NB threads per front)
-__global__ void __launch_bounds__(NB * NB) k_bf_diag(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
-                                                     double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags)
+// LU of the NB x NB diagonal block held in shared memory (identity padded).  The block is a dependent
+// chain of NB pivots, so it is done by ONE warp out of registers -- lane i holds row i, the pivot row is
+// broadcast by shuffles, no barrier and no shared-memory round trip per pivot -- while the other warps of
+// the CTA wait.  The pivot loop is NOT unrolled: the row is shifted left by one register per pivot, so one
+// loop body of ~150 instructions serves all NB pivots (straight-line code that runs once per launch is
+// bound by instruction fetch, not by arithmetic).  Every element sees l = a_ik * (1 / d) and a_ij -= l * a_kj in
+// pivot order, whoever runs it, so every CTA that repeats the factorisation gets the same bits.
+// Rinv[k] = 1 / U(k,k) for the row solves.
+__device__ __forceinline__ void bf_block_lu(double (*A)[NB + 1], double *Rinv, int nb, int t, double pivot_tol, int32_t *flags)
+{
+    if (t < NB)
+    {
+        double a[NB];
+#pragma unroll
+        for (int j = 0; j < NB; ++j) a[j] = A[t][j];
+        // The dependent chain per pivot is: multiplier -> update of the next pivot -> broadcast -> reciprocal.
+        // The next pivot is therefore updated and its reciprocal started BEFORE the other NB - 2 updates of the
+        // step, which then hide the reciprocal's latency (multipliers are a_ik * (1 / d)).
+        double d = __shfl_sync(0xffffffffu, a[0], 0);
+        bool bad = !(fabs(d) > pivot_tol) || isinf(d);
+        double r = 1.0 / d;
+#pragma unroll 1
+        for (int k = 0; k < nb; ++k)
+        {
+            const bool below = t > k;
+            const double l = below ? a[0] * r : a[0];
+            A[t][k] = l; // L(t,k) below the diagonal; on and above it U(t,k), final since pivot t-1
+            const double u1 = __shfl_sync(0xffffffffu, a[1], k);
+            const double a1 = below ? a[1] - l * u1 : a[1];
+            d = __shfl_sync(0xffffffffu, a1, (k + 1) & (NB - 1));
+            if (k + 1 < nb) bad = bad || !(fabs(d) > pivot_tol) || isinf(d);
+            r = 1.0 / d;
+#pragma unroll
+            for (int j = 1; j < NB - 1; ++j)
+            {
+                const double u = __shfl_sync(0xffffffffu, a[j + 1], k);
+                a[j] = below ? a[j + 1] - l * u : a[j + 1];
+            }
+            a[0] = a1;
+            a[NB - 1] = 0.0;
+        }
+        if (flags && t == 0 && bad) atomicOr(&flags[3], 1);
+        if (Rinv) Rinv[t] = 1.0 / A[t][t];
+    }
+    __syncthreads();
+}
+// Panel solves against the factored diagonal block A, one thread per row of L21 = A21 * U11^-1 (rows) or per
+// column of U12 = L11^-1 * A12 (!rows).  P[k][m] = U(k, m) resp. L(m, k) for m < NB, zero beyond: the thread's
+// NB entries are shifted left by one register per pivot, the finished entry is stored at once, and the
+// zero padding makes every step the same NB - 1 updates -- a rolled loop again.  q = row / column in the front.
+__device__ __forceinline__ void bf_fill_pad(double (*P)[2 * NB], const double (*A)[NB + 1], bool rows, int t, int nt)
+{
+    for (int e = t; e < NB * 2 * NB; e += nt)
+    {
+        const int k = e / (2 * NB), m = e % (2 * NB);
+        P[k][m] = m < NB ? (rows ? A[k][m] : A[m][k]) : 0.0;
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ void bf_panel_solve(const FrontRef &F, const double (*P)[2 * NB], const double *Rinv, bool rows,
+                                               int32_t k0, int nb, int32_t q)
+{
+    double x[NB];
+    if (rows)
+    {
+#pragma unroll
+        for (int k = 0; k < NB; ++k) x[k] = k < nb ? F.Lp[(int64_t)(k0 + k) * F.ld + q] : 0.0;
+#pragma unroll 1
+        for (int k = 0; k < nb; ++k)
+        {
+            const double xk = x[0] * Rinv[k];
+            F.Lp[(int64_t)(k0 + k) * F.ld + q] = xk;
+            const double *u = &P[k][k + 1];
+#pragma unroll
+            for (int j = 0; j < NB - 1; ++j) x[j] = x[j + 1] - xk * u[j];
+            x[NB - 1] = 0.0;
+        }
+    }
+    else
+    {
+#pragma unroll
+        for (int k = 0; k < NB; ++k) x[k] = k < nb ? *fr_at(F, k0 + k, q) : 0.0;
+#pragma unroll 1
+        for (int k = 0; k < nb; ++k)
+        {
+            const double xk = x[0];
+            *fr_at(F, k0 + k, q) = xk;
+            const double *l = &P[k][k + 1];
+#pragma unroll
+            for (int j = 0; j < NB - 1; ++j) x[j] = x[j + 1] - l[j] * xk;
+            x[NB - 1] = 0.0;
+        }
+    }
+}
+__device__ __forceinline__ void bf_load_diag(double (*A)[NB + 1], const FrontRef &F, int32_t k0, int nb, int t, int nt)
+{
+    for (int e = t; e < NB * NB; e += nt)
+    {
+        const int i = e % NB, j = e / NB; // column j contiguous in i
+        A[i][j] = (i < nb && j < nb) ? F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] : (i == j ? 1.0 : 0.0);
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ void bf_store_diag(const double (*A)[NB + 1], const FrontRef &F, int32_t k0, int nb, int t, int nt)
+{
+    for (int e = t; e < NB * NB; e += nt)
+    {
+        const int i = e % NB, j = e / NB;
+        if (i < nb && j < nb) F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] = A[i][j];
+    }
+}
+
+// panel, step 1 (separate-launch variant): LU of the NB x NB diagonal block, one CTA per front
+__global__ void __launch_bounds__(128) k_bf_diag(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
+                                                 double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags)
 {
     const int32_t f = T.level_sn[begin + blockIdx.x];
     const FrontRef F = front_ref(T, f, LU, CB);
     if (k0 >= F.s) return;
     const int32_t nb = min(k0 + NB, F.s) - k0;
     __shared__ double A[NB][NB + 1];
-    const int i = threadIdx.x % NB, j = threadIdx.x / NB; // A[i][j] = F(k0+i, k0+j), column j contiguous in i
-    A[i][j] = (i < nb && j < nb) ? F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] : (i == j ? 1.0 : 0.0);
-    __syncthreads();
-    for (int k = 0; k < nb; ++k)
-    {
-        const double d = A[k][k];
-        if (threadIdx.x == 0 && (!(fabs(d) > pivot_tol) || isinf(d))) atomicOr(&flags[3], 1);
-        __syncthreads();
-        if (j == k && i > k) A[i][k] = A[i][k] / d;
-        __syncthreads();
-        if (i > k && j > k) A[i][j] -= A[i][k] * A[k][j];
-        __syncthreads();
-    }
-    if (i < nb && j < nb) F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] = A[i][j];
+    const int t = threadIdx.x;
+    bf_load_diag(A, F, k0, nb, t, 128);
+    bf_block_lu(A, nullptr, nb, t, pivot_tol, flags);
+    bf_store_diag(A, F, k0, nb, t, 128);
 }
 
 // panel, step 2 (rows below the diagonal block): one thread per row, L21 = A21 * U11^-1 in registers
@@ -256,31 +374,18 @@ __global__ void __launch_bounds__(128) k_bf_rows(FrontTables T, int32_t begin, i
     if (k0 >= F.s) return;
     const int32_t k1 = min(k0 + NB, F.s), nb = k1 - k0;
     if ((int64_t)blockIdx.x * blockDim.x + k1 >= F.ld) return;
-    __shared__ double U11[NB][NB + 1]; // U11[kk][k] = U(k0+kk, k0+k), kk <= k
-    for (int e = threadIdx.x; e < NB * NB; e += blockDim.x)
-    {
-        const int kk = e % NB, k = e / NB;
-        U11[kk][k] = (k < nb && kk <= k) ? F.Lp[(int64_t)(k0 + k) * F.ld + (k0 + kk)] : (kk == k ? 1.0 : 0.0);
-    }
-    __syncthreads();
-    const int32_t i = k1 + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= F.ld) return;
-    double x[NB];
-#pragma unroll
-    for (int k = 0; k < NB; ++k) x[k] = k < nb ? F.Lp[(int64_t)(k0 + k) * F.ld + i] : 0.0;
-#pragma unroll
-    for (int k = 0; k < NB; ++k)
-    {
-        double acc = x[k];
-#pragma unroll
-        for (int kk = 0; kk < k; ++kk) acc -= x[kk] * U11[kk][k];
-        x[k] = acc / U11[k][k];
-    }
-#pragma unroll
-    for (int k = 0; k < NB; ++k)
-        if (k < nb) F.Lp[(int64_t)(k0 + k) * F.ld + i] = x[k];
+    __shared__ double A[NB][NB + 1];
+    __shared__ double Rinv[NB];
+    __shared__ double P[NB][2 * NB];
+    const int t = threadIdx.x;
+    bf_load_diag(A, F, k0, nb, t, 128); // factored already (k_bf_diag)
+    if (t < NB) Rinv[t] = 1.0 / A[t][t];
+    bf_fill_pad(P, A, true, t, 128);
+    const int32_t i = k1 + blockIdx.x * blockDim.x + t;
+    if (i < F.ld) bf_panel_solve(F, P, Rinv, true, k0, nb, i);
 }
 
+// panel, step 3 (columns right of the diagonal block): one thread per column, U12 = L11^-1 * A12
 __global__ void __launch_bounds__(128) k_bf_trsm(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
                                                  double *__restrict__ CB)
 {
@@ -289,57 +394,13 @@ __global__ void __launch_bounds__(128) k_bf_trsm(FrontTables T, int32_t begin, i
     if (k0 >= F.s) return;
     const int32_t k1 = min(k0 + NB, F.s), nb = k1 - k0;
     if ((int64_t)blockIdx.x * blockDim.x + k1 >= F.ld) return;
-    __shared__ double L11[NB][NB + 1];
-    for (int e = threadIdx.x; e < NB * NB; e += blockDim.x)
-    {
-        const int kk = e / NB, k = e % NB; // L11[k][kk] = multiplier of row k0+k, column k0+kk
-        L11[k][kk] = (k < nb && kk < k) ? F.Lp[(int64_t)(k0 + kk) * F.ld + (k0 + k)] : 0.0;
-    }
-    __syncthreads();
-    const int32_t j = k1 + blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= F.ld) return;
-    double x[NB];
-#pragma unroll
-    for (int k = 0; k < NB; ++k) x[k] = k < nb ? *fr_at(F, k0 + k, j) : 0.0;
-#pragma unroll
-    for (int k = 1; k < NB; ++k)
-    {
-        double acc = x[k];
-#pragma unroll
-        for (int kk = 0; kk < k; ++kk) acc -= L11[k][kk] * x[kk];
-        x[k] = acc;
-    }
-#pragma unroll
-    for (int k = 0; k < NB; ++k)
-        if (k < nb) *fr_at(F, k0 + k, j) = x[k];
-}
-
-// LU of the NB x NB diagonal block held in shared memory (identity padded), by all nt threads of the CTA:
-// the same operations in the same order as k_bf_diag, so every CTA that repeats it gets the same bits
-__device__ __forceinline__ void bf_block_lu(double (*A)[NB + 1], int nb, int t, int nt, double pivot_tol, int32_t *flags)
-{
-    for (int k = 0; k < nb; ++k)
-    {
-        const double d = A[k][k];
-        if (flags && t == 0 && (!(fabs(d) > pivot_tol) || isinf(d))) atomicOr(&flags[3], 1);
-        if (t < NB && t > k) A[t][k] = A[t][k] / d;
-        __syncthreads();
-        for (int e = t; e < NB * NB; e += nt)
-        {
-            const int i = e % NB, j = e / NB;
-            if (i > k && j > k) A[i][j] -= A[i][k] * A[k][j];
-        }
-        __syncthreads();
-    }
-}
-__device__ __forceinline__ void bf_load_diag(double (*A)[NB + 1], const FrontRef &F, int32_t k0, int nb, int t, int nt)
-{
-    for (int e = t; e < NB * NB; e += nt)
-    {
-        const int i = e % NB, j = e / NB; // column j contiguous in i
-        A[i][j] = (i < nb && j < nb) ? F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] : (i == j ? 1.0 : 0.0);
-    }
-    __syncthreads();
+    __shared__ double A[NB][NB + 1];
+    __shared__ double P[NB][2 * NB];
+    const int t = threadIdx.x;
+    bf_load_diag(A, F, k0, nb, t, 128);
+    bf_fill_pad(P, A, false, t, 128);
+    const int32_t j = k1 + blockIdx.x * blockDim.x + t;
+    if (j < F.ld) bf_panel_solve(F, P, nullptr, false, k0, nb, j);
 }
 
 // panel in ONE launch: every CTA factors the (still unfactored) diagonal block for itself in shared memory
@@ -358,46 +419,38 @@ __global__ void __launch_bounds__(128) k_bf_panel(FrontTables T, int32_t begin, 
     const int32_t blk = blockIdx.x >> 1;
     if ((int64_t)blk * 128 + k1 >= F.ld) return;
     __shared__ double A[NB][NB + 1];
+    __shared__ double Rinv[NB];
+    __shared__ double P[NB][2 * NB];
     const int t = threadIdx.x;
-    bf_load_diag(A, F, k0, nb, t, 128);
-    bf_block_lu(A, nb, t, 128, 0.0, nullptr);
     const int32_t q = k1 + blk * 128 + t;
-    if (q >= F.ld) return;
-    double x[NB];
-    if (rows)
-    {   // L21 = A21 * U11^-1
-#pragma unroll
-        for (int k = 0; k < NB; ++k) x[k] = k < nb ? F.Lp[(int64_t)(k0 + k) * F.ld + q] : 0.0;
-#pragma unroll
-        for (int k = 0; k < NB; ++k)
+    // pull this thread's panel entries towards L2 while the diagonal block is being factored
+    if (q < F.ld)
+    {
+#pragma unroll 4
+        for (int k = 0; k < nb; ++k)
         {
-            double acc = x[k];
-#pragma unroll
-            for (int kk = 0; kk < k; ++kk) acc -= x[kk] * A[kk][k];
-            x[k] = acc / A[k][k];
+            const double *ptr = rows ? F.Lp + (int64_t)(k0 + k) * F.ld + q : fr_at(F, k0 + k, q);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
         }
-#pragma unroll
-        for (int k = 0; k < NB; ++k)
-            if (k < nb) F.Lp[(int64_t)(k0 + k) * F.ld + q] = x[k];
     }
-    else
-    {   // U12 = L11^-1 * A12
-#pragma unroll
-        for (int k = 0; k < NB; ++k) x[k] = k < nb ? *fr_at(F, k0 + k, q) : 0.0;
-#pragma unroll
-        for (int k = 1; k < NB; ++k)
-        {
-            double acc = x[k];
-#pragma unroll
-            for (int kk = 0; kk < k; ++kk) acc -= A[k][kk] * x[kk];
-            x[k] = acc;
-        }
-#pragma unroll
-        for (int k = 0; k < NB; ++k)
-            if (k < nb) *fr_at(F, k0 + k, q) = x[k];
-    }
+    bf_load_diag(A, F, k0, nb, t, 128);
+    bf_block_lu(A, Rinv, nb, t, 0.0, nullptr);
+    bf_fill_pad(P, A, rows, t, 128);
+    if (q < F.ld) bf_panel_solve(F, P, Rinv, rows, k0, nb, q);
 }
 
+// FP64 tensor-core step: D(8x8) += A(8x4) * B(4x8).  Lane l holds A(l/4, l%4), B(l%4, l/4), D(l/4, 2*(l%4) + {0,1}).
+__device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+// Trailing update F -= L[:, k0:k1) * U[k0:k1, :) in 64 x 64 tiles.  DMMA: the eight warps of the CTA hold
+// 16 x 32 sub-tiles as 2 x 4 accumulator fragments of mma.m8n8k4.f64 (DMMA), operands from shared memory
+// (row stride 68 doubles: the 4 k x 8 rows of a fragment load fall in 32 different banks per half warp).
+// !DMMA: 4 x 4 register blocking on the FP64 FMA pipe (kept for A/B runs, option bf_dmma = 0).
+template <bool DMMA>
 __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
                                                  double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags)
 {
@@ -407,19 +460,19 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
     const int32_t k1 = min(k0 + NB, F.s), nb = k1 - k0;
     const int32_t i0 = k1 + blockIdx.x * 64, j0 = k1 + blockIdx.y * 64;
     const int t = threadIdx.x;
-    if (flags && blockIdx.x == 0 && blockIdx.y == 0)
-    {   // the panel launch is complete: nobody reads the unfactored diagonal block any more
+    if (flags && blockIdx.x == gridDim.x - 1)
+    {   // one extra CTA per front (fused panel): the panel launch is complete, nobody reads the unfactored
+        // diagonal block any more, so it is factored once more and written back -- beside the tiles, not before one
+        if (blockIdx.y != 0) return;
         __shared__ double Dg[NB][NB + 1];
         bf_load_diag(Dg, F, k0, nb, t, 256);
-        bf_block_lu(Dg, nb, t, 256, pivot_tol, flags);
-        for (int e = t; e < NB * NB; e += 256)
-        {
-            const int i = e % NB, j = e / NB;
-            if (i < nb && j < nb) F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] = Dg[i][j];
-        }
+        bf_block_lu(Dg, nullptr, nb, t, pivot_tol, flags);
+        bf_store_diag(Dg, F, k0, nb, t, 256);
+        return;
     }
     if (i0 >= F.ld || j0 >= F.ld) return;
-    __shared__ double A[NB][64 + 1], Bm[NB][64 + 1];
+    constexpr int LDS = DMMA ? 68 : 65;
+    __shared__ double A[NB][LDS], Bm[NB][LDS];
     for (int e = t; e < NB * 64; e += 256)
     {
         const int k = e / 64, q = e % 64;
@@ -434,6 +487,44 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
         Bm[k][q] = (k < nb && j0 + q < F.ld) ? *fr_at(F, k0 + k, j0 + q) : 0.0;
     }
     __syncthreads();
+    if (DMMA)
+    {
+        const int w = t >> 5, lane = t & 31, g = lane >> 2, c = lane & 3;
+        const int wi = (w & 3) * 16, wj = (w >> 2) * 32;
+        double acc[2][4][2];
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+            for (int nj = 0; nj < 4; ++nj) acc[mi][nj][0] = acc[mi][nj][1] = 0.0;
+#pragma unroll
+        for (int kk = 0; kk < NB; kk += 4)
+        {
+            double av[2], bv[4];
+#pragma unroll
+            for (int mi = 0; mi < 2; ++mi) av[mi] = A[kk + c][wi + mi * 8 + g];
+#pragma unroll
+            for (int nj = 0; nj < 4; ++nj) bv[nj] = Bm[kk + c][wj + nj * 8 + g];
+#pragma unroll
+            for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                for (int nj = 0; nj < 4; ++nj) dmma884(acc[mi][nj][0], acc[mi][nj][1], av[mi], bv[nj]);
+        }
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+        {
+            const int32_t i = i0 + wi + mi * 8 + g;
+            if (i >= F.ld) continue;
+#pragma unroll
+            for (int nj = 0; nj < 4; ++nj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+                {
+                    const int32_t j = j0 + wj + nj * 8 + 2 * c + e;
+                    if (j < F.ld) *fr_at(F, i, j) -= acc[mi][nj][e];
+                }
+        }
+        return;
+    }
     const int ti = (t % 16) * 4, tj = (t / 16) * 4;
     double acc[4][4];
 #pragma unroll
@@ -942,27 +1033,29 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
             }
             k_bf_zero<<<dim3(64, L.count), 256, 0, st>>>(T, L.begin, c->CB.p);
             for (int32_t ord = 0; ord < max_children; ++ord)
-                k_bf_extend<<<dim3(64, L.count), 256, 0, st>>>(T, L.begin, ord, c->LU.p, c->CB.p);
+                k_bf_extend<<<dim3(std::max(1, std::min(256, (max_ld + 7) / 8)), L.count), 256, 0, st>>>(T, L.begin, ord, c->LU.p, c->CB.p);
             c->kernels += 1 + max_children;
             for (int32_t k0 = 0; k0 < max_s; k0 += NB)
             {
                 const int32_t rest = max_ld - std::min(k0 + NB, max_s);
                 if (rest <= 0 || !c->bf_fused_panel)
                 {
-                    k_bf_diag<<<L.count, NB * NB, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                    k_bf_diag<<<L.count, 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
                     c->kernels += 1;
                     if (rest <= 0) continue;
                     k_bf_rows<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                     k_bf_trsm<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                     const int tiles = (rest + 63) / 64;
-                    k_bf_gemm<<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr);
+                    if (c->bf_dmma) k_bf_gemm<true><<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr);
+                    else k_bf_gemm<false><<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr);
                     c->kernels += 3;
                     continue;
                 }
                 // two launches per block column: panel (diagonal block factored redundantly by every CTA), trailing update
                 k_bf_panel<<<dim3(2 * ((rest + 127) / 128), L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                 const int tiles = (rest + 63) / 64;
-                k_bf_gemm<<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                if (c->bf_dmma) k_bf_gemm<true><<<dim3(tiles + 1, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                else k_bf_gemm<false><<<dim3(tiles + 1, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
                 c->kernels += 2;
             }
         }
