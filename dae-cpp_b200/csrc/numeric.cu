@@ -238,49 +238,38 @@ __global__ void __launch_bounds__(256) k_bf_extend(FrontTables T, int32_t begin,
     }
 }
 
-// LU of the NB x NB diagonal block held in shared memory (identity padded).  The block is a dependent
-// chain of NB pivots, so it is done by ONE warp out of registers -- lane i holds row i, the pivot row is
-// broadcast by shuffles, no barrier and no shared-memory round trip per pivot -- while the other warps of
-// the CTA wait.  The pivot loop is NOT unrolled: the row is shifted left by one register per pivot, so one
-// loop body of ~150 instructions serves all NB pivots (straight-line code that runs once per launch is
-// bound by instruction fetch, not by arithmetic).  Every element sees l = a_ik * (1 / d) and a_ij -= l * a_kj in
-// pivot order, whoever runs it, so every CTA that repeats the factorisation gets the same bits.
-// Rinv[k] = 1 / U(k,k) for the row solves.
-__device__ __forceinline__ void bf_block_lu(double (*A)[NB + 1], double *Rinv, int nb, int t, double pivot_tol, int32_t *flags)
+// LU of the NB x NB diagonal block held in shared memory (identity padded), by all nt threads of the CTA.
+// The block is a dependent chain of NB pivots, so what matters is the latency of one pivot step, and a step
+// is kept to: read the pivot, reciprocal (every thread for itself), one fused update per element straight
+// from the UNSCALED pivot column (a_ij -= (a_ik * r) * a_kj), one barrier.  The multipliers are scaled once
+// at the end.  (Measured on B200: one warp holding the block in registers and broadcasting the pivot row by
+// shuffles needs ~1300 cycles per pivot, a full-precision division plus two barriers per pivot ~700.)
+// The operations per element and their order do not depend on nt, so every CTA that repeats the
+// factorisation gets the same bits.  Rinv[k] = 1 / U(k,k), also used by the row solves.
+__device__ __forceinline__ void bf_block_lu(double (*A)[NB + 1], double *Rinv, int nb, int t, int nt, double pivot_tol, int32_t *flags)
 {
-    if (t < NB)
-    {
-        double a[NB];
-#pragma unroll
-        for (int j = 0; j < NB; ++j) a[j] = A[t][j];
-        // The dependent chain per pivot is: multiplier -> update of the next pivot -> broadcast -> reciprocal.
-        // The next pivot is therefore updated and its reciprocal started BEFORE the other NB - 2 updates of the
-        // step, which then hide the reciprocal's latency (multipliers are a_ik * (1 / d)).
-        double d = __shfl_sync(0xffffffffu, a[0], 0);
-        bool bad = !(fabs(d) > pivot_tol) || isinf(d);
-        double r = 1.0 / d;
+    bool bad = false;
+    const int i = t % NB;
 #pragma unroll 1
-        for (int k = 0; k < nb; ++k)
+    for (int k = 0; k < nb; ++k)
+    {
+        const double d = A[k][k];
+        bad = bad || !(fabs(d) > pivot_tol) || isinf(d);
+        const double r = 1.0 / d;
+        if (i > k)
         {
-            const bool below = t > k;
-            const double l = below ? a[0] * r : a[0];
-            A[t][k] = l; // L(t,k) below the diagonal; on and above it U(t,k), final since pivot t-1
-            const double u1 = __shfl_sync(0xffffffffu, a[1], k);
-            const double a1 = below ? a[1] - l * u1 : a[1];
-            d = __shfl_sync(0xffffffffu, a1, (k + 1) & (NB - 1));
-            if (k + 1 < nb) bad = bad || !(fabs(d) > pivot_tol) || isinf(d);
-            r = 1.0 / d;
-#pragma unroll
-            for (int j = 1; j < NB - 1; ++j)
-            {
-                const double u = __shfl_sync(0xffffffffu, a[j + 1], k);
-                a[j] = below ? a[j + 1] - l * u : a[j + 1];
-            }
-            a[0] = a1;
-            a[NB - 1] = 0.0;
+            const double l = A[i][k] * r;
+            for (int j = k + 1 + t / NB; j < NB; j += nt / NB) A[i][j] -= l * A[k][j];
         }
-        if (flags && t == 0 && bad) atomicOr(&flags[3], 1);
-        if (Rinv) Rinv[t] = 1.0 / A[t][t];
+        __syncthreads();
+    }
+    if (flags && t == 0 && bad) atomicOr(&flags[3], 1);
+    if (t < NB) Rinv[t] = 1.0 / A[t][t];
+    __syncthreads();
+    for (int e = t; e < NB * NB; e += nt)
+    {
+        const int ii = e % NB, j = e / NB;
+        if (ii > j && j < nb) A[ii][j] *= Rinv[j];
     }
     __syncthreads();
 }
@@ -300,36 +289,25 @@ __device__ __forceinline__ void bf_fill_pad(double (*P)[2 * NB], const double (*
 __device__ __forceinline__ void bf_panel_solve(const FrontRef &F, const double (*P)[2 * NB], const double *Rinv, bool rows,
                                                int32_t k0, int nb, int32_t q)
 {
+    // the thread's NB entries sit at base[k * stride]: a row of the L panel (stride ld), or a column of U12
+    // that lies in the L panel (q < s: contiguous) or in the transposed U panel (stride r)
+    double *base;
+    int64_t stride;
+    if (rows) { base = F.Lp + (int64_t)k0 * F.ld + q; stride = F.ld; }
+    else if (q < F.s) { base = F.Lp + (int64_t)q * F.ld + k0; stride = 1; }
+    else { base = F.Ut + (int64_t)k0 * F.r + (q - F.s); stride = F.r; }
     double x[NB];
-    if (rows)
-    {
 #pragma unroll
-        for (int k = 0; k < NB; ++k) x[k] = k < nb ? F.Lp[(int64_t)(k0 + k) * F.ld + q] : 0.0;
+    for (int k = 0; k < NB; ++k) x[k] = k < nb ? base[k * stride] : 0.0;
 #pragma unroll 1
-        for (int k = 0; k < nb; ++k)
-        {
-            const double xk = x[0] * Rinv[k];
-            F.Lp[(int64_t)(k0 + k) * F.ld + q] = xk;
-            const double *u = &P[k][k + 1];
-#pragma unroll
-            for (int j = 0; j < NB - 1; ++j) x[j] = x[j + 1] - xk * u[j];
-            x[NB - 1] = 0.0;
-        }
-    }
-    else
+    for (int k = 0; k < nb; ++k)
     {
+        const double xk = rows ? x[0] * Rinv[k] : x[0];
+        base[k * stride] = xk;
+        const double *p = &P[k][k + 1];
 #pragma unroll
-        for (int k = 0; k < NB; ++k) x[k] = k < nb ? *fr_at(F, k0 + k, q) : 0.0;
-#pragma unroll 1
-        for (int k = 0; k < nb; ++k)
-        {
-            const double xk = x[0];
-            *fr_at(F, k0 + k, q) = xk;
-            const double *l = &P[k][k + 1];
-#pragma unroll
-            for (int j = 0; j < NB - 1; ++j) x[j] = x[j + 1] - l[j] * xk;
-            x[NB - 1] = 0.0;
-        }
+        for (int j = 0; j < NB - 1; ++j) x[j] = x[j + 1] - xk * p[j];
+        x[NB - 1] = 0.0;
     }
 }
 __device__ __forceinline__ void bf_load_diag(double (*A)[NB + 1], const FrontRef &F, int32_t k0, int nb, int t, int nt)
@@ -359,9 +337,10 @@ __global__ void __launch_bounds__(128) k_bf_diag(FrontTables T, int32_t begin, i
     if (k0 >= F.s) return;
     const int32_t nb = min(k0 + NB, F.s) - k0;
     __shared__ double A[NB][NB + 1];
+    __shared__ double Rinv[NB];
     const int t = threadIdx.x;
     bf_load_diag(A, F, k0, nb, t, 128);
-    bf_block_lu(A, nullptr, nb, t, pivot_tol, flags);
+    bf_block_lu(A, Rinv, nb, t, 128, pivot_tol, flags);
     bf_store_diag(A, F, k0, nb, t, 128);
 }
 
@@ -423,18 +402,8 @@ __global__ void __launch_bounds__(128) k_bf_panel(FrontTables T, int32_t begin, 
     __shared__ double P[NB][2 * NB];
     const int t = threadIdx.x;
     const int32_t q = k1 + blk * 128 + t;
-    // pull this thread's panel entries towards L2 while the diagonal block is being factored
-    if (q < F.ld)
-    {
-#pragma unroll 4
-        for (int k = 0; k < nb; ++k)
-        {
-            const double *ptr = rows ? F.Lp + (int64_t)(k0 + k) * F.ld + q : fr_at(F, k0 + k, q);
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
-        }
-    }
     bf_load_diag(A, F, k0, nb, t, 128);
-    bf_block_lu(A, Rinv, nb, t, 0.0, nullptr);
+    bf_block_lu(A, Rinv, nb, t, 128, 0.0, nullptr);
     bf_fill_pad(P, A, rows, t, 128);
     if (q < F.ld) bf_panel_solve(F, P, Rinv, rows, k0, nb, q);
 }
@@ -465,26 +434,36 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
         // diagonal block any more, so it is factored once more and written back -- beside the tiles, not before one
         if (blockIdx.y != 0) return;
         __shared__ double Dg[NB][NB + 1];
+        __shared__ double Rinv[NB];
         bf_load_diag(Dg, F, k0, nb, t, 256);
-        bf_block_lu(Dg, nullptr, nb, t, pivot_tol, flags);
+        bf_block_lu(Dg, Rinv, nb, t, 256, pivot_tol, flags);
         bf_store_diag(Dg, F, k0, nb, t, 256);
         return;
     }
     if (i0 >= F.ld || j0 >= F.ld) return;
     constexpr int LDS = DMMA ? 68 : 65;
     __shared__ double A[NB][LDS], Bm[NB][LDS];
-    for (int e = t; e < NB * 64; e += 256)
-    {
-        const int k = e / 64, q = e % 64;
-        // A[k][q] = L(i0+q, k0+k): consecutive q are consecutive addresses of column k0+k
-        A[k][q] = (k < nb && i0 + q < F.ld) ? F.Lp[(int64_t)(k0 + k) * F.ld + (i0 + q)] : 0.0;
-    }
-    for (int e = t; e < NB * 64; e += 256)
-    {
-        // U(k0+k, j0+q): column major in the L panel (k fast), row major in the U panel (q fast)
-        int k, q;
-        if (j0 + 63 < F.s) { k = e % NB; q = e / NB; } else { k = e / 64; q = e % 64; }
-        Bm[k][q] = (k < nb && j0 + q < F.ld) ? *fr_at(F, k0 + k, j0 + q) : 0.0;
+    {   // operands: all 2 x 8 loads of a thread in flight before the first shared-memory store
+        constexpr int IT = NB * 64 / 256;
+        double va[IT], vb[IT];
+        const bool in_l = j0 + 63 < F.s; // U(k0+k, j0+q): column major in the L panel (k fast), row major in the U panel (q fast)
+#pragma unroll
+        for (int it = 0; it < IT; ++it)
+        {
+            const int e = t + it * 256;
+            const int k = e / 64, q = e % 64;
+            // A[k][q] = L(i0+q, k0+k): consecutive q are consecutive addresses of column k0+k
+            va[it] = (k < nb && i0 + q < F.ld) ? F.Lp[(int64_t)(k0 + k) * F.ld + (i0 + q)] : 0.0;
+            const int kb = in_l ? e % NB : k, qb = in_l ? e / NB : q;
+            vb[it] = (kb < nb && j0 + qb < F.ld) ? *fr_at(F, k0 + kb, j0 + qb) : 0.0;
+        }
+#pragma unroll
+        for (int it = 0; it < IT; ++it)
+        {
+            const int e = t + it * 256;
+            A[e / 64][e % 64] = va[it];
+            if (in_l) Bm[e % NB][e / NB] = vb[it]; else Bm[e / 64][e % 64] = vb[it];
+        }
     }
     __syncthreads();
     if (DMMA)
@@ -496,6 +475,20 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
         for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
             for (int nj = 0; nj < 4; ++nj) acc[mi][nj][0] = acc[mi][nj][1] = 0.0;
+        // the read-modify-write of the tile: addresses and old values first (independent loads), behind the MMAs
+        double *dst[2][4][2];
+        double old[2][4][2];
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+            for (int nj = 0; nj < 4; ++nj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+                {
+                    const int32_t i = i0 + wi + mi * 8 + g, j = j0 + wj + nj * 8 + 2 * c + e;
+                    dst[mi][nj][e] = (i < F.ld && j < F.ld) ? fr_at(F, i, j) : nullptr;
+                    old[mi][nj][e] = dst[mi][nj][e] ? *dst[mi][nj][e] : 0.0;
+                }
 #pragma unroll
         for (int kk = 0; kk < NB; kk += 4)
         {
@@ -511,18 +504,11 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
         }
 #pragma unroll
         for (int mi = 0; mi < 2; ++mi)
-        {
-            const int32_t i = i0 + wi + mi * 8 + g;
-            if (i >= F.ld) continue;
 #pragma unroll
             for (int nj = 0; nj < 4; ++nj)
 #pragma unroll
                 for (int e = 0; e < 2; ++e)
-                {
-                    const int32_t j = j0 + wj + nj * 8 + 2 * c + e;
-                    if (j < F.ld) *fr_at(F, i, j) -= acc[mi][nj][e];
-                }
-        }
+                    if (dst[mi][nj][e]) *dst[mi][nj][e] = old[mi][nj][e] - acc[mi][nj][e];
         return;
     }
     const int ti = (t % 16) * 4, tj = (t / 16) * 4;
@@ -807,13 +793,16 @@ __global__ void __launch_bounds__(512) k_bf_backward_tri(FrontTables T, int32_t 
             double uu[NB];
 #pragma unroll
             for (int q = 0; q < NB; ++q) uu[q] = (q < nb && t <= q) ? Lp[(int64_t)(k0 + q) * ld + i] : 1.0;
+            // reciprocal of the lane's own pivot up front: a division inside the chain costs more than the
+            // other NB - 1 steps of the block together
+            const double rinv = 1.0 / ((i < k1) ? Lp[(int64_t)i * ld + i] : 1.0);
             double yi = (i < k1) ? y1[i] : 0.0;
 #pragma unroll
             for (int q = NB - 1; q >= 0; --q)
             {
                 if (q < nb)
                 {
-                    if (t == q) yi = yi / uu[q];
+                    if (t == q) yi = yi * rinv;
                     const double xj = __shfl_sync(0xffffffffu, yi, q);
                     if (t < q) yi -= uu[q] * xj;
                 }
