@@ -256,16 +256,21 @@ __device__ __forceinline__ void bf_block_lu(double (*A)[NB + 1], double *Rinv, i
         const double d = A[k][k];
         bad = bad || !(fabs(d) > pivot_tol) || isinf(d);
         const double r = 1.0 / d;
-        if (i > k)
+        // each thread keeps the same (i, j) elements for every pivot; the loop is unrolled so that all
+        // shared-memory loads of a step are issued together, behind the reciprocal
+        const double l = A[i][k] * r;
+#pragma unroll
+        for (int m = 0; m < NB / 4; ++m)
         {
-            const double l = A[i][k] * r;
-            for (int j = k + 1 + t / NB; j < NB; j += nt / NB) A[i][j] -= l * A[k][j];
+            const int j = t / NB + m * (nt / NB);
+            if (j < NB && j > k && i > k) A[i][j] -= l * A[k][j];
         }
         __syncthreads();
     }
     if (flags && t == 0 && bad) atomicOr(&flags[3], 1);
     if (t < NB) Rinv[t] = 1.0 / A[t][t];
     __syncthreads();
+#pragma unroll 4
     for (int e = t; e < NB * NB; e += nt)
     {
         const int ii = e % NB, j = e / NB;
@@ -279,6 +284,7 @@ __device__ __forceinline__ void bf_block_lu(double (*A)[NB + 1], double *Rinv, i
 // zero padding makes every step the same NB - 1 updates -- a rolled loop again.  q = row / column in the front.
 __device__ __forceinline__ void bf_fill_pad(double (*P)[2 * NB], const double (*A)[NB + 1], bool rows, int t, int nt)
 {
+#pragma unroll 8
     for (int e = t; e < NB * 2 * NB; e += nt)
     {
         const int k = e / (2 * NB), m = e % (2 * NB);
@@ -310,12 +316,22 @@ __device__ __forceinline__ void bf_panel_solve(const FrontRef &F, const double (
         x[NB - 1] = 0.0;
     }
 }
-__device__ __forceinline__ void bf_load_diag(double (*A)[NB + 1], const FrontRef &F, int32_t k0, int nb, int t, int nt)
+template <int NT>
+__device__ __forceinline__ void bf_load_diag(double (*A)[NB + 1], const FrontRef &F, int32_t k0, int nb, int t)
 {
-    for (int e = t; e < NB * NB; e += nt)
+    constexpr int IT = NB * NB / NT;
+    double v[IT]; // all loads of the thread in flight before the first shared-memory store
+#pragma unroll
+    for (int it = 0; it < IT; ++it)
     {
-        const int i = e % NB, j = e / NB; // column j contiguous in i
-        A[i][j] = (i < nb && j < nb) ? F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] : (i == j ? 1.0 : 0.0);
+        const int e = t + it * NT, i = e % NB, j = e / NB; // column j contiguous in i
+        v[it] = (i < nb && j < nb) ? F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] : (i == j ? 1.0 : 0.0);
+    }
+#pragma unroll
+    for (int it = 0; it < IT; ++it)
+    {
+        const int e = t + it * NT;
+        A[e % NB][e / NB] = v[it];
     }
     __syncthreads();
 }
@@ -339,7 +355,7 @@ __global__ void __launch_bounds__(128) k_bf_diag(FrontTables T, int32_t begin, i
     __shared__ double A[NB][NB + 1];
     __shared__ double Rinv[NB];
     const int t = threadIdx.x;
-    bf_load_diag(A, F, k0, nb, t, 128);
+    bf_load_diag<128>(A, F, k0, nb, t);
     bf_block_lu(A, Rinv, nb, t, 128, pivot_tol, flags);
     bf_store_diag(A, F, k0, nb, t, 128);
 }
@@ -357,7 +373,7 @@ __global__ void __launch_bounds__(128) k_bf_rows(FrontTables T, int32_t begin, i
     __shared__ double Rinv[NB];
     __shared__ double P[NB][2 * NB];
     const int t = threadIdx.x;
-    bf_load_diag(A, F, k0, nb, t, 128); // factored already (k_bf_diag)
+    bf_load_diag<128>(A, F, k0, nb, t); // factored already (k_bf_diag)
     if (t < NB) Rinv[t] = 1.0 / A[t][t];
     bf_fill_pad(P, A, true, t, 128);
     const int32_t i = k1 + blockIdx.x * blockDim.x + t;
@@ -376,7 +392,7 @@ __global__ void __launch_bounds__(128) k_bf_trsm(FrontTables T, int32_t begin, i
     __shared__ double A[NB][NB + 1];
     __shared__ double P[NB][2 * NB];
     const int t = threadIdx.x;
-    bf_load_diag(A, F, k0, nb, t, 128);
+    bf_load_diag<128>(A, F, k0, nb, t);
     bf_fill_pad(P, A, false, t, 128);
     const int32_t j = k1 + blockIdx.x * blockDim.x + t;
     if (j < F.ld) bf_panel_solve(F, P, nullptr, false, k0, nb, j);
@@ -402,7 +418,22 @@ __global__ void __launch_bounds__(128) k_bf_panel(FrontTables T, int32_t begin, 
     __shared__ double P[NB][2 * NB];
     const int t = threadIdx.x;
     const int32_t q = k1 + blk * 128 + t;
-    bf_load_diag(A, F, k0, nb, t, 128);
+    if (q < F.ld)
+    {   // pull the thread's panel entries towards L2 while the diagonal block is being factored
+        const double *base = rows ? F.Lp + (int64_t)k0 * F.ld + q : q < F.s ? F.Lp + (int64_t)q * F.ld + k0 : F.Ut + (int64_t)k0 * F.r + (q - F.s);
+        const int64_t stride = rows ? F.ld : q < F.s ? 1 : F.r;
+        if (stride != 1)
+        {
+#pragma unroll 8
+            for (int k = 0; k < nb; ++k) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + k * stride));
+        }
+        else
+        {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(base));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(base + nb - 1));
+        }
+    }
+    bf_load_diag<128>(A, F, k0, nb, t);
     bf_block_lu(A, Rinv, nb, t, 128, 0.0, nullptr);
     bf_fill_pad(P, A, rows, t, 128);
     if (q < F.ld) bf_panel_solve(F, P, Rinv, rows, k0, nb, q);
@@ -435,7 +466,7 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
         if (blockIdx.y != 0) return;
         __shared__ double Dg[NB][NB + 1];
         __shared__ double Rinv[NB];
-        bf_load_diag(Dg, F, k0, nb, t, 256);
+        bf_load_diag<256>(Dg, F, k0, nb, t);
         bf_block_lu(Dg, Rinv, nb, t, 256, pivot_tol, flags);
         bf_store_diag(Dg, F, k0, nb, t, 256);
         return;
