@@ -279,20 +279,22 @@ __device__ __forceinline__ void bf_block_lu(double (*A)[NB + 1], double *Rinv, i
     __syncthreads();
 }
 // Panel solves against the factored diagonal block A, one thread per row of L21 = A21 * U11^-1 (rows) or per
-// column of U12 = L11^-1 * A12 (!rows).  P[k][m] = U(k, m) resp. L(m, k) for m < NB, zero beyond: the thread's
-// NB entries are shifted left by one register per pivot, the finished entry is stored at once, and the
-// zero padding makes every step the same NB - 1 updates -- a rolled loop again.  q = row / column in the front.
-__device__ __forceinline__ void bf_fill_pad(double (*P)[2 * NB], const double (*A)[NB + 1], bool rows, int t, int nt)
+// column of U12 = L11^-1 * A12 (!rows).  S[k][j] = U(k, k+1+j) resp. L(k+1+j, k), zero beyond the block: the
+// thread's NB entries are shifted left by one register per pivot, the finished entry is stored at once, and
+// the zero padding makes every step the same NB - 1 updates -- a rolled loop again.  Rows of S start on 16-byte
+// boundaries, so a step's coefficients arrive as NB/2 broadcast 16-byte loads issued together, ahead of the FMAs
+// (8-byte loads interleaved with the FMAs made the step wait for shared memory 31 times).
+__device__ __forceinline__ void bf_fill_pad(double (*S)[NB], const double (*A)[NB + 1], bool rows, int t, int nt)
 {
 #pragma unroll 8
-    for (int e = t; e < NB * 2 * NB; e += nt)
+    for (int e = t; e < NB * NB; e += nt)
     {
-        const int k = e / (2 * NB), m = e % (2 * NB);
-        P[k][m] = m < NB ? (rows ? A[k][m] : A[m][k]) : 0.0;
+        const int k = e / NB, j = e % NB, m = k + 1 + j;
+        S[k][j] = m < NB ? (rows ? A[k][m] : A[m][k]) : 0.0;
     }
     __syncthreads();
 }
-__device__ __forceinline__ void bf_panel_solve(const FrontRef &F, const double (*P)[2 * NB], const double *Rinv, bool rows,
+__device__ __forceinline__ void bf_panel_solve(const FrontRef &F, const double (*S)[NB], const double *Rinv, bool rows,
                                                int32_t k0, int nb, int32_t q)
 {
     // the thread's NB entries sit at base[k * stride]: a row of the L panel (stride ld), or a column of U12
@@ -308,11 +310,14 @@ __device__ __forceinline__ void bf_panel_solve(const FrontRef &F, const double (
 #pragma unroll 1
     for (int k = 0; k < nb; ++k)
     {
+        double2 c[NB / 2];
+        const double2 *row = reinterpret_cast<const double2 *>(S[k]);
+#pragma unroll
+        for (int j = 0; j < NB / 2; ++j) c[j] = row[j];
         const double xk = rows ? x[0] * Rinv[k] : x[0];
         base[k * stride] = xk;
-        const double *p = &P[k][k + 1];
 #pragma unroll
-        for (int j = 0; j < NB - 1; ++j) x[j] = x[j + 1] - xk * p[j];
+        for (int j = 0; j < NB - 1; ++j) x[j] = x[j + 1] - xk * ((j & 1) ? c[j / 2].y : c[j / 2].x);
         x[NB - 1] = 0.0;
     }
 }
@@ -371,7 +376,7 @@ __global__ void __launch_bounds__(128) k_bf_rows(FrontTables T, int32_t begin, i
     if ((int64_t)blockIdx.x * blockDim.x + k1 >= F.ld) return;
     __shared__ double A[NB][NB + 1];
     __shared__ double Rinv[NB];
-    __shared__ double P[NB][2 * NB];
+    __shared__ __align__(16) double P[NB][NB];
     const int t = threadIdx.x;
     bf_load_diag<128>(A, F, k0, nb, t); // factored already (k_bf_diag)
     if (t < NB) Rinv[t] = 1.0 / A[t][t];
@@ -390,7 +395,7 @@ __global__ void __launch_bounds__(128) k_bf_trsm(FrontTables T, int32_t begin, i
     const int32_t k1 = min(k0 + NB, F.s), nb = k1 - k0;
     if ((int64_t)blockIdx.x * blockDim.x + k1 >= F.ld) return;
     __shared__ double A[NB][NB + 1];
-    __shared__ double P[NB][2 * NB];
+    __shared__ __align__(16) double P[NB][NB];
     const int t = threadIdx.x;
     bf_load_diag<128>(A, F, k0, nb, t);
     bf_fill_pad(P, A, false, t, 128);
@@ -415,7 +420,7 @@ __global__ void __launch_bounds__(128) k_bf_panel(FrontTables T, int32_t begin, 
     if ((int64_t)blk * 128 + k1 >= F.ld) return;
     __shared__ double A[NB][NB + 1];
     __shared__ double Rinv[NB];
-    __shared__ double P[NB][2 * NB];
+    __shared__ __align__(16) double P[NB][NB];
     const int t = threadIdx.x;
     const int32_t q = k1 + blk * 128 + t;
     if (q < F.ld)
@@ -726,8 +731,12 @@ __global__ void __launch_bounds__(512) k_bf_forward_tri(FrontTables T, int32_t b
         __syncthreads();
         for (int32_t i = k1 + t; i < s; i += G)
         {
+            double lv[NB]; // the NB factor entries of the row in flight together
+#pragma unroll
+            for (int q = 0; q < NB; ++q) lv[q] = (k0 + q < k1) ? Lp[(int64_t)(k0 + q) * ld + i] : 0.0;
             double acc = 0.0;
-            for (int32_t k = k0; k < k1; ++k) acc += Lp[(int64_t)k * ld + i] * yb[k - k0];
+#pragma unroll
+            for (int q = 0; q < NB; ++q) acc += lv[q] * ((k0 + q < k1) ? yb[q] : 0.0);
             y1[i] -= acc;
         }
         __syncthreads();
@@ -843,8 +852,12 @@ __global__ void __launch_bounds__(512) k_bf_backward_tri(FrontTables T, int32_t 
         __syncthreads();
         for (int32_t i = t; i < k0; i += G)
         {
+            double uv[NB];
+#pragma unroll
+            for (int q = 0; q < NB; ++q) uv[q] = (k0 + q < k1) ? Lp[(int64_t)(k0 + q) * ld + i] : 0.0;
             double acc = 0.0;
-            for (int32_t j = k0; j < k1; ++j) acc += Lp[(int64_t)j * ld + i] * xb[j - k0];
+#pragma unroll
+            for (int q = 0; q < NB; ++q) acc += uv[q] * ((k0 + q < k1) ? xb[q] : 0.0);
             y1[i] -= acc;
         }
         __syncthreads();

@@ -387,3 +387,29 @@ def test_big_front_fused_panel_is_bit_identical():
         assert c.stat("max_front") >= 96
         c.close()
     assert out[0] == out[1]
+
+
+def test_big_front_dmma_matches_fma_tiles():
+    """Trailing update on the FP64 tensor cores (mma.m8n8k4.f64) vs the FP64 FMA tiles: same factorisation up to
+    the summation order inside a 32-deep dot product; both must meet the backward-error bar of the linear solve."""
+    m = 160
+    n = m * m
+    u = P.grid2d_state(m)
+    J = P.grid2d_jacobian(u, m)
+    M = P.identity_mass(n)
+    b = np.full(n, 1.24)
+    csc = O.assemble_jb(O.port, n, J, M, 50.0)
+    out = []
+    for dmma in (1, 0):
+        c = B.Context(n)
+        c.set_option("chain", 0); c.set_option("bf_dmma", dmma)
+        c.set_mass(M); c.set_jacobian(J)
+        c.refactor(50.0)
+        c.set_rhs(b)
+        x = c.solve()
+        eta, _ = O.backward_error(n, csc, x, b)
+        assert eta <= 1e-12, (dmma, eta)
+        assert c.stat("max_front") >= 96
+        out.append(x)
+        c.close()
+    assert np.max(np.abs(out[0] - out[1])) <= 1e-10 * np.max(np.abs(out[1]))
