@@ -1070,7 +1070,14 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
             c->kernels += 1 + max_children;
             for (int32_t k0 = 0; k0 < max_s; k0 += NB)
             {
-                const int32_t rest = max_ld - std::min(k0 + NB, max_s);
+                // largest trailing order among the fronts still being factored: a front with fewer pivots than
+                // the level's maximum ends its last block column early and has MORE rows and columns behind it
+                int32_t rest = 0;
+                for (int32_t q = 0; q < L.count; ++q)
+                {
+                    const int32_t f = S.big_sn[L.begin + q], sf = S.s_of(f);
+                    if (sf > k0) rest = std::max(rest, sf + S.r_of(f) - std::min(k0 + NB, sf));
+                }
                 if (rest <= 0 || !c->bf_fused_panel)
                 {
                     k_bf_diag<<<L.count, 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);

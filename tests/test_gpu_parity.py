@@ -413,3 +413,14 @@ def test_big_front_dmma_matches_fma_tiles():
         out.append(x)
         c.close()
     assert np.max(np.abs(out[0] - out[1])) <= 1e-10 * np.max(np.abs(out[1]))
+
+
+@pytest.mark.parametrize("m", [160, 512])
+def test_linear_solve_grid2d_default_options(m):
+    """C4-style Jacobian through the default path (unit kernels below, blocked big fronts above).  Levels mix
+    fronts with different pivot counts: a front with fewer pivots than the level's maximum has the larger
+    trailing matrix in its last block column, which the launch grids must cover (m = 160 caught them short)."""
+    n = m * m
+    u = P.grid2d_state(m)
+    x, st = _solve_and_check(n, P.grid2d_jacobian(u, m), P.identity_mass(n), 50.0, options={"chain": 0})
+    assert st["n_big_fronts"] > 0
