@@ -83,7 +83,7 @@ def make_workload(name, size):
         x0 = P.grid2d_state(m)
         J = P.grid2d_jacobian(x0, m)
         M = P.identity_mass(n)
-        f = np.zeros(n)
+        f = np.linspace(-1.0, 1.0, n)  # a non-zero right-hand side: the parity figure below compares dx with the reference's
         nlu = 153_876_742 if m == 1024 else None
         label = f"C4 grid-2D {m}x{m} 5-point (BASELINE configs[3])"
     return dict(n=n, J=J, M=M, x0=x0, f=f, dt=np.array([1e-2, 0.0, 0.0, 0.0]), order=1, label=label, nlu_ref=nlu,
