@@ -179,6 +179,7 @@ struct daecpp_b200_ctx
     double last_alpha = 0.0;
     bool blocked_lu = true;        // big fronts: blocked multi-CTA LU (numeric.cu) instead of one CTA per front
     int blocked_lu_min_dim = 96;   // level groups whose largest front is at least this order
+    bool bf_pdl = true;            // big fronts: panel / trailing-update launches chained by programmatic dependent launch
     bool bf_dmma = true;           // big fronts: trailing update on the FP64 tensor cores (mma.m8n8k4.f64), 0 = FP64 FMA tiles
     bool bf_fused_panel = true;    // big fronts: panel in one launch (numeric.cu: k_bf_panel), 0 = diag / rows / trsm launches
 

@@ -161,6 +161,26 @@ __global__ void __launch_bounds__(Grp<G>::THREADS) k_factor_level(FrontTables T,
 // U panel (r x s) and contribution block (r x r); fr_at() maps (i, j) of the front onto them.
 constexpr int NB = 32;
 
+// Programmatic dependent launch for the panel / trailing-update pairs of a block column: a kernel lets its
+// successor start launching at once (its CTAs read the static front tables and then wait), and waits itself
+// for its predecessor's memory before touching factor storage.  No-ops in a plain launch.
+__device__ __forceinline__ void bf_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void bf_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <class... P, class... A> inline void bf_launch_pdl(cudaStream_t st, void (*kernel)(P...), dim3 grid, int threads, A... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(threads, 1, 1);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
+}
+
 struct FrontRef
 {
     double *Lp, *Ut, *C;
@@ -423,6 +443,8 @@ __global__ void __launch_bounds__(128) k_bf_panel(FrontTables T, int32_t begin, 
     __shared__ __align__(16) double P[NB][NB];
     const int t = threadIdx.x;
     const int32_t q = k1 + blk * 128 + t;
+    bf_pdl_trigger();
+    bf_pdl_wait(); // everything above came from the static tables
     if (q < F.ld)
     {   // pull the thread's panel entries towards L2 while the diagonal block is being factored
         const double *base = rows ? F.Lp + (int64_t)k0 * F.ld + q : q < F.s ? F.Lp + (int64_t)q * F.ld + k0 : F.Ut + (int64_t)k0 * F.r + (q - F.s);
@@ -465,6 +487,8 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
     const int32_t k1 = min(k0 + NB, F.s), nb = k1 - k0;
     const int32_t i0 = k1 + blockIdx.x * 64, j0 = k1 + blockIdx.y * 64;
     const int t = threadIdx.x;
+    bf_pdl_trigger();
+    bf_pdl_wait();
     if (flags && blockIdx.x == gridDim.x - 1)
     {   // one extra CTA per front (fused panel): the panel launch is complete, nobody reads the unfactored
         // diagonal block any more, so it is factored once more and written back -- beside the tiles, not before one
@@ -1092,10 +1116,20 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
                     continue;
                 }
                 // two launches per block column: panel (diagonal block factored redundantly by every CTA), trailing update
-                k_bf_panel<<<dim3(2 * ((rest + 127) / 128), L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                 const int tiles = (rest + 63) / 64;
-                if (c->bf_dmma) k_bf_gemm<true><<<dim3(tiles + 1, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
-                else k_bf_gemm<false><<<dim3(tiles + 1, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                const dim3 gp(2 * ((rest + 127) / 128), L.count), gg(tiles + 1, tiles, L.count);
+                if (c->bf_pdl)
+                {
+                    bf_launch_pdl(st, k_bf_panel, gp, 128, T, L.begin, k0, c->LU.p, c->CB.p);
+                    if (c->bf_dmma) bf_launch_pdl(st, k_bf_gemm<true>, gg, 256, T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                    else bf_launch_pdl(st, k_bf_gemm<false>, gg, 256, T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                }
+                else
+                {
+                    k_bf_panel<<<gp, 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
+                    if (c->bf_dmma) k_bf_gemm<true><<<gg, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                    else k_bf_gemm<false><<<gg, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                }
                 c->kernels += 2;
             }
         }
