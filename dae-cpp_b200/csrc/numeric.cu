@@ -210,6 +210,8 @@ __global__ void k_bf_zero(FrontTables T, int32_t begin, double *__restrict__ CB)
     const int32_t f = T.level_sn[begin + blockIdx.y];
     const int64_t r = T.sn_rowptr[f + 1] - T.sn_rowptr[f];
     double *C = CB + T.sn_cb[f];
+    bf_pdl_trigger();
+    bf_pdl_wait();
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < r * r; e += (int64_t)gridDim.x * blockDim.x) C[e] = 0.0;
 }
 // extend-add of the `ord`-th child of every front of the level (grid.y = front).  Children are added
@@ -228,6 +230,8 @@ __global__ void __launch_bounds__(256) k_bf_extend(FrontTables T, int32_t begin,
     const double *Cc = CB + T.sn_cb[c];
     const int32_t *rel = T.sn_rel + rp;
     const int lane = threadIdx.x % 32, wid = threadIdx.x / 32, NW = blockDim.x / 32;
+    bf_pdl_trigger();
+    bf_pdl_wait();
     for (int32_t bc = blockIdx.x * NW + wid; bc < rc; bc += gridDim.x * NW)
     {
         const int32_t rb = rel[bc];
@@ -717,6 +721,8 @@ __global__ void __launch_bounds__(512) k_bf_forward_tri(FrontTables T, int32_t b
     const double *Lp = LU + T.sn_lu[f];
     double *u = upd + rp0;
     double *y1 = y + first;
+    bf_pdl_trigger();
+    bf_pdl_wait();
     __shared__ double yb[NB];
     for (int32_t a = t; a < r; a += G) u[a] = 0.0;
     __syncthreads();
@@ -783,6 +789,8 @@ __global__ void __launch_bounds__(GV_ROWS *GV_SEG) k_bf_forward_gemv(FrontTables
     const double *y1 = y + first;
     const int ri = threadIdx.x % GV_ROWS, seg = threadIdx.x / GV_ROWS;
     const int32_t a = a0 + ri;
+    bf_pdl_trigger();
+    bf_pdl_wait();
     __shared__ double part[GV_SEG][GV_ROWS];
     double acc0 = 0.0, acc1 = 0.0;
     if (a < r)
@@ -821,6 +829,8 @@ __global__ void __launch_bounds__(256) k_bf_backward_gemv(FrontTables T, int32_t
     const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - rp0);
     if (r == 0) return;
     const int32_t ld = s + r;
+    bf_pdl_trigger();
+    bf_pdl_wait();
     const double *utk = LU + T.sn_lu[f] + (int64_t)ld * s + (int64_t)k * r;
     const int32_t *rows = T.sn_rows + rp0;
     double acc0 = 0.0, acc1 = 0.0;
@@ -848,6 +858,8 @@ __global__ void __launch_bounds__(512) k_bf_backward_tri(FrontTables T, int32_t 
     const double *Lp = LU + T.sn_lu[f];
     double *y1 = y + first;
     __shared__ double xb[NB];
+    bf_pdl_trigger();
+    bf_pdl_wait();
     for (int32_t k1 = s; k1 > 0; k1 -= NB)
     {
         const int32_t k0 = max(k1 - NB, 0);
@@ -1088,9 +1100,9 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
                 const int32_t f = S.big_sn[L.begin + q];
                 max_children = std::max(max_children, S.child_ptr[f + 1] - S.child_ptr[f]);
             }
-            k_bf_zero<<<dim3(64, L.count), 256, 0, st>>>(T, L.begin, c->CB.p);
+            bf_launch_pdl(st, k_bf_zero, dim3(64, L.count), 256, T, L.begin, c->CB.p);
             for (int32_t ord = 0; ord < max_children; ++ord)
-                k_bf_extend<<<dim3(std::max(1, std::min(256, (max_ld + 7) / 8)), L.count), 256, 0, st>>>(T, L.begin, ord, c->LU.p, c->CB.p);
+                bf_launch_pdl(st, k_bf_extend, dim3(std::max(1, std::min(256, (max_ld + 7) / 8)), L.count), 256, T, L.begin, ord, c->LU.p, c->CB.p);
             c->kernels += 1 + max_children;
             for (int32_t k0 = 0; k0 < max_s; k0 += NB)
             {
@@ -1194,9 +1206,8 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
         if (L.kind == 0) { if ((rc = launch_unit_forward(c, L, direct))) return rc; }
         else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
         {
-            k_bf_forward_tri<<<L.count, 512, 0, st>>>(T, L.begin, c->LU.p, c->upd.p, c->work);
-            k_bf_forward_gemv<<<dim3((L.max_dim + GV_ROWS - 1) / GV_ROWS, L.count), GV_ROWS * GV_SEG, 0, st>>>(T, L.begin, c->LU.p, c->upd.p,
-                                                                                                            c->work);
+            bf_launch_pdl(st, k_bf_forward_tri, dim3(L.count), 512, T, L.begin, c->LU.p, c->upd.p, c->work);
+            bf_launch_pdl(st, k_bf_forward_gemv, dim3((L.max_dim + GV_ROWS - 1) / GV_ROWS, L.count), GV_ROWS * GV_SEG, T, L.begin, c->LU.p, c->upd.p, c->work);
             c->kernels += 2;
         }
         else
@@ -1211,8 +1222,8 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
         if (L.kind == 0) { if ((rc = launch_unit_backward(c, L, direct, fuse_update, atol, rtol, max_err_abs))) return rc; }
         else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
         {
-            k_bf_backward_gemv<<<dim3((L.max_dim + 7) / 8, L.count), 256, 0, st>>>(T, L.begin, c->LU.p, c->work);
-            k_bf_backward_tri<<<L.count, 512, 0, st>>>(T, L.begin, c->LU.p, c->work);
+            bf_launch_pdl(st, k_bf_backward_gemv, dim3((L.max_dim + 7) / 8, L.count), 256, T, L.begin, c->LU.p, c->work);
+            bf_launch_pdl(st, k_bf_backward_tri, dim3(L.count), 512, T, L.begin, c->LU.p, c->work);
             c->kernels += 2;
         }
         else
