@@ -177,7 +177,7 @@ int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *ctx, int64_t *out, int64_t cap
  * forward kernel; "keep_b" = 1 also writes it to HBM for daecpp_b200_get_vector), "lean_flags" (flag words
  * delivered through a mapped host word instead of memset + copy nodes).  General path: "blocked_lu",
  * "blocked_lu_min_dim", "bf_fused_panel" (panel of a block column in one launch), "bf_dmma" (trailing update of big
- * fronts on the FP64 tensor cores, default 1; 0 = FP64 FMA tiles).  Debug: "trace_units", "phase_timing", "pinned_io". */
+ * fronts on the FP64 tensor cores, default 1; 0 = FP64 FMA tiles), "bf_pdl" (programmatic dependent launch between them).  Debug: "trace_units", "phase_timing", "pinned_io". */
 int daecpp_b200_set_option(daecpp_b200_ctx *ctx, const char *key, double value);
 
 #ifdef __cplusplus
