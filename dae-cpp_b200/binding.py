@@ -25,7 +25,23 @@ SYMBOLS = [
     "daecpp_b200_solve", "daecpp_b200_get_csc", "daecpp_b200_get_vector", "daecpp_b200_set_vector", "daecpp_b200_get_stat",
     "daecpp_b200_set_option", "daecpp_b200_iteration_resident", "daecpp_b200_iterations_resident", "daecpp_b200_event_mark", "daecpp_b200_event_elapsed_ms", "daecpp_b200_debug_unit_trace", "daecpp_b200_host_register", "daecpp_b200_host_unregister",
     "daecpp_b200_set_blocking_sync", "daecpp_b200_set_pooling", "daecpp_b200_set_jacobian_values", "daecpp_b200_iteration_host",
+    "daecpp_b200_batch_create", "daecpp_b200_batch_destroy", "daecpp_b200_batch_last_error", "daecpp_b200_batch_set_pattern",
+    "daecpp_b200_batch_set_mass_values", "daecpp_b200_batch_set_jacobian_values", "daecpp_b200_batch_set_rhs_values",
+    "daecpp_b200_batch_set_state", "daecpp_b200_batch_get_vector", "daecpp_b200_batch_set_device_functors",
+    "daecpp_b200_batch_round", "daecpp_b200_batch_get_stat",
 ]
+
+LANE_IDLE, LANE_SOLVE, LANE_REFACTOR = 0, 1, 2
+LANE_KEEP, LANE_ACCEPT, LANE_ROLLBACK = 0, 1, 2
+
+
+class LaneCmd(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("pre", C.c_int32), ("order", C.c_int32), ("reserved", C.c_int32), ("t", C.c_double),
+                ("dt", C.c_double * 4)]
+
+
+class LaneResult(C.Structure):
+    _fields_ = [("flags", C.c_int32), ("status", C.c_int32), ("variability", C.c_double)]
 
 
 def load():
@@ -72,6 +88,21 @@ def load():
     lib.daecpp_b200_debug_unit_trace.argtypes = [_vp, _vp, C.c_int64, C.POINTER(C.c_int64)]
     lib.daecpp_b200_event_mark.argtypes = [_vp]
     lib.daecpp_b200_event_elapsed_ms.argtypes = [_vp, C.POINTER(C.c_double)]
+    lib.daecpp_b200_batch_create.argtypes = [C.c_int32, C.c_int32, C.c_int, C.POINTER(_vp)]
+    lib.daecpp_b200_batch_destroy.argtypes = [_vp]
+    lib.daecpp_b200_batch_destroy.restype = None
+    lib.daecpp_b200_batch_last_error.argtypes = [_vp]
+    lib.daecpp_b200_batch_last_error.restype = C.c_char_p
+    lib.daecpp_b200_batch_set_pattern.argtypes = [_vp, _vp, _vp, C.c_int64, _vp, _vp, C.c_int64]
+    lib.daecpp_b200_batch_set_mass_values.argtypes = [_vp, _vp, C.c_int32, C.c_int32]
+    lib.daecpp_b200_batch_set_jacobian_values.argtypes = [_vp, _vp, C.c_int32, C.c_int32]
+    lib.daecpp_b200_batch_set_rhs_values.argtypes = [_vp, _vp, C.c_int32, C.c_int32]
+    lib.daecpp_b200_batch_set_state.argtypes = [_vp, _vp, C.c_int32, C.c_int32]
+    lib.daecpp_b200_batch_get_vector.argtypes = [_vp, C.c_int32, _vp, C.c_int32, C.c_int32]
+    lib.daecpp_b200_batch_set_device_functors.argtypes = [_vp, _vp]
+    lib.daecpp_b200_batch_round.argtypes = [_vp, C.POINTER(LaneCmd), C.c_double, C.c_double, C.c_double, C.c_int32, C.c_double,
+                                            C.POINTER(LaneResult)]
+    lib.daecpp_b200_batch_get_stat.argtypes = [_vp, C.c_char_p, C.POINTER(C.c_double)]
     return lib
 
 
@@ -255,3 +286,83 @@ class Context:
 
     def set_option(self, key, value):
         self._ck(self.lib.daecpp_b200_set_option(self.h, key.encode(), float(value)))
+
+
+class Batch:
+    """`lanes` systems of one sparsity pattern advanced in lock step (include/daecpp_b200.h: daecpp_b200_batch_*).
+    Host-functor mode only from Python: right-hand sides and Jacobian values are uploaded as lane-major slabs."""
+
+    VEC = {"b": 0, "dx": 1, "xk": 3, "x0": 4, "x1": 5, "x2": 6, "x3": 7}
+
+    def __init__(self, n, lanes, device=0, lib=None):
+        self.lib = lib or load()
+        self.n, self.lanes = int(n), int(lanes)
+        h = _vp()
+        rc = self.lib.daecpp_b200_batch_create(self.n, self.lanes, device, C.byref(h))
+        if rc:
+            raise Error(rc, (self.lib.daecpp_b200_batch_last_error(None) or b"").decode())
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.daecpp_b200_batch_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _ck(self, rc, allow=()):
+        if rc and rc not in allow:
+            raise Error(rc, (self.lib.daecpp_b200_batch_last_error(self.h) or b"").decode())
+        return rc
+
+    def set_pattern(self, Ji, Jj, Mi, Mj, allow=()):
+        Ji, Jj, Mi, Mj = [np.ascontiguousarray(a, np.int32) for a in (Ji, Jj, Mi, Mj)]
+        self.nTJ, self.nTM = len(Ji), len(Mi)
+        return self._ck(self.lib.daecpp_b200_batch_set_pattern(self.h, _ptr(Ji), _ptr(Jj), len(Ji), _ptr(Mi), _ptr(Mj), len(Mi)), allow)
+
+    def _slab(self, a, width, first, count):
+        a = np.ascontiguousarray(a, np.float64)
+        assert a.size == max(count, 1) * width or (count == 0 and a.size == width), (a.shape, width, count)
+        return a
+
+    def set_mass_values(self, A, first=0, count=0):
+        A = self._slab(A, self.nTM, first, count)
+        self._ck(self.lib.daecpp_b200_batch_set_mass_values(self.h, _ptr(A), first, count))
+
+    def set_jacobian_values(self, A, first=0, count=None):
+        count = self.lanes if count is None else count
+        A = self._slab(A, self.nTJ, first, count)
+        self._ck(self.lib.daecpp_b200_batch_set_jacobian_values(self.h, _ptr(A), first, count))
+
+    def set_rhs_values(self, f, first=0, count=None):
+        count = self.lanes if count is None else count
+        f = self._slab(f, self.n, first, count)
+        self._ck(self.lib.daecpp_b200_batch_set_rhs_values(self.h, _ptr(f), first, count))
+
+    def set_state(self, x0, first=0, count=None):
+        count = self.lanes if count is None else count
+        x0 = self._slab(x0, self.n, first, count)
+        self._ck(self.lib.daecpp_b200_batch_set_state(self.h, _ptr(x0), first, count))
+
+    def get_vector(self, which, first=0, count=None):
+        count = self.lanes if count is None else count
+        out = np.empty((count, self.n))
+        self._ck(self.lib.daecpp_b200_batch_get_vector(self.h, self.VEC.get(which, which), out.ctypes.data, first, count))
+        return out
+
+    def round(self, cmds, atol, rtol, max_err_abs=1e100, variability_on=False, var_tol=1e-4, allow=()):
+        """cmds: list of dict(mode, pre, order, t, dt) per lane.  Returns (rc, [(flags, status, variability)])."""
+        arr = (LaneCmd * self.lanes)()
+        for k, q in enumerate(cmds):
+            arr[k].mode = q.get("mode", LANE_IDLE); arr[k].pre = q.get("pre", LANE_KEEP); arr[k].order = q.get("order", 1)
+            arr[k].t = q.get("t", 0.0)
+            for i, v in enumerate(q.get("dt", (0.0, 0.0, 0.0, 0.0))):
+                arr[k].dt[i] = v
+        res = (LaneResult * self.lanes)()
+        rc = self._ck(self.lib.daecpp_b200_batch_round(self.h, arr, atol, rtol, max_err_abs, int(variability_on), var_tol, res), allow)
+        return rc, [(r.flags, r.status, r.variability) for r in res]
+
+    def stat(self, key):
+        v = C.c_double(0)
+        self._ck(self.lib.daecpp_b200_batch_get_stat(self.h, key.encode(), C.byref(v)))
+        return v.value

@@ -65,11 +65,24 @@ struct ChainArgs
     int32_t seq;
     double *xk_host;     // mapped pinned copy of xk for the host (small systems), written with the fused update
     int32_t *host_flags; // mapped host mirror of dflags[2..4], written by the CTA that finishes the iteration last
-    // ensemble: member = blockIdx.y, strides in elements
+    // ensemble: lane = blockIdx.y, strides in elements; per-lane control words (ctx.hpp: LaneSet), null for a
+    // single system
     const double *alpha_arr;
-    int64_t s_jv, s_mv, s_F, s_Y, s_red, s_rv, s_x, s_vec;
+    int64_t s_jv, s_mv, s_F, s_Y, s_red, s_rv, s_x, s_vec, s_hist;
+    int32_t lanes;
+    const int32_t *lane_mode, *lane_hbase, *lane_order;
+    const double *lane_w; // [5][lanes]
+    double *hist;
+    int32_t *lane_flags;
+    unsigned long long *lane_var;
+    int32_t var_on;
+    double var_tol;
     long long *trace; // debug ("trace_units"): [kernel][tile][8] %globaltimer stamps, member 0
 };
+
+// flag words of a lane addressed like the context's d_flags: [2] update flags, [3] pivot failure, [4] wait time-out
+__device__ __forceinline__ int32_t *flag_words(const ChainArgs &a, int64_t mb) { return a.lane_flags ? a.lane_flags + 4 * mb - 2 : a.dflags; }
+__device__ __forceinline__ int lane_mode(const ChainArgs &a, int64_t mb) { return a.lane_mode ? a.lane_mode[mb] : 2; }
 
 constexpr int TRACE_SLOTS = 8, TRACE_KERNELS = 5; // factor tiles, factor top, forward tiles, top solve, backward tiles
 __device__ __forceinline__ void stamp(const ChainArgs &a, int kernel, int tile, int slot)
@@ -249,7 +262,7 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
     __syncthreads();
     stamp(a, tk, tile, 3);
     if (t == 0) factor_phase2<B>(tile, lv.ntiles, lv.is_top != 0, sh, Ft, lv.red_out + mb * a.s_red, a.tol, fail);
-    if (fail) atomicOr(&a.dflags[3], 1);
+    if (fail) atomicOr(&flag_words(a, mb)[3], 1);
     stamp(a, tk, tile, 4);
 }
 
@@ -267,6 +280,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
     }
     stamp(a, FIRST ? 0 : 1, tile, 5);
     pdl_wait();
+    if (lane_mode(a, mb) != 2) return; // this lane keeps its factors (uniform over the lane's CTAs)
     factor_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true);
     if (a.fuse_top && last_tile_done(a.counter + 2 * mb, a.lv.ntiles, t))
         factor_tile<B, false>(a, a.top, sh, t, 0, mb, false); // the grid-level reduced system, same CTA
@@ -293,8 +307,9 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
         if (!a.out) return;
         double *__restrict__ out = a.out + mb * a.s_vec;
         double *__restrict__ xk = a.xk + mb * a.s_vec;
-        const double *__restrict__ x0 = a.x0 + mb * a.s_vec;
+        const double *__restrict__ x0 = (a.lane_hbase ? a.hist + (int64_t)a.lane_hbase[mb] * a.s_hist : a.x0) + mb * a.s_vec;
         int flag = 0;
+        double vmax = 0.0;
         for (int i0 = t; i0 < total; i0 += D::T * U)
         {
             int64_t o[U];
@@ -329,10 +344,25 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
                     const double xn = __dadd_rn(xo[u], v[u]);
                     xk[o[u]] = xn;
                     if (a.xk_host) a.xk_host[o[u]] = xn;
+                    if (a.var_on && fabs(xa[u]) > a.var_tol && fabs(xn) > a.var_tol)
+                    {   // what accept_step would measure if this iterate is accepted (solver.hpp:703-717, vector_ops.cu: k_accept)
+                        const double rel = fabs(__ddiv_rn(__dsub_rn(xa[u], xn), xa[u]));
+                        if (rel > vmax) vmax = rel;
+                    }
                 }
             }
         }
-        if (flag) atomicOr(&a.dflags[2], flag);
+        if (flag) atomicOr(&flag_words(a, mb)[2], flag);
+        if (a.var_on && a.lane_var)
+        {   // non-negative doubles order like their bit patterns
+            unsigned long long bits = (unsigned long long)__double_as_longlong(vmax);
+            for (int o2 = 16; o2 > 0; o2 >>= 1)
+            {
+                const unsigned long long other = __shfl_xor_sync(0xffffffffu, bits, o2);
+                bits = other > bits ? other : bits;
+            }
+            if ((t & 31) == 0 && bits) atomicMax(a.lane_var + mb, bits);
+        }
         if (a.host_flags && last_tile_done(a.counter + 4, lv.ntiles, t, a.xk_host != nullptr))
         {
             if (t == 0)
@@ -361,7 +391,17 @@ __device__ __forceinline__ void stage_rhs_residual(int t, int tile, int n, doubl
 {
     using D = Dim<B>;
     constexpr int TOTAL = B * D::ROWS, U = 4, NT = D::T;
-    const Bdf &s = a.bdf;
+    Bdf s = a.bdf;
+    if (a.lane_w)
+    {   // the lane's own BDF order, weights and history ring
+        const int hb = a.lane_hbase[mb];
+        s.order = a.lane_order[mb];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) s.c[k] = a.lane_w[(int64_t)k * a.lanes + mb];
+        s.xk = a.xk;
+        s.x0 = a.hist + (int64_t)(hb & 3) * a.s_hist; s.x1 = a.hist + (int64_t)((hb + 1) & 3) * a.s_hist;
+        s.x2 = a.hist + (int64_t)((hb + 2) & 3) * a.s_hist; s.x3 = a.hist + (int64_t)((hb + 3) & 3) * a.s_hist;
+    }
     const int64_t sv = mb * a.s_vec;
     for (int i0 = t; i0 < TOTAL; i0 += NT * U)
     {
@@ -596,6 +636,7 @@ __global__ void __launch_bounds__(Cfg<B>::T, (B <= 2 ? 4 : 1)) k_chain_forward(C
     const int64_t mb = blockIdx.y;
     stamp(a, FIRST ? 2 : 3, tile, 5);
     pdl_wait();
+    if (lane_mode(a, mb) == 0) return; // idle lane
     if (a.extra_factor && tile == a.lv.ntiles)
     {   // uniform over the CTA: the grid-level reduced system is factored here while the other CTAs sweep forward
         factor_tile<B, false>(a, a.top, *reinterpret_cast<FactorShared<B> *>(smem), t, 0, mb, true);
@@ -607,7 +648,7 @@ __global__ void __launch_bounds__(Cfg<B>::T, (B <= 2 ? 4 : 1)) k_chain_forward(C
         if (a.top_pcr)
         {
             stamp(a, 3, 0, 0);
-            pcr_top<B>(a.top.rows, a.top.red_in + mb * a.s_red, a.top.rv_in + mb * a.s_rv, a.top.xlev + mb * a.s_x, a.tol, &a.dflags[3],
+            pcr_top<B>(a.top.rows, a.top.red_in + mb * a.s_red, a.top.rv_in + mb * a.s_rv, a.top.xlev + mb * a.s_x, a.tol, &flag_words(a, mb)[3],
                        reinterpret_cast<double *>(smem), t, a.trace ? a.trace + (size_t)3 * a.trace_tiles * TRACE_SLOTS : nullptr);
             stamp(a, 3, 0, 4);
         }
@@ -628,6 +669,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
     double *Ft = lv.F + mb * a.s_F + (size_t)tile * D::TILE_F;
     double *Yt = lv.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
     const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
+    if (lane_mode(a, mb) == 0) return; // idle lane
     stamp(a, 4, tile, 0);
     // The factors are two launches old (the forward kernel waited for the factor kernel before it let
     // this one start), so they may be touched before the dependency wait: while the top level is being
@@ -791,6 +833,16 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g, bool fuse)
     if (fuse) a.top = level_view(c, g + 1);
     a.counter = reinterpret_cast<uint32_t *>(c->dC.counter.p);
     a.dflags = c->d_flags;
+    if (const LaneSet *L = c->lanes)
+    {
+        const Plan &P = c->CH;
+        a.lanes = L->count;
+        a.alpha_arr = L->w; // w[0][lane]
+        a.s_jv = L->s_jv; a.s_mv = L->s_mv; a.s_vec = L->s_vec; a.s_hist = L->s_hist;
+        a.s_F = P.fac_doubles; a.s_Y = P.y_doubles; a.s_red = P.red_doubles; a.s_rv = P.rv_doubles; a.s_x = P.x_doubles;
+        a.lane_mode = L->mode; a.lane_hbase = L->hbase; a.lane_order = L->order; a.lane_w = L->w;
+        a.hist = L->hist; a.lane_flags = L->flags; a.lane_var = L->var; a.var_on = L->var_on; a.var_tol = L->var_tol;
+    }
     a.tol = c->pivot_tol;
     a.packed = c->chain_packed;
     a.prefetch = c->chain_prefetch;
@@ -810,7 +862,7 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g, bool fuse)
 template <class K> void launch_pdl(daecpp_b200_ctx *c, K kernel, const ChainArgs &a, int threads, size_t smem)
 {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(a.lv.ntiles + a.extra_factor, 1, 1);
+    cfg.gridDim = dim3(a.lv.ntiles + a.extra_factor, a.lanes > 0 ? a.lanes : 1, 1);
     cfg.blockDim = dim3(threads, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = c->stream;
@@ -916,7 +968,7 @@ int chain_refactor_async(daecpp_b200_ctx *c, double alpha)
         if (g == 0)
         {
             a.sj = c->dC.sj.p; a.sm = c->dC.sm.p; a.flags = c->dC.flags.p; a.desc = c->dC.desc.p;
-            a.jv = jv; a.mv = c->M.vals.p; a.alpha = alpha;
+            a.jv = c->lanes ? c->lanes->jv : jv; a.mv = c->lanes ? c->lanes->mv : c->M.vals.p; a.alpha = alpha;
         }
 #define LF(B) launch_factor<B>(c, a, g == 0)
         CHAIN_DISPATCH(P.B, LF)
@@ -941,7 +993,7 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         a.update = fuse_update ? 1 : 0;
         if (c->fuse_residual_now)
         {
-            a.fuse_res = 1; a.bdf = c->bdf_pending; a.mdiag = c->M.vals.p; a.fvec = c->f;
+            a.fuse_res = 1; a.bdf = c->bdf_pending; a.mdiag = c->lanes ? c->lanes->mv : c->M.vals.p; a.fvec = c->f;
             a.b_out = c->keep_b ? c->b : nullptr;
         }
         a.host_flags = c->publish_flags ? c->h_flags_dev + 2 : nullptr;

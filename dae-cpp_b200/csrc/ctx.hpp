@@ -92,6 +92,25 @@ struct DeviceChain
     }
 };
 
+// Lock-step batched ensemble (api: daecpp_b200_batch_*, batch.cu): `count` systems of the same pattern share
+// one plan; every per-system array of the chain path becomes [count][...] and the chain kernels take the
+// lane as blockIdx.y.  Per-lane control words are device arrays refreshed once per Newton round.
+struct LaneSet
+{
+    int32_t count = 0;
+    int64_t s_vec = 0, s_hist = 0, s_jv = 0, s_mv = 0;
+    double *hist = nullptr;                    // [4][count][s_vec] ring of accepted states; x[k] of a lane = slot (hbase + k) & 3
+    const int32_t *mode = nullptr;             // [count] DAECPP_B200_LANE_*
+    const int32_t *hbase = nullptr;            // [count]
+    const int32_t *order = nullptr;            // [count]
+    const double *w = nullptr;                 // [5][count] BDF weights, w[0] = alpha
+    int32_t *flags = nullptr;                  // [count][4]: update flags, pivot failure, wait time-out, spare
+    unsigned long long *var = nullptr;         // [count] bit pattern of the lane's maximum variability
+    const double *jv = nullptr, *mv = nullptr; // triplet values of J [count][s_jv], compressed values of M [count][s_mv]
+    int32_t var_on = 0;
+    double var_tol = 0.0;
+};
+
 struct GroupLaunch
 {
     int32_t kind = 0, begin = 0, count = 0;
@@ -156,6 +175,7 @@ struct daecpp_b200_ctx
     // pattern is recognised as a chain of blocks of order <= chain_max_b
     daecpp_b200::chain::Plan CH;
     daecpp_b200::DeviceChain dC;
+    const daecpp_b200::LaneSet *lanes = nullptr; // set by a batch context around its launches (batch.cu)
     bool chain_enabled = true, chain_affine = true;
     int chain_prefetch = 0;            // backward kernel: L2 prefetch of the tile's factors before the dependency wait
     int chain_packed = 1;              // contiguous-run staging of affine tiles (chain.cu), 0 = per-field strided copies

@@ -23,8 +23,13 @@
 #pragma once
 
 #include <dae-cpp/solver.hpp>
+#ifdef DAECPP_B200_H
+#include <dae-cpp/device-functor.hpp>
+#endif
 
+#include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstddef>
 #include <cstdlib>
 #include <thread>
@@ -112,5 +117,343 @@ ensemble_result solve_ensemble(std::size_t count, MemberFn member, unsigned thre
 {
     return solve_ensemble(0, count, member, threads);
 }
+
+#ifdef DAECPP_B200_H
+/*
+ * ---- lock-step batched ensembles (B200 only) ---------------------------------------------------------
+ *
+ * All members of a sweep share one sparsity pattern, so instead of one device context per member the
+ * members become LANES of one batch context (include/daecpp_b200.h: daecpp_b200_batch_*): every Newton
+ * round is one launch sequence for all lanes in flight.  Each lane keeps its own integrator state and makes
+ * its own step-size / order / refactorisation decisions -- `lane_control` below restates the decisions of
+ * the reference's time loop (dae-cpp/solver.hpp:402-797) as a state machine that is advanced once per
+ * round -- so exit code, accepted steps and final state of a member are those of a single daecpp::solve.
+ *
+ * Restrictions of this path (the thread-pool solve_ensemble above has none of them): one common pattern
+ * recognised as a block chain (banded systems), a mass matrix that does not change in time, no Solution
+ * Manager callbacks during the integration (the final state, exit code and step count are returned).
+ */
+namespace core
+{
+namespace detail
+{
+
+class lane_control
+{
+    const SolverOptions &m_opt;
+    std::vector<double> m_t_out;
+    std::size_t m_out{0};
+    bool m_in_time_loop{false};
+    double m_t1{0.0};
+
+    double m_dt[DAECPP_MAX_ORDER];
+    double m_t{0.0}, m_t_prev{0.0};
+    unsigned int m_order{1};
+    int m_iter{0};
+    bool m_fact{false};
+    int m_dt_increase_threshold{0}, m_dt_decrease_threshold{0}, m_max_Newton_iter{0};
+    uint64_t m_n_steps{0};
+    uint32_t m_n_iter_failed{0};
+    bool m_delay_timestep_inc{false};
+    int m_pending_pre{DAECPP_B200_LANE_KEEP};
+    bool m_done{false};
+    bool m_last_was_accept{false};
+
+    double &dt() { return m_dt[0]; }
+
+    // dae-cpp/solver.hpp:383-404 and the head of the time loop :402-408
+    void next_step()
+    {
+        for (;;)
+        {
+            if (!m_in_time_loop)
+            {
+                if (m_out >= m_t_out.size())
+                {
+                    status = exit_code::success;
+                    m_done = true;
+                    return;
+                }
+                m_t1 = m_t_out[m_out];
+                if (m_t1 <= 0.0) { ++m_out; continue; }
+                if (dt() > m_t1 - m_t)
+                {
+                    dt() = m_t1 - m_t;
+                    ASSERT(dt() > 0.0, "Negative or zero time step: dt = " << dt() << ".");
+                }
+                m_delay_timestep_inc = false;
+                m_in_time_loop = true;
+            }
+            if (m_t < m_t1)
+            {
+                m_t_prev = m_t;
+                m_t += dt();
+                m_n_steps++;
+                m_iter = 0;
+                return;
+            }
+            m_in_time_loop = false;
+            ++m_out;
+        }
+    }
+
+    // dae-cpp/solver.hpp:636-651
+    void shrink_and_rewind()
+    {
+        m_delay_timestep_inc = true;
+        m_t = m_t_prev;
+        m_n_steps--;
+        dt() /= m_opt.dt_decrease_factor;
+        m_pending_pre = DAECPP_B200_LANE_ROLLBACK;
+        m_last_was_accept = false;
+        if (dt() < m_opt.dt_min)
+        {
+            status = exit_code::diverged;
+            m_done = true;
+            return;
+        }
+        next_step();
+    }
+
+    // the Newton loop of this step has ended at iteration index `iter` (dae-cpp/solver.hpp:622-797)
+    void end_newton(bool diverged, double variability)
+    {
+        if (m_iter == m_max_Newton_iter) diverged = true; // "couldn't converge"
+        if (diverged)
+        {
+            m_n_iter_failed++;
+            shrink_and_rewind();
+            return;
+        }
+        // no Solution Manager on this path; the step is accepted
+        m_n_iter_failed = 0;
+        accepted_steps++;
+        m_pending_pre = DAECPP_B200_LANE_ACCEPT;
+        m_last_was_accept = true;
+        for (int k = DAECPP_MAX_ORDER - 1; k > 0; --k) m_dt[k] = m_dt[k - 1];
+        if ((m_iter >= m_dt_decrease_threshold) || (variability > m_opt.variability_threshold_high))
+        {
+            dt() /= m_opt.dt_decrease_factor;
+            if (dt() < m_opt.dt_min)
+            {
+                status = exit_code::diverged;
+                m_done = true;
+                return;
+            }
+        }
+        else if ((m_iter <= m_dt_increase_threshold - 1) && !m_delay_timestep_inc && (variability <= m_opt.variability_threshold_low))
+        {
+            dt() *= m_opt.dt_increase_factor;
+            if (dt() > m_opt.dt_max) dt() = m_opt.dt_max;
+        }
+        m_delay_timestep_inc = false;
+        if (dt() > m_t1 - m_t) dt() = m_t1 - m_t;
+        if (m_order < m_opt.BDF_order) m_order++;
+        if (dt() < m_opt.dt_min)
+        {
+            if (m_dt[2] > m_opt.dt_min) dt() = m_dt[2];
+            else if (m_dt[1] > m_opt.dt_min) dt() = m_dt[1];
+            else dt() = m_opt.dt_init;
+            m_in_time_loop = false; // leave the time loop of this output time
+            ++m_out;
+        }
+        next_step();
+    }
+
+public:
+    int status{exit_code::unknown};
+    long accepted_steps{0};
+    Counters count;
+
+    lane_control(const SolverOptions &opt, const std::vector<double> &t_out) : m_opt(opt), m_t_out(t_out)
+    {
+        std::fill(m_dt, m_dt + DAECPP_MAX_ORDER, 0.0);
+        m_dt_increase_threshold = 2 * (m_opt.Newton_scheme + 1) + m_opt.dt_increase_threshold_delta;
+        m_dt_decrease_threshold = 4 * (m_opt.Newton_scheme + 1) + m_opt.dt_decrease_threshold_delta;
+        ASSERT(m_dt_increase_threshold > 0, "Too small delta `dt_increase_threshold_delta`: " << m_opt.dt_increase_threshold_delta);
+        ASSERT(m_dt_decrease_threshold > 0, "Too small delta `dt_decrease_threshold_delta`: " << m_opt.dt_decrease_threshold_delta);
+        ASSERT(m_dt_decrease_threshold > m_dt_increase_threshold, "Adaptive time stepping thresholds are not consistent with each other.");
+        m_max_Newton_iter = m_opt.max_Jacobian_updates * (m_opt.Newton_scheme + 1);
+        dt() = m_opt.dt_init;
+        next_step();
+    }
+
+    bool done() const { return m_done; }
+    double time() const { return m_done && !m_last_was_accept ? m_t_prev : m_t; }
+    // the final state of a finished lane is its Newton iterate when the last event was an accepted step,
+    // the last accepted state x[0] otherwise
+    bool final_state_is_iterate() const { return m_last_was_accept; }
+
+    // what this lane does in the coming round (dae-cpp/solver.hpp:431-537)
+    void plan(daecpp_b200_lane_cmd &cmd)
+    {
+        cmd = daecpp_b200_lane_cmd{};
+        cmd.pre = m_pending_pre;
+        m_pending_pre = DAECPP_B200_LANE_KEEP;
+        if (m_done)
+        {
+            cmd.mode = DAECPP_B200_LANE_IDLE;
+            return;
+        }
+        m_fact = (m_n_iter_failed < m_opt.max_Newton_failed_attempts) ? !(m_iter % (m_opt.Newton_scheme + 1)) : true;
+        cmd.mode = m_fact ? DAECPP_B200_LANE_REFACTOR : DAECPP_B200_LANE_SOLVE;
+        cmd.order = static_cast<int32_t>(m_order);
+        cmd.t = m_t;
+        for (int k = 0; k < DAECPP_MAX_ORDER; ++k) cmd.dt[k] = m_dt[k];
+    }
+
+    // the outcome of that round (dae-cpp/solver.hpp:541-627)
+    void consume(const daecpp_b200_lane_result &res)
+    {
+        if (m_done) return;
+        if (m_fact) count.n_fact_calls++;
+        if (res.status == DAECPP_B200_EDECOMP || res.status == DAECPP_B200_ESOLVE)
+        {
+            if (m_opt.recover_from_linsolver_failure)
+            {
+                if (res.status == DAECPP_B200_ESOLVE) count.n_lin_calls++;
+                end_newton(true, 0.0);
+                return;
+            }
+            status = res.status == DAECPP_B200_EDECOMP ? exit_code::linsolver_failed_decomposition : exit_code::linsolver_failed_solving;
+            m_done = true;
+            return;
+        }
+        count.n_lin_calls++;
+        const bool diverged = (res.flags & DAECPP_B200_DIVERGED) != 0;
+        const bool converged = (res.flags & DAECPP_B200_NOT_CONVERGED) == 0;
+        const double variability = m_opt.solution_variability_control ? res.variability : 0.0;
+        if (converged || diverged)
+        {
+            end_newton(diverged, variability);
+            return;
+        }
+        if (++m_iter == m_max_Newton_iter) end_newton(false, variability);
+    }
+};
+
+} // namespace detail
+} // namespace core
+
+struct lockstep_stats
+{
+    long rounds{0};
+    double ms_device{0.0}; // CUDA-event time of all rounds
+    double ms_wall{0.0};
+    long lane_iterations{0}, lane_refactorisations{0};
+};
+
+/*
+ * Integrates eqs.size() members on [0, t_end] (or through every time of t_output) in lock step on one GPU.
+ *   Eq     -- device functor type of the equations (dae-cpp/device-functor.hpp), one object per member
+ *   shape  -- the non-zero elements of the Jacobian, shared by all members
+ *   mass   -- the usual host mass-matrix functor `mass(sparse_matrix &M, double t)`; evaluated once, at t = 0
+ *   x0     -- one initial state shared by all members, or one per member
+ * Needs nvcc for the translation unit (the equations are instantiated as kernels).
+ */
+template <class Eq, class Mass>
+ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::Shape &shape, Mass mass, const std::vector<state_vector> &x0,
+                                      const std::vector<double> &t_output, const SolverOptions &opt = SolverOptions(),
+                                      lockstep_stats *stats = nullptr)
+{
+    const std::size_t members = eqs.size();
+    ensemble_result R;
+    R.members.resize(members);
+    if (members == 0) return R;
+    ASSERT(x0.size() == 1 || x0.size() == members, "solve_ensemble_device: one initial state, or one per member.");
+    const std::size_t n = x0[0].size();
+    ASSERT(n > 0 && n <= 0x7fffffffu, "solve_ensemble_device: bad system size.");
+    opt.check();
+    std::vector<double> t_out(t_output);
+    std::sort(t_out.begin(), t_out.end());
+    t_out.erase(std::unique(t_out.begin(), t_out.end()), t_out.end());
+    ASSERT(!t_out.empty() && t_out.back() >= 0.0, "solve_ensemble_device: no (or a negative) target time.");
+
+    const auto wall0 = std::chrono::steady_clock::now();
+    int dev = 0;
+    if (const char *env = std::getenv("DAECPP_B200_DEVICE")) dev = std::atoi(env);
+    daecpp_b200_batch *b = nullptr;
+    int rc = daecpp_b200_batch_create(static_cast<int32_t>(n), static_cast<int32_t>(members), dev, &b);
+    if (rc) { ERROR("daecpp_b200: cannot create the batch context (code " << rc << "): " << daecpp_b200_batch_last_error(nullptr)); }
+    auto fatal = [&](const char *what, int code) { ERROR("daecpp_b200: " << what << " failed (code " << code << "): " << daecpp_b200_batch_last_error(b)); };
+
+    sparse_matrix M;
+    mass(M, 0.0);
+    M.check();
+    if ((rc = daecpp_b200_batch_set_pattern(b, shape.rows().data(), shape.cols().data(), static_cast<int64_t>(shape.size()), M.i.data(), M.j.data(),
+                                            static_cast<int64_t>(M.A.size()))))
+        fatal("batch_set_pattern", rc);
+    if ((rc = daecpp_b200_batch_set_mass_values(b, M.A.data(), 0, 0))) fatal("batch_set_mass_values", rc);
+    {
+        std::vector<double> slab(members * n);
+        for (std::size_t m = 0; m < members; ++m)
+        {
+            const state_vector &x = x0.size() == 1 ? x0[0] : x0[m];
+            ASSERT(x.size() == n, "solve_ensemble_device: initial states differ in size.");
+            std::copy(x.begin(), x.end(), slab.begin() + m * n);
+        }
+        if ((rc = daecpp_b200_batch_set_state(b, slab.data(), 0, static_cast<int32_t>(members)))) fatal("batch_set_state", rc);
+    }
+    device::DeviceFunctors<Eq> functors(eqs, shape);
+    daecpp_b200_device_functors fn = functors.binding();
+    if ((rc = daecpp_b200_batch_set_device_functors(b, &fn))) fatal("batch_set_device_functors", rc);
+
+    std::vector<core::detail::lane_control> lanes;
+    lanes.reserve(members);
+    for (std::size_t m = 0; m < members; ++m) lanes.emplace_back(opt, t_out);
+    std::vector<daecpp_b200_lane_cmd> cmd(members);
+    std::vector<daecpp_b200_lane_result> res(members);
+    lockstep_stats st;
+    for (;;)
+    {
+        std::size_t active = 0;
+        for (std::size_t m = 0; m < members; ++m)
+        {
+            lanes[m].plan(cmd[m]);
+            if (cmd[m].mode != DAECPP_B200_LANE_IDLE)
+            {
+                ++active;
+                st.lane_iterations++;
+                if (cmd[m].mode == DAECPP_B200_LANE_REFACTOR) st.lane_refactorisations++;
+            }
+        }
+        if (!active) break;
+        if ((rc = daecpp_b200_batch_round(b, cmd.data(), opt.atol, opt.rtol, opt.max_err_abs, opt.solution_variability_control ? 1 : 0,
+                                          opt.variability_tolerance, res.data())))
+            fatal("batch_round", rc);
+        st.rounds++;
+        for (std::size_t m = 0; m < members; ++m)
+            if (cmd[m].mode != DAECPP_B200_LANE_IDLE) lanes[m].consume(res[m]);
+    }
+    {   // final states: the iterate of lanes that ended on an accepted step, x[0] of the others
+        std::vector<double> xk(members * n), xa(members * n);
+        if ((rc = daecpp_b200_batch_get_vector(b, 3, xk.data(), 0, static_cast<int32_t>(members)))) fatal("batch_get_vector", rc);
+        bool need_x0 = false;
+        for (std::size_t m = 0; m < members; ++m) need_x0 = need_x0 || !lanes[m].final_state_is_iterate();
+        if (need_x0 && (rc = daecpp_b200_batch_get_vector(b, 4, xa.data(), 0, static_cast<int32_t>(members)))) fatal("batch_get_vector", rc);
+        for (std::size_t m = 0; m < members; ++m)
+        {
+            const double *src = (lanes[m].final_state_is_iterate() ? xk.data() : xa.data()) + m * n;
+            R.members[m].status = lanes[m].status;
+            R.members[m].steps = lanes[m].accepted_steps;
+            R.members[m].x.assign(src, src + n);
+            if (R.members[m].status != 0) R.failed++;
+        }
+    }
+    double v = 0.0;
+    if (daecpp_b200_batch_get_stat(b, "ms_device", &v) == DAECPP_B200_OK) st.ms_device = v;
+    daecpp_b200_batch_destroy(b);
+    st.ms_wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+    if (stats) *stats = st;
+    return R;
+}
+
+template <class Eq, class Mass>
+ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::Shape &shape, Mass mass, const std::vector<state_vector> &x0,
+                                      const double t_end, const SolverOptions &opt = SolverOptions(), lockstep_stats *stats = nullptr)
+{
+    return solve_ensemble_device(eqs, shape, mass, x0, std::vector<double>{t_end}, opt, stats);
+}
+#endif // DAECPP_B200_H
 
 } // namespace daecpp

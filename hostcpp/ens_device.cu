@@ -1,0 +1,126 @@
+// Driver of the device-functor / lock-step batched path (dae-cpp/ensemble.hpp: solve_ensemble_device).
+// The same file is compiled twice (hostcpp/Makefile):
+//   _bin/ens_device      nvcc, libdaecpp_b200.so          (the B200 path: equations instantiated as kernels)
+//   _bin/ens_device_emu  g++,  tests/emu/libbatchemu.so   (TEST ONLY: host loops + the oracle's arithmetic,
+//                                                          checks the host-side lane logic without a GPU)
+// Usage: ens_device ensemble|flame1d [key=value ...]
+//   ensemble: members (whole sweep), first, count (this process's block), n (perovskite N), t_end, out=<file>
+//   flame1d : n, t_end, out=<file>           (one lane: a single system integrated on the device)
+// Prints one JSON line.  Output file layout per member: {status, accepted steps, final state[n]} as f64.
+#include <dae-cpp/ensemble.hpp>
+
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+
+#include "problems_device.hpp"
+
+using namespace daecpp;
+
+namespace
+{
+double arg(const std::map<std::string, std::string> &kv, const char *key, double dflt)
+{
+    auto it = kv.find(key);
+    return it == kv.end() ? dflt : std::atof(it->second.c_str());
+}
+struct PerovskiteMass
+{
+    int N;
+    void operator()(sparse_matrix &M, const double) const
+    {
+        M.reserve(N);
+        for (int k = 0; k < N; ++k) M(k, k, 1.0);
+    }
+};
+int dump(const std::map<std::string, std::string> &kv, const ensemble_result &R)
+{
+    auto it = kv.find("out");
+    if (it == kv.end()) return 0;
+    FILE *fp = std::fopen(it->second.c_str(), "wb");
+    if (!fp) { std::perror("out"); return 65; }
+    for (const ensemble_member &m : R.members)
+    {
+        const double head[2] = {(double)m.status, (double)m.steps};
+        std::fwrite(head, sizeof(double), 2, fp);
+        std::fwrite(m.x.data(), sizeof(double), m.x.size(), fp);
+    }
+    std::fclose(fp);
+    return 0;
+}
+} // namespace
+
+int main(int argc, char **argv)
+{
+    if (argc < 2) { std::fprintf(stderr, "usage: ens_device ensemble|flame1d [key=value ...]\n"); return 64; }
+    const std::string wl = argv[1];
+    std::map<std::string, std::string> kv;
+    for (int a = 2; a < argc; ++a)
+    {
+        const char *eq = std::strchr(argv[a], '=');
+        if (eq) kv[std::string(argv[a], eq - argv[a])] = eq + 1;
+    }
+#if defined(__CUDACC__)
+    const char *impl = "b200-lockstep";
+#else
+    const char *impl = "emulated-lockstep";
+#endif
+    const int repeat = std::max(1, (int)arg(kv, "repeat", 1));
+    ensemble_result R;
+    lockstep_stats st;
+    std::size_t n = 0, members = 1, first = 0, count = 1;
+    double first_ms = 0.0;
+    for (int rep = 0; rep < repeat; ++rep)
+    {
+        if (wl == "ensemble")
+        {
+            members = (std::size_t)arg(kv, "members", 4096); first = (std::size_t)arg(kv, "first", 0);
+            count = (std::size_t)arg(kv, "count", (double)(members - first));
+            const int N = (int)arg(kv, "n", 4000);
+            n = 2 * (std::size_t)N;
+            std::vector<problems::PerovskiteEq> eqs;
+            for (std::size_t m = first; m < first + count; ++m)
+                eqs.push_back(problems::PerovskiteEq::make(N, 1.0, 0.5 * std::pow(4.0, members > 1 ? double(m) / double(members - 1) : 0.0)));
+            state_vector x0(n, 0.0);
+            for (int k = 0; k < N; ++k) x0[k] = 1.0;
+            SolverOptions o;
+            o.solution_variability_control = arg(kv, "variability", 0) != 0;
+            R = solve_ensemble_device(eqs, problems::perovskite_shape(N), PerovskiteMass{N}, std::vector<state_vector>{x0}, arg(kv, "t_end", 10.0), o, &st);
+        }
+        else if (wl == "flame1d")
+        {
+            const int nn = (int)arg(kv, "n", 1000000);
+            n = (std::size_t)nn;
+            const double t_end = arg(kv, "t_end", 50.0);
+            SolverOptions o;
+            o.dt_init = arg(kv, "dt_init", t_end / 100.0);
+            o.dt_increase_threshold_delta = -2;
+            o.variability_threshold_low = 0.10;
+            o.variability_threshold_high = 0.10;
+            o.is_mass_matrix_static = true;
+            o.solution_variability_control = arg(kv, "variability", 1) != 0;
+            std::vector<problems::Flame1DEq> eqs{problems::Flame1DEq::make(nn)};
+            R = solve_ensemble_device(eqs, problems::flame1d_shape(nn), MassMatrixIdentity(n), std::vector<state_vector>{problems::flame1d_initial(nn)}, t_end, o, &st);
+        }
+        else { std::fprintf(stderr, "unknown workload %s\n", wl.c_str()); return 64; }
+        if (rep == 0) first_ms = st.ms_wall;
+    }
+    long steps = 0;
+    double checksum = 0.0;
+    for (const ensemble_member &m : R.members)
+    {
+        steps += m.steps;
+        for (double v : m.x) checksum += v;
+    }
+    if (int rc = dump(kv, R)) return rc;
+    std::printf("{\"impl\": \"%s\", \"workload\": \"%s\", \"n\": %zu, \"members\": %zu, \"first\": %zu, \"count\": %zu, \"failed\": %d, "
+                "\"steps\": %ld, \"rounds\": %ld, \"lane_iterations\": %ld, \"lane_refactorisations\": %ld, \"wall_ms\": %.3f, "
+                "\"first_wall_ms\": %.3f, \"device_ms\": %.3f, \"systems_per_s\": %.6f, \"status0\": %d, \"checksum\": %.17g}\n",
+                impl, wl.c_str(), n, members, first, count, R.failed, steps, st.rounds, st.lane_iterations, st.lane_refactorisations, st.ms_wall,
+                first_ms, st.ms_device, 1e3 * double(count) / st.ms_wall, R.members.empty() ? -1 : R.members[0].status, checksum);
+    return R.failed ? 1 : 0;
+}

@@ -180,6 +180,95 @@ int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *ctx, int64_t *out, int64_t cap
  * fronts on the FP64 tensor cores, default 1; 0 = FP64 FMA tiles), "bf_pdl" (programmatic dependent launch between them).  Debug: "trace_units", "phase_timing", "pinned_io". */
 int daecpp_b200_set_option(daecpp_b200_ctx *ctx, const char *key, double value);
 
+/* ==== lock-step batched ensemble (an ADDITION: the reference has no ensemble API) =========
+ * `lanes` independent DAE systems of the same size and the same sparsity pattern (parameter sweeps) live
+ * in one batch context on one GPU.  One call of daecpp_b200_batch_round performs ONE Newton iteration of
+ * dae-cpp/solver.hpp:431-627 for every lane that asks for it: the kernels of the single-system path run
+ * with the lane as the outer grid dimension, each lane with its own BDF order / step history / alpha, its
+ * own matrix values, flags and factors, so a round costs one launch sequence and one flag read however
+ * many lanes are in flight.  The caller keeps one integrator state per lane (dae-cpp/solver.hpp:38-69,
+ * 402-797: dae-cpp/ensemble.hpp does) and tells every round what each lane does next.  Results of a lane are
+ * bit-identical to the same iteration run through a single-system context on the same inputs.
+ * Patterns the block-chain path does not take (2-D grids, arbitrary sparsity) and Jacobian triplet streams
+ * with duplicates are refused with DAECPP_B200_EINVAL: such ensembles run one context per member. */
+typedef struct daecpp_b200_batch daecpp_b200_batch;
+
+enum /* daecpp_b200_lane_cmd.mode */
+{
+    DAECPP_B200_LANE_IDLE = 0,     /* the lane sits this round out (finished, or waiting)                  */
+    DAECPP_B200_LANE_SOLVE = 1,    /* Newton iteration that reuses the lane's factors  (solver.hpp:533)    */
+    DAECPP_B200_LANE_REFACTOR = 2  /* Newton iteration with Jacobian update + refactorisation              */
+};
+enum /* daecpp_b200_lane_cmd.pre: applied to the lane before anything else of the round */
+{
+    DAECPP_B200_LANE_KEEP = 0,
+    DAECPP_B200_LANE_ACCEPT = 1,   /* x[3]<-x[2]<-x[1]<-x[0]<-xk   (solver.hpp:698-721)                    */
+    DAECPP_B200_LANE_ROLLBACK = 2  /* xk = x[0]                    (solver.hpp:643,671)                    */
+};
+typedef struct
+{
+    int32_t mode, pre, order, reserved;
+    double t;     /* time handed to the lane's functors (solver.hpp:432: state.t after the increment)    */
+    double dt[4]; /* SolverState::dt (solver.hpp:41)                                                      */
+} daecpp_b200_lane_cmd;
+typedef struct
+{
+    int32_t flags;      /* DAECPP_B200_DIVERGED | DAECPP_B200_NOT_CONVERGED of this round's iteration     */
+    int32_t status;     /* DAECPP_B200_OK, or DAECPP_B200_EDECOMP / DAECPP_B200_ESOLVE for this lane      */
+    double variability; /* max |(x[0] - xk_new) / x[0]| over the elements the reference looks at
+                           (solver.hpp:703-717), computed with the update: what accept_step would return */
+} daecpp_b200_lane_result;
+
+/* Device functors (opt-in).  The callbacks are given DEVICE pointers and the CUDA stream
+ * to launch on; they must only enqueue work on that stream and return 0.  dae-cpp/device-functor.cuh builds
+ * them from one templated equations(x, t, i) functor (the device twin of VectorFunctionElements +
+ * JacobianMatrixShape, vector-function.hpp:46-72, jacobian-matrix.hpp:66-92).  Lanes with mode[lane] below
+ * min_mode are skipped. */
+typedef struct
+{
+    int32_t n, lanes, min_mode, reserved;
+    int64_t x_stride, out_stride; /* elements between consecutive lanes                                     */
+    const double *x;              /* [lanes][x_stride]  Newton iterates xk                                   */
+    const double *t;              /* [lanes]                                                                 */
+    const int32_t *mode;          /* [lanes]                                                                 */
+    double *out;                  /* rhs: f [lanes][out_stride];  jacobian: triplet values [lanes][out_stride] */
+    void *stream;                 /* cudaStream_t                                                            */
+} daecpp_b200_functor_args;
+typedef int (*daecpp_b200_device_fn)(void *user, const daecpp_b200_functor_args *args);
+typedef struct
+{
+    void *user;
+    daecpp_b200_device_fn rhs;      /* f = rhs(xk, t)                          (solver.hpp:450-464)          */
+    daecpp_b200_device_fn jacobian; /* values of the Jacobian triplets, in the order of the (i, j) stream
+                                       given to daecpp_b200_batch_set_pattern (solver.hpp:499)              */
+} daecpp_b200_device_functors;
+
+int daecpp_b200_batch_create(int32_t n, int32_t lanes, int device, daecpp_b200_batch **out);
+void daecpp_b200_batch_destroy(daecpp_b200_batch *b);
+const char *daecpp_b200_batch_last_error(const daecpp_b200_batch *b);
+/* The (i, j) streams every lane's Jacobian / mass functor emits (sparse-matrix.hpp:36-56).  Sorts, builds the
+ * union pattern and runs the symbolic analysis once for all lanes. */
+int daecpp_b200_batch_set_pattern(daecpp_b200_batch *b, const int32_t *Ji, const int32_t *Jj, int64_t nTJ, const int32_t *Mi,
+                                  const int32_t *Mj, int64_t nTM);
+/* Triplet VALUES, lane-major host slabs [count][nT] for lanes [first, first + count).  count = 0 (mass only):
+ * one set of nTM values shared by all lanes. */
+int daecpp_b200_batch_set_mass_values(daecpp_b200_batch *b, const double *A, int32_t first, int32_t count);
+int daecpp_b200_batch_set_jacobian_values(daecpp_b200_batch *b, const double *A, int32_t first, int32_t count);
+int daecpp_b200_batch_set_rhs_values(daecpp_b200_batch *b, const double *f, int32_t first, int32_t count); /* [count][n] */
+/* xk = x[0] = x0, history cleared (solver.hpp:310-313);  x0: [count][n] */
+int daecpp_b200_batch_set_state(daecpp_b200_batch *b, const double *x0, int32_t first, int32_t count);
+/* which: same selectors as daecpp_b200_get_vector (0 b, 1 dx, 3 xk, 4..7 x[0..3]); out: [count][n] */
+int daecpp_b200_batch_get_vector(daecpp_b200_batch *b, int32_t which, double *out, int32_t first, int32_t count);
+/* NULL or all-NULL members: functor values come from set_rhs_values / set_jacobian_values */
+int daecpp_b200_batch_set_device_functors(daecpp_b200_batch *b, const daecpp_b200_device_functors *fn);
+/* One Newton round.  cmd, res: [lanes].  variability_on / variability_tolerance: SolverOptions
+ * solution_variability_control / variability_tolerance (solver.hpp:700-717). */
+int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cmd, double atol, double rtol, double max_err_abs,
+                            int32_t variability_on, double variability_tolerance, daecpp_b200_lane_result *res);
+/* "rounds", "kernels_launched", "chain_block", "chain_tiles", "ms_device" (CUDA-event time of all rounds so far),
+ * "bytes_per_lane" ... */
+int daecpp_b200_batch_get_stat(daecpp_b200_batch *b, const char *key, double *value);
+
 #ifdef __cplusplus
 }
 #endif

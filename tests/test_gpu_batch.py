@@ -1,0 +1,208 @@
+"""Lock-step batched ensemble on the device (include/daecpp_b200.h: daecpp_b200_batch_*).
+
+1. A lane of a batch is BIT-IDENTICAL to the same Newton iteration run through a single-system context on the
+   same inputs (same kernels, lane = blockIdx.y): iterate, dx, flags -- with refactorisation, with reused
+   factors, after an accepted step (history ring), after a rollback, with idle lanes in between.
+2. Whole ensembles through dae-cpp/ensemble.hpp: solve_ensemble_device (device functors, per-lane adaptive
+   stepping) against the unmodified reference member by member: exit code, accepted steps +-2 %, final state
+   within 10 x (atol, rtol)  (BASELINE.json north_star; SURVEY.md 8(c) definition 3).
+3. The device functors (dae-cpp/device-functor.hpp) against the host triplet streams of tests/problems.py.
+"""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import problems as P
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "hostcpp", "_bin")
+pytestmark = pytest.mark.gpu
+
+
+def _need(name):
+    exe = os.path.join(BIN, name)
+    if not os.path.exists(exe):
+        pytest.skip(f"{exe} not built (needs /root/reference at build time)")
+    return exe
+
+
+def _perovskite_case(N, lanes, seed):
+    r = np.random.default_rng(seed)
+    xs = [P.perovskite_state(N, seed + l) for l in range(lanes)]
+    Js = [P.perovskite_jacobian(x, N, lam=0.5 + 0.3 * l) for l, x in enumerate(xs)]
+    M = P.perovskite_mass(N)
+    fs = [r.standard_normal(2 * N) for _ in range(lanes)]
+    return 2 * N, xs, Js, M, fs
+
+
+def _flame_case(n, lanes, seed):
+    r = np.random.default_rng(seed)
+    xs = [np.clip(P.flame1d_state(n) + 0.01 * r.standard_normal(n), 1e-6, 1.0) for _ in range(lanes)]
+    Js = [P.flame1d_jacobian(x) for x in xs]
+    M = P.identity_mass(n)
+    fs = [P.flame1d_rhs(x) for x in xs]
+    return n, xs, Js, M, fs
+
+
+@pytest.mark.parametrize("case", ["perovskite_1tile", "perovskite_3tiles", "flame_3tiles"])
+def test_batch_lane_bit_identical_to_single_context(case):
+    from gpu_lib import binding as B
+    lanes = 4
+    if case == "perovskite_1tile":
+        n, xs, Js, M, fs = _perovskite_case(200, lanes, 1)
+    elif case == "perovskite_3tiles":
+        n, xs, Js, M, fs = _perovskite_case(700, lanes, 2)
+    else:
+        n, xs, Js, M, fs = _flame_case(5000, lanes, 3)
+    atol = rtol = 1e-6
+    lib = B.load()
+    b = B.Batch(n, lanes, 0, lib)
+    b.set_pattern(Js[0][1], Js[0][2], M[1], M[2])
+    b.set_mass_values(M[0])
+    b.set_state(np.stack(xs))
+    singles = []
+    for l in range(lanes):
+        c = B.Context(n, 0, lib)
+        c.set_state(xs[l]); c.set_mass(M); c.set_jacobian(Js[l])
+        singles.append(c)
+    assert b.stat("chain_block") == singles[0].stat("chain_block") > 0
+
+    def single_iter(l, f, refactor, order, dt):
+        c = singles[l]
+        c.residual(f, order, dt)  # uploads f (and forms b; the resident iteration forms it again)
+        rc, flags = c.iteration_resident(refactor, order, dt, atol, rtol, allow=(B.EDECOMP,))
+        return rc, flags
+
+    def compare(active):
+        xk, dx = b.get_vector("xk"), b.get_vector("dx")
+        for l in active:
+            assert xk[l].tobytes() == singles[l].get_vector("xk").tobytes(), f"lane {l}: iterate differs"
+            assert dx[l].tobytes() == singles[l].get_vector("dx").tobytes(), f"lane {l}: dx differs"
+
+    # round 1: every lane refactors, BDF-1, lane-dependent step size
+    dts = [np.array([1e-2 * (l + 1), 0, 0, 0.0]) for l in range(lanes)]
+    b.set_jacobian_values(np.stack([J[0] for J in Js])); b.set_rhs_values(np.stack(fs))
+    rc, res = b.round([dict(mode=B.LANE_REFACTOR, order=1, dt=dts[l]) for l in range(lanes)], atol, rtol)
+    for l in range(lanes):
+        rc1, fl1 = single_iter(l, fs[l], 1, 1, dts[l])
+        assert res[l][1] == rc1 == 0 and res[l][0] == fl1
+    compare(range(lanes))
+    # round 2: lanes 0 and 2 reuse their factors, lane 1 refactors with new values, lane 3 sits out
+    fs2 = [f * 0.5 for f in fs]
+    J1 = Js[1][0] * 1.01
+    b.set_rhs_values(np.stack(fs2)); b.set_jacobian_values(J1, 1, 1)
+    cmds = [dict(mode=B.LANE_SOLVE, order=1, dt=dts[0]), dict(mode=B.LANE_REFACTOR, order=1, dt=dts[1]),
+            dict(mode=B.LANE_SOLVE, order=1, dt=dts[2]), dict(mode=B.LANE_IDLE)]
+    x3_before = b.get_vector("xk")[3].copy()
+    rc, res = b.round(cmds, atol, rtol)
+    singles[1].set_jacobian((J1, Js[1][1], Js[1][2]))
+    for l, refac in ((0, 0), (1, 1), (2, 0)):
+        rc1, fl1 = single_iter(l, fs2[l], refac, 1, dts[l])
+        assert res[l][1] == rc1 == 0 and res[l][0] == fl1
+    compare((0, 1, 2))
+    assert b.get_vector("xk")[3].tobytes() == x3_before.tobytes() and res[3] == (0, 0, 0.0)
+    # round 3: lane 0 accepts its step and goes on at BDF-2 with the variability measured in the update,
+    # lane 2 rolls back, lanes 1 and 3 idle
+    dt2 = np.array([2e-2, dts[0][0], 0, 0.0])
+    b.set_rhs_values(fs[0], 0, 1); b.set_rhs_values(fs[2], 2, 1)
+    b.set_jacobian_values(Js[0][0], 0, 1); b.set_jacobian_values(Js[2][0], 2, 1)
+    cmds = [dict(mode=B.LANE_REFACTOR, pre=B.LANE_ACCEPT, order=2, dt=dt2), dict(mode=B.LANE_IDLE),
+            dict(mode=B.LANE_REFACTOR, pre=B.LANE_ROLLBACK, order=1, dt=dts[2]), dict(mode=B.LANE_IDLE)]
+    rc, res = b.round(cmds, atol, rtol, variability_on=True, var_tol=1e-4)
+    singles[0].accept_step(False); singles[2].rollback()
+    x0_old = singles[0].get_vector("x0")
+    rc1, fl1 = single_iter(0, fs[0], 1, 2, dt2)
+    assert res[0][1] == rc1 == 0 and res[0][0] == fl1
+    rc1, fl1 = single_iter(2, fs[2], 1, 1, dts[2])
+    assert res[2][1] == rc1 == 0 and res[2][0] == fl1
+    compare((0, 2))
+    for k in range(4):
+        assert b.get_vector(f"x{k}", 0, 1)[0].tobytes() == singles[0].get_vector(f"x{k}").tobytes()
+    # the variability the update reported is what accept_step measures afterwards (solver.hpp:703-717)
+    assert res[0][2] == singles[0].accept_step(True, 1e-4)
+    assert np.array_equal(singles[0].get_vector("x1"), x0_old)
+    for c in singles:
+        c.close()
+    b.close()
+
+
+def test_batch_refuses_what_it_cannot_take():
+    from gpu_lib import binding as B
+    lib = B.load()
+    m = 24
+    J = P.grid2d_jacobian(P.grid2d_state(m), m)
+    M = P.identity_mass(m * m)
+    b = B.Batch(m * m, 2, 0, lib)
+    assert b.set_pattern(J[1], J[2], M[1], M[2], allow=(B.EINVAL,)) == B.EINVAL  # a 2-D grid is no block chain
+    b.close()
+    n = 600
+    x = P.flame1d_state(n)
+    A, i, j = P.flame1d_jacobian(x)
+    b = B.Batch(n, 2, 0, lib)
+    assert b.set_pattern(np.concatenate([i, i[:5]]), np.concatenate([j, j[:5]]), *P.identity_mass(n)[1:], allow=(B.EINVAL,)) == B.EINVAL  # duplicates
+    b.close()
+
+
+def test_singular_lane_reports_decomposition_failure_and_leaves_the_others_alone():
+    from gpu_lib import binding as B
+    lib = B.load()
+    n, lanes = 3000, 3
+    x = P.flame1d_state(n)
+    A, i, j = P.flame1d_jacobian(x)
+    M = P.identity_mass(n)
+    b = B.Batch(n, lanes, 0, lib)
+    b.set_pattern(i, j, M[1], M[2]); b.set_mass_values(M[0]); b.set_state(np.stack([x] * lanes))
+    bad = A.copy()
+    bad[:] = 0.0  # J = 0 and alpha*M cancelled below: a zero matrix
+    Mz = np.zeros(n)
+    b.set_mass_values(np.stack([M[0], Mz, M[0]]), 0, 3)
+    b.set_jacobian_values(np.stack([A, bad, A])); b.set_rhs_values(np.stack([P.flame1d_rhs(x)] * lanes))
+    rc, res = b.round([dict(mode=B.LANE_REFACTOR, order=1, dt=[1e-2, 0, 0, 0])] * lanes, 1e-6, 1e-6)
+    assert rc == 0
+    assert res[1][1] == B.EDECOMP and res[0][1] == 0 and res[2][1] == 0
+    xk = b.get_vector("xk")
+    assert xk[0].tobytes() == xk[2].tobytes() and np.all(np.isfinite(xk[0]))
+    b.close()
+
+
+def _members(exe, args, out, members, n):
+    p = subprocess.run([exe, "ensemble", f"members={members}", "first=0", f"count={members}", f"n={n}", f"out={out}"] + args,
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900)
+    assert p.returncode == 0, p.stderr[-3000:]
+    info = json.loads(p.stdout.strip().splitlines()[-1])
+    data = np.fromfile(out, dtype=np.float64).reshape(members, 2 * n + 2)
+    os.remove(out)
+    return info, data
+
+
+@pytest.mark.parametrize("N,members", [(150, 16), (300, 12), (4000, 24)])
+def test_lockstep_ensemble_members_match_reference(tmp_path, N, members):
+    ref_info, ref = _members(_need("traj_dump_ref"), ["threads=8"], str(tmp_path / "ref.f64"), members, N)
+    info, got = _members(_need("ens_device"), [], str(tmp_path / "gpu.f64"), members, N)
+    assert info["impl"] == "b200-lockstep" and info["failed"] == 0
+    assert np.array_equal(got[:, 0], ref[:, 0])  # exit codes
+    assert np.all(np.abs(got[:, 1] - ref[:, 1]) <= np.maximum(0.02 * ref[:, 1], 0.5))  # accepted steps +-2 %
+    atol = rtol = 1e-6
+    err = np.abs(got[:, 2:] - ref[:, 2:])
+    assert np.all(err <= 10.0 * (atol + rtol * np.abs(ref[:, 2:]))), float(err.max())
+    assert info["rounds"] < info["lane_iterations"] / 2  # the lanes really shared their rounds
+
+
+def test_single_lane_device_functor_trajectory_matches_reference_golden(tmp_path):
+    """C3 (flame-1D, n = 20 000) integrated entirely on the device -- RHS and shape Jacobian by device functors,
+    state never on the host -- against the reference's golden trajectory."""
+    meta = json.load(open(os.path.join(ROOT, "tests", "golden", "traj_flame1d_20000.json")))
+    want = np.fromfile(os.path.join(ROOT, "tests", "golden", "traj_flame1d_20000.f64"))
+    out = str(tmp_path / "x.f64")
+    p = subprocess.run([_need("ens_device"), "flame1d", "n=20000", "t_end=5", f"out={out}"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-2000:]
+    info = json.loads(p.stdout.strip().splitlines()[-1])
+    got = np.fromfile(out)
+    assert got[0] == meta["status"] == 0
+    assert abs(got[1] - meta["steps"]) <= max(0.02 * meta["steps"], 0.5)
+    tol = 10.0 * meta["tol"]
+    assert np.all(np.abs(got[2:] - want) <= tol + tol * np.abs(want)), float(np.max(np.abs(got[2:] - want)))
+    assert info["lane_iterations"] == info["rounds"]
