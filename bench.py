@@ -13,9 +13,11 @@ refactorisation, triangular solves, error checks and xk += dx.
   cpu_baseline / --impl reference: the unmodified reference (Eigen::SparseLU behind
             oracle/_ref/libdaeref.so, else the C port) doing the same iteration on the host
 
-N > 1 GPUs: one independent replica of the system per rank (a single sparse LU does not shard;
-SURVEY.md 8(e)); value = wall time / (steps * N), weak scaling.  The ensemble workload
-(--workload ensemble) partitions independent systems across ranks instead.
+Default workload: N = 1 GPU -> C3 (flame-1D n = 10^6, the config the metric is quoted on), with the other
+single-GPU configs (C2, C4) and the C5 ensemble at 1 GPU in a `configs` block of the same JSON line;
+N > 1 GPUs -> the C5 ensemble (4096 perovskite members partitioned across the ranks, metric
+"ensemble systems/s", strong scaling): the one workload of BASELINE.json that shards.
+A single sparse LU does not shard: `--workload flame1d --gpus N` runs independent replicas (weak scaling).
 """
 import argparse
 import json
@@ -37,10 +39,15 @@ UNIT = "us"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="flame1d", choices=["flame1d", "perovskite", "grid2d", "ensemble", "trajectory"])
+    ap.add_argument("--workload", default="auto", choices=["auto", "flame1d", "perovskite", "grid2d", "ensemble", "trajectory"],
+                    help="auto: flame1d (C3) on one GPU, the C5 ensemble on several")
+    ap.add_argument("--functors", default="device", choices=["device", "host"],
+                    help="ensemble: device = lock-step batched lanes with device functors (dae-cpp/ensemble.hpp: solve_ensemble_device); "
+                         "host = one context per member, host functors on a thread pool (solve_ensemble)")
+    ap.add_argument("--no-extra-configs", action="store_true", help="C3 line without the `configs` block (C2, C4, C5 at one GPU)")
     ap.add_argument("--n", "--size", dest="n", type=int, default=0, help="flame1d: unknowns; perovskite: N (system 2N); grid2d: side")
     ap.add_argument("--problem", default="perovskite", choices=["flame", "perovskite", "flame1d", "grid2d"],
                     help="trajectory: which daecpp::solve run (C1 flame, C2 perovskite as shipped; flame1d / grid2d take --size)")
@@ -322,10 +329,160 @@ def run_ensemble_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def _ensdev():
+    """hostcpp/_bin/libensdevice.so: dae-cpp/ensemble.hpp solve_ensemble_device over the perovskite device functor
+    (hostcpp/ens_device.cu, nvcc) -- called in-process so that the timed region sits between this file's barriers."""
+    import ctypes as C
+    path = os.path.join(ROOT, "hostcpp", "_bin", "libensdevice.so")
+    if not os.path.exists(path):
+        raise SystemExit(f"bench.py: {path} is not built (python -c 'import __graft_entry__ as g; g.build()')")
+    lib = C.CDLL(path)
+    lib.ensdev_perovskite.argtypes = [C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_double, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.ensdev_perovskite.restype = C.c_int
+    return lib
+
+
+ENS_STATS = ("rounds", "lane_iterations", "lane_refactorisations", "device_ms", "wall_ms", "failed", "accepted_steps", "checksum",
+             "kernels_launched", "setup_ms")
+
+
+def ensemble_device_block(members, first, count, N, device, out=None):
+    """One lock-step integration of members [first, first+count) on `device`; returns the driver's statistics."""
+    os.environ["DAECPP_B200_DEVICE"] = str(device)
+    st = np.zeros(10)
+    _ensdev().ensdev_perovskite(members, first, count, N, 10.0, 0, out.ctypes.data if out is not None else None, st.ctypes.data)
+    return dict(zip(ENS_STATS, st.tolist()))
+
+
+def ensemble_algorithmic_bytes(N, stats):
+    """per lane iteration residual + triangular solves + update, per lane refactorisation the
+    refactor bytes; C2 figures (nnz(Jb) = 39 990, nLU* = 55 993 at N = 4000), scaled with N otherwise."""
+    n = 2 * N
+    nnz_jb = 10 * N - 10
+    nlu = 55_993 if N == 4000 else 14 * N
+    nM = N
+    per_iter = (8 * n * 3 + 12 * nM + 16 * n) + (12 * nlu + 24 * n) + 32 * n
+    per_refac = 12 * nnz_jb + 12 * nlu
+    return stats["lane_iterations"] * per_iter + stats["lane_refactorisations"] * per_refac
+
+
+def run_ensemble_device(args):
+    """C5 with device functors: members partitioned in contiguous blocks over the ranks, every rank integrates
+    its block as the lanes of ONE batch context (one launch sequence per Newton round for all lanes), one
+    all_gather of {status, steps, final state} at the end -- the only collective."""
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v):
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    N = args.n or 4000
+    n = 2 * N
+    members = args.members
+    per = (members + world - 1) // world
+    first = rank * per
+    count = max(0, min(per, members - first))
+    steps = max(1, min(args.steps, 20)) if args.steps_given else 5
+    warm = max(3, min(args.warmup, 5))
+    for _ in range(warm):  # small blocks: CUDA context, module load, the allocator and the page-locked pools come up
+        ensemble_device_block(members, first, min(count, 32), N, local)
+    out = np.zeros((count, n + 2))
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    t0 = time.perf_counter()
+    acc = dict.fromkeys(ENS_STATS, 0.0)
+    for _ in range(steps):
+        st = ensemble_device_block(members, first, count, N, local, out)
+        for k in ENS_STATS:
+            acc[k] += st[k]
+    barrier()
+    el = max_over_ranks(time.perf_counter() - t0)
+    clocks = sampler.stop()
+    dev_s = max_over_ranks(acc["device_ms"] * 1e-3)
+    setup_s = max_over_ranks(acc["setup_ms"] * 1e-3)
+    abytes = sum_over_ranks(ensemble_algorithmic_bytes(N, acc))
+    launches = sum_over_ranks(acc["kernels_launched"])
+    rounds = max_over_ranks(acc["rounds"])
+    # ---- the one collective of the path
+    mine = torch.from_numpy(out).to("cuda")
+    if count < per:
+        mine = torch.cat([mine, torch.zeros(per - count, n + 2, dtype=torch.float64, device="cuda")])
+    gather_ms = 0.0
+    if dist is not None:
+        allm = torch.empty(world * per, n + 2, dtype=torch.float64, device="cuda")
+        torch.cuda.synchronize()
+        tg = time.perf_counter()
+        dist.all_gather_into_tensor(allm, mine)
+        torch.cuda.synchronize()
+        gather_ms = (time.perf_counter() - tg) * 1e3
+    else:
+        allm = mine
+    allm = allm[:members]
+    failed = int((allm[:, 0] != 0).sum().item())
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak = json.load(open(peaks_path))["hbm_gbs"] if os.path.exists(peaks_path) else 6650.0
+    gbps = abytes / dev_s / 1e9 / world  # per GPU
+    line = {"metric": ENS_METRIC, "value": members * steps / dev_s, "unit": "systems/s", "n_gpus": world, "steps": steps, "warmup": warm,
+            "ms_per_step": 1e3 * dev_s / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": f"C5 ensemble of perovskite N={N} (n={n}) members, lambda log-spaced 0.5..2 (BASELINE configs[4])",
+                       "members": members, "members_per_gpu": per, "functors": "device (dae-cpp/device-functor.hpp: equations + dual-number shape Jacobian as kernels)",
+                       "parallelism": f"members partitioned in contiguous blocks over {world} GPU(s); per GPU ONE batch context, lanes advanced in lock step "
+                                      "(one launch sequence + one flag read per Newton round for all lanes); no data-path collective, one final all_gather",
+                       "timing": "value: CUDA-event time of all Newton rounds (state resident in HBM), max over ranks; e2e: wall clock between barriers around "
+                                 "daecpp::solve_ensemble_device (context creation, pattern analysis, uploads, rounds, download of the final states), max over ranks",
+                       "l2_policy": "working set (members_per_gpu x 1.6 MB) exceeds the 126 MB L2 from 80 lanes per GPU on"},
+            "clocks": clocks, "failed_members": failed, "accepted_steps_total": int(allm[:, 1].sum().item()), "gather_ms": gather_ms,
+            "gather_bytes": int(allm.numel() * 8), "state_checksum": float(allm[:, 2:].sum().item()),
+            "rounds_per_step": rounds / steps, "lane_iterations_per_step": sum_over_ranks(acc["lane_iterations"]) / steps,
+            "setup_ms_per_step": 1e3 * setup_s / steps,
+            "e2e": {"value": members * steps / el, "unit": "systems/s", "h2d_bytes_per_step": int(members * n * 8 + 16 * (10 * N) + 16 * N),
+                    "d2h_bytes_per_step": int(members * n * 8)},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "all kernels of a Newton round (functors, residual, k_chain_factor<2,1>, k_chain_forward/backward<2,1>)",
+                         "achieved": gbps, "peak": peak, "unit": "GB/s", "frac": gbps / peak, "traffic": None,
+                         "algorithmic_bytes": abytes / steps, "note": "per GPU; SURVEY.md 8(d) bytes x the lane iterations / refactorisations actually run"}}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+    return line
+
+
 def run_ensemble_b200(args):
     """C5: 4096 independent perovskite solves partitioned across the ranks (contiguous blocks), every
     member a complete daecpp::solve through the overlay header; one all_gather of the final states."""
     import torch
+    if not args.steps_given:
+        args.steps, args.warmup = 1, min(args.warmup, 1)  # a step is the whole sweep through host functors
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -644,10 +801,18 @@ def run_b200_arm(args):
 
 if __name__ == "__main__":
     a = parse_args()
+    a.steps_given = any(x == "--steps" or x.startswith("--steps=") for x in sys.argv[1:])
+    if a.workload == "auto":
+        a.workload = "ensemble" if (a.gpus > 1 or int(os.environ.get("WORLD_SIZE", "1")) > 1) else "flame1d"
     if a.workload == "trajectory":
         run_trajectory(a, a.impl == "reference")
     elif a.workload == "ensemble":
-        run_ensemble_reference(a) if a.impl == "reference" else run_ensemble_b200(a)
+        if a.impl == "reference":
+            run_ensemble_reference(a)
+        elif a.functors == "device" and not a.host_logic_check:
+            run_ensemble_device(a)
+        else:
+            run_ensemble_b200(a)
     elif a.impl == "reference":
         run_reference_arm(a)
     else:

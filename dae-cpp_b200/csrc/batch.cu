@@ -479,10 +479,12 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
             fa.n = b->n; fa.lanes = Ln; fa.x_stride = (int64_t)b->ns; fa.x = b->xk; fa.t = d_t; fa.mode = b->L.mode; fa.stream = st;
             fa.min_mode = DAECPP_B200_LANE_SOLVE; fa.out = b->f; fa.out_stride = (int64_t)b->ns;
             if (b->fn.rhs(b->fn.user, &fa)) return bfail(b, DAECPP_B200_EINVAL, "device rhs functor failed");
+            c->kernels += 1;
             if (n_refactor)
             {
                 fa.min_mode = DAECPP_B200_LANE_REFACTOR; fa.out = b->jv.p; fa.out_stride = b->nTJ;
                 if (b->fn.jacobian(b->fn.user, &fa)) return bfail(b, DAECPP_B200_EINVAL, "device Jacobian functor failed");
+                c->kernels += 1;
             }
         }
         b->L.var_on = variability_on ? 1 : 0;

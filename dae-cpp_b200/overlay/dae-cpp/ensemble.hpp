@@ -30,7 +30,9 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <cmath>
 #include <cstddef>
+#include <cstdio>
 #include <cstdlib>
 #include <thread>
 #include <utility>
@@ -341,6 +343,8 @@ struct lockstep_stats
     double ms_device{0.0}; // CUDA-event time of all rounds
     double ms_wall{0.0};
     long lane_iterations{0}, lane_refactorisations{0};
+    double kernels_launched{0.0};
+    double ms_setup{0.0}; // batch creation, pattern analysis, uploads (before the first round)
 };
 
 /*
@@ -370,6 +374,7 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     ASSERT(!t_out.empty() && t_out.back() >= 0.0, "solve_ensemble_device: no (or a negative) target time.");
 
     const auto wall0 = std::chrono::steady_clock::now();
+    double st_setup_ms = 0.0;
     int dev = 0;
     if (const char *env = std::getenv("DAECPP_B200_DEVICE")) dev = std::atoi(env);
     daecpp_b200_batch *b = nullptr;
@@ -398,12 +403,15 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     daecpp_b200_device_functors fn = functors.binding();
     if ((rc = daecpp_b200_batch_set_device_functors(b, &fn))) fatal("batch_set_device_functors", rc);
 
+    st_setup_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
     std::vector<core::detail::lane_control> lanes;
     lanes.reserve(members);
     for (std::size_t m = 0; m < members; ++m) lanes.emplace_back(opt, t_out);
     std::vector<daecpp_b200_lane_cmd> cmd(members);
     std::vector<daecpp_b200_lane_result> res(members);
     lockstep_stats st;
+    long trace_lane = -1; // debug: DAECPP_B200_TRACE_LANE=<lane> prints that lane's rounds to stderr
+    if (const char *env = std::getenv("DAECPP_B200_TRACE_LANE")) trace_lane = std::atol(env);
     for (;;)
     {
         std::size_t active = 0;
@@ -422,6 +430,25 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
                                           opt.variability_tolerance, res.data())))
             fatal("batch_round", rc);
         st.rounds++;
+        if (trace_lane >= 0 && (std::size_t)trace_lane < members && cmd[trace_lane].mode != DAECPP_B200_LANE_IDLE)
+            std::fprintf(stderr, "lane %ld round %ld: t=%.10g dt=%.6g order=%d mode=%d pre=%d -> flags=%d status=%d var=%.3g\n", trace_lane, st.rounds,
+                         cmd[trace_lane].t, cmd[trace_lane].dt[0], cmd[trace_lane].order, cmd[trace_lane].mode, cmd[trace_lane].pre, res[trace_lane].flags,
+                         res[trace_lane].status, res[trace_lane].variability);
+        if (trace_lane >= 0 && (std::size_t)trace_lane < members && cmd[trace_lane].mode != DAECPP_B200_LANE_IDLE && std::getenv("DAECPP_B200_TRACE_DX"))
+        {
+            std::vector<double> dx(n), xa(n);
+            daecpp_b200_batch_get_vector(b, 1, dx.data(), (int32_t)trace_lane, 1);
+            daecpp_b200_batch_get_vector(b, 4, xa.data(), (int32_t)trace_lane, 1);
+            std::size_t ia = 0, ir = 0;
+            double ma = 0, mr = 0;
+            for (std::size_t k = 0; k < n; ++k)
+            {
+                const double e = std::fabs(dx[k]), a = std::fabs(xa[k]);
+                if (e > ma) { ma = e; ia = k; }
+                if (a > 1e-14 && e / a > mr) { mr = e / a; ir = k; }
+            }
+            std::fprintf(stderr, "    max|dx| = %.3e at %zu (x0 = %.3e)   max rel = %.3e at %zu (x0 = %.3e, dx = %.3e)\n", ma, ia, xa[ia], mr, ir, xa[ir], dx[ir]);
+        }
         for (std::size_t m = 0; m < members; ++m)
             if (cmd[m].mode != DAECPP_B200_LANE_IDLE) lanes[m].consume(res[m]);
     }
@@ -442,6 +469,8 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     }
     double v = 0.0;
     if (daecpp_b200_batch_get_stat(b, "ms_device", &v) == DAECPP_B200_OK) st.ms_device = v;
+    if (daecpp_b200_batch_get_stat(b, "kernels_launched", &v) == DAECPP_B200_OK) st.kernels_launched = v;
+    st.ms_setup = st_setup_ms;
     daecpp_b200_batch_destroy(b);
     st.ms_wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
     if (stats) *stats = st;

@@ -54,6 +54,48 @@ int dump(const std::map<std::string, std::string> &kv, const ensemble_result &R)
 }
 } // namespace
 
+// In-process entry for bench.py (ctypes): integrates members [first, first + count) of the C5 sweep
+// (perovskite, lambda_m = 0.5 * 4^(m / (members - 1))) in lock step on the device named by DAECPP_B200_DEVICE.
+// out: [count][2N + 2] = {status, accepted steps, final state} per member (may be NULL);
+// stats[10]: {rounds, lane iterations, lane refactorisations, device ms, wall ms, failed members, accepted steps, checksum,
+//             kernels launched, setup ms}
+extern "C" int ensdev_perovskite(int64_t members, int64_t first, int64_t count, int32_t N, double t_end, int32_t variability, double *out,
+                                 double *stats)
+{
+    const std::size_t n = 2 * (std::size_t)N;
+    std::vector<problems::PerovskiteEq> eqs;
+    for (int64_t m = first; m < first + count; ++m)
+        eqs.push_back(problems::PerovskiteEq::make(N, 1.0, 0.5 * std::pow(4.0, members > 1 ? double(m) / double(members - 1) : 0.0)));
+    state_vector x0(n, 0.0);
+    for (int k = 0; k < N; ++k) x0[k] = 1.0;
+    SolverOptions o;
+    o.solution_variability_control = variability != 0;
+    lockstep_stats st;
+    ensemble_result R = solve_ensemble_device(eqs, problems::perovskite_shape(N), PerovskiteMass{N}, std::vector<state_vector>{x0}, t_end, o, &st);
+    long steps = 0;
+    double checksum = 0.0;
+    for (std::size_t k = 0; k < R.members.size(); ++k)
+    {
+        const ensemble_member &m = R.members[k];
+        steps += m.steps;
+        for (double v : m.x) checksum += v;
+        if (out)
+        {
+            double *row = out + k * (n + 2);
+            row[0] = (double)m.status; row[1] = (double)m.steps;
+            std::copy(m.x.begin(), m.x.end(), row + 2);
+        }
+    }
+    if (stats)
+    {
+        stats[0] = (double)st.rounds; stats[1] = (double)st.lane_iterations; stats[2] = (double)st.lane_refactorisations; stats[3] = st.ms_device;
+        stats[4] = st.ms_wall; stats[5] = (double)R.failed; stats[6] = (double)steps; stats[7] = checksum;
+        stats[8] = st.kernels_launched; stats[9] = st.ms_setup;
+    }
+    return R.failed;
+}
+
+#ifndef ENSDEV_NO_MAIN
 int main(int argc, char **argv)
 {
     if (argc < 2) { std::fprintf(stderr, "usage: ens_device ensemble|flame1d [key=value ...]\n"); return 64; }
@@ -124,3 +166,4 @@ int main(int argc, char **argv)
                 first_ms, st.ms_device, 1e3 * double(count) / st.ms_wall, R.members.empty() ? -1 : R.members[0].status, checksum);
     return R.failed ? 1 : 0;
 }
+#endif // ENSDEV_NO_MAIN
