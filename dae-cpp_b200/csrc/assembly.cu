@@ -345,4 +345,36 @@ int build_mass_csr(daecpp_b200_ctx *c)
     return classify_mass(c);
 }
 
+// Row-major view of J's compressed-column slots (same construction as build_mass_csr), built on first use by
+// the refinement step and cached per pattern.
+int build_jac_csr(daecpp_b200_ctx *c)
+{
+    TripletSet &J = c->J;
+    if (!J.have_pattern) { c->err = "no Jacobian pattern"; return DAECPP_B200_EINVAL; }
+    if (c->j_csr_version == J.pattern_version) return DAECPP_B200_OK;
+    const int32_t n = c->n;
+    cudaStream_t st = c->stream;
+    DAECPP_CUDA_TRY(c, c->j_rowptr.reserve((size_t)n + 1));
+    if (J.nnz == 0)
+        DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->j_rowptr.p, 0, sizeof(int32_t) * ((size_t)n + 1), st));
+    else
+    {
+        DAECPP_CUDA_TRY(c, c->keys_a.reserve(J.nnz));
+        DAECPP_CUDA_TRY(c, c->pay_a.reserve(J.nnz));
+        DAECPP_CUDA_TRY(c, c->j_rowslot.reserve(J.nnz));
+        DAECPP_CUDA_TRY(c, c->j_rowcol.reserve(J.nnz));
+        k_slot_keys<<<blocks_for(n), TPB, 0, st>>>(J.outer.p, J.inner.p, n, c->keys_a.p, c->pay_a.p, 0, 1);
+        int32_t nseg = 0;
+        int rc = sort_and_scan(c, J.nnz, n, &nseg);
+        if (rc) return rc;
+        k_segments<<<blocks_for(J.nnz), TPB, 0, st>>>(c->keys_b.p, c->scan.p, J.nnz, n, nullptr, nullptr, c->j_rowptr.p);
+        k_csr_cols<<<blocks_for(J.nnz), TPB, 0, st>>>(c->keys_b.p, J.nnz, c->j_rowcol.p);
+        DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->j_rowslot.p, c->pay_b.p, sizeof(int32_t) * J.nnz, cudaMemcpyDeviceToDevice, st));
+        c->kernels += 3;
+        DAECPP_CUDA_TRY(c, cudaGetLastError());
+    }
+    c->j_csr_version = J.pattern_version;
+    return DAECPP_B200_OK;
+}
+
 } // namespace daecpp_b200

@@ -30,6 +30,8 @@ struct daecpp_b200_batch
     double *slab = nullptr;       // xk, f, b, dx [lanes][ns] each, then the history ring [4][lanes][ns]
     double *xk = nullptr, *f = nullptr, *b = nullptr, *dx = nullptr, *hist = nullptr;
     double *proto_xk = nullptr, *proto_f = nullptr, *proto_b = nullptr, *proto_dx = nullptr;
+    DevBuf<double> refine_buf;    // residual and correction of the guarded refinement step, [2][lanes][ns], on first use
+    double n_refine_rounds = 0, n_refined_lanes = 0;
     DevBuf<double> jv, mv;        // triplet values of J [lanes][nTJ]; compressed-column values of M [lanes][nnzM]
     int64_t nTJ = 0, nTM = 0, nnzM = 0;
     std::vector<int32_t> m_src, m_src_ptr; // mass: triplets of every slot in input order (host copy)
@@ -164,7 +166,7 @@ void release(daecpp_b200_batch *b)
         daecpp_b200_destroy(b->c);
     }
     if (b->slab) cudaFree(b->slab);
-    b->jv.release(); b->mv.release();
+    b->jv.release(); b->mv.release(); b->refine_buf.release();
     if (b->h_ctl) cudaFreeHost(b->h_ctl);
     if (b->d_ctl) cudaFree(b->d_ctl);
     if (b->h_res) cudaFreeHost(b->h_res);
@@ -516,8 +518,53 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
         if (rc) return bfail(b, rc, c->err);
     }
     BATCH_TRY(b, cudaMemcpyAsync(b->h_res, b->d_res, b->res_bytes, cudaMemcpyDeviceToHost, st));
-    BATCH_TRY(b, cudaEventRecord(b->ev1, st));
     BATCH_TRY(b, cudaStreamSynchronize(st));
+    if (n_active > 0 && c->refine_steps > 0)
+    {   // guarded refinement (api.cu: wants_refinement) for the lanes whose update failed the convergence test only on
+        // elements below the refinement floor: a second, small pass over those lanes
+        const int32_t *fl0 = reinterpret_cast<const int32_t *>(b->h_res);
+        int n_ref = 0;
+        for (int32_t l = 0; l < Ln; ++l)
+        {
+            const int32_t f = fl0[4 * l];
+            const bool want = cmd[l].mode != DAECPP_B200_LANE_IDLE && fl0[4 * l + 1] == 0 && (f & DAECPP_B200_NOT_CONVERGED) &&
+                              !(f & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED));
+            b->ctl_mode()[l] = want ? DAECPP_B200_LANE_SOLVE : DAECPP_B200_LANE_IDLE;
+            b->ctl_pre()[l] = DAECPP_B200_LANE_KEEP;
+            n_ref += want ? 1 : 0;
+        }
+        if (n_ref)
+        {
+            std::vector<int32_t> keep(fl0, fl0 + 4 * (size_t)Ln);
+            std::vector<unsigned long long> keep_var((size_t)Ln);
+            std::memcpy(keep_var.data(), b->h_res + sizeof(int32_t) * 4 * (size_t)Ln, sizeof(unsigned long long) * (size_t)Ln);
+            const size_t per = (size_t)Ln * b->ns;
+            BATCH_TRY(b, b->refine_buf.reserve(2 * per));
+            b->L.refine_r = b->refine_buf.p; b->L.refine_e = b->refine_buf.p + per;
+            BATCH_TRY(b, cudaMemcpyAsync(b->d_ctl, b->h_ctl, b->ctl_bytes, cudaMemcpyHostToDevice, st));
+            c->lanes = &b->L;
+            c->xk = b->xk; c->f = b->f; c->b = b->b; c->dx = b->dx;
+            const int rc = refine_last_solve(c, 0.0, atol, rtol, max_err_abs, !(c->m_diag && c->chain_fuse_residual));
+            c->lanes = nullptr;
+            c->xk = b->proto_xk; c->f = b->proto_f; c->b = b->proto_b; c->dx = b->proto_dx;
+            if (rc) return bfail(b, rc, c->err);
+            BATCH_TRY(b, cudaMemcpyAsync(b->h_res, b->d_res, b->res_bytes, cudaMemcpyDeviceToHost, st));
+            BATCH_TRY(b, cudaStreamSynchronize(st));
+            // lanes that were not refined keep the results of the round
+            int32_t *fl1 = reinterpret_cast<int32_t *>(b->h_res);
+            unsigned long long *var1 = reinterpret_cast<unsigned long long *>(b->h_res + sizeof(int32_t) * 4 * (size_t)Ln);
+            for (int32_t l = 0; l < Ln; ++l)
+                if (b->ctl_mode()[l] == DAECPP_B200_LANE_IDLE)
+                {
+                    for (int k = 0; k < 4; ++k) fl1[4 * l + k] = keep[4 * (size_t)l + k];
+                    var1[l] = keep_var[l];
+                }
+            b->n_refine_rounds += 1;
+            b->n_refined_lanes += n_ref;
+        }
+    }
+    BATCH_TRY(b, cudaEventRecord(b->ev1, st));
+    BATCH_TRY(b, cudaEventSynchronize(b->ev1));
     {
         float ms = 0;
         if (cudaEventElapsedTime(&ms, b->ev0, b->ev1) == cudaSuccess) b->ms_device += ms;
@@ -528,7 +575,7 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
     for (int32_t l = 0; l < Ln; ++l)
     {
         daecpp_b200_lane_result &r = res[l];
-        r.flags = fl[4 * l];
+        r.flags = fl[4 * l] & (DAECPP_B200_DIVERGED | DAECPP_B200_NOT_CONVERGED);
         r.status = DAECPP_B200_OK;
         if (cmd[l].mode != DAECPP_B200_LANE_IDLE && fl[4 * l + 1]) r.status = DAECPP_B200_EDECOMP;
         double v;
@@ -546,6 +593,8 @@ int daecpp_b200_batch_get_stat(daecpp_b200_batch *b, const char *key, double *va
     if (k == "rounds") *value = b->rounds;
     else if (k == "ms_device") *value = b->ms_device;
     else if (k == "lanes") *value = b->lanes;
+    else if (k == "refine_rounds") *value = b->n_refine_rounds;
+    else if (k == "refined_lanes") *value = b->n_refined_lanes;
     else if (k == "bytes_per_lane")
         *value = 8.0 * (8.0 * (double)b->ns + (double)b->nTJ + (double)b->nnzM + (double)(b->c->CH.fac_doubles + b->c->CH.y_doubles + b->c->CH.red_doubles + b->c->CH.rv_doubles + b->c->CH.x_doubles));
     else return daecpp_b200_get_stat(b->c, key, value);

@@ -54,7 +54,7 @@ struct ChainArgs
     const int32_t *perm;
     double *out, *xk;
     const double *x0;
-    double atol, rtol, max_err_abs;
+    double atol, rtol, max_err_abs, floor;
     int32_t update;
     int32_t *dflags;
     // fused residual (diagonal mass): rhs = M*dxdt - f formed while staging (vector_ops.cu: k_residual_diag)
@@ -339,8 +339,8 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
                 {   // dae-cpp/solver.hpp:590-619
                     const double e = fabs(v[u]), ax = fabs(xa[u]);
                     if (e > a.max_err_abs || isnan(v[u])) flag |= DAECPP_B200_DIVERGED;
-                    if (ax > 1e-14 && __ddiv_rn(e, ax) > a.rtol) flag |= DAECPP_B200_NOT_CONVERGED;
-                    if (e > a.atol) flag |= DAECPP_B200_NOT_CONVERGED;
+                    if ((ax > 1e-14 && __ddiv_rn(e, ax) > a.rtol) || e > a.atol)
+                        flag |= e > a.floor ? (DAECPP_B200_NOT_CONVERGED | DAECPP_B200_ABOVE_FLOOR) : DAECPP_B200_NOT_CONVERGED;
                     const double xn = __dadd_rn(xo[u], v[u]);
                     xk[o[u]] = xn;
                     if (a.xk_host) a.xk_host[o[u]] = xn;
@@ -989,7 +989,7 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         a.rhs = c->b;
         a.perm = P.identity_perm ? nullptr : c->dC.perm.p;
         a.out = c->dx; a.xk = c->xk; a.x0 = c->xh[0];
-        a.atol = atol; a.rtol = rtol; a.max_err_abs = max_err_abs;
+        a.atol = atol; a.rtol = rtol; a.max_err_abs = max_err_abs; a.floor = c->refine_floor;
         a.update = fuse_update ? 1 : 0;
         if (c->fuse_residual_now)
         {

@@ -109,6 +109,8 @@ struct LaneSet
     const double *jv = nullptr, *mv = nullptr; // triplet values of J [count][s_jv], compressed values of M [count][s_mv]
     int32_t var_on = 0;
     double var_tol = 0.0;
+    double *f = nullptr, *b = nullptr, *dx = nullptr, *xk = nullptr; // lane slabs [count][s_vec]
+    double *refine_r = nullptr, *refine_e = nullptr;                 // [count][s_vec], allocated on first use
 };
 
 struct GroupLaunch
@@ -145,6 +147,7 @@ struct daecpp_b200_ctx
     bool spin_flags = true;            // resident iteration: spin on that word instead of cudaStreamSynchronize
     bool flags_clean = false;          // d_flags[2..4] are zero (the publishing CTA of a fused chain iteration resets them)
     bool chain_fuse_residual = true;   // diagonal mass: b = M*dxdt - f is formed while the forward kernel stages its right-hand side
+    bool residual_was_fused = false;   // the last fused iteration formed b inside the forward kernel (b is not in HBM)
     bool fuse_residual_now = false;    // set by the fused iteration for the solve that follows
     bool keep_b = false;               // fused residual: also write b to HBM (get_vector(b) after a fused iteration)
     daecpp_b200::Bdf bdf_pending{};
@@ -156,6 +159,10 @@ struct daecpp_b200_ctx
     // CSR view of M for the residual (row-wise accumulation in column order)
     daecpp_b200::DevBuf<int32_t> m_rowptr, m_rowslot, m_rowcol;
     uint64_t m_csr_version = ~0ull;
+    // CSR view of J (slots of the compressed-column form by row): only the guarded refinement step reads it
+    daecpp_b200::DevBuf<int32_t> j_rowptr, j_rowslot, j_rowcol;
+    uint64_t j_csr_version = ~0ull;
+    daecpp_b200::DevBuf<double> refine_r, refine_e; // residual and correction of the refinement step
     bool m_diag = false; // M is diagonal with slots in row order: index-free residual kernel
 
     // union pattern of J and M = pattern of Jb
@@ -209,7 +216,12 @@ struct daecpp_b200_ctx
     daecpp_b200::DevBuf<char> cub_tmp;
 
     // options
-    int refine_steps = 0;
+    // Guarded iterative refinement (one step of r = b - Jb*dx, Jb*e = r, dx += e): taken only when the Newton update
+    // failed the convergence test on elements whose |dx| is below refine_floor, i.e. where the outcome of the
+    // reference's relative test (solver.hpp:603-609) hangs on the componentwise accuracy of the linear solve
+    int refine_steps = 1;
+    double refine_floor = 1e-11;
+    double n_refine = 0;
     bool assemble_only = false;
     bool pinned_io = false; // host vectors handed to the ABI are page-locked: no staging copies
     double pivot_tol = 0.0;
@@ -225,6 +237,10 @@ struct daecpp_b200_ctx
     double ms_phase[5] = {0, 0, 0, 0, 0};
     double n_phase_samples = 0;
 };
+
+// internal bit of the update flags: an element failed a convergence test with |dx| above the refinement floor
+// (never returned through the ABI)
+#define DAECPP_B200_ABOVE_FLOOR 4
 
 #define DAECPP_CUDA_TRY(ctx, call)                                                                        \
     do                                                                                                    \
@@ -244,6 +260,7 @@ int assemble_triplets(daecpp_b200_ctx *c, TripletSet &T, const double *A, const 
                       int64_t nT, bool lazy_vals);
 int build_union(daecpp_b200_ctx *c);
 int build_mass_csr(daecpp_b200_ctx *c);
+int build_jac_csr(daecpp_b200_ctx *c);
 int regather_values(daecpp_b200_ctx *c, TripletSet &T); // hot path on the resident staging values, async
 // numeric.cu
 int upload_symbolic(daecpp_b200_ctx *c);
@@ -273,4 +290,7 @@ int classify_mass(daecpp_b200_ctx *c);
 int launch_dxdt(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
 int launch_update(daecpp_b200_ctx *c, double atol, double rtol, double max_err_abs);
 int launch_accept(daecpp_b200_ctx *c, int32_t variability_on, double tol);
+// guarded refinement of the last solve (single system, or the lanes of c->lanes whose mode word is not idle):
+// r = b - Jb*dx, Jb*e = r with the current factors, dx += e, xk += e, flags (and variability) recomputed
+int refine_last_solve(daecpp_b200_ctx *c, double alpha, double atol, double rtol, double max_err_abs, bool b_is_stored);
 } // namespace daecpp_b200

@@ -70,7 +70,7 @@ struct UnitArgs
     // fused update (solver.hpp:590-619)
     double *xk;
     const double *x0;
-    double atol, rtol, max_err_abs;
+    double atol, rtol, max_err_abs, floor;
 };
 
 constexpr int SPIN_LIMIT = 1 << 22;
@@ -349,8 +349,8 @@ __global__ void k_unit_backward(UnitArgs A)
                         const double e = fabs(v);
                         if (e > A.max_err_abs || isnan(v)) flag |= DAECPP_B200_DIVERGED;
                         const double xa = fabs(A.x0[o]);
-                        if (xa > 1e-14 && __ddiv_rn(e, xa) > A.rtol) flag |= DAECPP_B200_NOT_CONVERGED;
-                        if (e > A.atol) flag |= DAECPP_B200_NOT_CONVERGED;
+                        if ((xa > 1e-14 && __ddiv_rn(e, xa) > A.rtol) || e > A.atol)
+                            flag |= e > A.floor ? (DAECPP_B200_NOT_CONVERGED | DAECPP_B200_ABOVE_FLOOR) : DAECPP_B200_NOT_CONVERGED;
                         A.xk[o] = __dadd_rn(A.xk[o], v);
                     }
                 }
@@ -503,7 +503,7 @@ int launch_unit_backward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, 
     A.y = c->work;
     A.out = direct ? c->dx : nullptr;
     A.xk = c->xk; A.x0 = c->xh[0];
-    A.atol = atol; A.rtol = rtol; A.max_err_abs = max_err_abs;
+    A.atol = atol; A.rtol = rtol; A.max_err_abs = max_err_abs; A.floor = c->refine_floor;
     if (c->trace_units && c->trace.p) A.trace = c->trace.p + (size_t)c->S.nunit * 8;
     const int grid = grid_for(g, c->unit_grid_solve);
     if (direct && update) k_unit_backward<true><<<grid, c->unit_threads, c->S.solve_smem_bytes, c->stream>>>(A);

@@ -76,7 +76,7 @@ __global__ void k_check_diag(int32_t n, const int32_t *__restrict__ rowptr, cons
 }
 
 __global__ void k_update(int32_t n, const double *__restrict__ dx, const double *__restrict__ x0, double *__restrict__ xk,
-                         double atol, double rtol, double max_err_abs, int32_t *__restrict__ flags)
+                         double atol, double rtol, double max_err_abs, double floor, int32_t *__restrict__ flags)
 {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int f = 0;
@@ -86,8 +86,8 @@ __global__ void k_update(int32_t n, const double *__restrict__ dx, const double 
         const double e = fabs(d);
         if (e > max_err_abs || isnan(d)) f |= DAECPP_B200_DIVERGED;
         const double xa = fabs(x0[i]);
-        if (xa > 1e-14 && __ddiv_rn(e, xa) > rtol) f |= DAECPP_B200_NOT_CONVERGED;
-        if (e > atol) f |= DAECPP_B200_NOT_CONVERGED;
+        if ((xa > 1e-14 && __ddiv_rn(e, xa) > rtol) || e > atol)
+            f |= e > floor ? (DAECPP_B200_NOT_CONVERGED | DAECPP_B200_ABOVE_FLOOR) : DAECPP_B200_NOT_CONVERGED;
         xk[i] = __dadd_rn(xk[i], d);
     }
     // one atomic per warp that has something to report
@@ -121,6 +121,121 @@ __global__ void k_accept(int32_t n, const double *__restrict__ xk, const double 
         bits = other > bits ? other : bits;
     }
     if ((threadIdx.x & 31) == 0 && bits) atomicMax(vmax_bits, bits);
+}
+
+
+// ---- guarded iterative refinement (ctx.hpp: refine_steps) -------------------------------------------------
+// One step r = b - Jb*dx, Jb*e = r, dx += e for the Newton update just computed; Jb = J - (M*alpha) is applied
+// row by row from the triplet values (deterministic order, fused multiply-adds: r is wanted as accurately as
+// FP64 gives it, it is not compared bit for bit with anything).  Works on a single system or on the lanes of a
+// batch (blockIdx.y, idle lanes skipped).
+struct RefineArgs
+{
+    int32_t n, lanes;
+    int64_t s_vec, s_hist, s_jv, s_mv;
+    const int32_t *mode;
+    const int32_t *jrowptr, *jrowslot, *jrowcol, *jsrc; // jsrc: slot -> triplet whose value it is (values stay in triplet order), or null
+    const double *jv;
+    const int32_t *mrowptr, *mrowslot, *mrowcol;
+    const double *mv;
+    double alpha;
+    const double *alpha_arr;
+    const double *b; // the right-hand side of the solve, or null: diagonal mass, b_i = M_ii*dxdt(xk_i - dx_i) - f_i is formed again
+    Bdf bdf;
+    const double *lane_w;
+    const int32_t *lane_order, *lane_hbase;
+    const double *hist;
+    const double *f, *dx_in;
+    double *xk, *dx, *r;
+    const double *e;
+    const double *x0;
+    double atol, rtol, max_err_abs, floor;
+    int32_t *flags; // single: d_flags (word [2]); lanes: [lanes][4] (word [0])
+    unsigned long long *var;
+    int32_t var_on;
+    double var_tol;
+};
+
+__device__ __forceinline__ Bdf refine_bdf(const RefineArgs &a, int lane)
+{
+    if (!a.lane_w) return a.bdf;
+    Bdf s;
+    const int hb = a.lane_hbase[lane];
+    const int64_t off = (int64_t)lane * a.s_vec;
+    s.order = a.lane_order[lane];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) s.c[k] = a.lane_w[(int64_t)k * a.lanes + lane];
+    s.xk = a.xk + off;
+    s.x0 = a.hist + (int64_t)(hb & 3) * a.s_hist + off; s.x1 = a.hist + (int64_t)((hb + 1) & 3) * a.s_hist + off;
+    s.x2 = a.hist + (int64_t)((hb + 2) & 3) * a.s_hist + off; s.x3 = a.hist + (int64_t)((hb + 3) & 3) * a.s_hist + off;
+    return s;
+}
+
+__global__ void k_refine_residual(RefineArgs a)
+{
+    const int lane = blockIdx.y;
+    if (a.mode && a.mode[lane] == 0) return;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    const int64_t off = (int64_t)lane * a.s_vec;
+    const double *dx = a.dx_in + off;
+    const double *mv = a.mv + (int64_t)lane * a.s_mv;
+    double acc;
+    if (a.b) acc = a.b[off + i];
+    else
+    {   // xk already holds xk + dx
+        const Bdf s = refine_bdf(a, lane);
+        const double xo = __dsub_rn(s.xk[i], dx[i]);
+        const double x1 = s.order >= 2 ? s.x1[i] : 0.0, x2 = s.order >= 3 ? s.x2[i] : 0.0, x3 = s.order >= 4 ? s.x3[i] : 0.0;
+        acc = __dsub_rn(__dadd_rn(0.0, __dmul_rn(mv[i], bdf_one(s, xo, s.x0[i], x1, x2, x3))), a.f[off + i]);
+    }
+    const double *jv = a.jv + (int64_t)lane * a.s_jv;
+    for (int32_t p = a.jrowptr[i], e = a.jrowptr[i + 1]; p < e; ++p)
+    {
+        const int32_t slot = a.jrowslot[p];
+        acc = fma(-jv[a.jsrc ? a.jsrc[slot] : slot], dx[a.jrowcol[p]], acc);
+    }
+    const double alpha = a.alpha_arr ? a.alpha_arr[lane] : a.alpha;
+    for (int32_t p = a.mrowptr[i], e = a.mrowptr[i + 1]; p < e; ++p)
+        acc = fma(__dmul_rn(mv[a.mrowslot[p]], alpha), dx[a.mrowcol[p]], acc);
+    a.r[off + i] = acc;
+}
+
+// dx += e, xk += e and the error checks of dae-cpp/solver.hpp:590-619 on the corrected update
+__global__ void k_refine_apply(RefineArgs a)
+{
+    const int lane = blockIdx.y;
+    if (a.mode && a.mode[lane] == 0) return;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t off = (int64_t)lane * a.s_vec;
+    int f = 0;
+    double v = 0.0;
+    if (i < a.n)
+    {
+        const double *x0 = a.lane_hbase ? a.hist + (int64_t)(a.lane_hbase[lane] & 3) * a.s_hist + off : a.x0;
+        const double e = a.e[off + i];
+        const double d = __dadd_rn(a.dx[off + i], e);
+        a.dx[off + i] = d;
+        const double xn = __dadd_rn(a.xk[off + i], e);
+        a.xk[off + i] = xn;
+        const double ad = fabs(d), xa = fabs(x0[i]);
+        if (ad > a.max_err_abs || isnan(d)) f |= DAECPP_B200_DIVERGED;
+        if ((xa > 1e-14 && __ddiv_rn(ad, xa) > a.rtol) || ad > a.atol)
+            f |= ad > a.floor ? (DAECPP_B200_NOT_CONVERGED | DAECPP_B200_ABOVE_FLOOR) : DAECPP_B200_NOT_CONVERGED;
+        if (a.var_on && xa > a.var_tol && fabs(xn) > a.var_tol) v = fabs(__ddiv_rn(__dsub_rn(x0[i], xn), x0[i]));
+    }
+    const unsigned any = __reduce_or_sync(0xffffffffu, (unsigned)f);
+    if (any && (threadIdx.x & 31) == 0) atomicOr(a.lane_hbase ? &a.flags[4 * lane] : &a.flags[2], (int32_t)any);
+    if (a.var_on && a.var)
+    {
+        unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+        for (int o = 16; o > 0; o >>= 1)
+        {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, bits, o);
+            bits = other > bits ? other : bits;
+        }
+        if ((threadIdx.x & 31) == 0 && bits) atomicMax(a.var + lane, bits);
+    }
 }
 
 } // namespace
@@ -175,8 +290,73 @@ int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5], boo
 
 int launch_update(daecpp_b200_ctx *c, double atol, double rtol, double max_err_abs)
 {
-    k_update<<<(c->n + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->n, c->dx, c->xh[0], c->xk, atol, rtol, max_err_abs, c->d_flags);
+    k_update<<<(c->n + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->n, c->dx, c->xh[0], c->xk, atol, rtol, max_err_abs, c->refine_floor, c->d_flags);
     c->kernels += 1;
+    DAECPP_CUDA_TRY(c, cudaGetLastError());
+    return DAECPP_B200_OK;
+}
+
+
+int refine_last_solve(daecpp_b200_ctx *c, double alpha, double atol, double rtol, double max_err_abs, bool b_is_stored)
+{
+    int rc;
+    const LaneSet *L = c->lanes;
+    cudaStream_t st = c->stream;
+    if ((rc = build_jac_csr(c))) return rc;
+    c->h_flags[4] = 0; // (the sort behind build_jac_csr parks a count there)
+    if (!c->jvals_from_triplets && !L && (rc = ensure_csc_values(c, c->J))) return rc;
+    double *r, *e;
+    if (L) { r = L->refine_r; e = L->refine_e; }
+    else
+    {
+        const size_t ns = ((size_t)c->n + 31) / 32 * 32;
+        DAECPP_CUDA_TRY(c, c->refine_r.reserve(ns));
+        DAECPP_CUDA_TRY(c, c->refine_e.reserve(ns));
+        r = c->refine_r.p; e = c->refine_e.p;
+    }
+    if (!r || !e) { c->err = "refinement buffers missing"; return DAECPP_B200_EINVAL; }
+    RefineArgs a{};
+    a.n = c->n;
+    a.lanes = L ? L->count : 0;
+    a.jrowptr = c->j_rowptr.p; a.jrowslot = c->j_rowslot.p; a.jrowcol = c->j_rowcol.p;
+    a.jsrc = c->jvals_from_triplets ? c->J.src.p : nullptr;
+    a.mrowptr = c->m_rowptr.p; a.mrowslot = c->m_rowslot.p; a.mrowcol = c->m_rowcol.p;
+    a.alpha = alpha;
+    a.f = c->f; a.dx_in = c->dx; a.dx = c->dx; a.xk = c->xk; a.r = r; a.e = e;
+    a.b = b_is_stored ? c->b : nullptr;
+    a.atol = atol; a.rtol = rtol; a.max_err_abs = max_err_abs; a.floor = c->refine_floor;
+    if (L)
+    {
+        a.s_vec = L->s_vec; a.s_hist = L->s_hist; a.s_jv = L->s_jv; a.s_mv = L->s_mv;
+        a.mode = L->mode; a.jv = L->jv; a.mv = L->mv; a.alpha_arr = L->w;
+        a.lane_w = L->w; a.lane_order = L->order; a.lane_hbase = L->hbase; a.hist = L->hist;
+        a.flags = L->flags; a.var = L->var; a.var_on = L->var_on; a.var_tol = L->var_tol;
+    }
+    else
+    {
+        a.jv = c->jvals_from_triplets ? c->J.A.p : c->J.vals.p;
+        a.mv = c->M.vals.p;
+        a.bdf = c->bdf_pending;
+        a.x0 = c->xh[0];
+        a.flags = c->d_flags;
+    }
+    const dim3 grid((unsigned)((c->n + TPB - 1) / TPB), (unsigned)(L ? L->count : 1));
+    k_refine_residual<<<grid, TPB, 0, st>>>(a);
+    // Jb*e = r with the factors at hand: the solve reads c->b and writes c->dx
+    double *keep_b = c->b, *keep_dx = c->dx;
+    c->b = r; c->dx = e;
+    const bool keep_fuse = c->fuse_residual_now, keep_pub = c->publish_flags;
+    c->fuse_residual_now = false; c->publish_flags = false;
+    rc = numeric_solve(c, false);
+    c->fuse_residual_now = keep_fuse; c->publish_flags = keep_pub;
+    c->b = keep_b; c->dx = keep_dx;
+    if (rc) return rc;
+    if (L) DAECPP_CUDA_TRY(c, cudaMemsetAsync(L->flags, 0, sizeof(int32_t) * 4 * (size_t)L->count + sizeof(unsigned long long) * (size_t)L->count, st));
+    else DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 2, 0, sizeof(int32_t), st));
+    c->flags_clean = false;
+    k_refine_apply<<<grid, TPB, 0, st>>>(a);
+    c->kernels += 2;
+    c->n_refine += 1;
     DAECPP_CUDA_TRY(c, cudaGetLastError());
     return DAECPP_B200_OK;
 }

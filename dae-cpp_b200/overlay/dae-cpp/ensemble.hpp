@@ -374,6 +374,10 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     ASSERT(!t_out.empty() && t_out.back() >= 0.0, "solve_ensemble_device: no (or a negative) target time.");
 
     const auto wall0 = std::chrono::steady_clock::now();
+    const bool timing = std::getenv("DAECPP_B200_TIMING") != nullptr; // debug: host-side phases to stderr
+    auto stamp = [&](const char *what) {
+        if (timing) std::fprintf(stderr, "  [solve_ensemble_device] %-18s at %8.3f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count());
+    };
     double st_setup_ms = 0.0;
     int dev = 0;
     if (const char *env = std::getenv("DAECPP_B200_DEVICE")) dev = std::atoi(env);
@@ -382,12 +386,14 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     if (rc) { ERROR("daecpp_b200: cannot create the batch context (code " << rc << "): " << daecpp_b200_batch_last_error(nullptr)); }
     auto fatal = [&](const char *what, int code) { ERROR("daecpp_b200: " << what << " failed (code " << code << "): " << daecpp_b200_batch_last_error(b)); };
 
+    stamp("batch_create");
     sparse_matrix M;
     mass(M, 0.0);
     M.check();
     if ((rc = daecpp_b200_batch_set_pattern(b, shape.rows().data(), shape.cols().data(), static_cast<int64_t>(shape.size()), M.i.data(), M.j.data(),
                                             static_cast<int64_t>(M.A.size()))))
         fatal("batch_set_pattern", rc);
+    stamp("set_pattern");
     if ((rc = daecpp_b200_batch_set_mass_values(b, M.A.data(), 0, 0))) fatal("batch_set_mass_values", rc);
     {
         std::vector<double> slab(members * n);
@@ -399,6 +405,7 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
         }
         if ((rc = daecpp_b200_batch_set_state(b, slab.data(), 0, static_cast<int32_t>(members)))) fatal("batch_set_state", rc);
     }
+    stamp("set_state");
     device::DeviceFunctors<Eq> functors(eqs, shape);
     daecpp_b200_device_functors fn = functors.binding();
     if ((rc = daecpp_b200_batch_set_device_functors(b, &fn))) fatal("batch_set_device_functors", rc);
@@ -452,6 +459,7 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
         for (std::size_t m = 0; m < members; ++m)
             if (cmd[m].mode != DAECPP_B200_LANE_IDLE) lanes[m].consume(res[m]);
     }
+    stamp("rounds");
     {   // final states: the iterate of lanes that ended on an accepted step, x[0] of the others
         std::vector<double> xk(members * n), xa(members * n);
         if ((rc = daecpp_b200_batch_get_vector(b, 3, xk.data(), 0, static_cast<int32_t>(members)))) fatal("batch_get_vector", rc);
@@ -471,7 +479,9 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     if (daecpp_b200_batch_get_stat(b, "ms_device", &v) == DAECPP_B200_OK) st.ms_device = v;
     if (daecpp_b200_batch_get_stat(b, "kernels_launched", &v) == DAECPP_B200_OK) st.kernels_launched = v;
     st.ms_setup = st_setup_ms;
+    stamp("final states");
     daecpp_b200_batch_destroy(b);
+    stamp("destroy");
     st.ms_wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
     if (stats) *stats = st;
     return R;

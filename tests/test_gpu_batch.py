@@ -206,3 +206,50 @@ def test_single_lane_device_functor_trajectory_matches_reference_golden(tmp_path
     tol = 10.0 * meta["tol"]
     assert np.all(np.abs(got[2:] - want) <= tol + tol * np.abs(want)), float(np.max(np.abs(got[2:] - want)))
     assert info["lane_iterations"] == info["rounds"]
+
+
+def test_guarded_refinement_single_and_batched():
+    """The update fails the relative test only on elements whose |dx| sits below the refinement floor (an element of
+    x[0] that is tiny but above the 1e-14 floor of solver.hpp:603): one refinement step runs, in the single-system
+    context and in the batch alike, with bit-identical results; a converged / clearly unconverged update takes none."""
+    from gpu_lib import binding as B
+    import scipy.sparse as sp
+    lib = B.load()
+    n, lanes = 6000, 3
+    u = P.flame1d_state(n)
+    u[n // 2] = 3e-13  # passes the 1e-14 floor, so the relative test needs |dx| < 3e-19 there
+    A, i, j = P.flame1d_jacobian(u)
+    M = P.identity_mass(n)
+    dt = np.array([1e-2, 0, 0, 0.0])
+    Jb = sp.csr_matrix((A, (i, j)), shape=(n, n)) - sp.identity(n) * (1.0 / dt[0])
+    r = np.random.default_rng(5)
+    z = 1e-13 * r.standard_normal(n)          # the update the iteration must deliver: everywhere below the floor 1e-11
+    f = -(Jb @ z)                              # b = M*dxdt - f = -f  (xk == x[0] at the first iteration of a BDF-1 step)
+    c = B.Context(n, 0, lib)
+    c.set_state(u); c.set_mass(M); c.set_jacobian((A, i, j))
+    c.residual(f, 1, dt)
+    rc, flags = c.iteration_resident(1, 1, dt, 1e-6, 1e-6)
+    assert rc == 0 and flags == B.NOT_CONVERGED and c.stat("n_refine") == 1
+    dx = c.get_vector("dx")
+    assert np.max(np.abs(dx - z)) <= 1e-12 * np.max(np.abs(z))
+    # the same lane three times in a batch, the middle one with a large update (no refinement for it)
+    b = B.Batch(n, lanes, 0, lib)
+    b.set_pattern(i, j, M[1], M[2]); b.set_mass_values(M[0]); b.set_state(np.stack([u] * lanes))
+    b.set_jacobian_values(np.stack([A] * lanes)); b.set_rhs_values(np.stack([f, 1e6 * f, f]))
+    rc, res = b.round([dict(mode=B.LANE_REFACTOR, order=1, dt=dt)] * lanes, 1e-6, 1e-6)
+    assert [q[0] for q in res] == [B.NOT_CONVERGED] * 3 and [q[1] for q in res] == [0, 0, 0]
+    assert b.stat("refine_rounds") == 1 and b.stat("refined_lanes") == 2
+    bdx, bxk = b.get_vector("dx"), b.get_vector("xk")
+    assert bdx[0].tobytes() == dx.tobytes() == bdx[2].tobytes()
+    assert bxk[0].tobytes() == c.get_vector("xk").tobytes()
+    assert np.max(np.abs(bdx[1] - 1e6 * z)) <= 1e-9 * np.max(np.abs(1e6 * z))
+    # refinement switched off: the unrefined update is what the plain solve delivers
+    c2 = B.Context(n, 0, lib)
+    c2.set_option("refine_steps", 0)
+    c2.set_state(u); c2.set_mass(M); c2.set_jacobian((A, i, j))
+    c2.residual(f, 1, dt)
+    rc, flags = c2.iteration_resident(1, 1, dt, 1e-6, 1e-6)
+    assert c2.stat("n_refine") == 0 and flags == B.NOT_CONVERGED
+    for q in (c, c2):
+        q.close()
+    b.close()
