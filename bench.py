@@ -337,7 +337,7 @@ def _ensdev():
     if not os.path.exists(path):
         raise SystemExit(f"bench.py: {path} is not built (python -c 'import __graft_entry__ as g; g.build()')")
     lib = C.CDLL(path)
-    lib.ensdev_perovskite.argtypes = [C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_double, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.ensdev_perovskite.argtypes = [C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_double, C.c_int32, C.c_void_p, C.c_void_p]
     lib.ensdev_perovskite.restype = C.c_int
     return lib
 
@@ -346,11 +346,11 @@ ENS_STATS = ("rounds", "lane_iterations", "lane_refactorisations", "device_ms", 
              "kernels_launched", "setup_ms")
 
 
-def ensemble_device_block(members, first, count, N, device, out=None):
-    """One lock-step integration of members [first, first+count) on `device`; returns the driver's statistics."""
+def ensemble_device_block(members, first, count, stride, N, device, out=None):
+    """One lock-step integration of members first, first+stride, ... (count of them) on `device`; returns the driver's statistics."""
     os.environ["DAECPP_B200_DEVICE"] = str(device)
     st = np.zeros(10)
-    _ensdev().ensdev_perovskite(members, first, count, N, 10.0, 0, out.ctypes.data if out is not None else None, st.ctypes.data)
+    _ensdev().ensdev_perovskite(members, first, count, stride, N, 10.0, 0, out.ctypes.data if out is not None else None, st.ctypes.data)
     return dict(zip(ENS_STATS, st.tolist()))
 
 
@@ -407,12 +407,14 @@ def run_ensemble_device(args):
     n = 2 * N
     members = args.members
     per = (members + world - 1) // world
-    first = rank * per
-    count = max(0, min(per, members - first))
+    # round-robin: rank r integrates members r, r + world, ... -- every rank sees the whole lambda range, so the slow
+    # members (small lambda: more steps) are spread evenly
+    first, stride = rank, world
+    count = len(range(rank, members, world))
     steps = max(1, min(args.steps, 20)) if args.steps_given else 5
     warm = max(3, min(args.warmup, 5))
     for _ in range(warm):  # small blocks: CUDA context, module load, the allocator and the page-locked pools come up
-        ensemble_device_block(members, first, min(count, 32), N, local)
+        ensemble_device_block(members, first, min(count, 32), stride, N, local)
     out = np.zeros((count, n + 2))
     sampler = ClockSampler(local)
     sampler.start()
@@ -420,7 +422,7 @@ def run_ensemble_device(args):
     t0 = time.perf_counter()
     acc = dict.fromkeys(ENS_STATS, 0.0)
     for _ in range(steps):
-        st = ensemble_device_block(members, first, count, N, local, out)
+        st = ensemble_device_block(members, first, count, stride, N, local, out)
         for k in ENS_STATS:
             acc[k] += st[k]
     barrier()
@@ -445,6 +447,8 @@ def run_ensemble_device(args):
         gather_ms = (time.perf_counter() - tg) * 1e3
     else:
         allm = mine
+    if dist is not None:  # rank-major blocks back to member order: member m sits at block m % world, row m // world
+        allm = allm.view(world, per, n + 2).transpose(0, 1).reshape(world * per, n + 2)
     allm = allm[:members]
     failed = int((allm[:, 0] != 0).sum().item())
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -455,7 +459,7 @@ def run_ensemble_device(args):
             "data": "synthetic",
             "config": {"workload": f"C5 ensemble of perovskite N={N} (n={n}) members, lambda log-spaced 0.5..2 (BASELINE configs[4])",
                        "members": members, "members_per_gpu": per, "functors": "device (dae-cpp/device-functor.hpp: equations + dual-number shape Jacobian as kernels)",
-                       "parallelism": f"members partitioned in contiguous blocks over {world} GPU(s); per GPU ONE batch context, lanes advanced in lock step "
+                       "parallelism": f"members dealt round-robin to {world} GPU(s); per GPU ONE batch context, lanes advanced in lock step "
                                       "(one launch sequence + one flag read per Newton round for all lanes); no data-path collective, one final all_gather",
                        "timing": "value: CUDA-event time of all Newton rounds (state resident in HBM), max over ranks; e2e: wall clock between barriers around "
                                  "daecpp::solve_ensemble_device (context creation, pattern analysis, uploads, rounds, download of the final states), max over ranks",

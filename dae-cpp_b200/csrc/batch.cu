@@ -8,6 +8,7 @@
 // round = one small control upload, the functor launches (device functors) or the slabs the caller
 // uploaded (host functors), residual, refactorisation of the lanes that asked for one, the triangular
 // solves with the fused error check / update / variability, one small result download.
+#include <algorithm>
 #include <chrono>
 #include <cstring>
 #include <new>
@@ -38,7 +39,8 @@ struct daecpp_b200_batch
     bool have_pattern = false, have_mass = false;
 
     // control words of a round: pinned structure-of-arrays block and its device mirror
-    //   mode i32[L] | pre i32[L] | order i32[L] | hbase i32[L] | t f64[L] | w f64[5][L]
+    //   mode | pre | order | hbase | active lanes | refactoring lanes | lanes with a pre action  (i32[L] each, L even-padded)
+    //   | t f64[L] | w f64[5][L]
     char *h_ctl = nullptr, *d_ctl = nullptr;
     size_t ctl_bytes = 0;
     // results: flags i32[4][L] (lane-major [L][4]) | var u64[L]
@@ -51,6 +53,9 @@ struct daecpp_b200_batch
     bool have_fn = false;
     std::vector<char> rhs_loaded, jac_loaded; // host-functor mode: the lane has values to iterate on
 
+    static constexpr size_t BOUNCE_BYTES = (size_t)8 << 20;
+    char *h_bounce = nullptr;     // two page-locked bounce buffers for the lane slabs of pageable callers
+    cudaEvent_t ev_bounce[2] = {nullptr, nullptr};
     double rounds = 0, ms_device = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool ev_pending = false;
@@ -59,7 +64,12 @@ struct daecpp_b200_batch
     int32_t *ctl_pre() const { return ctl_mode() + lanes; }
     int32_t *ctl_order() const { return ctl_mode() + 2 * lanes; }
     int32_t *ctl_hbase() const { return ctl_mode() + 3 * lanes; }
-    double *ctl_t() const { return reinterpret_cast<double *>(h_ctl + sizeof(int32_t) * 4 * (size_t)lanes); }
+    int32_t *ctl_list_active() const { return ctl_mode() + 4 * lanes; }
+    int32_t *ctl_list_refactor() const { return ctl_mode() + 5 * lanes; }
+    int32_t *ctl_list_pre() const { return ctl_mode() + 6 * lanes; }
+    size_t ctl_int_bytes() const { return (sizeof(int32_t) * 7 * (size_t)lanes + 7) / 8 * 8; }
+    double *ctl_t() const { return reinterpret_cast<double *>(h_ctl + ctl_int_bytes()); }
+    template <class T> T *dev(const T *host_ptr) const { return reinterpret_cast<T *>(d_ctl + (reinterpret_cast<const char *>(host_ptr) - h_ctl)); }
     double *ctl_w() const { return ctl_t() + lanes; }
 };
 
@@ -88,19 +98,15 @@ struct PreArgs
 {
     int32_t n, lanes;
     int64_t s_vec, s_hist;
-    const int32_t *pre, *hbase;
+    const int32_t *pre, *hbase, *list;
     double *xk, *hist;
-    int32_t *flags;
-    unsigned long long *var;
 };
 
 // accept: x[0] <- xk into the ring slot the host rotated to (dae-cpp/solver.hpp:698-702, the shift itself is
-// the rotation of hbase); rollback: xk <- x[0] (solver.hpp:643,671).  Also clears the lane's result words.
+// the rotation of hbase); rollback: xk <- x[0] (solver.hpp:643,671).  One grid row per lane with such an action.
 __global__ void k_batch_pre(PreArgs a)
 {
-    const int lane = blockIdx.y;
-    if (blockIdx.x == 0 && threadIdx.x < 4) a.flags[4 * lane + threadIdx.x] = 0;
-    if (blockIdx.x == 0 && threadIdx.x == 4) a.var[lane] = 0ull;
+    const int lane = a.list[blockIdx.y];
     const int pre = a.pre[lane];
     if (pre == DAECPP_B200_LANE_KEEP) return;
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -115,7 +121,7 @@ struct ResArgs
 {
     int32_t n, lanes;
     int64_t s_vec, s_hist, s_mv;
-    const int32_t *mode, *hbase, *order;
+    const int32_t *mode, *hbase, *order, *list;
     const double *w;
     const double *xk, *hist, *mv, *f;
     double *b;
@@ -140,8 +146,7 @@ __device__ __forceinline__ Bdf lane_bdf(const ResArgs &a, int lane)
 // (the arithmetic of vector_ops.cu: k_residual; dae-cpp/solver.hpp:141-217, 516-518)
 __global__ void k_batch_residual(ResArgs a)
 {
-    const int lane = blockIdx.y;
-    if (a.mode[lane] == DAECPP_B200_LANE_IDLE) return;
+    const int lane = a.list[blockIdx.y];
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= a.n) return;
     const Bdf s = lane_bdf(a, lane);
@@ -170,6 +175,8 @@ void release(daecpp_b200_batch *b)
     if (b->h_ctl) cudaFreeHost(b->h_ctl);
     if (b->d_ctl) cudaFree(b->d_ctl);
     if (b->h_res) cudaFreeHost(b->h_res);
+    if (b->h_bounce) cudaFreeHost(b->h_bounce);
+    for (cudaEvent_t e : b->ev_bounce) if (e) cudaEventDestroy(e);
     if (b->d_res) cudaFree(b->d_res);
     if (b->ev0) cudaEventDestroy(b->ev0);
     if (b->ev1) cudaEventDestroy(b->ev1);
@@ -232,7 +239,7 @@ int daecpp_b200_batch_create(int32_t n, int32_t lanes, int device, daecpp_b200_b
     if ((e = cudaMalloc((void **)&b->slab, sizeof(double) * 8 * per)) != cudaSuccess) return bail(e, "cudaMalloc(state)");
     b->xk = b->slab; b->f = b->slab + per; b->b = b->slab + 2 * per; b->dx = b->slab + 3 * per; b->hist = b->slab + 4 * per;
     if ((e = cudaMemsetAsync(b->slab, 0, sizeof(double) * 8 * per, b->c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
-    b->ctl_bytes = sizeof(int32_t) * 4 * (size_t)lanes + sizeof(double) * 6 * (size_t)lanes;
+    b->ctl_bytes = b->ctl_int_bytes() + sizeof(double) * 6 * (size_t)lanes;
     b->res_bytes = sizeof(int32_t) * 4 * (size_t)lanes + sizeof(unsigned long long) * (size_t)lanes;
     if ((e = cudaMallocHost((void **)&b->h_ctl, b->ctl_bytes)) != cudaSuccess) return bail(e, "cudaMallocHost");
     if ((e = cudaMalloc((void **)&b->d_ctl, b->ctl_bytes)) != cudaSuccess) return bail(e, "cudaMalloc(ctl)");
@@ -252,9 +259,9 @@ int daecpp_b200_batch_create(int32_t n, int32_t lanes, int device, daecpp_b200_b
     L.count = lanes;
     L.s_vec = (int64_t)b->ns; L.s_hist = (int64_t)per;
     L.hist = b->hist;
-    int32_t *dm = reinterpret_cast<int32_t *>(b->d_ctl);
-    L.mode = dm; L.hbase = dm + 3 * (size_t)lanes; L.order = dm + 2 * (size_t)lanes;
-    L.w = reinterpret_cast<double *>(b->d_ctl + sizeof(int32_t) * 4 * (size_t)lanes) + lanes;
+    L.mode = b->dev(b->ctl_mode()); L.hbase = b->dev(b->ctl_hbase()); L.order = b->dev(b->ctl_order());
+    L.w = b->dev(b->ctl_w());
+    L.list_active = b->dev(b->ctl_list_active()); L.list_refactor = b->dev(b->ctl_list_refactor());
     L.flags = reinterpret_cast<int32_t *>(b->d_res);
     L.var = reinterpret_cast<unsigned long long *>(b->d_res + sizeof(int32_t) * 4 * (size_t)lanes);
     if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return bail(e, "cudaStreamSynchronize");
@@ -364,13 +371,59 @@ int daecpp_b200_batch_set_jacobian_values(daecpp_b200_batch *b, const double *A,
 
 static int copy_lanes(daecpp_b200_batch *b, double *dev, double *host_out, const double *host_in, int32_t first, int32_t count)
 {
-    // lane-major host slab [count][n] <-> device [lanes][ns]
+    // lane-major host slab [count][n] <-> device [lanes][ns], through two page-locked bounce buffers so that the
+    // DMA of one chunk of lanes overlaps the host copy of the previous one (the caller's memory is pageable)
     const size_t n = (size_t)b->n;
-    if (host_in)
-        BATCH_TRY(b, cudaMemcpy2DAsync(dev + (size_t)first * b->ns, sizeof(double) * b->ns, host_in, sizeof(double) * n, sizeof(double) * n, (size_t)count, cudaMemcpyHostToDevice, b->c->stream));
-    else
-        BATCH_TRY(b, cudaMemcpy2DAsync(host_out, sizeof(double) * n, dev + (size_t)first * b->ns, sizeof(double) * b->ns, sizeof(double) * n, (size_t)count, cudaMemcpyDeviceToHost, b->c->stream));
-    BATCH_TRY(b, cudaStreamSynchronize(b->c->stream));
+    cudaStream_t st = b->c->stream;
+    if (!b->h_bounce)
+    {
+        BATCH_TRY(b, cudaMallocHost((void **)&b->h_bounce, 2 * daecpp_b200_batch::BOUNCE_BYTES));
+        BATCH_TRY(b, cudaEventCreateWithFlags(&b->ev_bounce[0], cudaEventDisableTiming));
+        BATCH_TRY(b, cudaEventCreateWithFlags(&b->ev_bounce[1], cudaEventDisableTiming));
+    }
+    size_t rows = daecpp_b200_batch::BOUNCE_BYTES / (sizeof(double) * n);
+    if (rows == 0)
+    {   // one lane does not fit a bounce buffer: plain copies
+        for (int32_t l = 0; l < count; ++l)
+        {
+            if (host_in) BATCH_TRY(b, cudaMemcpyAsync(dev + ((size_t)first + l) * b->ns, host_in + (size_t)l * n, sizeof(double) * n, cudaMemcpyHostToDevice, st));
+            else BATCH_TRY(b, cudaMemcpyAsync(host_out + (size_t)l * n, dev + ((size_t)first + l) * b->ns, sizeof(double) * n, cudaMemcpyDeviceToHost, st));
+        }
+        BATCH_TRY(b, cudaStreamSynchronize(st));
+        return DAECPP_B200_OK;
+    }
+    const int32_t nchunks = (int32_t)(((size_t)count + rows - 1) / rows);
+    auto chunk_rows = [&](int32_t k) { return (size_t)std::min<size_t>(rows, (size_t)count - (size_t)k * rows); };
+    auto bounce = [&](int32_t k) { return reinterpret_cast<double *>(b->h_bounce + (size_t)(k & 1) * daecpp_b200_batch::BOUNCE_BYTES); };
+    for (int32_t k = 0; k <= nchunks; ++k)
+    {
+        if (host_in)
+        {
+            if (k < nchunks)
+            {
+                if (k >= 2) BATCH_TRY(b, cudaEventSynchronize(b->ev_bounce[k & 1])); // the DMA that last read this buffer
+                std::memcpy(bounce(k), host_in + (size_t)k * rows * n, sizeof(double) * chunk_rows(k) * n);
+                BATCH_TRY(b, cudaMemcpy2DAsync(dev + ((size_t)first + (size_t)k * rows) * b->ns, sizeof(double) * b->ns, bounce(k), sizeof(double) * n,
+                                               sizeof(double) * n, chunk_rows(k), cudaMemcpyHostToDevice, st));
+                BATCH_TRY(b, cudaEventRecord(b->ev_bounce[k & 1], st));
+            }
+        }
+        else
+        {
+            if (k < nchunks)
+            {
+                BATCH_TRY(b, cudaMemcpy2DAsync(bounce(k), sizeof(double) * n, dev + ((size_t)first + (size_t)k * rows) * b->ns, sizeof(double) * b->ns,
+                                               sizeof(double) * n, chunk_rows(k), cudaMemcpyDeviceToHost, st));
+                BATCH_TRY(b, cudaEventRecord(b->ev_bounce[k & 1], st));
+            }
+            if (k >= 1)
+            {
+                BATCH_TRY(b, cudaEventSynchronize(b->ev_bounce[(k - 1) & 1]));
+                std::memcpy(host_out + (size_t)(k - 1) * rows * n, bounce(k - 1), sizeof(double) * chunk_rows(k - 1) * n);
+            }
+        }
+    }
+    BATCH_TRY(b, cudaStreamSynchronize(st));
     return DAECPP_B200_OK;
 }
 
@@ -464,27 +517,43 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
         }
         for (int k = 0; k < 5; ++k) b->ctl_w()[(size_t)k * Ln + l] = w[k];
     }
+    int n_pre = 0;
+    {
+        int na = 0, nr = 0;
+        for (int32_t l = 0; l < Ln; ++l)
+        {
+            if (cmd[l].mode != DAECPP_B200_LANE_IDLE) b->ctl_list_active()[na++] = l;
+            if (cmd[l].mode == DAECPP_B200_LANE_REFACTOR) b->ctl_list_refactor()[nr++] = l;
+            if (cmd[l].pre != DAECPP_B200_LANE_KEEP) b->ctl_list_pre()[n_pre++] = l;
+        }
+        b->L.n_active = na; b->L.n_refactor = nr;
+    }
     BATCH_TRY(b, cudaEventRecord(b->ev0, st));
     BATCH_TRY(b, cudaMemcpyAsync(b->d_ctl, b->h_ctl, b->ctl_bytes, cudaMemcpyHostToDevice, st));
-    const dim3 gv((unsigned)((b->n + TPB - 1) / TPB), (unsigned)Ln);
+    BATCH_TRY(b, cudaMemsetAsync(b->d_res, 0, b->res_bytes, st));
+    const unsigned gx = (unsigned)((b->n + TPB - 1) / TPB);
+    if (n_pre)
     {
-        PreArgs a{b->n, Ln, (int64_t)b->ns, b->L.s_hist, reinterpret_cast<const int32_t *>(b->d_ctl) + Ln, b->L.hbase, b->xk, b->hist, b->L.flags, b->L.var};
-        k_batch_pre<<<gv, TPB, 0, st>>>(a);
+        PreArgs a{b->n, Ln, (int64_t)b->ns, b->L.s_hist, b->dev(b->ctl_pre()), b->L.hbase, b->dev(b->ctl_list_pre()), b->xk, b->hist};
+        k_batch_pre<<<dim3(gx, (unsigned)n_pre), TPB, 0, st>>>(a);
         c->kernels += 1;
     }
+    const dim3 gv(gx, (unsigned)(n_active > 0 ? n_active : 1));
     if (n_active > 0)
     {
-        const double *d_t = reinterpret_cast<const double *>(b->d_ctl + sizeof(int32_t) * 4 * (size_t)Ln);
+        const double *d_t = b->dev(b->ctl_t());
         if (b->have_fn)
         {
             daecpp_b200_functor_args fa{};
             fa.n = b->n; fa.lanes = Ln; fa.x_stride = (int64_t)b->ns; fa.x = b->xk; fa.t = d_t; fa.mode = b->L.mode; fa.stream = st;
             fa.min_mode = DAECPP_B200_LANE_SOLVE; fa.out = b->f; fa.out_stride = (int64_t)b->ns;
+            fa.lane_list = b->L.list_active; fa.n_list = n_active;
             if (b->fn.rhs(b->fn.user, &fa)) return bfail(b, DAECPP_B200_EINVAL, "device rhs functor failed");
             c->kernels += 1;
             if (n_refactor)
             {
                 fa.min_mode = DAECPP_B200_LANE_REFACTOR; fa.out = b->jv.p; fa.out_stride = b->nTJ;
+                fa.lane_list = b->L.list_refactor; fa.n_list = n_refactor;
                 if (b->fn.jacobian(b->fn.user, &fa)) return bfail(b, DAECPP_B200_EINVAL, "device Jacobian functor failed");
                 c->kernels += 1;
             }
@@ -498,7 +567,7 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
         const bool fuse_res = c->m_diag && c->chain_fuse_residual;
         if (!fuse_res)
         {
-            ResArgs a{b->n, Ln, (int64_t)b->ns, b->L.s_hist, b->L.s_mv, b->L.mode, b->L.hbase, b->L.order, b->L.w,
+            ResArgs a{b->n, Ln, (int64_t)b->ns, b->L.s_hist, b->L.s_mv, b->L.mode, b->L.hbase, b->L.order, b->L.list_active, b->L.w,
                       b->xk, b->hist, b->mv.p, b->f, b->b, c->m_rowptr.p, c->m_rowslot.p, c->m_rowcol.p};
             k_batch_residual<<<gv, TPB, 0, st>>>(a);
             c->kernels += 1;
@@ -531,7 +600,7 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
                               !(f & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED));
             b->ctl_mode()[l] = want ? DAECPP_B200_LANE_SOLVE : DAECPP_B200_LANE_IDLE;
             b->ctl_pre()[l] = DAECPP_B200_LANE_KEEP;
-            n_ref += want ? 1 : 0;
+            if (want) b->ctl_list_active()[n_ref++] = l;
         }
         if (n_ref)
         {
@@ -542,6 +611,7 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
             BATCH_TRY(b, b->refine_buf.reserve(2 * per));
             b->L.refine_r = b->refine_buf.p; b->L.refine_e = b->refine_buf.p + per;
             BATCH_TRY(b, cudaMemcpyAsync(b->d_ctl, b->h_ctl, b->ctl_bytes, cudaMemcpyHostToDevice, st));
+            b->L.n_active = n_ref; b->L.n_refactor = 0;
             c->lanes = &b->L;
             c->xk = b->xk; c->f = b->f; c->b = b->b; c->dx = b->dx;
             const int rc = refine_last_solve(c, 0.0, atol, rtol, max_err_abs, !(c->m_diag && c->chain_fuse_residual));

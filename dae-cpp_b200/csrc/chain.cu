@@ -69,7 +69,9 @@ struct ChainArgs
     // single system
     const double *alpha_arr;
     int64_t s_jv, s_mv, s_F, s_Y, s_red, s_rv, s_x, s_vec, s_hist;
-    int32_t lanes;
+    int32_t lanes;      // lanes of the batch (stride of the per-lane control arrays)
+    int32_t grid_lanes; // lanes this launch covers = gridDim.y
+    const int32_t *lane_list; // [grid_lanes] lane of every grid row, null: the row index itself
     const int32_t *lane_mode, *lane_hbase, *lane_order;
     const double *lane_w; // [5][lanes]
     double *hist;
@@ -87,7 +89,7 @@ __device__ __forceinline__ int lane_mode(const ChainArgs &a, int64_t mb) { retur
 constexpr int TRACE_SLOTS = 8, TRACE_KERNELS = 5; // factor tiles, factor top, forward tiles, top solve, backward tiles
 __device__ __forceinline__ void stamp(const ChainArgs &a, int kernel, int tile, int slot)
 {
-    if (a.trace && threadIdx.x == 0 && blockIdx.y == 0)
+    if (a.trace && threadIdx.x == 0 && blockIdx.y == 0 && !a.lane_list)
     {
         long long ns;
         asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns));
@@ -272,7 +274,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
     extern __shared__ __align__(16) unsigned char smem[];
     FactorShared<B> &sh = *reinterpret_cast<FactorShared<B> *>(smem);
     const int t = threadIdx.x, tile = blockIdx.x;
-    const int64_t mb = blockIdx.y;
+    const int64_t mb = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
     if (FIRST && a.trace && t == 0 && tile == 0 && mb == 0)
     {   // keep the previous iteration's first and last stamp of tile 0: the idle time between iterations
         a.trace[6] = a.trace[5];
@@ -633,7 +635,7 @@ __global__ void __launch_bounds__(Cfg<B>::T, (B <= 2 ? 4 : 1)) k_chain_forward(C
     extern __shared__ __align__(16) unsigned char smem[];
     SolveShared<B> &sh = *reinterpret_cast<SolveShared<B> *>(smem);
     const int t = threadIdx.x, tile = blockIdx.x;
-    const int64_t mb = blockIdx.y;
+    const int64_t mb = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
     stamp(a, FIRST ? 2 : 3, tile, 5);
     pdl_wait();
     if (lane_mode(a, mb) == 0) return; // idle lane
@@ -664,7 +666,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
     extern __shared__ __align__(16) unsigned char smem[];
     SolveShared<B> &sh = *reinterpret_cast<SolveShared<B> *>(smem);
     const int t = threadIdx.x, tile = blockIdx.x;
-    const int64_t mb = blockIdx.y;
+    const int64_t mb = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
     const LevelView &lv = a.lv;
     double *Ft = lv.F + mb * a.s_F + (size_t)tile * D::TILE_F;
     double *Yt = lv.Y + mb * a.s_Y + (size_t)tile * D::TILE_Y;
@@ -837,6 +839,8 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g, bool fuse)
     {
         const Plan &P = c->CH;
         a.lanes = L->count;
+        a.grid_lanes = L->list_active ? L->n_active : L->count;
+        a.lane_list = L->list_active;
         a.alpha_arr = L->w; // w[0][lane]
         a.s_jv = L->s_jv; a.s_mv = L->s_mv; a.s_vec = L->s_vec; a.s_hist = L->s_hist;
         a.s_F = P.fac_doubles; a.s_Y = P.y_doubles; a.s_red = P.red_doubles; a.s_rv = P.rv_doubles; a.s_x = P.x_doubles;
@@ -862,7 +866,7 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g, bool fuse)
 template <class K> void launch_pdl(daecpp_b200_ctx *c, K kernel, const ChainArgs &a, int threads, size_t smem)
 {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(a.lv.ntiles + a.extra_factor, a.lanes > 0 ? a.lanes : 1, 1);
+    cfg.gridDim = dim3(a.lv.ntiles + a.extra_factor, a.grid_lanes > 0 ? a.grid_lanes : 1, 1);
     cfg.blockDim = dim3(threads, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = c->stream;
@@ -965,6 +969,7 @@ int chain_refactor_async(daecpp_b200_ctx *c, double alpha)
     for (int g = 0; g < nlaunch; ++g)
     {
         ChainArgs a = level_args(c, g, fuse);
+        if (c->lanes && c->lanes->list_refactor) { a.lane_list = c->lanes->list_refactor; a.grid_lanes = c->lanes->n_refactor; }
         if (g == 0)
         {
             a.sj = c->dC.sj.p; a.sm = c->dC.sm.p; a.flags = c->dC.flags.p; a.desc = c->dC.desc.p;

@@ -103,6 +103,10 @@ struct LaneSet
     const int32_t *mode = nullptr;             // [count] DAECPP_B200_LANE_*
     const int32_t *hbase = nullptr;            // [count]
     const int32_t *order = nullptr;            // [count]
+    // compacted lane lists of the round: the kernels are launched over these (grid.y = list length), so a round with
+    // few lanes in flight costs few CTAs
+    const int32_t *list_active = nullptr, *list_refactor = nullptr;
+    int32_t n_active = 0, n_refactor = 0;
     const double *w = nullptr;                 // [5][count] BDF weights, w[0] = alpha
     int32_t *flags = nullptr;                  // [count][4]: update flags, pivot failure, wait time-out, spare
     unsigned long long *var = nullptr;         // [count] bit pattern of the lane's maximum variability

@@ -133,7 +133,7 @@ struct RefineArgs
 {
     int32_t n, lanes;
     int64_t s_vec, s_hist, s_jv, s_mv;
-    const int32_t *mode;
+    const int32_t *mode, *lane_list;
     const int32_t *jrowptr, *jrowslot, *jrowcol, *jsrc; // jsrc: slot -> triplet whose value it is (values stay in triplet order), or null
     const double *jv;
     const int32_t *mrowptr, *mrowslot, *mrowcol;
@@ -173,7 +173,7 @@ __device__ __forceinline__ Bdf refine_bdf(const RefineArgs &a, int lane)
 
 __global__ void k_refine_residual(RefineArgs a)
 {
-    const int lane = blockIdx.y;
+    const int lane = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
     if (a.mode && a.mode[lane] == 0) return;
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.n) return;
@@ -204,7 +204,7 @@ __global__ void k_refine_residual(RefineArgs a)
 // dx += e, xk += e and the error checks of dae-cpp/solver.hpp:590-619 on the corrected update
 __global__ void k_refine_apply(RefineArgs a)
 {
-    const int lane = blockIdx.y;
+    const int lane = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
     if (a.mode && a.mode[lane] == 0) return;
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t off = (int64_t)lane * a.s_vec;
@@ -328,7 +328,7 @@ int refine_last_solve(daecpp_b200_ctx *c, double alpha, double atol, double rtol
     if (L)
     {
         a.s_vec = L->s_vec; a.s_hist = L->s_hist; a.s_jv = L->s_jv; a.s_mv = L->s_mv;
-        a.mode = L->mode; a.jv = L->jv; a.mv = L->mv; a.alpha_arr = L->w;
+        a.mode = L->mode; a.lane_list = L->list_active; a.jv = L->jv; a.mv = L->mv; a.alpha_arr = L->w;
         a.lane_w = L->w; a.lane_order = L->order; a.lane_hbase = L->hbase; a.hist = L->hist;
         a.flags = L->flags; a.var = L->var; a.var_on = L->var_on; a.var_tol = L->var_tol;
     }
@@ -340,7 +340,7 @@ int refine_last_solve(daecpp_b200_ctx *c, double alpha, double atol, double rtol
         a.x0 = c->xh[0];
         a.flags = c->d_flags;
     }
-    const dim3 grid((unsigned)((c->n + TPB - 1) / TPB), (unsigned)(L ? L->count : 1));
+    const dim3 grid((unsigned)((c->n + TPB - 1) / TPB), (unsigned)(L ? (L->list_active ? L->n_active : L->count) : 1));
     k_refine_residual<<<grid, TPB, 0, st>>>(a);
     // Jb*e = r with the factors at hand: the solve reads c->b and writes c->dx
     double *keep_b = c->b, *keep_dx = c->dx;

@@ -137,8 +137,8 @@ namespace detail
 template <class Eq>
 __global__ void k_rhs(const Eq *__restrict__ eq, const daecpp_b200_functor_args a)
 {
-    const int lane = blockIdx.y;
-    if (a.mode[lane] < a.min_mode) return;
+    const int lane = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
+    if (!a.lane_list && a.mode[lane] < a.min_mode) return;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.n) return;
     const StateView x{a.x + (int64_t)lane * a.x_stride};
@@ -148,8 +148,8 @@ template <class Eq>
 __global__ void k_jacobian(const Eq *__restrict__ eq, const int32_t *__restrict__ ti, const int32_t *__restrict__ tj,
                            const int64_t nT, const daecpp_b200_functor_args a)
 {
-    const int lane = blockIdx.y;
-    if (a.mode[lane] < a.min_mode) return;
+    const int lane = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
+    if (!a.lane_list && a.mode[lane] < a.min_mode) return;
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= nT) return;
     const SeededView x{a.x + (int64_t)lane * a.x_stride, tj[k]};
@@ -186,7 +186,8 @@ class DeviceFunctors
     {
         const DeviceFunctors *self = static_cast<const DeviceFunctors *>(user);
         if (a->lanes != self->m_lanes) return 1;
-        const dim3 grid((unsigned)((a->n + 255) / 256), (unsigned)a->lanes);
+        if (a->lane_list && a->n_list == 0) return 0;
+        const dim3 grid((unsigned)((a->n + 255) / 256), (unsigned)(a->lane_list ? a->n_list : a->lanes));
         detail::k_rhs<Eq><<<grid, 256, 0, static_cast<cudaStream_t>(a->stream)>>>(self->m_eq, *a);
         return cudaGetLastError() == cudaSuccess ? 0 : 2;
     }
@@ -194,7 +195,8 @@ class DeviceFunctors
     {
         const DeviceFunctors *self = static_cast<const DeviceFunctors *>(user);
         if (a->lanes != self->m_lanes) return 1;
-        const dim3 grid((unsigned)((self->m_nT + 255) / 256), (unsigned)a->lanes);
+        if (a->lane_list && a->n_list == 0) return 0;
+        const dim3 grid((unsigned)((self->m_nT + 255) / 256), (unsigned)(a->lane_list ? a->n_list : a->lanes));
         detail::k_jacobian<Eq><<<grid, 256, 0, static_cast<cudaStream_t>(a->stream)>>>(self->m_eq, self->m_i, self->m_j, self->m_nT, *a);
         return cudaGetLastError() == cudaSuccess ? 0 : 2;
     }
@@ -210,9 +212,10 @@ class DeviceFunctors
     {
         const DeviceFunctors *self = static_cast<const DeviceFunctors *>(user);
         if (a->lanes != self->m_lanes) return 1;
-        for (int32_t lane = 0; lane < a->lanes; ++lane)
+        for (int32_t q = 0; q < (a->lane_list ? a->n_list : a->lanes); ++q)
         {
-            if (a->mode[lane] < a->min_mode) continue;
+            const int32_t lane = a->lane_list ? a->lane_list[q] : q;
+            if (!a->lane_list && a->mode[lane] < a->min_mode) continue;
             const StateView x{a->x + (int64_t)lane * a->x_stride};
             for (int32_t i = 0; i < a->n; ++i)
                 a->out[(int64_t)lane * a->out_stride + i] = self->m_eq[lane].template operator()<double>(x, a->t[lane], i);
@@ -223,9 +226,10 @@ class DeviceFunctors
     {
         const DeviceFunctors *self = static_cast<const DeviceFunctors *>(user);
         if (a->lanes != self->m_lanes) return 1;
-        for (int32_t lane = 0; lane < a->lanes; ++lane)
+        for (int32_t q = 0; q < (a->lane_list ? a->n_list : a->lanes); ++q)
         {
-            if (a->mode[lane] < a->min_mode) continue;
+            const int32_t lane = a->lane_list ? a->lane_list[q] : q;
+            if (!a->lane_list && a->mode[lane] < a->min_mode) continue;
             for (int64_t k = 0; k < self->m_nT; ++k)
             {
                 const SeededView x{a->x + (int64_t)lane * a->x_stride, self->m_j[k]};

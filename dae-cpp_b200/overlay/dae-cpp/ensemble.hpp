@@ -34,6 +34,7 @@
 #include <cstddef>
 #include <cstdio>
 #include <cstdlib>
+#include <memory>
 #include <thread>
 #include <utility>
 #include <vector>
@@ -396,14 +397,14 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     stamp("set_pattern");
     if ((rc = daecpp_b200_batch_set_mass_values(b, M.A.data(), 0, 0))) fatal("batch_set_mass_values", rc);
     {
-        std::vector<double> slab(members * n);
+        std::unique_ptr<double[]> slab(new double[members * n]);
         for (std::size_t m = 0; m < members; ++m)
         {
             const state_vector &x = x0.size() == 1 ? x0[0] : x0[m];
             ASSERT(x.size() == n, "solve_ensemble_device: initial states differ in size.");
-            std::copy(x.begin(), x.end(), slab.begin() + m * n);
+            std::copy(x.begin(), x.end(), slab.get() + m * n);
         }
-        if ((rc = daecpp_b200_batch_set_state(b, slab.data(), 0, static_cast<int32_t>(members)))) fatal("batch_set_state", rc);
+        if ((rc = daecpp_b200_batch_set_state(b, slab.get(), 0, static_cast<int32_t>(members)))) fatal("batch_set_state", rc);
     }
     stamp("set_state");
     device::DeviceFunctors<Eq> functors(eqs, shape);
@@ -461,14 +462,18 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     }
     stamp("rounds");
     {   // final states: the iterate of lanes that ended on an accepted step, x[0] of the others
-        std::vector<double> xk(members * n), xa(members * n);
-        if ((rc = daecpp_b200_batch_get_vector(b, 3, xk.data(), 0, static_cast<int32_t>(members)))) fatal("batch_get_vector", rc);
+        std::unique_ptr<double[]> xk(new double[members * n]), xa; // (not value-initialised: hundreds of megabytes for big sweeps)
+        if ((rc = daecpp_b200_batch_get_vector(b, 3, xk.get(), 0, static_cast<int32_t>(members)))) fatal("batch_get_vector", rc);
         bool need_x0 = false;
         for (std::size_t m = 0; m < members; ++m) need_x0 = need_x0 || !lanes[m].final_state_is_iterate();
-        if (need_x0 && (rc = daecpp_b200_batch_get_vector(b, 4, xa.data(), 0, static_cast<int32_t>(members)))) fatal("batch_get_vector", rc);
+        if (need_x0)
+        {
+            xa.reset(new double[members * n]);
+            if ((rc = daecpp_b200_batch_get_vector(b, 4, xa.get(), 0, static_cast<int32_t>(members)))) fatal("batch_get_vector", rc);
+        }
         for (std::size_t m = 0; m < members; ++m)
         {
-            const double *src = (lanes[m].final_state_is_iterate() ? xk.data() : xa.data()) + m * n;
+            const double *src = (lanes[m].final_state_is_iterate() ? xk.get() : xa.get()) + m * n;
             R.members[m].status = lanes[m].status;
             R.members[m].steps = lanes[m].accepted_steps;
             R.members[m].x.assign(src, src + n);

@@ -54,18 +54,21 @@ int dump(const std::map<std::string, std::string> &kv, const ensemble_result &R)
 }
 } // namespace
 
-// In-process entry for bench.py (ctypes): integrates members [first, first + count) of the C5 sweep
+// In-process entry for bench.py (ctypes): integrates members first, first + stride, ... (count of them) of the C5 sweep
 // (perovskite, lambda_m = 0.5 * 4^(m / (members - 1))) in lock step on the device named by DAECPP_B200_DEVICE.
 // out: [count][2N + 2] = {status, accepted steps, final state} per member (may be NULL);
 // stats[10]: {rounds, lane iterations, lane refactorisations, device ms, wall ms, failed members, accepted steps, checksum,
 //             kernels launched, setup ms}
-extern "C" int ensdev_perovskite(int64_t members, int64_t first, int64_t count, int32_t N, double t_end, int32_t variability, double *out,
-                                 double *stats)
+extern "C" int ensdev_perovskite(int64_t members, int64_t first, int64_t count, int64_t stride, int32_t N, double t_end, int32_t variability,
+                                 double *out, double *stats)
 {
     const std::size_t n = 2 * (std::size_t)N;
     std::vector<problems::PerovskiteEq> eqs;
-    for (int64_t m = first; m < first + count; ++m)
+    for (int64_t k = 0; k < count; ++k)
+    {   // members first, first + stride, ...: round-robin over the ranks spreads the slow (small lambda) members evenly
+        const int64_t m = first + k * stride;
         eqs.push_back(problems::PerovskiteEq::make(N, 1.0, 0.5 * std::pow(4.0, members > 1 ? double(m) / double(members - 1) : 0.0)));
+    }
     state_vector x0(n, 0.0);
     for (int k = 0; k < N; ++k) x0[k] = 1.0;
     SolverOptions o;

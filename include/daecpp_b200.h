@@ -222,8 +222,8 @@ typedef struct
 /* Device functors (opt-in).  The callbacks are given DEVICE pointers and the CUDA stream
  * to launch on; they must only enqueue work on that stream and return 0.  dae-cpp/device-functor.cuh builds
  * them from one templated equations(x, t, i) functor (the device twin of VectorFunctionElements +
- * JacobianMatrixShape, vector-function.hpp:46-72, jacobian-matrix.hpp:66-92).  Lanes with mode[lane] below
- * min_mode are skipped. */
+ * JacobianMatrixShape, vector-function.hpp:46-72, jacobian-matrix.hpp:66-92).  The lanes to evaluate are
+ * lane_list[0 .. n_list); when lane_list is NULL they are the lanes whose mode[lane] is at least min_mode. */
 typedef struct
 {
     int32_t n, lanes, min_mode, reserved;
@@ -231,6 +231,8 @@ typedef struct
     const double *x;              /* [lanes][x_stride]  Newton iterates xk                                   */
     const double *t;              /* [lanes]                                                                 */
     const int32_t *mode;          /* [lanes]                                                                 */
+    const int32_t *lane_list;     /* [n_list] or NULL                                                        */
+    int32_t n_list, reserved2;
     double *out;                  /* rhs: f [lanes][out_stride];  jacobian: triplet values [lanes][out_stride] */
     void *stream;                 /* cudaStream_t                                                            */
 } daecpp_b200_functor_args;
