@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -76,6 +77,8 @@ struct daecpp_b200_batch
 namespace
 {
 constexpr int TPB = 256;
+std::mutex g_bounce_mu;
+std::vector<char *> g_bounce_free; // page-locked bounce buffers of destroyed batches (process-wide, a few 16 MB blocks)
 
 #define BATCH_TRY(b, call)                                                                          \
     do                                                                                              \
@@ -175,7 +178,12 @@ void release(daecpp_b200_batch *b)
     if (b->h_ctl) cudaFreeHost(b->h_ctl);
     if (b->d_ctl) cudaFree(b->d_ctl);
     if (b->h_res) cudaFreeHost(b->h_res);
-    if (b->h_bounce) cudaFreeHost(b->h_bounce);
+    if (b->h_bounce)
+    {
+        std::lock_guard<std::mutex> lk(g_bounce_mu);
+        if (g_bounce_free.size() < 16) g_bounce_free.push_back(b->h_bounce);
+        else cudaFreeHost(b->h_bounce);
+    }
     for (cudaEvent_t e : b->ev_bounce) if (e) cudaEventDestroy(e);
     if (b->d_res) cudaFree(b->d_res);
     if (b->ev0) cudaEventDestroy(b->ev0);
@@ -377,7 +385,11 @@ static int copy_lanes(daecpp_b200_batch *b, double *dev, double *host_out, const
     cudaStream_t st = b->c->stream;
     if (!b->h_bounce)
     {
-        BATCH_TRY(b, cudaMallocHost((void **)&b->h_bounce, 2 * daecpp_b200_batch::BOUNCE_BYTES));
+        {   // page-locking 16 MB costs milliseconds: the buffers are kept for the next batch of the process
+            std::lock_guard<std::mutex> lk(g_bounce_mu);
+            if (!g_bounce_free.empty()) { b->h_bounce = g_bounce_free.back(); g_bounce_free.pop_back(); }
+        }
+        if (!b->h_bounce) BATCH_TRY(b, cudaMallocHost((void **)&b->h_bounce, 2 * daecpp_b200_batch::BOUNCE_BYTES));
         BATCH_TRY(b, cudaEventCreateWithFlags(&b->ev_bounce[0], cudaEventDisableTiming));
         BATCH_TRY(b, cudaEventCreateWithFlags(&b->ev_bounce[1], cudaEventDisableTiming));
     }
