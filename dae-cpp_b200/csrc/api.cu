@@ -704,12 +704,27 @@ int daecpp_b200_solve(daecpp_b200_ctx *c, double *dx_host)
     DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev0, c->stream));
     int rc = numeric_solve(c);
     if (rc) return rc;
+    // the linear-solver entry has no Newton loop behind it to absorb an inaccurate solve: one refinement step
+    // (r = b - Jb*dx in FP64 with fused multiply-adds, Jb*e = r, dx += e) always runs here.  Eigen::SparseLU reaches
+    // the same accuracy by pivoting (Eigen/src/SparseLU/SparseLU_pivotL.h:62-131).
+    if (c->refine_steps > 0 && !c->direct_csc && c->M.have_pattern && c->J.have_pattern &&
+        (rc = refine_last_solve(c, c->last_alpha, 0, 0, 0, true, false)))
+        return rc;
     DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev1, c->stream));
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     c->ms_last_solve = ms;
-    if (dx_host) return download_vector(c, dx_host, c->dx);
+    // a factorisation that went through without a flagged pivot can still deliver garbage (growth): a solution that
+    // is not finite is reported the way the reference reports a failed solve (solver.hpp:562-572)
+    if (dx_host)
+    {
+        rc = download_vector(c, dx_host, c->dx);
+        if (rc) return rc;
+        for (int32_t k = 0; k < c->n; ++k)
+            if (!std::isfinite(dx_host[k])) return fail(c, DAECPP_B200_ESOLVE, "the solution is not finite");
+        return DAECPP_B200_OK;
+    }
     return DAECPP_B200_OK;
 }
 
@@ -825,6 +840,7 @@ int daecpp_b200_get_stat(daecpp_b200_ctx *c, const char *key, double *value)
     else if (k == "cb_doubles") *value = (double)c->S.cb_size;
     else if (k == "nnz_jb") *value = (double)c->nnzU;
     else if (k == "n_missing_diag") *value = c->S.n_missing_diag;
+    else if (k == "n_rows_moved") *value = c->S.n_rows_moved;
     else if (k == "ms_phase_assembly") *value = c->n_phase_samples ? c->ms_phase[0] / c->n_phase_samples : 0;
     else if (k == "ms_phase_residual") *value = c->n_phase_samples ? c->ms_phase[1] / c->n_phase_samples : 0;
     else if (k == "ms_phase_refactor") *value = c->n_phase_samples ? c->ms_phase[2] / c->n_phase_samples : 0;
@@ -887,6 +903,8 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "chain_min_n") { c->chain_min_n = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "chain_max_block") { c->chain_max_b = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "trace_units") c->trace_units = value != 0.0;
+    else if (k == "transversal") { c->sopt.transversal = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "pivot_rel") c->pivot_rel = value;
     else if (k == "max_super") { c->sopt.max_super = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else return fail(c, DAECPP_B200_EINVAL, "unknown option key");
     return DAECPP_B200_OK;

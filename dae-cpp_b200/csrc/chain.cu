@@ -48,7 +48,7 @@ struct ChainArgs
     // factor
     const int32_t *sj, *sm, *flags, *desc;
     const double *jv, *mv;
-    double alpha, tol;
+    double alpha, tol, rel;
     // solve
     const double *rhs;
     const int32_t *perm;
@@ -254,16 +254,16 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
     int fail = 0;
     {
         Mat<B> G, Dk, SL, H;
-        factor_phase0<B>(t, nvalid, sh, Ft, a.tol, fail, G, Dk, SL, H);
+        factor_phase0<B>(t, nvalid, sh, Ft, a.tol, a.rel, fail, G, Dk, SL, H);
         __syncthreads();
         factor_store1<B>(t, sh, G, Dk, SL, H);
     }
     __syncthreads();
     stamp(a, tk, tile, 2);
-    factor_phase1<B>(t, nvalid, sh, Ft, a.tol, fail);
+    factor_phase1<B>(t, nvalid, sh, Ft, a.tol, a.rel, fail);
     __syncthreads();
     stamp(a, tk, tile, 3);
-    if (t == 0) factor_phase2<B>(tile, lv.ntiles, lv.is_top != 0, sh, Ft, lv.red_out + mb * a.s_red, a.tol, fail);
+    if (t == 0) factor_phase2<B>(tile, lv.ntiles, lv.is_top != 0, sh, Ft, lv.red_out + mb * a.s_red, a.tol, a.rel, fail);
     if (fail) atomicOr(&flag_words(a, mb)[3], 1);
     stamp(a, tk, tile, 4);
 }
@@ -848,6 +848,7 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g, bool fuse)
         a.hist = L->hist; a.lane_flags = L->flags; a.lane_var = L->var; a.var_on = L->var_on; a.var_tol = L->var_tol;
     }
     a.tol = c->pivot_tol;
+    a.rel = c->pivot_rel;
     a.packed = c->chain_packed;
     a.prefetch = c->chain_prefetch;
     if (c->trace_units && c->CH.levels.size() == 2)

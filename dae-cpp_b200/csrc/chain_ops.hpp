@@ -262,20 +262,31 @@ template <int B> CH_HD Vec<B> ldv(const double *p, int count, int i)
 // ---- elimination of one chunk's interior (QI rows).  The rows of step k+1 are fetched before the
 // arithmetic of step k and the factor stores come last, so that the only thing a step waits for is
 // the previous pivot: reciprocal, one multiply, one fused multiply-add.
+template <int B> CH_HD double mmaxabs(const Mat<B> &X)
+{
+    double m = 0.0;
+#pragma unroll
+    for (int e = 0; e < B * B; ++e) m = fmax(m, fabs(X.a[e]));
+    return m;
+}
+// tol: absolute pivot threshold; rel: a pivot below rel x (largest entry of the row's own diagonal and
+// super-diagonal blocks before elimination) has been cancelled to noise and counts as zero as well.
 template <int B, int QI, class Rows, class Fac>
-CH_HD void chunk_factor(const Rows &src, const Fac &dst, double tol, int &fail, Mat<B> &G, Mat<B> &Dk, Mat<B> &SL, Mat<B> &H)
+CH_HD void chunk_factor(const Rows &src, const Fac &dst, double tol, double rel, int &fail, Mat<B> &G, Mat<B> &Dk, Mat<B> &SL, Mat<B> &H)
 {
     G = src.A(0);
     Dk = src.D(0);
     H = src.Hinit();
     SL = mzero<B>();
     Mat<B> C = src.C(0), An = src.A(1), Dn = src.D(1);
+    double scale = mmaxabs<B>(Dk);
 #pragma unroll
     for (int k = 0; k < QI; ++k)
     {
         Mat<B> C1, A2, D2;
         if (k + 1 < QI) { C1 = src.C(k + 1); A2 = src.A(k + 2); D2 = src.D(k + 2); }
-        const Mat<B> Dinv = minv<B>(Dk, tol, fail);
+        const Mat<B> Dinv = minv<B>(Dk, fmax(tol, rel * fmax(scale, mmaxabs<B>(C))), fail);
+        scale = mmaxabs<B>(Dn);
         const Mat<B> L = mmul<B>(An, Dinv);
         const Mat<B> LL = mmul<B>(H, Dinv);
         Dk = Dn;
@@ -669,13 +680,13 @@ template <int B> CH_HD void stage_rhs_reduced(int t, int nt, int tile, int rows,
 // nvalid: rows of the tile that exist at this level (the rest is identity padding whose chunks
 // are skipped consistently by factor and solve).
 template <int B>
-CH_HD void factor_phase0(int t, int nvalid, FactorShared<B> &sh, double *Ftile, double tol, int &fail, Mat<B> &G, Mat<B> &Dk,
+CH_HD void factor_phase0(int t, int nvalid, FactorShared<B> &sh, double *Ftile, double tol, double rel, int &fail, Mat<B> &G, Mat<B> &Dk,
                          Mat<B> &SL, Mat<B> &H)
 {
     using D = Dim<B>;
     G = mzero<B>(); Dk = mident<B>(); SL = mzero<B>(); H = mzero<B>();
     if (t * D::Q0 < nvalid)
-        chunk_factor<B, D::Q0 - 1>(staged_rows<B>(sh.S, t), FacRef<B, D::T>{Ftile + t}, tol, fail, G, Dk, SL, H);
+        chunk_factor<B, D::Q0 - 1>(staged_rows<B>(sh.S, t), FacRef<B, D::T>{Ftile + t}, tol, rel, fail, G, Dk, SL, H);
 }
 // after a barrier: every thread is done reading the staged tile
 template <int B>
@@ -684,7 +695,7 @@ CH_HD void factor_store1(int t, FactorShared<B> &sh, const Mat<B> &G, const Mat<
     using D = Dim<B>;
     st<B>(sh.G1(), D::T, t, G); st<B>(sh.D1(), D::T, t, Dk); st<B>(sh.SL1(), D::T, t, SL); st<B>(sh.H1(), D::T, t, H);
 }
-template <int B> CH_HD void factor_phase1(int c, int nvalid, FactorShared<B> &sh, double *Ftile, double tol, int &fail)
+template <int B> CH_HD void factor_phase1(int c, int nvalid, FactorShared<B> &sh, double *Ftile, double tol, double rel, int &fail)
 {
     using D = Dim<B>;
     if (c >= D::Q2) return;
@@ -692,19 +703,19 @@ template <int B> CH_HD void factor_phase1(int c, int nvalid, FactorShared<B> &sh
     if (c * D::Q1 * D::Q0 < nvalid)
     {
         ReducedRows<B, D::T> src{sh.G1(), sh.D1(), sh.SL1(), sh.H1(), c * D::Q1};
-        chunk_factor<B, D::Q1 - 1>(src, FacRef<B, D::Q2>{Ftile + D::F0 + c}, tol, fail, G, Dk, SL, H);
+        chunk_factor<B, D::Q1 - 1>(src, FacRef<B, D::Q2>{Ftile + D::F0 + c}, tol, rel, fail, G, Dk, SL, H);
     }
     st<B>(sh.G2(), D::Q2, c, G); st<B>(sh.D2(), D::Q2, c, Dk); st<B>(sh.SL2(), D::Q2, c, SL); st<B>(sh.H2(), D::Q2, c, H);
 }
 // thread 0 only.  red: this level's reduced system [4][ntiles][BB] (G, Df, SL, Hf).
 template <int B>
-CH_HD void factor_phase2(int tile, int ntiles, bool is_top, FactorShared<B> &sh, double *Ftile, double *red, double tol,
+CH_HD void factor_phase2(int tile, int ntiles, bool is_top, FactorShared<B> &sh, double *Ftile, double *red, double tol, double rel,
                          int &fail)
 {
     using D = Dim<B>;
     Mat<B> G, Dk, SL, H;
     ReducedRows<B, D::Q2> src{sh.G2(), sh.D2(), sh.SL2(), sh.H2(), 0};
-    chunk_factor<B, D::Q2 - 1>(src, FacRef<B, 1>{Ftile + D::F0 + D::F1}, tol, fail, G, Dk, SL, H);
+    chunk_factor<B, D::Q2 - 1>(src, FacRef<B, 1>{Ftile + D::F0 + D::F1}, tol, rel, fail, G, Dk, SL, H);
     // updates of the left tile's separator collected from the first chunk of every level
     for (int e = 0; e < B * B; ++e) SL.a[e] += sh.SL1()[e * D::T] + sh.SL2()[e * D::Q2];
     if (is_top)

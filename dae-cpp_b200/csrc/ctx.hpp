@@ -64,6 +64,7 @@ struct TripletSet
 struct DeviceSymbolic
 {
     // global front tables (used by the per-level kernels that handle big fronts)
+    DevBuf<int32_t> perm_rhs; // row of the right-hand side that feeds elimination position k (= perm unless rows were moved to fill the diagonal)
     DevBuf<int32_t> perm, iperm, sn_first, sn_rows, sn_rel, child_ptr, child_idx, big_sn;
     DevBuf<int64_t> sn_rowptr, sn_lu, sn_cb;
     // subtree-unit schedule (schedule.hpp)
@@ -72,7 +73,7 @@ struct DeviceSymbolic
     DevBuf<int32_t> sync_words; // [0] ticket, [1..nunit] dep counters, [1+nunit..] backward done epochs
     void release()
     {
-        perm.release(); iperm.release(); sn_first.release(); sn_rows.release(); sn_rel.release();
+        perm.release(); perm_rhs.release(); iperm.release(); sn_first.release(); sn_rows.release(); sn_rel.release();
         child_ptr.release(); child_idx.release(); big_sn.release(); sn_rowptr.release(); sn_lu.release();
         sn_cb.release(); blob.release(); unit_blob.release(); ent_u.release(); ent_dst.release();
         ent_sj.release(); ent_sm.release(); big_u.release(); big_sj.release(); big_sm.release(); big_dst.release();
@@ -229,6 +230,9 @@ struct daecpp_b200_ctx
     bool assemble_only = false;
     bool pinned_io = false; // host vectors handed to the ABI are page-locked: no staging copies
     double pivot_tol = 0.0;
+    // chain path: a pivot below pivot_rel x (largest entry of its own matrix row) has lost every significant digit
+    // to cancellation and is reported like a zero pivot (Eigen would have pivoted away from it)
+    double pivot_rel = 1e-14;
 
     // statistics
     double n_symbolic = 0, n_refactor = 0, n_solve = 0, n_cold = 0, kernels = 0;
@@ -296,5 +300,5 @@ int launch_update(daecpp_b200_ctx *c, double atol, double rtol, double max_err_a
 int launch_accept(daecpp_b200_ctx *c, int32_t variability_on, double tol);
 // guarded refinement of the last solve (single system, or the lanes of c->lanes whose mode word is not idle):
 // r = b - Jb*dx, Jb*e = r with the current factors, dx += e, xk += e, flags (and variability) recomputed
-int refine_last_solve(daecpp_b200_ctx *c, double alpha, double atol, double rtol, double max_err_abs, bool b_is_stored);
+int refine_last_solve(daecpp_b200_ctx *c, double alpha, double atol, double rtol, double max_err_abs, bool b_is_stored, bool update = true);
 } // namespace daecpp_b200

@@ -973,6 +973,13 @@ int upload_symbolic(daecpp_b200_ctx *c)
     int rc;
     if ((rc = upload(c, c->dS.perm, S.perm))) return rc;
     if ((rc = upload(c, c->dS.iperm, S.iperm))) return rc;
+    {
+        std::vector<int32_t> pr(S.perm);
+        if (!S.row_src.empty())
+            for (int32_t &v : pr) v = S.row_src[(size_t)v];
+        if ((rc = upload(c, c->dS.perm_rhs, pr))) return rc;
+        DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st)); // pr is a local
+    }
     if (S.nbig)
     { // the global front tables are only read by the per-level kernels of big fronts
         if ((rc = upload(c, c->dS.sn_first, S.sn_first))) return rc;
@@ -1197,7 +1204,7 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
     c->solve_epoch += 1;
     if (!direct)
     {
-        k_permute_in<<<(n + 255) / 256, 256, 0, st>>>(n, c->dS.perm.p, c->b, c->work);
+        k_permute_in<<<(n + 255) / 256, 256, 0, st>>>(n, c->dS.perm_rhs.p, c->b, c->work);
         c->kernels += 1;
     }
     for (size_t l = 0; l < c->groups.size(); ++l)

@@ -65,6 +65,7 @@ struct UnitArgs
     double *LU, *CB;
     // solve
     const int32_t *perm; // nullptr: rhs / solution already in elimination order
+    const int32_t *perm_rhs; // forward sweep: row of the right-hand side per elimination position (ctx.hpp: DeviceSymbolic)
     const double *rhs;
     double *y, *upd, *out;
     // fused update (solver.hpp:590-619)
@@ -246,7 +247,7 @@ __global__ void k_unit_forward(UnitArgs A)
             for (int32_t k = 0; k < F[F_S]; ++k)
             {
                 const int32_t col = F[F_COL0] + k;
-                Y[F[F_YOFF] + k] = A.rhs[A.perm ? A.perm[col] : col];
+                Y[F[F_YOFF] + k] = A.rhs[A.perm_rhs ? A.perm_rhs[col] : col];
             }
         }
         stamp(A, unit, 1);
@@ -485,6 +486,7 @@ int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct)
 {
     UnitArgs A = base_args(c, g);
     A.perm = direct ? c->dS.perm.p : nullptr;
+    A.perm_rhs = direct ? c->dS.perm_rhs.p : nullptr;
     A.rhs = direct ? c->b : c->work;
     A.y = c->work; A.upd = c->upd.p;
     if (c->trace_units && c->trace.p) A.trace = c->trace.p + (size_t)c->S.nunit * 4;

@@ -222,8 +222,109 @@ struct Dissector
 static bool build_schedule(int32_t n, const int32_t *outer, const int32_t *inner, const SymbolicOptions &opt, Symbolic &S,
                            const std::vector<int32_t> &sn_of_col, const char **err);
 
+static bool analyse_core(int32_t n, const int32_t *outer, const int32_t *inner, const SymbolicOptions &opt, Symbolic &S, const char **err);
+
+// Maximum transversal: a row for every column such that the permuted matrix has a structurally zero-free
+// diagonal (depth-first augmenting paths with a cheap first pass that keeps existing diagonal entries;
+// Duff's MC21 idea).  The reference needs none: Eigen::SparseLU pivots numerically at factorisation time
+// (Eigen/src/SparseLU/SparseLU_pivotL.h:62-131); a static-pivot factorisation must at least start from a
+// pattern whose diagonal exists -- index-1 DAEs routinely write `0 = x_j - g(t)` in a row other than j.
+// Returns false when the pattern is structurally singular.
+static bool maximum_transversal(int32_t n, const int32_t *outer, const int32_t *inner, std::vector<int32_t> &row_of_col)
+{
+    row_of_col.assign((size_t)n, -1);
+    std::vector<int32_t> col_of_row((size_t)n, -1);
+    for (int32_t j = 0; j < n; ++j) // keep the diagonal wherever it exists
+        if (std::binary_search(inner + outer[j], inner + outer[j + 1], j)) { row_of_col[j] = j; col_of_row[j] = j; }
+    for (int32_t j = 0; j < n; ++j) // cheap assignment
+    {
+        if (row_of_col[j] >= 0) continue;
+        for (int32_t p = outer[j]; p < outer[j + 1]; ++p)
+            if (col_of_row[inner[p]] < 0) { row_of_col[j] = inner[p]; col_of_row[inner[p]] = j; break; }
+    }
+    std::vector<int32_t> visited((size_t)n, -1), stack_col, stack_pos;
+    for (int32_t j0 = 0; j0 < n; ++j0)
+    {
+        if (row_of_col[j0] >= 0) continue;
+        // iterative depth-first search for an augmenting path from column j0
+        stack_col.assign(1, j0); stack_pos.assign(1, outer[j0]);
+        visited[j0] = j0;
+        bool found = false;
+        while (!stack_col.empty() && !found)
+        {
+            const int32_t j = stack_col.back();
+            int32_t &p = stack_pos.back();
+            bool descended = false;
+            for (; p < outer[j + 1]; ++p)
+            {
+                const int32_t i = inner[p];
+                const int32_t jn = col_of_row[i];
+                if (jn < 0)
+                {   // free row: flip the path
+                    int32_t row = i;
+                    for (size_t d = stack_col.size(); d-- > 0;)
+                    {
+                        const int32_t cj = stack_col[d];
+                        const int32_t prev = row_of_col[cj];
+                        row_of_col[cj] = row; col_of_row[row] = cj;
+                        row = prev;
+                    }
+                    found = true;
+                    break;
+                }
+                if (visited[jn] != j0)
+                {
+                    visited[jn] = j0;
+                    ++p;
+                    stack_col.push_back(jn); stack_pos.push_back(outer[jn]);
+                    descended = true;
+                    break;
+                }
+            }
+            if (found) break;
+            if (!descended) { stack_col.pop_back(); stack_pos.pop_back(); }
+        }
+        if (!found) return false;
+    }
+    return true;
+}
+
 bool analyse_pattern(int32_t n, const int32_t *outer, const int32_t *inner, const SymbolicOptions &opt,
                      Symbolic &S, const char **err)
+{
+    int32_t missing = 0;
+    for (int32_t j = 0; j < n; ++j)
+        if (!std::binary_search(inner + outer[j], inner + outer[j + 1], j)) ++missing;
+    std::vector<int32_t> row_of_col;
+    if (missing == 0 || !opt.transversal || !maximum_transversal(n, outer, inner, row_of_col))
+        return analyse_core(n, outer, inner, opt, S, err); // (a structurally singular pattern fails numerically, like Eigen's would)
+    // Row i of the matrix is moved to position rowmap[i]: A' = Q A has a zero-free diagonal.  The analysis runs on
+    // A'; matrix slots are mapped back, and the right-hand side is read through row_src (Q A x = Q b).
+    std::vector<int32_t> rowmap((size_t)n);
+    for (int32_t j = 0; j < n; ++j) rowmap[row_of_col[j]] = j;
+    const int64_t nnz = outer[n];
+    std::vector<int32_t> inner2((size_t)nnz), slot2((size_t)nnz);
+    std::vector<std::pair<int32_t, int32_t>> colbuf;
+    for (int32_t j = 0; j < n; ++j)
+    {
+        colbuf.clear();
+        for (int32_t p = outer[j]; p < outer[j + 1]; ++p) colbuf.emplace_back(rowmap[inner[p]], p);
+        std::sort(colbuf.begin(), colbuf.end());
+        for (size_t k = 0; k < colbuf.size(); ++k) { inner2[(size_t)outer[j] + k] = colbuf[k].first; slot2[(size_t)outer[j] + k] = colbuf[k].second; }
+    }
+    if (!analyse_core(n, outer, inner2.data(), opt, S, err)) return false;
+    for (int32_t &u : S.ent_u) u = slot2[(size_t)u];
+    for (int32_t &u : S.big_u) u = slot2[(size_t)u];
+    S.row_src.assign((size_t)n, 0);
+    for (int32_t i = 0; i < n; ++i) S.row_src[(size_t)rowmap[i]] = i;
+    S.n_missing_diag = missing;
+    S.n_rows_moved = 0;
+    for (int32_t i = 0; i < n; ++i) S.n_rows_moved += rowmap[i] != i;
+    return true;
+}
+
+static bool analyse_core(int32_t n, const int32_t *outer, const int32_t *inner, const SymbolicOptions &opt,
+                         Symbolic &S, const char **err)
 {
     S = Symbolic();
     S.n = n;

@@ -23,6 +23,7 @@ struct SymbolicOptions
     int unit_smem_bytes = -1; // shared-memory budget of one subtree unit (-1: chosen from the problem
                               // size; 0: no units, every front goes through the per-level kernels)
     int serial_dim = 4;     // fronts up to this order are factored by one thread each
+    int transversal = 1;    // permute rows to a structurally zero-free diagonal first when the diagonal has holes
 };
 
 struct LaunchGroup
@@ -82,6 +83,10 @@ struct Symbolic
     double flops = 0.0;
     int32_t max_front = 0, max_pivot_block = 0;
     int32_t n_missing_diag = 0; // structurally absent diagonal entries (become explicit zeros)
+    // maximum transversal (only when the diagonal has holes): the analysed matrix is Q*A with row row_src[r] of A in
+    // row r; the right-hand side is read through it.  Empty: Q = I.
+    std::vector<int32_t> row_src;
+    int32_t n_rows_moved = 0;
 
     int32_t s_of(int32_t f) const { return sn_first[f + 1] - sn_first[f]; }
     int32_t r_of(int32_t f) const { return (int32_t)(sn_rowptr[f + 1] - sn_rowptr[f]); }

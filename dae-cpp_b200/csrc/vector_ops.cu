@@ -154,6 +154,7 @@ struct RefineArgs
     unsigned long long *var;
     int32_t var_on;
     double var_tol;
+    int32_t update; // 0: dx += e only (linear-solver entry: no iterate, no flags)
 };
 
 __device__ __forceinline__ Bdf refine_bdf(const RefineArgs &a, int lane)
@@ -212,10 +213,11 @@ __global__ void k_refine_apply(RefineArgs a)
     double v = 0.0;
     if (i < a.n)
     {
-        const double *x0 = a.lane_hbase ? a.hist + (int64_t)(a.lane_hbase[lane] & 3) * a.s_hist + off : a.x0;
         const double e = a.e[off + i];
         const double d = __dadd_rn(a.dx[off + i], e);
         a.dx[off + i] = d;
+        if (!a.update) return;
+        const double *x0 = a.lane_hbase ? a.hist + (int64_t)(a.lane_hbase[lane] & 3) * a.s_hist + off : a.x0;
         const double xn = __dadd_rn(a.xk[off + i], e);
         a.xk[off + i] = xn;
         const double ad = fabs(d), xa = fabs(x0[i]);
@@ -297,7 +299,7 @@ int launch_update(daecpp_b200_ctx *c, double atol, double rtol, double max_err_a
 }
 
 
-int refine_last_solve(daecpp_b200_ctx *c, double alpha, double atol, double rtol, double max_err_abs, bool b_is_stored)
+int refine_last_solve(daecpp_b200_ctx *c, double alpha, double atol, double rtol, double max_err_abs, bool b_is_stored, bool update)
 {
     int rc;
     const LaneSet *L = c->lanes;
@@ -325,6 +327,7 @@ int refine_last_solve(daecpp_b200_ctx *c, double alpha, double atol, double rtol
     a.f = c->f; a.dx_in = c->dx; a.dx = c->dx; a.xk = c->xk; a.r = r; a.e = e;
     a.b = b_is_stored ? c->b : nullptr;
     a.atol = atol; a.rtol = rtol; a.max_err_abs = max_err_abs; a.floor = c->refine_floor;
+    a.update = update ? 1 : 0;
     if (L)
     {
         a.s_vec = L->s_vec; a.s_hist = L->s_hist; a.s_jv = L->s_jv; a.s_mv = L->s_mv;

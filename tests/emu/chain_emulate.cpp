@@ -43,10 +43,10 @@ int run(const Plan &P, const double *vals, const double *b, double *x, int nrhs_
                 else stage_matrix_reduced<B>(t, D::T, tile, L.rows, fsh->S, RED.data() + P.levels[g - 1].red0);
             }
             std::vector<Mat<B>> rG(D::T), rD(D::T), rS(D::T), rH(D::T);
-            for (int t = 0; t < D::T; ++t) factor_phase0<B>(t, nvalid, *fsh, Ft, 0.0, fail, rG[t], rD[t], rS[t], rH[t]);
+            for (int t = 0; t < D::T; ++t) factor_phase0<B>(t, nvalid, *fsh, Ft, 0.0, 1e-14, fail, rG[t], rD[t], rS[t], rH[t]);
             for (int t = 0; t < D::T; ++t) factor_store1<B>(t, *fsh, rG[t], rD[t], rS[t], rH[t]);
-            for (int t = 0; t < D::T; ++t) factor_phase1<B>(t, nvalid, *fsh, Ft, 0.0, fail);
-            factor_phase2<B>(tile, L.ntiles, top, *fsh, Ft, RED.data() + L.red0, 0.0, fail);
+            for (int t = 0; t < D::T; ++t) factor_phase1<B>(t, nvalid, *fsh, Ft, 0.0, 1e-14, fail);
+            factor_phase2<B>(tile, L.ntiles, top, *fsh, Ft, RED.data() + L.red0, 0.0, 1e-14, fail);
         }
     }
     if (fail) return 2;

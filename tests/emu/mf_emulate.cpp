@@ -123,7 +123,7 @@ extern "C" int mfemu_solve(int32_t n, const int32_t *outer, const int32_t *inner
     }
 
     // ---------------------------------------------------------------- forward sweep
-    for (int32_t k = 0; k < n; ++k) y[k] = b[S.perm[k]];
+    for (int32_t k = 0; k < n; ++k) y[k] = b[S.row_src.empty() ? S.perm[k] : S.row_src[(size_t)S.perm[k]]]; // Q A x = Q b
     std::vector<double> Y, U, X;
     for (const LaunchGroup &g : S.groups)
     {
