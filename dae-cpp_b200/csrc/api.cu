@@ -1,6 +1,7 @@
 // C ABI of libdaecpp_b200.so (see include/daecpp_b200.h for the contract and the reference
 // regions each entry point replaces).
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <chrono>
 #include <mutex>
@@ -313,12 +314,18 @@ int daecpp_b200_set_blocking_sync(int device, int on)
 int daecpp_b200_host_register(void *p, size_t bytes)
 {
     if (!p || !bytes) return DAECPP_B200_EINVAL;
-    return cudaHostRegister(p, bytes, cudaHostRegisterPortable) == cudaSuccess ? DAECPP_B200_OK : DAECPP_B200_ECUDA;
+    const cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+    if (e != cudaSuccess) cudaGetLastError();
+    if (std::getenv("DAECPP_B200_TRACE_PIN")) std::fprintf(stderr, "daecpp_b200: page lock of %zu bytes %s\n", bytes, e == cudaSuccess ? "taken" : "refused");
+    return e == cudaSuccess ? DAECPP_B200_OK : DAECPP_B200_ECUDA;
 }
 int daecpp_b200_host_unregister(void *p)
 {
     if (!p) return DAECPP_B200_EINVAL;
-    return cudaHostUnregister(p) == cudaSuccess ? DAECPP_B200_OK : DAECPP_B200_ECUDA;
+    const cudaError_t e = cudaHostUnregister(p);
+    if (e != cudaSuccess) cudaGetLastError();
+    if (std::getenv("DAECPP_B200_TRACE_PIN")) std::fprintf(stderr, "daecpp_b200: page lock %s\n", e == cudaSuccess ? "released" : "release failed");
+    return e == cudaSuccess ? DAECPP_B200_OK : DAECPP_B200_ECUDA;
 }
 
 int daecpp_b200_set_state(daecpp_b200_ctx *c, const double *x0)
@@ -398,6 +405,7 @@ int daecpp_b200_refactor(daecpp_b200_ctx *c, double alpha)
     int rc = build_union(c);
     if (rc) return rc;
     if (c->assemble_only) return assemble_values_only(c, alpha);
+    c->alpha_hint = alpha;
     if (!c->have_symbolic && (rc = upload_symbolic(c))) return rc;
     return numeric_refactor(c, alpha);
 }
@@ -562,6 +570,7 @@ static int prepare_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t or
     if (!bdf_weights(order, dt, w)) return fail(c, DAECPP_B200_EINVAL, "unsupported time integration order");
     int rc = build_union(c);
     if (rc) return rc;
+    c->alpha_hint = w[0];
     if (!c->have_symbolic && (rc = upload_symbolic(c))) return rc;
     if (!do_refactor && !c->have_factor) return fail(c, DAECPP_B200_EINVAL, "no valid factorisation");
     return DAECPP_B200_OK;

@@ -209,6 +209,7 @@ struct daecpp_b200_ctx
     bool jvals_from_triplets = false; // fused assembly reads the staged triplet values directly
     daecpp_b200::DevBuf<double> LU, CB, upd;
     double last_alpha = 0.0;
+    double alpha_hint = 0.0; // alpha of the factorisation about to follow a symbolic analysis (row matching weights)
     bool blocked_lu = true;        // big fronts: blocked multi-CTA LU (numeric.cu) instead of one CTA per front
     int blocked_lu_min_dim = 96;   // level groups whose largest front is at least this order
     bool bf_pdl = true;            // big fronts: panel / trailing-update launches chained by programmatic dependent launch

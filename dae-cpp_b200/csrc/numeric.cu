@@ -964,7 +964,27 @@ int upload_symbolic(daecpp_b200_ctx *c)
         }
     }
     const char *err = nullptr;
-    if (!analyse_pattern(n, outer.data(), inner.data(), c->sopt, c->S, &err))
+    // a diagonal with holes: the row matching of the analysis prefers big entries, so hand it the magnitudes of the
+    // matrix about to be factored (Jb = J - alpha*M with the alpha the caller announced; static afterwards)
+    std::vector<double> weights;
+    {
+        int32_t missing = 0;
+        for (int32_t j = 0; j < n; ++j)
+            if (!std::binary_search(inner.begin() + outer[j], inner.begin() + outer[j + 1], j)) ++missing;
+        if (missing && c->sopt.transversal && !c->direct_csc && c->nnzU)
+        {
+            int rcw = jb_values(c, c->alpha_hint);
+            if (rcw) return rcw;
+            weights.resize((size_t)c->nnzU);
+            DAECPP_CUDA_TRY(c, cudaMemcpyAsync(weights.data(), c->u_vals.p, sizeof(double) * c->nnzU, cudaMemcpyDeviceToHost, st));
+            DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
+            for (double &v : weights) v = std::fabs(v);
+        }
+    }
+    c->sopt.weights = weights.empty() ? nullptr : weights.data();
+    const bool analysed = analyse_pattern(n, outer.data(), inner.data(), c->sopt, c->S, &err);
+    c->sopt.weights = nullptr;
+    if (!analysed)
     {
         c->err = err ? err : "symbolic analysis failed";
         return DAECPP_B200_ENOMEM;

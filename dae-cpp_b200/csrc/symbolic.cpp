@@ -230,17 +230,29 @@ static bool analyse_core(int32_t n, const int32_t *outer, const int32_t *inner, 
 // (Eigen/src/SparseLU/SparseLU_pivotL.h:62-131); a static-pivot factorisation must at least start from a
 // pattern whose diagonal exists -- index-1 DAEs routinely write `0 = x_j - g(t)` in a row other than j.
 // Returns false when the pattern is structurally singular.
-static bool maximum_transversal(int32_t n, const int32_t *outer, const int32_t *inner, std::vector<int32_t> &row_of_col)
+static bool maximum_transversal(int32_t n, const int32_t *outer, const int32_t *inner, const double *w, std::vector<int32_t> &row_of_col)
 {
     row_of_col.assign((size_t)n, -1);
     std::vector<int32_t> col_of_row((size_t)n, -1);
+    // candidate rows of every column, heaviest first when magnitudes are known (a poor man's weighted matching:
+    // the static elimination order has to live with the diagonal chosen here, so big entries are preferred --
+    // the idea of MC64 / SuperLU_DIST's static pivoting, without the optimality)
+    std::vector<int32_t> cand(inner, inner + outer[n]);
+    if (w)
+        for (int32_t j = 0; j < n; ++j)
+            std::stable_sort(cand.begin() + outer[j], cand.begin() + outer[j + 1], [&](int32_t a, int32_t b) {
+                const int32_t *lo = inner + outer[j];
+                const double wa = w[outer[j] + (std::lower_bound(lo, inner + outer[j + 1], a) - lo)];
+                const double wb = w[outer[j] + (std::lower_bound(lo, inner + outer[j + 1], b) - lo)];
+                return wa > wb;
+            });
     for (int32_t j = 0; j < n; ++j) // keep the diagonal wherever it exists
         if (std::binary_search(inner + outer[j], inner + outer[j + 1], j)) { row_of_col[j] = j; col_of_row[j] = j; }
     for (int32_t j = 0; j < n; ++j) // cheap assignment
     {
         if (row_of_col[j] >= 0) continue;
         for (int32_t p = outer[j]; p < outer[j + 1]; ++p)
-            if (col_of_row[inner[p]] < 0) { row_of_col[j] = inner[p]; col_of_row[inner[p]] = j; break; }
+            if (col_of_row[cand[p]] < 0) { row_of_col[j] = cand[p]; col_of_row[cand[p]] = j; break; }
     }
     std::vector<int32_t> visited((size_t)n, -1), stack_col, stack_pos;
     for (int32_t j0 = 0; j0 < n; ++j0)
@@ -253,11 +265,11 @@ static bool maximum_transversal(int32_t n, const int32_t *outer, const int32_t *
         while (!stack_col.empty() && !found)
         {
             const int32_t j = stack_col.back();
-            int32_t &p = stack_pos.back();
+            int32_t p = stack_pos.back();
             bool descended = false;
             for (; p < outer[j + 1]; ++p)
             {
-                const int32_t i = inner[p];
+                const int32_t i = cand[p];
                 const int32_t jn = col_of_row[i];
                 if (jn < 0)
                 {   // free row: flip the path
@@ -275,7 +287,7 @@ static bool maximum_transversal(int32_t n, const int32_t *outer, const int32_t *
                 if (visited[jn] != j0)
                 {
                     visited[jn] = j0;
-                    ++p;
+                    stack_pos.back() = p + 1;
                     stack_col.push_back(jn); stack_pos.push_back(outer[jn]);
                     descended = true;
                     break;
@@ -296,7 +308,7 @@ bool analyse_pattern(int32_t n, const int32_t *outer, const int32_t *inner, cons
     for (int32_t j = 0; j < n; ++j)
         if (!std::binary_search(inner + outer[j], inner + outer[j + 1], j)) ++missing;
     std::vector<int32_t> row_of_col;
-    if (missing == 0 || !opt.transversal || !maximum_transversal(n, outer, inner, row_of_col))
+    if (missing == 0 || !opt.transversal || !maximum_transversal(n, outer, inner, opt.weights, row_of_col))
         return analyse_core(n, outer, inner, opt, S, err); // (a structurally singular pattern fails numerically, like Eigen's would)
     // Row i of the matrix is moved to position rowmap[i]: A' = Q A has a zero-free diagonal.  The analysis runs on
     // A'; matrix slots are mapped back, and the right-hand side is read through row_src (Q A x = Q b).

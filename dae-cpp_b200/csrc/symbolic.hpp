@@ -23,6 +23,7 @@ struct SymbolicOptions
     int unit_smem_bytes = -1; // shared-memory budget of one subtree unit (-1: chosen from the problem
                               // size; 0: no units, every front goes through the per-level kernels)
     int serial_dim = 4;     // fronts up to this order are factored by one thread each
+    const double *weights = nullptr; // optional |a_ij| per slot of the analysed pattern: the transversal prefers big entries
     int transversal = 1;    // permute rows to a structurally zero-free diagonal first when the diagonal has holes
 };
 

@@ -179,12 +179,18 @@ class DeviceNewton
     double *m_f{nullptr};  // page-locked RHS values
     double *m_xk{nullptr}; // page-locked copy of the Newton iterate
 
+    // Page-locked registration of the Jacobian VALUE array of a JacobianMatrixShape functor.  Only that array
+    // is ever registered: the functor reserves and fills exactly its fixed element list on every call
+    // (dae-cpp/jacobian-matrix.hpp:66-92), so after the first call the storage behind J.A can never be reallocated
+    // -- and therefore never freed while registered (CUDA requires the unregister to come first).  Every other
+    // triplet array (mass matrix, index arrays, user-written Jacobian functors whose element count may change)
+    // is handed over as ordinary pageable memory.
     struct Pinned
     {
         const void *p{nullptr};
         std::size_t bytes{0};
     };
-    Pinned m_pin[6];
+    Pinned m_pin;
     std::size_t m_nT_pattern{0}; // length of the (i, j) stream the device has cached for J
 
     void fatal(int rc, const char *what) const
@@ -192,21 +198,27 @@ class DeviceNewton
         ERROR("daecpp_b200: " << what << " failed (code " << rc << "): " << daecpp_b200_last_error(m_ctx));
     }
 
-    // Page-lock the storage behind a triplet array once it is large and has stopped moving.
+    void unpin()
+    {
+        if (m_pin.p && daecpp_b200_host_unregister(const_cast<void *>(m_pin.p)) != DAECPP_B200_OK)
+        {
+            WARNING("daecpp_b200: could not release the page lock on the Jacobian values.");
+        }
+        m_pin = Pinned();
+    }
+    // Page-lock the storage once it is large and has stopped moving.
     template <class Vec>
-    void pin(Pinned &slot, const Vec &v)
+    void pin(const Vec &v)
     {
         const void *p = v.data();
         const std::size_t bytes = v.capacity() * sizeof(typename Vec::value_type);
-        if (p == slot.p && bytes == slot.bytes)
+        if (p == m_pin.p && bytes == m_pin.bytes)
             return;
-        if (slot.p)
-            daecpp_b200_host_unregister(const_cast<void *>(slot.p));
-        slot = Pinned();
+        unpin();
         if (bytes >= (std::size_t(1) << 22) && daecpp_b200_host_register(const_cast<void *>(p), bytes) == DAECPP_B200_OK)
         {
-            slot.p = p;
-            slot.bytes = bytes;
+            m_pin.p = p;
+            m_pin.bytes = bytes;
         }
     }
 
@@ -234,15 +246,14 @@ public:
     DeviceNewton &operator=(const DeviceNewton &) = delete;
     ~DeviceNewton()
     {
-        for (auto &slot : m_pin)
-            if (slot.p)
-                daecpp_b200_host_unregister(const_cast<void *>(slot.p));
+        unpin(); // (the integrator declares its sparse matrices before this object: their storage is still alive here)
         daecpp_b200_host_free(m_f);
         daecpp_b200_host_free(m_xk);
         daecpp_b200_destroy(m_ctx);
     }
 
     double *f_host() { return m_f; }
+    bool jacobian_values_page_locked() const { return m_pin.p != nullptr; }
     const double *xk_host() const { return m_xk; }
 
     void set_state(const state_vector &x0)
@@ -255,7 +266,6 @@ public:
     // M_ = M.convert(size)   (dae-cpp/solver.hpp:481)
     void set_mass(const sparse_matrix &M)
     {
-        pin(m_pin[0], M.A); pin(m_pin[1], M.i); pin(m_pin[2], M.j);
         const int rc = daecpp_b200_set_mass(m_ctx, M.A.data(), M.i.data(), M.j.data(), static_cast<int64_t>(M.A.size()));
         ASSERT(rc != DAECPP_B200_EINDEX, "Mass matrix: sparse matrix index is out of boundaries, matrix size is " << m_n << "x" << m_n);
         if (rc)
@@ -266,7 +276,8 @@ public:
     // after the first hand-off only the values travel.
     void set_jacobian(const sparse_matrix &J, bool fixed_pattern)
     {
-        pin(m_pin[3], J.A);
+        if (fixed_pattern)
+            pin(J.A);
         if (fixed_pattern && m_nT_pattern == J.A.size() && m_nT_pattern > 0)
         {
             const int rc = daecpp_b200_set_jacobian_values(m_ctx, J.A.data(), static_cast<int64_t>(J.A.size()));
@@ -274,7 +285,6 @@ public:
                 fatal(rc, "set_jacobian_values");
             return;
         }
-        pin(m_pin[4], J.i); pin(m_pin[5], J.j);
         m_nT_pattern = J.A.size();
         const int rc = daecpp_b200_set_jacobian(m_ctx, J.A.data(), J.i.data(), J.j.data(), static_cast<int64_t>(J.A.size()));
         ASSERT(rc != DAECPP_B200_EINDEX, "Jacobian matrix: sparse matrix index is out of boundaries, matrix size is " << m_n << "x" << m_n);
@@ -427,12 +437,12 @@ class Integrator
     Counters m_count;
     timer::Time m_time;
     SolverState m_state;
+    sparse_matrix m_M, m_J; // declared BEFORE the device object: it may hold a page lock on m_J.A and must be destroyed first
     DeviceNewton m_dev;
 
     state_vector m_xk;     // host copy of the Newton iterate (what the functors see)
     state_vector m_x_prev; // host copy of the last accepted state, x[0]
     state_type m_f_ad, m_xk_ad; // autodiff-typed views handed to the RHS functor
-    sparse_matrix m_M, m_J;
 
     int m_dt_increase_threshold{0}, m_dt_decrease_threshold{0}, m_max_Newton_iter{0};
     uint64_t m_n_steps{0};

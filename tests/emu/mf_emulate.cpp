@@ -33,6 +33,9 @@ extern "C" int mfemu_solve(int32_t n, const int32_t *outer, const int32_t *inner
     if (leaf_size > 0) opt.leaf_size = leaf_size;
     if (unit_smem_bytes >= 0) opt.unit_smem_bytes = unit_smem_bytes;
     const char *err = nullptr;
+    std::vector<double> mag(vals, vals + outer[n]); // what numeric.cu: upload_symbolic hands over when the diagonal has holes
+    for (double &v : mag) v = v < 0 ? -v : v;
+    opt.weights = mag.data();
     if (!analyse_pattern(n, outer, inner, opt, S, &err)) return 21;
     if (stats)
     {
