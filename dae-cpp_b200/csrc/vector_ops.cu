@@ -214,9 +214,15 @@ __global__ void k_refine_apply(RefineArgs a)
     if (i < a.n)
     {
         const double e = a.e[off + i];
+        if (!a.update)
+        {   // linear-solver entry: corrections at the level of the last bits are rounding noise of the correction
+            // solve itself; a solution that is already that accurate is left exactly as it is
+            const double d0 = a.dx[off + i];
+            if (fabs(e) > 4.0 * 2.220446049250313e-16 * fabs(d0)) a.dx[off + i] = __dadd_rn(d0, e);
+            return;
+        }
         const double d = __dadd_rn(a.dx[off + i], e);
         a.dx[off + i] = d;
-        if (!a.update) return;
         const double *x0 = a.lane_hbase ? a.hist + (int64_t)(a.lane_hbase[lane] & 3) * a.s_hist + off : a.x0;
         const double xn = __dadd_rn(a.xk[off + i], e);
         a.xk[off + i] = xn;
