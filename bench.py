@@ -165,9 +165,11 @@ class ClockSampler:
 
 # ------------------------------------------------------------------------------ CPU reference
 def cpu_reference_iterations(w, budget_s, max_iters, warmup=0):
-    """The reference's own Newton linear step (sparse_matrix::convert x2, Jb -= M*alpha, b, Eigen
-    SparseLU compute + solve) on ONE host core -- the reference is single-threaded
-    (SURVEY.md section 0).  Returns (us_per_iter, iters, kind, dx, buckets_ms)."""
+    """The reference's own Newton linear step on ONE host core -- the reference is single-threaded.
+    Held the way the reference's solve() holds it (oracle/ref_shim.cpp: daeref_newton_open): triplet buffers, the converted
+    static mass matrix and the SparseLU object persist; a timed iteration is J.convert, b = M*dxdt - f, Jb -= M*alpha,
+    compute (analyzePattern + factorize, redone every time: solver.hpp:537) and solve.
+    Returns (us_per_iter, iters, kind, dx, buckets_ms, per_iteration_us)."""
     import oracle_lib as O  # the checker; only this leg may touch oracle/
     n = w["n"]
     JA, Ji, Jj = [np.ascontiguousarray(a) for a in w["J"]]
@@ -178,12 +180,13 @@ def cpu_reference_iterations(w, budget_s, max_iters, warmup=0):
     dx = np.zeros(n)
     times = np.zeros(4)
     acc = np.zeros(4)
-    if O.ref is not None:
+    session = None
+    if O.ref is not None and hasattr(O.ref, "daeref_newton_open"):
         kind = "reference"
+        session = O.ref.daeref_newton_open(n, len(JA), JA, Ji, Jj, len(MA), MA, Mi, Mj, dxdt, f)
 
         def one():
-            rc = O.ref.daeref_newton_step(n, len(JA), JA, Ji, Jj, len(MA), MA, Mi, Mj, alpha, dxdt, f, dx,
-                                          times.ctypes.data)
+            rc = O.ref.daeref_newton_iterate(session, alpha, dx.ctypes.data, times.ctypes.data)
             assert rc == 0, rc
     else:
         kind = "port"
@@ -194,16 +197,34 @@ def cpu_reference_iterations(w, budget_s, max_iters, warmup=0):
             assert O.port.oracle_lu_solve(n, *csc, b, dx) == 0
     for _ in range(warmup):
         one()
-    t0 = time.perf_counter()
-    iters = 0
-    while iters < max_iters:
+    per = []
+    t_start = time.perf_counter()
+    while len(per) < max_iters:
+        t0 = time.perf_counter()
         one()
+        per.append((time.perf_counter() - t0) * 1e6)
         acc += times
-        iters += 1
-        if time.perf_counter() - t0 > budget_s:
+        if time.perf_counter() - t_start > budget_s:
             break
-    el = time.perf_counter() - t0
-    return el / iters * 1e6, iters, kind, dx.copy(), (acc / iters).tolist()
+    if session is not None:
+        O.ref.daeref_newton_close(session)
+    iters = len(per)
+    return float(np.mean(per)), iters, kind, dx.copy(), (acc / iters).tolist(), per
+
+
+def spread(samples):
+    a = np.asarray(samples, dtype=float)
+    return {"min": float(a.min()), "median": float(np.median(a)), "max": float(a.max()), "samples": int(a.size)}
+
+
+def c3_config(w, nnz_jb=None):
+    """The `config` object both arms print for the single-system workloads (same keys, same values)."""
+    n = w["n"]
+    cfg = {"workload": w["label"], "n": n, "nnz_triplets": len(w["J"][0]),
+           "parallelism": "1 system per GPU (replicas only; sparse LU of one DAE does not shard)",
+           "l2_policy": "working set (factors + tables + triplets + state) exceeds the 126 MB L2" if n >= 500_000
+                        else "working set fits L2 (latency-bound config)"}
+    return cfg
 
 
 def run_reference_arm(args):
@@ -211,13 +232,14 @@ def run_reference_arm(args):
     if rank != 0:
         return
     w = make_workload(args.workload, args.n)
-    us, iters, kind, _, buckets = cpu_reference_iterations(w, budget_s=150.0, max_iters=args.steps, warmup=min(args.warmup, 1))
+    # each reference iteration takes 0.45 s (C3) to 40 s (C4): the sample is bounded, the warm-up is the port arm's
+    us, iters, kind, _, buckets, per = cpu_reference_iterations(w, budget_s=150.0, max_iters=args.steps, warmup=min(args.warmup, 5))
     sample = f"{iters} full-size Newton iterations of {w['label']} on 1 host core"
     line = {
-        "impl": "reference", "metric": METRIC, "value": us, "unit": UNIT, "n_gpus": args.gpus, "steps": iters,
-        "warmup": min(args.warmup, 1), "ms_per_step": us / 1e3, "higher_is_better": False, "scaling": "weak",
+        "impl": "reference", "metric": METRIC, "value": us, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": us / 1e3, "higher_is_better": False, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": w["label"], "n": w["n"], "nnz_triplets": len(w["J"][0])},
+        "config": c3_config(w), "spread_us": spread(per), "steps_timed": iters,
         "cpu_baseline": {"value": us, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample,
                          "buckets_ms": dict(zip(["convert", "linear_algebra", "compute", "solve"], buckets))},
         "e2e": {"value": us, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -366,35 +388,15 @@ def ensemble_algorithmic_bytes(N, stats):
     return stats["lane_iterations"] * per_iter + stats["lane_refactorisations"] * per_refac
 
 
-def run_ensemble_device(args):
-    """C5 with device functors: members partitioned in contiguous blocks over the ranks, every rank integrates
-    its block as the lanes of ONE batch context (one launch sequence per Newton round for all lanes), one
-    all_gather of {status, steps, final state} at the end -- the only collective."""
-    import torch
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(v):
-        if dist is None:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+def run_ensemble_device(args, env=None, emit=True):
+    """C5 with device functors: members dealt round-robin to the ranks, every rank integrates its share as the
+    lanes of ONE batch context (one launch sequence per Newton round for all lanes), one all_gather of
+    {status, steps, final state} at the end -- the only collective."""
+    own_env = env is None
+    if own_env:
+        env = Env()
+    torch, dist, world, rank, local = env.torch, env.dist, env.world, env.rank, env.local
+    barrier, max_over_ranks = env.barrier, env.max_over_ranks
 
     def sum_over_ranks(v):
         if dist is None:
@@ -474,10 +476,10 @@ def run_ensemble_device(args):
             "roofline": {"bound": "hbm", "kernel": "all kernels of a Newton round (functors, residual, k_chain_factor<2,1>, k_chain_forward/backward<2,1>)",
                          "achieved": gbps, "peak": peak, "unit": "GB/s", "frac": gbps / peak, "traffic": None,
                          "algorithmic_bytes": abytes / steps, "note": "per GPU; SURVEY.md 8(d) bytes x the lane iterations / refactorisations actually run"}}
-    if rank == 0:
+    if rank == 0 and emit:
         print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+    if own_env:
+        env.close()
     return line
 
 
@@ -581,36 +583,49 @@ def run_ensemble_b200(args):
 
 
 # ------------------------------------------------------------------------------ B200 arm
-def run_b200_arm(args):
-    import torch  # device bring-up, barrier and the max-over-ranks reduction only
-    from gpu_lib import binding as B
+class Env:
+    """Device bring-up, barrier and the max-over-ranks reduction (torch is plumbing only)."""
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    def __init__(self):
+        import torch
+        self.torch = torch
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+        torch.cuda.set_device(self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.dist = dist
 
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
 
-    def max_over_ranks(v):
-        if dist is None:
+    def max_over_ranks(self, v):
+        if self.dist is None:
             return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return float(t.item())
 
-    w = make_workload(args.workload, args.n)
+    def close(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+
+def single_system_line(args, env, workload, size, steps, warmup, want_cpu, want_e2e):
+    """One single-system workload (C2, C3 or C4) measured on this rank's GPU; returns the JSON line as a dict."""
+    from gpu_lib import binding as B
+    torch, dist, world, rank, local = env.torch, env.dist, env.world, env.rank, env.local
+    barrier, max_over_ranks = env.barrier, env.max_over_ranks
+    w = make_workload(workload, size)
     n, dt, order = w["n"], w["dt"], w["order"]
     atol = rtol = 1e-6
     lib = B.load()
@@ -643,29 +658,37 @@ def run_b200_arm(args):
             c.iterations_resident(k_iters, refactor, order, dt, atol, rtol)
 
     # ---- value: K iterations, data resident in HBM
-    resident(args.warmup)
+    resident(warmup)
     sampler = ClockSampler(local)
     sampler.start()
     time.sleep(0.3)
     barrier()
     k0 = c.stat("kernels_launched")
-    c.event_mark()
-    resident(args.steps)
-    ms_total = c.event_elapsed_ms()
+    # K iterations in blocks of (at most) 10, each block timed by CUDA events on the context's stream: the sum is the
+    # timed region, the block means give the spread
+    blocks = []
+    left = steps
+    while left > 0:
+        kb = min(10, left)
+        c.event_mark()
+        resident(kb)
+        blocks.append((c.event_elapsed_ms(), kb))
+        left -= kb
+    ms_total = sum(b[0] for b in blocks)
     barrier()
     launches = int(c.stat("kernels_launched") - k0)
     ms_total = max_over_ranks(ms_total)
     time.sleep(0.3)
     clocks = sampler.stop()
-    us_iter = ms_total * 1e3 / (args.steps * world)
+    us_iter = ms_total * 1e3 / (steps * world)
 
     # solve-only iterations (quasi-Newton iterations that reuse the factors)
     resident(2, 0)
-    c.event_mark(); resident(args.steps, 0); us_solve_only = c.event_elapsed_ms() * 1e3 / args.steps
+    c.event_mark(); resident(steps, 0); us_solve_only = c.event_elapsed_ms() * 1e3 / steps
 
     # per-phase device times (events between phases; separate pass so `value` is undisturbed)
     c.set_option("phase_timing", 1)
-    resident(args.steps)
+    resident(steps)
     phases = {}
     for ph in ("assembly", "residual", "refactor", "solve", "update"):
         ms = c.stat("ms_phase_" + ph)
@@ -696,7 +719,7 @@ def run_b200_arm(args):
     # very command (profiles/: dram__bytes_read.sum + dram__bytes_write.sum, MB per launch), C3 only
     traffic = None
     cap = os.path.join(ROOT, "profiles", "r01_v10_ncu_full_chain_kernels.csv")
-    if args.workload == "flame1d" and n == 1_000_000 and os.path.exists(cap):
+    if workload == "flame1d" and n == 1_000_000 and os.path.exists(cap):
         import csv
         rows = list(csv.reader(open(cap)))
         hd = rows[0]
@@ -717,11 +740,11 @@ def run_b200_arm(args):
                     "peak_source": peak_src, "algorithmic_bytes": abytes["refactor"],
                     "us": phases["refactor"]["us"]}
 
-    if args.workload == "grid2d" and roofline is not None:
+    if workload == "grid2d" and roofline is not None:
         # C4's refactorisation is bound by the FP64 pipe, not by HBM.  Flops = the REFERENCE structure's
         # (Eigen/COLAMD, 8.99e10 at 1024^2; extra or saved fill of this ordering is not credited); peak = a cuBLAS DGEMM
         # measured here (MEASURED_PEAKS.json holds no FP64 figure).
-        ref_flops = {1024: 8.99e10}.get(args.n or 1024)
+        ref_flops = {1024: 8.99e10}.get(size or 1024)
         a64 = torch.randn(4096, 4096, dtype=torch.float64, device="cuda"); b64 = torch.randn(4096, 4096, dtype=torch.float64, device="cuda")
         for _ in range(2):
             torch.mm(a64, b64)
@@ -744,12 +767,12 @@ def run_b200_arm(args):
 
     # ---- e2e: the host-buffer calls of the overlay header, copies inside the timed region
     e2e = None
-    if not args.no_e2e:
+    if want_e2e:
         # what the overlay header does per iteration (dae-cpp_b200/overlay/dae-cpp/solver.hpp): hand the
         # Jacobian over -- values only when the functor is a JacobianMatrixShape, whose (i, j) stream is
         # fixed (BASELINE configs[2] names it for C3), the full triplet stream otherwise -- then ONE
         # fused call: f upload, residual, refactor, solves, update, xk download, one synchronisation.
-        fixed_pattern = args.workload == "flame1d"
+        fixed_pattern = workload == "flame1d"
         c.set_option("pinned_io", 1)
 
         def e2e_iter():
@@ -758,15 +781,15 @@ def run_b200_arm(args):
             else:
                 c.set_jacobian_raw(pA.array, pi.array, pj.array, nT)
             c.iteration_host(pf.array, 1, order, dt, atol, rtol, px.array)
-        for _ in range(max(args.warmup, 3)):
+        for _ in range(max(warmup, 3)):
             e2e_iter()
         barrier()
         t0 = time.perf_counter()
-        for _ in range(args.steps):
+        for _ in range(steps):
             e2e_iter()
         torch.cuda.synchronize()
         el = max_over_ranks(time.perf_counter() - t0)
-        e2e = {"value": el * 1e6 / (args.steps * world), "unit": UNIT,
+        e2e = {"value": el * 1e6 / (steps * world), "unit": UNIT,
                "h2d_bytes_per_step": int((8 if fixed_pattern else 16) * nT + 8 * n), "d2h_bytes_per_step": int(8 * n + 12),
                "path": ("set_jacobian_values + iteration_host (JacobianMatrixShape: fixed pattern)" if fixed_pattern
                         else "set_jacobian + iteration_host")}
@@ -774,21 +797,18 @@ def run_b200_arm(args):
     stats = {k: c.stat(k) for k in ("n_fronts", "n_levels", "nnz_factor", "max_front", "ms_symbolic", "lu_doubles",
                                     "cb_doubles")}
     line = {
-        "metric": METRIC, "value": us_iter, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_total / args.steps, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
+        "metric": METRIC, "value": us_iter, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms_total / steps, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": w["label"], "n": n, "nnz_triplets": nT, "nnz_jb": nnz_jb,
-                   "parallelism": "1 system per GPU (replicas only; sparse LU of one DAE does not shard)",
-                   "l2_policy": "working set (factors + tables + triplets + state) exceeds the 126 MB L2"
-                                if n >= 500_000 else "working set fits L2 (latency-bound config)",
-                   "cold_start_ms": cold_ms},
+        "config": c3_config(w), "nnz_jb": nnz_jb, "cold_start_ms": cold_ms,
+        "spread_us": spread([1e3 * ms / kb for ms, kb in blocks]),
         "clocks": clocks, "gpu_launches": launches, "solve_only_us": us_solve_only, "phases": phases,
         "roofline": roofline, "e2e": e2e, "factor": stats,
     }
 
     # ---- CPU baseline (rank 0, N = 1 only): the reference on the host, bounded sample
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        us_cpu, iters, kind, dx_ref, buckets = cpu_reference_iterations(w, budget_s=12.0, max_iters=12)
+    if rank == 0 and world == 1 and want_cpu:
+        us_cpu, iters, kind, dx_ref, buckets, _ = cpu_reference_iterations(w, budget_s=12.0, max_iters=12)
         scale = float(np.max(np.abs(dx_ref))) or 1.0
         line["cpu_baseline"] = {"value": us_cpu, "unit": UNIT, "cores": 1, "kind": kind,
                                 "sample": f"{iters} full-size Newton iterations of {w['label']} on 1 host core "
@@ -797,10 +817,45 @@ def run_b200_arm(args):
         line["parity"] = {"dx_max_abs_diff_vs_reference": float(np.max(np.abs(dx_first - dx_ref))),
                           "dx_max_abs": scale}
     c.close()
-    if rank == 0:
+    for buf in (pA, pi, pj, pf, px):
+        buf.free()
+    return line
+
+
+def run_b200_arm(args):
+    env = Env()
+    line = single_system_line(args, env, args.workload, args.n, args.steps, args.warmup, not args.no_cpu_baseline, not args.no_e2e)
+    if args.workload == "flame1d" and not args.n and env.world == 1 and not args.no_extra_configs:
+        # the other configurations BASELINE.json names, measured on the same box in the same run (the driver records
+        # this one line): C2 and C4 single systems, C5 at one GPU.  Each is the same measurement as the headline's.
+        extra = {}
+        for key, wl, st, wu, cpu in (("C2_perovskite", "perovskite", 200, 5, True), ("C4_grid2d_1024", "grid2d", 10, 3, False)):
+            try:
+                q = single_system_line(args, env, wl, 0, st, wu, cpu, True)
+                extra[key] = {k: q.get(k) for k in ("metric", "value", "unit", "steps", "warmup", "spread_us", "solve_only_us", "phases", "roofline",
+                                                     "e2e", "gpu_launches", "cold_start_ms", "factor", "cpu_baseline", "parity", "config")}
+            except Exception as exc:  # a failure here must not take the headline down with it
+                extra[key] = {"error": repr(exc)}
+        if "cpu_baseline" not in extra.get("C4_grid2d_1024", {}) or extra["C4_grid2d_1024"].get("cpu_baseline") is None:
+            gold = os.path.join(ROOT, "tests", "golden", "solve_c4_grid2d_1024.json")
+            if os.path.exists(gold) and "error" not in extra["C4_grid2d_1024"]:
+                g = json.load(open(gold))
+                extra["C4_grid2d_1024"]["cpu_baseline"] = {
+                    "value": None, "unit": UNIT, "cores": 1, "kind": "reference",
+                    "sample": "not timed in this run: one Eigen::SparseLU compute+solve of this system takes "
+                              f"{g['reference_seconds']:.0f} s on one core of the build container (tests/golden/make_golden_large.py)"}
+        try:
+            ens_args = argparse.Namespace(**vars(args))
+            ens_args.steps, ens_args.steps_given, ens_args.warmup = 2, True, 3
+            e = run_ensemble_device(ens_args, env=env, emit=False)
+            extra["C5_ensemble_1gpu"] = {k: e.get(k) for k in ("metric", "value", "unit", "steps", "ms_per_step", "failed_members", "rounds_per_step",
+                                                               "lane_iterations_per_step", "e2e", "gpu_launches", "roofline", "config")}
+        except Exception as exc:
+            extra["C5_ensemble_1gpu"] = {"error": repr(exc)}
+        line["configs"] = extra
+    if env.rank == 0:
         print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+    env.close()
 
 
 if __name__ == "__main__":

@@ -190,6 +190,64 @@ int daeref_newton_step(int32_t n, int64_t nJ, const double *JA, const int32_t *J
     return 0;
 }
 
+// The same step as a session, the way the reference's solve() holds its objects (dae-cpp/solver.hpp:325-337): the
+// triplet buffers, the converted mass matrix (is_mass_matrix_static: M.convert runs once, solver.hpp:477-481) and the
+// Eigen::SparseLU object live across iterations; one iteration is Jb = J.convert(n) (:502), b = M_*dxdt - f
+// (:516-518), Jb -= M_*alpha (:523), linsolver.compute(Jb) (:537), dx = linsolver.solve(b) (:558).
+struct RefSession
+{
+    int32_t n;
+    sparse_matrix J, M;
+    core::eimat M_;
+    Eigen::SparseLU<core::eimat> lin;
+    core::eivec d, f_, b, dx;
+};
+void *daeref_newton_open(int32_t n, int64_t nJ, const double *JA, const int32_t *Ji, const int32_t *Jj, int64_t nM, const double *MA,
+                         const int32_t *Mi, const int32_t *Mj, const double *dxdt, const double *f)
+{
+    RefSession *s = new RefSession();
+    s->n = n;
+    s->J = make_triplets(nJ, JA, Ji, Jj);
+    s->M = make_triplets(nM, MA, Mi, Mj);
+    s->M_ = s->M.convert(n);
+    s->d = Eigen::Map<const core::eivec>(dxdt, n);
+    s->f_ = Eigen::Map<const core::eivec>(f, n);
+    return s;
+}
+int daeref_newton_iterate(void *h, double alpha, double *dx_out, double *times_ms)
+{
+    RefSession *s = static_cast<RefSession *>(h);
+    auto t0 = clk::now();
+    core::eimat Jb = s->J.convert(s->n);
+    double tc = ms_since(t0);
+    t0 = clk::now();
+    s->b = s->M_ * s->d;
+    s->b -= s->f_;
+    Jb -= s->M_ * alpha;
+    double tl = ms_since(t0);
+    t0 = clk::now();
+    s->lin.compute(Jb);
+    double tf = ms_since(t0);
+    if (s->lin.info() != Eigen::Success)
+        return 2;
+    t0 = clk::now();
+    s->dx = s->lin.solve(s->b);
+    double ts = ms_since(t0);
+    if (s->lin.info() != Eigen::Success)
+        return 3;
+    if (dx_out)
+        std::memcpy(dx_out, s->dx.data(), sizeof(double) * s->n);
+    if (times_ms)
+    {
+        times_ms[0] = tc;
+        times_ms[1] = tl;
+        times_ms[2] = tf;
+        times_ms[3] = ts;
+    }
+    return 0;
+}
+void daeref_newton_close(void *h) { delete static_cast<RefSession *>(h); }
+
 const char *daeref_version() { return "dae-cpp 2.2.0 reference headers + Eigen 3.4.90 (unmodified)"; }
 
 } // extern "C"

@@ -60,6 +60,15 @@ if ref is not None:
                                        C.c_double, _f64, _f64, _f64, _vp]
 
 
+    if hasattr(ref, "daeref_newton_open"):
+        ref.daeref_newton_open.restype = _vp
+        ref.daeref_newton_open.argtypes = [C.c_int32, C.c_int64, _f64, _i32, _i32, C.c_int64, _f64, _i32, _i32, _f64, _f64]
+        ref.daeref_newton_iterate.restype = C.c_int
+        ref.daeref_newton_iterate.argtypes = [_vp, C.c_double, _vp, _vp]
+        ref.daeref_newton_close.restype = None
+        ref.daeref_newton_close.argtypes = [_vp]
+
+
 def _trip(A, i, j):
     return (np.ascontiguousarray(A, np.float64), np.ascontiguousarray(i, np.int32),
             np.ascontiguousarray(j, np.int32))
