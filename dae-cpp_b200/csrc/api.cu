@@ -128,6 +128,7 @@ static void recycle(daecpp_b200_ctx *c)
     c->err.clear();
     c->have_factor = false;
     c->direct_csc = false;
+    c->tiny.enabled = fresh.tiny.enabled; c->tiny.have_factor = false; c->tiny.spec_valid = false; c->tiny.var_tol = fresh.tiny.var_tol;
     c->M.vals_valid = false; c->J.vals_valid = false;
     if (c->chain_enabled != fresh.chain_enabled || c->chain_min_n != fresh.chain_min_n || c->chain_max_b != fresh.chain_max_b ||
         c->chain_affine != fresh.chain_affine || c->unit_threads != fresh.unit_threads || c->sopt.leaf_size != fresh.sopt.leaf_size ||
@@ -249,6 +250,7 @@ static void destroy_now(daecpp_b200_ctx *c)
 {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    tiny_release(c);
     c->M.release(); c->J.release(); c->dS.release(); c->dC.release();
     c->m_rowptr.release(); c->m_rowslot.release(); c->m_rowcol.release();
     c->u_outer.release(); c->u_inner.release(); c->u_J.release(); c->u_M.release(); c->u_vals.release();
@@ -351,6 +353,7 @@ int daecpp_b200_rollback(daecpp_b200_ctx *c)
 {
     if (!c) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
+    c->tiny.spec_valid = false;
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->xk, c->xh[0], sizeof(double) * c->n, cudaMemcpyDeviceToDevice, c->stream));
     return DAECPP_B200_OK;
 }
@@ -359,6 +362,7 @@ int daecpp_b200_set_mass(daecpp_b200_ctx *c, const double *A, const int32_t *i, 
 {
     if (!c) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
+    if (tiny_eligible(c)) return tiny_set_triplets(c, false, A, i, j, nT, false);
     int rc = assemble_triplets(c, c->M, A, i, j, nT, false);
     if (rc) return rc;
     return build_mass_csr(c);
@@ -369,6 +373,7 @@ int daecpp_b200_set_jacobian(daecpp_b200_ctx *c, const double *A, const int32_t 
     if (!c) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
     c->direct_csc = false;
+    if (tiny_eligible(c)) return tiny_set_triplets(c, true, A, i, j, nT, false);
     return assemble_triplets(c, c->J, A, i, j, nT, true);
 }
 
@@ -376,6 +381,7 @@ int daecpp_b200_residual(daecpp_b200_ctx *c, const double *f_host, int32_t order
 {
     if (!c || !f_host || !dt) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
+    if (int rcf = tiny_flush(c)) return rcf;
     if (!c->M.have_pattern) return fail(c, DAECPP_B200_EINVAL, "set_mass must precede residual");
     double w[5];
     if (!bdf_weights(order, dt, w)) return fail(c, DAECPP_B200_EINVAL, "unsupported time integration order");
@@ -402,8 +408,9 @@ int daecpp_b200_refactor(daecpp_b200_ctx *c, double alpha)
 {
     if (!c) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
-    int rc = build_union(c);
+    int rc = tiny_flush(c);
     if (rc) return rc;
+    if ((rc = build_union(c))) return rc;
     if (c->assemble_only) return assemble_values_only(c, alpha);
     c->alpha_hint = alpha;
     if (!c->have_symbolic && (rc = upload_symbolic(c))) return rc;
@@ -437,6 +444,15 @@ int daecpp_b200_accept_step(daecpp_b200_ctx *c, int32_t variability_on, double t
 {
     if (!c) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
+    if (tiny_eligible(c) && c->tiny.spec_valid && (!variability_on || tol == c->tiny.var_tol))
+    {   // the tiny iteration measured the variability with its update: shift the history, no read-back
+        c->tiny.spec_valid = false;
+        int rct = launch_accept(c, 0, tol);
+        if (rct) return rct;
+        if (variability_out) *variability_out = variability_on ? c->tiny.spec_var : 0.0;
+        return DAECPP_B200_OK;
+    }
+    if (tiny_eligible(c)) { c->tiny.var_tol = tol; c->tiny.spec_valid = false; }
     if (variability_on) DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_scalars, 0, sizeof(double), c->stream));
     int rc = launch_accept(c, variability_on, tol);
     if (rc) return rc;
@@ -566,6 +582,7 @@ static int wait_iteration(daecpp_b200_ctx *c)
 
 static int prepare_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t order, const double dt[4], double w[5])
 {
+    if (int rcf = tiny_flush(c)) return rcf;
     if (!c->M.have_pattern || !c->J.have_pattern) return fail(c, DAECPP_B200_EINVAL, "set_mass/set_jacobian must precede");
     if (!bdf_weights(order, dt, w)) return fail(c, DAECPP_B200_EINVAL, "unsupported time integration order");
     int rc = build_union(c);
@@ -610,6 +627,7 @@ int daecpp_b200_set_jacobian_values(daecpp_b200_ctx *c, const double *A, int64_t
 {
     if (!c || (nT > 0 && !A)) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
+    if (tiny_eligible(c)) return tiny_set_triplets(c, true, A, nullptr, nullptr, nT, true);
     TripletSet &J = c->J;
     if (!J.have_pattern || J.nT_cached != nT) return fail(c, DAECPP_B200_EINVAL, "set_jacobian_values: no cached pattern of this length");
     if (nT > 0) DAECPP_CUDA_TRY(c, cudaMemcpyAsync(J.A.p, A, sizeof(double) * nT, cudaMemcpyHostToDevice, c->stream));
@@ -626,6 +644,12 @@ int daecpp_b200_iteration_host(daecpp_b200_ctx *c, const double *f_host, int32_t
     if (!c || !dt || !flags || !f_host) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
     double w[5];
+    if (tiny_eligible(c) && c->tiny.haveJ && c->tiny.haveM && !c->phase_timing)
+    {   // one launch, mapped hand-off, no synchronisation (tiny.cu)
+        if (!bdf_weights(order, dt, w)) return fail(c, DAECPP_B200_EINVAL, "unsupported time integration order");
+        if (alpha_out) *alpha_out = w[0];
+        return tiny_iteration(c, f_host, do_refactor, order, w, atol, rtol, max_err_abs, xk_host, flags);
+    }
     int rc = prepare_iteration(c, do_refactor, order, dt, w);
     if (rc) return rc;
     if (alpha_out) *alpha_out = w[0];
@@ -742,6 +766,7 @@ int daecpp_b200_get_csc(daecpp_b200_ctx *c, int32_t which, int32_t *outer, int32
 {
     if (!c) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
+    if (int rcf = tiny_flush(c)) return rcf;
     const int32_t *d_outer, *d_inner; const double *d_vals; int64_t nnz;
     if (which == 0 || which == 1)
     {
@@ -754,7 +779,9 @@ int daecpp_b200_get_csc(daecpp_b200_ctx *c, int32_t which, int32_t *outer, int32
     else if (which == 2)
     {
         if (c->n_refactor == 0) return fail(c, DAECPP_B200_EINVAL, "refactor has not run");
-        int rc = jb_values(c, c->last_alpha); // computed on demand: the factorisation assembles straight into the fronts
+        int rc = build_union(c); // (tiny systems iterate without ever building it)
+        if (rc) return rc;
+        rc = jb_values(c, c->last_alpha); // computed on demand: the factorisation assembles straight into the fronts
         if (rc) return rc;
         d_outer = c->u_outer.p; d_inner = c->u_inner.p; d_vals = c->u_vals.p; nnz = c->nnzU;
     }
@@ -899,7 +926,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "chain_fuse_residual") c->chain_fuse_residual = value != 0.0;
     else if (k == "keep_b") c->keep_b = value != 0.0;
     else if (k == "chain_prefetch") c->chain_prefetch = (int)value;
-    else if (k == "chain_packed") c->chain_packed = value != 0.0 ? 1 : 0;
+    else if (k == "chain_packed") c->chain_packed = (int)value;
     else if (k == "chain_affine") { c->chain_affine = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "blocked_lu") c->blocked_lu = value != 0.0;
     else if (k == "blocked_lu_min_dim") c->blocked_lu_min_dim = (int)value;
@@ -914,6 +941,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "trace_units") c->trace_units = value != 0.0;
     else if (k == "transversal") { c->sopt.transversal = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "pivot_rel") c->pivot_rel = value;
+    else if (k == "tiny") c->tiny.enabled = value != 0.0;
     else if (k == "max_super") { c->sopt.max_super = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else return fail(c, DAECPP_B200_EINVAL, "unknown option key");
     return DAECPP_B200_OK;

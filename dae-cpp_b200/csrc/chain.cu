@@ -224,6 +224,87 @@ __device__ __forceinline__ bool stage_matrix_affine_async(int t, int tile, doubl
     return true;
 }
 
+// ---- bulk-copy staging (B = 1, interior tiles of a row-major triplet stream) ------------------------------
+// When every row of the tile has its three entries and they sit in one contiguous run of the triplet values
+// (JacobianMatrixShape emits (i,i-1),(i,i),(i,i+1) row by row: flame-1D), a thread's chunk of Q0 rows is 48
+// consecutive doubles.  Each thread then fetches its own chunk with ONE bulk asynchronous copy
+// (cp.async.bulk global -> shared, completion counted in bytes on an mbarrier; UBLKCP in the SASS) instead of 48
+// eight-byte LDGSTS, and eliminates straight out of that array-of-rows image: chunk t sits at S + 50 t doubles
+// (400 bytes: a multiple of 16 as the bulk copy wants; consecutive chunks start two 8-byte banks apart, a 2-way
+// conflict on three loads per elimination step).  Source windows are aligned down to 16 bytes; `delta` is the
+// 0- or 8-byte offset of the data inside the window, the same for every chunk of the tile.
+struct PackedRows1
+{
+    const double *Cb;   // first interior row of the chunk: row k, field f at Cb[3 k + f]
+    const double *prev; // the row before the chunk (previous chunk's separator, or the halo row of the tile)
+    __device__ __forceinline__ Mat<1> get(int f, int k) const
+    {
+        Mat<1> X;
+        X.a[0] = k >= 0 ? Cb[3 * k + f] : prev[f];
+        return X;
+    }
+    __device__ __forceinline__ Mat<1> A(int k) const { return get(0, k); }
+    __device__ __forceinline__ Mat<1> D(int k) const { return get(1, k); }
+    __device__ __forceinline__ Mat<1> C(int k) const { return get(2, k); }
+    __device__ __forceinline__ Mat<1> Hinit() const { return get(2, -1); }
+};
+constexpr int BULK_STRIDE = 50;                       // doubles between consecutive chunks of the image
+constexpr int BULK_HALO = BULK_STRIDE * Cfg<1>::T;    // the tile's halo row sits behind the chunks
+static_assert(BULK_HALO + 3 <= 3 * Dim<1>::RP, "the bulk image must fit the staged-tile buffer");
+
+// Returns the chunk's row accessor through `rows`; false (uniform over the CTA) when the tile does not qualify.
+__device__ __forceinline__ bool stage_matrix_bulk1(int t, int tile, double *S, const int32_t *desc, const double *jv, const double *mvals,
+                                                   double alpha, PackedRows1 &rows)
+{
+    using D = Dim<1>;
+    constexpr int PER = D::ROWS + 1, NFE = 3, NT = D::T, Q0 = D::Q0;
+    __shared__ int32_t sd[NFE * DESC];
+    __shared__ __align__(8) unsigned long long mbar;
+    for (int k = t; k < NFE * DESC; k += NT) sd[k] = desc[(size_t)tile * NFE * DESC + k];
+    if (t == 0)
+    {
+        const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mb) : "memory");
+    }
+    __syncthreads();
+    bool ok = true;
+#pragma unroll
+    for (int fe = 0; fe < NFE; ++fe)
+    {
+        const int32_t *e = sd + fe * DESC;
+        ok = ok && e[DJLO] == 0 && e[DJHI] == PER - 1 && e[DONE] >= PER && e[DJ0] == sd[DJ0] + fe && e[DJS] == NFE;
+        const bool diag = fe == 1;
+        ok = ok && (diag ? (e[DMLO] <= 1 && e[DMHI] == PER - 1) : (e[DMLO] > e[DMHI])); // a mass entry on every diagonal, none elsewhere
+    }
+    if (!ok) return false;
+    const uint32_t mb = (uint32_t)__cvta_generic_to_shared(&mbar);
+    constexpr uint32_t BYTES = BULK_STRIDE * 8;
+    if (t == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(BYTES * NT) : "memory");
+    const double *src = jv + sd[DJ0] + NFE * (1 + Q0 * t); // first interior row of this thread's chunk
+    const uintptr_t sa = reinterpret_cast<uintptr_t>(src);
+    const uint32_t delta = (uint32_t)(sa & 15u);
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(S + BULK_STRIDE * t);
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(sa - delta), "r"(BYTES), "r"(mb)
+                 : "memory");
+    // meanwhile: the halo row and this chunk's mass entries (diagonal field) through ordinary loads
+    if (t < NFE) S[BULK_HALO + t] = jv[sd[DJ0] + t];
+    const int32_t *em = sd + 1 * DESC;
+    double m[Q0];
+#pragma unroll
+    for (int k = 0; k < Q0; ++k) m[k] = mvals[em[DM0] + em[DMS] * (1 + Q0 * t + k)];
+    {   // wait for every chunk of the tile (the previous chunk's separator row is read as row -1)
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(mb) : "memory");
+    }
+    double *cb = S + BULK_STRIDE * t + (delta >> 3);
+#pragma unroll
+    for (int k = 0; k < Q0; ++k) cb[3 * k + 1] = __dsub_rn(cb[3 * k + 1], __dmul_rn(m[k], alpha)); // Jb = J - (M*alpha), solver.hpp:523
+    rows.Cb = cb;
+    rows.prev = t > 0 ? cb - BULK_STRIDE + 3 * (Q0 - 1) : S + BULK_HALO;
+    return true;
+}
+
 template <int B, bool FIRST>
 __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView &lv, FactorShared<B> &sh, int t, int tile,
                                             int64_t mb, bool trigger)
@@ -233,6 +314,8 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
     const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
     const int tk = FIRST ? 0 : 1;
     stamp(a, tk, tile, 0);
+    bool bulk = false; // the tile was staged by per-chunk bulk copies (B = 1): level 0 reads the array-of-rows image
+    PackedRows1 prow{nullptr, nullptr};
     if (FIRST)
     {
         const double alpha = a.alpha_arr ? a.alpha_arr[mb] : a.alpha;
@@ -241,7 +324,9 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
         for (int fe = 0; fe < 3 * D::BB; ++fe) affine = affine && (a.flags[tile * 3 * D::BB + fe] & TF_AFF);
         if (affine)
         {
-            if (!stage_matrix_affine_async<B>(t, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha, a.packed != 0))
+            if constexpr (B == 1)
+                if (a.packed >= 2) bulk = stage_matrix_bulk1(t, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha, prow);
+            if (!bulk && !stage_matrix_affine_async<B>(t, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha, a.packed != 0))
                 stage_matrix_affine<B>(t, D::T, tile, sh.S, a.desc, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
         }
         else stage_matrix_first<B>(t, D::T, tile, sh.S, a.sj, a.sm, a.flags, a.jv + mb * a.s_jv, a.mv + mb * a.s_mv, alpha);
@@ -254,7 +339,13 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
     int fail = 0;
     {
         Mat<B> G, Dk, SL, H;
-        factor_phase0<B>(t, nvalid, sh, Ft, a.tol, a.rel, fail, G, Dk, SL, H);
+        if constexpr (B == 1)
+        {
+            if (bulk) chunk_factor<1, D::Q0 - 1>(prow, FacRef<1, D::T>{Ft + t}, a.tol, a.rel, fail, G, Dk, SL, H); // interior tile: every chunk is live
+            else factor_phase0<B>(t, nvalid, sh, Ft, a.tol, a.rel, fail, G, Dk, SL, H);
+        }
+        else
+            factor_phase0<B>(t, nvalid, sh, Ft, a.tol, a.rel, fail, G, Dk, SL, H);
         __syncthreads();
         factor_store1<B>(t, sh, G, Dk, SL, H);
     }

@@ -96,10 +96,18 @@ template <int B> CH_HD Vec<B> mv(const Mat<B> &X, const Vec<B> &v)
 template <int B> CH_HD void vsub(Vec<B> &d, const Vec<B> &x) { for (int i = 0; i < B; ++i) d.a[i] -= x.a[i]; }
 template <int B> CH_HD void vadd(Vec<B> &d, const Vec<B> &x) { for (int i = 0; i < B; ++i) d.a[i] += x.a[i]; }
 
+// Reciprocal of a pivot.  Device: hardware seed + two Newton steps, branch-free -- the IEEE-rounded __drcp_rn carries
+// a slow-path subroutine call that sits in the middle of every elimination step's dependency chain.  The result is
+// within an ulp or two of 1/x; factors are never compared bit for bit (only dx / residuals are), and
+// a zero or non-finite pivot is caught by bad_pivot, not here.
 CH_HD double rcp(double x)
 {
 #if defined(__CUDA_ARCH__)
-    return __drcp_rn(x);
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    y = fma(y, fma(-x, y, 1.0), y);
+    y = fma(y, fma(-x, y, 1.0), y);
+    return y;
 #else
     return 1.0 / x;
 #endif
@@ -262,15 +270,16 @@ template <int B> CH_HD Vec<B> ldv(const double *p, int count, int i)
 // ---- elimination of one chunk's interior (QI rows).  The rows of step k+1 are fetched before the
 // arithmetic of step k and the factor stores come last, so that the only thing a step waits for is
 // the previous pivot: reciprocal, one multiply, one fused multiply-add.
-template <int B> CH_HD double mmaxabs(const Mat<B> &X)
+template <int B> CH_HD double mabssum(const Mat<B> &X)
 {
     double m = 0.0;
 #pragma unroll
-    for (int e = 0; e < B * B; ++e) m = fmax(m, fabs(X.a[e]));
+    for (int e = 0; e < B * B; ++e) m += fabs(X.a[e]);
     return m;
 }
-// tol: absolute pivot threshold; rel: a pivot below rel x (largest entry of the row's own diagonal and
-// super-diagonal blocks before elimination) has been cancelled to noise and counts as zero as well.
+// tol: absolute pivot threshold; rel: a pivot below rel x (sum of the magnitudes of the row's own diagonal and
+// super-diagonal blocks before elimination) has been cancelled to noise and counts as zero as well.  (Sums, not
+// maxima: a double-precision max is a multi-instruction sequence on this machine, an add is one.)
 template <int B, int QI, class Rows, class Fac>
 CH_HD void chunk_factor(const Rows &src, const Fac &dst, double tol, double rel, int &fail, Mat<B> &G, Mat<B> &Dk, Mat<B> &SL, Mat<B> &H)
 {
@@ -279,14 +288,14 @@ CH_HD void chunk_factor(const Rows &src, const Fac &dst, double tol, double rel,
     H = src.Hinit();
     SL = mzero<B>();
     Mat<B> C = src.C(0), An = src.A(1), Dn = src.D(1);
-    double scale = mmaxabs<B>(Dk);
+    double scale = mabssum<B>(Dk);
 #pragma unroll
     for (int k = 0; k < QI; ++k)
     {
         Mat<B> C1, A2, D2;
         if (k + 1 < QI) { C1 = src.C(k + 1); A2 = src.A(k + 2); D2 = src.D(k + 2); }
-        const Mat<B> Dinv = minv<B>(Dk, fmax(tol, rel * fmax(scale, mmaxabs<B>(C))), fail);
-        scale = mmaxabs<B>(Dn);
+        const Mat<B> Dinv = minv<B>(Dk, fma(rel, scale + mabssum<B>(C), tol), fail);
+        scale = mabssum<B>(Dn);
         const Mat<B> L = mmul<B>(An, Dinv);
         const Mat<B> LL = mmul<B>(H, Dinv);
         Dk = Dn;

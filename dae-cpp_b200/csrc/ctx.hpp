@@ -118,6 +118,28 @@ struct LaneSet
     double *refine_r = nullptr, *refine_e = nullptr;                 // [count][s_vec], allocated on first use
 };
 
+// Tiny systems (tiny.cu): one-launch Newton iteration with mapped page-locked hand-off.
+constexpr int TINY_MAX_N = 32;
+struct TinyState
+{
+    bool enabled = true;
+    std::vector<int32_t> Ji, Jj, Mi, Mj; // the cached (i, j) streams, compared on the host
+    bool haveJ = false, haveM = false;
+    bool staleJ = false, staleM = false; // the regular device-side triplet staging lags behind the mapped values
+    DevBuf<int32_t> jptr, jidx, mptr, midx; // dense slot lists
+    DevBuf<double> lu;                      // n*n factors + the row permutation
+    bool have_factor = false;
+    // one mapped page-locked block: f[n] | xk[n] | jv[capJ] | mv[capM] | var | ... | res[8]
+    char *h = nullptr, *d = nullptr;
+    size_t capJ = 0, capM = 0;
+    double *h_f = nullptr, *h_xk = nullptr, *h_jv = nullptr, *h_mv = nullptr, *h_var = nullptr;
+    int32_t *h_res = nullptr;
+    uint32_t seq = 0;
+    double var_tol = 1e-4; // tolerance of the speculative variability (SolverOptions::variability_tolerance default)
+    double spec_var = 0.0;
+    bool spec_valid = false;
+};
+
 struct GroupLaunch
 {
     int32_t kind = 0, begin = 0, count = 0;
@@ -188,9 +210,11 @@ struct daecpp_b200_ctx
     daecpp_b200::chain::Plan CH;
     daecpp_b200::DeviceChain dC;
     const daecpp_b200::LaneSet *lanes = nullptr; // set by a batch context around its launches (batch.cu)
+    daecpp_b200::TinyState tiny;
     bool chain_enabled = true, chain_affine = true;
     int chain_prefetch = 0;            // backward kernel: L2 prefetch of the tile's factors before the dependency wait
-    int chain_packed = 1;              // contiguous-run staging of affine tiles (chain.cu), 0 = per-field strided copies
+    int chain_packed = 2;              // staging of affine tiles (chain.cu): 2 = one bulk copy per thread chunk where the tile qualifies,
+                                       // 1 = contiguous-run LDGSTS, 0 = per-field strided copies
     bool chain_defer_top = true;       // two-level chains inside a fused iteration: the top level is factored by one
                                        // extra CTA of the forward launch, concurrently with the tiles' forward sweeps
     int sm_count = 0;
@@ -292,6 +316,13 @@ int launch_unit_backward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, 
 int chain_try_setup(daecpp_b200_ctx *c, int32_t n, const int32_t *outer, const int32_t *inner);
 int chain_refactor_async(daecpp_b200_ctx *c, double alpha);
 int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, double max_err_abs);
+// tiny.cu
+bool tiny_eligible(const daecpp_b200_ctx *c);
+int tiny_set_triplets(daecpp_b200_ctx *c, bool jac, const double *A, const int32_t *i, const int32_t *j, int64_t nT, bool values_only);
+int tiny_flush(daecpp_b200_ctx *c);
+int tiny_iteration(daecpp_b200_ctx *c, const double *f_host, int32_t do_refactor, int32_t order, const double w[5], double atol, double rtol,
+                   double max_err_abs, double *xk_host, int32_t *flags);
+void tiny_release(daecpp_b200_ctx *c);
 // vector_ops.cu
 int launch_residual(daecpp_b200_ctx *c, int32_t order, const double coef[5], bool clear_flags = false);
 Bdf make_bdf(daecpp_b200_ctx *c, int32_t order, const double coef[5]);
