@@ -334,6 +334,8 @@ int daecpp_b200_set_state(daecpp_b200_ctx *c, const double *x0)
 {
     if (!c || !x0) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
+    c->refine_futile = false;
+    c->tiny.spec_valid = false;
     int rc = upload_vector(c, c->xk, x0);
     if (rc) return rc;
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->xh[0], c->xk, sizeof(double) * c->n, cudaMemcpyDeviceToDevice, c->stream));
@@ -354,6 +356,7 @@ int daecpp_b200_rollback(daecpp_b200_ctx *c)
     if (!c) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
     c->tiny.spec_valid = false;
+    c->refine_futile = false;
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->xk, c->xh[0], sizeof(double) * c->n, cudaMemcpyDeviceToDevice, c->stream));
     return DAECPP_B200_OK;
 }
@@ -444,6 +447,7 @@ int daecpp_b200_accept_step(daecpp_b200_ctx *c, int32_t variability_on, double t
 {
     if (!c) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
+    c->refine_futile = false;
     if (tiny_eligible(c) && c->tiny.spec_valid && (!variability_on || tol == c->tiny.var_tol))
     {   // the tiny iteration measured the variability with its update: shift the history, no read-back
         c->tiny.spec_valid = false;
@@ -522,7 +526,8 @@ static int enqueue_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t or
 // One refinement step restores it; flags are recomputed from the corrected update.
 static bool wants_refinement(const daecpp_b200_ctx *c, int32_t fl)
 {
-    return c->refine_steps > 0 && !c->direct_csc && (fl & DAECPP_B200_NOT_CONVERGED) && !(fl & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED));
+    return c->refine_steps > 0 && !c->direct_csc && !c->refine_futile && (fl & DAECPP_B200_NOT_CONVERGED) &&
+           !(fl & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED));
 }
 static int refine_sync(daecpp_b200_ctx *c, double atol, double rtol, double max_err_abs, bool b_is_stored)
 {
@@ -530,6 +535,9 @@ static int refine_sync(daecpp_b200_ctx *c, double atol, double rtol, double max_
     if (rc) return rc;
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 2, c->d_flags + 2, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
+    // the corrected update fails the same way: the noise is not the solve's, no second attempt within this Newton loop
+    const int32_t fl = c->h_flags[2];
+    c->refine_futile = (fl & DAECPP_B200_NOT_CONVERGED) && !(fl & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED));
     return DAECPP_B200_OK;
 }
 

@@ -48,6 +48,7 @@ struct daecpp_b200_batch
     char *h_res = nullptr, *d_res = nullptr;
     size_t res_bytes = 0;
     std::vector<int32_t> hbase;
+    std::vector<char> refine_futile; // the lane's last refinement in this Newton loop did not change the outcome: no second one
     LaneSet L;
 
     daecpp_b200_device_functors fn{};
@@ -258,6 +259,7 @@ int daecpp_b200_batch_create(int32_t n, int32_t lanes, int device, daecpp_b200_b
     if ((e = cudaEventCreate(&b->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
     std::memset(b->h_ctl, 0, b->ctl_bytes);
     b->hbase.assign((size_t)lanes, 0);
+    b->refine_futile.assign((size_t)lanes, 0);
     b->rhs_loaded.assign((size_t)lanes, 0);
     b->jac_loaded.assign((size_t)lanes, 0);
     // the chain kernels of the prototype read / write the lane slabs
@@ -608,8 +610,9 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
         for (int32_t l = 0; l < Ln; ++l)
         {
             const int32_t f = fl0[4 * l];
+            if (cmd[l].pre != DAECPP_B200_LANE_KEEP) b->refine_futile[l] = 0; // a new step (or a new attempt at it)
             const bool want = cmd[l].mode != DAECPP_B200_LANE_IDLE && fl0[4 * l + 1] == 0 && (f & DAECPP_B200_NOT_CONVERGED) &&
-                              !(f & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED));
+                              !(f & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED)) && !b->refine_futile[l];
             b->ctl_mode()[l] = want ? DAECPP_B200_LANE_SOLVE : DAECPP_B200_LANE_IDLE;
             b->ctl_pre()[l] = DAECPP_B200_LANE_KEEP;
             if (want) b->ctl_list_active()[n_ref++] = l;
@@ -641,6 +644,8 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
                     for (int k = 0; k < 4; ++k) fl1[4 * l + k] = keep[4 * (size_t)l + k];
                     var1[l] = keep_var[l];
                 }
+                else if ((fl1[4 * l] & DAECPP_B200_NOT_CONVERGED) && !(fl1[4 * l] & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED)))
+                    b->refine_futile[l] = 1; // the corrected update fails the same way: the noise is not the solve's
             b->n_refine_rounds += 1;
             b->n_refined_lanes += n_ref;
         }

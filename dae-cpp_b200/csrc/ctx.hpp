@@ -252,6 +252,7 @@ struct daecpp_b200_ctx
     int refine_steps = 1;
     double refine_floor = 1e-11;
     double n_refine = 0;
+    bool refine_futile = false; // the last refinement of this Newton loop left the outcome as it was: not repeated until the step changes
     bool assemble_only = false;
     bool pinned_io = false; // host vectors handed to the ABI are page-locked: no staging copies
     double pivot_tol = 0.0;

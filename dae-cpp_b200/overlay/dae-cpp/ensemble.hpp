@@ -345,6 +345,7 @@ struct lockstep_stats
     double ms_wall{0.0};
     long lane_iterations{0}, lane_refactorisations{0};
     double kernels_launched{0.0};
+    double refine_rounds{0.0}, refined_lanes{0.0}; // guarded refinement passes (include/daecpp_b200.h) and the lanes they touched
     double ms_setup{0.0}; // batch creation, pattern analysis, uploads (before the first round)
 };
 
@@ -483,6 +484,8 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     double v = 0.0;
     if (daecpp_b200_batch_get_stat(b, "ms_device", &v) == DAECPP_B200_OK) st.ms_device = v;
     if (daecpp_b200_batch_get_stat(b, "kernels_launched", &v) == DAECPP_B200_OK) st.kernels_launched = v;
+    if (daecpp_b200_batch_get_stat(b, "refine_rounds", &v) == DAECPP_B200_OK) st.refine_rounds = v;
+    if (daecpp_b200_batch_get_stat(b, "refined_lanes", &v) == DAECPP_B200_OK) st.refined_lanes = v;
     st.ms_setup = st_setup_ms;
     stamp("final states");
     daecpp_b200_batch_destroy(b);

@@ -164,9 +164,9 @@ int main(int argc, char **argv)
     if (int rc = dump(kv, R)) return rc;
     std::printf("{\"impl\": \"%s\", \"workload\": \"%s\", \"n\": %zu, \"members\": %zu, \"first\": %zu, \"count\": %zu, \"failed\": %d, "
                 "\"steps\": %ld, \"rounds\": %ld, \"lane_iterations\": %ld, \"lane_refactorisations\": %ld, \"wall_ms\": %.3f, "
-                "\"first_wall_ms\": %.3f, \"device_ms\": %.3f, \"systems_per_s\": %.6f, \"status0\": %d, \"checksum\": %.17g}\n",
+                "\"first_wall_ms\": %.3f, \"refine_rounds\": %.0f, \"refined_lanes\": %.0f, \"device_ms\": %.3f, \"systems_per_s\": %.6f, \"status0\": %d, \"checksum\": %.17g}\n",
                 impl, wl.c_str(), n, members, first, count, R.failed, steps, st.rounds, st.lane_iterations, st.lane_refactorisations, st.ms_wall,
-                first_ms, st.ms_device, 1e3 * double(count) / st.ms_wall, R.members.empty() ? -1 : R.members[0].status, checksum);
+                first_ms, st.refine_rounds, st.refined_lanes, st.ms_device, 1e3 * double(count) / st.ms_wall, R.members.empty() ? -1 : R.members[0].status, checksum);
     return R.failed ? 1 : 0;
 }
 #endif // ENSDEV_NO_MAIN
