@@ -28,7 +28,7 @@ SYMBOLS = [
     "daecpp_b200_batch_create", "daecpp_b200_batch_destroy", "daecpp_b200_batch_last_error", "daecpp_b200_batch_set_pattern",
     "daecpp_b200_batch_set_mass_values", "daecpp_b200_batch_set_jacobian_values", "daecpp_b200_batch_set_rhs_values",
     "daecpp_b200_batch_set_state", "daecpp_b200_batch_get_vector", "daecpp_b200_batch_set_device_functors",
-    "daecpp_b200_batch_round", "daecpp_b200_batch_get_stat",
+    "daecpp_b200_batch_round", "daecpp_b200_batch_get_stat", "daecpp_b200_variability_noalloc",
 ]
 
 LANE_IDLE, LANE_SOLVE, LANE_REFACTOR = 0, 1, 2
@@ -103,6 +103,7 @@ def load():
     lib.daecpp_b200_batch_round.argtypes = [_vp, C.POINTER(LaneCmd), C.c_double, C.c_double, C.c_double, C.c_int32, C.c_double,
                                             C.POINTER(LaneResult)]
     lib.daecpp_b200_batch_get_stat.argtypes = [_vp, C.c_char_p, C.POINTER(C.c_double)]
+    lib.daecpp_b200_variability_noalloc.argtypes = [_vp, _vp, C.c_int64, C.c_double, _vp, _vp, C.c_char_p, C.c_size_t]
     return lib
 
 

@@ -271,6 +271,25 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
  * "bytes_per_lane" ... */
 int daecpp_b200_batch_get_stat(daecpp_b200_batch *b, const char *key, double *value);
 
+/* ==== an entry point that allocates nothing ================================================================
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Maximum relative variability of solver.hpp:703-717 -- max_i |(x0_i - xk_i) / x0_i| over the elements with
+ * |x0_i| > tolerance and |xk_i| > tolerance, NaN counted as 0 -- i.e. what daecpp_b200_accept_step reports, computed
+ * by a variant of its kernel whose scratch (per-block partial maxima + a ticket word) lives in a file-scope
+ * `static __device__` array of fixed size (33 KB per GPU that loads the library, held until exit) instead of
+ * memory the context allocated.  xk_dev, x0_dev (n doubles each) and result_dev (1 double) are DEVICE pointers owned
+ * by the caller.  The call only enqueues a memset node and one kernel on `stream` (a cudaStream_t; NULL = the
+ * default stream) and returns; *result_dev is valid once that stream work has completed.  It calls no cudaMalloc,
+ * cudaFree or allocating library routine.  The first call on a device also looks up the scratch array's device
+ * address (cudaGetSymbolAddress): make one call per device outside any capture.
+ * n > DAECPP_B200_NOALLOC_MAX_N is refused with DAECPP_B200_EINVAL and a message in errbuf (may be NULL).
+ * Every call on a device shares the one scratch array: calls that overlap on the GPU (different streams, different
+ * host threads) race on it -- serialise them. */
+#define DAECPP_B200_NOALLOC_MAX_N 16777216
+int daecpp_b200_variability_noalloc(const double *xk_dev, const double *x0_dev, int64_t n, double tolerance, double *result_dev,
+                                    void *stream, char *errbuf, size_t errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif
