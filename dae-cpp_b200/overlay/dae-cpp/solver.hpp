@@ -252,6 +252,22 @@ public:
         daecpp_b200_destroy(m_ctx);
     }
 
+    // Device-side phase stopwatch (CUDA events between the phases of every iteration; costs a stream synchronisation per
+    // iteration, so it is only switched on when the caller wants the timing report: verbosity >= 1, systems above the
+    // one-launch tiny path).  phase_totals: milliseconds spent in {assembly, residual, refactor, solve, update} so far.
+    void enable_phase_timing() { daecpp_b200_set_option(m_ctx, "phase_timing", 1.0); }
+    void phase_totals(double ms[5]) const
+    {
+        static const char *keys[5] = {"ms_phase_assembly", "ms_phase_residual", "ms_phase_refactor", "ms_phase_solve", "ms_phase_update"};
+        double samples = 0.0;
+        daecpp_b200_get_stat(m_ctx, "n_phase_samples", &samples);
+        for (int k = 0; k < 5; ++k)
+        {
+            double avg = 0.0;
+            daecpp_b200_get_stat(m_ctx, keys[k], &avg);
+            ms[k] = avg * samples;
+        }
+    }
     double *f_host() { return m_f; }
     bool jacobian_values_page_locked() const { return m_pin.p != nullptr; }
     const double *xk_host() const { return m_xk; }
@@ -448,6 +464,7 @@ class Integrator
     uint64_t m_n_steps{0};
     uint32_t m_n_iter_failed{0};
     bool m_delay_timestep_inc{false};
+    bool m_phase_timing{false}, m_phase_folded{false};
 
     enum class StepResult { accepted, redo, leave_time_loop, finished };
     exit_code::status m_status{exit_code::unknown};
@@ -687,7 +704,33 @@ public:
     }
 
     const Counters &counters() const { return m_count; }
-    timer::Time &time() { return m_time; }
+    // The reference's timer buckets (dae-cpp/timer.hpp:59-71, filled at dae-cpp/solver.hpp:438,514,535-539,556-560,588).
+    // Here one device submission does the work of five of them, so the host stopwatch around it can only feed
+    // "factorization" / "linear_solver"; with the device-side phase stopwatch on, its split is handed on:
+    //   linear_algebra <- assembly of Jb + residual b (which forms dxdt on the fly: time_derivative stays with it)
+    //   linear_solver  <- triangular solves          error_check <- error check + update
+    //   factorization  <- everything else of the submissions: numeric refactorisation, transfers, host turn-around
+    // (kernels that fuse two phases report the fused time under the phase that hosts them).
+    timer::Time &time()
+    {
+        if (m_phase_timing && !m_phase_folded)
+        {
+            m_phase_folded = true;
+            double ms[5];
+            m_dev.phase_totals(ms);
+            auto &t = m_time.timers;
+            const double submissions = t[timer::factorization] + t[timer::linear_solver];
+            const double moved = ms[0] + ms[1] + ms[3] + ms[4];
+            if (moved > 0.0 && moved <= submissions)
+            {
+                t[timer::linear_algebra] += ms[0] + ms[1];
+                t[timer::error_check] += ms[4];
+                t[timer::linear_solver] = ms[3];
+                t[timer::factorization] = submissions - moved;
+            }
+        }
+        return m_time;
+    }
 
     exit_code::status run(const state_vector &x0, const std::vector<double> &t_out, bool is_jac_auto)
     {
@@ -706,6 +749,9 @@ public:
 
             dt() = m_opt.dt_init;
             m_dev.set_state(x0);
+            m_phase_timing = verbose(1) && m_size > 32;
+            if (m_phase_timing)
+                m_dev.enable_phase_timing();
 
             PRINT(verbose(2), "Float size:      " << 8 * sizeof(float_type) << " bit");
             PRINT(verbose(2), "Integer size:    " << 8 * sizeof(int_type) << " bit");
