@@ -36,12 +36,13 @@ LANE_KEEP, LANE_ACCEPT, LANE_ROLLBACK = 0, 1, 2
 
 
 class LaneCmd(C.Structure):
-    _fields_ = [("mode", C.c_int32), ("pre", C.c_int32), ("order", C.c_int32), ("reserved", C.c_int32), ("t", C.c_double),
-                ("dt", C.c_double * 4)]
+    _fields_ = [("mode", C.c_int32), ("pre", C.c_int32), ("order", C.c_int32), ("period", C.c_int32), ("t", C.c_double),
+                ("dt", C.c_double * 4), ("phase", C.c_int32), ("max_iterations", C.c_int32)]
 
 
 class LaneResult(C.Structure):
-    _fields_ = [("flags", C.c_int32), ("status", C.c_int32), ("variability", C.c_double)]
+    _fields_ = [("flags", C.c_int32), ("status", C.c_int32), ("variability", C.c_double), ("iterations", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 def load():
@@ -357,10 +358,12 @@ class Batch:
         for k, q in enumerate(cmds):
             arr[k].mode = q.get("mode", LANE_IDLE); arr[k].pre = q.get("pre", LANE_KEEP); arr[k].order = q.get("order", 1)
             arr[k].t = q.get("t", 0.0)
+            arr[k].period = q.get("period", 0); arr[k].phase = q.get("phase", 0); arr[k].max_iterations = q.get("max_iterations", 1)
             for i, v in enumerate(q.get("dt", (0.0, 0.0, 0.0, 0.0))):
                 arr[k].dt[i] = v
         res = (LaneResult * self.lanes)()
         rc = self._ck(self.lib.daecpp_b200_batch_round(self.h, arr, atol, rtol, max_err_abs, int(variability_on), var_tol, res), allow)
+        self.last_iterations = [r.iterations for r in res]
         return rc, [(r.flags, r.status, r.variability) for r in res]
 
     def stat(self, key):

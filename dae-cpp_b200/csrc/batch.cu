@@ -40,8 +40,8 @@ struct daecpp_b200_batch
     bool have_pattern = false, have_mass = false;
 
     // control words of a round: pinned structure-of-arrays block and its device mirror
-    //   mode | pre | order | hbase | active lanes | refactoring lanes | lanes with a pre action  (i32[L] each, L even-padded)
-    //   | t f64[L] | w f64[5][L]
+    //   mode | pre | order | hbase | active lanes | refactoring lanes | lanes with a pre action | no-refinement marks |
+    //   planned modes of iterations 0..7  (i32[L] each, padded to 8 bytes)  | t f64[L] | w f64[5][L]
     char *h_ctl = nullptr, *d_ctl = nullptr;
     size_t ctl_bytes = 0;
     // results: flags i32[4][L] (lane-major [L][4]) | var u64[L]
@@ -55,6 +55,7 @@ struct daecpp_b200_batch
     bool have_fn = false;
     std::vector<char> rhs_loaded, jac_loaded; // host-functor mode: the lane has values to iterate on
 
+    static constexpr int KMAX = DAECPP_B200_MAX_ROUND_ITERATIONS;
     static constexpr size_t BOUNCE_BYTES = (size_t)8 << 20;
     char *h_bounce = nullptr;     // two page-locked bounce buffers for the lane slabs of pageable callers
     cudaEvent_t ev_bounce[2] = {nullptr, nullptr};
@@ -69,7 +70,12 @@ struct daecpp_b200_batch
     int32_t *ctl_list_active() const { return ctl_mode() + 4 * lanes; }
     int32_t *ctl_list_refactor() const { return ctl_mode() + 5 * lanes; }
     int32_t *ctl_list_pre() const { return ctl_mode() + 6 * lanes; }
-    size_t ctl_int_bytes() const { return (sizeof(int32_t) * 7 * (size_t)lanes + 7) / 8 * 8; }
+    int32_t *ctl_norefine() const { return ctl_mode() + 7 * lanes; }
+    int32_t *ctl_plan(int j) const { return ctl_mode() + (8 + j) * (size_t)lanes; }
+    size_t ctl_int_bytes() const { return (sizeof(int32_t) * (8 + KMAX) * (size_t)lanes + 7) / 8 * 8; }
+    // results: per iteration j of the round  flags i32[L][4] | var u64[L];  behind them  iterations run i32[L] | effective mode i32[L]
+    size_t res_stride() const { return sizeof(int32_t) * 4 * (size_t)lanes + sizeof(unsigned long long) * (size_t)lanes; }
+    int32_t *res_iters(char *base) const { return reinterpret_cast<int32_t *>(base + KMAX * res_stride()); }
     double *ctl_t() const { return reinterpret_cast<double *>(h_ctl + ctl_int_bytes()); }
     template <class T> T *dev(const T *host_ptr) const { return reinterpret_cast<T *>(d_ctl + (reinterpret_cast<const char *>(host_ptr) - h_ctl)); }
     double *ctl_w() const { return ctl_t() + lanes; }
@@ -121,6 +127,32 @@ __global__ void k_batch_pre(PreArgs a)
     else xk[i] = x0[i];
 }
 
+struct PlanArgs
+{
+    int32_t lanes, j, n_list;
+    const int32_t *list, *plan_j, *norefine;
+    const int32_t *prev_flags; // [lanes][4] of iteration j-1
+    int32_t *eff, *iters;
+};
+// Which lanes run iteration j of the round: all planned ones for j = 0; afterwards those whose previous iteration ended
+// the way the reference's Newton loop continues (solver.hpp:431-627).  One thread per lane of the round's list.
+__global__ void k_batch_plan(PlanArgs a)
+{
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= a.n_list) return;
+    const int lane = a.list[q];
+    int m = a.plan_j[lane];
+    if (a.j > 0 && m != DAECPP_B200_LANE_IDLE)
+    {
+        const int32_t *pf = a.prev_flags + 4 * lane;
+        const bool go_on = a.eff[lane] != DAECPP_B200_LANE_IDLE && (pf[0] & DAECPP_B200_NOT_CONVERGED) && !(pf[0] & DAECPP_B200_DIVERGED) &&
+                           pf[1] == 0 && ((pf[0] & DAECPP_B200_ABOVE_FLOOR) || a.norefine[lane]);
+        if (!go_on) m = DAECPP_B200_LANE_IDLE;
+    }
+    a.eff[lane] = m;
+    if (m != DAECPP_B200_LANE_IDLE) a.iters[lane] += 1;
+}
+
 struct ResArgs
 {
     int32_t n, lanes;
@@ -151,6 +183,7 @@ __device__ __forceinline__ Bdf lane_bdf(const ResArgs &a, int lane)
 __global__ void k_batch_residual(ResArgs a)
 {
     const int lane = a.list[blockIdx.y];
+    if (a.mode[lane] == DAECPP_B200_LANE_IDLE) return; // halted earlier in this round
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= a.n) return;
     const Bdf s = lane_bdf(a, lane);
@@ -249,7 +282,7 @@ int daecpp_b200_batch_create(int32_t n, int32_t lanes, int device, daecpp_b200_b
     b->xk = b->slab; b->f = b->slab + per; b->b = b->slab + 2 * per; b->dx = b->slab + 3 * per; b->hist = b->slab + 4 * per;
     if ((e = cudaMemsetAsync(b->slab, 0, sizeof(double) * 8 * per, b->c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
     b->ctl_bytes = b->ctl_int_bytes() + sizeof(double) * 6 * (size_t)lanes;
-    b->res_bytes = sizeof(int32_t) * 4 * (size_t)lanes + sizeof(unsigned long long) * (size_t)lanes;
+    b->res_bytes = daecpp_b200_batch::KMAX * b->res_stride() + sizeof(int32_t) * 2 * (size_t)lanes;
     if ((e = cudaMallocHost((void **)&b->h_ctl, b->ctl_bytes)) != cudaSuccess) return bail(e, "cudaMallocHost");
     if ((e = cudaMalloc((void **)&b->d_ctl, b->ctl_bytes)) != cudaSuccess) return bail(e, "cudaMalloc(ctl)");
     if ((e = cudaMallocHost((void **)&b->h_res, b->res_bytes)) != cudaSuccess) return bail(e, "cudaMallocHost");
@@ -269,7 +302,7 @@ int daecpp_b200_batch_create(int32_t n, int32_t lanes, int device, daecpp_b200_b
     L.count = lanes;
     L.s_vec = (int64_t)b->ns; L.s_hist = (int64_t)per;
     L.hist = b->hist;
-    L.mode = b->dev(b->ctl_mode()); L.hbase = b->dev(b->ctl_hbase()); L.order = b->dev(b->ctl_order());
+    L.mode = b->res_iters(b->d_res) + lanes; /* the EFFECTIVE mode of the iteration in flight (k_batch_plan) */ L.hbase = b->dev(b->ctl_hbase()); L.order = b->dev(b->ctl_order());
     L.w = b->dev(b->ctl_w());
     L.list_active = b->dev(b->ctl_list_active()); L.list_refactor = b->dev(b->ctl_list_refactor());
     L.flags = reinterpret_cast<int32_t *>(b->d_res);
@@ -509,7 +542,8 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
     daecpp_b200_ctx *c = b->c;
     cudaStream_t st = c->stream;
     const int32_t Ln = b->lanes;
-    int n_active = 0, n_refactor = 0;
+    constexpr int KMAX = daecpp_b200_batch::KMAX;
+    int n_active = 0, n_refactor0 = 0, n_pre = 0, K = 1;
     for (int32_t l = 0; l < Ln; ++l)
     {
         const daecpp_b200_lane_cmd &q = cmd[l];
@@ -517,30 +551,35 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
         b->ctl_mode()[l] = q.mode;
         b->ctl_pre()[l] = q.pre;
         if (q.pre == DAECPP_B200_LANE_ACCEPT) b->hbase[l] = (b->hbase[l] + 3) & 3; // the oldest slot receives xk and becomes x[0]
+        if (q.pre != DAECPP_B200_LANE_KEEP) { b->refine_futile[l] = 0; b->ctl_list_pre()[n_pre++] = l; } // a new step, or a new attempt at it
         b->ctl_hbase()[l] = b->hbase[l];
         b->ctl_order()[l] = q.order;
         b->ctl_t()[l] = q.t;
+        b->ctl_norefine()[l] = (c->refine_steps <= 0 || b->refine_futile[l]) ? 1 : 0;
         double w[5] = {0, 0, 0, 0, 0};
+        int kl = 0;
         if (q.mode != DAECPP_B200_LANE_IDLE)
         {
             if (!weights(q.order, q.dt, w)) return bfail(b, DAECPP_B200_EINVAL, "unsupported time integration order");
-            if (!b->have_fn && (!b->rhs_loaded[l] || (q.mode == DAECPP_B200_LANE_REFACTOR && !b->jac_loaded[l])))
-                return bfail(b, DAECPP_B200_EINVAL, "host-functor lane without uploaded rhs / Jacobian values");
-            ++n_active;
-            if (q.mode == DAECPP_B200_LANE_REFACTOR) ++n_refactor;
+            kl = q.max_iterations > 1 ? (q.max_iterations < KMAX ? q.max_iterations : KMAX) : 1;
+            if (!b->have_fn)
+            {
+                kl = 1; // host functors: every iteration needs fresh values from the caller
+                if (!b->rhs_loaded[l] || (q.mode == DAECPP_B200_LANE_REFACTOR && !b->jac_loaded[l]))
+                    return bfail(b, DAECPP_B200_EINVAL, "host-functor lane without uploaded rhs / Jacobian values");
+            }
+            b->ctl_list_active()[n_active++] = l;
+            if (q.mode == DAECPP_B200_LANE_REFACTOR) b->ctl_list_refactor()[n_refactor0++] = l;
+            if (kl > K) K = kl;
+        }
+        for (int j = 0; j < KMAX; ++j)
+        {
+            int m = DAECPP_B200_LANE_IDLE;
+            if (j == 0) m = q.mode;
+            else if (j < kl) m = (q.period <= 1 || (q.phase + j) % q.period == 0) ? DAECPP_B200_LANE_REFACTOR : DAECPP_B200_LANE_SOLVE;
+            b->ctl_plan(j)[l] = m;
         }
         for (int k = 0; k < 5; ++k) b->ctl_w()[(size_t)k * Ln + l] = w[k];
-    }
-    int n_pre = 0;
-    {
-        int na = 0, nr = 0;
-        for (int32_t l = 0; l < Ln; ++l)
-        {
-            if (cmd[l].mode != DAECPP_B200_LANE_IDLE) b->ctl_list_active()[na++] = l;
-            if (cmd[l].mode == DAECPP_B200_LANE_REFACTOR) b->ctl_list_refactor()[nr++] = l;
-            if (cmd[l].pre != DAECPP_B200_LANE_KEEP) b->ctl_list_pre()[n_pre++] = l;
-        }
-        b->L.n_active = na; b->L.n_refactor = nr;
     }
     BATCH_TRY(b, cudaEventRecord(b->ev0, st));
     BATCH_TRY(b, cudaMemcpyAsync(b->d_ctl, b->h_ctl, b->ctl_bytes, cudaMemcpyHostToDevice, st));
@@ -552,80 +591,126 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
         k_batch_pre<<<dim3(gx, (unsigned)n_pre), TPB, 0, st>>>(a);
         c->kernels += 1;
     }
-    const dim3 gv(gx, (unsigned)(n_active > 0 ? n_active : 1));
+    const size_t rstride = b->res_stride();
+    auto flags_of = [&](char *base, int j) { return reinterpret_cast<int32_t *>(base + (size_t)j * rstride); };
+    auto var_of = [&](char *base, int j) { return reinterpret_cast<unsigned long long *>(base + (size_t)j * rstride + sizeof(int32_t) * 4 * (size_t)Ln); };
     if (n_active > 0)
     {
+        const dim3 gv(gx, (unsigned)n_active);
         const double *d_t = b->dev(b->ctl_t());
-        if (b->have_fn)
-        {
-            daecpp_b200_functor_args fa{};
-            fa.n = b->n; fa.lanes = Ln; fa.x_stride = (int64_t)b->ns; fa.x = b->xk; fa.t = d_t; fa.mode = b->L.mode; fa.stream = st;
-            fa.min_mode = DAECPP_B200_LANE_SOLVE; fa.out = b->f; fa.out_stride = (int64_t)b->ns;
-            fa.lane_list = b->L.list_active; fa.n_list = n_active;
-            if (b->fn.rhs(b->fn.user, &fa)) return bfail(b, DAECPP_B200_EINVAL, "device rhs functor failed");
-            c->kernels += 1;
-            if (n_refactor)
-            {
-                fa.min_mode = DAECPP_B200_LANE_REFACTOR; fa.out = b->jv.p; fa.out_stride = b->nTJ;
-                fa.lane_list = b->L.list_refactor; fa.n_list = n_refactor;
-                if (b->fn.jacobian(b->fn.user, &fa)) return bfail(b, DAECPP_B200_EINVAL, "device Jacobian functor failed");
-                c->kernels += 1;
-            }
-        }
         b->L.var_on = variability_on ? 1 : 0;
         b->L.var_tol = variability_tolerance;
-        // the prototype's launch code runs over the lane slabs
-        c->lanes = &b->L;
-        c->xk = b->xk; c->f = b->f; c->b = b->b; c->dx = b->dx;
-        int rc = DAECPP_B200_OK;
+        b->L.n_active = n_active;
+        b->L.list_active = b->dev(b->ctl_list_active());
         const bool fuse_res = c->m_diag && c->chain_fuse_residual;
-        if (!fuse_res)
+        int rc = DAECPP_B200_OK;
+        for (int j = 0; j < K && !rc; ++j)
         {
-            ResArgs a{b->n, Ln, (int64_t)b->ns, b->L.s_hist, b->L.s_mv, b->L.mode, b->L.hbase, b->L.order, b->L.list_active, b->L.w,
-                      b->xk, b->hist, b->mv.p, b->f, b->b, c->m_rowptr.p, c->m_rowslot.p, c->m_rowcol.p};
-            k_batch_residual<<<gv, TPB, 0, st>>>(a);
-            c->kernels += 1;
+            // the round's lists stay those of iteration 0 (a superset): lanes that halted on the device leave through
+            // their effective mode word.  Iterations after the first refactorise whoever planned to.
+            int n_refac = n_refactor0;
+            if (j > 0)
+            {
+                n_refac = 0;
+                for (int32_t q = 0; q < n_active; ++q)
+                    if (b->ctl_plan(j)[b->ctl_list_active()[q]] == DAECPP_B200_LANE_REFACTOR) ++n_refac;
+            }
+            b->L.flags = flags_of(b->d_res, j);
+            b->L.var = var_of(b->d_res, j);
+            {
+                PlanArgs pa{Ln, j, n_active, b->L.list_active, b->dev(b->ctl_plan(j)), b->dev(b->ctl_norefine()),
+                            j > 0 ? flags_of(b->d_res, j - 1) : nullptr, b->res_iters(b->d_res) + Ln, b->res_iters(b->d_res)};
+                k_batch_plan<<<(n_active + 127) / 128, 128, 0, st>>>(pa);
+                c->kernels += 1;
+            }
+            // j == 0: the compacted list of refactoring lanes is exact; later iterations run the factor kernels over the
+            // whole active list (the effective mode sorts the lanes out)
+            b->L.list_refactor = j == 0 ? b->dev(b->ctl_list_refactor()) : b->L.list_active;
+            b->L.n_refactor = j == 0 ? n_refactor0 : n_active;
+            if (b->have_fn)
+            {
+                daecpp_b200_functor_args fa{};
+                fa.n = b->n; fa.lanes = Ln; fa.x_stride = (int64_t)b->ns; fa.x = b->xk; fa.t = d_t; fa.mode = b->L.mode; fa.stream = st;
+                fa.min_mode = DAECPP_B200_LANE_SOLVE; fa.out = b->f; fa.out_stride = (int64_t)b->ns;
+                fa.lane_list = b->L.list_active; fa.n_list = n_active;
+                if (b->fn.rhs(b->fn.user, &fa)) return bfail(b, DAECPP_B200_EINVAL, "device rhs functor failed");
+                c->kernels += 1;
+                if (n_refac)
+                {
+                    fa.min_mode = DAECPP_B200_LANE_REFACTOR; fa.out = b->jv.p; fa.out_stride = b->nTJ;
+                    fa.lane_list = b->L.list_refactor; fa.n_list = b->L.n_refactor;
+                    if (b->fn.jacobian(b->fn.user, &fa)) return bfail(b, DAECPP_B200_EINVAL, "device Jacobian functor failed");
+                    c->kernels += 1;
+                }
+            }
+            // the prototype's launch code runs over the lane slabs
+            c->lanes = &b->L;
+            c->xk = b->xk; c->f = b->f; c->b = b->b; c->dx = b->dx;
+            if (!fuse_res)
+            {
+                ResArgs a{b->n, Ln, (int64_t)b->ns, b->L.s_hist, b->L.s_mv, b->L.mode, b->L.hbase, b->L.order, b->L.list_active, b->L.w,
+                          b->xk, b->hist, b->mv.p, b->f, b->b, c->m_rowptr.p, c->m_rowslot.p, c->m_rowcol.p};
+                k_batch_residual<<<gv, TPB, 0, st>>>(a);
+                c->kernels += 1;
+            }
+            c->chain_may_defer = true; // the solve follows on the stream: the top level may ride in the forward launch
+            if (n_refac) rc = chain_refactor_async(c, 0.0);
+            c->chain_may_defer = false;
+            if (!rc)
+            {
+                c->fuse_residual_now = fuse_res;
+                c->publish_flags = false;
+                rc = chain_solve(c, true, atol, rtol, max_err_abs);
+                c->fuse_residual_now = false;
+            }
+            c->lanes = nullptr;
+            c->xk = b->proto_xk; c->f = b->proto_f; c->b = b->proto_b; c->dx = b->proto_dx;
         }
-        c->chain_may_defer = true; // the solve follows on the stream: the top level may ride in the forward launch
-        if (n_refactor) rc = chain_refactor_async(c, 0.0);
-        c->chain_may_defer = false;
-        if (!rc)
-        {
-            c->fuse_residual_now = fuse_res;
-            c->publish_flags = false;
-            rc = chain_solve(c, true, atol, rtol, max_err_abs);
-            c->fuse_residual_now = false;
-        }
-        c->lanes = nullptr;
-        c->xk = b->proto_xk; c->f = b->proto_f; c->b = b->proto_b; c->dx = b->proto_dx;
         if (rc) return bfail(b, rc, c->err);
     }
     BATCH_TRY(b, cudaMemcpyAsync(b->h_res, b->d_res, b->res_bytes, cudaMemcpyDeviceToHost, st));
     BATCH_TRY(b, cudaStreamSynchronize(st));
+    const int32_t *iters = b->res_iters(b->h_res);
+    // the results of a lane are those of the last iteration it ran
+    std::vector<int32_t> last((size_t)Ln, 0);
+    for (int32_t l = 0; l < Ln; ++l) last[l] = iters[l] > 0 ? iters[l] - 1 : 0;
     if (n_active > 0 && c->refine_steps > 0)
     {   // guarded refinement (api.cu: wants_refinement) for the lanes whose update failed the convergence test only on
         // elements below the refinement floor: a second, small pass over those lanes
-        const int32_t *fl0 = reinterpret_cast<const int32_t *>(b->h_res);
         int n_ref = 0;
         for (int32_t l = 0; l < Ln; ++l)
         {
-            const int32_t f = fl0[4 * l];
-            if (cmd[l].pre != DAECPP_B200_LANE_KEEP) b->refine_futile[l] = 0; // a new step (or a new attempt at it)
-            const bool want = cmd[l].mode != DAECPP_B200_LANE_IDLE && fl0[4 * l + 1] == 0 && (f & DAECPP_B200_NOT_CONVERGED) &&
+            const int32_t *fl0 = flags_of(b->h_res, last[l]) + 4 * l;
+            const int32_t f = fl0[0];
+            const bool want = cmd[l].mode != DAECPP_B200_LANE_IDLE && fl0[1] == 0 && (f & DAECPP_B200_NOT_CONVERGED) &&
                               !(f & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED)) && !b->refine_futile[l];
-            b->ctl_mode()[l] = want ? DAECPP_B200_LANE_SOLVE : DAECPP_B200_LANE_IDLE;
-            b->ctl_pre()[l] = DAECPP_B200_LANE_KEEP;
+            b->ctl_mode()[l] = want ? DAECPP_B200_LANE_SOLVE : DAECPP_B200_LANE_IDLE; // (host-side mark; the device reads the plan words)
+            b->ctl_plan(0)[l] = b->ctl_mode()[l];
             if (want) b->ctl_list_active()[n_ref++] = l;
         }
         if (n_ref)
         {
-            std::vector<int32_t> keep(fl0, fl0 + 4 * (size_t)Ln);
-            std::vector<unsigned long long> keep_var((size_t)Ln);
-            std::memcpy(keep_var.data(), b->h_res + sizeof(int32_t) * 4 * (size_t)Ln, sizeof(unsigned long long) * (size_t)Ln);
             const size_t per = (size_t)Ln * b->ns;
             BATCH_TRY(b, b->refine_buf.reserve(2 * per));
             b->L.refine_r = b->refine_buf.p; b->L.refine_e = b->refine_buf.p + per;
             BATCH_TRY(b, cudaMemcpyAsync(b->d_ctl, b->h_ctl, b->ctl_bytes, cudaMemcpyHostToDevice, st));
+            // results of the pass go to a scratch slot (iteration slot KMAX-1 is free unless the round ran KMAX
+            // iterations; then slot K-1 is borrowed and what the other lanes left there is put back)
+            const int slot = K < KMAX ? KMAX - 1 : K - 1;
+            b->L.flags = flags_of(b->d_res, slot);
+            b->L.var = var_of(b->d_res, slot);
+            std::vector<int32_t> keep_fl;
+            std::vector<unsigned long long> keep_var;
+            if (slot == K - 1)
+            {
+                keep_fl.assign(flags_of(b->h_res, slot), flags_of(b->h_res, slot) + 4 * (size_t)Ln);
+                keep_var.assign(var_of(b->h_res, slot), var_of(b->h_res, slot) + Ln);
+            }
+            {
+                PlanArgs pa{Ln, 0, n_ref, b->L.list_active, b->dev(b->ctl_plan(0)), b->dev(b->ctl_norefine()), nullptr,
+                            b->res_iters(b->d_res) + Ln, b->res_iters(b->d_res)};
+                k_batch_plan<<<(n_ref + 127) / 128, 128, 0, st>>>(pa); // sets the effective mode words of the refined lanes
+            }
             b->L.n_active = n_ref; b->L.n_refactor = 0;
             c->lanes = &b->L;
             c->xk = b->xk; c->f = b->f; c->b = b->b; c->dx = b->dx;
@@ -633,19 +718,30 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
             c->lanes = nullptr;
             c->xk = b->proto_xk; c->f = b->proto_f; c->b = b->proto_b; c->dx = b->proto_dx;
             if (rc) return bfail(b, rc, c->err);
-            BATCH_TRY(b, cudaMemcpyAsync(b->h_res, b->d_res, b->res_bytes, cudaMemcpyDeviceToHost, st));
+            BATCH_TRY(b, cudaMemcpyAsync(b->h_res + (size_t)slot * rstride, b->d_res + (size_t)slot * rstride, rstride, cudaMemcpyDeviceToHost, st));
             BATCH_TRY(b, cudaStreamSynchronize(st));
-            // lanes that were not refined keep the results of the round
-            int32_t *fl1 = reinterpret_cast<int32_t *>(b->h_res);
-            unsigned long long *var1 = reinterpret_cast<unsigned long long *>(b->h_res + sizeof(int32_t) * 4 * (size_t)Ln);
-            for (int32_t l = 0; l < Ln; ++l)
-                if (b->ctl_mode()[l] == DAECPP_B200_LANE_IDLE)
-                {
-                    for (int k = 0; k < 4; ++k) fl1[4 * l + k] = keep[4 * (size_t)l + k];
-                    var1[l] = keep_var[l];
-                }
-                else if ((fl1[4 * l] & DAECPP_B200_NOT_CONVERGED) && !(fl1[4 * l] & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED)))
+            int32_t *fls = flags_of(b->h_res, slot);
+            unsigned long long *vas = var_of(b->h_res, slot);
+            for (int32_t q = 0; q < n_ref; ++q)
+            {   // move the refined lanes' results to their own last slot
+                const int32_t l = b->ctl_list_active()[q];
+                int32_t *dstf = flags_of(b->h_res, last[l]) + 4 * l;
+                const int32_t f0 = fls[4 * l];
+                if ((f0 & DAECPP_B200_NOT_CONVERGED) && !(f0 & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED)))
                     b->refine_futile[l] = 1; // the corrected update fails the same way: the noise is not the solve's
+                if (last[l] != slot)
+                {
+                    for (int k = 0; k < 4; ++k) dstf[k] = fls[4 * l + k];
+                    var_of(b->h_res, last[l])[l] = vas[l];
+                }
+            }
+            if (slot == K - 1)
+                for (int32_t l = 0; l < Ln; ++l)
+                    if (b->ctl_mode()[l] == DAECPP_B200_LANE_IDLE)
+                    {   // lanes that were not refined keep what the round left in this slot
+                        for (int k = 0; k < 4; ++k) fls[4 * l + k] = keep_fl[4 * (size_t)l + k];
+                        vas[l] = keep_var[l];
+                    }
             b->n_refine_rounds += 1;
             b->n_refined_lanes += n_ref;
         }
@@ -657,16 +753,17 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
         if (cudaEventElapsedTime(&ms, b->ev0, b->ev1) == cudaSuccess) b->ms_device += ms;
     }
     b->rounds += 1;
-    const int32_t *fl = reinterpret_cast<const int32_t *>(b->h_res);
-    const unsigned long long *var = reinterpret_cast<const unsigned long long *>(b->h_res + sizeof(int32_t) * 4 * (size_t)Ln);
     for (int32_t l = 0; l < Ln; ++l)
     {
         daecpp_b200_lane_result &r = res[l];
-        r.flags = fl[4 * l] & (DAECPP_B200_DIVERGED | DAECPP_B200_NOT_CONVERGED);
+        const int32_t *fl = flags_of(b->h_res, last[l]) + 4 * l;
+        r.flags = fl[0] & (DAECPP_B200_DIVERGED | DAECPP_B200_NOT_CONVERGED);
         r.status = DAECPP_B200_OK;
-        if (cmd[l].mode != DAECPP_B200_LANE_IDLE && fl[4 * l + 1]) r.status = DAECPP_B200_EDECOMP;
+        r.iterations = cmd[l].mode != DAECPP_B200_LANE_IDLE ? iters[l] : 0;
+        r.reserved = 0;
+        if (cmd[l].mode != DAECPP_B200_LANE_IDLE && fl[1]) r.status = DAECPP_B200_EDECOMP;
         double v;
-        std::memcpy(&v, &var[l], sizeof(double));
+        std::memcpy(&v, &var_of(b->h_res, last[l])[l], sizeof(double));
         r.variability = v;
         if (!b->have_fn && cmd[l].mode != DAECPP_B200_LANE_IDLE) { b->rhs_loaded[l] = 0; b->jac_loaded[l] = b->jac_loaded[l] && cmd[l].mode != DAECPP_B200_LANE_REFACTOR; }
     }

@@ -138,7 +138,7 @@ template <class Eq>
 __global__ void k_rhs(const Eq *__restrict__ eq, const daecpp_b200_functor_args a)
 {
     const int lane = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
-    if (!a.lane_list && a.mode[lane] < a.min_mode) return;
+    if (a.mode[lane] < a.min_mode) return; // (also lanes that halted earlier in a multi-iteration round)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.n) return;
     const StateView x{a.x + (int64_t)lane * a.x_stride};
@@ -149,7 +149,7 @@ __global__ void k_jacobian(const Eq *__restrict__ eq, const int32_t *__restrict_
                            const int64_t nT, const daecpp_b200_functor_args a)
 {
     const int lane = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
-    if (!a.lane_list && a.mode[lane] < a.min_mode) return;
+    if (a.mode[lane] < a.min_mode) return; // (also lanes that halted earlier in a multi-iteration round)
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= nT) return;
     const SeededView x{a.x + (int64_t)lane * a.x_stride, tj[k]};
@@ -215,7 +215,7 @@ class DeviceFunctors
         for (int32_t q = 0; q < (a->lane_list ? a->n_list : a->lanes); ++q)
         {
             const int32_t lane = a->lane_list ? a->lane_list[q] : q;
-            if (!a->lane_list && a->mode[lane] < a->min_mode) continue;
+            if (a->mode[lane] < a->min_mode) continue;
             const StateView x{a->x + (int64_t)lane * a->x_stride};
             for (int32_t i = 0; i < a->n; ++i)
                 a->out[(int64_t)lane * a->out_stride + i] = self->m_eq[lane].template operator()<double>(x, a->t[lane], i);
@@ -229,7 +229,7 @@ class DeviceFunctors
         for (int32_t q = 0; q < (a->lane_list ? a->n_list : a->lanes); ++q)
         {
             const int32_t lane = a->lane_list ? a->lane_list[q] : q;
-            if (!a->lane_list && a->mode[lane] < a->min_mode) continue;
+            if (a->mode[lane] < a->min_mode) continue;
             for (int64_t k = 0; k < self->m_nT; ++k)
             {
                 const SeededView x{a->x + (int64_t)lane * a->x_stride, self->m_j[k]};

@@ -288,7 +288,7 @@ public:
     bool final_state_is_iterate() const { return m_last_was_accept; }
 
     // what this lane does in the coming round (dae-cpp/solver.hpp:431-537)
-    void plan(daecpp_b200_lane_cmd &cmd)
+    void plan(daecpp_b200_lane_cmd &cmd, int max_iterations = 1)
     {
         cmd = daecpp_b200_lane_cmd{};
         cmd.pre = m_pending_pre;
@@ -303,12 +303,25 @@ public:
         cmd.order = static_cast<int32_t>(m_order);
         cmd.t = m_t;
         for (int k = 0; k < DAECPP_MAX_ORDER; ++k) cmd.dt[k] = m_dt[k];
+        // should the driver let the lane run several iterations in one round: which of them refactorise (:533) and how
+        // many the Newton loop has left
+        cmd.period = (m_n_iter_failed < m_opt.max_Newton_failed_attempts) ? static_cast<int32_t>(m_opt.Newton_scheme + 1) : 1;
+        cmd.phase = m_iter;
+        cmd.max_iterations = std::min(max_iterations, m_max_Newton_iter - m_iter);
     }
 
     // the outcome of that round (dae-cpp/solver.hpp:541-627)
     void consume(const daecpp_b200_lane_result &res)
     {
         if (m_done) return;
+        // iterations the lane ran ahead of the last one of the round ended "not converged, not diverged"
+        for (int k = 1; k < res.iterations; ++k)
+        {
+            if (m_fact) count.n_fact_calls++;
+            count.n_lin_calls++;
+            ++m_iter;
+            m_fact = (m_n_iter_failed < m_opt.max_Newton_failed_attempts) ? !(m_iter % (m_opt.Newton_scheme + 1)) : true;
+        }
         if (m_fact) count.n_fact_calls++;
         if (res.status == DAECPP_B200_EDECOMP || res.status == DAECPP_B200_ESOLVE)
         {
@@ -421,19 +434,21 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     lockstep_stats st;
     long trace_lane = -1; // debug: DAECPP_B200_TRACE_LANE=<lane> prints that lane's rounds to stderr
     if (const char *env = std::getenv("DAECPP_B200_TRACE_LANE")) trace_lane = std::atol(env);
+    // With many lanes in flight a round is one Newton iteration (the device is busy, the host round trip is small
+    // change); when only a few stragglers are left the round trip dominates, and they run several iterations per round.
+    std::size_t in_flight = members;
+    std::size_t straggler_threshold = 64; // (DAECPP_B200_STRAGGLERS=<lanes> overrides: tests force either regime)
+    if (const char *env = std::getenv("DAECPP_B200_STRAGGLERS")) straggler_threshold = (std::size_t)std::atol(env);
     for (;;)
     {
+        const int per_round = in_flight >= straggler_threshold ? 1 : DAECPP_B200_MAX_ROUND_ITERATIONS;
         std::size_t active = 0;
         for (std::size_t m = 0; m < members; ++m)
         {
-            lanes[m].plan(cmd[m]);
-            if (cmd[m].mode != DAECPP_B200_LANE_IDLE)
-            {
-                ++active;
-                st.lane_iterations++;
-                if (cmd[m].mode == DAECPP_B200_LANE_REFACTOR) st.lane_refactorisations++;
-            }
+            lanes[m].plan(cmd[m], per_round);
+            if (cmd[m].mode != DAECPP_B200_LANE_IDLE) ++active;
         }
+        in_flight = active;
         if (!active) break;
         if ((rc = daecpp_b200_batch_round(b, cmd.data(), opt.atol, opt.rtol, opt.max_err_abs, opt.solution_variability_control ? 1 : 0,
                                           opt.variability_tolerance, res.data())))
@@ -459,7 +474,16 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
             std::fprintf(stderr, "    max|dx| = %.3e at %zu (x0 = %.3e)   max rel = %.3e at %zu (x0 = %.3e, dx = %.3e)\n", ma, ia, xa[ia], mr, ir, xa[ir], dx[ir]);
         }
         for (std::size_t m = 0; m < members; ++m)
-            if (cmd[m].mode != DAECPP_B200_LANE_IDLE) lanes[m].consume(res[m]);
+            if (cmd[m].mode != DAECPP_B200_LANE_IDLE)
+            {
+                for (int k = 0; k < res[m].iterations; ++k)
+                {
+                    const bool refac = k == 0 ? cmd[m].mode == DAECPP_B200_LANE_REFACTOR : (cmd[m].period <= 1 || (cmd[m].phase + k) % cmd[m].period == 0);
+                    st.lane_iterations++;
+                    if (refac) st.lane_refactorisations++;
+                }
+                lanes[m].consume(res[m]);
+            }
     }
     stamp("rounds");
     {   // final states: the iterate of lanes that ended on an accepted step, x[0] of the others

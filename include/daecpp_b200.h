@@ -205,18 +205,29 @@ enum /* daecpp_b200_lane_cmd.pre: applied to the lane before anything else of th
     DAECPP_B200_LANE_ACCEPT = 1,   /* x[3]<-x[2]<-x[1]<-x[0]<-xk   (solver.hpp:698-721)                    */
     DAECPP_B200_LANE_ROLLBACK = 2  /* xk = x[0]                    (solver.hpp:643,671)                    */
 };
+#define DAECPP_B200_MAX_ROUND_ITERATIONS 8
 typedef struct
 {
-    int32_t mode, pre, order, reserved;
+    int32_t mode, pre, order;
+    /* Several Newton iterations of one time step in one round (fewer host round trips when few lanes are in
+     * flight): after its first iteration the lane goes on, up to max_iterations in all (<= 1: just the one, at most
+     * DAECPP_B200_MAX_ROUND_ITERATIONS), for as long as the iteration before ended like the reference's loop
+     * continues (solver.hpp:431-627): not converged, not diverged, factorisation fine, no refinement called for.
+     * Iteration j refactorises when period <= 1 or (phase + j) % period == 0 -- phase = Newton index of the first
+     * iteration, period = Newton_scheme + 1 (solver.hpp:533) -- and reuses the factors otherwise. */
+    int32_t period;
     double t;     /* time handed to the lane's functors (solver.hpp:432: state.t after the increment)    */
     double dt[4]; /* SolverState::dt (solver.hpp:41)                                                      */
+    int32_t phase, max_iterations;
 } daecpp_b200_lane_cmd;
 typedef struct
 {
-    int32_t flags;      /* DAECPP_B200_DIVERGED | DAECPP_B200_NOT_CONVERGED of this round's iteration     */
+    int32_t flags;      /* DAECPP_B200_DIVERGED | DAECPP_B200_NOT_CONVERGED of the lane's LAST iteration of the round */
     int32_t status;     /* DAECPP_B200_OK, or DAECPP_B200_EDECOMP / DAECPP_B200_ESOLVE for this lane      */
     double variability; /* max |(x[0] - xk_new) / x[0]| over the elements the reference looks at
                            (solver.hpp:703-717), computed with the update: what accept_step would return */
+    int32_t iterations; /* Newton iterations the lane ran this round (all but the last: not converged)     */
+    int32_t reserved;
 } daecpp_b200_lane_result;
 
 /* Device functors (opt-in).  The callbacks are given DEVICE pointers and the CUDA stream

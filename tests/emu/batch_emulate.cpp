@@ -107,11 +107,15 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
                             int32_t variability_on, double var_tol, daecpp_b200_lane_result *res)
 {
     const int32_t n = b->n, L = b->lanes;
-    std::vector<int32_t> mode(L);
+    std::vector<int32_t> mode(L), running(L);
     std::vector<double> t(L);
+    int K = 1;
     for (int32_t l = 0; l < L; ++l)
     {
-        mode[l] = cmd[l].mode; t[l] = cmd[l].t;
+        t[l] = cmd[l].t;
+        running[l] = cmd[l].mode != DAECPP_B200_LANE_IDLE;
+        res[l] = daecpp_b200_lane_result{0, 0, 0.0, 0, 0};
+        if (running[l] && cmd[l].max_iterations > K) K = cmd[l].max_iterations < DAECPP_B200_MAX_ROUND_ITERATIONS ? cmd[l].max_iterations : DAECPP_B200_MAX_ROUND_ITERATIONS;
         double *xk = b->xk.data() + (size_t)l * n, *xh = b->xh.data() + (size_t)l * 4 * n;
         if (cmd[l].pre == DAECPP_B200_LANE_ACCEPT)
         {
@@ -120,56 +124,67 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
         }
         else if (cmd[l].pre == DAECPP_B200_LANE_ROLLBACK) std::memcpy(xk, xh, sizeof(double) * n);
     }
-    if (b->have_fn)
-    {   // the functor callbacks, on host pointers (dae-cpp/device-functor.hpp compiled without nvcc)
-        daecpp_b200_functor_args a{};
-        a.n = n; a.lanes = L; a.x_stride = n; a.x = b->xk.data(); a.t = t.data(); a.mode = mode.data(); a.stream = nullptr;
-        a.min_mode = DAECPP_B200_LANE_SOLVE; a.out = b->f.data(); a.out_stride = n;
-        if (b->fn.rhs(b->fn.user, &a)) return DAECPP_B200_EINVAL;
-        a.min_mode = DAECPP_B200_LANE_REFACTOR; a.out = b->JA.data(); a.out_stride = (int64_t)b->Ji.size();
-        if (b->fn.jacobian(b->fn.user, &a)) return DAECPP_B200_EINVAL;
-    }
     const int64_t nTJ = (int64_t)b->Ji.size(), nTM = (int64_t)b->Mi.size();
     std::vector<double> dxdt(n);
     std::vector<int32_t> mo(n + 1), mi(nTM ? nTM : 1);
     std::vector<double> mv(nTM ? nTM : 1);
-    for (int32_t l = 0; l < L; ++l)
-    {
-        res[l] = daecpp_b200_lane_result{0, 0, 0.0};
-        if (cmd[l].mode == DAECPP_B200_LANE_IDLE) continue;
-        double *xk = b->xk.data() + (size_t)l * n, *xh = b->xh.data() + (size_t)l * 4 * n;
-        const double alpha = oracle_time_derivative(n, cmd[l].order, cmd[l].dt, xk, xh, dxdt.data());
-        oracle_convert(n, nTM, b->MA.data() + (size_t)l * nTM, b->Mi.data(), b->Mj.data(), mo.data(), mi.data(), mv.data());
-        oracle_residual(n, mo.data(), mi.data(), mv.data(), dxdt.data(), b->f.data() + (size_t)l * n, b->b.data() + (size_t)l * n);
-        if (cmd[l].mode == DAECPP_B200_LANE_REFACTOR)
+    for (int j = 0; j < K; ++j)
+    {   // iteration j of the round: the lanes whose loop goes on (include/daecpp_b200.h: daecpp_b200_lane_cmd)
+        for (int32_t l = 0; l < L; ++l)
         {
-            b->outer[l].assign(n + 1, 0); b->inner[l].assign(nTJ + nTM + 1, 0); b->vals[l].assign(nTJ + nTM + 1, 0.0);
-            oracle_assemble_jb(n, nTJ, b->JA.data() + (size_t)l * nTJ, b->Ji.data(), b->Jj.data(), nTM, b->MA.data() + (size_t)l * nTM,
-                               b->Mi.data(), b->Mj.data(), alpha, b->outer[l].data(), b->inner[l].data(), b->vals[l].data());
+            mode[l] = DAECPP_B200_LANE_IDLE;
+            if (!running[l] || j >= (cmd[l].max_iterations > 1 ? cmd[l].max_iterations : 1)) { running[l] = 0; continue; }
+            mode[l] = j == 0 ? cmd[l].mode : ((cmd[l].period <= 1 || (cmd[l].phase + j) % cmd[l].period == 0) ? DAECPP_B200_LANE_REFACTOR : DAECPP_B200_LANE_SOLVE);
         }
-        double *dx = b->dx.data() + (size_t)l * n;
-        if (oracle_lu_solve(n, b->outer[l].data(), b->inner[l].data(), b->vals[l].data(), b->b.data() + (size_t)l * n, dx))
+        if (b->have_fn)
+        {   // the functor callbacks, on host pointers (dae-cpp/device-functor.hpp compiled without nvcc)
+            daecpp_b200_functor_args a{};
+            a.n = n; a.lanes = L; a.x_stride = n; a.x = b->xk.data(); a.t = t.data(); a.mode = mode.data(); a.stream = nullptr;
+            a.min_mode = DAECPP_B200_LANE_SOLVE; a.out = b->f.data(); a.out_stride = n;
+            if (b->fn.rhs(b->fn.user, &a)) return DAECPP_B200_EINVAL;
+            a.min_mode = DAECPP_B200_LANE_REFACTOR; a.out = b->JA.data(); a.out_stride = (int64_t)b->Ji.size();
+            if (b->fn.jacobian(b->fn.user, &a)) return DAECPP_B200_EINVAL;
+        }
+        for (int32_t l = 0; l < L; ++l)
         {
-            res[l].status = DAECPP_B200_EDECOMP;
-            continue;
-        }
-        int flags = 0;
-        double v = 0.0;
-        for (int32_t i = 0; i < n; ++i)
-        {   // dae-cpp/solver.hpp:590-619 over ALL elements (the device does not stop at the first offender) + :703-717
-            const double e = std::fabs(dx[i]), xa = std::fabs(xh[i]);
-            if (e > max_err_abs || std::isnan(dx[i])) flags |= DAECPP_B200_DIVERGED;
-            if (xa > 1e-14 && e / xa > rtol) flags |= DAECPP_B200_NOT_CONVERGED;
-            if (e > atol) flags |= DAECPP_B200_NOT_CONVERGED;
-            xk[i] += dx[i];
-            if (variability_on && xa > var_tol && std::fabs(xk[i]) > var_tol)
+            if (mode[l] == DAECPP_B200_LANE_IDLE) continue;
+            res[l].iterations += 1;
+            double *xk = b->xk.data() + (size_t)l * n, *xh = b->xh.data() + (size_t)l * 4 * n;
+            const double alpha = oracle_time_derivative(n, cmd[l].order, cmd[l].dt, xk, xh, dxdt.data());
+            oracle_convert(n, nTM, b->MA.data() + (size_t)l * nTM, b->Mi.data(), b->Mj.data(), mo.data(), mi.data(), mv.data());
+            oracle_residual(n, mo.data(), mi.data(), mv.data(), dxdt.data(), b->f.data() + (size_t)l * n, b->b.data() + (size_t)l * n);
+            if (mode[l] == DAECPP_B200_LANE_REFACTOR)
             {
-                const double rel = std::fabs((xh[i] - xk[i]) / xh[i]);
-                if (rel > v) v = rel;
+                b->outer[l].assign(n + 1, 0); b->inner[l].assign(nTJ + nTM + 1, 0); b->vals[l].assign(nTJ + nTM + 1, 0.0);
+                oracle_assemble_jb(n, nTJ, b->JA.data() + (size_t)l * nTJ, b->Ji.data(), b->Jj.data(), nTM, b->MA.data() + (size_t)l * nTM,
+                                   b->Mi.data(), b->Mj.data(), alpha, b->outer[l].data(), b->inner[l].data(), b->vals[l].data());
             }
+            double *dx = b->dx.data() + (size_t)l * n;
+            if (oracle_lu_solve(n, b->outer[l].data(), b->inner[l].data(), b->vals[l].data(), b->b.data() + (size_t)l * n, dx))
+            {
+                res[l].status = DAECPP_B200_EDECOMP;
+                running[l] = 0;
+                continue;
+            }
+            int flags = 0;
+            double v = 0.0;
+            for (int32_t i = 0; i < n; ++i)
+            {   // dae-cpp/solver.hpp:590-619 over ALL elements (the device does not stop at the first offender) + :703-717
+                const double e = std::fabs(dx[i]), xa = std::fabs(xh[i]);
+                if (e > max_err_abs || std::isnan(dx[i])) flags |= DAECPP_B200_DIVERGED;
+                if (xa > 1e-14 && e / xa > rtol) flags |= DAECPP_B200_NOT_CONVERGED;
+                if (e > atol) flags |= DAECPP_B200_NOT_CONVERGED;
+                xk[i] += dx[i];
+                if (variability_on && xa > var_tol && std::fabs(xk[i]) > var_tol)
+                {
+                    const double rel = std::fabs((xh[i] - xk[i]) / xh[i]);
+                    if (rel > v) v = rel;
+                }
+            }
+            res[l].flags = flags;
+            res[l].variability = v;
+            if (!(flags & DAECPP_B200_NOT_CONVERGED) || (flags & DAECPP_B200_DIVERGED)) running[l] = 0; // the Newton loop of this step is over
         }
-        res[l].flags = flags;
-        res[l].variability = v;
     }
     b->rounds += 1;
     return 0;

@@ -22,13 +22,26 @@ def _need(name):
     return exe
 
 
-def _run(exe, args, out, rows, n):
-    p = subprocess.run([exe] + args + [f"out={out}"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900)
+def _run(exe, args, out, rows, n, env=None):
+    p = subprocess.run([exe] + args + [f"out={out}"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900,
+                       env=dict(os.environ, **(env or {})))
     assert p.returncode == 0, p.stderr[-2000:]
     info = json.loads(p.stdout.strip().splitlines()[-1])
     data = np.fromfile(out, dtype=np.float64)
     os.remove(out)
     return info, data.reshape(rows, -1)
+
+
+@pytest.mark.parametrize("stragglers", ["0", "1000000"])  # one Newton iteration per round / up to 8 per round
+def test_multi_iteration_rounds_make_the_same_decisions(tmp_path, stragglers):
+    members, N = 4, 100
+    args = ["ensemble", f"members={members}", "first=0", f"count={members}", f"n={N}"]
+    ref_info, ref = _run(_need("traj_dump_ref"), args + ["threads=2"], str(tmp_path / "r.f64"), members, 2 * N)
+    info, got = _run(_need("ens_device_emu"), args, str(tmp_path / "e.f64"), members, 2 * N, env={"DAECPP_B200_STRAGGLERS": stragglers})
+    assert np.array_equal(got[:, :2], ref[:, :2])  # exit codes and accepted steps
+    assert info["lane_iterations"] == ref_info["rhs_calls"] and info["lane_refactorisations"] == ref_info["jac_calls"]
+    if stragglers != "0":
+        assert info["rounds"] * 3 < info["lane_iterations"] / members * 2  # several iterations per round really happened
 
 
 @pytest.mark.parametrize("variability", [0, 1])
