@@ -32,6 +32,7 @@
 #include <cmath>
 #include <cstdint>
 #include <stdexcept>
+#include <type_traits>
 #include <utility>
 #include <vector>
 
@@ -131,6 +132,22 @@ public:
     const std::vector<int32_t> &cols() const { return m_j; }
 };
 
+// Optional: a functor may also provide its Jacobian elements in closed form,
+//     template <class X> DAECPP_HD double jacobian(const X &x, const double t, const int i, const int j) const;
+// (the device twin of a hand-written JacobianMatrix functor, dae-cpp/jacobian-matrix.hpp:30-43).  When present it is
+// used for the shape's elements instead of differentiating `operator()`.
+namespace detail
+{
+template <class Eq, class = void> struct has_jacobian : std::false_type {};
+template <class Eq>
+struct has_jacobian<Eq, std::void_t<decltype(std::declval<const Eq &>().jacobian(std::declval<const StateView &>(), 0.0, 0, 0))>> : std::true_type {};
+template <class Eq> DAECPP_HD double jacobian_element(const Eq &eq, const double *x, const double t, const int32_t i, const int32_t j)
+{
+    if constexpr (has_jacobian<Eq>::value) return eq.jacobian(StateView{x}, t, i, j);
+    else return eq.template operator()<dual>(SeededView{x, j}, t, i).d;
+}
+} // namespace detail
+
 #if defined(__CUDACC__)
 namespace detail
 {
@@ -152,8 +169,7 @@ __global__ void k_jacobian(const Eq *__restrict__ eq, const int32_t *__restrict_
     if (a.mode[lane] < a.min_mode) return; // (also lanes that halted earlier in a multi-iteration round)
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= nT) return;
-    const SeededView x{a.x + (int64_t)lane * a.x_stride, tj[k]};
-    a.out[(int64_t)lane * a.out_stride + k] = eq[lane].template operator()<dual>(x, a.t[lane], ti[k]).d;
+    a.out[(int64_t)lane * a.out_stride + k] = jacobian_element(eq[lane], a.x + (int64_t)lane * a.x_stride, a.t[lane], ti[k], tj[k]);
 }
 } // namespace detail
 #endif
@@ -232,8 +248,8 @@ class DeviceFunctors
             if (a->mode[lane] < a->min_mode) continue;
             for (int64_t k = 0; k < self->m_nT; ++k)
             {
-                const SeededView x{a->x + (int64_t)lane * a->x_stride, self->m_j[k]};
-                a->out[(int64_t)lane * a->out_stride + k] = self->m_eq[lane].template operator()<dual>(x, a->t[lane], self->m_i[k]).d;
+                a->out[(int64_t)lane * a->out_stride + k] =
+                    detail::jacobian_element(self->m_eq[lane], a->x + (int64_t)lane * a->x_stride, a->t[lane], self->m_i[k], self->m_j[k]);
             }
         }
         return 0;

@@ -72,9 +72,16 @@ extern "C" int ensdev_perovskite(int64_t members, int64_t first, int64_t count, 
     state_vector x0(n, 0.0);
     for (int k = 0; k < N; ++k) x0[k] = 1.0;
     SolverOptions o;
-    o.solution_variability_control = variability != 0;
+    o.solution_variability_control = (variability & 1) != 0;
     lockstep_stats st;
-    ensemble_result R = solve_ensemble_device(eqs, problems::perovskite_shape(N), PerovskiteMass{N}, std::vector<state_vector>{x0}, t_end, o, &st);
+    ensemble_result R;
+    if (variability & 2) // shape Jacobian by dual numbers (what JacobianMatrixShape does); default: the example's closed-form Jacobian
+        R = solve_ensemble_device(eqs, problems::perovskite_shape(N), PerovskiteMass{N}, std::vector<state_vector>{x0}, t_end, o, &st);
+    else
+    {
+        std::vector<problems::PerovskiteEqAnalytic> eqa(eqs.begin(), eqs.end());
+        R = solve_ensemble_device(eqa, problems::perovskite_shape(N), PerovskiteMass{N}, std::vector<state_vector>{x0}, t_end, o, &st);
+    }
     long steps = 0;
     double checksum = 0.0;
     for (std::size_t k = 0; k < R.members.size(); ++k)
@@ -134,7 +141,13 @@ int main(int argc, char **argv)
             for (int k = 0; k < N; ++k) x0[k] = 1.0;
             SolverOptions o;
             o.solution_variability_control = arg(kv, "variability", 0) != 0;
-            R = solve_ensemble_device(eqs, problems::perovskite_shape(N), PerovskiteMass{N}, std::vector<state_vector>{x0}, arg(kv, "t_end", 10.0), o, &st);
+            if (arg(kv, "dual", 0) != 0) // shape Jacobian by dual numbers; default: the example's closed-form Jacobian
+                R = solve_ensemble_device(eqs, problems::perovskite_shape(N), PerovskiteMass{N}, std::vector<state_vector>{x0}, arg(kv, "t_end", 10.0), o, &st);
+            else
+            {
+                std::vector<problems::PerovskiteEqAnalytic> eqa(eqs.begin(), eqs.end());
+                R = solve_ensemble_device(eqa, problems::perovskite_shape(N), PerovskiteMass{N}, std::vector<state_vector>{x0}, arg(kv, "t_end", 10.0), o, &st);
+            }
         }
         else if (wl == "flame1d")
         {

@@ -33,6 +33,46 @@ struct PerovskiteEq
         return x[2 * N - 1] - t;
     }
 };
+// The same member with its Jacobian in closed form: the expressions of the example's hand-written Jacobian functor
+// (examples/perovskite_model/perovskite.cpp:132-186, restated in hostcpp/traj_dump.cpp: PerovskiteJac), so that the values
+// handed to the solver are those of the host functor bit for bit.
+struct PerovskiteEqAnalytic : PerovskiteEq
+{
+    explicit PerovskiteEqAnalytic(const PerovskiteEq &e) : PerovskiteEq(e) {}
+    template <class X>
+    DAECPP_HD double jacobian(const X &x, const double, const int r, const int c) const
+    {
+        if (r == 0)
+        {
+            const double dphi = x[N + 1] - x[N], ps = x[0] + x[1];
+            if (c == 0) return (-1.0 + 0.5 * dphi) * ih2;
+            if (c == 1) return (1.0 + 0.5 * dphi) * ih2;
+            if (c == N) return -0.5 * ps * ih2;
+            return 0.5 * ps * ih2;
+        }
+        if (r < N - 1)
+        {
+            if (c == r - 1) return (1.0 - 0.5 * (x[N + r] - x[N + r - 1])) * ih2;
+            if (c == r) return (-2.0 + 0.5 * (x[N + r + 1] - 2.0 * x[N + r] + x[N + r - 1])) * ih2;
+            if (c == r + 1) return (1.0 + 0.5 * (x[N + r + 1] - x[N + r])) * ih2;
+            if (c == N + r - 1) return 0.5 * (x[r] + x[r - 1]) * ih2;
+            if (c == N + r) return -0.5 * (x[r + 1] + 2.0 * x[r] + x[r - 1]) * ih2;
+            return 0.5 * (x[r + 1] + x[r]) * ih2;
+        }
+        if (r == N - 1)
+        {
+            const double dphi = x[2 * N - 1] - x[2 * N - 2], ps = x[N - 1] + x[N - 2];
+            if (c == r - 1) return (1.0 - 0.5 * dphi) * ih2;
+            if (c == r) return (-1.0 - 0.5 * dphi) * ih2;
+            if (c == N + r - 1) return 0.5 * ps * ih2;
+            return -0.5 * ps * ih2;
+        }
+        if (r == N || r == 2 * N - 1) return 1.0;
+        if (c == r - N) return il2;
+        if (c == r) return -2.0 * ih2;
+        return ih2;
+    }
+};
 inline daecpp::device::Shape perovskite_shape(int N)
 {
     daecpp::device::Shape s;

@@ -216,6 +216,26 @@ def test_lockstep_ensemble_members_match_reference(tmp_path, N, members):
     assert info["rounds"] < info["lane_iterations"] / 2  # the lanes really shared their rounds
 
 
+@pytest.mark.parametrize("N,members,first", [(300, 10, 0), (4000, 16, 360)])
+def test_lockstep_members_bit_identical_to_single_context_solves(tmp_path, N, members, first):
+    """Whole trajectories: every lane of the lock-step batch (device functors with the example's closed-form Jacobian,
+    -fmad=false) against the SAME member integrated alone by daecpp::solve through the overlay header -- one context,
+    host functors: accepted steps, exit code and the final state BIT FOR BIT.  Members 360..375 of the C5 sweep include
+    the one whose potential crosses zero at a grid point (the reference's relative test is on a knife edge there)."""
+    def run(exe, extra):
+        out = str(tmp_path / "o.f64")
+        p = subprocess.run([exe, "ensemble", "members=4096", f"first={first}", f"count={members}", f"n={N}", f"out={out}"] + extra,
+                           stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900)
+        assert p.returncode in (0, 1), p.stderr[-2000:]
+        data = np.fromfile(out, dtype=np.float64).reshape(members, 2 * N + 2)
+        os.remove(out)
+        return data
+    single = run(_need("traj_dump"), ["threads=4"])
+    batch = run(_need("ens_device"), [])
+    assert np.array_equal(batch[:, :2], single[:, :2])
+    assert batch[:, 2:].tobytes() == single[:, 2:].tobytes()
+
+
 def test_single_lane_device_functor_trajectory_matches_reference_golden(tmp_path):
     """C3 (flame-1D, n = 20 000) integrated entirely on the device -- RHS and shape Jacobian by device functors,
     state never on the host -- against the reference's golden trajectory."""
