@@ -470,8 +470,11 @@ def run_ensemble_device(args, env=None, emit=True):
             "gather_bytes": int(allm.numel() * 8), "state_checksum": float(allm[:, 2:].sum().item()),
             "rounds_per_step": rounds / steps, "lane_iterations_per_step": sum_over_ranks(acc["lane_iterations"]) / steps,
             "setup_ms_per_step": 1e3 * setup_s / steps,
-            "e2e": {"value": members * steps / el, "unit": "systems/s", "h2d_bytes_per_step": int(members * n * 8 + 16 * (10 * N) + 16 * N),
-                    "d2h_bytes_per_step": int(members * n * 8)},
+            "e2e": {"value": members * steps / el, "unit": "systems/s", "h2d_bytes_per_step": int(world * (n * 8 + 16 * (10 * N) + 16 * N) + members * 8 + 64 * members * rounds / steps),
+                    "d2h_bytes_per_step": int(members * n * 8 + 24 * members * rounds / steps),
+                    "bytes_note": "h2d: per GPU the shared initial state (n doubles, replicated to the lanes on the device), the Jacobian-shape and mass "
+                                  "triplets, one parameter per member, and a 64-byte lane command per member per round; d2h: the final states and a "
+                                  "24-byte lane result per member per round"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "all kernels of a Newton round (functors, residual, k_chain_factor<2,1>, k_chain_forward/backward<2,1>)",
                          "achieved": gbps, "peak": peak, "unit": "GB/s", "frac": gbps / peak, "traffic": None,

@@ -153,6 +153,18 @@ __global__ void k_batch_plan(PlanArgs a)
     if (m != DAECPP_B200_LANE_IDLE) a.iters[lane] += 1;
 }
 
+struct BroadcastArgs
+{
+    int32_t n;
+    int64_t s_vec;
+    double *x; // lane 0 holds the state, lanes 1.. receive it
+};
+__global__ void k_batch_broadcast(BroadcastArgs a)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < a.n) a.x[(int64_t)(blockIdx.y + 1) * a.s_vec + i] = a.x[i];
+}
+
 struct ResArgs
 {
     int32_t n, lanes;
@@ -379,10 +391,11 @@ int daecpp_b200_batch_set_mass_values(daecpp_b200_batch *b, const double *A, int
     if (shared) { first = 0; count = b->lanes; }
     if (b->nnzM == 0) { b->have_mass = true; return DAECPP_B200_OK; }
     // compressed-column values: per slot 0.0 + a_k1 + a_k2 + ... in input order (sparse-matrix.hpp:124-152)
-    std::vector<double> csc((size_t)count * (size_t)b->nnzM);
-    for (int32_t l = 0; l < count; ++l)
+    const int32_t host_lanes = shared ? 1 : count; // shared values travel once and are replicated on the device
+    std::vector<double> csc((size_t)host_lanes * (size_t)b->nnzM);
+    for (int32_t l = 0; l < host_lanes; ++l)
     {
-        const double *src = A + (shared ? 0 : (size_t)l * (size_t)b->nTM);
+        const double *src = A + (size_t)l * (size_t)b->nTM;
         double *dst = csc.data() + (size_t)l * (size_t)b->nnzM;
         for (int64_t s = 0; s < b->nnzM; ++s)
         {
@@ -390,13 +403,14 @@ int daecpp_b200_batch_set_mass_values(daecpp_b200_batch *b, const double *A, int
             for (int32_t p = b->m_src_ptr[s]; p < b->m_src_ptr[s + 1]; ++p) v = v + src[b->m_src[p]];
             dst[s] = v;
         }
-        if (shared && l == 0)
-        {   // every lane holds the same values: replicate the first
-            for (int32_t q = 1; q < count; ++q) std::memcpy(csc.data() + (size_t)q * (size_t)b->nnzM, dst, sizeof(double) * (size_t)b->nnzM);
-            break;
-        }
     }
     BATCH_TRY(b, cudaMemcpyAsync(b->mv.p + (size_t)first * (size_t)b->nnzM, csc.data(), sizeof(double) * csc.size(), cudaMemcpyHostToDevice, c->stream));
+    if (shared && count > 1)
+    {
+        BroadcastArgs a{(int32_t)b->nnzM, (int64_t)b->nnzM, b->mv.p};
+        k_batch_broadcast<<<dim3((unsigned)((b->nnzM + TPB - 1) / TPB), (unsigned)(count - 1)), TPB, 0, c->stream>>>(a);
+        c->kernels += 1;
+    }
     BATCH_TRY(b, cudaStreamSynchronize(c->stream));
     b->have_mass = true;
     return DAECPP_B200_OK;
@@ -489,13 +503,26 @@ int daecpp_b200_batch_set_state(daecpp_b200_batch *b, const double *x0, int32_t 
 {
     if (!b || !x0 || !lane_range_ok(b, first, count)) return DAECPP_B200_EINVAL;
     cudaSetDevice(b->device);
-    if (count == 0) return DAECPP_B200_OK;
-    int rc = copy_lanes(b, b->xk, nullptr, x0, first, count);
-    if (rc) return rc;
-    const size_t per = (size_t)b->lanes * b->ns, off = (size_t)first * b->ns, bytes = sizeof(double) * (size_t)count * b->ns;
-    BATCH_TRY(b, cudaMemcpyAsync(b->hist + off, b->xk + off, bytes, cudaMemcpyDeviceToDevice, b->c->stream));
-    for (int k = 1; k < 4; ++k) BATCH_TRY(b, cudaMemsetAsync(b->hist + (size_t)k * per + off, 0, bytes, b->c->stream));
-    BATCH_TRY(b, cudaStreamSynchronize(b->c->stream));
+    cudaStream_t st = b->c->stream;
+    const size_t per = (size_t)b->lanes * b->ns;
+    if (count == 0)
+    {   // one state shared by every lane: n doubles travel, the lanes are filled on the device
+        first = 0; count = b->lanes;
+        int rc = copy_lanes(b, b->xk, nullptr, x0, 0, 1);
+        if (rc) return rc;
+        BroadcastArgs a{b->n, (int64_t)b->ns, b->xk};
+        if (b->lanes > 1) k_batch_broadcast<<<dim3((unsigned)((b->n + TPB - 1) / TPB), (unsigned)(b->lanes - 1)), TPB, 0, st>>>(a);
+        b->c->kernels += 1;
+    }
+    else
+    {
+        int rc = copy_lanes(b, b->xk, nullptr, x0, first, count);
+        if (rc) return rc;
+    }
+    const size_t off = (size_t)first * b->ns, bytes = sizeof(double) * (size_t)count * b->ns;
+    BATCH_TRY(b, cudaMemcpyAsync(b->hist + off, b->xk + off, bytes, cudaMemcpyDeviceToDevice, st));
+    for (int k = 1; k < 4; ++k) BATCH_TRY(b, cudaMemsetAsync(b->hist + (size_t)k * per + off, 0, bytes, st));
+    BATCH_TRY(b, cudaStreamSynchronize(st));
     for (int32_t l = 0; l < count; ++l) b->hbase[(size_t)first + l] = 0;
     return DAECPP_B200_OK;
 }

@@ -30,6 +30,7 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <future>
 #include <cmath>
 #include <cstddef>
 #include <cstdio>
@@ -411,14 +412,21 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     stamp("set_pattern");
     if ((rc = daecpp_b200_batch_set_mass_values(b, M.A.data(), 0, 0))) fatal("batch_set_mass_values", rc);
     {
-        std::unique_ptr<double[]> slab(new double[members * n]);
-        for (std::size_t m = 0; m < members; ++m)
-        {
-            const state_vector &x = x0.size() == 1 ? x0[0] : x0[m];
-            ASSERT(x.size() == n, "solve_ensemble_device: initial states differ in size.");
-            std::copy(x.begin(), x.end(), slab.get() + m * n);
+        if (x0.size() == 1 && members > 1)
+        {   // every member starts from the same state: it travels once
+            if ((rc = daecpp_b200_batch_set_state(b, x0[0].data(), 0, 0))) fatal("batch_set_state", rc);
         }
-        if ((rc = daecpp_b200_batch_set_state(b, slab.get(), 0, static_cast<int32_t>(members)))) fatal("batch_set_state", rc);
+        else
+        {
+            std::unique_ptr<double[]> slab(new double[members * n]);
+            for (std::size_t m = 0; m < members; ++m)
+            {
+                const state_vector &x = x0.size() == 1 ? x0[0] : x0[m];
+                ASSERT(x.size() == n, "solve_ensemble_device: initial states differ in size.");
+                std::copy(x.begin(), x.end(), slab.get() + m * n);
+            }
+            if ((rc = daecpp_b200_batch_set_state(b, slab.get(), 0, static_cast<int32_t>(members)))) fatal("batch_set_state", rc);
+        }
     }
     stamp("set_state");
     device::DeviceFunctors<Eq> functors(eqs, shape);
@@ -487,21 +495,37 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     }
     stamp("rounds");
     {   // final states: the iterate of lanes that ended on an accepted step, x[0] of the others
-        std::unique_ptr<double[]> xk(new double[members * n]), xa; // (not value-initialised: hundreds of megabytes for big sweeps)
-        if ((rc = daecpp_b200_batch_get_vector(b, 3, xk.get(), 0, static_cast<int32_t>(members)))) fatal("batch_get_vector", rc);
-        bool need_x0 = false;
-        for (std::size_t m = 0; m < members; ++m) need_x0 = need_x0 || !lanes[m].final_state_is_iterate();
-        if (need_x0)
+        // downloaded in chunks of lanes through a few small buffers; the copy into the members' vectors (first touch of
+        // fresh pages: the slow part) runs on helper threads while the next chunk is on its way
+        constexpr int RING = 4;
+        const std::size_t chunk = std::max<std::size_t>(1, (std::size_t(4) << 20) / (n * sizeof(double)));
+        std::unique_ptr<double[]> buf[RING];
+        std::future<void> busy[RING];
+        for (auto &p : buf) p.reset(new double[2 * chunk * n]);
+        int slot = 0;
+        for (std::size_t m0 = 0; m0 < members; m0 += chunk, slot = (slot + 1) % RING)
         {
-            xa.reset(new double[members * n]);
-            if ((rc = daecpp_b200_batch_get_vector(b, 4, xa.get(), 0, static_cast<int32_t>(members)))) fatal("batch_get_vector", rc);
+            const std::size_t cnt = std::min(chunk, members - m0);
+            if (busy[slot].valid()) busy[slot].get();
+            double *xk = buf[slot].get(), *xa = xk + chunk * n;
+            if ((rc = daecpp_b200_batch_get_vector(b, 3, xk, static_cast<int32_t>(m0), static_cast<int32_t>(cnt)))) fatal("batch_get_vector", rc);
+            bool need_x0 = false;
+            for (std::size_t m = m0; m < m0 + cnt; ++m) need_x0 = need_x0 || !lanes[m].final_state_is_iterate();
+            if (need_x0 && (rc = daecpp_b200_batch_get_vector(b, 4, xa, static_cast<int32_t>(m0), static_cast<int32_t>(cnt)))) fatal("batch_get_vector", rc);
+            busy[slot] = std::async(std::launch::async, [&R, &lanes, xk, xa, m0, cnt, n] {
+                for (std::size_t m = m0; m < m0 + cnt; ++m)
+                {
+                    const double *src = (lanes[m].final_state_is_iterate() ? xk : xa) + (m - m0) * n;
+                    R.members[m].x.assign(src, src + n);
+                }
+            });
         }
+        for (auto &f : busy)
+            if (f.valid()) f.get();
         for (std::size_t m = 0; m < members; ++m)
         {
-            const double *src = (lanes[m].final_state_is_iterate() ? xk.get() : xa.get()) + m * n;
             R.members[m].status = lanes[m].status;
             R.members[m].steps = lanes[m].accepted_steps;
-            R.members[m].x.assign(src, src + n);
             if (R.members[m].status != 0) R.failed++;
         }
     }

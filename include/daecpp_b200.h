@@ -268,7 +268,8 @@ int daecpp_b200_batch_set_pattern(daecpp_b200_batch *b, const int32_t *Ji, const
 int daecpp_b200_batch_set_mass_values(daecpp_b200_batch *b, const double *A, int32_t first, int32_t count);
 int daecpp_b200_batch_set_jacobian_values(daecpp_b200_batch *b, const double *A, int32_t first, int32_t count);
 int daecpp_b200_batch_set_rhs_values(daecpp_b200_batch *b, const double *f, int32_t first, int32_t count); /* [count][n] */
-/* xk = x[0] = x0, history cleared (solver.hpp:310-313);  x0: [count][n] */
+/* xk = x[0] = x0, history cleared (solver.hpp:310-313);  x0: [count][n].  count = 0: ONE state of n values shared by
+ * all lanes (a sweep that starts every member from the same initial condition uploads it once). */
 int daecpp_b200_batch_set_state(daecpp_b200_batch *b, const double *x0, int32_t first, int32_t count);
 /* which: same selectors as daecpp_b200_get_vector (0 b, 1 dx, 3 xk, 4..7 x[0..3]); out: [count][n] */
 int daecpp_b200_batch_get_vector(daecpp_b200_batch *b, int32_t which, double *out, int32_t first, int32_t count);

@@ -77,11 +77,14 @@ int daecpp_b200_batch_set_rhs_values(daecpp_b200_batch *b, const double *f, int3
 int daecpp_b200_batch_set_state(daecpp_b200_batch *b, const double *x0, int32_t first, int32_t count)
 {
     const size_t n = b->n;
+    const bool shared = count == 0;
+    if (shared) { first = 0; count = b->lanes; }
     for (int32_t l = first; l < first + count; ++l)
     {
-        std::memcpy(b->xk.data() + l * n, x0 + (size_t)(l - first) * n, sizeof(double) * n);
+        const double *src = x0 + (shared ? 0 : (size_t)(l - first) * n);
+        std::memcpy(b->xk.data() + l * n, src, sizeof(double) * n);
         std::memset(b->xh.data() + (size_t)l * 4 * n, 0, sizeof(double) * 4 * n);
-        std::memcpy(b->xh.data() + (size_t)l * 4 * n, x0 + (size_t)(l - first) * n, sizeof(double) * n);
+        std::memcpy(b->xh.data() + (size_t)l * 4 * n, src, sizeof(double) * n);
     }
     return 0;
 }
