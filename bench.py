@@ -365,13 +365,13 @@ def _ensdev():
 
 
 ENS_STATS = ("rounds", "lane_iterations", "lane_refactorisations", "device_ms", "wall_ms", "failed", "accepted_steps", "checksum",
-             "kernels_launched", "setup_ms")
+             "kernels_launched", "setup_ms", "rounds_wall_ms", "download_ms", "destroy_ms")
 
 
 def ensemble_device_block(members, first, count, stride, N, device, out=None):
     """One lock-step integration of members first, first+stride, ... (count of them) on `device`; returns the driver's statistics."""
     os.environ["DAECPP_B200_DEVICE"] = str(device)
-    st = np.zeros(10)
+    st = np.zeros(len(ENS_STATS))
     _ensdev().ensdev_perovskite(members, first, count, stride, N, 10.0, 0, out.ctypes.data if out is not None else None, st.ctypes.data)
     return dict(zip(ENS_STATS, st.tolist()))
 
@@ -415,8 +415,8 @@ def run_ensemble_device(args, env=None, emit=True):
     count = len(range(rank, members, world))
     steps = max(1, min(args.steps, 20)) if args.steps_given else 5
     warm = max(3, min(args.warmup, 5))
-    for _ in range(warm):  # small blocks: CUDA context, module load, the allocator and the page-locked pools come up
-        ensemble_device_block(members, first, min(count, 32), stride, N, local)
+    for _ in range(warm):  # whole sweeps, like the timed ones: CUDA context, module load, the context pool and the page-locked buffers come up
+        ensemble_device_block(members, first, count, stride, N, local)
     out = np.zeros((count, n + 2))
     sampler = ClockSampler(local)
     sampler.start()
@@ -427,6 +427,7 @@ def run_ensemble_device(args, env=None, emit=True):
         st = ensemble_device_block(members, first, count, stride, N, local, out)
         for k in ENS_STATS:
             acc[k] += st[k]
+    my_wall = time.perf_counter() - t0
     barrier()
     el = max_over_ranks(time.perf_counter() - t0)
     clocks = sampler.stop()
@@ -435,6 +436,15 @@ def run_ensemble_device(args, env=None, emit=True):
     abytes = sum_over_ranks(ensemble_algorithmic_bytes(N, acc))
     launches = sum_over_ranks(acc["kernels_launched"])
     rounds = max_over_ranks(acc["rounds"])
+    # where each rank's wall clock went, per sweep [ms]: the slowest rank sets e2e
+    keys = ("setup_ms", "rounds_wall_ms", "device_ms", "download_ms", "destroy_ms", "wall_ms")
+    mine_t = torch.tensor([acc[k] / steps for k in keys] + [1e3 * my_wall / steps], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        all_t = [torch.empty_like(mine_t) for _ in range(world)]
+        dist.all_gather(all_t, mine_t)
+    else:
+        all_t = [mine_t]
+    per_rank = {k: [round(float(t[i]), 2) for t in all_t] for i, k in enumerate(keys + ("call_ms",))}
     # ---- the one collective of the path
     mine = torch.from_numpy(out).to("cuda")
     if count < per:
@@ -469,7 +479,7 @@ def run_ensemble_device(args, env=None, emit=True):
             "clocks": clocks, "failed_members": failed, "accepted_steps_total": int(allm[:, 1].sum().item()), "gather_ms": gather_ms,
             "gather_bytes": int(allm.numel() * 8), "state_checksum": float(allm[:, 2:].sum().item()),
             "rounds_per_step": rounds / steps, "lane_iterations_per_step": sum_over_ranks(acc["lane_iterations"]) / steps,
-            "setup_ms_per_step": 1e3 * setup_s / steps,
+            "setup_ms_per_step": 1e3 * setup_s / steps, "per_rank_ms_per_step": per_rank,
             "e2e": {"value": members * steps / el, "unit": "systems/s", "h2d_bytes_per_step": int(world * (n * 8 + 16 * (10 * N) + 16 * N) + members * 8 + 64 * members * rounds / steps),
                     "d2h_bytes_per_step": int(members * n * 8 + 24 * members * rounds / steps),
                     "bytes_note": "h2d: per GPU the shared initial state (n doubles, replicated to the lanes on the device), the Jacobian-shape and mass "
@@ -856,6 +866,9 @@ def run_b200_arm(args):
         except Exception as exc:
             extra["C5_ensemble_1gpu"] = {"error": repr(exc)}
         line["configs"] = extra
+        # the 1-GPU point of the 1/2/4/8-GPU ensemble curve (N > 1 runs print this metric as their `value`)
+        c5 = extra["C5_ensemble_1gpu"]
+        line["ensemble_1gpu"] = {k: c5.get(k) for k in ("metric", "value", "unit", "e2e", "error") if k in c5}
     if env.rank == 0:
         print(json.dumps(line), flush=True)
     env.close()

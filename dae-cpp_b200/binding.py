@@ -105,6 +105,8 @@ def load():
                                             C.POINTER(LaneResult)]
     lib.daecpp_b200_batch_get_stat.argtypes = [_vp, C.c_char_p, C.POINTER(C.c_double)]
     lib.daecpp_b200_variability_noalloc.argtypes = [_vp, _vp, C.c_int64, C.c_double, _vp, _vp, C.c_char_p, C.c_size_t]
+    if os.environ.get("DAECPP_B200_TEST_POOLING"):  # tests: every context of the process comes out of / goes back to the pool
+        lib.daecpp_b200_set_pooling(1)
     return lib
 
 

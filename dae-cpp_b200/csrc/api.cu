@@ -5,6 +5,8 @@
 #include <cstring>
 #include <chrono>
 #include <mutex>
+#include <unordered_map>
+#include <map>
 #include <new>
 #include <utility>
 
@@ -22,6 +24,93 @@ static std::mutex g_pool_mu;
 static bool g_pool_on = false;
 static std::vector<daecpp_b200_ctx *> g_ctx_pool;
 static std::vector<std::pair<size_t, void *>> g_host_pool;
+
+// Large device blocks (ctx.hpp: dev_alloc / dev_free).  live: every block of kCacheMin bytes or more handed out;
+// idle: freed ones waiting for a request of the same device and size.
+namespace
+{
+constexpr size_t kCacheMin = size_t(4) << 20;
+constexpr size_t kCacheMaxIdle = size_t(64) << 30; // per process; beyond it a freed block really is freed
+struct Block { int device; size_t bytes; };
+std::mutex g_dev_mu;
+// (never destroyed: a context may be released after the static destructors of this library have run)
+std::unordered_map<void *, Block> &g_dev_live = *new std::unordered_map<void *, Block>();
+std::multimap<std::pair<int, size_t>, void *> &g_dev_idle = *new std::multimap<std::pair<int, size_t>, void *>();
+size_t g_dev_idle_bytes = 0;
+} // namespace
+
+namespace daecpp_b200
+{
+cudaError_t dev_alloc(void **p, size_t bytes)
+{
+    if (bytes < kCacheMin) return cudaMalloc(p, bytes);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    {
+        std::lock_guard<std::mutex> lk(g_dev_mu);
+        auto it = g_dev_idle.find({dev, bytes});
+        if (it != g_dev_idle.end())
+        {
+            *p = it->second;
+            g_dev_idle.erase(it);
+            g_dev_idle_bytes -= bytes;
+            g_dev_live[*p] = Block{dev, bytes};
+            return cudaSuccess;
+        }
+    }
+    cudaError_t e = cudaMalloc(p, bytes);
+    if (e != cudaSuccess && g_dev_idle_bytes)
+    {   // out of memory with blocks parked: give them back and try once more
+        cudaGetLastError();
+        dev_cache_release();
+        e = cudaMalloc(p, bytes);
+    }
+    if (e == cudaSuccess)
+    {
+        std::lock_guard<std::mutex> lk(g_dev_mu);
+        g_dev_live[*p] = Block{dev, bytes};
+    }
+    return e;
+}
+
+void dev_free(void *p)
+{
+    if (!p) return;
+    {
+        std::lock_guard<std::mutex> lk(g_dev_mu);
+        auto it = g_dev_live.find(p);
+        if (it != g_dev_live.end())
+        {
+            const Block blk = it->second;
+            g_dev_live.erase(it);
+            bool keep;
+            { std::lock_guard<std::mutex> lp(g_pool_mu); keep = g_pool_on; }
+            if (keep && g_dev_idle_bytes + blk.bytes <= kCacheMaxIdle)
+            {   // cudaFree waits for the device; a parked block may be handed to another context at once, so wait here too
+                cudaDeviceSynchronize();
+                g_dev_idle.insert({{blk.device, blk.bytes}, p});
+                g_dev_idle_bytes += blk.bytes;
+                return;
+            }
+        }
+    }
+    cudaFree(p);
+}
+
+void dev_cache_release()
+{
+    std::multimap<std::pair<int, size_t>, void *> idle;
+    {
+        std::lock_guard<std::mutex> lk(g_dev_mu);
+        idle.swap(g_dev_idle);
+        g_dev_idle_bytes = 0;
+    }
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (auto &kv : idle) { cudaSetDevice(kv.first.first); cudaFree(kv.second); }
+    cudaSetDevice(cur);
+}
+} // namespace daecpp_b200
 
 namespace
 {
@@ -243,6 +332,7 @@ int daecpp_b200_set_pooling(int on)
     }
     for (daecpp_b200_ctx *c : ctxs) destroy_now(c);
     for (auto &b : bufs) cudaFreeHost(b.second);
+    if (!on) daecpp_b200::dev_cache_release();
     return DAECPP_B200_OK;
 }
 
@@ -252,7 +342,7 @@ static void destroy_now(daecpp_b200_ctx *c)
     if (c->stream) cudaStreamSynchronize(c->stream);
     tiny_release(c);
     c->M.release(); c->J.release(); c->dS.release(); c->dC.release();
-    c->m_rowptr.release(); c->m_rowslot.release(); c->m_rowcol.release();
+    c->m_rowptr.release(); c->m_rowslot.release(); c->m_rowcol.release(); c->m_dslot.release();
     c->u_outer.release(); c->u_inner.release(); c->u_J.release(); c->u_M.release(); c->u_vals.release();
     c->LU.release(); c->CB.release(); c->upd.release(); c->trace.release();
     c->keys_a.release(); c->keys_b.release(); c->pay_a.release(); c->pay_b.release(); c->scan.release(); c->cub_tmp.release();
@@ -493,7 +583,7 @@ static int enqueue_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t or
     if (pt) cudaEventRecord(c->pev[1], st);
     // diagonal mass on the chain path: b = M*dxdt - f is formed by the forward kernel while it stages its
     // right-hand side (same roundings), the residual kernel and the round trip of b through HBM go away
-    const bool fuse_res = lean && c->m_diag && c->chain_fuse_residual;
+    const bool fuse_res = lean && (c->m_diag || c->m_pdiag) && c->chain_fuse_residual;
     c->residual_was_fused = fuse_res;
     if (fuse_res) c->bdf_pending = make_bdf(c, order, w);
     else if ((rc = launch_residual(c, order, w, false))) return rc;
@@ -891,7 +981,7 @@ int daecpp_b200_get_stat(daecpp_b200_ctx *c, const char *key, double *value)
     else if (k == "ms_phase_solve") *value = c->n_phase_samples ? c->ms_phase[3] / c->n_phase_samples : 0;
     else if (k == "ms_phase_update") *value = c->n_phase_samples ? c->ms_phase[4] / c->n_phase_samples : 0;
     else if (k == "n_phase_samples") *value = c->n_phase_samples;
-    else if (k == "residual_fused") *value = (c->lean_flags && c->CH.active && c->m_diag && c->chain_fuse_residual) ? 1 : 0;
+    else if (k == "residual_fused") *value = (c->lean_flags && c->CH.active && (c->m_diag || c->m_pdiag) && c->chain_fuse_residual) ? 1 : 0;
     else if (k == "jvals_from_triplets") *value = c->jvals_from_triplets ? 1 : 0;
     else if (k == "upd_doubles") *value = (double)c->S.upd_size;
     else if (k == "n_units") *value = c->S.nunit;

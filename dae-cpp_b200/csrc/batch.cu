@@ -219,7 +219,7 @@ void release(daecpp_b200_batch *b)
         b->c->lanes = nullptr;
         daecpp_b200_destroy(b->c);
     }
-    if (b->slab) cudaFree(b->slab);
+    if (b->slab) dev_free(b->slab);
     b->jv.release(); b->mv.release(); b->refine_buf.release();
     if (b->h_ctl) cudaFreeHost(b->h_ctl);
     if (b->d_ctl) cudaFree(b->d_ctl);
@@ -290,7 +290,7 @@ int daecpp_b200_batch_create(int32_t n, int32_t lanes, int device, daecpp_b200_b
     cudaError_t e;
     b->ns = ((size_t)n + 31) / 32 * 32;
     const size_t per = (size_t)lanes * b->ns;
-    if ((e = cudaMalloc((void **)&b->slab, sizeof(double) * 8 * per)) != cudaSuccess) return bail(e, "cudaMalloc(state)");
+    if ((e = dev_alloc((void **)&b->slab, sizeof(double) * 8 * per)) != cudaSuccess) return bail(e, "cudaMalloc(state)");
     b->xk = b->slab; b->f = b->slab + per; b->b = b->slab + 2 * per; b->dx = b->slab + 3 * per; b->hist = b->slab + 4 * per;
     if ((e = cudaMemsetAsync(b->slab, 0, sizeof(double) * 8 * per, b->c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
     b->ctl_bytes = b->ctl_int_bytes() + sizeof(double) * 6 * (size_t)lanes;
@@ -629,7 +629,7 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
         b->L.var_tol = variability_tolerance;
         b->L.n_active = n_active;
         b->L.list_active = b->dev(b->ctl_list_active());
-        const bool fuse_res = c->m_diag && c->chain_fuse_residual;
+        const bool fuse_res = (c->m_diag || c->m_pdiag) && c->chain_fuse_residual;
         int rc = DAECPP_B200_OK;
         for (int j = 0; j < K && !rc; ++j)
         {
@@ -741,7 +741,7 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
             b->L.n_active = n_ref; b->L.n_refactor = 0;
             c->lanes = &b->L;
             c->xk = b->xk; c->f = b->f; c->b = b->b; c->dx = b->dx;
-            const int rc = refine_last_solve(c, 0.0, atol, rtol, max_err_abs, !(c->m_diag && c->chain_fuse_residual));
+            const int rc = refine_last_solve(c, 0.0, atol, rtol, max_err_abs, !((c->m_diag || c->m_pdiag) && c->chain_fuse_residual));
             c->lanes = nullptr;
             c->xk = b->proto_xk; c->f = b->proto_f; c->b = b->proto_b; c->dx = b->proto_dx;
             if (rc) return bfail(b, rc, c->err);

@@ -59,6 +59,7 @@ struct ChainArgs
     int32_t *dflags;
     // fused residual (diagonal mass): rhs = M*dxdt - f formed while staging (vector_ops.cu: k_residual_diag)
     int32_t fuse_res;
+    const int32_t *mslot; // partial-diagonal mass: row -> slot of M_rr or -1 (null: slot = row)
     Bdf bdf;
     const double *mdiag, *fvec;
     double *b_out; // optional copy of b to HBM
@@ -500,6 +501,7 @@ __device__ __forceinline__ void stage_rhs_residual(int t, int tile, int n, doubl
     {
         int64_t o[U];
         double xk[U], x0[U], x1[U], x2[U], x3[U], m[U], f[U];
+        int64_t ms[U];
 #pragma unroll
         for (int u = 0; u < U; ++u)
         {
@@ -509,6 +511,8 @@ __device__ __forceinline__ void stage_rhs_residual(int t, int tile, int n, doubl
             o[u] = (idx < TOTAL && k < n) ? (a.perm ? (int64_t)a.perm[k] : k) : -1;
         }
 #pragma unroll
+        for (int u = 0; u < U; ++u) ms[u] = o[u] < 0 ? -1 : (a.mslot ? (int64_t)a.mslot[o[u]] : o[u]);
+#pragma unroll
         for (int u = 0; u < U; ++u)
         {
             const bool ok = o[u] >= 0;
@@ -517,7 +521,7 @@ __device__ __forceinline__ void stage_rhs_residual(int t, int tile, int n, doubl
             x1[u] = (ok && s.order >= 2) ? s.x1[j] : 0.0;
             x2[u] = (ok && s.order >= 3) ? s.x2[j] : 0.0;
             x3[u] = (ok && s.order >= 4) ? s.x3[j] : 0.0;
-            m[u] = ok ? a.mdiag[o[u] + mb * a.s_mv] : 0.0;
+            m[u] = ms[u] >= 0 ? a.mdiag[ms[u] + mb * a.s_mv] : 0.0;
             f[u] = ok ? a.fvec[j] : 0.0;
         }
 #pragma unroll
@@ -527,7 +531,9 @@ __device__ __forceinline__ void stage_rhs_residual(int t, int tile, int n, doubl
             if (idx < TOTAL)
             {
                 const int q = idx / D::ROWS, row = idx - q * D::ROWS;
-                const double v = o[u] >= 0 ? __dsub_rn(__dadd_rn(0.0, __dmul_rn(m[u], bdf_one(s, xk[u], x0[u], x1[u], x2[u], x3[u]))), f[u]) : 0.0;
+                // (a row without a mass element: the product M*dxdt holds +0.0 there)
+                const double md = ms[u] >= 0 ? __dadd_rn(0.0, __dmul_rn(m[u], bdf_one(s, xk[u], x0[u], x1[u], x2[u], x3[u]))) : 0.0;
+                const double v = o[u] >= 0 ? __dsub_rn(md, f[u]) : 0.0;
                 R[(size_t)q * D::RP + sidx<B>(row)] = v;
                 if (a.b_out && o[u] >= 0) a.b_out[o[u] + sv] = v;
             }
@@ -1091,6 +1097,7 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         if (c->fuse_residual_now)
         {
             a.fuse_res = 1; a.bdf = c->bdf_pending; a.mdiag = c->lanes ? c->lanes->mv : c->M.vals.p; a.fvec = c->f;
+            a.mslot = c->m_pdiag ? c->m_dslot.p : nullptr;
             a.b_out = c->keep_b ? c->b : nullptr;
         }
         a.host_flags = c->publish_flags ? c->h_flags_dev + 2 : nullptr;

@@ -15,6 +15,13 @@
 namespace daecpp_b200
 {
 
+// Device memory of the library.  With pooling on (daecpp_b200_set_pooling) a freed block of 4 MB or more is kept, per
+// device and size, for the next request of that size: cudaFree of gigabytes costs tens to hundreds of milliseconds
+// (more with peer mappings in the process), and an ensemble driver builds the same buffers sweep after sweep.
+cudaError_t dev_alloc(void **p, size_t bytes);
+void dev_free(void *p);
+void dev_cache_release(); // hand every cached block back to the driver
+
 // Grow-only device buffer.
 template <class T>
 struct DevBuf
@@ -24,14 +31,14 @@ struct DevBuf
     cudaError_t reserve(size_t count)
     {
         if (count <= cap) return cudaSuccess;
-        if (p) cudaFree(p);
+        if (p) dev_free(p);
         p = nullptr; cap = 0;
         size_t want = count + count / 8 + 16;
-        cudaError_t e = cudaMalloc((void **)&p, want * sizeof(T));
+        cudaError_t e = dev_alloc((void **)&p, want * sizeof(T));
         if (e == cudaSuccess) cap = want;
         return e;
     }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    void release() { if (p) dev_free(p); p = nullptr; cap = 0; }
 };
 
 // One triplet stream (mass matrix or Jacobian) and its compressed-column form on the device.
@@ -191,6 +198,9 @@ struct daecpp_b200_ctx
     uint64_t j_csr_version = ~0ull;
     daecpp_b200::DevBuf<double> refine_r, refine_e; // residual and correction of the refinement step
     bool m_diag = false; // M is diagonal with slots in row order: index-free residual kernel
+    bool m_pdiag = false; // every stored element of M lies on the diagonal, some rows have none (a DAE's algebraic rows, or M = 0):
+                          // m_dslot[row] = slot of M_rr or -1, and the residual is still formed inside the forward kernel
+    daecpp_b200::DevBuf<int32_t> m_dslot;
 
     // union pattern of J and M = pattern of Jb
     uint64_t union_J_version = ~0ull, union_M_version = ~0ull;
@@ -276,13 +286,24 @@ struct daecpp_b200_ctx
 // (never returned through the ABI)
 #define DAECPP_B200_ABOVE_FLOOR 4
 
+namespace daecpp_b200
+{
+inline const char *base_name(const char *path)
+{
+    const char *b = path;
+    for (const char *q = path; *q; ++q)
+        if (*q == '/') b = q + 1;
+    return b;
+}
+} // namespace daecpp_b200
+
 #define DAECPP_CUDA_TRY(ctx, call)                                                                        \
     do                                                                                                    \
     {                                                                                                     \
         cudaError_t e__ = (call);                                                                         \
         if (e__ != cudaSuccess)                                                                           \
         {                                                                                                 \
-            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);                             \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__) + " (" + daecpp_b200::base_name(__FILE__) + ":" + std::to_string(__LINE__) + ")"; \
             return (e__ == cudaErrorMemoryAllocation) ? DAECPP_B200_ENOMEM : DAECPP_B200_ECUDA;           \
         }                                                                                                 \
     } while (0)

@@ -17,6 +17,7 @@
 //      or all threads depending on the level's largest front;
 //   5. factor panels are written once to HBM; only root fronts export a contribution block.
 #include "ctx.hpp"
+#include <mutex>
 #include "unit_ops.hpp"
 
 namespace daecpp_b200
@@ -419,10 +420,25 @@ int unit_setup(daecpp_b200_ctx *c)
     DAECPP_CUDA_TRY(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
     const int fs = S.factor_smem_bytes, ss = S.solve_smem_bytes;
     if (fs > 227 * 1024 || ss > 227 * 1024) { c->err = "unit exceeds shared memory"; return DAECPP_B200_ENOMEM; }
-    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_unit_factor, cudaFuncAttributeMaxDynamicSharedMemorySize, fs));
-    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_unit_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, ss));
-    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_unit_backward<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ss));
-    DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_unit_backward<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ss));
+    {   // The opt-in is a property of the FUNCTION, shared by every context of the process on this device: it only ever
+        // grows (another context with bigger units may be alive, or come back from the pool with its plan intact).
+        static std::mutex mu;
+        static int fs_max[64] = {0}, ss_max[64] = {0};
+        std::lock_guard<std::mutex> lk(mu);
+        const int d = c->device & 63;
+        if (fs > fs_max[d])
+        {
+            DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_unit_factor, cudaFuncAttributeMaxDynamicSharedMemorySize, fs));
+            fs_max[d] = fs;
+        }
+        if (ss > ss_max[d])
+        {
+            DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_unit_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, ss));
+            DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_unit_backward<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ss));
+            DAECPP_CUDA_TRY(c, cudaFuncSetAttribute(k_unit_backward<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ss));
+            ss_max[d] = ss;
+        }
+    }
     int of = 0, os = 0, ob = 0;
     DAECPP_CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&of, k_unit_factor, c->unit_threads, fs));
     DAECPP_CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&os, k_unit_forward, c->unit_threads, ss));

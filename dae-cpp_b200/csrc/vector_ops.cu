@@ -75,6 +75,19 @@ __global__ void k_check_diag(int32_t n, const int32_t *__restrict__ rowptr, cons
     if (rowptr[r] != r || rowptr[r + 1] != r + 1 || rowslot[r] != r || rowcol[r] != r) *flag = 0;
 }
 
+// partial diagonal: dslot[r] = slot of M_rr, -1 for a row without elements; *flag = 0 if a row holds anything else
+__global__ void k_diag_slots(int32_t n, const int32_t *__restrict__ rowptr, const int32_t *__restrict__ rowslot,
+                             const int32_t *__restrict__ rowcol, int32_t *__restrict__ dslot, int32_t *__restrict__ flag)
+{
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const int32_t p = rowptr[r], cnt = rowptr[r + 1] - p;
+    int32_t s = -1;
+    if (cnt == 1 && rowcol[p] == r) s = rowslot[p];
+    else if (cnt != 0) *flag = 0;
+    dslot[r] = s;
+}
+
 __global__ void k_update(int32_t n, const double *__restrict__ dx, const double *__restrict__ x0, double *__restrict__ xk,
                          double atol, double rtol, double max_err_abs, double floor, int32_t *__restrict__ flags)
 {
@@ -138,6 +151,7 @@ struct RefineArgs
     const double *jv;
     const int32_t *mrowptr, *mrowslot, *mrowcol;
     const double *mv;
+    const int32_t *mslot; // partial-diagonal mass: row -> slot of M_rr or -1 (null: slot = row)
     double alpha;
     const double *alpha_arr;
     const double *b; // the right-hand side of the solve, or null: diagonal mass, b_i = M_ii*dxdt(xk_i - dx_i) - f_i is formed again
@@ -188,7 +202,8 @@ __global__ void k_refine_residual(RefineArgs a)
         const Bdf s = refine_bdf(a, lane);
         const double xo = __dsub_rn(s.xk[i], dx[i]);
         const double x1 = s.order >= 2 ? s.x1[i] : 0.0, x2 = s.order >= 3 ? s.x2[i] : 0.0, x3 = s.order >= 4 ? s.x3[i] : 0.0;
-        acc = __dsub_rn(__dadd_rn(0.0, __dmul_rn(mv[i], bdf_one(s, xo, s.x0[i], x1, x2, x3))), a.f[off + i]);
+        const int64_t slot = a.mslot ? (int64_t)a.mslot[i] : i;
+        acc = slot >= 0 ? __dsub_rn(__dadd_rn(0.0, __dmul_rn(mv[slot], bdf_one(s, xo, s.x0[i], x1, x2, x3))), a.f[off + i]) : __dsub_rn(0.0, a.f[off + i]);
     }
     const double *jv = a.jv + (int64_t)lane * a.s_jv;
     for (int32_t p = a.jrowptr[i], e = a.jrowptr[i + 1]; p < e; ++p)
@@ -269,12 +284,19 @@ int launch_dxdt(daecpp_b200_ctx *c, int32_t order, const double coef[5])
 int classify_mass(daecpp_b200_ctx *c)
 {
     c->m_diag = false;
-    if (c->M.nnz != c->n) return DAECPP_B200_OK;
+    c->m_pdiag = false;
+    if (c->M.nnz > c->n) return DAECPP_B200_OK;
+    const bool full = c->M.nnz == c->n;
     DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 7, 0xff, sizeof(int32_t), c->stream));
-    k_check_diag<<<(c->n + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->n, c->m_rowptr.p, c->m_rowslot.p, c->m_rowcol.p, c->d_flags + 7);
+    if (full) k_check_diag<<<(c->n + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->n, c->m_rowptr.p, c->m_rowslot.p, c->m_rowcol.p, c->d_flags + 7);
+    else
+    {
+        DAECPP_CUDA_TRY(c, c->m_dslot.reserve((size_t)c->n));
+        k_diag_slots<<<(c->n + TPB - 1) / TPB, TPB, 0, c->stream>>>(c->n, c->m_rowptr.p, c->m_rowslot.p, c->m_rowcol.p, c->m_dslot.p, c->d_flags + 7);
+    }
     DAECPP_CUDA_TRY(c, cudaMemcpyAsync(c->h_flags + 7, c->d_flags + 7, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
-    c->m_diag = c->h_flags[7] != 0;
+    (full ? c->m_diag : c->m_pdiag) = c->h_flags[7] != 0;
     c->kernels += 1;
     return DAECPP_B200_OK;
 }
@@ -329,6 +351,7 @@ int refine_last_solve(daecpp_b200_ctx *c, double alpha, double atol, double rtol
     a.jrowptr = c->j_rowptr.p; a.jrowslot = c->j_rowslot.p; a.jrowcol = c->j_rowcol.p;
     a.jsrc = c->jvals_from_triplets ? c->J.src.p : nullptr;
     a.mrowptr = c->m_rowptr.p; a.mrowslot = c->m_rowslot.p; a.mrowcol = c->m_rowcol.p;
+    a.mslot = c->m_pdiag ? c->m_dslot.p : nullptr;
     a.alpha = alpha;
     a.f = c->f; a.dx_in = c->dx; a.dx = c->dx; a.xk = c->xk; a.r = r; a.e = e;
     a.b = b_is_stored ? c->b : nullptr;

@@ -361,6 +361,7 @@ struct lockstep_stats
     double kernels_launched{0.0};
     double refine_rounds{0.0}, refined_lanes{0.0}; // guarded refinement passes (include/daecpp_b200.h) and the lanes they touched
     double ms_setup{0.0}; // batch creation, pattern analysis, uploads (before the first round)
+    double ms_rounds_wall{0.0}, ms_download{0.0}, ms_destroy{0.0}; // host wall clock of the round loop, of the final-state download, of the teardown
 };
 
 /*
@@ -397,6 +398,9 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     double st_setup_ms = 0.0;
     int dev = 0;
     if (const char *env = std::getenv("DAECPP_B200_DEVICE")) dev = std::atoi(env);
+    // The batch's device memory (gigabytes) and its analysed pattern are parked at the end for the next sweep of this
+    // process instead of going through cudaFree; daecpp_b200_set_pooling(0) hands everything back.
+    daecpp_b200_set_pooling(1);
     daecpp_b200_batch *b = nullptr;
     int rc = daecpp_b200_batch_create(static_cast<int32_t>(n), static_cast<int32_t>(members), dev, &b);
     if (rc) { ERROR("daecpp_b200: cannot create the batch context (code " << rc << "): " << daecpp_b200_batch_last_error(nullptr)); }
@@ -440,6 +444,7 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     std::vector<daecpp_b200_lane_cmd> cmd(members);
     std::vector<daecpp_b200_lane_result> res(members);
     lockstep_stats st;
+    const bool trace_rounds = std::getenv("DAECPP_B200_TRACE_ROUNDS") != nullptr; // debug: lanes in flight and wall clock per round
     long trace_lane = -1; // debug: DAECPP_B200_TRACE_LANE=<lane> prints that lane's rounds to stderr
     if (const char *env = std::getenv("DAECPP_B200_TRACE_LANE")) trace_lane = std::atol(env);
     // With many lanes in flight a round is one Newton iteration (the device is busy, the host round trip is small
@@ -462,6 +467,7 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
                                           opt.variability_tolerance, res.data())))
             fatal("batch_round", rc);
         st.rounds++;
+        if (trace_rounds) std::fprintf(stderr, "round %ld: %zu lanes, %d iteration(s), done at %.3f ms\n", st.rounds, active, per_round, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count());
         if (trace_lane >= 0 && (std::size_t)trace_lane < members && cmd[trace_lane].mode != DAECPP_B200_LANE_IDLE)
             std::fprintf(stderr, "lane %ld round %ld: t=%.10g dt=%.6g order=%d mode=%d pre=%d -> flags=%d status=%d var=%.3g\n", trace_lane, st.rounds,
                          cmd[trace_lane].t, cmd[trace_lane].dt[0], cmd[trace_lane].order, cmd[trace_lane].mode, cmd[trace_lane].pre, res[trace_lane].flags,
@@ -494,6 +500,8 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
             }
     }
     stamp("rounds");
+    auto since0 = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count(); };
+    st.ms_rounds_wall = since0() - st_setup_ms;
     {   // final states: the iterate of lanes that ended on an accepted step, x[0] of the others
         // downloaded in chunks of lanes through a few small buffers; the copy into the members' vectors (first touch of
         // fresh pages: the slow part) runs on helper threads while the next chunk is on its way
@@ -535,9 +543,11 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     if (daecpp_b200_batch_get_stat(b, "refine_rounds", &v) == DAECPP_B200_OK) st.refine_rounds = v;
     if (daecpp_b200_batch_get_stat(b, "refined_lanes", &v) == DAECPP_B200_OK) st.refined_lanes = v;
     st.ms_setup = st_setup_ms;
+    st.ms_download = since0() - st_setup_ms - st.ms_rounds_wall;
     stamp("final states");
     daecpp_b200_batch_destroy(b);
     stamp("destroy");
+    st.ms_destroy = since0() - st_setup_ms - st.ms_rounds_wall - st.ms_download;
     st.ms_wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
     if (stats) *stats = st;
     return R;

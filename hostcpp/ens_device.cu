@@ -57,8 +57,8 @@ int dump(const std::map<std::string, std::string> &kv, const ensemble_result &R)
 // In-process entry for bench.py (ctypes): integrates members first, first + stride, ... (count of them) of the C5 sweep
 // (perovskite, lambda_m = 0.5 * 4^(m / (members - 1))) in lock step on the device named by DAECPP_B200_DEVICE.
 // out: [count][2N + 2] = {status, accepted steps, final state} per member (may be NULL);
-// stats[10]: {rounds, lane iterations, lane refactorisations, device ms, wall ms, failed members, accepted steps, checksum,
-//             kernels launched, setup ms}
+// stats[13]: {rounds, lane iterations, lane refactorisations, device ms, wall ms, failed members, accepted steps, checksum,
+//             kernels launched, setup ms, wall ms of the round loop, of the final-state download, of the teardown}
 extern "C" int ensdev_perovskite(int64_t members, int64_t first, int64_t count, int64_t stride, int32_t N, double t_end, int32_t variability,
                                  double *out, double *stats)
 {
@@ -101,6 +101,7 @@ extern "C" int ensdev_perovskite(int64_t members, int64_t first, int64_t count, 
         stats[0] = (double)st.rounds; stats[1] = (double)st.lane_iterations; stats[2] = (double)st.lane_refactorisations; stats[3] = st.ms_device;
         stats[4] = st.ms_wall; stats[5] = (double)R.failed; stats[6] = (double)steps; stats[7] = checksum;
         stats[8] = st.kernels_launched; stats[9] = st.ms_setup;
+        stats[10] = st.ms_rounds_wall; stats[11] = st.ms_download; stats[12] = st.ms_destroy;
     }
     return R.failed;
 }

@@ -200,4 +200,5 @@ int daecpp_b200_batch_get_stat(daecpp_b200_batch *b, const char *key, double *va
     return 0;
 }
 
+int daecpp_b200_set_pooling(int) { return 0; } // (nothing is pooled here)
 } // extern "C"

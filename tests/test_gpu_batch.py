@@ -145,7 +145,7 @@ def test_multi_iteration_round_equals_single_iteration_rounds():
     outs, stats = [], []
     for stragglers in ("0", "1000000"):
         os.environ["DAECPP_B200_STRAGGLERS"] = stragglers
-        out = np.zeros((members, 2 * N + 2)); st = np.zeros(10)
+        out = np.zeros((members, 2 * N + 2)); st = np.zeros(16)
         ens.ensdev_perovskite(members, 0, members, 1, N, 10.0, 0, out.ctypes.data, st.ctypes.data)
         outs.append(out); stats.append(st)
     os.environ.pop("DAECPP_B200_STRAGGLERS")

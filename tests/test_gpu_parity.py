@@ -334,6 +334,25 @@ def test_newton_iterations_perovskite_vs_oracle():
     c.close()
 
 
+def test_two_live_contexts_with_different_unit_sizes():
+    """The shared-memory opt-in of the unit kernels belongs to the function, not to a context (subtree.cu: unit_setup):
+    a context with small units set up while one with big units is alive must not shrink it under the other's feet."""
+    m1, m2 = 128, 64
+    J1, J2 = P.grid2d_probe_matrix(m1), P.grid2d_probe_matrix(m2)
+    c1 = B.Context(m1 * m1)
+    c1.set_mass(EMPTY); c1.set_jacobian(J1); c1.refactor(0.0)
+    c2 = B.Context(m2 * m2)
+    c2.set_option("unit_smem_bytes", 4096)
+    c2.set_mass(EMPTY); c2.set_jacobian(J2); c2.refactor(0.0)
+    c1.refactor(0.0)  # used to fail: invalid argument (dynamic shared memory above the opt-in the second context left)
+    b = np.full(m1 * m1, 1.24)
+    c1.set_rhs(b)
+    x = c1.solve()
+    eta, _ = O.backward_error(m1 * m1, O.assemble_jb(O.port, m1 * m1, J1, EMPTY, 0.0), x, b)
+    assert eta <= 1e-12
+    c1.close(); c2.close()
+
+
 @pytest.mark.parametrize("m,budget", [(33, 2048), (48, 2048), (64, 4096), (128, -1), (200, -1)])
 def test_linear_solve_blocked_big_fronts(m, budget):
     """Big fronts through the blocked multi-CTA LU (panel / trsm / gemm kernels of numeric.cu): pivot
