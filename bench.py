@@ -866,6 +866,32 @@ def run_b200_arm(args):
         except Exception as exc:
             extra["C5_ensemble_1gpu"] = {"error": repr(exc)}
         line["configs"] = extra
+        # C3 once more, end to end with DEVICE functors (dae-cpp/device-functor.hpp): the whole flame-1D integration through
+        # daecpp::solve_ensemble_device with one lane -- per Newton iteration nothing but the lane command and the flag word
+        # crosses PCIe.  us per Newton iteration = wall clock of the round loop / Newton iterations run.
+        try:
+            import ctypes as C
+            lib = _ensdev()
+            lib.ensdev_flame1d.argtypes = [C.c_int32, C.c_double, C.c_int32, C.c_void_p]
+            lib.ensdev_flame1d.restype = C.c_int
+            os.environ["DAECPP_B200_DEVICE"] = str(env.local)
+            best = None
+            for _ in range(3):  # the first pass pays module load and pool warm-up
+                st = np.zeros(len(ENS_STATS))
+                failed = lib.ensdev_flame1d(1_000_000, 50.0, 1, st.ctypes.data)
+                q = dict(zip(ENS_STATS, st.tolist()))
+                if best is None or q["rounds_wall_ms"] < best["rounds_wall_ms"]:
+                    best = q
+            line["e2e_device_functors"] = {
+                "value": 1e3 * best["rounds_wall_ms"] / best["lane_iterations"], "unit": UNIT,
+                "device_us_per_iteration": 1e3 * best["device_ms"] / best["lane_iterations"],
+                "newton_iterations": int(best["lane_iterations"]), "accepted_steps": int(best["accepted_steps"]), "failed": int(failed),
+                "rounds": int(best["rounds"]), "setup_ms": best["setup_ms"], "final_state_download_ms": best["download_ms"],
+                "whole_solve_wall_ms": best["wall_ms"], "h2d_bytes_per_step": 64, "d2h_bytes_per_step": 24,
+                "path": "daecpp::solve_ensemble_device, one lane, flame-1D n=1e6 to t=50 (hostcpp/ens_device.cu: ensdev_flame1d); "
+                        "equations and shape Jacobian (dual numbers) evaluated by kernels, state resident; best of 3 passes"}
+        except Exception as exc:
+            line["e2e_device_functors"] = {"error": repr(exc)}
         # the 1-GPU point of the 1/2/4/8-GPU ensemble curve (N > 1 runs print this metric as their `value`)
         c5 = extra["C5_ensemble_1gpu"]
         line["ensemble_1gpu"] = {k: c5.get(k) for k in ("metric", "value", "unit", "e2e", "error") if k in c5}

@@ -37,6 +37,7 @@
 #include <cstdlib>
 #include <memory>
 #include <thread>
+#include <type_traits>
 #include <utility>
 #include <vector>
 
@@ -134,8 +135,10 @@ ensemble_result solve_ensemble(std::size_t count, MemberFn member, unsigned thre
  * round -- so exit code, accepted steps and final state of a member are those of a single daecpp::solve.
  *
  * Restrictions of this path (the thread-pool solve_ensemble above has none of them): one common pattern
- * recognised as a block chain (banded systems), a mass matrix that does not change in time, no Solution
- * Manager callbacks during the integration (the final state, exit code and step count are returned).
+ * recognised as a block chain (banded systems), a mass matrix that does not change in time, and a Solution
+ * Manager that only observes: solve_ensemble_device_observed hands it the states of the output times (a lane's
+ * state is downloaded only then -- with device functors nothing else on the host needs it) and honours
+ * solver_command::stop_intergration; the two "decrease the time step" commands are not available.
  */
 namespace core
 {
@@ -162,6 +165,8 @@ class lane_control
     int m_pending_pre{DAECPP_B200_LANE_KEEP};
     bool m_done{false};
     bool m_last_was_accept{false};
+    bool m_event_accept{false}; // a step was accepted in the round just consumed, at time m_event_t
+    double m_event_t{0.0};
 
     double &dt() { return m_dt[0]; }
 
@@ -234,6 +239,8 @@ class lane_control
         accepted_steps++;
         m_pending_pre = DAECPP_B200_LANE_ACCEPT;
         m_last_was_accept = true;
+        m_event_accept = true;
+        m_event_t = m_t;
         for (int k = DAECPP_MAX_ORDER - 1; k > 0; --k) m_dt[k] = m_dt[k - 1];
         if ((m_iter >= m_dt_decrease_threshold) || (variability > m_opt.variability_threshold_high))
         {
@@ -283,6 +290,21 @@ public:
     }
 
     bool done() const { return m_done; }
+    // did the round just consumed end with an accepted step (the point where the reference calls the Solution Manager,
+    // dae-cpp/solver.hpp:659)?  Its time goes to `t`; the lane's Newton iterate is the accepted state until the next round.
+    bool take_accept(double &t)
+    {
+        const bool e = m_event_accept;
+        m_event_accept = false;
+        t = m_event_t;
+        return e;
+    }
+    // solver_command::stop_intergration from an observer (dae-cpp/solver.hpp:683-689): the member ends here, successfully
+    void stop()
+    {
+        status = exit_code::success;
+        m_done = true;
+    }
     double time() const { return m_done && !m_last_was_accept ? m_t_prev : m_t; }
     // the final state of a finished lane is its Newton iterate when the last event was an accepted step,
     // the last accepted state x[0] otherwise
@@ -361,6 +383,7 @@ struct lockstep_stats
     double kernels_launched{0.0};
     double refine_rounds{0.0}, refined_lanes{0.0}; // guarded refinement passes (include/daecpp_b200.h) and the lanes they touched
     double ms_setup{0.0}; // batch creation, pattern analysis, uploads (before the first round)
+    long observed_states{0}; // lane states downloaded for the observer (solve_ensemble_device_observed)
     double ms_rounds_wall{0.0}, ms_download{0.0}, ms_destroy{0.0}; // host wall clock of the round loop, of the final-state download, of the teardown
 };
 
@@ -371,12 +394,23 @@ struct lockstep_stats
  *   mass   -- the usual host mass-matrix functor `mass(sparse_matrix &M, double t)`; evaluated once, at t = 0
  *   x0     -- one initial state shared by all members, or one per member
  * Needs nvcc for the translation unit (the equations are instantiated as kernels).
+ *
+ * solve_ensemble_device_observed: the same with an observer `int observer(std::size_t member, const state_vector &x, double t)`
+ * called for the initial state (if 0 is an output time) and for every accepted step that lands on a time of t_output --
+ * what `daecpp::Solution(holder, t_output)` records (dae-cpp/solution-manager.hpp:175-189).  Only then is the lane's
+ * state brought to the host.  A return value of solver_command::stop_intergration ends that member.
  */
-template <class Eq, class Mass>
-ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::Shape &shape, Mass mass, const std::vector<state_vector> &x0,
-                                      const std::vector<double> &t_output, const SolverOptions &opt = SolverOptions(),
-                                      lockstep_stats *stats = nullptr)
+struct no_observer
 {
+    int operator()(std::size_t, const state_vector &, double) const { return 0; }
+};
+
+template <class Eq, class Mass, class Observer>
+ensemble_result solve_ensemble_device_observed(const std::vector<Eq> &eqs, const device::Shape &shape, Mass mass, const std::vector<state_vector> &x0,
+                                               const std::vector<double> &t_output, Observer &&observer, const SolverOptions &opt = SolverOptions(),
+                                               lockstep_stats *stats = nullptr)
+{
+    constexpr bool observe = !std::is_same<typename std::decay<Observer>::type, no_observer>::value;
     const std::size_t members = eqs.size();
     ensemble_result R;
     R.members.resize(members);
@@ -396,6 +430,7 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
         if (timing) std::fprintf(stderr, "  [solve_ensemble_device] %-18s at %8.3f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count());
     };
     double st_setup_ms = 0.0;
+    std::vector<char> initial_stop;
     int dev = 0;
     if (const char *env = std::getenv("DAECPP_B200_DEVICE")) dev = std::atoi(env);
     // The batch's device memory (gigabytes) and its analysed pattern are parked at the end for the next sweep of this
@@ -433,6 +468,10 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
         }
     }
     stamp("set_state");
+    if (observe && std::binary_search(t_out.begin(), t_out.end(), 0.0))
+    {   // the initial condition is reported first (dae-cpp/solver.hpp:358)
+        for (std::size_t m = 0; m < members; ++m) initial_stop.push_back(observer(m, x0.size() == 1 ? x0[0] : x0[m], 0.0) == 1);
+    }
     device::DeviceFunctors<Eq> functors(eqs, shape);
     daecpp_b200_device_functors fn = functors.binding();
     if ((rc = daecpp_b200_batch_set_device_functors(b, &fn))) fatal("batch_set_device_functors", rc);
@@ -441,6 +480,9 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     std::vector<core::detail::lane_control> lanes;
     lanes.reserve(members);
     for (std::size_t m = 0; m < members; ++m) lanes.emplace_back(opt, t_out);
+    for (std::size_t m = 0; m < initial_stop.size(); ++m)
+        if (initial_stop[m]) lanes[m].stop();
+    state_vector observed; // one lane's state on its way to the observer
     std::vector<daecpp_b200_lane_cmd> cmd(members);
     std::vector<daecpp_b200_lane_result> res(members);
     lockstep_stats st;
@@ -497,6 +539,17 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
                     if (refac) st.lane_refactorisations++;
                 }
                 lanes[m].consume(res[m]);
+                if (observe)
+                {
+                    double ta = 0.0;
+                    if (lanes[m].take_accept(ta) && std::binary_search(t_out.begin(), t_out.end(), ta))
+                    {   // the lane's iterate is the accepted state until its next round: the only download of this step
+                        observed.resize(n);
+                        if ((rc = daecpp_b200_batch_get_vector(b, 3, observed.data(), static_cast<int32_t>(m), 1))) fatal("batch_get_vector", rc);
+                        st.observed_states++;
+                        if (observer(m, observed, ta) == 1) lanes[m].stop();
+                    }
+                }
             }
     }
     stamp("rounds");
@@ -551,6 +604,14 @@ ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::
     st.ms_wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
     if (stats) *stats = st;
     return R;
+}
+
+template <class Eq, class Mass>
+ensemble_result solve_ensemble_device(const std::vector<Eq> &eqs, const device::Shape &shape, Mass mass, const std::vector<state_vector> &x0,
+                                      const std::vector<double> &t_output, const SolverOptions &opt = SolverOptions(),
+                                      lockstep_stats *stats = nullptr)
+{
+    return solve_ensemble_device_observed(eqs, shape, mass, x0, t_output, no_observer{}, opt, stats);
 }
 
 template <class Eq, class Mass>

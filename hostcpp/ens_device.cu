@@ -106,6 +106,34 @@ extern "C" int ensdev_perovskite(int64_t members, int64_t first, int64_t count, 
     return R.failed;
 }
 
+// In-process entry for bench.py: C3 (flame-1D, n unknowns) integrated to t_end through solve_ensemble_device with ONE lane --
+// a single system whose equations and shape Jacobian are evaluated on the device, so that no state or triplet crosses
+// PCIe per Newton iteration.  stats as in ensdev_perovskite.
+extern "C" int ensdev_flame1d(int32_t n, double t_end, int32_t variability, double *stats)
+{
+    SolverOptions o;
+    o.dt_init = t_end / 100.0;
+    o.dt_increase_threshold_delta = -2;
+    o.variability_threshold_low = 0.10;
+    o.variability_threshold_high = 0.10;
+    o.is_mass_matrix_static = true;
+    o.solution_variability_control = variability != 0;
+    lockstep_stats st;
+    std::vector<problems::Flame1DEq> eqs{problems::Flame1DEq::make(n)};
+    ensemble_result R = solve_ensemble_device(eqs, problems::flame1d_shape(n), MassMatrixIdentity((std::size_t)n),
+                                              std::vector<state_vector>{problems::flame1d_initial(n)}, t_end, o, &st);
+    double checksum = 0.0;
+    for (double v : R.members[0].x) checksum += v;
+    if (stats)
+    {
+        stats[0] = (double)st.rounds; stats[1] = (double)st.lane_iterations; stats[2] = (double)st.lane_refactorisations; stats[3] = st.ms_device;
+        stats[4] = st.ms_wall; stats[5] = (double)R.failed; stats[6] = (double)R.members[0].steps; stats[7] = checksum;
+        stats[8] = st.kernels_launched; stats[9] = st.ms_setup;
+        stats[10] = st.ms_rounds_wall; stats[11] = st.ms_download; stats[12] = st.ms_destroy;
+    }
+    return R.failed;
+}
+
 #ifndef ENSDEV_NO_MAIN
 int main(int argc, char **argv)
 {
@@ -127,6 +155,7 @@ int main(int argc, char **argv)
     lockstep_stats st;
     std::size_t n = 0, members = 1, first = 0, count = 1;
     double first_ms = 0.0;
+    long observed_total = -1;
     for (int rep = 0; rep < repeat; ++rep)
     {
         if (wl == "ensemble")
@@ -142,7 +171,32 @@ int main(int argc, char **argv)
             for (int k = 0; k < N; ++k) x0[k] = 1.0;
             SolverOptions o;
             o.solution_variability_control = arg(kv, "variability", 0) != 0;
-            if (arg(kv, "dual", 0) != 0) // shape Jacobian by dual numbers; default: the example's closed-form Jacobian
+            if (arg(kv, "outputs", 0) > 0)
+            {   // observer path: every member's state at K output times; the first member's go to observed=<file> as {t, x} rows
+                const int K = (int)arg(kv, "outputs", 0);
+                const double t_end = arg(kv, "t_end", 10.0);
+                std::vector<double> t_output;
+                for (int k = 1; k <= K; ++k) t_output.push_back(t_end * double(k) / double(K));
+                std::vector<SolutionHolder> sols(count);
+                std::vector<problems::PerovskiteEqAnalytic> eqa(eqs.begin(), eqs.end());
+                R = solve_ensemble_device_observed(eqa, problems::perovskite_shape(N), PerovskiteMass{N}, std::vector<state_vector>{x0}, t_output,
+                                                   [&](std::size_t m, const state_vector &x, double t) { sols[m].x.push_back(x); sols[m].t.push_back(t); return 0; }, o, &st);
+                observed_total = 0;
+                for (const SolutionHolder &h : sols) observed_total += (long)h.t.size();
+                auto ob = kv.find("observed");
+                if (ob != kv.end())
+                {
+                    FILE *fp = std::fopen(ob->second.c_str(), "wb");
+                    if (!fp) { std::perror("observed"); return 65; }
+                    for (std::size_t k = 0; k < sols[0].t.size(); ++k)
+                    {
+                        std::fwrite(&sols[0].t[k], sizeof(double), 1, fp);
+                        std::fwrite(sols[0].x[k].data(), sizeof(double), sols[0].x[k].size(), fp);
+                    }
+                    std::fclose(fp);
+                }
+            }
+            else if (arg(kv, "dual", 0) != 0) // shape Jacobian by dual numbers; default: the example's closed-form Jacobian
                 R = solve_ensemble_device(eqs, problems::perovskite_shape(N), PerovskiteMass{N}, std::vector<state_vector>{x0}, arg(kv, "t_end", 10.0), o, &st);
             else
             {
@@ -178,9 +232,9 @@ int main(int argc, char **argv)
     if (int rc = dump(kv, R)) return rc;
     std::printf("{\"impl\": \"%s\", \"workload\": \"%s\", \"n\": %zu, \"members\": %zu, \"first\": %zu, \"count\": %zu, \"failed\": %d, "
                 "\"steps\": %ld, \"rounds\": %ld, \"lane_iterations\": %ld, \"lane_refactorisations\": %ld, \"wall_ms\": %.3f, "
-                "\"first_wall_ms\": %.3f, \"refine_rounds\": %.0f, \"refined_lanes\": %.0f, \"device_ms\": %.3f, \"systems_per_s\": %.6f, \"status0\": %d, \"checksum\": %.17g}\n",
+                "\"first_wall_ms\": %.3f, \"refine_rounds\": %.0f, \"refined_lanes\": %.0f, \"device_ms\": %.3f, \"systems_per_s\": %.6f, \"status0\": %d, \"observed\": %ld, \"observed_downloads\": %ld, \"checksum\": %.17g}\n",
                 impl, wl.c_str(), n, members, first, count, R.failed, steps, st.rounds, st.lane_iterations, st.lane_refactorisations, st.ms_wall,
-                first_ms, st.refine_rounds, st.refined_lanes, st.ms_device, 1e3 * double(count) / st.ms_wall, R.members.empty() ? -1 : R.members[0].status, checksum);
+                first_ms, st.refine_rounds, st.refined_lanes, st.ms_device, 1e3 * double(count) / st.ms_wall, R.members.empty() ? -1 : R.members[0].status, observed_total, st.observed_states, checksum);
     return R.failed ? 1 : 0;
 }
 #endif // ENSDEV_NO_MAIN

@@ -361,6 +361,28 @@ int main(int argc, char **argv)
             jac.add_element(2 * N - 1, 2 * N - 1);
             status = solve(PerovskiteMass{p, &tally}, rhs, jac, x0, t_end, Observer{&tally}, opt);
         }
+        else if (arg(kv, "outputs", 0) > 0)
+        {   // daecpp::Solution with output times: what the lock-step driver's observer path is checked against
+            const int K = (int)arg(kv, "outputs", 0);
+            std::vector<double> t_output;
+            for (int k = 1; k <= K; ++k) t_output.push_back(t_end * double(k) / double(K));
+            SolutionHolder sol;
+            status = solve(PerovskiteMass{p, &tally}, PerovskiteRHS{p, &tally}, PerovskiteJac{p, &tally}, x0, t_output, Solution(sol, t_output), opt);
+            tally.mgr = (long)sol.t.size() + 1;
+            if (!sol.x.empty()) { tally.last = sol.x.back(); tally.t_last = sol.t.back(); }
+            auto ob = kv.find("observed");
+            if (ob != kv.end())
+            {
+                FILE *fp = std::fopen(ob->second.c_str(), "wb");
+                if (!fp) { std::perror("observed"); return 65; }
+                for (std::size_t k = 0; k < sol.t.size(); ++k)
+                {
+                    std::fwrite(&sol.t[k], sizeof(double), 1, fp);
+                    std::fwrite(sol.x[k].data(), sizeof(double), sol.x[k].size(), fp);
+                }
+                std::fclose(fp);
+            }
+        }
         else
             status = solve(PerovskiteMass{p, &tally}, PerovskiteRHS{p, &tally}, PerovskiteJac{p, &tally}, x0, t_end, Observer{&tally}, opt);
     }

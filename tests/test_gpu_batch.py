@@ -216,6 +216,29 @@ def test_lockstep_ensemble_members_match_reference(tmp_path, N, members):
     assert info["rounds"] < info["lane_iterations"] / 2  # the lanes really shared their rounds
 
 
+@pytest.mark.parametrize("N,members", [(300, 5), (4000, 6)])
+def test_observer_path_downloads_only_the_output_states(tmp_path, N, members):
+    """f3 (SURVEY.md 8f): solve_ensemble_device_observed against daecpp::Solution(holder, t_output) of the unmodified
+    reference (dae-cpp/solution-manager.hpp:175-189): the same output times bit for bit, the recorded states within
+    10x the tolerances, and exactly one lane download per recorded state."""
+    K = 5
+    def observed(exe, args):
+        path = str(tmp_path / "obs.f64")
+        p = subprocess.run([exe] + args + [f"observed={path}"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900)
+        assert p.returncode == 0, p.stderr[-2000:]
+        rows = np.fromfile(path, dtype=np.float64).reshape(-1, 2 * N + 1)
+        os.remove(path)
+        return json.loads(p.stdout.strip().splitlines()[-1]), rows
+    _, ref = observed(_need("traj_dump_ref"), ["perovskite", f"n={N}", "lambda=0.5", f"outputs={K}"])
+    info, got = observed(_need("ens_device"), ["ensemble", f"members={members}", "first=0", f"count={members}", f"n={N}", f"outputs={K}"])
+    assert info["impl"] == "b200-lockstep" and info["failed"] == 0
+    assert got.shape == ref.shape == (K, 2 * N + 1)
+    assert np.array_equal(got[:, 0], ref[:, 0])
+    err = np.abs(got[:, 1:] - ref[:, 1:])
+    assert np.all(err <= 10.0 * (1e-6 + 1e-6 * np.abs(ref[:, 1:]))), float(err.max())
+    assert info["observed"] == members * K and info["observed_downloads"] == members * K
+
+
 @pytest.mark.parametrize("N,members,first", [(300, 10, 0), (4000, 16, 360)])
 def test_lockstep_members_bit_identical_to_single_context_solves(tmp_path, N, members, first):
     """Whole trajectories: every lane of the lock-step batch (device functors with the example's closed-form Jacobian,

@@ -102,3 +102,32 @@ int main() {
         subprocess.check_call(["g++", "-std=c++17", "-O1", f"-I{ROOT}/dae-cpp_b200/overlay", f"-I{ROOT}/include", os.path.join(d, "t.cpp"), "-o", exe])
         got, want = map(float, subprocess.check_output([exe], text=True).split())
     assert abs(got - want) <= 1e-13 * abs(want)
+
+
+def _observed(exe, args, path, n, env=None):
+    p = subprocess.run([exe] + args + [f"observed={path}"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900,
+                       env=dict(os.environ, **(env or {})))
+    assert p.returncode == 0, p.stderr[-2000:]
+    info = json.loads(p.stdout.strip().splitlines()[-1])
+    rows = np.fromfile(path, dtype=np.float64).reshape(-1, n + 1)
+    os.remove(path)
+    return info, rows
+
+
+@pytest.mark.parametrize("stragglers", ["0", "1000000"])
+def test_observer_sees_the_states_of_the_output_times(tmp_path, stragglers):
+    """Observer path (solve_ensemble_device_observed; the reference: daecpp::Solution(holder, t_output),
+    dae-cpp/solution-manager.hpp:175-189, called from dae-cpp/solver.hpp:659): the same output times, in order, the
+    states within the solver tolerances, and ONE state download per recorded state -- nothing else leaves the device."""
+    N, K, members = 100, 4, 3
+    lam = 0.5  # member 0 of the sweep
+    ref_info, ref = _observed(_need("traj_dump_ref"), ["perovskite", f"n={N}", f"lambda={lam}", f"outputs={K}"], str(tmp_path / "r.f64"), 2 * N)
+    info, got = _observed(_need("ens_device_emu"), ["ensemble", f"members={members}", "first=0", f"count={members}", f"n={N}", f"outputs={K}"],
+                          str(tmp_path / "e.f64"), 2 * N, env={"DAECPP_B200_STRAGGLERS": stragglers})
+    assert info["failed"] == 0
+    assert got.shape == ref.shape == (K, 2 * N + 1)
+    assert np.array_equal(got[:, 0], ref[:, 0])                       # the output times, bit for bit
+    assert np.array_equal(got[:, 0], 10.0 * np.arange(1, K + 1) / K)
+    tol = 10 * 1e-6                                                   # SolverOptions defaults: atol = rtol = 1e-6
+    assert np.all(np.abs(got[:, 1:] - ref[:, 1:]) <= tol * (1.0 + np.abs(ref[:, 1:])))
+    assert info["observed"] == members * K and info["observed_downloads"] == members * K
