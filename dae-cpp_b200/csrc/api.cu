@@ -231,7 +231,8 @@ static void recycle(daecpp_b200_ctx *c)
     c->n_symbolic = c->n_refactor = c->n_solve = c->n_cold = c->kernels = 0;
     c->ms_symbolic = c->ms_last_refactor = c->ms_last_solve = 0;
     c->last_alpha = 0.0;
-    for (int k = 0; k < 8; ++k) { c->h_flags[k] = 0; c->h_scalars[k] = 0.0; }
+    for (int k = 0; k < 8; ++k) { c->h_flags[k] = 0; c->h_flags[8 + k] = 0; c->h_scalars[k] = 0.0; }
+    c->publish_slot = 0; c->cancel_armed = false; c->pipeline_iterations = fresh.pipeline_iterations;
 }
 
 extern "C" {
@@ -293,7 +294,7 @@ int daecpp_b200_create(int32_t n, int device, daecpp_b200_ctx **out)
     if ((e = cudaMemsetAsync(slab, 0, sizeof(double) * nv * ns, c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
     if ((e = cudaMalloc((void **)&c->d_flags, sizeof(int32_t) * 8)) != cudaSuccess) return bail(e, "cudaMalloc(flags)");
     if ((e = cudaMalloc((void **)&c->d_scalars, sizeof(double) * 8)) != cudaSuccess) return bail(e, "cudaMalloc(scalars)");
-    if ((e = cudaHostAlloc((void **)&c->h_flags, sizeof(int32_t) * 8, cudaHostAllocMapped)) != cudaSuccess) return bail(e, "cudaHostAlloc");
+    if ((e = cudaHostAlloc((void **)&c->h_flags, sizeof(int32_t) * 16, cudaHostAllocMapped)) != cudaSuccess) return bail(e, "cudaHostAlloc");
     if ((e = cudaHostGetDevicePointer((void **)&c->h_flags_dev, c->h_flags, 0)) != cudaSuccess) return bail(e, "cudaHostGetDevicePointer");
     if ((e = cudaMallocHost((void **)&c->h_scalars, sizeof(double) * 8)) != cudaSuccess) return bail(e, "cudaMallocHost");
     if ((e = cudaMemsetAsync(c->d_flags, 0, sizeof(int32_t) * 8, c->stream)) != cudaSuccess) return bail(e, "cudaMemset");
@@ -595,12 +596,14 @@ static int enqueue_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t or
     c->chain_may_defer = false;
     if (do_refactor && rc) return rc;
     if (pt) cudaEventRecord(c->pev[3], st);
+    c->forward_follows_factor = do_refactor && lean && !pt;
     c->fuse_residual_now = fuse_res;
     c->publish_flags = lean; // (a pattern change inside the refactorisation may have left the chain path: then nothing is published)
     c->flags_published = false;
     rc = numeric_solve(c, true, atol, rtol, max_err_abs);
     c->publish_flags = false;
     c->fuse_residual_now = false;
+    c->forward_follows_factor = false;
     if (rc) return rc;
     c->flags_clean = c->flags_published;
     if (pt) cudaEventRecord(c->pev[4], st);
@@ -631,13 +634,17 @@ static int refine_sync(daecpp_b200_ctx *c, double atol, double rtol, double max_
     return DAECPP_B200_OK;
 }
 
-static int finish_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t *flags, double atol, double rtol, double max_err_abs)
+static int finish_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t *flags, double atol, double rtol, double max_err_abs, int slot = 0)
 {
-    if (c->h_flags[4]) return fail(c, DAECPP_B200_ECUDA, "unit dependency wait timed out");
-    if (c->h_flags[3] == 0 && wants_refinement(c, c->h_flags[2]))
+    const volatile int32_t *hf = c->h_flags + 2 + 8 * slot; // {update flags, pivot failure, wait time-out} of this iteration
+    int32_t f2 = hf[0];
+    const int32_t f3 = hf[1], f4 = hf[2];
+    if (f4) return fail(c, DAECPP_B200_ECUDA, "unit dependency wait timed out");
+    if (f3 == 0 && wants_refinement(c, f2))
     {
         int rc = refine_sync(c, atol, rtol, max_err_abs, !c->residual_was_fused);
         if (rc) return rc;
+        f2 = c->h_flags[2];
     }
     if (c->phase_timing)
     {
@@ -649,10 +656,10 @@ static int finish_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t *fl
         }
         c->n_phase_samples += 1;
     }
-    *flags = c->h_flags[2] & (DAECPP_B200_DIVERGED | DAECPP_B200_NOT_CONVERGED);
+    *flags = f2 & (DAECPP_B200_DIVERGED | DAECPP_B200_NOT_CONVERGED);
     if (do_refactor)
     {
-        c->have_factor = c->h_flags[3] == 0;
+        c->have_factor = f3 == 0;
         if (!c->have_factor) return DAECPP_B200_EDECOMP;
     }
     return DAECPP_B200_OK;
@@ -661,18 +668,19 @@ static int finish_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t *fl
 // The host side of "flags ready".  When the iteration's last CTA published the flags to the mapped mirror
 // (chain path) the host spins on the sequence word it wrote behind them -- a few hundred nanoseconds after
 // the write instead of a driver round trip; everything else (and a long wait) synchronises the stream.
-static int wait_iteration(daecpp_b200_ctx *c)
+static int wait_iteration(daecpp_b200_ctx *c, int slot = 0, uint32_t want_seq = 0)
 {
     if (c->flags_published && c->spin_flags && !c->phase_timing)
     {
-        volatile int32_t *seq = c->h_flags + 5;
+        volatile int32_t *seq = c->h_flags + 5 + 8 * slot;
+        const int32_t want = (int32_t)(want_seq ? want_seq : c->flag_seq);
         const auto t0 = std::chrono::steady_clock::now();
-        for (uint32_t spins = 0; *seq != (int32_t)c->flag_seq; ++spins)
+        for (uint32_t spins = 0; *seq != want; ++spins)
         {
             __builtin_ia32_pause();
             if ((spins & 1023u) == 1023u && std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(500)) break;
         }
-        if (*seq == (int32_t)c->flag_seq) return DAECPP_B200_OK;
+        if (*seq == want) return DAECPP_B200_OK;
     }
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
     return DAECPP_B200_OK;
@@ -699,6 +707,9 @@ int daecpp_b200_iteration_resident(daecpp_b200_ctx *c, int32_t do_refactor, int3
     double w[5];
     int rc = prepare_iteration(c, do_refactor, order, dt, w);
     if (rc) return rc;
+    // every entry point returns with its stream work done: nothing in front of this iteration's kernels writes the matrix values
+    struct Quiescent { daecpp_b200_ctx *c; ~Quiescent() { c->values_quiescent = false; } } q{c};
+    c->values_quiescent = true;
     if ((rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs))) return rc;
     if ((rc = wait_iteration(c))) return rc;
     return finish_iteration(c, do_refactor, flags, atol, rtol, max_err_abs);
@@ -710,15 +721,78 @@ int daecpp_b200_iterations_resident(daecpp_b200_ctx *c, int32_t count, int32_t d
     if (!c || !dt || !flags || count < 1) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
     double w[5];
+    int rc = prepare_iteration(c, do_refactor, order, dt, w);
+    if (rc) return rc;
+    // Chain path: iteration k+1 is enqueued while k runs, so the device goes from one to the next without waiting for the
+    // host's spin-and-launch turn-around (its kernels start behind k's by programmatic dependent launch).  Every iteration
+    // still publishes its own flag words (two mirror slots, alternating) and the host still looks at each; where the host
+    // has to act between two iterations -- a failed pivot, a time-out, an update it would refine -- the device raises the
+    // cancel word and the queued iteration leaves without touching anything, to be enqueued again afterwards.
+    struct Quiescent { daecpp_b200_ctx *c; ~Quiescent() { c->values_quiescent = false; } } q{c};
+    c->values_quiescent = true; // (as in daecpp_b200_iteration_resident; between iterations only the iterations' own kernels run)
+    const bool pipelined = count > 1 && c->pipeline_iterations && c->lean_flags && c->CH.active && c->have_symbolic && c->spin_flags &&
+                           !c->phase_timing && !c->trace_units && !tiny_eligible(c);
+    if (!pipelined)
+    {
+        for (int32_t k = 0; k < count; ++k)
+        {
+            if (k && (rc = prepare_iteration(c, do_refactor, order, dt, w))) return rc;
+            if ((rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs))) return rc;
+            if ((rc = wait_iteration(c))) return rc;
+            if ((rc = finish_iteration(c, do_refactor, flags, atol, rtol, max_err_abs))) return rc;
+        }
+        return DAECPP_B200_OK;
+    }
+    cudaStream_t st = c->stream;
+    auto disarm = [&](int code) { c->cancel_armed = false; c->publish_slot = 0; return code; };
+    DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 5, 0, sizeof(int32_t), st));
+    c->cancel_armed = true;
+    uint32_t seq_of[2] = {0, 0};
+    bool queued = false; // iteration k is already on the stream
     for (int32_t k = 0; k < count; ++k)
     {
-        int rc = prepare_iteration(c, do_refactor, order, dt, w);
-        if (rc) return rc;
-        if ((rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs))) return rc;
-        if ((rc = wait_iteration(c))) return rc;
-        if ((rc = finish_iteration(c, do_refactor, flags, atol, rtol, max_err_abs))) return rc;
+        const int slot = k & 1;
+        if (!queued)
+        {
+            c->publish_slot = slot;
+            if ((rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs))) return disarm(rc);
+            if (!c->flags_published)
+            {   // (left the chain path: nothing was published, finish this one the plain way and go on unpipelined)
+                c->cancel_armed = false; c->publish_slot = 0;
+                if ((rc = wait_iteration(c))) return rc;
+                if ((rc = finish_iteration(c, do_refactor, flags, atol, rtol, max_err_abs))) return rc;
+                return k + 1 < count ? daecpp_b200_iterations_resident(c, count - k - 1, do_refactor, order, dt, atol, rtol, max_err_abs, flags) : DAECPP_B200_OK;
+            }
+            seq_of[slot] = c->flag_seq;
+        }
+        queued = false;
+        const double keep_counts[3] = {c->n_refactor, c->n_solve, c->kernels};
+        if (k + 1 < count)
+        {   // the next one goes behind it now
+            c->publish_slot = slot ^ 1;
+            if ((rc = enqueue_iteration(c, do_refactor, order, w, atol, rtol, max_err_abs))) return disarm(rc);
+            queued = c->flags_published;
+            seq_of[slot ^ 1] = c->flag_seq;
+            if (!queued) { DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st)); return disarm(fail(c, DAECPP_B200_EINVAL, "pattern changed inside a resident iteration block")); }
+        }
+        if ((rc = wait_iteration(c, slot, seq_of[slot]))) return disarm(rc);
+        const volatile int32_t *hf = c->h_flags + 2 + 8 * slot;
+        const bool host_turn = hf[1] || hf[2] || wants_refinement(c, hf[0]);
+        if (host_turn && queued)
+        {   // the queued iteration was cancelled on the device: let it drain, re-arm, and do what the host has to do
+            DAECPP_CUDA_TRY(c, cudaStreamSynchronize(st));
+            DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->d_flags + 5, 0, sizeof(int32_t), st));
+            c->flags_clean = true; // (k's publisher reset the words; the cancelled iteration raised none)
+            c->n_refactor = keep_counts[0]; c->n_solve = keep_counts[1]; c->kernels = keep_counts[2]; // it did not happen
+            queued = false;
+        }
+        if ((rc = finish_iteration(c, do_refactor, flags, atol, rtol, max_err_abs, slot)))
+        {
+            if (queued) cudaStreamSynchronize(st);
+            return disarm(rc);
+        }
     }
-    return DAECPP_B200_OK;
+    return disarm(DAECPP_B200_OK);
 }
 
 int daecpp_b200_set_jacobian_values(daecpp_b200_ctx *c, const double *A, int64_t nT)
@@ -1039,6 +1113,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "trace_units") c->trace_units = value != 0.0;
     else if (k == "transversal") { c->sopt.transversal = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "pivot_rel") c->pivot_rel = value;
+    else if (k == "pipeline_iterations") c->pipeline_iterations = value != 0.0;
     else if (k == "tiny") c->tiny.enabled = value != 0.0;
     else if (k == "max_super") { c->sopt.max_super = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else return fail(c, DAECPP_B200_EINVAL, "unknown option key");

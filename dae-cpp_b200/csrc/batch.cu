@@ -687,8 +687,10 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
             {
                 c->fuse_residual_now = fuse_res;
                 c->publish_flags = false;
+                c->forward_follows_factor = n_refac > 0;
                 rc = chain_solve(c, true, atol, rtol, max_err_abs);
                 c->fuse_residual_now = false;
+                c->forward_follows_factor = false;
             }
             c->lanes = nullptr;
             c->xk = b->proto_xk; c->f = b->proto_f; c->b = b->proto_b; c->dx = b->proto_dx;

@@ -59,6 +59,10 @@ struct ChainArgs
     int32_t *dflags;
     // fused residual (diagonal mass): rhs = M*dxdt - f formed while staging (vector_ops.cu: k_residual_diag)
     int32_t fuse_res;
+    int32_t *cancel;   // pipelined resident iterations: non-zero = the previous iteration ended in a way the host must look at first; every CTA of this one leaves at once
+    int32_t stage_early; // factor: the matrix values are not produced by the kernel in front: stage them before the dependency wait
+    int32_t rhs_early;   // forward: the launch in front is this iteration's factor kernel, which does not touch the right-hand side's sources
+    int32_t refine_on; // (the publisher raises `cancel` where the host would refine)
     const int32_t *mslot; // partial-diagonal mass: row -> slot of M_rr or -1 (null: slot = row)
     Bdf bdf;
     const double *mdiag, *fvec;
@@ -306,9 +310,11 @@ __device__ __forceinline__ bool stage_matrix_bulk1(int t, int tile, double *S, c
     return true;
 }
 
+// (wait_here: the caller left the dependency wait to this function -- it comes after the staging, which reads only the
+// resident matrix values and writes shared memory; returns false if the iteration turned out to be cancelled)
 template <int B, bool FIRST>
-__device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView &lv, FactorShared<B> &sh, int t, int tile,
-                                            int64_t mb, bool trigger)
+__device__ __forceinline__ bool factor_tile(const ChainArgs &a, const LevelView &lv, FactorShared<B> &sh, int t, int tile,
+                                            int64_t mb, bool trigger, bool wait_here = false)
 {
     using D = Dim<B>;
     double *Ft = lv.F + mb * a.s_F + (size_t)tile * D::TILE_F;
@@ -335,6 +341,11 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
     else
         stage_matrix_reduced<B>(t, D::T, tile, lv.rows, sh.S, lv.red_in + mb * a.s_red);
     __syncthreads();
+    if (wait_here)
+    {
+        pdl_wait();
+        if (a.cancel && *reinterpret_cast<volatile int32_t *>(a.cancel)) return false;
+    }
     stamp(a, tk, tile, 1);
     if (trigger) pdl_trigger();
     int fail = 0;
@@ -358,6 +369,7 @@ __device__ __forceinline__ void factor_tile(const ChainArgs &a, const LevelView 
     if (t == 0) factor_phase2<B>(tile, lv.ntiles, lv.is_top != 0, sh, Ft, lv.red_out + mb * a.s_red, a.tol, a.rel, fail);
     if (fail) atomicOr(&flag_words(a, mb)[3], 1);
     stamp(a, tk, tile, 4);
+    return true;
 }
 
 template <int B, bool FIRST>
@@ -373,9 +385,14 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
         a.trace[7] = a.trace[((size_t)4 * a.trace_tiles) * TRACE_SLOTS + 3];
     }
     stamp(a, FIRST ? 0 : 1, tile, 5);
-    pdl_wait();
-    if (lane_mode(a, mb) != 2) return; // this lane keeps its factors (uniform over the lane's CTAs)
-    factor_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true);
+    const bool early = FIRST && a.stage_early; // single system, values resident: the wait moves behind the staging
+    if (!early)
+    {
+        pdl_wait();
+        if (a.cancel && *reinterpret_cast<volatile int32_t *>(a.cancel)) return;
+        if (lane_mode(a, mb) != 2) return; // this lane keeps its factors (uniform over the lane's CTAs)
+    }
+    if (!factor_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true, early)) return;
     if (a.fuse_top && last_tile_done(a.counter + 2 * mb, a.lv.ntiles, t))
         factor_tile<B, false>(a, a.top, sh, t, 0, mb, false); // the grid-level reduced system, same CTA
 }
@@ -461,7 +478,14 @@ __device__ __forceinline__ void backward_tail(const ChainArgs &a, const LevelVie
         {
             if (t == 0)
             {   // published, reset for the next iteration, then the sequence number the host may spin on
-                for (int k = 0; k < 3; ++k) a.host_flags[k] = atomicExch(&a.dflags[2 + k], 0);
+                int32_t fw[3];
+                for (int k = 0; k < 3; ++k) a.host_flags[k] = fw[k] = atomicExch(&a.dflags[2 + k], 0);
+                if (a.cancel)
+                {   // the iteration queued behind this one must not run if the host has something to do first:
+                    // a failed pivot, a dependency time-out, or an update the host would refine (api.cu: wants_refinement)
+                    const bool refine = a.refine_on && (fw[0] & DAECPP_B200_NOT_CONVERGED) && !(fw[0] & (DAECPP_B200_ABOVE_FLOOR | DAECPP_B200_DIVERGED));
+                    if (fw[1] || fw[2] || refine) *a.cancel = 1;
+                }
                 __threadfence_system();
                 *reinterpret_cast<volatile int32_t *>(a.host_flags + 3) = a.seq;
             }
@@ -693,7 +717,7 @@ __device__ __noinline__ void pcr_top(int R, const double *__restrict__ red, cons
 // forward sweep of one tile; the single tile of the top level carries on into the backward sweep
 template <int B, bool FIRST>
 __device__ __forceinline__ void forward_tile(const ChainArgs &a, const LevelView &lv, SolveShared<B> &sh, int t, int tile,
-                                             int64_t mb, bool trigger)
+                                             int64_t mb, bool trigger, bool rhs_staged = false)
 {
     using D = Dim<B>;
     double *Ft = lv.F + mb * a.s_F + (size_t)tile * D::TILE_F;
@@ -701,7 +725,8 @@ __device__ __forceinline__ void forward_tile(const ChainArgs &a, const LevelView
     const int nvalid = min(D::ROWS, lv.rows - tile * D::ROWS);
     const int tk = FIRST ? 2 : 3;
     stamp(a, tk, tile, 0);
-    if (FIRST && a.fuse_res) stage_rhs_residual<B>(t, tile, a.n, sh.R, a, mb);
+    if (rhs_staged) {}
+    else if (FIRST && a.fuse_res) stage_rhs_residual<B>(t, tile, a.n, sh.R, a, mb);
     else if (FIRST) stage_rhs_first<B>(t, D::T, tile, a.n, sh.R, a.rhs + mb * a.s_vec, a.perm);
     else stage_rhs_reduced<B>(t, D::T, tile, lv.rows, sh.R, lv.rv_in + mb * a.s_rv);
     load_small_factors<B>(t, D::T, sh, Ft);
@@ -734,14 +759,24 @@ __global__ void __launch_bounds__(Cfg<B>::T, (B <= 2 ? 4 : 1)) k_chain_forward(C
     const int t = threadIdx.x, tile = blockIdx.x;
     const int64_t mb = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
     stamp(a, FIRST ? 2 : 3, tile, 5);
+    // The launch in front is this iteration's factor kernel (it passed its own dependency wait before it let this grid start):
+    // the right-hand side's sources -- iterate, history, f, mass values -- are final, only the factors are still being written
+    const bool early = FIRST && a.rhs_early && !(a.extra_factor && tile == a.lv.ntiles);
+    if (early)
+    {
+        using D = Dim<B>;
+        if (a.fuse_res) stage_rhs_residual<B>(t, tile, a.n, sh.R, a, mb);
+        else stage_rhs_first<B>(t, D::T, tile, a.n, sh.R, a.rhs + mb * a.s_vec, a.perm);
+    }
     pdl_wait();
+    if (a.cancel && *reinterpret_cast<volatile int32_t *>(a.cancel)) return;
     if (lane_mode(a, mb) == 0) return; // idle lane
     if (a.extra_factor && tile == a.lv.ntiles)
     {   // uniform over the CTA: the grid-level reduced system is factored here while the other CTAs sweep forward
         factor_tile<B, false>(a, a.top, *reinterpret_cast<FactorShared<B> *>(smem), t, 0, mb, true);
     }
     else
-        forward_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true);
+        forward_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true, early);
     if (a.fuse_top && last_tile_done(a.counter + 2 * mb + 1, a.lv.ntiles + a.extra_factor, t))
     {
         if (a.top_pcr)
@@ -794,6 +829,7 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_backward(ChainArgs a)
     }
     load_small_factors<B>(t, D::T, sh, Ft);
     pdl_wait();
+    if (a.cancel && *reinterpret_cast<volatile int32_t *>(a.cancel)) return;
     stamp(a, 4, tile, 1);
     if (t < B)
     {
@@ -932,6 +968,8 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g, bool fuse)
     if (fuse) a.top = level_view(c, g + 1);
     a.counter = reinterpret_cast<uint32_t *>(c->dC.counter.p);
     a.dflags = c->d_flags;
+    a.cancel = c->cancel_armed ? c->d_flags + 5 : nullptr;
+    a.refine_on = (c->refine_steps > 0 && !c->direct_csc && !c->refine_futile) ? 1 : 0;
     if (const LaneSet *L = c->lanes)
     {
         const Plan &P = c->CH;
@@ -1072,6 +1110,7 @@ int chain_refactor_async(daecpp_b200_ctx *c, double alpha)
         {
             a.sj = c->dC.sj.p; a.sm = c->dC.sm.p; a.flags = c->dC.flags.p; a.desc = c->dC.desc.p;
             a.jv = c->lanes ? c->lanes->jv : jv; a.mv = c->lanes ? c->lanes->mv : c->M.vals.p; a.alpha = alpha;
+            a.stage_early = (!c->lanes && c->values_quiescent && c->jvals_from_triplets) ? 1 : 0;
         }
 #define LF(B) launch_factor<B>(c, a, g == 0)
         CHAIN_DISPATCH(P.B, LF)
@@ -1094,13 +1133,14 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         a.out = c->dx; a.xk = c->xk; a.x0 = c->xh[0];
         a.atol = atol; a.rtol = rtol; a.max_err_abs = max_err_abs; a.floor = c->refine_floor;
         a.update = fuse_update ? 1 : 0;
+        a.rhs_early = c->forward_follows_factor ? 1 : 0;
         if (c->fuse_residual_now)
         {
             a.fuse_res = 1; a.bdf = c->bdf_pending; a.mdiag = c->lanes ? c->lanes->mv : c->M.vals.p; a.fvec = c->f;
             a.mslot = c->m_pdiag ? c->m_dslot.p : nullptr;
             a.b_out = c->keep_b ? c->b : nullptr;
         }
-        a.host_flags = c->publish_flags ? c->h_flags_dev + 2 : nullptr;
+        a.host_flags = c->publish_flags ? c->h_flags_dev + 2 + 8 * c->publish_slot : nullptr;
         if (a.host_flags) { c->flags_published = true; a.seq = (int32_t)++c->flag_seq; }
         if (a.host_flags && fuse_update && c->xk_host_target) { a.xk_host = c->xk_host_target; c->xk_direct_used = true; }
     };

@@ -170,6 +170,13 @@ struct daecpp_b200_ctx
     int32_t *h_flags = nullptr; // pinned mirror (mapped: the last kernel of a fused chain iteration writes it directly)
     int32_t *h_flags_dev = nullptr;
     bool lean_flags = true, publish_flags = false, flags_published = false;
+    // pipelined resident iterations (api.cu: daecpp_b200_iterations_resident): iteration k+1 is enqueued before the host has
+    // seen k's flags; the mirror has two slots ([2..5] and [10..13]) and the device cancels k+1 if k needs the host
+    bool values_quiescent = false;       // resident iterations: nothing on the stream in front of the factor kernel writes the matrix values
+    bool forward_follows_factor = false; // the forward launch being built comes right behind this iteration's factor launch
+    int publish_slot = 0;
+    bool cancel_armed = false;
+    bool pipeline_iterations = true;
     // small systems: the fused update also stores xk straight into the caller's pinned buffer (mapped), so a host
     // iteration needs neither a device-to-host copy node nor a stream synchronisation
     bool host_xk_direct = true;

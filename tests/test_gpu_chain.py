@@ -280,6 +280,62 @@ def test_iterations_resident_equals_single_iterations():
     assert all(r == res[0] for r in res[1:])
 
 
+@pytest.mark.parametrize("problem,n,count", [("flame1d", 200000, 9), ("perovskite", 8000, 6), ("flame1d", 3000, 2)])
+def test_pipelined_resident_iterations_equal_unpipelined(problem, n, count):
+    """daecpp_b200_iterations_resident enqueues iteration k+1 behind k before the host has read k's flags (api.cu): the
+    iterates, updates, flags and the refactorisation count must be those of the one-at-a-time loop, bit for bit."""
+    if problem == "flame1d":
+        x = P.flame1d_state(n); M = P.identity_mass(n); J = P.flame1d_jacobian(x); f = P.flame1d_rhs(x)
+    else:
+        N = n // 2
+        x = P.perovskite_state(N); M = P.perovskite_mass(N); J = P.perovskite_jacobian(x, N)
+        f = np.sin(np.arange(n) * 0.01) * 1e-3
+    dt4 = np.array([1e-3, 0.0, 0.0, 0.0])
+    res = []
+    for pipe in (1, 0):
+        for refactor in (1, 0):
+            c = B.Context(n)
+            c.set_option("pipeline_iterations", pipe)
+            c.set_state(x); c.set_mass(M); c.set_jacobian(J)
+            c.residual(f, 1, dt4)
+            rc0, _ = c.iteration_resident(1, 1, dt4, 1e-6, 1e-6)  # factors for the refactor = 0 variant
+            rc, flags = c.iterations_resident(count, refactor, 1, dt4, 1e-6, 1e-6)
+            res.append((refactor, rc0, rc, flags, c.stat("n_refactor"), c.get_vector("xk").tobytes(), c.get_vector("dx").tobytes()))
+            c.close()
+    assert res[0] == res[2] and res[1] == res[3]
+    assert res[0][4] == count + 1 and res[1][4] == 1
+
+
+def test_pipelined_resident_iterations_stop_where_the_host_must_act():
+    """A factorisation that fails inside a pipelined block: the iteration queued behind it is cancelled on the device, the
+    call returns EDECOMP and leaves the iterate exactly where the one-at-a-time loop leaves it."""
+    n = 50000
+    x = P.flame1d_state(n)
+    A, i, j = P.flame1d_jacobian(x)
+    M = P.identity_mass(n)
+    dt4 = np.array([1e-3, 0.0, 0.0, 0.0])
+    res = []
+    for pipe in (1, 0):
+        c = B.Context(n)
+        c.set_option("pipeline_iterations", pipe)
+        c.set_state(x); c.set_mass(M); c.set_jacobian((A, i, j))
+        c.residual(P.flame1d_rhs(x), 1, dt4)
+        rc, flags = c.iterations_resident(3, 1, 1, dt4, 1e-6, 1e-6)
+        assert rc == 0
+        bad = A.copy()
+        bad[(i == j)] = 1.0 / dt4[0]  # J_ii = alpha * M_ii: the diagonal of Jb = J - alpha*M cancels, the off-diagonals stay
+        bad[(i != j)] = 0.0           # ... and with them gone Jb = 0
+        c.set_jacobian_values_raw(np.ascontiguousarray(bad), len(bad))
+        rc, flags = c.iterations_resident(5, 1, 1, dt4, 1e-6, 1e-6, allow=(B.EDECOMP,))
+        res.append((rc, c.stat("n_refactor"), c.get_vector("xk").tobytes()))
+        c.set_jacobian_values_raw(np.ascontiguousarray(A), len(A))      # and the context is usable again afterwards
+        rc2, _ = c.iterations_resident(2, 1, 1, dt4, 1e-6, 1e-6)
+        res[-1] += (rc2, c.get_vector("xk").tobytes())
+        c.close()
+    assert res[0][0] == B.EDECOMP
+    assert res[0] == res[1]
+
+
 @pytest.mark.parametrize("problem,n", [("flame1d", 30001), ("perovskite", 8000)])
 def test_iteration_host_direct_xk_store(problem, n):
     """Small systems: xk reaches the caller's pinned buffer by stores of the backward kernel (no copy node,
