@@ -11,12 +11,17 @@ lib = B.load(); c = B.Context(w["n"], 0, lib)
 c.set_state(w["x0"]); c.set_mass(w["M"]); c.set_jacobian(w["J"])
 alpha = c.residual(w["f"], w["order"], w["dt"]); c.refactor(alpha); c.solve_update(1e-6, 1e-6)
 # usage: chain_trace.py [key=value ...]   (daecpp_b200_set_option before the first iteration)
+# usage: chain_trace.py [block=K] [key=value ...]   block=K: the traced iterations run as one daecpp_b200_iterations_resident(K) (pipelined)
+block = 0
 for kv in sys.argv[1:]:
     k, v = kv.split("=", 1)
-    c.set_option(k, float(v))
+    if k == "block": block = int(v)
+    else: c.set_option(k, float(v))
 for _ in range(5): c.iteration_resident(1, w["order"], w["dt"], 1e-6, 1e-6)
 c.set_option("trace_units", 1)
-for _ in range(3): c.iteration_resident(1, w["order"], w["dt"], 1e-6, 1e-6)
+if block: c.iterations_resident(block, 1, w["order"], w["dt"], 1e-6, 1e-6)
+else:
+    for _ in range(3): c.iteration_resident(1, w["order"], w["dt"], 1e-6, 1e-6)
 tr = c.unit_trace().astype(np.int64).ravel()
 nt = int(c.stat("chain_tiles"))
 tr = tr.reshape(5, nt, 8)
