@@ -731,18 +731,18 @@ def single_system_line(args, env, workload, size, steps, warmup, want_cpu, want_
     # DRAM traffic of the refactorisation kernels from the committed `ncu --set full` capture of this
     # very command (profiles/: dram__bytes_read.sum + dram__bytes_write.sum, MB per launch), C3 only
     traffic = None
-    cap = os.path.join(ROOT, "profiles", "r01_v10_ncu_full_chain_kernels.csv")
+    cap = os.path.join(ROOT, "profiles", "r02_ncu_full_c3_chain_kernels.csv")  # rows: kernel, metric, value, unit (one launch)
     if workload == "flame1d" and n == 1_000_000 and os.path.exists(cap):
         import csv
-        rows = list(csv.reader(open(cap)))
-        hd = rows[0]
-        kn, rd, wr = hd.index("Kernel Name"), hd.index("dram__bytes_read.sum"), hd.index("dram__bytes_write.sum")
-        mb = [float(r[rd]) + float(r[wr]) for r in rows[2:] if "k_chain_factor<1, 1>" in r[kn]]
-        if mb:
-            traffic = {"bytes_per_launch": sum(mb) / len(mb) * 1e6, "launches_averaged": len(mb), "source": os.path.relpath(cap, ROOT),
-                       "note": "tile-level factor kernel (the 489-row top level is factored by one extra CTA of the forward launch); "
-                               "the 40 MB of factor stores stay in the 126 MB write-back L2 and are re-read from there by the forward "
-                               "sweep, so DRAM traffic is below the algorithmic bytes"}
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        got = {}
+        for kernel, metric, value, unit in list(csv.reader(open(cap)))[1:]:
+            if "k_chain_factor<1, 1>" in kernel and metric in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                got[metric] = float(value) * scale[unit]
+        if len(got) == 2:
+            traffic = {"bytes_per_launch": sum(got.values()), "launches_averaged": 1, "source": os.path.relpath(cap, ROOT),
+                       "note": "tile-level factor kernel; the 40 MB of factor stores stay in the 126 MB write-back L2 and are re-read from "
+                               "there by the forward sweep, so DRAM traffic is below the algorithmic bytes"}
     roofline = None
     if "GBps" in phases["refactor"]:
         a = phases["refactor"]["GBps"]

@@ -592,7 +592,9 @@ static int enqueue_iteration(daecpp_b200_ctx *c, int32_t do_refactor, int32_t or
     // the solve follows on the same stream and the flags are read once at the end: a two-level chain
     // may leave its (tiny) top-level factorisation to an extra CTA of the forward launch
     c->chain_may_defer = true;
+    c->rhs_prefetch_hint = fuse_res && !pt;
     if (do_refactor) rc = numeric_refactor_async(c, w[0], false);
+    c->rhs_prefetch_hint = false;
     c->chain_may_defer = false;
     if (do_refactor && rc) return rc;
     if (pt) cudaEventRecord(c->pev[3], st);
@@ -731,7 +733,7 @@ int daecpp_b200_iterations_resident(daecpp_b200_ctx *c, int32_t count, int32_t d
     struct Quiescent { daecpp_b200_ctx *c; ~Quiescent() { c->values_quiescent = false; } } q{c};
     c->values_quiescent = true; // (as in daecpp_b200_iteration_resident; between iterations only the iterations' own kernels run)
     const bool pipelined = count > 1 && c->pipeline_iterations && c->lean_flags && c->CH.active && c->have_symbolic && c->spin_flags &&
-                           !c->phase_timing && !c->trace_units && !tiny_eligible(c);
+                           !c->phase_timing && !tiny_eligible(c);
     if (!pipelined)
     {
         for (int32_t k = 0; k < count; ++k)

@@ -60,6 +60,7 @@ struct ChainArgs
     // fused residual (diagonal mass): rhs = M*dxdt - f formed while staging (vector_ops.cu: k_residual_diag)
     int32_t fuse_res;
     int32_t *cancel;   // pipelined resident iterations: non-zero = the previous iteration ended in a way the host must look at first; every CTA of this one leaves at once
+    int32_t pf_rhs;      // factor: pull the sources of the coming forward sweep's right-hand side (a.bdf, a.fvec, a.mdiag) into L2
     int32_t stage_early; // factor: the matrix values are not produced by the kernel in front: stage them before the dependency wait
     int32_t rhs_early;   // forward: the launch in front is this iteration's factor kernel, which does not touch the right-hand side's sources
     int32_t refine_on; // (the publisher raises `cancel` where the host would refine)
@@ -385,6 +386,21 @@ __global__ void __launch_bounds__(Cfg<B>::T) k_chain_factor(ChainArgs a)
         a.trace[7] = a.trace[((size_t)4 * a.trace_tiles) * TRACE_SLOTS + 3];
     }
     stamp(a, FIRST ? 0 : 1, tile, 5);
+    if (FIRST && a.pf_rhs)
+    {   // the forward sweep that follows forms b = M*dxdt - f for these rows: by then its CTAs find the operands in L2
+        // instead of waiting for DRAM with nothing else to do (prefetches neither read nor order anything)
+        using D = Dim<B>;
+        const int64_t k0 = (int64_t)tile * D::ROWS * B;
+        const int bytes = (int)(min((int64_t)D::ROWS * B, (int64_t)a.n - k0) * sizeof(double));
+        const char *src[6] = {reinterpret_cast<const char *>(a.fvec + k0), reinterpret_cast<const char *>(a.bdf.x0 + k0),
+                              reinterpret_cast<const char *>(a.mdiag + k0), a.bdf.order >= 2 ? reinterpret_cast<const char *>(a.bdf.x1 + k0) : nullptr,
+                              a.bdf.order >= 3 ? reinterpret_cast<const char *>(a.bdf.x2 + k0) : nullptr,
+                              a.bdf.order >= 4 ? reinterpret_cast<const char *>(a.bdf.x3 + k0) : nullptr};
+#pragma unroll
+        for (int v = 0; v < 6; ++v)
+            if (src[v])
+                for (int off = t * 128; off < bytes; off += Cfg<B>::T * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(src[v] + off));
+    }
     const bool early = FIRST && a.stage_early; // single system, values resident: the wait moves behind the staging
     if (!early)
     {
@@ -1111,6 +1127,10 @@ int chain_refactor_async(daecpp_b200_ctx *c, double alpha)
             a.sj = c->dC.sj.p; a.sm = c->dC.sm.p; a.flags = c->dC.flags.p; a.desc = c->dC.desc.p;
             a.jv = c->lanes ? c->lanes->jv : jv; a.mv = c->lanes ? c->lanes->mv : c->M.vals.p; a.alpha = alpha;
             a.stage_early = (!c->lanes && c->values_quiescent && c->jvals_from_triplets) ? 1 : 0;
+            if (!c->lanes && c->rhs_prefetch_hint && P.identity_perm && c->m_diag)
+            {   // (single system, natural order, full diagonal mass: the rows of a tile are one contiguous range of every source)
+                a.pf_rhs = 1; a.bdf = c->bdf_pending; a.fvec = c->f; a.mdiag = c->M.vals.p;
+            }
         }
 #define LF(B) launch_factor<B>(c, a, g == 0)
         CHAIN_DISPATCH(P.B, LF)

@@ -173,6 +173,7 @@ struct daecpp_b200_ctx
     // pipelined resident iterations (api.cu: daecpp_b200_iterations_resident): iteration k+1 is enqueued before the host has
     // seen k's flags; the mirror has two slots ([2..5] and [10..13]) and the device cancels k+1 if k needs the host
     bool values_quiescent = false;       // resident iterations: nothing on the stream in front of the factor kernel writes the matrix values
+    bool rhs_prefetch_hint = false;      // the fused residual of this iteration will be formed by the forward launch: bdf_pending is set
     bool forward_follows_factor = false; // the forward launch being built comes right behind this iteration's factor launch
     int publish_slot = 0;
     bool cancel_armed = false;
