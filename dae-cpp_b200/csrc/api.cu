@@ -213,26 +213,33 @@ int download_vector(daecpp_b200_ctx *c, double *dst_host, const double *src)
 // owner's uploads exactly like between two calls of one owner.
 static void recycle(daecpp_b200_ctx *c)
 {
-    const daecpp_b200_ctx fresh;
+    const daecpp_b200_options fresh;
+    daecpp_b200_options &o = *c;
+    // a plan built under other plan-affecting options is not this owner's plan
+    if (o.chain_enabled != fresh.chain_enabled || o.chain_min_n != fresh.chain_min_n || o.chain_max_b != fresh.chain_max_b ||
+        o.chain_affine != fresh.chain_affine || o.unit_threads != fresh.unit_threads || o.sopt.leaf_size != fresh.sopt.leaf_size ||
+        o.sopt.unit_smem_bytes != fresh.sopt.unit_smem_bytes || o.sopt.serial_dim != fresh.sopt.serial_dim ||
+        o.sopt.max_super != fresh.sopt.max_super || o.sopt.transversal != fresh.sopt.transversal)
+        c->have_symbolic = false;
+    o = fresh; // every option back to its default, whatever is added to daecpp_b200_options later
+    const daecpp_b200::TinyState tiny_fresh;
+    c->tiny.enabled = tiny_fresh.enabled; c->tiny.have_factor = false; c->tiny.spec_valid = false; c->tiny.var_tol = tiny_fresh.var_tol;
     c->err.clear();
     c->have_factor = false;
     c->direct_csc = false;
-    c->tiny.enabled = fresh.tiny.enabled; c->tiny.have_factor = false; c->tiny.spec_valid = false; c->tiny.var_tol = fresh.tiny.var_tol;
     c->M.vals_valid = false; c->J.vals_valid = false;
-    if (c->chain_enabled != fresh.chain_enabled || c->chain_min_n != fresh.chain_min_n || c->chain_max_b != fresh.chain_max_b ||
-        c->chain_affine != fresh.chain_affine || c->unit_threads != fresh.unit_threads || c->sopt.leaf_size != fresh.sopt.leaf_size ||
-        c->sopt.unit_smem_bytes != fresh.sopt.unit_smem_bytes || c->sopt.serial_dim != fresh.sopt.serial_dim ||
-        c->sopt.max_super != fresh.sopt.max_super)
-        c->have_symbolic = false;
-    c->chain_enabled = fresh.chain_enabled; c->chain_min_n = fresh.chain_min_n; c->chain_max_b = fresh.chain_max_b;
-    c->chain_affine = fresh.chain_affine; c->chain_packed = fresh.chain_packed; c->lean_flags = fresh.lean_flags; c->spin_flags = fresh.spin_flags; c->host_xk_direct = fresh.host_xk_direct; c->host_xk_direct_max_n = fresh.host_xk_direct_max_n; c->xk_host_target = nullptr; c->xk_direct_used = false; c->publish_flags = false; c->flags_clean = false; c->chain_fuse_residual = fresh.chain_fuse_residual; c->keep_b = fresh.keep_b; c->fuse_residual_now = false; c->chain_prefetch = fresh.chain_prefetch; c->chain_fuse_top = fresh.chain_fuse_top; c->chain_defer_top = fresh.chain_defer_top; c->chain_top_pcr = fresh.chain_top_pcr; c->chain_top_mode = 0; c->chain_may_defer = false; c->chain_top_pending = false; c->unit_threads = fresh.unit_threads; c->sopt = fresh.sopt;
-    c->refine_steps = fresh.refine_steps; c->refine_floor = fresh.refine_floor; c->n_refine = 0; c->assemble_only = false; c->pinned_io = false; c->pivot_tol = 0.0;
-    c->phase_timing = false; c->trace_units = false; c->blocked_lu = fresh.blocked_lu; c->blocked_lu_min_dim = fresh.blocked_lu_min_dim;
+    // transient state of the iteration protocol
+    c->xk_host_target = nullptr; c->xk_direct_used = false; c->publish_flags = false; c->flags_published = false; c->flags_clean = false;
+    c->fuse_residual_now = false; c->residual_was_fused = false; c->forward_follows_factor = false; c->rhs_prefetch_hint = false;
+    c->values_quiescent = false; c->publish_slot = 0; c->cancel_armed = false;
+    c->chain_top_mode = 0; c->chain_may_defer = false; c->chain_top_pending = false;
+    c->refine_futile = false; c->n_refine = 0; c->alpha_hint = 0.0; c->last_alpha = 0.0;
+    // statistics
     c->n_symbolic = c->n_refactor = c->n_solve = c->n_cold = c->kernels = 0;
     c->ms_symbolic = c->ms_last_refactor = c->ms_last_solve = 0;
-    c->last_alpha = 0.0;
+    for (int k = 0; k < 5; ++k) c->ms_phase[k] = 0;
+    c->n_phase_samples = 0;
     for (int k = 0; k < 8; ++k) { c->h_flags[k] = 0; c->h_flags[8 + k] = 0; c->h_scalars[k] = 0.0; }
-    c->publish_slot = 0; c->cancel_armed = false; c->pipeline_iterations = fresh.pipeline_iterations;
 }
 
 extern "C" {

@@ -156,7 +156,54 @@ struct GroupLaunch
 
 } // namespace daecpp_b200
 
-struct daecpp_b200_ctx
+// Everything daecpp_b200_set_option can change, with its default.  A pooled context handed to a new owner gets a fresh
+// copy (api.cu: recycle), so an option added here cannot leak from one owner to the next.
+struct daecpp_b200_options
+{
+    // plan-affecting (a change invalidates the symbolic analysis)
+    daecpp_b200::SymbolicOptions sopt;
+    int unit_threads = 256;
+    bool chain_enabled = true, chain_affine = true;
+    int chain_min_n = 256, chain_max_b = 3;
+    // chain path
+    bool lean_flags = true;            // flag words published to a mapped host mirror by the CTA that finishes the iteration
+    bool spin_flags = true;            // resident iteration: spin on that word instead of cudaStreamSynchronize
+    bool pipeline_iterations = true;   // daecpp_b200_iterations_resident: iteration k+1 enqueued while k runs
+    bool host_xk_direct = true;        // small systems: the fused update stores xk straight into the caller's pinned buffer
+    int64_t host_xk_direct_max_n = 131072;
+    bool chain_fuse_residual = true;   // (partial) diagonal mass: b = M*dxdt - f is formed while the forward kernel stages its right-hand side
+    bool keep_b = false;               // fused residual: also write b to HBM (get_vector(b) after a fused iteration)
+    int chain_prefetch = 0;            // backward kernel: L2 prefetch of the tile's factors before the dependency wait
+    int chain_packed = 2;              // staging of affine tiles (chain.cu): 2 = one bulk copy per thread chunk where the tile qualifies,
+                                       // 1 = contiguous-run LDGSTS, 0 = per-field strided copies
+    bool chain_defer_top = true;       // two-level chains inside a fused iteration: the top level is factored by one
+                                       // extra CTA of the forward launch, concurrently with the tiles' forward sweeps
+    bool chain_top_pcr = true;         // ... or solved by parallel cyclic reduction with no top-level factors at all (chain.cu: pcr_top)
+    int chain_fuse_top = 2;            // bit 0: factor, bit 1: solve (top level swept by the last CTA of the level-0 launch)
+    // general multifrontal path
+    bool blocked_lu = true;            // big fronts: blocked multi-CTA LU (numeric.cu) instead of one CTA per front
+    int blocked_lu_min_dim = 96;       // level groups whose largest front is at least this order
+    bool bf_pdl = true;                // big fronts: panel / trailing-update launches chained by programmatic dependent launch
+    bool bf_dmma = true;               // big fronts: trailing update on the FP64 tensor cores (mma.m8n8k4.f64), 0 = FP64 FMA tiles
+    bool bf_fused_panel = true;        // big fronts: panel in one launch (numeric.cu: k_bf_panel), 0 = diag / rows / trsm launches
+    // numerics
+    // Guarded iterative refinement (one step of r = b - Jb*dx, Jb*e = r, dx += e): taken only when the Newton update
+    // failed the convergence test on elements whose |dx| is below refine_floor, i.e. where the outcome of the
+    // reference's relative test (solver.hpp:603-609) hangs on the componentwise accuracy of the linear solve
+    int refine_steps = 1;
+    double refine_floor = 1e-11;
+    double pivot_tol = 0.0;
+    // chain path: a pivot below pivot_rel x (largest entry of its own matrix row) has lost every significant digit
+    // to cancellation and is reported like a zero pivot (Eigen would have pivoted away from it)
+    double pivot_rel = 1e-14;
+    // hand-off / debugging
+    bool assemble_only = false;
+    bool pinned_io = false;            // host vectors handed to the ABI are page-locked: no staging copies
+    bool phase_timing = false;         // per-phase device times of iteration_resident
+    bool trace_units = false;          // debug: per-unit globaltimer stamps of the factor kernel
+};
+
+struct daecpp_b200_ctx : daecpp_b200_options
 {
     int32_t n = 0;
     int device = 0;
@@ -169,7 +216,7 @@ struct daecpp_b200_ctx
     int32_t *d_flags = nullptr; // [8] device flag words
     int32_t *h_flags = nullptr; // pinned mirror (mapped: the last kernel of a fused chain iteration writes it directly)
     int32_t *h_flags_dev = nullptr;
-    bool lean_flags = true, publish_flags = false, flags_published = false;
+    bool publish_flags = false, flags_published = false;
     // pipelined resident iterations (api.cu: daecpp_b200_iterations_resident): iteration k+1 is enqueued before the host has
     // seen k's flags; the mirror has two slots ([2..5] and [10..13]) and the device cancels k+1 if k needs the host
     bool values_quiescent = false;       // resident iterations: nothing on the stream in front of the factor kernel writes the matrix values
@@ -177,21 +224,15 @@ struct daecpp_b200_ctx
     bool forward_follows_factor = false; // the forward launch being built comes right behind this iteration's factor launch
     int publish_slot = 0;
     bool cancel_armed = false;
-    bool pipeline_iterations = true;
     // small systems: the fused update also stores xk straight into the caller's pinned buffer (mapped), so a host
     // iteration needs neither a device-to-host copy node nor a stream synchronisation
-    bool host_xk_direct = true;
-    int64_t host_xk_direct_max_n = 131072;
     const double *xk_host_cached = nullptr;
     double *xk_host_dev_cached = nullptr, *xk_host_target = nullptr;
     bool xk_direct_used = false;
     uint32_t flag_seq = 0;             // sequence number written behind the published flags (h_flags[5])
-    bool spin_flags = true;            // resident iteration: spin on that word instead of cudaStreamSynchronize
     bool flags_clean = false;          // d_flags[2..4] are zero (the publishing CTA of a fused chain iteration resets them)
-    bool chain_fuse_residual = true;   // diagonal mass: b = M*dxdt - f is formed while the forward kernel stages its right-hand side
     bool residual_was_fused = false;   // the last fused iteration formed b inside the forward kernel (b is not in HBM)
     bool fuse_residual_now = false;    // set by the fused iteration for the solve that follows
-    bool keep_b = false;               // fused residual: also write b to HBM (get_vector(b) after a fused iteration)
     daecpp_b200::Bdf bdf_pending{};
     double *d_scalars = nullptr, *h_scalars = nullptr; // [8]
     double *h_stage = nullptr;  // pinned staging for n doubles
@@ -219,7 +260,6 @@ struct daecpp_b200_ctx
 
     // symbolic + numeric factor
     bool have_symbolic = false, have_factor = false;
-    daecpp_b200::SymbolicOptions sopt;
     daecpp_b200::Symbolic S;
     daecpp_b200::DeviceSymbolic dS;
     std::vector<daecpp_b200::GroupLaunch> groups;
@@ -229,54 +269,27 @@ struct daecpp_b200_ctx
     daecpp_b200::DeviceChain dC;
     const daecpp_b200::LaneSet *lanes = nullptr; // set by a batch context around its launches (batch.cu)
     daecpp_b200::TinyState tiny;
-    bool chain_enabled = true, chain_affine = true;
-    int chain_prefetch = 0;            // backward kernel: L2 prefetch of the tile's factors before the dependency wait
-    int chain_packed = 2;              // staging of affine tiles (chain.cu): 2 = one bulk copy per thread chunk where the tile qualifies,
-                                       // 1 = contiguous-run LDGSTS, 0 = per-field strided copies
-    bool chain_defer_top = true;       // two-level chains inside a fused iteration: the top level is factored by one
-                                       // extra CTA of the forward launch, concurrently with the tiles' forward sweeps
     int sm_count = 0;
     bool chain_may_defer = false;      // set by the fused iteration around its refactor + solve pair
-    bool chain_top_pcr = true;         // ... or solved by parallel cyclic reduction with no top-level factors at all (chain.cu: pcr_top)
     int chain_top_mode = 0;            // 0: top-level LU factors are current, 1: there are none (cyclic reduction at solve time)
     bool chain_top_pending = false;    // level-0 factors are current, the top level's are not yet
-    int chain_fuse_top = 2; // bit 0: factor, bit 1: solve (top level swept by the last CTA of the level-0 launch)
-    int chain_min_n = 256, chain_max_b = 3;
     uint32_t ticket_base = 0; // value of the ticket word before the next unit launch
     int32_t solve_epoch = 0;
-    int unit_threads = 256;
     int unit_grid_factor = 0, unit_grid_solve = 0; // resident blocks (SMs x occupancy)
-    bool trace_units = false;          // debug: per-unit globaltimer stamps of the factor kernel
     daecpp_b200::DevBuf<long long> trace;
     bool jvals_from_triplets = false; // fused assembly reads the staged triplet values directly
     daecpp_b200::DevBuf<double> LU, CB, upd;
     double last_alpha = 0.0;
     double alpha_hint = 0.0; // alpha of the factorisation about to follow a symbolic analysis (row matching weights)
-    bool blocked_lu = true;        // big fronts: blocked multi-CTA LU (numeric.cu) instead of one CTA per front
-    int blocked_lu_min_dim = 96;   // level groups whose largest front is at least this order
-    bool bf_pdl = true;            // big fronts: panel / trailing-update launches chained by programmatic dependent launch
-    bool bf_dmma = true;           // big fronts: trailing update on the FP64 tensor cores (mma.m8n8k4.f64), 0 = FP64 FMA tiles
-    bool bf_fused_panel = true;    // big fronts: panel in one launch (numeric.cu: k_bf_panel), 0 = diag / rows / trsm launches
 
     // scratch for the cold (sorting) path
     daecpp_b200::DevBuf<uint64_t> keys_a, keys_b;
     daecpp_b200::DevBuf<int32_t> pay_a, pay_b, scan;
     daecpp_b200::DevBuf<char> cub_tmp;
 
-    // options
-    // Guarded iterative refinement (one step of r = b - Jb*dx, Jb*e = r, dx += e): taken only when the Newton update
-    // failed the convergence test on elements whose |dx| is below refine_floor, i.e. where the outcome of the
-    // reference's relative test (solver.hpp:603-609) hangs on the componentwise accuracy of the linear solve
-    int refine_steps = 1;
-    double refine_floor = 1e-11;
+    // guarded refinement (options: refine_steps, refine_floor)
     double n_refine = 0;
     bool refine_futile = false; // the last refinement of this Newton loop left the outcome as it was: not repeated until the step changes
-    bool assemble_only = false;
-    bool pinned_io = false; // host vectors handed to the ABI are page-locked: no staging copies
-    double pivot_tol = 0.0;
-    // chain path: a pivot below pivot_rel x (largest entry of its own matrix row) has lost every significant digit
-    // to cancellation and is reported like a zero pivot (Eigen would have pivoted away from it)
-    double pivot_rel = 1e-14;
 
     // statistics
     double n_symbolic = 0, n_refactor = 0, n_solve = 0, n_cold = 0, kernels = 0;
@@ -284,7 +297,6 @@ struct daecpp_b200_ctx
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mark = nullptr;
     // per-phase device times of iteration_resident (option "phase_timing"):
     // 0 assembly, 1 residual, 2 refactor, 3 solve, 4 update
-    bool phase_timing = false;
     cudaEvent_t pev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     double ms_phase[5] = {0, 0, 0, 0, 0};
     double n_phase_samples = 0;
