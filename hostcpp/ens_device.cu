@@ -16,6 +16,7 @@
 #include <cstring>
 #include <map>
 #include <string>
+#include <thread>
 
 #include "problems_device.hpp"
 
@@ -84,17 +85,30 @@ extern "C" int ensdev_perovskite(int64_t members, int64_t first, int64_t count, 
     }
     long steps = 0;
     double checksum = 0.0;
-    for (std::size_t k = 0; k < R.members.size(); ++k)
-    {
-        const ensemble_member &m = R.members[k];
-        steps += m.steps;
-        for (double v : m.x) checksum += v;
-        if (out)
-        {
-            double *row = out + k * (n + 2);
-            row[0] = (double)m.status; row[1] = (double)m.steps;
-            std::copy(m.x.begin(), m.x.end(), row + 2);
-        }
+    {   // hand the members to the caller's array (and sum them up) on a few threads: this is harness work, not the solver's
+        const std::size_t nm = R.members.size();
+        const unsigned nt = (unsigned)std::max<std::size_t>(1, std::min<std::size_t>(4, nm / 64));
+        std::vector<double> part(nt, 0.0);
+        std::vector<std::thread> pool;
+        for (unsigned w = 0; w < nt; ++w)
+            pool.emplace_back([&, w] {
+                double acc = 0.0;
+                for (std::size_t k = w * nm / nt; k < (w + 1) * nm / nt; ++k)
+                {
+                    const ensemble_member &m = R.members[k];
+                    for (double v : m.x) acc += v;
+                    if (out)
+                    {
+                        double *row = out + k * (n + 2);
+                        row[0] = (double)m.status; row[1] = (double)m.steps;
+                        std::copy(m.x.begin(), m.x.end(), row + 2);
+                    }
+                }
+                part[w] = acc;
+            });
+        for (std::thread &t : pool) t.join();
+        for (double v : part) checksum += v;
+        for (const ensemble_member &m : R.members) steps += m.steps;
     }
     if (stats)
     {
