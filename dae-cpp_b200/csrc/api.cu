@@ -1114,6 +1114,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "chain_fuse_top") c->chain_fuse_top = (int)value;
     else if (k == "bf_fused_panel") c->bf_fused_panel = value != 0.0;
     else if (k == "bf_dmma") c->bf_dmma = value != 0.0;
+    else if (k == "bf_schur") c->bf_schur = value != 0.0;
     else if (k == "bf_pdl") c->bf_pdl = value != 0.0;
     else if (k == "chain_defer_top") c->chain_defer_top = value != 0.0;
     else if (k == "chain_top_pcr") c->chain_top_pcr = value != 0.0;

@@ -186,6 +186,10 @@ struct daecpp_b200_options
     bool bf_pdl = true;                // big fronts: panel / trailing-update launches chained by programmatic dependent launch
     bool bf_dmma = true;               // big fronts: trailing update on the FP64 tensor cores (mma.m8n8k4.f64), 0 = FP64 FMA tiles
     bool bf_fused_panel = true;        // big fronts: panel in one launch (numeric.cu: k_bf_panel), 0 = diag / rows / trsm launches
+    bool bf_schur = false;             // big fronts: contribution block updated in one pass after the last block column (k_bf_schur).
+                                       // Bit-identical and it reads / writes the block once instead of once per block column, but measured
+                                       // slower on C4 (11.8 vs 11.1 ms): a block column costs ~40 us of launch + dependent latency whatever
+                                       // its trailing update touches, so the extra pass per level is not paid back
     // numerics
     // Guarded iterative refinement (one step of r = b - Jb*dx, Jb*e = r, dx += e): taken only when the Newton update
     // failed the convergence test on elements whose |dx| is below refine_floor, i.e. where the outcome of the

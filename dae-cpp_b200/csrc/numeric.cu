@@ -481,9 +481,11 @@ __device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double
 // 16 x 32 sub-tiles as 2 x 4 accumulator fragments of mma.m8n8k4.f64 (DMMA), operands from shared memory
 // (row stride 68 doubles: the 4 k x 8 rows of a fragment load fall in 32 different banks per half warp).
 // !DMMA: 4 x 4 register blocking on the FP64 FMA pipe (kept for A/B runs, option bf_dmma = 0).
+// strip != 0: only the part of the trailing matrix that later block columns of THIS front read -- rows or columns inside the
+// pivot block -- is updated per block column; the contribution block gets all its updates in one pass at the end (k_bf_schur).
 template <bool DMMA>
 __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
-                                                 double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags)
+                                                 double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags, int32_t strip)
 {
     const int32_t f = T.level_sn[begin + blockIdx.z];
     const FrontRef F = front_ref(T, f, LU, CB);
@@ -505,6 +507,7 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
         return;
     }
     if (i0 >= F.ld || j0 >= F.ld) return;
+    if (strip && i0 >= F.s && j0 >= F.s) return; // the tile lies inside the contribution block
     constexpr int LDS = DMMA ? 68 : 65;
     __shared__ double A[NB][LDS], Bm[NB][LDS];
     {   // operands: all 2 x 8 loads of a thread in flight before the first shared-memory store
@@ -550,7 +553,7 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
                 for (int e = 0; e < 2; ++e)
                 {
                     const int32_t i = i0 + wi + mi * 8 + g, j = j0 + wj + nj * 8 + 2 * c + e;
-                    dst[mi][nj][e] = (i < F.ld && j < F.ld) ? fr_at(F, i, j) : nullptr;
+                    dst[mi][nj][e] = (i < F.ld && j < F.ld && !(strip && i >= F.s && j >= F.s)) ? fr_at(F, i, j) : nullptr;
                     old[mi][nj][e] = dst[mi][nj][e] ? *dst[mi][nj][e] : 0.0;
                 }
 #pragma unroll
@@ -601,9 +604,105 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
         for (int a = 0; a < 4; ++a)
         {
             const int32_t i = i0 + ti + a;
-            if (i < F.ld) *fr_at(F, i, j) -= acc[a][b];
+            if (i < F.ld && !(strip && i >= F.s && j >= F.s)) *fr_at(F, i, j) -= acc[a][b];
         }
     }
+}
+
+// Contribution block of every front of a level in ONE pass: C -= L21 * U12 over all s pivots, 64 x 64 tiles on the FP64
+// tensor cores.  Per tile the block columns are applied in order, each as "old - (sum of its 32 products)" -- the
+// arithmetic of k_bf_gemm applied block column by block column, so the result is the same bit for bit -- but the tile
+// is read and written once instead of once per block column.
+__global__ void __launch_bounds__(256) k_bf_schur(FrontTables T, int32_t begin, double *__restrict__ LU, double *__restrict__ CB)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.z];
+    const FrontRef F = front_ref(T, f, LU, CB);
+    const int32_t i0 = F.s + blockIdx.x * 64, j0 = F.s + blockIdx.y * 64;
+    const int t = threadIdx.x;
+    bf_pdl_trigger();
+    bf_pdl_wait();
+    if (i0 >= F.ld || j0 >= F.ld) return;
+    constexpr int LDS = 68;
+    __shared__ double A[NB][LDS], Bm[NB][LDS];
+    const int w = t >> 5, lane = t & 31, g = lane >> 2, c = lane & 3;
+    const int wi = (w & 3) * 16, wj = (w >> 2) * 32;
+    double *dst[2][4][2];
+    double v[2][4][2];
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+        for (int nj = 0; nj < 4; ++nj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+            {
+                const int32_t i = i0 + wi + mi * 8 + g, j = j0 + wj + nj * 8 + 2 * c + e;
+                dst[mi][nj][e] = (i < F.ld && j < F.ld) ? F.C + (int64_t)(j - F.s) * F.r + (i - F.s) : nullptr;
+                v[mi][nj][e] = dst[mi][nj][e] ? *dst[mi][nj][e] : 0.0;
+            }
+    constexpr int IT = NB * 64 / 256;
+    double va[IT], vb[IT];
+    auto fetch = [&](int32_t k0) {
+        const int32_t nb = min(NB, F.s - k0);
+#pragma unroll
+        for (int it = 0; it < IT; ++it)
+        {
+            const int e = t + it * 256;
+            const int k = e / 64, q = e % 64;
+            va[it] = (k < nb && i0 + q < F.ld) ? F.Lp[(int64_t)(k0 + k) * F.ld + (i0 + q)] : 0.0;
+            vb[it] = (k < nb && j0 + q < F.ld) ? F.Ut[(int64_t)(k0 + k) * F.r + (j0 - F.s + q)] : 0.0;
+        }
+    };
+    auto park = [&]() {
+#pragma unroll
+        for (int it = 0; it < IT; ++it)
+        {
+            const int e = t + it * 256;
+            A[e / 64][e % 64] = va[it];
+            Bm[e / 64][e % 64] = vb[it];
+        }
+    };
+    fetch(0);
+    park();
+    __syncthreads();
+    for (int32_t k0 = 0; k0 < F.s; k0 += NB)
+    {
+        const bool more = k0 + NB < F.s;
+        if (more) fetch(k0 + NB); // the next block column's operands are in flight during this one's MMAs
+        double acc[2][4][2];
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+            for (int nj = 0; nj < 4; ++nj) acc[mi][nj][0] = acc[mi][nj][1] = 0.0;
+#pragma unroll
+        for (int kk = 0; kk < NB; kk += 4)
+        {
+            double av[2], bv[4];
+#pragma unroll
+            for (int mi = 0; mi < 2; ++mi) av[mi] = A[kk + c][wi + mi * 8 + g];
+#pragma unroll
+            for (int nj = 0; nj < 4; ++nj) bv[nj] = Bm[kk + c][wj + nj * 8 + g];
+#pragma unroll
+            for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                for (int nj = 0; nj < 4; ++nj) dmma884(acc[mi][nj][0], acc[mi][nj][1], av[mi], bv[nj]);
+        }
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+            for (int nj = 0; nj < 4; ++nj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) v[mi][nj][e] = v[mi][nj][e] - acc[mi][nj][e];
+        __syncthreads(); // everybody is done reading this block column's operands
+        if (more) park();
+        __syncthreads();
+    }
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+        for (int nj = 0; nj < 4; ++nj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+                if (dst[mi][nj][e]) *dst[mi][nj][e] = v[mi][nj][e];
 }
 
 __global__ void k_permute_in(int32_t n, const int32_t *__restrict__ perm, const double *__restrict__ b, double *__restrict__ y)
@@ -1127,6 +1226,10 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
                 const int32_t f = S.big_sn[L.begin + q];
                 max_children = std::max(max_children, S.child_ptr[f + 1] - S.child_ptr[f]);
             }
+            int32_t max_r = 0;
+            for (int32_t q = 0; q < L.count; ++q) max_r = std::max(max_r, S.r_of(S.big_sn[L.begin + q]));
+            // contribution blocks updated once, behind the last block column (k_bf_schur), not once per block column
+            const int32_t strip = (c->bf_schur && c->bf_dmma && max_r > 0) ? 1 : 0;
             bf_launch_pdl(st, k_bf_zero, dim3(64, L.count), 256, T, L.begin, c->CB.p);
             for (int32_t ord = 0; ord < max_children; ++ord)
                 bf_launch_pdl(st, k_bf_extend, dim3(std::max(1, std::min(256, (max_ld + 7) / 8)), L.count), 256, T, L.begin, ord, c->LU.p, c->CB.p);
@@ -1149,8 +1252,8 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
                     k_bf_rows<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                     k_bf_trsm<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                     const int tiles = (rest + 63) / 64;
-                    if (c->bf_dmma) k_bf_gemm<true><<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr);
-                    else k_bf_gemm<false><<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr);
+                    if (c->bf_dmma) k_bf_gemm<true><<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr, strip);
+                    else k_bf_gemm<false><<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr, strip);
                     c->kernels += 3;
                     continue;
                 }
@@ -1160,16 +1263,22 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
                 if (c->bf_pdl)
                 {
                     bf_launch_pdl(st, k_bf_panel, gp, 128, T, L.begin, k0, c->LU.p, c->CB.p);
-                    if (c->bf_dmma) bf_launch_pdl(st, k_bf_gemm<true>, gg, 256, T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
-                    else bf_launch_pdl(st, k_bf_gemm<false>, gg, 256, T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                    if (c->bf_dmma) bf_launch_pdl(st, k_bf_gemm<true>, gg, 256, T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip);
+                    else bf_launch_pdl(st, k_bf_gemm<false>, gg, 256, T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip);
                 }
                 else
                 {
                     k_bf_panel<<<gp, 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
-                    if (c->bf_dmma) k_bf_gemm<true><<<gg, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
-                    else k_bf_gemm<false><<<gg, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                    if (c->bf_dmma) k_bf_gemm<true><<<gg, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip);
+                    else k_bf_gemm<false><<<gg, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip);
                 }
                 c->kernels += 2;
+            }
+            if (strip)
+            {
+                const int32_t ct = (max_r + 63) / 64;
+                bf_launch_pdl(st, k_bf_schur, dim3(ct, ct, L.count), 256, T, L.begin, c->LU.p, c->CB.p);
+                c->kernels += 1;
             }
         }
         else

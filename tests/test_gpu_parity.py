@@ -408,6 +408,29 @@ def test_big_front_fused_panel_is_bit_identical():
     assert out[0] == out[1]
 
 
+@pytest.mark.parametrize("m", [160, 300])
+def test_big_front_single_pass_contribution_block_is_bit_identical(m):
+    """The contribution block of a big front updated once behind the last block column (k_bf_schur: block columns applied in
+    order, each as old - sum of its 32 products) vs once per block column by the trailing update: the same bits."""
+    n = m * m
+    u = P.grid2d_state(m)
+    J = P.grid2d_jacobian(u, m)
+    M = P.identity_mass(n)
+    b = np.full(n, 1.24)
+    out = []
+    for schur in (1, 0):
+        c = B.Context(n)
+        c.set_option("chain", 0); c.set_option("bf_schur", schur)
+        c.set_mass(M); c.set_jacobian(J)
+        c.refactor(50.0)
+        c.set_rhs(b)
+        out.append((c.solve().tobytes(), c.stat("kernels_launched")))
+        assert c.stat("max_front") >= 96
+        c.close()
+    assert out[0][0] == out[1][0]
+    assert out[0][1] > out[1][1]  # (one more launch per level of big fronts: the single pass really ran)
+
+
 def test_big_front_dmma_matches_fma_tiles():
     """Trailing update on the FP64 tensor cores (mma.m8n8k4.f64) vs the FP64 FMA tiles: same factorisation up to
     the summation order inside a 32-deep dot product; both must meet the backward-error bar of the linear solve."""
