@@ -165,6 +165,7 @@ class lane_control
     int m_pending_pre{DAECPP_B200_LANE_KEEP};
     bool m_done{false};
     bool m_last_was_accept{false};
+    int m_prev_iters{0};        // Newton iterations the last finished Newton loop of this lane took
     bool m_event_accept{false}; // a step was accepted in the round just consumed, at time m_event_t
     double m_event_t{0.0};
 
@@ -227,6 +228,7 @@ class lane_control
     // the Newton loop of this step has ended at iteration index `iter` (dae-cpp/solver.hpp:622-797)
     void end_newton(bool diverged, double variability)
     {
+        m_prev_iters = std::min(m_iter + 1, m_max_Newton_iter);
         if (m_iter == m_max_Newton_iter) diverged = true; // "couldn't converge"
         if (diverged)
         {
@@ -290,6 +292,10 @@ public:
     }
 
     bool done() const { return m_done; }
+    // How many iterations the Newton loop in progress will probably still run: what the last one took (3 before there is a
+    // last one), less those already done.  A multi-iteration round is planned this long -- iterations queued beyond the
+    // end of the loop are launches that find nothing to do, a loop that needs more simply goes on in the next round.
+    int expected_iterations() const { return std::max(1, (m_prev_iters > 0 ? m_prev_iters : 3) - m_iter); }
     // did the round just consumed end with an accepted step (the point where the reference calls the Solution Manager,
     // dae-cpp/solver.hpp:659)?  Its time goes to `t`; the lane's Newton iterate is the accepted state until the next round.
     bool take_accept(double &t)
@@ -496,7 +502,13 @@ ensemble_result solve_ensemble_device_observed(const std::vector<Eq> &eqs, const
     if (const char *env = std::getenv("DAECPP_B200_STRAGGLERS")) straggler_threshold = (std::size_t)std::atol(env);
     for (;;)
     {
-        const int per_round = in_flight >= straggler_threshold ? 1 : DAECPP_B200_MAX_ROUND_ITERATIONS;
+        int per_round = 1;
+        if (in_flight < straggler_threshold)
+        {
+            for (std::size_t m = 0; m < members; ++m)
+                if (!lanes[m].done()) per_round = std::max(per_round, lanes[m].expected_iterations());
+            per_round = std::min(per_round, DAECPP_B200_MAX_ROUND_ITERATIONS);
+        }
         std::size_t active = 0;
         for (std::size_t m = 0; m < members; ++m)
         {
