@@ -138,6 +138,9 @@ struct PlanArgs
 // the way the reference's Newton loop continues (solver.hpp:431-627).  One thread per lane of the round's list.
 __global__ void k_batch_plan(PlanArgs a)
 {
+    // launched with programmatic stream serialisation like the kernels around it (every thread passes the wait)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= a.n_list) return;
     const int lane = a.list[q];
@@ -647,7 +650,18 @@ int daecpp_b200_batch_round(daecpp_b200_batch *b, const daecpp_b200_lane_cmd *cm
             {
                 PlanArgs pa{Ln, j, n_active, b->L.list_active, b->dev(b->ctl_plan(j)), b->dev(b->ctl_norefine()),
                             j > 0 ? flags_of(b->d_res, j - 1) : nullptr, b->res_iters(b->d_res) + Ln, b->res_iters(b->d_res)};
-                k_batch_plan<<<(n_active + 127) / 128, 128, 0, st>>>(pa);
+                {
+                    cudaLaunchConfig_t cfg = {};
+                    cfg.gridDim = dim3((unsigned)((n_active + 127) / 128), 1, 1);
+                    cfg.blockDim = dim3(128, 1, 1);
+                    cfg.stream = st;
+                    cudaLaunchAttribute at[1];
+                    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+                    at[0].val.programmaticStreamSerializationAllowed = 1;
+                    cfg.attrs = at;
+                    cfg.numAttrs = 1;
+                    BATCH_TRY(b, cudaLaunchKernelEx(&cfg, k_batch_plan, pa));
+                }
                 c->kernels += 1;
             }
             // j == 0: the compacted list of refactoring lanes is exact; later iterations run the factor kernels over the

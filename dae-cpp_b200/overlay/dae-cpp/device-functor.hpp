@@ -151,9 +151,34 @@ template <class Eq> DAECPP_HD double jacobian_element(const Eq &eq, const double
 #if defined(__CUDACC__)
 namespace detail
 {
+// The functor kernels sit between the library's own kernels on the stream and are launched like them with programmatic
+// stream serialisation: a kernel lets its successor start launching at once and waits for its predecessor's memory
+// before it reads anything (every path through the kernel passes the wait: the chain of dependencies stays transitive).
+__device__ __forceinline__ void pdl_entry()
+{
+#if defined(__CUDA_ARCH__) && __CUDA_ARCH__ >= 900
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+#endif
+}
+template <class... P, class... A> inline cudaError_t launch_pdl(cudaStream_t st, void (*kernel)(P...), dim3 grid, int threads, A... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3((unsigned)threads, 1, 1);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
+}
 template <class Eq>
 __global__ void k_rhs(const Eq *__restrict__ eq, const daecpp_b200_functor_args a)
 {
+    pdl_entry();
     const int lane = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
     if (a.mode[lane] < a.min_mode) return; // (also lanes that halted earlier in a multi-iteration round)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -165,6 +190,7 @@ template <class Eq>
 __global__ void k_jacobian(const Eq *__restrict__ eq, const int32_t *__restrict__ ti, const int32_t *__restrict__ tj,
                            const int64_t nT, const daecpp_b200_functor_args a)
 {
+    pdl_entry();
     const int lane = a.lane_list ? a.lane_list[blockIdx.y] : blockIdx.y;
     if (a.mode[lane] < a.min_mode) return; // (also lanes that halted earlier in a multi-iteration round)
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -204,8 +230,8 @@ class DeviceFunctors
         if (a->lanes != self->m_lanes) return 1;
         if (a->lane_list && a->n_list == 0) return 0;
         const dim3 grid((unsigned)((a->n + 255) / 256), (unsigned)(a->lane_list ? a->n_list : a->lanes));
-        detail::k_rhs<Eq><<<grid, 256, 0, static_cast<cudaStream_t>(a->stream)>>>(self->m_eq, *a);
-        return cudaGetLastError() == cudaSuccess ? 0 : 2;
+        const cudaError_t e = detail::launch_pdl(static_cast<cudaStream_t>(a->stream), detail::k_rhs<Eq>, grid, 256, self->m_eq, *a);
+        return (e == cudaSuccess && cudaGetLastError() == cudaSuccess) ? 0 : 2;
     }
     static int jac_cb(void *user, const daecpp_b200_functor_args *a)
     {
@@ -213,8 +239,8 @@ class DeviceFunctors
         if (a->lanes != self->m_lanes) return 1;
         if (a->lane_list && a->n_list == 0) return 0;
         const dim3 grid((unsigned)((self->m_nT + 255) / 256), (unsigned)(a->lane_list ? a->n_list : a->lanes));
-        detail::k_jacobian<Eq><<<grid, 256, 0, static_cast<cudaStream_t>(a->stream)>>>(self->m_eq, self->m_i, self->m_j, self->m_nT, *a);
-        return cudaGetLastError() == cudaSuccess ? 0 : 2;
+        const cudaError_t e = detail::launch_pdl(static_cast<cudaStream_t>(a->stream), detail::k_jacobian<Eq>, grid, 256, self->m_eq, self->m_i, self->m_j, self->m_nT, *a);
+        return (e == cudaSuccess && cudaGetLastError() == cudaSuccess) ? 0 : 2;
     }
 #else
     template <class T> static T *to_device(const T *h, std::size_t count)
