@@ -6,9 +6,13 @@ re-assemble J from its triplet values, b = M*dxdt - f, Jb = J - alpha*M, numeric
 refactorisation, triangular solves, error checks and xk += dx.
 
   value   : device time per iteration with the triplet values / f already resident in HBM
-            (daecpp_b200_iteration_resident), CUDA events on the context's stream
+            (daecpp_b200_iterations_resident: blocks of 10 iterations, iteration k+1 enqueued behind k, every
+            iteration's flag words read by the host), CUDA events on the context's stream
   e2e     : the same iteration through the host-buffer C-ABI calls the overlay solver.hpp makes
-            (set_jacobian -> residual -> refactor -> solve_update -> get_xk), H2D/D2H inside
+            (set_jacobian[_values] -> iteration_host), H2D/D2H inside
+  e2e_device_functors : C3 once more with the equations evaluated on the device (dae-cpp/device-functor.hpp,
+            daecpp::solve_ensemble_device with one lane): wall clock per Newton iteration of a whole integration
+  ensemble_1gpu : the N = 1 point of the C5 curve the N > 1 runs continue
   roofline: the numeric refactorisation phase against the measured HBM copy bandwidth
   cpu_baseline / --impl reference: the unmodified reference (Eigen::SparseLU behind
             oracle/_ref/libdaeref.so, else the C port) doing the same iteration on the host
