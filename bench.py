@@ -669,8 +669,9 @@ def single_system_line(args, env, workload, size, steps, warmup, want_cpu, want_
     abytes = algorithmic_bytes(w, nnz_jb)
 
     def resident(k_iters, refactor=1):
-        # k complete Newton iterations, each with its flags on the host before the next is enqueued; the
-        # loop itself runs behind the C ABI (what a C++ caller does) rather than through ctypes
+        # k complete Newton iterations behind the C ABI (daecpp_b200_iterations_resident): every iteration publishes its flag
+        # words and the host reads each of them, but iteration k+1 is enqueued while k runs -- where the host would have to
+        # act between two iterations (failed pivot, refinement) the device cancels the queued one (api.cu)
         if k_iters > 0:
             c.iterations_resident(k_iters, refactor, order, dt, atol, rtol)
 
@@ -821,6 +822,9 @@ def single_system_line(args, env, workload, size, steps, warmup, want_cpu, want_
         "spread_us": spread([1e3 * ms / kb for ms, kb in blocks]),
         "clocks": clocks, "gpu_launches": launches, "solve_only_us": us_solve_only, "phases": phases,
         "roofline": roofline, "e2e": e2e, "factor": stats,
+        "value_protocol": "blocks of 10 iterations per daecpp_b200_iterations_resident call, CUDA events around each block; inside a block "
+                          "iteration k+1 is enqueued behind k (programmatic dependent launch) while the host reads k's flag words; "
+                          "--option pipeline_iterations=0 gives the one-at-a-time loop",
     }
 
     # ---- CPU baseline (rank 0, N = 1 only): the reference on the host, bounded sample
