@@ -119,9 +119,13 @@ int daecpp_b200_accept_step(daecpp_b200_ctx *ctx, int32_t variability_on, double
  * "dx applied, flags ready"); bench.py's `value` is measured through it. */
 int daecpp_b200_iteration_resident(daecpp_b200_ctx *ctx, int32_t do_refactor, int32_t order, const double dt[4],
                                    double atol, double rtol, double max_err_abs, int32_t *flags);
-/* `count` such iterations back to back, each complete (flags on the host) before the next is
- * enqueued; *flags receives the last iteration's.  What a C++ Newton loop over resident data costs,
- * without a foreign-function call per iteration (bench.py's `value`). */
+/* `count` such iterations back to back; *flags receives the last iteration's.  On the block-chain path the
+ * iterations are PIPELINED: iteration k+1 is enqueued while k runs, every iteration still publishes its own
+ * flag words and the host still reads each of them in order; where the host has to act between two
+ * iterations (a failed pivot -> DAECPP_B200_EDECOMP is returned, a dependency time-out, an update it would
+ * refine) the device cancels the queued iteration before it touches anything, so the state on return is
+ * exactly that of the one-at-a-time loop (option "pipeline_iterations" = 0 selects that loop).  This is what
+ * bench.py times as `value`. */
 int daecpp_b200_iterations_resident(daecpp_b200_ctx *ctx, int32_t count, int32_t do_refactor, int32_t order,
                                     const double dt[4], double atol, double rtol, double max_err_abs, int32_t *flags);
 /* Values-only Jacobian hand-off: the (i, j) stream is the one of the last
@@ -177,7 +181,13 @@ int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *ctx, int64_t *out, int64_t cap
  * forward kernel; "keep_b" = 1 also writes it to HBM for daecpp_b200_get_vector), "lean_flags" (flag words
  * delivered through a mapped host word instead of memset + copy nodes).  General path: "blocked_lu",
  * "blocked_lu_min_dim", "bf_fused_panel" (panel of a block column in one launch), "bf_dmma" (trailing update of big
- * fronts on the FP64 tensor cores, default 1; 0 = FP64 FMA tiles), "bf_pdl" (programmatic dependent launch between them).  Debug: "trace_units", "phase_timing", "pinned_io". */
+ * fronts on the FP64 tensor cores, default 1; 0 = FP64 FMA tiles), "bf_pdl" (programmatic dependent launch between them),
+ * "bf_schur" (contribution block of a big front updated in one pass behind its last block column; bit-identical, default 0:
+ * measured slower).  Numerics: "refine_steps" / "refine_floor" (guarded refinement step), "pivot_rel" (row-relative pivot
+ * test of the chain path), "transversal" (row matching before the ordering when the diagonal has structural holes),
+ * "tiny" (one-launch path for n <= 32).  "chain_packed": 2 = bulk copies (cp.async.bulk) where the tile qualifies,
+ * 1 = contiguous-run LDGSTS, 0 = per-field copies.  "pipeline_iterations": see daecpp_b200_iterations_resident.
+ * Debug: "trace_units", "phase_timing", "pinned_io". */
 int daecpp_b200_set_option(daecpp_b200_ctx *ctx, const char *key, double value);
 
 /* ==== lock-step batched ensemble (an ADDITION: the reference has no ensemble API) =========
