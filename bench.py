@@ -355,11 +355,12 @@ def run_ensemble_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def _ensdev():
+def _ensdev(emulated=False):
     """hostcpp/_bin/libensdevice.so: dae-cpp/ensemble.hpp solve_ensemble_device over the perovskite device functor
-    (hostcpp/ens_device.cu, nvcc) -- called in-process so that the timed region sits between this file's barriers."""
+    (hostcpp/ens_device.cu, nvcc) -- called in-process so that the timed region sits between this file's barriers.
+    emulated (tests only, --host-logic-check): the same driver compiled by g++ over the CPU emulation of the batch entry points."""
     import ctypes as C
-    path = os.path.join(ROOT, "hostcpp", "_bin", "libensdevice.so")
+    path = os.path.join(ROOT, "hostcpp", "_bin", "libensdevice_emu.so" if emulated else "libensdevice.so")
     if not os.path.exists(path):
         raise SystemExit(f"bench.py: {path} is not built (python -c 'import __graft_entry__ as g; g.build()')")
     lib = C.CDLL(path)
@@ -372,11 +373,11 @@ ENS_STATS = ("rounds", "lane_iterations", "lane_refactorisations", "device_ms", 
              "kernels_launched", "setup_ms", "rounds_wall_ms", "download_ms", "destroy_ms")
 
 
-def ensemble_device_block(members, first, count, stride, N, device, out=None):
+def ensemble_device_block(members, first, count, stride, N, device, out=None, emulated=False):
     """One lock-step integration of members first, first+stride, ... (count of them) on `device`; returns the driver's statistics."""
     os.environ["DAECPP_B200_DEVICE"] = str(device)
     st = np.zeros(len(ENS_STATS))
-    _ensdev().ensdev_perovskite(members, first, count, stride, N, 10.0, 0, out.ctypes.data if out is not None else None, st.ctypes.data)
+    _ensdev(emulated).ensdev_perovskite(members, first, count, stride, N, 10.0, 0, out.ctypes.data if out is not None else None, st.ctypes.data)
     return dict(zip(ENS_STATS, st.tolist()))
 
 
@@ -397,15 +398,17 @@ def run_ensemble_device(args, env=None, emit=True):
     lanes of ONE batch context (one launch sequence per Newton round for all lanes), one all_gather of
     {status, steps, final state} at the end -- the only collective."""
     own_env = env is None
+    emulated = bool(getattr(args, "host_logic_check", False))
     if own_env:
-        env = Env()
+        env = Env(host_logic_check=emulated)
     torch, dist, world, rank, local = env.torch, env.dist, env.world, env.rank, env.local
     barrier, max_over_ranks = env.barrier, env.max_over_ranks
+    dev = env.device
 
     def sum_over_ranks(v):
         if dist is None:
             return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
@@ -418,9 +421,9 @@ def run_ensemble_device(args, env=None, emit=True):
     first, stride = rank, world
     count = len(range(rank, members, world))
     steps = max(1, min(args.steps, 20)) if args.steps_given else 5
-    warm = max(3, min(args.warmup, 5))
+    warm = args.warmup if emulated else max(3, min(args.warmup, 5))
     for _ in range(warm):  # whole sweeps, like the timed ones: CUDA context, module load, the context pool and the page-locked buffers come up
-        ensemble_device_block(members, first, count, stride, N, local)
+        ensemble_device_block(members, first, count, stride, N, local, emulated=emulated)
     out = np.zeros((count, n + 2))
     sampler = ClockSampler(local)
     sampler.start()
@@ -428,7 +431,7 @@ def run_ensemble_device(args, env=None, emit=True):
     t0 = time.perf_counter()
     acc = dict.fromkeys(ENS_STATS, 0.0)
     for _ in range(steps):
-        st = ensemble_device_block(members, first, count, stride, N, local, out)
+        st = ensemble_device_block(members, first, count, stride, N, local, out, emulated=emulated)
         for k in ENS_STATS:
             acc[k] += st[k]
     my_wall = time.perf_counter() - t0
@@ -442,7 +445,7 @@ def run_ensemble_device(args, env=None, emit=True):
     rounds = max_over_ranks(acc["rounds"])
     # where each rank's wall clock went, per sweep [ms]: the slowest rank sets e2e
     keys = ("setup_ms", "rounds_wall_ms", "device_ms", "download_ms", "destroy_ms", "wall_ms")
-    mine_t = torch.tensor([acc[k] / steps for k in keys] + [1e3 * my_wall / steps], dtype=torch.float64, device="cuda")
+    mine_t = torch.tensor([acc[k] / steps for k in keys] + [1e3 * my_wall / steps], dtype=torch.float64, device=dev)
     if dist is not None:
         all_t = [torch.empty_like(mine_t) for _ in range(world)]
         dist.all_gather(all_t, mine_t)
@@ -450,16 +453,16 @@ def run_ensemble_device(args, env=None, emit=True):
         all_t = [mine_t]
     per_rank = {k: [round(float(t[i]), 2) for t in all_t] for i, k in enumerate(keys + ("call_ms",))}
     # ---- the one collective of the path
-    mine = torch.from_numpy(out).to("cuda")
+    mine = torch.from_numpy(out).to(dev)
     if count < per:
-        mine = torch.cat([mine, torch.zeros(per - count, n + 2, dtype=torch.float64, device="cuda")])
+        mine = torch.cat([mine, torch.zeros(per - count, n + 2, dtype=torch.float64, device=dev)])
     gather_ms = 0.0
     if dist is not None:
-        allm = torch.empty(world * per, n + 2, dtype=torch.float64, device="cuda")
-        torch.cuda.synchronize()
+        allm = torch.empty(world * per, n + 2, dtype=torch.float64, device=dev)
+        env.sync()
         tg = time.perf_counter()
         dist.all_gather_into_tensor(allm, mine)
-        torch.cuda.synchronize()
+        env.sync()
         gather_ms = (time.perf_counter() - tg) * 1e3
     else:
         allm = mine
@@ -469,8 +472,8 @@ def run_ensemble_device(args, env=None, emit=True):
     failed = int((allm[:, 0] != 0).sum().item())
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     peak = json.load(open(peaks_path))["hbm_gbs"] if os.path.exists(peaks_path) else 6650.0
-    gbps = abytes / dev_s / 1e9 / world  # per GPU
-    line = {"metric": ENS_METRIC, "value": members * steps / dev_s, "unit": "systems/s", "n_gpus": world, "steps": steps, "warmup": warm,
+    gbps = abytes / max(dev_s, 1e-12) / 1e9 / world  # per GPU
+    line = {"metric": ENS_METRIC, "value": members * steps / max(dev_s, 1e-12), "unit": "systems/s", "n_gpus": world, "steps": steps, "warmup": warm,
             "ms_per_step": 1e3 * dev_s / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": f"C5 ensemble of perovskite N={N} (n={n}) members, lambda log-spaced 0.5..2 (BASELINE configs[4])",
@@ -603,32 +606,43 @@ def run_ensemble_b200(args):
 class Env:
     """Device bring-up, barrier and the max-over-ranks reduction (torch is plumbing only)."""
 
-    def __init__(self):
+    def __init__(self, host_logic_check=False):
+        """host_logic_check (tests only): gloo and CPU tensors, so that the dealing / gather logic around the lock-step
+        driver can be exercised without a GPU (the driver itself is then the emulated one, tests/emu)."""
         import torch
         self.torch = torch
         self.world = int(os.environ.get("WORLD_SIZE", "1"))
         self.rank = int(os.environ.get("RANK", "0"))
         self.local = int(os.environ.get("LOCAL_RANK", "0"))
-        if not torch.cuda.is_available():
-            raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
-        torch.cuda.set_device(self.local)
+        self.device = "cpu" if host_logic_check else "cuda"
+        if not host_logic_check:
+            if not torch.cuda.is_available():
+                raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+            torch.cuda.set_device(self.local)
         self.dist = None
         if self.world > 1:
             import torch.distributed as dist
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            if host_logic_check:
+                dist.init_process_group("gloo")
+            else:
+                dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
             self.dist = dist
 
+    def sync(self):
+        if self.device == "cuda":
+            self.torch.cuda.synchronize()
+
     def barrier(self):
-        self.torch.cuda.synchronize()
+        self.sync()
         if self.dist is not None:
             self.dist.barrier()
-        self.torch.cuda.synchronize()
+        self.sync()
 
     def max_over_ranks(self, v):
         if self.dist is None:
             return v
-        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        t = self.torch.tensor([v], dtype=self.torch.float64, device=self.device)
         self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return float(t.item())
 
@@ -918,8 +932,8 @@ if __name__ == "__main__":
     elif a.workload == "ensemble":
         if a.impl == "reference":
             run_ensemble_reference(a)
-        elif a.functors == "device" and not a.host_logic_check:
-            run_ensemble_device(a)
+        elif a.functors == "device":
+            run_ensemble_device(a)  # (--host-logic-check: the emulated driver, gloo, CPU tensors -- tests only)
         else:
             run_ensemble_b200(a)
     elif a.impl == "reference":

@@ -38,7 +38,7 @@ def _bench(extra, nproc):
 
 def test_partition_and_gather_do_not_depend_on_rank_count():
     _need("traj_dump_ref")
-    args = ["--host-logic-check", "--members", "7", "--size", "150", "--threads", "2"]
+    args = ["--host-logic-check", "--functors", "host", "--members", "7", "--size", "150", "--threads", "2"]
     one = _bench(args, 1)
     two = _bench(args, 2)
     assert one["n_gpus"] == 1 and two["n_gpus"] == 2
@@ -46,6 +46,25 @@ def test_partition_and_gather_do_not_depend_on_rank_count():
     assert one["accepted_steps_total"] == two["accepted_steps_total"] > 0
     assert one["state_checksum"] == two["state_checksum"]  # members are bit-identical wherever they run
     assert two["config"]["members_per_gpu"] == 4  # contiguous blocks of ceil(7/2)
+    assert two["scaling"] == "strong" and two["metric"] == "ensemble systems/s"
+
+
+def test_lockstep_dealing_and_gather_do_not_depend_on_rank_count():
+    """The lock-step driver's sharding (bench.py: run_ensemble_device): members dealt round-robin to the ranks, every rank's
+    share integrated as the lanes of one batch, one all_gather, rank-major blocks transposed back to member order.  On CPU:
+    gloo, world_size 1 and 2, the driver compiled over the emulated batch entry points (tests/emu) -- every member must
+    come out bit-identical and in the same place whatever the number of ranks."""
+    if not os.path.exists(os.path.join(BIN, "libensdevice_emu.so")):
+        pytest.skip("hostcpp/_bin/libensdevice_emu.so not built")
+    args = ["--host-logic-check", "--members", "7", "--size", "60"]
+    one = _bench(args, 1)
+    two = _bench(args, 2)
+    assert one["n_gpus"] == 1 and two["n_gpus"] == 2
+    assert one["failed_members"] == 0 and two["failed_members"] == 0
+    assert one["accepted_steps_total"] == two["accepted_steps_total"] > 0
+    assert one["state_checksum"] == two["state_checksum"]
+    assert two["config"]["members_per_gpu"] == 4 and "round-robin" in two["config"]["parallelism"]
+    assert two["lane_iterations_per_step"] == one["lane_iterations_per_step"]
     assert two["scaling"] == "strong" and two["metric"] == "ensemble systems/s"
 
 
