@@ -1112,6 +1112,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "blocked_lu") c->blocked_lu = value != 0.0;
     else if (k == "blocked_lu_min_dim") c->blocked_lu_min_dim = (int)value;
     else if (k == "chain_fuse_top") c->chain_fuse_top = (int)value;
+    else if (k == "chain_top_cta") c->chain_top_cta = value != 0.0;
     else if (k == "bf_fused_panel") c->bf_fused_panel = value != 0.0;
     else if (k == "bf_dmma") c->bf_dmma = value != 0.0;
     else if (k == "bf_schur") c->bf_schur = value != 0.0;

@@ -60,6 +60,7 @@ struct ChainArgs
     // fused residual (diagonal mass): rhs = M*dxdt - f formed while staging (vector_ops.cu: k_residual_diag)
     int32_t fuse_res;
     int32_t *cancel;   // pipelined resident iterations: non-zero = the previous iteration ended in a way the host must look at first; every CTA of this one leaves at once
+    int32_t top_cta;     // forward: one extra CTA does nothing but the grid-level solve (cyclic reduction); the tiles only count themselves off
     int32_t pf_rhs;      // factor: pull the sources of the coming forward sweep's right-hand side (a.bdf, a.fvec, a.mdiag) into L2
     int32_t stage_early; // factor: the matrix values are not produced by the kernel in front: stage them before the dependency wait
     int32_t rhs_early;   // forward: the launch in front is this iteration's factor kernel, which does not touch the right-hand side's sources
@@ -634,7 +635,7 @@ template <int B> __device__ __forceinline__ Mat<B> pcr_inv(const Mat<B> &X, doub
 
 template <int B>
 __device__ __noinline__ void pcr_top(int R, const double *__restrict__ red, const double *__restrict__ rv, double *__restrict__ xl,
-                                     double tol, int32_t *fail_flag, double *__restrict__ W, int t, long long *trace)
+                                     double tol, int32_t *fail_flag, double *__restrict__ W, int t, long long *trace, bool dry = false)
 {
     auto mark = [&](int slot) {
         if (trace && t == 0) { long long ns; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns)); trace[slot] = ns; }
@@ -724,10 +725,11 @@ __device__ __noinline__ void pcr_top(int R, const double *__restrict__ red, cons
     for (int i = t; i < R; i += NT)
     {
         const Vec<B> x = mv<B>(pcr_inv<B>(pcr_ldm<B>(sD, i), tol, fail), pcr_ldv<B>(sr, i));
+        if (dry) continue; // (a rehearsal on whatever the arrays hold: nothing leaves the CTA)
 #pragma unroll
         for (int q = 0; q < B; ++q) xl[(size_t)i * B + q] = x.a[q];
     }
-    if (fail) atomicOr(fail_flag, 1);
+    if (fail && !dry) atomicOr(fail_flag, 1);
 }
 
 // forward sweep of one tile; the single tile of the top level carries on into the backward sweep
@@ -777,6 +779,37 @@ __global__ void __launch_bounds__(Cfg<B>::T, (B <= 2 ? 4 : 1)) k_chain_forward(C
     stamp(a, FIRST ? 2 : 3, tile, 5);
     // The launch in front is this iteration's factor kernel (it passed its own dependency wait before it let this grid start):
     // the right-hand side's sources -- iterate, history, f, mass values -- are final, only the factors are still being written
+    if (FIRST && a.top_cta && tile == a.lv.ntiles)
+    {   // The CTA of the grid-level system.  Which tile finishes last is not known in advance, so the cyclic reduction used
+        // to start cold -- instruction cache, address arithmetic, the reduced matrix rows -- in whatever CTA that was, with
+        // every other SM waiting for it.  This CTA rehearses it while the tiles sweep (results discarded), then waits for
+        // their count and runs it for real.
+        pdl_wait();
+        if (a.cancel && *reinterpret_cast<volatile int32_t *>(a.cancel)) return;
+        pdl_trigger();
+        double *W = reinterpret_cast<double *>(smem);
+        pcr_top<B>(a.top.rows, a.top.red_in + mb * a.s_red, a.top.rv_in + mb * a.s_rv, a.top.xlev + mb * a.s_x, a.tol, nullptr, W, t, nullptr, true);
+        __syncthreads();
+        if (t == 0)
+        {
+            volatile uint32_t *cnt = a.counter + 2 * mb + 1;
+            long long t0, t1;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+            while (*cnt < (uint32_t)a.lv.ntiles)
+            {
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 2000000000ll) { atomicOr(&flag_words(a, mb)[4], 1); break; } // (2 s: something is badly wrong; do not hang the GPU)
+            }
+            *cnt = 0u;
+        }
+        __syncthreads();
+        __threadfence();
+        stamp(a, 3, 0, 0);
+        pcr_top<B>(a.top.rows, a.top.red_in + mb * a.s_red, a.top.rv_in + mb * a.s_rv, a.top.xlev + mb * a.s_x, a.tol, &flag_words(a, mb)[3], W, t,
+                   a.trace ? a.trace + (size_t)3 * a.trace_tiles * TRACE_SLOTS : nullptr);
+        stamp(a, 3, 0, 4);
+        return;
+    }
     const bool early = FIRST && a.rhs_early && !(a.extra_factor && tile == a.lv.ntiles);
     if (early)
     {
@@ -793,6 +826,13 @@ __global__ void __launch_bounds__(Cfg<B>::T, (B <= 2 ? 4 : 1)) k_chain_forward(C
     }
     else
         forward_tile<B, FIRST>(a, a.lv, sh, t, tile, mb, true, early);
+    if (FIRST && a.top_cta)
+    {   // count this tile off: its reduced right-hand side is in global memory
+        __threadfence();
+        __syncthreads();
+        if (t == 0) atomicAdd(a.counter + 2 * mb + 1, 1u);
+        return;
+    }
     if (a.fuse_top && last_tile_done(a.counter + 2 * mb + 1, a.lv.ntiles + a.extra_factor, t))
     {
         if (a.top_pcr)
@@ -1018,7 +1058,7 @@ ChainArgs level_args(daecpp_b200_ctx *c, int g, bool fuse)
 template <class K> void launch_pdl(daecpp_b200_ctx *c, K kernel, const ChainArgs &a, int threads, size_t smem)
 {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(a.lv.ntiles + a.extra_factor, a.grid_lanes > 0 ? a.grid_lanes : 1, 1);
+    cfg.gridDim = dim3(a.lv.ntiles + a.extra_factor + a.top_cta, a.grid_lanes > 0 ? a.grid_lanes : 1, 1);
     cfg.blockDim = dim3(threads, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = c->stream;
@@ -1180,6 +1220,11 @@ int chain_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol, 
         if (g == 0) first_args(a);
         if (g == 0 && c->chain_top_pending) { a.extra_factor = 1; c->chain_top_pending = false; }
         if (g == 0 && c->chain_top_mode == 1) a.top_pcr = 1;
+        // a CTA of its own for the grid-level solve: single system (with lanes the spinning CTAs of later lanes could keep
+        // tiles of earlier ones off the SMs), every CTA of the launch resident at once
+        if (g == 0 && a.top_pcr && fuse && !a.extra_factor && !c->lanes && c->chain_top_cta && c->sm_count > 0 &&
+            a.lv.ntiles + 1 <= 4 * c->sm_count)
+            a.top_cta = 1;
 #define LW(B) launch_forward<B>(c, a, g == 0)
         CHAIN_DISPATCH(P.B, LW)
 #undef LW

@@ -180,6 +180,7 @@ struct daecpp_b200_options
                                        // extra CTA of the forward launch, concurrently with the tiles' forward sweeps
     bool chain_top_pcr = true;         // ... or solved by parallel cyclic reduction with no top-level factors at all (chain.cu: pcr_top)
     int chain_fuse_top = 2;            // bit 0: factor, bit 1: solve (top level swept by the last CTA of the level-0 launch)
+    bool chain_top_cta = true;         // fused iteration, cyclic-reduction top level: a dedicated CTA of the forward launch rehearses and runs it
     // general multifrontal path
     bool blocked_lu = true;            // big fronts: blocked multi-CTA LU (numeric.cu) instead of one CTA per front
     int blocked_lu_min_dim = 96;       // level groups whose largest front is at least this order
