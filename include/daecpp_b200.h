@@ -187,6 +187,8 @@ int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *ctx, int64_t *out, int64_t cap
  * test of the chain path), "transversal" (row matching before the ordering when the diagonal has structural holes),
  * "tiny" (one-launch path for n <= 32).  "chain_packed": 2 = bulk copies (cp.async.bulk) where the tile qualifies,
  * 1 = contiguous-run LDGSTS, 0 = per-field copies.  "pipeline_iterations": see daecpp_b200_iterations_resident.
+ * "chain_top_cta" (default 1): fused iteration of a single system, the grid-level cyclic reduction runs in a CTA of its own
+ * that rehearses it while the tiles sweep.
  * Debug: "trace_units", "phase_timing", "pinned_io". */
 int daecpp_b200_set_option(daecpp_b200_ctx *ctx, const char *key, double value);
 
