@@ -352,7 +352,7 @@ static void destroy_now(daecpp_b200_ctx *c)
     c->M.release(); c->J.release(); c->dS.release(); c->dC.release();
     c->m_rowptr.release(); c->m_rowslot.release(); c->m_rowcol.release(); c->m_dslot.release();
     c->u_outer.release(); c->u_inner.release(); c->u_J.release(); c->u_M.release(); c->u_vals.release();
-    c->LU.release(); c->CB.release(); c->upd.release(); c->trace.release();
+    c->LU.release(); c->CB.release(); c->bf_diag.release(); c->upd.release(); c->trace.release();
     c->keys_a.release(); c->keys_b.release(); c->pay_a.release(); c->pay_b.release(); c->scan.release(); c->cub_tmp.release();
     if (c->xk) cudaFree(c->xk);
     if (c->d_flags) cudaFree(c->d_flags);
@@ -1116,6 +1116,9 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "bf_fused_panel") c->bf_fused_panel = value != 0.0;
     else if (k == "bf_dmma") c->bf_dmma = value != 0.0;
     else if (k == "bf_schur") c->bf_schur = value != 0.0;
+    else if (k == "bf_fast_solve") c->bf_fast_solve = value != 0.0;
+    else if (k == "bf_diag_copy") c->bf_diag_copy = value != 0.0;
+    else if (k == "bf_lu_lookahead") c->bf_lu_lookahead = value != 0.0;
     else if (k == "bf_pdl") c->bf_pdl = value != 0.0;
     else if (k == "chain_defer_top") c->chain_defer_top = value != 0.0;
     else if (k == "chain_top_pcr") c->chain_top_pcr = value != 0.0;

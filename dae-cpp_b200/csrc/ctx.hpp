@@ -152,6 +152,7 @@ struct GroupLaunch
     int32_t kind = 0, begin = 0, count = 0;
     int32_t group = 32, max_dim = 0; // kind 1: threads cooperating on one front
     int32_t grid = 0;                // kind 0: persistent blocks
+    int32_t max_s = 0, max_r = 0, max_children = 0; // kind 1: over the fronts of the level (pivots, rows below, children)
 };
 
 } // namespace daecpp_b200
@@ -187,6 +188,13 @@ struct daecpp_b200_options
     bool bf_pdl = true;                // big fronts: panel / trailing-update launches chained by programmatic dependent launch
     bool bf_dmma = true;               // big fronts: trailing update on the FP64 tensor cores (mma.m8n8k4.f64), 0 = FP64 FMA tiles
     bool bf_fused_panel = true;        // big fronts: panel in one launch (numeric.cu: k_bf_panel), 0 = diag / rows / trsm launches
+    bool bf_fast_solve = true;         // big fronts: triangular sweeps with the pivot unknowns in shared memory and the factor loads of a
+                                       // block issued ahead of the dependent chain, matrix-vector kernels with batched loads (same
+                                       // operations in the same order: bit-identical to 0 = the round-1 kernels)
+    bool bf_diag_copy = true;          // big fronts, fused panel: the factored diagonal block is handed from the panel launch to the trailing
+                                       // update through a side buffer and copied into place instead of being factored a second time
+    bool bf_lu_lookahead = true;       // big fronts: the reciprocal of pivot k+1 is formed by every thread during the update of pivot k
+                                       // (off the barrier path); same bits
     bool bf_schur = false;             // big fronts: contribution block updated in one pass after the last block column (k_bf_schur).
                                        // Bit-identical and it reads / writes the block once instead of once per block column, but measured
                                        // slower on C4 (11.8 vs 11.1 ms): a block column costs ~40 us of launch + dependent latency whatever
@@ -284,6 +292,7 @@ struct daecpp_b200_ctx : daecpp_b200_options
     daecpp_b200::DevBuf<long long> trace;
     bool jvals_from_triplets = false; // fused assembly reads the staged triplet values directly
     daecpp_b200::DevBuf<double> LU, CB, upd;
+    daecpp_b200::DevBuf<double> bf_diag; // big fronts: factored diagonal block of the current block column, per front of the level (bf_diag_copy)
     double last_alpha = 0.0;
     double alpha_hint = 0.0; // alpha of the factorisation about to follow a symbolic analysis (row matching weights)
 

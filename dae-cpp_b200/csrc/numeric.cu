@@ -166,12 +166,17 @@ constexpr int NB = 32;
 // for its predecessor's memory before touching factor storage.  No-ops in a plain launch.
 __device__ __forceinline__ void bf_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void bf_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <class... P, class... A> inline void bf_launch_pdl_smem(cudaStream_t st, void (*kernel)(P...), dim3 grid, int threads, size_t smem, A... args);
 template <class... P, class... A> inline void bf_launch_pdl(cudaStream_t st, void (*kernel)(P...), dim3 grid, int threads, A... args)
+{
+    bf_launch_pdl_smem(st, kernel, grid, threads, 0, args...);
+}
+template <class... P, class... A> inline void bf_launch_pdl_smem(cudaStream_t st, void (*kernel)(P...), dim3 grid, int threads, size_t smem, A... args)
 {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(threads, 1, 1);
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -270,24 +275,54 @@ __global__ void __launch_bounds__(256) k_bf_extend(FrontTables T, int32_t begin,
 // shuffles needs ~1300 cycles per pivot, a full-precision division plus two barriers per pivot ~700.)
 // The operations per element and their order do not depend on nt, so every CTA that repeats the
 // factorisation gets the same bits.  Rinv[k] = 1 / U(k,k), also used by the row solves.
-__device__ __forceinline__ void bf_block_lu(double (*A)[NB + 1], double *Rinv, int nb, int t, int nt, double pivot_tol, int32_t *flags)
+// look: the reciprocal of pivot k+1 is formed by every thread for itself while pivot k is applied --
+// d(k+1) = a(k+1,k+1) - (a(k+1,k) * r(k)) * a(k,k+1), the very operations the element's owner would perform -- so the
+// division runs beside the update instead of between two barriers.  The owner leaves that element alone and one
+// thread stores d(k) at the start of step k, when nobody reads it any more.  Same bits either way.
+__device__ __forceinline__ void bf_block_lu(double (*A)[NB + 1], double *Rinv, int nb, int t, int nt, double pivot_tol, int32_t *flags,
+                                            bool look = false)
 {
     bool bad = false;
     const int i = t % NB;
+    double d_cur = 1.0, r_cur = 1.0;
+    if (look && nb > 0)
+    {
+        d_cur = A[0][0];
+        bad = !(fabs(d_cur) > pivot_tol) || isinf(d_cur);
+        r_cur = 1.0 / d_cur;
+    }
 #pragma unroll 1
     for (int k = 0; k < nb; ++k)
     {
-        const double d = A[k][k];
-        bad = bad || !(fabs(d) > pivot_tol) || isinf(d);
-        const double r = 1.0 / d;
+        double r;
+        if (look)
+        {
+            r = r_cur;
+            if (t == 0) A[k][k] = d_cur;
+        }
+        else
+        {
+            const double d = A[k][k];
+            bad = bad || !(fabs(d) > pivot_tol) || isinf(d);
+            r = 1.0 / d;
+        }
         // each thread keeps the same (i, j) elements for every pivot; the loop is unrolled so that all
         // shared-memory loads of a step are issued together, behind the reciprocal
-        const double l = A[i][k] * r;
+        const double l = __dmul_rn(A[i][k], r);
+        const bool more = look && k + 1 < nb;
+        double dn = 1.0;
+        if (more) dn = __fma_rn(-__dmul_rn(A[k + 1][k], r), A[k][k + 1], A[k + 1][k + 1]);
 #pragma unroll
         for (int m = 0; m < NB / 4; ++m)
         {
             const int j = t / NB + m * (nt / NB);
-            if (j < NB && j > k && i > k) A[i][j] -= l * A[k][j];
+            if (j < NB && j > k && i > k && !(more && i == k + 1 && j == k + 1)) A[i][j] = __fma_rn(-l, A[k][j], A[i][j]);
+        }
+        if (more)
+        {
+            bad = bad || !(fabs(dn) > pivot_tol) || isinf(dn);
+            d_cur = dn;
+            r_cur = 1.0 / dn;
         }
         __syncthreads();
     }
@@ -375,7 +410,7 @@ __device__ __forceinline__ void bf_store_diag(const double (*A)[NB + 1], const F
 
 // panel, step 1 (separate-launch variant): LU of the NB x NB diagonal block, one CTA per front
 __global__ void __launch_bounds__(128) k_bf_diag(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
-                                                 double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags)
+                                                 double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags, bool look)
 {
     const int32_t f = T.level_sn[begin + blockIdx.x];
     const FrontRef F = front_ref(T, f, LU, CB);
@@ -385,7 +420,7 @@ __global__ void __launch_bounds__(128) k_bf_diag(FrontTables T, int32_t begin, i
     __shared__ double Rinv[NB];
     const int t = threadIdx.x;
     bf_load_diag<128>(A, F, k0, nb, t);
-    bf_block_lu(A, Rinv, nb, t, 128, pivot_tol, flags);
+    bf_block_lu(A, Rinv, nb, t, 128, pivot_tol, flags, look);
     bf_store_diag(A, F, k0, nb, t, 128);
 }
 
@@ -431,9 +466,11 @@ __global__ void __launch_bounds__(128) k_bf_trsm(FrontTables T, int32_t begin, i
 // -- 2 us of redundant work instead of a dependent launch -- and then solves its 128 rows of L21
 // (even blockIdx.x) or its 128 columns of U12 (odd blockIdx.x) out of registers.  The factored
 // diagonal block is written back by the trailing update's first CTA (k_bf_gemm), when no CTA of this
-// launch can still be reading the unfactored one.
+// launch can still be reading the unfactored one: factored a second time there (diagbuf == nullptr), or -- the
+// front's first CTA of this launch leaves its copy in diagbuf and reports the pivots -- just copied into place.
 __global__ void __launch_bounds__(128) k_bf_panel(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
-                                                  double *__restrict__ CB)
+                                                  double *__restrict__ CB, double *__restrict__ diagbuf, double pivot_tol,
+                                                  int32_t *__restrict__ flags, bool look)
 {
     const int32_t f = T.level_sn[begin + blockIdx.y];
     const FrontRef F = front_ref(T, f, LU, CB);
@@ -465,7 +502,14 @@ __global__ void __launch_bounds__(128) k_bf_panel(FrontTables T, int32_t begin, 
         }
     }
     bf_load_diag<128>(A, F, k0, nb, t);
-    bf_block_lu(A, Rinv, nb, t, 128, 0.0, nullptr);
+    const bool keeper = diagbuf != nullptr && blockIdx.x == 0;
+    bf_block_lu(A, Rinv, nb, t, 128, keeper ? pivot_tol : 0.0, keeper ? flags : nullptr, look);
+    if (keeper)
+    {
+        double *D = diagbuf + (int64_t)blockIdx.y * (NB * NB);
+#pragma unroll
+        for (int e = t; e < NB * NB; e += 128) D[e] = A[e % NB][e / NB];
+    }
     bf_fill_pad(P, A, rows, t, 128);
     if (q < F.ld) bf_panel_solve(F, P, Rinv, rows, k0, nb, q);
 }
@@ -485,7 +529,8 @@ __device__ __forceinline__ void dmma884(double &d0, double &d1, double a, double
 // pivot block -- is updated per block column; the contribution block gets all its updates in one pass at the end (k_bf_schur).
 template <bool DMMA>
 __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, int32_t k0, double *__restrict__ LU,
-                                                 double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags, int32_t strip)
+                                                 double *__restrict__ CB, double pivot_tol, int32_t *__restrict__ flags, int32_t strip,
+                                                 const double *__restrict__ diagbuf, bool look)
 {
     const int32_t f = T.level_sn[begin + blockIdx.z];
     const FrontRef F = front_ref(T, f, LU, CB);
@@ -499,10 +544,24 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
     {   // one extra CTA per front (fused panel): the panel launch is complete, nobody reads the unfactored
         // diagonal block any more, so it is factored once more and written back -- beside the tiles, not before one
         if (blockIdx.y != 0) return;
+        if (diagbuf && k1 < F.ld)
+        {   // the panel launch kept its factored copy (and reported the pivots)
+            const double *D = diagbuf + (int64_t)blockIdx.z * (NB * NB);
+            double v[NB * NB / 256];
+#pragma unroll
+            for (int it = 0; it < NB * NB / 256; ++it) v[it] = D[t + it * 256];
+#pragma unroll
+            for (int it = 0; it < NB * NB / 256; ++it)
+            {
+                const int e = t + it * 256, i = e % NB, j = e / NB;
+                if (i < nb && j < nb) F.Lp[(int64_t)(k0 + j) * F.ld + (k0 + i)] = v[it];
+            }
+            return;
+        }
         __shared__ double Dg[NB][NB + 1];
         __shared__ double Rinv[NB];
         bf_load_diag<256>(Dg, F, k0, nb, t);
-        bf_block_lu(Dg, Rinv, nb, t, 256, pivot_tol, flags);
+        bf_block_lu(Dg, Rinv, nb, t, 256, pivot_tol, flags, look);
         bf_store_diag(Dg, F, k0, nb, t, 256);
         return;
     }
@@ -510,6 +569,26 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
     if (strip && i0 >= F.s && j0 >= F.s) return; // the tile lies inside the contribution block
     constexpr int LDS = DMMA ? 68 : 65;
     __shared__ double A[NB][LDS], Bm[NB][LDS];
+    // DMMA: the read-modify-write of the tile -- addresses and old values (independent loads) requested first, so that
+    // they travel together with the operands instead of after the barrier behind them
+    const int w = t >> 5, lane = t & 31, g = lane >> 2, c = lane & 3;
+    const int wi = (w & 3) * 16, wj = (w >> 2) * 32;
+    double *dst[2][4][2];
+    double old[2][4][2];
+    if (DMMA)
+    {
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+            for (int nj = 0; nj < 4; ++nj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+                {
+                    const int32_t i = i0 + wi + mi * 8 + g, j = j0 + wj + nj * 8 + 2 * c + e;
+                    dst[mi][nj][e] = (i < F.ld && j < F.ld && !(strip && i >= F.s && j >= F.s)) ? fr_at(F, i, j) : nullptr;
+                    old[mi][nj][e] = dst[mi][nj][e] ? *dst[mi][nj][e] : 0.0;
+                }
+    }
     {   // operands: all 2 x 8 loads of a thread in flight before the first shared-memory store
         constexpr int IT = NB * 64 / 256;
         double va[IT], vb[IT];
@@ -535,27 +614,11 @@ __global__ void __launch_bounds__(256) k_bf_gemm(FrontTables T, int32_t begin, i
     __syncthreads();
     if (DMMA)
     {
-        const int w = t >> 5, lane = t & 31, g = lane >> 2, c = lane & 3;
-        const int wi = (w & 3) * 16, wj = (w >> 2) * 32;
         double acc[2][4][2];
 #pragma unroll
         for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
             for (int nj = 0; nj < 4; ++nj) acc[mi][nj][0] = acc[mi][nj][1] = 0.0;
-        // the read-modify-write of the tile: addresses and old values first (independent loads), behind the MMAs
-        double *dst[2][4][2];
-        double old[2][4][2];
-#pragma unroll
-        for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-            for (int nj = 0; nj < 4; ++nj)
-#pragma unroll
-                for (int e = 0; e < 2; ++e)
-                {
-                    const int32_t i = i0 + wi + mi * 8 + g, j = j0 + wj + nj * 8 + 2 * c + e;
-                    dst[mi][nj][e] = (i < F.ld && j < F.ld && !(strip && i >= F.s && j >= F.s)) ? fr_at(F, i, j) : nullptr;
-                    old[mi][nj][e] = dst[mi][nj][e] ? *dst[mi][nj][e] : 0.0;
-                }
 #pragma unroll
         for (int kk = 0; kk < NB; kk += 4)
         {
@@ -999,6 +1062,361 @@ __global__ void __launch_bounds__(512) k_bf_backward_tri(FrontTables T, int32_t 
     }
 }
 
+// ---- the same sweeps with the memory latency taken out of the dependent chain (option bf_fast_solve) --------------------
+// Every operation of the kernels above in the same order, so the results are the same bits.  What changes: the pivot
+// unknowns of the front live in shared memory for the whole sweep (the round-1 kernels went through global memory twice
+// per block of NB pivots), the factor entries a block needs -- the diagonal block of warp 0, one panel row per thread -- are
+// loaded BEFORE the chain they do not depend on (next block's diagonal block while this block's rows are applied), and
+// the matrix-vector kernels issue their loads in batches of 16 instead of two per loop trip.
+constexpr int TRI_T = 256, TRI_W = TRI_T / 32;
+
+// Loads the compiler must not sink towards their uses (it serialised the batches of the matrix-vector kernels into
+// load - multiply-add pairs, one memory round trip each): volatile asm keeps the requests together, in program order.
+__device__ __forceinline__ double ld_nc_f64(const double *p)
+{
+    double v;
+    asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ double ld_f64(const double *p)
+{
+    double v;
+    asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ int32_t ld_nc_s32(const int32_t *p)
+{
+    int32_t v;
+    asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+
+// Block b of NB pivots belongs to warp b % TRI_W, which holds the block's triangle in registers from the start of the
+// kernel (the factors are final long before the sweep: requested before the wait for the level below) -- no memory
+// round trip sits between two dependent chains any more.
+__global__ void __launch_bounds__(TRI_T) k_bf_forward_tri2(FrontTables T, int32_t begin, const double *__restrict__ LU,
+                                                           double *__restrict__ upd, double *__restrict__ y)
+{
+    extern __shared__ double ys[]; // the front's pivot unknowns
+    const int32_t f = T.level_sn[begin + blockIdx.x];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int32_t first = T.sn_first[f];
+    const int32_t s = T.sn_first[f + 1] - first;
+    const int64_t rp0 = T.sn_rowptr[f];
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - rp0);
+    const int32_t ld = s + r;
+    const double *Lp = LU + T.sn_lu[f];
+    double *u = upd + rp0;
+    double *y1 = y + first;
+    const int32_t cb = T.child_ptr[f], ce = T.child_ptr[f + 1];
+    // the first children's table entries, all requested together
+    constexpr int PC = 4;
+    int64_t c_rp[PC];
+    int32_t c_rc[PC];
+#pragma unroll
+    for (int q = 0; q < PC; ++q)
+    {
+        c_rp[q] = 0; c_rc[q] = 0;
+        if (cb + q < ce)
+        {
+            const int32_t c = T.child_idx[cb + q];
+            c_rp[q] = T.sn_rowptr[c];
+            c_rc[q] = (int32_t)(T.sn_rowptr[c + 1] - c_rp[q]);
+        }
+    }
+    __shared__ double yb[NB];
+    double l[NB];  // the warp's block: lane i holds row i of the unit lower triangle
+    double lv[NB]; // every thread: its row of the panel below the current block
+    auto load_block = [&](int32_t k0) {
+        const int32_t k1 = min(k0 + NB, s), i = k0 + lane;
+#pragma unroll
+        for (int q = 0; q < NB; ++q) l[q] = (i < k1 && q < lane) ? Lp[(int64_t)(k0 + q) * ld + i] : 0.0;
+    };
+    if (w * NB < s) load_block(w * NB);
+    bf_pdl_trigger();
+    bf_pdl_wait();
+    for (int32_t a = t; a < s; a += TRI_T) ys[a] = y1[a];
+    for (int32_t a = t; a < r; a += TRI_T) u[a] = 0.0;
+    __syncthreads();
+    for (int32_t ci = cb; ci < ce; ++ci)
+    {
+        int64_t rp; int32_t rc;
+        if (ci - cb < PC) { rp = c_rp[0]; rc = c_rc[0]; }
+        else { const int32_t c = T.child_idx[ci]; rp = T.sn_rowptr[c]; rc = (int32_t)(T.sn_rowptr[c + 1] - rp); }
+#pragma unroll
+        for (int q = 0; q + 1 < PC; ++q) { c_rp[q] = c_rp[q + 1]; c_rc[q] = c_rc[q + 1]; }
+        const double *uc = upd + rp;
+        const int32_t *rel = T.sn_rel + rp;
+        for (int32_t a = t; a < rc; a += TRI_T)
+        {
+            const int32_t ra = rel[a];
+            if (ra < s) ys[ra] += uc[a]; else u[ra - s] += uc[a];
+        }
+        __syncthreads();
+    }
+    int32_t blk = 0;
+    for (int32_t k0 = 0; k0 < s; k0 += NB, ++blk)
+    {
+        const int32_t k1 = min(k0 + NB, s);
+        const int32_t i = k1 + t;
+        if (i < s)
+        {
+#pragma unroll
+            for (int q = 0; q < NB; ++q) lv[q] = (k0 + q < k1) ? Lp[(int64_t)(k0 + q) * ld + i] : 0.0;
+        }
+        if (w == (blk % TRI_W))
+        {
+            const int32_t ib = k0 + lane;
+            double yi = (ib < k1) ? ys[ib] : 0.0;
+#pragma unroll
+            for (int q = 0; q < NB; ++q)
+            {
+                const double yk = __shfl_sync(0xffffffffu, yi, q);
+                if (q < lane) yi -= l[q] * yk;
+            }
+            if (ib < k1) { ys[ib] = yi; yb[lane] = yi; }
+            if (k0 + TRI_W * NB < s) load_block(k0 + TRI_W * NB); // the warp's next block, TRI_W blocks ahead
+        }
+        __syncthreads();
+        if (i < s)
+        {
+            double acc = 0.0;
+#pragma unroll
+            for (int q = 0; q < NB; ++q) acc += lv[q] * ((k0 + q < k1) ? yb[q] : 0.0);
+            ys[i] -= acc;
+        }
+        for (int32_t i2 = i + TRI_T; i2 < s; i2 += TRI_T)
+        {
+            double lw[NB];
+#pragma unroll
+            for (int q = 0; q < NB; ++q) lw[q] = (k0 + q < k1) ? Lp[(int64_t)(k0 + q) * ld + i2] : 0.0;
+            double acc = 0.0;
+#pragma unroll
+            for (int q = 0; q < NB; ++q) acc += lw[q] * ((k0 + q < k1) ? yb[q] : 0.0);
+            ys[i2] -= acc;
+        }
+        __syncthreads();
+    }
+    for (int32_t a = t; a < s; a += TRI_T) y1[a] = ys[a];
+}
+
+__global__ void __launch_bounds__(GV_ROWS *GV_SEG) k_bf_forward_gemv2(FrontTables T, int32_t begin, const double *__restrict__ LU,
+                                                                      double *__restrict__ upd, const double *__restrict__ y)
+{
+    extern __shared__ double ysh[]; // the front's pivot unknowns
+    const int32_t f = T.level_sn[begin + blockIdx.y];
+    const int32_t first = T.sn_first[f];
+    const int32_t s = T.sn_first[f + 1] - first;
+    const int64_t rp0 = T.sn_rowptr[f];
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - rp0);
+    const int32_t a0 = blockIdx.x * GV_ROWS;
+    if (a0 >= r) return;
+    const int32_t ld = s + r;
+    const double *Lp = LU + T.sn_lu[f];
+    const double *y1 = y + first;
+    const int ri = threadIdx.x % GV_ROWS, seg = threadIdx.x / GV_ROWS;
+    const int32_t a = a0 + ri;
+    constexpr int UB = 8;
+    const double *row = Lp + s + min(a, r - 1);
+    // the factors are final: the first batch travels while the level below finishes
+    double v0[UB], v1[UB];
+    const bool first_batch = seg + (2 * UB - 1) * GV_SEG < s;
+    if (first_batch)
+    {
+#pragma unroll
+        for (int q = 0; q < UB; ++q)
+        {
+            v0[q] = ld_nc_f64(row + (int64_t)(seg + 2 * q * GV_SEG) * ld);
+            v1[q] = ld_nc_f64(row + (int64_t)(seg + (2 * q + 1) * GV_SEG) * ld);
+        }
+    }
+    bf_pdl_trigger();
+    bf_pdl_wait();
+    __shared__ double part[GV_SEG][GV_ROWS];
+    for (int32_t k = threadIdx.x; k < s; k += GV_ROWS * GV_SEG) ysh[k] = y1[k];
+    __syncthreads();
+    double acc0 = 0.0, acc1 = 0.0;
+    if (a < r)
+    {
+        int32_t k = seg;
+        for (; k + (2 * UB - 1) * GV_SEG < s; k += 2 * UB * GV_SEG)
+        {
+            if (k != seg)
+            {
+#pragma unroll
+                for (int q = 0; q < UB; ++q)
+                {
+                    v0[q] = ld_nc_f64(row + (int64_t)(k + 2 * q * GV_SEG) * ld);
+                    v1[q] = ld_nc_f64(row + (int64_t)(k + (2 * q + 1) * GV_SEG) * ld);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < UB; ++q)
+            {
+                acc0 += v0[q] * ysh[k + 2 * q * GV_SEG];
+                acc1 += v1[q] * ysh[k + (2 * q + 1) * GV_SEG];
+            }
+        }
+        for (; k + GV_SEG < s; k += 2 * GV_SEG)
+        {
+            acc0 += row[(int64_t)k * ld] * ysh[k];
+            acc1 += row[(int64_t)(k + GV_SEG) * ld] * ysh[k + GV_SEG];
+        }
+        if (k < s) acc0 += row[(int64_t)k * ld] * ysh[k];
+    }
+    part[seg][ri] = acc0 + acc1;
+    __syncthreads();
+    if (seg == 0 && a < r)
+    {
+        double sum = part[0][ri];
+#pragma unroll
+        for (int q = 1; q < GV_SEG; ++q) sum += part[q][ri];
+        upd[rp0 + a] -= sum;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_bf_backward_gemv2(FrontTables T, int32_t begin, const double *__restrict__ LU,
+                                                           double *__restrict__ y)
+{
+    const int32_t f = T.level_sn[begin + blockIdx.y];
+    const int lane = threadIdx.x % 32, wid = threadIdx.x / 32;
+    const int32_t first = T.sn_first[f];
+    const int32_t s = T.sn_first[f + 1] - first;
+    const int32_t k = blockIdx.x * 8 + wid;
+    if (k >= s) return;
+    const int64_t rp0 = T.sn_rowptr[f];
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - rp0);
+    if (r == 0) return;
+    const int32_t ld = s + r;
+    const double *utk = LU + T.sn_lu[f] + (int64_t)ld * s + (int64_t)k * r;
+    const int32_t *rows = T.sn_rows + rp0;
+    // row indices and factor entries are static: the first batch is requested before the wait for the level above
+    constexpr int UB = 4;
+    int32_t i0[UB], i1[UB];
+    double v0[UB], v1[UB];
+    const bool first_batch = lane + 64 * (UB - 1) + 32 < r;
+    if (first_batch)
+    {
+#pragma unroll
+        for (int q = 0; q < UB; ++q)
+        {
+            i0[q] = ld_nc_s32(rows + lane + 64 * q);
+            i1[q] = ld_nc_s32(rows + lane + 64 * q + 32);
+            v0[q] = ld_nc_f64(utk + lane + 64 * q);
+            v1[q] = ld_nc_f64(utk + lane + 64 * q + 32);
+        }
+    }
+    bf_pdl_trigger();
+    bf_pdl_wait();
+    double acc0 = 0.0, acc1 = 0.0;
+    int32_t a = lane;
+    for (; a + 64 * (UB - 1) + 32 < r; a += 64 * UB)
+    {
+        double x0[UB], x1[UB];
+        if (a != lane)
+        {
+#pragma unroll
+            for (int q = 0; q < UB; ++q)
+            {
+                i0[q] = ld_nc_s32(rows + a + 64 * q);
+                i1[q] = ld_nc_s32(rows + a + 64 * q + 32);
+                v0[q] = ld_nc_f64(utk + a + 64 * q);
+                v1[q] = ld_nc_f64(utk + a + 64 * q + 32);
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < UB; ++q) { x0[q] = ld_f64(y + i0[q]); x1[q] = ld_f64(y + i1[q]); }
+#pragma unroll
+        for (int q = 0; q < UB; ++q) { acc0 += v0[q] * x0[q]; acc1 += v1[q] * x1[q]; }
+    }
+    for (; a + 32 < r; a += 64)
+    {
+        acc0 += utk[a] * y[rows[a]];
+        acc1 += utk[a + 32] * y[rows[a + 32]];
+    }
+    if (a < r) acc0 += utk[a] * y[rows[a]];
+    double acc = acc0 + acc1;
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) y[first + k] -= acc;
+}
+
+__global__ void __launch_bounds__(TRI_T) k_bf_backward_tri2(FrontTables T, int32_t begin, const double *__restrict__ LU,
+                                                            double *__restrict__ y)
+{
+    extern __shared__ double ys[];
+    const int32_t f = T.level_sn[begin + blockIdx.x];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int32_t first = T.sn_first[f];
+    const int32_t s = T.sn_first[f + 1] - first;
+    const int32_t r = (int32_t)(T.sn_rowptr[f + 1] - T.sn_rowptr[f]);
+    const int32_t ld = s + r;
+    const double *Lp = LU + T.sn_lu[f];
+    double *y1 = y + first;
+    __shared__ double xb[NB];
+    double uu[NB], uv[NB];
+    double rinv = 1.0;
+    // blocks are counted from the end of the pivot range; block b belongs to warp b % TRI_W, which holds its triangle
+    // and the reciprocals of its pivots from the start of the kernel
+    auto load_block = [&](int32_t k1) {
+        const int32_t k0 = max(k1 - NB, 0), i = k0 + lane, nb = k1 - k0;
+#pragma unroll
+        for (int q = 0; q < NB; ++q) uu[q] = (q < nb && lane <= q) ? Lp[(int64_t)(k0 + q) * ld + i] : 1.0;
+        rinv = 1.0 / ((i < k1) ? Lp[(int64_t)i * ld + i] : 1.0);
+    };
+    if (s - w * NB > 0) load_block(s - w * NB);
+    bf_pdl_trigger();
+    bf_pdl_wait();
+    for (int32_t a = t; a < s; a += TRI_T) ys[a] = y1[a];
+    __syncthreads();
+    int32_t blk = 0;
+    for (int32_t k1 = s; k1 > 0; k1 -= NB, ++blk)
+    {
+        const int32_t k0 = max(k1 - NB, 0);
+        if (t < k0)
+        {
+#pragma unroll
+            for (int q = 0; q < NB; ++q) uv[q] = (k0 + q < k1) ? Lp[(int64_t)(k0 + q) * ld + t] : 0.0;
+        }
+        if (w == (blk % TRI_W))
+        {
+            const int32_t i = k0 + lane, nb = k1 - k0;
+            double yi = (i < k1) ? ys[i] : 0.0;
+#pragma unroll
+            for (int q = NB - 1; q >= 0; --q)
+            {
+                if (q < nb)
+                {
+                    if (lane == q) yi = yi * rinv;
+                    const double xj = __shfl_sync(0xffffffffu, yi, q);
+                    if (lane < q) yi -= uu[q] * xj;
+                }
+            }
+            if (i < k1) { ys[i] = yi; xb[lane] = yi; }
+            if (k1 - TRI_W * NB > 0) load_block(k1 - TRI_W * NB);
+        }
+        __syncthreads();
+        if (t < k0)
+        {
+            double acc = 0.0;
+#pragma unroll
+            for (int q = 0; q < NB; ++q) acc += uv[q] * ((k0 + q < k1) ? xb[q] : 0.0);
+            ys[t] -= acc;
+        }
+        for (int32_t i2 = t + TRI_T; i2 < k0; i2 += TRI_T)
+        {
+            double uw[NB];
+#pragma unroll
+            for (int q = 0; q < NB; ++q) uw[q] = (k0 + q < k1) ? Lp[(int64_t)(k0 + q) * ld + i2] : 0.0;
+            double acc = 0.0;
+#pragma unroll
+            for (int q = 0; q < NB; ++q) acc += uw[q] * ((k0 + q < k1) ? xb[q] : 0.0);
+            ys[i2] -= acc;
+        }
+        __syncthreads();
+    }
+    for (int32_t a = t; a < s; a += TRI_T) y1[a] = ys[a];
+}
+
 FrontTables tables(daecpp_b200_ctx *c)
 {
     FrontTables T;
@@ -1130,13 +1548,24 @@ int upload_symbolic(daecpp_b200_ctx *c)
     DAECPP_CUDA_TRY(c, c->CB.reserve((size_t)S.cb_size + 1));
     DAECPP_CUDA_TRY(c, c->upd.reserve((size_t)S.upd_size + 1));
     c->groups.clear();
+    int32_t max_level_fronts = 0;
     for (const LaunchGroup &g : S.groups)
     {
         GroupLaunch L;
         L.kind = g.kind; L.begin = g.begin; L.count = g.end - g.begin; L.max_dim = g.max_dim;
         L.group = pick_group(g.max_dim);
+        if (L.kind != 0)
+            for (int32_t q = 0; q < L.count; ++q)
+            {
+                const int32_t f = S.big_sn[L.begin + q];
+                L.max_s = std::max(L.max_s, S.s_of(f));
+                L.max_r = std::max(L.max_r, S.r_of(f));
+                L.max_children = std::max(L.max_children, S.child_ptr[f + 1] - S.child_ptr[f]);
+                max_level_fronts = std::max(max_level_fronts, L.count);
+            }
         c->groups.push_back(L);
     }
+    if (max_level_fronts) DAECPP_CUDA_TRY(c, c->bf_diag.reserve((size_t)max_level_fronts * NB * NB));
     // the fused assembly reads the staged triplet values when every slot has exactly one triplet
     c->jvals_from_triplets = !c->direct_csc && c->J.no_duplicates && c->J.nnz > 0;
     if ((rc = unit_setup(c))) return rc;
@@ -1213,21 +1642,9 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
         }
         else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
         {   // blocked right-looking LU, all fronts of the level in the same launches
-            int32_t max_s = 0, max_ld = 0;
-            for (int32_t q = 0; q < L.count; ++q)
-            {
-                const int32_t f = S.big_sn[L.begin + q];
-                max_s = std::max(max_s, S.s_of(f));
-                max_ld = std::max(max_ld, S.s_of(f) + S.r_of(f));
-            }
-            int32_t max_children = 0;
-            for (int32_t q = 0; q < L.count; ++q)
-            {
-                const int32_t f = S.big_sn[L.begin + q];
-                max_children = std::max(max_children, S.child_ptr[f + 1] - S.child_ptr[f]);
-            }
-            int32_t max_r = 0;
-            for (int32_t q = 0; q < L.count; ++q) max_r = std::max(max_r, S.r_of(S.big_sn[L.begin + q]));
+            const int32_t max_s = L.max_s, max_ld = L.max_dim, max_children = L.max_children, max_r = L.max_r;
+            const bool look = c->bf_lu_lookahead;
+            double *dbuf = c->bf_diag_copy ? c->bf_diag.p : nullptr;
             // contribution blocks updated once, behind the last block column (k_bf_schur), not once per block column
             const int32_t strip = (c->bf_schur && c->bf_dmma && max_r > 0) ? 1 : 0;
             bf_launch_pdl(st, k_bf_zero, dim3(64, L.count), 256, T, L.begin, c->CB.p);
@@ -1246,14 +1663,14 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
                 }
                 if (rest <= 0 || !c->bf_fused_panel)
                 {
-                    k_bf_diag<<<L.count, 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
+                    k_bf_diag<<<L.count, 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, look);
                     c->kernels += 1;
                     if (rest <= 0) continue;
                     k_bf_rows<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                     k_bf_trsm<<<dim3((rest + 127) / 128, L.count), 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
                     const int tiles = (rest + 63) / 64;
-                    if (c->bf_dmma) k_bf_gemm<true><<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr, strip);
-                    else k_bf_gemm<false><<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr, strip);
+                    if (c->bf_dmma) k_bf_gemm<true><<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr, strip, nullptr, look);
+                    else k_bf_gemm<false><<<dim3(tiles, tiles, L.count), 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, 0.0, nullptr, strip, nullptr, look);
                     c->kernels += 3;
                     continue;
                 }
@@ -1262,15 +1679,15 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
                 const dim3 gp(2 * ((rest + 127) / 128), L.count), gg(tiles + 1, tiles, L.count);
                 if (c->bf_pdl)
                 {
-                    bf_launch_pdl(st, k_bf_panel, gp, 128, T, L.begin, k0, c->LU.p, c->CB.p);
-                    if (c->bf_dmma) bf_launch_pdl(st, k_bf_gemm<true>, gg, 256, T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip);
-                    else bf_launch_pdl(st, k_bf_gemm<false>, gg, 256, T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip);
+                    bf_launch_pdl(st, k_bf_panel, gp, 128, T, L.begin, k0, c->LU.p, c->CB.p, dbuf, c->pivot_tol, c->d_flags, look);
+                    if (c->bf_dmma) bf_launch_pdl(st, k_bf_gemm<true>, gg, 256, T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip, dbuf, look);
+                    else bf_launch_pdl(st, k_bf_gemm<false>, gg, 256, T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip, dbuf, look);
                 }
                 else
                 {
-                    k_bf_panel<<<gp, 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p);
-                    if (c->bf_dmma) k_bf_gemm<true><<<gg, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip);
-                    else k_bf_gemm<false><<<gg, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip);
+                    k_bf_panel<<<gp, 128, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, dbuf, c->pivot_tol, c->d_flags, look);
+                    if (c->bf_dmma) k_bf_gemm<true><<<gg, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip, dbuf, look);
+                    else k_bf_gemm<false><<<gg, 256, 0, st>>>(T, L.begin, k0, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags, strip, dbuf, look);
                 }
                 c->kernels += 2;
             }
@@ -1342,6 +1759,15 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
         if (L.kind == 0) { if ((rc = launch_unit_forward(c, L, direct))) return rc; }
         else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
         {
+            const size_t ysm = sizeof(double) * (size_t)L.max_s;
+            if (c->bf_fast_solve && ysm <= 40 * 1024)
+            {
+                bf_launch_pdl_smem(st, k_bf_forward_tri2, dim3(L.count), TRI_T, ysm, T, L.begin, c->LU.p, c->upd.p, c->work);
+                if (L.max_r > 0)
+                    bf_launch_pdl_smem(st, k_bf_forward_gemv2, dim3((L.max_r + GV_ROWS - 1) / GV_ROWS, L.count), GV_ROWS * GV_SEG, ysm, T, L.begin, c->LU.p, c->upd.p, c->work);
+                c->kernels += L.max_r > 0 ? 2 : 1;
+                continue;
+            }
             bf_launch_pdl(st, k_bf_forward_tri, dim3(L.count), 512, T, L.begin, c->LU.p, c->upd.p, c->work);
             bf_launch_pdl(st, k_bf_forward_gemv, dim3((L.max_dim + GV_ROWS - 1) / GV_ROWS, L.count), GV_ROWS * GV_SEG, T, L.begin, c->LU.p, c->upd.p, c->work);
             c->kernels += 2;
@@ -1358,6 +1784,14 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
         if (L.kind == 0) { if ((rc = launch_unit_backward(c, L, direct, fuse_update, atol, rtol, max_err_abs))) return rc; }
         else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
         {
+            const size_t ysm = sizeof(double) * (size_t)L.max_s;
+            if (c->bf_fast_solve && ysm <= 40 * 1024)
+            {
+                if (L.max_r > 0) bf_launch_pdl(st, k_bf_backward_gemv2, dim3((L.max_s + 7) / 8, L.count), 256, T, L.begin, c->LU.p, c->work);
+                bf_launch_pdl_smem(st, k_bf_backward_tri2, dim3(L.count), TRI_T, ysm, T, L.begin, c->LU.p, c->work);
+                c->kernels += L.max_r > 0 ? 2 : 1;
+                continue;
+            }
             bf_launch_pdl(st, k_bf_backward_gemv, dim3((L.max_dim + 7) / 8, L.count), 256, T, L.begin, c->LU.p, c->work);
             bf_launch_pdl(st, k_bf_backward_tri, dim3(L.count), 512, T, L.begin, c->LU.p, c->work);
             c->kernels += 2;

@@ -74,7 +74,7 @@ DAE_HD void factor_front(const P &p, const int32_t *B, const int32_t *F, double 
         const double piv = colk[k];
         if (lane == 0 && (!(fabs(piv) > pivot_tol) || std::isinf(piv))) *fail = 1;
         const double inv = 1.0 / piv;
-        p.sync(); // everybody has read the pivot before the column is scaled
+        // (no barrier here: the scaling below leaves the pivot itself alone, and the last update ended with one)
         for (int32_t i = k + 1 + lane; i < d; i += G) colk[i] *= inv;
         p.sync();
         const int32_t m = d - k - 1;

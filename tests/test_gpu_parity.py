@@ -466,3 +466,53 @@ def test_linear_solve_grid2d_default_options(m):
     u = P.grid2d_state(m)
     x, st = _solve_and_check(n, P.grid2d_jacobian(u, m), P.identity_mass(n), 50.0, options={"chain": 0})
     assert st["n_big_fronts"] > 0
+
+
+def _grid_solve_bytes(m, options, zero_row=None):
+    n = m * m
+    u = P.grid2d_state(m)
+    A, I, Jc = P.grid2d_jacobian(u, m)
+    if zero_row is not None:
+        A = A.copy(); A[I == zero_row] = 0.0
+    c = B.Context(n)
+    c.set_option("chain", 0)
+    for k, v in options.items():
+        c.set_option(k, v)
+    c.set_mass(P.identity_mass(n) if zero_row is None else EMPTY); c.set_jacobian((A, I, Jc))
+    rc = c.refactor(50.0 if zero_row is None else 0.0, allow=(B.EDECOMP,))
+    out = None
+    if rc == 0:
+        c.set_rhs(np.full(n, 1.24))
+        out = c.solve().tobytes()
+    assert c.stat("max_front") >= 96
+    c.close()
+    return rc, out
+
+
+@pytest.mark.parametrize("m", [160, 300])
+def test_big_front_latency_variants_are_bit_identical(m):
+    """Round-2 latency work on the big fronts -- triangular sweeps with the pivot unknowns in shared memory and batched
+    loads (bf_fast_solve), the factored diagonal block handed from the panel launch to the trailing update instead of
+    being factored twice (bf_diag_copy), the next pivot's reciprocal formed beside the update (bf_lu_lookahead) -- performs
+    the same operations in the same order: each switch alone and all together give the bits of the round-1 kernels."""
+    base = {"bf_fast_solve": 0, "bf_diag_copy": 0, "bf_lu_lookahead": 0}
+    rc0, ref = _grid_solve_bytes(m, base)
+    assert rc0 == 0
+    for on in (("bf_fast_solve",), ("bf_diag_copy",), ("bf_lu_lookahead",), ("bf_fast_solve", "bf_diag_copy", "bf_lu_lookahead")):
+        rc, got = _grid_solve_bytes(m, {**base, **{k: 1 for k in on}})
+        assert rc == 0 and got == ref, on
+    rc, got = _grid_solve_bytes(m, {**base, "bf_diag_copy": 1, "bf_lu_lookahead": 1, "bf_fused_panel": 0})
+    assert rc == 0 and got == ref
+
+
+@pytest.mark.parametrize("opts", [{}, {"bf_diag_copy": 0, "bf_lu_lookahead": 0}, {"bf_diag_copy": 1, "bf_lu_lookahead": 0},
+                                  {"bf_diag_copy": 0, "bf_lu_lookahead": 1}, {"bf_fused_panel": 0}])
+def test_big_front_zero_pivot_is_reported(opts):
+    """A numerically empty row in the top separator: its pivot is exactly zero when its block column is reached, whichever
+    launch factors the diagonal block (panel CTA that keeps the copy, trailing update's extra CTA, separate launch)."""
+    m = 160
+    mid = (m // 2) * m + m // 2
+    rc, _ = _grid_solve_bytes(m, opts, zero_row=mid)
+    assert rc == B.EDECOMP
+    rc, _ = _grid_solve_bytes(m, opts, zero_row=m * m - 1)
+    assert rc == B.EDECOMP
