@@ -239,7 +239,7 @@ class Context:
         self._ck(self.lib.daecpp_b200_debug_unit_trace(self.h, None, 0, C.byref(cnt)))
         out = np.zeros(max(cnt.value, 1), np.int64)
         self._ck(self.lib.daecpp_b200_debug_unit_trace(self.h, out.ctypes.data, cnt.value, C.byref(cnt)))
-        return out[:cnt.value].reshape(-1, 4)
+        return out[:cnt.value - cnt.value % 4].reshape(-1, 4)
 
     def event_mark(self):
         self._ck(self.lib.daecpp_b200_event_mark(self.h))

@@ -219,7 +219,9 @@ static void recycle(daecpp_b200_ctx *c)
     if (o.chain_enabled != fresh.chain_enabled || o.chain_min_n != fresh.chain_min_n || o.chain_max_b != fresh.chain_max_b ||
         o.chain_affine != fresh.chain_affine || o.unit_threads != fresh.unit_threads || o.sopt.leaf_size != fresh.sopt.leaf_size ||
         o.sopt.unit_smem_bytes != fresh.sopt.unit_smem_bytes || o.sopt.serial_dim != fresh.sopt.serial_dim ||
-        o.sopt.max_super != fresh.sopt.max_super || o.sopt.transversal != fresh.sopt.transversal)
+        o.sopt.max_super != fresh.sopt.max_super || o.sopt.transversal != fresh.sopt.transversal ||
+        o.sopt.warp_dim != fresh.sopt.warp_dim || o.sopt.warp_dim_many != fresh.sopt.warp_dim_many ||
+        o.sopt.warp_min_fronts != fresh.sopt.warp_min_fronts)
         c->have_symbolic = false;
     o = fresh; // every option back to its default, whatever is added to daecpp_b200_options later
     const daecpp_b200::TinyState tiny_fresh;
@@ -1021,7 +1023,7 @@ int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *c, int64_t *out, int64_t cap, 
     if (!c || !count) return DAECPP_B200_EINVAL;
     cudaSetDevice(c->device);
     // subtree units: factor, forward, backward x 4 stamps; chain path: 5 kernels x tiles x 8 stamps (chain.cu)
-    const int64_t m = c->CH.active ? (int64_t)5 * c->CH.levels[0].ntiles * 8 : (int64_t)c->S.nunit * 12;
+    const int64_t m = c->CH.active ? (int64_t)5 * c->CH.levels[0].ntiles * 8 : (int64_t)c->S.nunit * 12 + 4 + 256; // (+ the per-level stamps of one unit)
     *count = m;
     if (!c->trace.p || !out) return DAECPP_B200_OK;
     DAECPP_CUDA_TRY(c, cudaStreamSynchronize(c->stream));
@@ -1096,8 +1098,15 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     }
     else if (k == "leaf_size") { c->sopt.leaf_size = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "unit_smem_bytes") { c->sopt.unit_smem_bytes = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "warp_dim") { c->sopt.warp_dim = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "warp_dim_many") { c->sopt.warp_dim_many = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "warp_min_fronts") { c->sopt.warp_min_fronts = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "serial_dim") { c->sopt.serial_dim = (int)value; c->have_symbolic = false; c->have_factor = false; }
-    else if (k == "unit_threads") { c->unit_threads = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "unit_threads")
+    {
+        if (value < 32 || value > 256 || ((int)value & 31)) return fail(c, DAECPP_B200_EINVAL, "unit_threads: a multiple of 32 up to 256");
+        c->unit_threads = (int)value; c->have_symbolic = false; c->have_factor = false;
+    }
     else if (k == "pinned_io") c->pinned_io = value != 0.0;
     else if (k == "chain") { c->chain_enabled = value != 0.0; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "lean_flags") c->lean_flags = value != 0.0;
@@ -1125,6 +1134,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "chain_min_n") { c->chain_min_n = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "chain_max_block") { c->chain_max_b = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "trace_units") c->trace_units = value != 0.0;
+    else if (k == "trace_unit_index") c->trace_unit_index = (int)value;
     else if (k == "transversal") { c->sopt.transversal = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "pivot_rel") c->pivot_rel = value;
     else if (k == "pipeline_iterations") c->pipeline_iterations = value != 0.0;

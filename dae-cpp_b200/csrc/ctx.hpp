@@ -214,6 +214,7 @@ struct daecpp_b200_options
     bool pinned_io = false;            // host vectors handed to the ABI are page-locked: no staging copies
     bool phase_timing = false;         // per-phase device times of iteration_resident
     bool trace_units = false;          // debug: per-unit globaltimer stamps of the factor kernel
+    int trace_unit_index = 0;          // debug: unit (of the first launch group) whose local levels are stamped one by one
 };
 
 struct daecpp_b200_ctx : daecpp_b200_options

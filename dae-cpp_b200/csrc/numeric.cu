@@ -240,8 +240,8 @@ __global__ void __launch_bounds__(256) k_bf_extend(FrontTables T, int32_t begin,
     for (int32_t bc = blockIdx.x * NW + wid; bc < rc; bc += gridDim.x * NW)
     {
         const int32_t rb = rel[bc];
-        constexpr int U = 4; // independent entries per lane: all loads of a batch first, then the stores
-        for (int32_t a0 = 0; a0 < rc; a0 += 32 * U)
+        constexpr int U = 8; // independent entries per lane: all loads of a batch first, then the stores
+        for (int32_t a0 = blockIdx.z * 32 * U; a0 < rc; a0 += gridDim.z * 32 * U)
         {
             double *dst[U];
             double v[U], old[U];
@@ -1133,6 +1133,12 @@ __global__ void __launch_bounds__(TRI_T) k_bf_forward_tri2(FrontTables T, int32_
         for (int q = 0; q < NB; ++q) l[q] = (i < k1 && q < lane) ? Lp[(int64_t)(k0 + q) * ld + i] : 0.0;
     };
     if (w * NB < s) load_block(w * NB);
+    for (int32_t c = t; c + 1 < s; c += TRI_T)
+    {   // the rest of the pivot block's lower triangle on its way to L2 (one request per 128-byte line of a column)
+        const double *col = Lp + (int64_t)c * ld;
+        for (int32_t i = c + 1; i < s; i += 16) asm volatile("prefetch.global.L2 [%0];" ::"l"(col + i));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(col + s - 1));
+    }
     bf_pdl_trigger();
     bf_pdl_wait();
     for (int32_t a = t; a < s; a += TRI_T) ys[a] = y1[a];
@@ -1364,6 +1370,12 @@ __global__ void __launch_bounds__(TRI_T) k_bf_backward_tri2(FrontTables T, int32
         rinv = 1.0 / ((i < k1) ? Lp[(int64_t)i * ld + i] : 1.0);
     };
     if (s - w * NB > 0) load_block(s - w * NB);
+    for (int32_t c = t + 1; c < s; c += TRI_T)
+    {   // the pivot block's upper triangle on its way to L2
+        const double *col = Lp + (int64_t)c * ld;
+        for (int32_t i = 0; i < c; i += 16) asm volatile("prefetch.global.L2 [%0];" ::"l"(col + i));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(col + c - 1));
+    }
     bf_pdl_trigger();
     bf_pdl_wait();
     for (int32_t a = t; a < s; a += TRI_T) ys[a] = y1[a];
@@ -1648,8 +1660,11 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
             // contribution blocks updated once, behind the last block column (k_bf_schur), not once per block column
             const int32_t strip = (c->bf_schur && c->bf_dmma && max_r > 0) ? 1 : 0;
             bf_launch_pdl(st, k_bf_zero, dim3(64, L.count), 256, T, L.begin, c->CB.p);
+            // few fronts in the level: the rows of a child's column are spread over grid.z as well, so that a large
+            // contribution block is not added by a handful of warps one batch after the other
+            const int ez = L.count >= 16 ? 1 : std::max(1, std::min(4, (max_ld + 255) / 256));
             for (int32_t ord = 0; ord < max_children; ++ord)
-                bf_launch_pdl(st, k_bf_extend, dim3(std::max(1, std::min(256, (max_ld + 7) / 8)), L.count), 256, T, L.begin, ord, c->LU.p, c->CB.p);
+                bf_launch_pdl(st, k_bf_extend, dim3(std::max(1, std::min(256, (max_ld + 7) / 8)), L.count, ez), 256, T, L.begin, ord, c->LU.p, c->CB.p);
             c->kernels += 1 + max_children;
             for (int32_t k0 = 0; k0 < max_s; k0 += NB)
             {

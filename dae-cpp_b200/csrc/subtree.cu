@@ -58,6 +58,8 @@ struct UnitArgs
     int32_t epoch;
     int32_t *flags; // [3] pivot failure, [4] dependency wait timed out
     long long *trace; // optional: 4 globaltimer stamps per unit (debug)
+    long long *trace_levels; // optional: (time, cooperation width, fronts, largest order) per local level of unit trace_unit (debug)
+    int32_t trace_unit;
     // factor
     const int32_t *ent_sj, *ent_sm, *ent_dst;
     const double *jvals, *mvals;
@@ -146,7 +148,8 @@ __device__ __forceinline__ void wait_counter(const UnitArgs &A, const int32_t *w
         for (int32_t fi = (fb) + (int32_t)threadIdx.x / (G); fi < (fe); fi += ng) { CALL; }                     \
     }
 
-__global__ void k_unit_factor(UnitArgs A)
+// (register budget: three resident CTAs of 256 threads per SM, what the units' shared memory allows on C4)
+__global__ void __launch_bounds__(256, 3) k_unit_factor(UnitArgs A)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ uint32_t s_t;
@@ -203,6 +206,14 @@ __global__ void k_unit_factor(UnitArgs A)
                                  unit_ops::factor_front(P, B, fronts + (int64_t)fi * F_SIZE, W, LUu, A.CB, A.pivot_tol, &fail));
             }
             __syncthreads();
+            if (A.trace_levels && unit == A.trace_unit && threadIdx.x == 0 && l < 60)
+            {
+                long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                int32_t md = 0;
+                for (int32_t fi = fb; fi < fe; ++fi) md = max(md, fronts[fi * F_SIZE + F_S] + fronts[fi * F_SIZE + F_R]);
+                A.trace_levels[4 * l + 0] = now; A.trace_levels[4 * l + 1] = G; A.trace_levels[4 * l + 2] = fe - fb; A.trace_levels[4 * l + 3] = md;
+            }
         }
         if (fail) atomicOr(&A.flags[3], 1);
         stamp(A, unit, 3);
@@ -490,7 +501,11 @@ int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha)
     A.jvals = jvals_of(c); A.mvals = c->M.vals.p;
     A.alpha = alpha; A.pivot_tol = c->pivot_tol;
     A.serial_dim = c->sopt.serial_dim;
-    if (c->trace_units && c->trace.reserve((size_t)c->S.nunit * 12 + 4) == cudaSuccess) A.trace = c->trace.p;
+    if (c->trace_units && c->trace.reserve((size_t)c->S.nunit * 12 + 4 + 256) == cudaSuccess)
+    {
+        A.trace = c->trace.p;
+        if (g.begin == 0) { A.trace_levels = c->trace.p + (size_t)c->S.nunit * 12 + 4; A.trace_unit = c->trace_unit_index; }
+    }
     const int grid = grid_for(g, c->unit_grid_factor);
     k_unit_factor<<<grid, c->unit_threads, c->S.factor_smem_bytes, c->stream>>>(A);
     c->ticket_base += (uint32_t)(g.count + grid);

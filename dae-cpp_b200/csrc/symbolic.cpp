@@ -722,7 +722,9 @@ static bool build_schedule(int32_t n, const int32_t *outer, const int32_t *inner
             for (int32_t l = 0; l < nl; ++l)
             {
                 const int32_t d = maxd[l];
-                lg[l] = d <= opt.serial_dim ? 1 : (d <= 12 ? 8 : (d <= 40 ? 32 : 0));
+                const int32_t cnt = lp[l + 1] - lp[l];
+                const bool warp = d <= opt.warp_dim || (d <= opt.warp_dim_many && cnt >= opt.warp_min_fronts);
+                lg[l] = d <= opt.serial_dim ? 1 : (d <= 12 ? 8 : (warp ? 32 : 0));
                 if (lg[l] == 1) S.n_serial_fronts += lp[l + 1] - lp[l];
             }
         }

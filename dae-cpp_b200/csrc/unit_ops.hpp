@@ -25,6 +25,12 @@
 #define DAE_LDCG(p) (*(p))
 #endif
 
+#if defined(__CUDA_ARCH__)
+#define DAE_UNROLL _Pragma("unroll")
+#else
+#define DAE_UNROLL
+#endif
+
 namespace daecpp_b200
 {
 namespace unit_ops
@@ -68,7 +74,19 @@ DAE_HD void factor_front(const P &p, const int32_t *B, const int32_t *F, double 
         }
         p.sync();
     }
-    for (int32_t k = 0; k < s; ++k)
+    // Pivots are eliminated KB at a time.  Inside a block of KB pivots only the block's own columns and rows are brought up
+    // to date pivot by pivot; everything behind them then receives the KB rank-1 updates in one pass, every lane holding an
+    // RI x RJ patch in registers -- each element still sees a(i,j) -= l(i,k) * u(k,j) for k in ascending order with the same
+    // operands, so the factors are the same bits as with one full update per pivot, but the patch is read and written once
+    // per KB pivots and the multipliers are shared across it (the rank-1 form needed four shared-memory accesses per
+    // multiply-add).  Only fronts swept by the whole block (or a warp on a large front) go this way; the small fronts of the
+    // lower local levels, a few lanes each, keep one full update per pivot (measured: no faster in patches).
+    // (G == 1 with a large front only happens in the scalar walk of the GPU-less tests: they cover the blocked form too.)
+    constexpr int KBMAX = 4, KB = 4, RI = 2, RJ = 2;
+    const bool blocked = G > 32 || ((G == 32 || G == 1) && d >= 48);
+    const int GI = G < 32 ? G : 32, GJ = G / GI; // lanes along a column, lane groups across columns
+    const int li = lane % GI, lj = lane / GI;
+    for (int32_t k = 0; !blocked && k < s; ++k)
     {
         double *colk = A + (int64_t)k * d;
         const double piv = colk[k];
@@ -84,6 +102,72 @@ DAE_HD void factor_front(const P &p, const int32_t *B, const int32_t *F, double 
             A[(int64_t)j * d + i] -= colk[i] * A[(int64_t)j * d + k];
         }
         p.sync();
+    }
+    for (int32_t k0 = 0; blocked && k0 < s; k0 += KB)
+    {
+        const int32_t k1 = (k0 + KB < s) ? k0 + KB : s;
+        for (int32_t k = k0; k < k1; ++k)
+        {
+            double *colk = A + (int64_t)k * d;
+            const double piv = colk[k];
+            if (lane == 0 && (!(fabs(piv) > pivot_tol) || std::isinf(piv))) *fail = 1;
+            const double inv = 1.0 / piv;
+            // (no barrier here: the scaling leaves the pivot itself alone, and the last update ended with one)
+            for (int32_t i = k + 1 + lane; i < d; i += G) colk[i] *= inv;
+            p.sync();
+            if (k + 1 < k1)
+            {
+                for (int32_t j = k + 1; j < k1; ++j)
+                {   // the block's columns right of the pivot
+                    double *colj = A + (int64_t)j * d;
+                    const double ukj = colj[k];
+                    for (int32_t i = k + 1 + lane; i < d; i += G) colj[i] -= colk[i] * ukj;
+                }
+                for (int32_t i = k + 1; i < k1; ++i)
+                {   // the block's rows below the pivot, right of the block
+                    const double lik = colk[i];
+                    for (int32_t j = k1 + lane; j < d; j += G) A[(int64_t)j * d + i] -= lik * A[(int64_t)j * d + k];
+                }
+                p.sync();
+            }
+        }
+        const int32_t m = d - k1, kb = k1 - k0;
+        if (m > 0)
+        {
+            for (int32_t jt = lj * RJ; jt < m; jt += GJ * RJ)
+                for (int32_t it = li; it < m; it += GI * RI)
+                {
+                    double acc[RI][RJ], lv[KBMAX][RI], uv[KBMAX][RJ];
+                    DAE_UNROLL
+                    for (int b = 0; b < RJ; ++b)
+                        DAE_UNROLL
+                        for (int a = 0; a < RI; ++a)
+                            acc[a][b] = (it + a * GI < m && jt + b < m) ? A[(int64_t)(k1 + jt + b) * d + k1 + it + a * GI] : 0.0;
+                    DAE_UNROLL
+                    for (int kk = 0; kk < KBMAX; ++kk)
+                    {
+                        DAE_UNROLL
+                        for (int a = 0; a < RI; ++a) lv[kk][a] = (kk < kb && it + a * GI < m) ? A[(int64_t)(k0 + kk) * d + k1 + it + a * GI] : 0.0;
+                        DAE_UNROLL
+                        for (int b = 0; b < RJ; ++b) uv[kk][b] = (kk < kb && jt + b < m) ? A[(int64_t)(k1 + jt + b) * d + k0 + kk] : 0.0;
+                    }
+                    DAE_UNROLL
+                    for (int kk = 0; kk < KBMAX; ++kk)
+                        if (kk < kb)
+                        {
+                            DAE_UNROLL
+                            for (int b = 0; b < RJ; ++b)
+                                DAE_UNROLL
+                                for (int a = 0; a < RI; ++a) acc[a][b] -= lv[kk][a] * uv[kk][b];
+                        }
+                    DAE_UNROLL
+                    for (int b = 0; b < RJ; ++b)
+                        DAE_UNROLL
+                        for (int a = 0; a < RI; ++a)
+                            if (it + a * GI < m && jt + b < m) A[(int64_t)(k1 + jt + b) * d + k1 + it + a * GI] = acc[a][b];
+                }
+            p.sync();
+        }
     }
     double *Lp = LUunit + (uint32_t)F[F_LUOFF];
     for (int32_t e = lane; e < d * s; e += G) Lp[e] = A[e];
@@ -103,12 +187,6 @@ DAE_HD void factor_front(const P &p, const int32_t *B, const int32_t *F, double 
         }
     }
 }
-
-#if defined(__CUDA_ARCH__)
-#define DAE_UNROLL _Pragma("unroll")
-#else
-#define DAE_UNROLL
-#endif
 
 // One-thread fast path for a front of order exactly D (compile-time strides): extend-add in the
 // arena, one load of the D x D block into registers, elimination fully unrolled, and the
