@@ -1125,6 +1125,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "bf_fused_panel") c->bf_fused_panel = value != 0.0;
     else if (k == "bf_dmma") c->bf_dmma = value != 0.0;
     else if (k == "bf_schur") c->bf_schur = value != 0.0;
+    else if (k == "bf_schur_fronts") c->bf_schur_fronts = (int)value;
     else if (k == "bf_fast_solve") c->bf_fast_solve = value != 0.0;
     else if (k == "bf_diag_copy") c->bf_diag_copy = value != 0.0;
     else if (k == "bf_lu_lookahead") c->bf_lu_lookahead = value != 0.0;

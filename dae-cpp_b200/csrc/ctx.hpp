@@ -199,6 +199,8 @@ struct daecpp_b200_options
                                        // Bit-identical and it reads / writes the block once instead of once per block column, but measured
                                        // slower on C4 (11.8 vs 11.1 ms): a block column costs ~40 us of launch + dependent latency whatever
                                        // its trailing update touches, so the extra pass per level is not paid back
+    int bf_schur_fronts = 0;           // ... only on levels with at least this many fronts and more than one block column (0: never;
+                                       // measured slower at 30, 100 and 400 as well)
     // numerics
     // Guarded iterative refinement (one step of r = b - Jb*dx, Jb*e = r, dx += e): taken only when the Newton update
     // failed the convergence test on elements whose |dx| is below refine_floor, i.e. where the outcome of the

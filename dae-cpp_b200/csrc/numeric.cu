@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(256) k_bf_extend(FrontTables T, int32_t begin,
     for (int32_t bc = blockIdx.x * NW + wid; bc < rc; bc += gridDim.x * NW)
     {
         const int32_t rb = rel[bc];
-        constexpr int U = 8; // independent entries per lane: all loads of a batch first, then the stores
+        constexpr int U = 4; // independent entries per lane: all loads of a batch first, then the stores
         for (int32_t a0 = blockIdx.z * 32 * U; a0 < rc; a0 += gridDim.z * 32 * U)
         {
             double *dst[U];
@@ -1658,11 +1658,12 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
             const bool look = c->bf_lu_lookahead;
             double *dbuf = c->bf_diag_copy ? c->bf_diag.p : nullptr;
             // contribution blocks updated once, behind the last block column (k_bf_schur), not once per block column
-            const int32_t strip = (c->bf_schur && c->bf_dmma && max_r > 0) ? 1 : 0;
+            const bool schur_level = c->bf_schur || (c->bf_schur_fronts > 0 && L.count >= c->bf_schur_fronts && max_s > NB);
+            const int32_t strip = (schur_level && c->bf_dmma && max_r > 0) ? 1 : 0;
             bf_launch_pdl(st, k_bf_zero, dim3(64, L.count), 256, T, L.begin, c->CB.p);
             // few fronts in the level: the rows of a child's column are spread over grid.z as well, so that a large
             // contribution block is not added by a handful of warps one batch after the other
-            const int ez = L.count >= 16 ? 1 : std::max(1, std::min(4, (max_ld + 255) / 256));
+            const int ez = L.count > 4 ? 1 : std::max(1, std::min(4, (max_ld + 255) / 256));
             for (int32_t ord = 0; ord < max_children; ++ord)
                 bf_launch_pdl(st, k_bf_extend, dim3(std::max(1, std::min(256, (max_ld + 7) / 8)), L.count, ez), 256, T, L.begin, ord, c->LU.p, c->CB.p);
             c->kernels += 1 + max_children;

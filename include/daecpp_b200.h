@@ -183,13 +183,19 @@ int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *ctx, int64_t *out, int64_t cap
  * "blocked_lu_min_dim", "bf_fused_panel" (panel of a block column in one launch), "bf_dmma" (trailing update of big
  * fronts on the FP64 tensor cores, default 1; 0 = FP64 FMA tiles), "bf_pdl" (programmatic dependent launch between them),
  * "bf_schur" (contribution block of a big front updated in one pass behind its last block column; bit-identical, default 0:
- * measured slower).  Numerics: "refine_steps" / "refine_floor" (guarded refinement step), "pivot_rel" (row-relative pivot
+ * measured slower; "bf_schur_fronts" = N > 0: only on levels with at least N fronts, also measured slower),
+ * "bf_fast_solve" (default 1: triangular sweeps of big fronts with the pivot unknowns in shared memory, diagonal blocks held in
+ * registers from the start of the kernel and batched loads; 0 = the round-1 kernels; bit-identical), "bf_diag_copy" (default 1:
+ * the factored diagonal block of a block column travels from the panel launch to the trailing update through a side buffer
+ * instead of being factored a second time; bit-identical), "bf_lu_lookahead" (default 1: reciprocal of the next pivot formed
+ * beside the update; bit-identical), "warp_dim" / "warp_dim_many" / "warp_min_fronts" (local levels of a subtree unit swept one
+ * warp per front up to this front order; defaults 40 / 40 / 4), "unit_threads" (a multiple of 32, at most 256).  Numerics: "refine_steps" / "refine_floor" (guarded refinement step), "pivot_rel" (row-relative pivot
  * test of the chain path), "transversal" (row matching before the ordering when the diagonal has structural holes),
  * "tiny" (one-launch path for n <= 32).  "chain_packed": 2 = bulk copies (cp.async.bulk) where the tile qualifies,
  * 1 = contiguous-run LDGSTS, 0 = per-field copies.  "pipeline_iterations": see daecpp_b200_iterations_resident.
  * "chain_top_cta" (default 1): fused iteration of a single system, the grid-level cyclic reduction runs in a CTA of its own
  * that rehearses it while the tiles sweep.
- * Debug: "trace_units", "phase_timing", "pinned_io". */
+ * Debug: "trace_units" (with "trace_unit_index": the unit whose local levels are stamped one by one), "phase_timing", "pinned_io". */
 int daecpp_b200_set_option(daecpp_b200_ctx *ctx, const char *key, double value);
 
 /* ==== lock-step batched ensemble (an ADDITION: the reference has no ensemble API) =========

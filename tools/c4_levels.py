@@ -19,12 +19,22 @@ for r in csv.DictReader(lines):
 starts = [i for i, r in enumerate(rows) if r[0].startswith("k_scatter_big")]
 if len(starts) >= 2:
     rows = rows[starts[-2]:starts[-1]]
+    ends = [i for i, r in enumerate(rows) if r[0].startswith("k_permute_out")]
+    if ends:  # the bench repeats the solve phase on its own: keep the first one (and the update behind it)
+        e = ends[0] + 1
+        if e < len(rows) and rows[e][0].startswith("k_update"):
+            e += 1
+        rows = rows[:e]
 per = OrderedDict()
 for name, us, grid in rows:
     n, t = per.get(name, (0, 0.0))
     per[name] = (n + 1, t + us)
 tot = sum(t for _, t in per.values())
 print(f"# one Newton iteration (refactor + solve), {len(rows)} launches, serialised sum {tot / 1e3:.3f} ms")
+try:
+    sys.stdout.reconfigure(line_buffering=True)
+except Exception:
+    pass
 for name, (n, t) in sorted(per.items(), key=lambda kv: -kv[1][1]):
     print(f"{name:28s} {n:4d} launches {t / 1e3:8.3f} ms {100 * t / tot:5.1f}%  avg {t / n:8.1f} us")
 print("\n## k_unit_factor launches (us, grid)")
