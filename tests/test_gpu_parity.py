@@ -505,6 +505,16 @@ def test_big_front_latency_variants_are_bit_identical(m):
     assert rc == 0 and got == ref
 
 
+@pytest.mark.parametrize("max_super", [100, 512])
+def test_big_front_latency_variants_other_pivot_block_sizes(max_super):
+    """Pivot blocks that are not multiples of the 32-pivot step (max_super = 100) and fronts with more than eight steps
+    (max_super = 512: a warp of the triangular sweeps reloads its registers for the block eight steps ahead)."""
+    base = {"bf_fast_solve": 0, "bf_diag_copy": 0, "bf_lu_lookahead": 0, "max_super": max_super}
+    rc0, ref = _grid_solve_bytes(400, base)
+    rc, got = _grid_solve_bytes(400, {"max_super": max_super})
+    assert rc0 == 0 and rc == 0 and got == ref
+
+
 @pytest.mark.parametrize("opts", [{}, {"bf_diag_copy": 0, "bf_lu_lookahead": 0}, {"bf_diag_copy": 1, "bf_lu_lookahead": 0},
                                   {"bf_diag_copy": 0, "bf_lu_lookahead": 1}, {"bf_fused_panel": 0}])
 def test_big_front_zero_pivot_is_reported(opts):
