@@ -1068,7 +1068,7 @@ __global__ void __launch_bounds__(512) k_bf_backward_tri(FrontTables T, int32_t 
 // per block of NB pivots), the factor entries a block needs -- the diagonal block of warp 0, one panel row per thread -- are
 // loaded BEFORE the chain they do not depend on (next block's diagonal block while this block's rows are applied), and
 // the matrix-vector kernels issue their loads in batches of 16 instead of two per loop trip.
-constexpr int TRI_T = 256, TRI_W = TRI_T / 32;
+
 
 // Loads the compiler must not sink towards their uses (it serialised the batches of the matrix-vector kernels into
 // load - multiply-add pairs, one memory round trip each): volatile asm keeps the requests together, in program order.
@@ -1094,9 +1094,13 @@ __device__ __forceinline__ int32_t ld_nc_s32(const int32_t *p)
 // Block b of NB pivots belongs to warp b % TRI_W, which holds the block's triangle in registers from the start of the
 // kernel (the factors are final long before the sweep: requested before the wait for the level below) -- no memory
 // round trip sits between two dependent chains any more.
+// (TRI_T threads: 256 for pivot blocks of up to 288, 128 / 64 on levels whose fronts have at most 128 / 64 pivots -- the
+// kernel needs ~250 registers per thread, so the smaller CTAs are what lets two or four fronts share an SM there)
+template <int TRI_T>
 __global__ void __launch_bounds__(TRI_T) k_bf_forward_tri2(FrontTables T, int32_t begin, const double *__restrict__ LU,
                                                            double *__restrict__ upd, double *__restrict__ y)
 {
+    constexpr int TRI_W = TRI_T / 32;
     extern __shared__ double ys[]; // the front's pivot unknowns
     const int32_t f = T.level_sn[begin + blockIdx.x];
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
@@ -1346,9 +1350,11 @@ __global__ void __launch_bounds__(256) k_bf_backward_gemv2(FrontTables T, int32_
     if (lane == 0) y[first + k] -= acc;
 }
 
+template <int TRI_T>
 __global__ void __launch_bounds__(TRI_T) k_bf_backward_tri2(FrontTables T, int32_t begin, const double *__restrict__ LU,
                                                             double *__restrict__ y)
 {
+    constexpr int TRI_W = TRI_T / 32;
     extern __shared__ double ys[];
     const int32_t f = T.level_sn[begin + blockIdx.x];
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
@@ -1778,7 +1784,9 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
             const size_t ysm = sizeof(double) * (size_t)L.max_s;
             if (c->bf_fast_solve && ysm <= 40 * 1024)
             {
-                bf_launch_pdl_smem(st, k_bf_forward_tri2, dim3(L.count), TRI_T, ysm, T, L.begin, c->LU.p, c->upd.p, c->work);
+                if (L.max_s <= 64) bf_launch_pdl_smem(st, k_bf_forward_tri2<64>, dim3(L.count), 64, ysm, T, L.begin, c->LU.p, c->upd.p, c->work);
+                else if (L.max_s <= 128) bf_launch_pdl_smem(st, k_bf_forward_tri2<128>, dim3(L.count), 128, ysm, T, L.begin, c->LU.p, c->upd.p, c->work);
+                else bf_launch_pdl_smem(st, k_bf_forward_tri2<256>, dim3(L.count), 256, ysm, T, L.begin, c->LU.p, c->upd.p, c->work);
                 if (L.max_r > 0)
                     bf_launch_pdl_smem(st, k_bf_forward_gemv2, dim3((L.max_r + GV_ROWS - 1) / GV_ROWS, L.count), GV_ROWS * GV_SEG, ysm, T, L.begin, c->LU.p, c->upd.p, c->work);
                 c->kernels += L.max_r > 0 ? 2 : 1;
@@ -1804,7 +1812,9 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
             if (c->bf_fast_solve && ysm <= 40 * 1024)
             {
                 if (L.max_r > 0) bf_launch_pdl(st, k_bf_backward_gemv2, dim3((L.max_s + 7) / 8, L.count), 256, T, L.begin, c->LU.p, c->work);
-                bf_launch_pdl_smem(st, k_bf_backward_tri2, dim3(L.count), TRI_T, ysm, T, L.begin, c->LU.p, c->work);
+                if (L.max_s <= 64) bf_launch_pdl_smem(st, k_bf_backward_tri2<64>, dim3(L.count), 64, ysm, T, L.begin, c->LU.p, c->work);
+                else if (L.max_s <= 128) bf_launch_pdl_smem(st, k_bf_backward_tri2<128>, dim3(L.count), 128, ysm, T, L.begin, c->LU.p, c->work);
+                else bf_launch_pdl_smem(st, k_bf_backward_tri2<256>, dim3(L.count), 256, ysm, T, L.begin, c->LU.p, c->work);
                 c->kernels += L.max_r > 0 ? 2 : 1;
                 continue;
             }

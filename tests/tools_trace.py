@@ -22,7 +22,8 @@ for _ in range(3):
 print("refactor ms", c.stat("ms_last_refactor"), "solve ms (next)")
 c.solve_update(1e-6, 1e-6)
 print("solve ms", c.stat("ms_last_solve"))
-T = c.unit_trace().astype(np.float64).reshape(3, -1, 4)
+nu = int(c.stat("n_units"))
+T = c.unit_trace().astype(np.float64)[:3 * nu].reshape(3, -1, 4)  # (the rows behind them: per-level stamps of one unit)
 print({k: c.stat(k) for k in ("n_units", "n_stages", "factor_smem_bytes", "solve_smem_bytes", "unit_grid_factor", "unit_grid_solve", "n_fronts")})
 for name, t in zip(("factor", "forward", "backward"), T):
     t = (t - t[:, 0].min()) / 1e3
