@@ -220,7 +220,7 @@ static void recycle(daecpp_b200_ctx *c)
         o.chain_affine != fresh.chain_affine || o.unit_threads != fresh.unit_threads || o.sopt.leaf_size != fresh.sopt.leaf_size ||
         o.sopt.unit_smem_bytes != fresh.sopt.unit_smem_bytes || o.sopt.serial_dim != fresh.sopt.serial_dim ||
         o.sopt.max_super != fresh.sopt.max_super || o.sopt.transversal != fresh.sopt.transversal ||
-        o.sopt.warp_dim != fresh.sopt.warp_dim || o.sopt.warp_dim_many != fresh.sopt.warp_dim_many ||
+        o.sopt.warp_dim != fresh.sopt.warp_dim || o.sopt.group8_dim != fresh.sopt.group8_dim || o.sopt.warp_dim_many != fresh.sopt.warp_dim_many ||
         o.sopt.warp_min_fronts != fresh.sopt.warp_min_fronts)
         c->have_symbolic = false;
     o = fresh; // every option back to its default, whatever is added to daecpp_b200_options later
@@ -1098,13 +1098,14 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     }
     else if (k == "leaf_size") { c->sopt.leaf_size = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "unit_smem_bytes") { c->sopt.unit_smem_bytes = (int)value; c->have_symbolic = false; c->have_factor = false; }
+    else if (k == "group8_dim") { c->sopt.group8_dim = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "warp_dim") { c->sopt.warp_dim = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "warp_dim_many") { c->sopt.warp_dim_many = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "warp_min_fronts") { c->sopt.warp_min_fronts = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "serial_dim") { c->sopt.serial_dim = (int)value; c->have_symbolic = false; c->have_factor = false; }
     else if (k == "unit_threads")
     {
-        if (value < 32 || value > 256 || ((int)value & 31)) return fail(c, DAECPP_B200_EINVAL, "unit_threads: a multiple of 32 up to 256");
+        if (value != 0 && (value < 32 || value > 256 || ((int)value & 31))) return fail(c, DAECPP_B200_EINVAL, "unit_threads: 0 (automatic) or a multiple of 32 up to 256");
         c->unit_threads = (int)value; c->have_symbolic = false; c->have_factor = false;
     }
     else if (k == "pinned_io") c->pinned_io = value != 0.0;

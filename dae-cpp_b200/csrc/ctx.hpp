@@ -163,7 +163,7 @@ struct daecpp_b200_options
 {
     // plan-affecting (a change invalidates the symbolic analysis)
     daecpp_b200::SymbolicOptions sopt;
-    int unit_threads = 256;
+    int unit_threads = 0;  // threads per subtree unit; 0: 256, or 128 where the automatic unit budget hit its ceiling (symbolic.cpp)
     bool chain_enabled = true, chain_affine = true;
     int chain_min_n = 256, chain_max_b = 3;
     // chain path
@@ -291,6 +291,7 @@ struct daecpp_b200_ctx : daecpp_b200_options
     bool chain_top_pending = false;    // level-0 factors are current, the top level's are not yet
     uint32_t ticket_base = 0; // value of the ticket word before the next unit launch
     int32_t solve_epoch = 0;
+    int unit_threads_eff = 256; // what unit_threads resolved to for the current plan
     int unit_grid_factor = 0, unit_grid_solve = 0; // resident blocks (SMs x occupancy)
     daecpp_b200::DevBuf<long long> trace;
     bool jvals_from_triplets = false; // fused assembly reads the staged triplet values directly

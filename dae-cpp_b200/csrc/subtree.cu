@@ -450,10 +450,11 @@ int unit_setup(daecpp_b200_ctx *c)
             ss_max[d] = ss;
         }
     }
+    c->unit_threads_eff = c->unit_threads > 0 ? c->unit_threads : (c->S.budget_capped ? 128 : 256);
     int of = 0, os = 0, ob = 0;
-    DAECPP_CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&of, k_unit_factor, c->unit_threads, fs));
-    DAECPP_CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&os, k_unit_forward, c->unit_threads, ss));
-    DAECPP_CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ob, k_unit_backward<true>, c->unit_threads, ss));
+    DAECPP_CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&of, k_unit_factor, c->unit_threads_eff, fs));
+    DAECPP_CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&os, k_unit_forward, c->unit_threads_eff, ss));
+    DAECPP_CUDA_TRY(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ob, k_unit_backward<true>, c->unit_threads_eff, ss));
     if (ob < os) os = ob;
     if (of < 1 || os < 1) { c->err = "unit kernels do not fit on an SM"; return DAECPP_B200_ENOMEM; }
     c->unit_grid_factor = sms * of;
@@ -507,7 +508,7 @@ int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha)
         if (g.begin == 0) { A.trace_levels = c->trace.p + (size_t)c->S.nunit * 12 + 4; A.trace_unit = c->trace_unit_index; }
     }
     const int grid = grid_for(g, c->unit_grid_factor);
-    k_unit_factor<<<grid, c->unit_threads, c->S.factor_smem_bytes, c->stream>>>(A);
+    k_unit_factor<<<grid, c->unit_threads_eff, c->S.factor_smem_bytes, c->stream>>>(A);
     c->ticket_base += (uint32_t)(g.count + grid);
     c->kernels += 1;
     return DAECPP_B200_OK;
@@ -522,7 +523,7 @@ int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct)
     A.y = c->work; A.upd = c->upd.p;
     if (c->trace_units && c->trace.p) A.trace = c->trace.p + (size_t)c->S.nunit * 4;
     const int grid = grid_for(g, c->unit_grid_solve);
-    k_unit_forward<<<grid, c->unit_threads, c->S.solve_smem_bytes, c->stream>>>(A);
+    k_unit_forward<<<grid, c->unit_threads_eff, c->S.solve_smem_bytes, c->stream>>>(A);
     c->ticket_base += (uint32_t)(g.count + grid);
     c->kernels += 1;
     return DAECPP_B200_OK;
@@ -539,8 +540,8 @@ int launch_unit_backward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, 
     A.atol = atol; A.rtol = rtol; A.max_err_abs = max_err_abs; A.floor = c->refine_floor;
     if (c->trace_units && c->trace.p) A.trace = c->trace.p + (size_t)c->S.nunit * 8;
     const int grid = grid_for(g, c->unit_grid_solve);
-    if (direct && update) k_unit_backward<true><<<grid, c->unit_threads, c->S.solve_smem_bytes, c->stream>>>(A);
-    else k_unit_backward<false><<<grid, c->unit_threads, c->S.solve_smem_bytes, c->stream>>>(A);
+    if (direct && update) k_unit_backward<true><<<grid, c->unit_threads_eff, c->S.solve_smem_bytes, c->stream>>>(A);
+    else k_unit_backward<false><<<grid, c->unit_threads_eff, c->S.solve_smem_bytes, c->stream>>>(A);
     c->ticket_base += (uint32_t)(g.count + grid);
     c->kernels += 1;
     return DAECPP_B200_OK;

@@ -23,6 +23,7 @@ struct SymbolicOptions
     int unit_smem_bytes = -1; // shared-memory budget of one subtree unit (-1: chosen from the problem
                               // size; 0: no units, every front goes through the per-level kernels)
     int serial_dim = 4;     // fronts up to this order are factored by one thread each
+    int group8_dim = 8;     // local levels whose largest front is at most this order are swept eight lanes per front
     int warp_dim = 40;      // local levels of a unit whose largest front is at most this order are swept one warp per front
     int warp_dim_many = 40; // ... or at most this order when the level has at least warp_min_fronts fronts (enough to keep
     int warp_min_fronts = 4; //    the block's warps busy); larger fronts take the whole block, one after the other
@@ -92,6 +93,7 @@ struct Symbolic
     std::vector<int32_t> row_src;
     int32_t n_rows_moved = 0;
 
+    bool budget_capped = false; // the automatic unit budget hit its ceiling (a large problem)
     int32_t s_of(int32_t f) const { return sn_first[f + 1] - sn_first[f]; }
     int32_t r_of(int32_t f) const { return (int32_t)(sn_rowptr[f + 1] - sn_rowptr[f]); }
 };
