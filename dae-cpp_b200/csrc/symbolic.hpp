@@ -24,8 +24,8 @@ struct SymbolicOptions
                               // size; 0: no units, every front goes through the per-level kernels)
     int serial_dim = 4;     // fronts up to this order are factored by one thread each
     int group8_dim = 8;     // local levels whose largest front is at most this order are swept eight lanes per front
-    int warp_dim = 40;      // local levels of a unit whose largest front is at most this order are swept one warp per front
-    int warp_dim_many = 40; // ... or at most this order when the level has at least warp_min_fronts fronts (enough to keep
+    int warp_dim = 16;      // local levels of a unit whose largest front is at most this order are swept one warp per front
+    int warp_dim_many = 16; // ... or at most this order when the level has at least warp_min_fronts fronts (enough to keep
     int warp_min_fronts = 4; //    the block's warps busy); larger fronts take the whole block, one after the other
     const double *weights = nullptr; // optional |a_ij| per slot of the analysed pattern: the transversal prefers big entries
     int transversal = 1;    // permute rows to a structurally zero-free diagonal first when the diagonal has holes

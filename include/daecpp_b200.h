@@ -188,8 +188,10 @@ int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *ctx, int64_t *out, int64_t cap
  * registers from the start of the kernel and batched loads; 0 = the round-1 kernels; bit-identical), "bf_diag_copy" (default 1:
  * the factored diagonal block of a block column travels from the panel launch to the trailing update through a side buffer
  * instead of being factored a second time; bit-identical), "bf_lu_lookahead" (default 1: reciprocal of the next pivot formed
- * beside the update; bit-identical), "warp_dim" / "warp_dim_many" / "warp_min_fronts" (local levels of a subtree unit swept one
- * warp per front up to this front order; defaults 40 / 40 / 4), "unit_threads" (a multiple of 32, at most 256).  Numerics: "refine_steps" / "refine_floor" (guarded refinement step), "pivot_rel" (row-relative pivot
+ * beside the update; bit-identical), "group8_dim" / "warp_dim" / "warp_dim_many" / "warp_min_fronts" (local levels of a subtree unit
+ * swept eight lanes / one warp per front up to this front order, larger fronts by the whole block; defaults 8 / 16 / 16 / 4,
+ * round 1: 12 / 40), "unit_threads" (0 = automatic: 256, or 128 with 40 KB units where the automatic unit budget hits its ceiling;
+ * else a multiple of 32, at most 256).  Numerics: "refine_steps" / "refine_floor" (guarded refinement step), "pivot_rel" (row-relative pivot
  * test of the chain path), "transversal" (row matching before the ordering when the diagonal has structural holes),
  * "tiny" (one-launch path for n <= 32).  "chain_packed": 2 = bulk copies (cp.async.bulk) where the tile qualifies,
  * 1 = contiguous-run LDGSTS, 0 = per-field copies.  "pipeline_iterations": see daecpp_b200_iterations_resident.
