@@ -365,6 +365,9 @@ static void destroy_now(daecpp_b200_ctx *c)
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev_mark) cudaEventDestroy(c->ev_mark);
+    if (c->ev_z0) cudaEventDestroy(c->ev_z0);
+    if (c->ev_z1) cudaEventDestroy(c->ev_z1);
+    if (c->stream_zero) { cudaStreamSynchronize(c->stream_zero); cudaStreamDestroy(c->stream_zero); }
     for (int k = 0; k < 6; ++k) if (c->pev[k]) cudaEventDestroy(c->pev[k]);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -1126,6 +1129,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "bf_fused_panel") c->bf_fused_panel = value != 0.0;
     else if (k == "bf_dmma") c->bf_dmma = value != 0.0;
     else if (k == "bf_schur") c->bf_schur = value != 0.0;
+    else if (k == "bf_zero_ahead") c->bf_zero_ahead = value != 0.0;
     else if (k == "bf_schur_fronts") c->bf_schur_fronts = (int)value;
     else if (k == "bf_fast_solve") c->bf_fast_solve = value != 0.0;
     else if (k == "bf_diag_copy") c->bf_diag_copy = value != 0.0;

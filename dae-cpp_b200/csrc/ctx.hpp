@@ -199,6 +199,8 @@ struct daecpp_b200_options
                                        // Bit-identical and it reads / writes the block once instead of once per block column, but measured
                                        // slower on C4 (11.8 vs 11.1 ms): a block column costs ~40 us of launch + dependent latency whatever
                                        // its trailing update touches, so the extra pass per level is not paid back
+    bool bf_zero_ahead = true;         // big fronts: all contribution blocks zeroed by one launch on a side stream at the start of the
+                                       // refactorisation, under the latency-bound unit launches, instead of one launch per level
     int bf_schur_fronts = 0;           // ... only on levels with at least this many fronts and more than one block column (0: never;
                                        // measured slower at 30, 100 and 400 as well)
     // numerics
@@ -313,6 +315,8 @@ struct daecpp_b200_ctx : daecpp_b200_options
     double n_symbolic = 0, n_refactor = 0, n_solve = 0, n_cold = 0, kernels = 0;
     double ms_symbolic = 0, ms_last_refactor = 0, ms_last_solve = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mark = nullptr;
+    cudaStream_t stream_zero = nullptr;            // big fronts: contribution blocks zeroed beside the unit launches (bf_zero_ahead)
+    cudaEvent_t ev_z0 = nullptr, ev_z1 = nullptr;
     // per-phase device times of iteration_resident (option "phase_timing"):
     // 0 assembly, 1 residual, 2 refactor, 3 solve, 4 update
     cudaEvent_t pev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -367,7 +371,7 @@ int jb_values(daecpp_b200_ctx *c, double alpha);          // u_vals = J - alpha*
 // subtree.cu
 int unit_setup(daecpp_b200_ctx *c);
 int compose_entries(daecpp_b200_ctx *c);
-int launch_scatter_big(daecpp_b200_ctx *c, double alpha);
+int launch_scatter_big(daecpp_b200_ctx *c, double alpha, cudaStream_t st);
 int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha);
 int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct);
 int launch_unit_backward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, bool update, double atol, double rtol,

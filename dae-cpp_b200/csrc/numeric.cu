@@ -1646,14 +1646,37 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
         c->last_alpha = alpha;
         return DAECPP_B200_OK;
     }
-    if (S.nbig)
+    const bool side = S.nbig && c->blocked_lu && c->bf_zero_ahead;
+    if (S.nbig && !side)
     {
         DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->LU.p + S.lu_big_begin, 0, sizeof(double) * (size_t)(S.lu_size - S.lu_big_begin), st));
-        if ((rc = launch_scatter_big(c, alpha))) return rc;
+        if ((rc = launch_scatter_big(c, alpha, st))) return rc;
     }
     FrontTables T = tables(c);
+    bool zero_ahead = false, zero_waited = false;
+    if (side)
+    {   // the big fronts' factor storage (zeroed, matrix entries scattered) and the contribution blocks of ALL big fronts
+        // (zeroed) are prepared on a side stream while the unit launches (a chain of dependent latencies that leaves the
+        // memory system idle) run on the main one; the first level of big fronts waits for it
+        if (!c->stream_zero)
+        {
+            DAECPP_CUDA_TRY(c, cudaStreamCreateWithFlags(&c->stream_zero, cudaStreamNonBlocking));
+            DAECPP_CUDA_TRY(c, cudaEventCreateWithFlags(&c->ev_z0, cudaEventDisableTiming));
+            DAECPP_CUDA_TRY(c, cudaEventCreateWithFlags(&c->ev_z1, cudaEventDisableTiming));
+        }
+        DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev_z0, st)); // behind everything that still reads the blocks
+        DAECPP_CUDA_TRY(c, cudaStreamWaitEvent(c->stream_zero, c->ev_z0, 0));
+        DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->LU.p + S.lu_big_begin, 0, sizeof(double) * (size_t)(S.lu_size - S.lu_big_begin), c->stream_zero));
+        if ((rc = launch_scatter_big(c, alpha, c->stream_zero))) return rc;
+        for (int32_t b0 = 0; b0 < S.nbig; b0 += 32768)
+            k_bf_zero<<<dim3(64, std::min(32768, S.nbig - b0)), 256, 0, c->stream_zero>>>(T, b0, c->CB.p);
+        DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev_z1, c->stream_zero));
+        c->kernels += 1;
+        zero_ahead = true;
+    }
     for (const GroupLaunch &L : c->groups)
     {
+        if (L.kind != 0 && zero_ahead && !zero_waited) { DAECPP_CUDA_TRY(c, cudaStreamWaitEvent(st, c->ev_z1, 0)); zero_waited = true; }
         if (L.kind == 0)
         {
             if ((rc = launch_unit_factor(c, L, alpha))) return rc;
@@ -1666,13 +1689,13 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
             // contribution blocks updated once, behind the last block column (k_bf_schur), not once per block column
             const bool schur_level = c->bf_schur || (c->bf_schur_fronts > 0 && L.count >= c->bf_schur_fronts && max_s > NB);
             const int32_t strip = (schur_level && c->bf_dmma && max_r > 0) ? 1 : 0;
-            bf_launch_pdl(st, k_bf_zero, dim3(64, L.count), 256, T, L.begin, c->CB.p);
+            if (!zero_ahead) bf_launch_pdl(st, k_bf_zero, dim3(64, L.count), 256, T, L.begin, c->CB.p);
             // few fronts in the level: the rows of a child's column are spread over grid.z as well, so that a large
             // contribution block is not added by a handful of warps one batch after the other
             const int ez = L.count > 4 ? 1 : std::max(1, std::min(4, (max_ld + 255) / 256));
             for (int32_t ord = 0; ord < max_children; ++ord)
                 bf_launch_pdl(st, k_bf_extend, dim3(std::max(1, std::min(256, (max_ld + 7) / 8)), L.count, ez), 256, T, L.begin, ord, c->LU.p, c->CB.p);
-            c->kernels += 1 + max_children;
+            c->kernels += (zero_ahead ? 0 : 1) + max_children;
             for (int32_t k0 = 0; k0 < max_s; k0 += NB)
             {
                 // largest trailing order among the fronts still being factored: a front with fewer pivots than
@@ -1726,6 +1749,7 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
             c->kernels += 1;
         }
     }
+    if (zero_ahead && !zero_waited) DAECPP_CUDA_TRY(c, cudaStreamWaitEvent(st, c->ev_z1, 0));
     DAECPP_CUDA_TRY(c, cudaGetLastError());
     c->n_refactor += 1;
     c->last_alpha = alpha;

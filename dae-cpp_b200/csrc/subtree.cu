@@ -485,11 +485,11 @@ static const double *jvals_of(daecpp_b200_ctx *c)
     return c->jvals_from_triplets ? c->J.A.p : c->J.vals.p;
 }
 
-int launch_scatter_big(daecpp_b200_ctx *c, double alpha)
+int launch_scatter_big(daecpp_b200_ctx *c, double alpha, cudaStream_t st)
 {
     const int64_t nb = (int64_t)c->S.big_u.size();
     if (!nb) return DAECPP_B200_OK;
-    k_scatter_big<<<(int)((nb + 255) / 256), 256, 0, c->stream>>>(nb, c->dS.big_sj.p, c->dS.big_sm.p, c->dS.big_dst.p,
+    k_scatter_big<<<(int)((nb + 255) / 256), 256, 0, st>>>(nb, c->dS.big_sj.p, c->dS.big_sm.p, c->dS.big_dst.p,
                                                                  jvals_of(c), c->M.vals.p, alpha, c->LU.p);
     c->kernels += 1;
     return DAECPP_B200_OK;
