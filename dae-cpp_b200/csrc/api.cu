@@ -367,6 +367,8 @@ static void destroy_now(daecpp_b200_ctx *c)
     if (c->ev_mark) cudaEventDestroy(c->ev_mark);
     if (c->ev_z0) cudaEventDestroy(c->ev_z0);
     if (c->ev_z1) cudaEventDestroy(c->ev_z1);
+    if (c->ev_u0) cudaEventDestroy(c->ev_u0);
+    if (c->ev_u1) cudaEventDestroy(c->ev_u1);
     if (c->stream_zero) { cudaStreamSynchronize(c->stream_zero); cudaStreamDestroy(c->stream_zero); }
     for (int k = 0; k < 6; ++k) if (c->pev[k]) cudaEventDestroy(c->pev[k]);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -1129,6 +1131,7 @@ int daecpp_b200_set_option(daecpp_b200_ctx *c, const char *key, double value)
     else if (k == "bf_fused_panel") c->bf_fused_panel = value != 0.0;
     else if (k == "bf_dmma") c->bf_dmma = value != 0.0;
     else if (k == "bf_schur") c->bf_schur = value != 0.0;
+    else if (k == "bf_overlap_units") c->bf_overlap_units = value != 0.0;
     else if (k == "bf_zero_ahead") c->bf_zero_ahead = value != 0.0;
     else if (k == "bf_schur_fronts") c->bf_schur_fronts = (int)value;
     else if (k == "bf_fast_solve") c->bf_fast_solve = value != 0.0;

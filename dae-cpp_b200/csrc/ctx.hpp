@@ -152,6 +152,7 @@ struct GroupLaunch
     int32_t kind = 0, begin = 0, count = 0;
     int32_t group = 32, max_dim = 0; // kind 1: threads cooperating on one front
     int32_t grid = 0;                // kind 0: persistent blocks
+    int32_t overlap = 0;             // kind 0: independent of the big-front group behind it (symbolic.hpp: same_stage)
     int32_t max_s = 0, max_r = 0, max_children = 0; // kind 1: over the fronts of the level (pivots, rows below, children)
 };
 
@@ -201,6 +202,8 @@ struct daecpp_b200_options
                                        // its trailing update touches, so the extra pass per level is not paid back
     bool bf_zero_ahead = true;         // big fronts: all contribution blocks zeroed by one launch on a side stream at the start of the
                                        // refactorisation, under the latency-bound unit launches, instead of one launch per level
+    bool bf_overlap_units = true;      // a launch of subtree units that sits in the same stage of the tree as the level of big fronts behind it
+                                       // runs beside that level on the side stream (they do not depend on each other)
     int bf_schur_fronts = 0;           // ... only on levels with at least this many fronts and more than one block column (0: never;
                                        // measured slower at 30, 100 and 400 as well)
     // numerics
@@ -316,7 +319,7 @@ struct daecpp_b200_ctx : daecpp_b200_options
     double ms_symbolic = 0, ms_last_refactor = 0, ms_last_solve = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mark = nullptr;
     cudaStream_t stream_zero = nullptr;            // big fronts: contribution blocks zeroed beside the unit launches (bf_zero_ahead)
-    cudaEvent_t ev_z0 = nullptr, ev_z1 = nullptr;
+    cudaEvent_t ev_z0 = nullptr, ev_z1 = nullptr, ev_u0 = nullptr, ev_u1 = nullptr;
     // per-phase device times of iteration_resident (option "phase_timing"):
     // 0 assembly, 1 residual, 2 refactor, 3 solve, 4 update
     cudaEvent_t pev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -372,10 +375,10 @@ int jb_values(daecpp_b200_ctx *c, double alpha);          // u_vals = J - alpha*
 int unit_setup(daecpp_b200_ctx *c);
 int compose_entries(daecpp_b200_ctx *c);
 int launch_scatter_big(daecpp_b200_ctx *c, double alpha, cudaStream_t st);
-int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha);
-int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct);
+int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha, cudaStream_t st = nullptr);
+int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, cudaStream_t st = nullptr);
 int launch_unit_backward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, bool update, double atol, double rtol,
-                         double max_err_abs);
+                         double max_err_abs, cudaStream_t st = nullptr);
 // chain.cu
 int chain_try_setup(daecpp_b200_ctx *c, int32_t n, const int32_t *outer, const int32_t *inner);
 int chain_refactor_async(daecpp_b200_ctx *c, double alpha);

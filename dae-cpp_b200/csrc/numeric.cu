@@ -1570,7 +1570,7 @@ int upload_symbolic(daecpp_b200_ctx *c)
     for (const LaunchGroup &g : S.groups)
     {
         GroupLaunch L;
-        L.kind = g.kind; L.begin = g.begin; L.count = g.end - g.begin; L.max_dim = g.max_dim;
+        L.kind = g.kind; L.begin = g.begin; L.count = g.end - g.begin; L.max_dim = g.max_dim; L.overlap = g.same_stage;
         L.group = pick_group(g.max_dim);
         if (L.kind != 0)
             for (int32_t q = 0; q < L.count; ++q)
@@ -1631,6 +1631,27 @@ int assemble_values_only(daecpp_b200_ctx *c, double alpha)
     return DAECPP_B200_OK;
 }
 
+// The context's side stream and its fork / join events (created on first use).
+static int ensure_side_stream(daecpp_b200_ctx *c)
+{
+    if (c->stream_zero) return DAECPP_B200_OK;
+    DAECPP_CUDA_TRY(c, cudaStreamCreateWithFlags(&c->stream_zero, cudaStreamNonBlocking));
+    DAECPP_CUDA_TRY(c, cudaEventCreateWithFlags(&c->ev_z0, cudaEventDisableTiming));
+    DAECPP_CUDA_TRY(c, cudaEventCreateWithFlags(&c->ev_z1, cudaEventDisableTiming));
+    DAECPP_CUDA_TRY(c, cudaEventCreateWithFlags(&c->ev_u0, cudaEventDisableTiming));
+    DAECPP_CUDA_TRY(c, cudaEventCreateWithFlags(&c->ev_u1, cudaEventDisableTiming));
+    return DAECPP_B200_OK;
+}
+// A launch of subtree units in the same stage of the tree as the level of big fronts behind it: neither depends on the
+// other, and the units are a chain of dependent latencies on a few SMs' worth of lanes -- they run beside the level.
+static bool overlaps_next(const daecpp_b200_ctx *c, size_t l)
+{
+    return c->bf_overlap_units && c->blocked_lu && c->groups[l].kind == 0 && c->groups[l].overlap && l + 1 < c->groups.size() &&
+           c->groups[l + 1].kind != 0;
+}
+#define FORK_SIDE(c, st) do { DAECPP_CUDA_TRY(c, cudaEventRecord((c)->ev_u0, st)); DAECPP_CUDA_TRY(c, cudaStreamWaitEvent((c)->stream_zero, (c)->ev_u0, 0)); } while (0)
+#define JOIN_SIDE(c, st) do { DAECPP_CUDA_TRY(c, cudaEventRecord((c)->ev_u1, (c)->stream_zero)); DAECPP_CUDA_TRY(c, cudaStreamWaitEvent(st, (c)->ev_u1, 0)); } while (0)
+
 int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
 {
     cudaStream_t st = c->stream;
@@ -1658,12 +1679,7 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
     {   // the big fronts' factor storage (zeroed, matrix entries scattered) and the contribution blocks of ALL big fronts
         // (zeroed) are prepared on a side stream while the unit launches (a chain of dependent latencies that leaves the
         // memory system idle) run on the main one; the first level of big fronts waits for it
-        if (!c->stream_zero)
-        {
-            DAECPP_CUDA_TRY(c, cudaStreamCreateWithFlags(&c->stream_zero, cudaStreamNonBlocking));
-            DAECPP_CUDA_TRY(c, cudaEventCreateWithFlags(&c->ev_z0, cudaEventDisableTiming));
-            DAECPP_CUDA_TRY(c, cudaEventCreateWithFlags(&c->ev_z1, cudaEventDisableTiming));
-        }
+        if ((rc = ensure_side_stream(c))) return rc;
         DAECPP_CUDA_TRY(c, cudaEventRecord(c->ev_z0, st)); // behind everything that still reads the blocks
         DAECPP_CUDA_TRY(c, cudaStreamWaitEvent(c->stream_zero, c->ev_z0, 0));
         DAECPP_CUDA_TRY(c, cudaMemsetAsync(c->LU.p + S.lu_big_begin, 0, sizeof(double) * (size_t)(S.lu_size - S.lu_big_begin), c->stream_zero));
@@ -1674,11 +1690,21 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
         c->kernels += 1;
         zero_ahead = true;
     }
-    for (const GroupLaunch &L : c->groups)
+    bool join_pending = false;
+    for (size_t gl = 0; gl < c->groups.size(); ++gl)
     {
+        const GroupLaunch &L = c->groups[gl];
         if (L.kind != 0 && zero_ahead && !zero_waited) { DAECPP_CUDA_TRY(c, cudaStreamWaitEvent(st, c->ev_z1, 0)); zero_waited = true; }
         if (L.kind == 0)
         {
+            if (gl > 0 && overlaps_next(c, gl))
+            {   // beside the level of big fronts that follows; joined behind that level
+                if ((rc = ensure_side_stream(c))) return rc;
+                FORK_SIDE(c, st);
+                if ((rc = launch_unit_factor(c, L, alpha, c->stream_zero))) return rc;
+                join_pending = true;
+                continue;
+            }
             if ((rc = launch_unit_factor(c, L, alpha))) return rc;
         }
         else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
@@ -1748,7 +1774,9 @@ int numeric_refactor_async(daecpp_b200_ctx *c, double alpha, bool clear_flags)
             DISPATCH_GROUP(L.group, k_factor_level, L.count, T, L.begin, L.count, c->LU.p, c->CB.p, c->pivot_tol, c->d_flags);
             c->kernels += 1;
         }
+        if (join_pending && L.kind != 0) { JOIN_SIDE(c, st); join_pending = false; }
     }
+    if (join_pending) JOIN_SIDE(c, st);
     if (zero_ahead && !zero_waited) DAECPP_CUDA_TRY(c, cudaStreamWaitEvent(st, c->ev_z1, 0));
     DAECPP_CUDA_TRY(c, cudaGetLastError());
     c->n_refactor += 1;
@@ -1799,10 +1827,22 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
         k_permute_in<<<(n + 255) / 256, 256, 0, st>>>(n, c->dS.perm_rhs.p, c->b, c->work);
         c->kernels += 1;
     }
+    bool join_pending = false;
     for (size_t l = 0; l < c->groups.size(); ++l)
     {
         const GroupLaunch &L = c->groups[l];
-        if (L.kind == 0) { if ((rc = launch_unit_forward(c, L, direct))) return rc; }
+        if (L.kind == 0)
+        {
+            if (l > 0 && overlaps_next(c, l))
+            {   // same stage as the level of big fronts behind it: beside that level, joined behind it
+                if ((rc = ensure_side_stream(c))) return rc;
+                FORK_SIDE(c, st);
+                if ((rc = launch_unit_forward(c, L, direct, c->stream_zero))) return rc;
+                join_pending = true;
+                continue;
+            }
+            if ((rc = launch_unit_forward(c, L, direct))) return rc;
+        }
         else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
         {
             const size_t ysm = sizeof(double) * (size_t)L.max_s;
@@ -1814,22 +1854,37 @@ int numeric_solve(daecpp_b200_ctx *c, bool fuse_update, double atol, double rtol
                 if (L.max_r > 0)
                     bf_launch_pdl_smem(st, k_bf_forward_gemv2, dim3((L.max_r + GV_ROWS - 1) / GV_ROWS, L.count), GV_ROWS * GV_SEG, ysm, T, L.begin, c->LU.p, c->upd.p, c->work);
                 c->kernels += L.max_r > 0 ? 2 : 1;
-                continue;
             }
-            bf_launch_pdl(st, k_bf_forward_tri, dim3(L.count), 512, T, L.begin, c->LU.p, c->upd.p, c->work);
-            bf_launch_pdl(st, k_bf_forward_gemv, dim3((L.max_dim + GV_ROWS - 1) / GV_ROWS, L.count), GV_ROWS * GV_SEG, T, L.begin, c->LU.p, c->upd.p, c->work);
-            c->kernels += 2;
+            else
+            {
+                bf_launch_pdl(st, k_bf_forward_tri, dim3(L.count), 512, T, L.begin, c->LU.p, c->upd.p, c->work);
+                bf_launch_pdl(st, k_bf_forward_gemv, dim3((L.max_dim + GV_ROWS - 1) / GV_ROWS, L.count), GV_ROWS * GV_SEG, T, L.begin, c->LU.p, c->upd.p, c->work);
+                c->kernels += 2;
+            }
         }
         else
         {
             DISPATCH_GROUP(L.group, k_forward_level, L.count, T, L.begin, L.count, c->LU.p, c->upd.p, c->work);
             c->kernels += 1;
         }
+        if (join_pending && L.kind != 0) { JOIN_SIDE(c, st); join_pending = false; }
     }
+    if (join_pending) { JOIN_SIDE(c, st); join_pending = false; }
     for (size_t l = c->groups.size(); l-- > 0;)
     {
         const GroupLaunch &L = c->groups[l];
-        if (L.kind == 0) { if ((rc = launch_unit_backward(c, L, direct, fuse_update, atol, rtol, max_err_abs))) return rc; }
+        if (L.kind != 0 && l > 1 && overlaps_next(c, l - 1))
+        {   // the launch of units in front of this level (next in the backward order) is independent of it: started beside it
+            if ((rc = ensure_side_stream(c))) return rc;
+            FORK_SIDE(c, st);
+            if ((rc = launch_unit_backward(c, c->groups[l - 1], direct, fuse_update, atol, rtol, max_err_abs, c->stream_zero))) return rc;
+            join_pending = true;
+        }
+        if (L.kind == 0)
+        {
+            if (join_pending) { JOIN_SIDE(c, st); join_pending = false; continue; } // ran beside the level behind it
+            if ((rc = launch_unit_backward(c, L, direct, fuse_update, atol, rtol, max_err_abs))) return rc;
+        }
         else if (c->blocked_lu && L.max_dim >= c->blocked_lu_min_dim)
         {
             const size_t ysm = sizeof(double) * (size_t)L.max_s;

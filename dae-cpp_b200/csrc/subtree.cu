@@ -495,8 +495,9 @@ int launch_scatter_big(daecpp_b200_ctx *c, double alpha, cudaStream_t st)
     return DAECPP_B200_OK;
 }
 
-int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha)
+int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha, cudaStream_t st)
 {
+    if (!st) st = c->stream;
     UnitArgs A = base_args(c, g);
     A.ent_sj = c->dS.ent_sj.p; A.ent_sm = c->dS.ent_sm.p; A.ent_dst = c->dS.ent_dst.p;
     A.jvals = jvals_of(c); A.mvals = c->M.vals.p;
@@ -508,14 +509,15 @@ int launch_unit_factor(daecpp_b200_ctx *c, const GroupLaunch &g, double alpha)
         if (g.begin == 0) { A.trace_levels = c->trace.p + (size_t)c->S.nunit * 12 + 4; A.trace_unit = c->trace_unit_index; }
     }
     const int grid = grid_for(g, c->unit_grid_factor);
-    k_unit_factor<<<grid, c->unit_threads_eff, c->S.factor_smem_bytes, c->stream>>>(A);
+    k_unit_factor<<<grid, c->unit_threads_eff, c->S.factor_smem_bytes, st>>>(A);
     c->ticket_base += (uint32_t)(g.count + grid);
     c->kernels += 1;
     return DAECPP_B200_OK;
 }
 
-int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct)
+int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, cudaStream_t st)
 {
+    if (!st) st = c->stream;
     UnitArgs A = base_args(c, g);
     A.perm = direct ? c->dS.perm.p : nullptr;
     A.perm_rhs = direct ? c->dS.perm_rhs.p : nullptr;
@@ -523,15 +525,16 @@ int launch_unit_forward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct)
     A.y = c->work; A.upd = c->upd.p;
     if (c->trace_units && c->trace.p) A.trace = c->trace.p + (size_t)c->S.nunit * 4;
     const int grid = grid_for(g, c->unit_grid_solve);
-    k_unit_forward<<<grid, c->unit_threads_eff, c->S.solve_smem_bytes, c->stream>>>(A);
+    k_unit_forward<<<grid, c->unit_threads_eff, c->S.solve_smem_bytes, st>>>(A);
     c->ticket_base += (uint32_t)(g.count + grid);
     c->kernels += 1;
     return DAECPP_B200_OK;
 }
 
 int launch_unit_backward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, bool update, double atol, double rtol,
-                         double max_err_abs)
+                         double max_err_abs, cudaStream_t st)
 {
+    if (!st) st = c->stream;
     UnitArgs A = base_args(c, g);
     A.perm = c->dS.perm.p;
     A.y = c->work;
@@ -540,8 +543,8 @@ int launch_unit_backward(daecpp_b200_ctx *c, const GroupLaunch &g, bool direct, 
     A.atol = atol; A.rtol = rtol; A.max_err_abs = max_err_abs; A.floor = c->refine_floor;
     if (c->trace_units && c->trace.p) A.trace = c->trace.p + (size_t)c->S.nunit * 8;
     const int grid = grid_for(g, c->unit_grid_solve);
-    if (direct && update) k_unit_backward<true><<<grid, c->unit_threads_eff, c->S.solve_smem_bytes, c->stream>>>(A);
-    else k_unit_backward<false><<<grid, c->unit_threads_eff, c->S.solve_smem_bytes, c->stream>>>(A);
+    if (direct && update) k_unit_backward<true><<<grid, c->unit_threads_eff, c->S.solve_smem_bytes, st>>>(A);
+    else k_unit_backward<false><<<grid, c->unit_threads_eff, c->S.solve_smem_bytes, st>>>(A);
     c->ticket_base += (uint32_t)(g.count + grid);
     c->kernels += 1;
     return DAECPP_B200_OK;

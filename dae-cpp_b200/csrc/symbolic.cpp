@@ -646,12 +646,12 @@ static bool build_schedule(int32_t n, const int32_t *outer, const int32_t *inner
             while (tb < S.nbig && stage[nunit + S.big_sn[tb]] == st) { md = std::max<int32_t>(md, (int32_t)dim(S.big_sn[tb])); ++tb; }
             if (tb > b0)
             {
-                if (tu > open_begin) S.groups.push_back({0, open_begin, tu, 0});
+                if (tu > open_begin) S.groups.push_back({0, open_begin, tu, 0, stage[order[open_begin]] == st ? 1 : 0});
                 open_begin = tu;
-                S.groups.push_back({1, b0, tb, md});
+                S.groups.push_back({1, b0, tb, md, 0});
             }
         }
-        if (nunit > open_begin) S.groups.push_back({0, open_begin, nunit, 0});
+        if (nunit > open_begin) S.groups.push_back({0, open_begin, nunit, 0, 0});
     }
     S.nunit = nunit;
     S.nstages = nstage;

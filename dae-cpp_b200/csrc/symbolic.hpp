@@ -36,6 +36,7 @@ struct LaunchGroup
     int32_t kind = 0;           // 0: subtree units [begin,end) handed out by ticket; 1: big fronts big_sn[begin,end)
     int32_t begin = 0, end = 0;
     int32_t max_dim = 0;        // kind 1: largest front order in the group
+    int32_t same_stage = 0;     // kind 0: every unit of the group is in the stage of the big-front group that follows it (independent of it)
 };
 
 struct Symbolic

@@ -526,3 +526,15 @@ def test_big_front_zero_pivot_is_reported(opts):
     assert rc == B.EDECOMP
     rc, _ = _grid_solve_bytes(m, opts, zero_row=m * m - 1)
     assert rc == B.EDECOMP
+
+
+def test_big_front_side_stream_variants_are_bit_identical():
+    """The side stream of a context: big-front storage prepared under the unit launches (bf_zero_ahead) and unit launches
+    that share a stage of the tree with a level of big fronts run beside it (bf_overlap_units).  Scheduling only: the same
+    bits with either switch off, and from one run to the next."""
+    m = 400
+    rc0, ref = _grid_solve_bytes(m, {"bf_zero_ahead": 0, "bf_overlap_units": 0})
+    assert rc0 == 0
+    for opts in ({}, {}, {"bf_zero_ahead": 0}, {"bf_overlap_units": 0}, {}):
+        rc, got = _grid_solve_bytes(m, opts)
+        assert rc == 0 and got == ref, opts
