@@ -189,7 +189,9 @@ int daecpp_b200_debug_unit_trace(daecpp_b200_ctx *ctx, int64_t *out, int64_t cap
  * the factored diagonal block of a block column travels from the panel launch to the trailing update through a side buffer
  * instead of being factored a second time; bit-identical), "bf_lu_lookahead" (default 1: reciprocal of the next pivot formed
  * beside the update; bit-identical), "bf_zero_ahead" (default 1: the big fronts' factor storage and contribution blocks are
- * prepared on a side stream of the context while the subtree-unit launches run; 0 = in line, one zeroing launch per level), "group8_dim" / "warp_dim" / "warp_dim_many" / "warp_min_fronts" (local levels of a subtree unit
+ * prepared on a side stream of the context while the subtree-unit launches run; 0 = in line, one zeroing launch per level),
+ * "bf_overlap_units" (default 1: a launch of subtree units in the same stage of the tree as the level of big fronts behind it
+ * runs beside that level on the side stream; scheduling only), "group8_dim" / "warp_dim" / "warp_dim_many" / "warp_min_fronts" (local levels of a subtree unit
  * swept eight lanes / one warp per front up to this front order, larger fronts by the whole block; defaults 8 / 16 / 16 / 4,
  * round 1: 12 / 40), "unit_threads" (0 = automatic: 256, or 128 with 40 KB units where the automatic unit budget hits its ceiling;
  * else a multiple of 32, at most 256).  Numerics: "refine_steps" / "refine_floor" (guarded refinement step), "pivot_rel" (row-relative pivot
