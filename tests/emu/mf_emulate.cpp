@@ -43,6 +43,18 @@ extern "C" int mfemu_solve(int32_t n, const int32_t *outer, const int32_t *inner
         stats[4] = S.max_front; stats[5] = (double)S.lu_size; stats[6] = (double)S.cb_size; stats[7] = S.max_pivot_block;
         stats[8] = S.nunit; stats[9] = S.nbig; stats[10] = (double)S.groups.size(); stats[11] = S.factor_smem_bytes;
     }
+    // The CUDA path runs a launch of units beside the level of big fronts behind it when the schedule says they share a
+    // stage of the tree (LaunchGroup::same_stage): neither may depend on the other.  The walk here takes such a pair in
+    // the OPPOSITE order -- the level first, then the units -- so a schedule that flags a dependent pair gives wrong numbers.
+    std::vector<LaunchGroup> order(S.groups.begin(), S.groups.end());
+    int swapped = 0;
+    for (size_t gi = 1; gi + 1 < order.size(); ++gi)
+        if (order[gi].kind == 0 && order[gi].same_stage && order[gi + 1].kind != 0)
+        {
+            std::swap(order[gi], order[gi + 1]);
+            ++gi; ++swapped;
+        }
+    if (stats) stats[10] = (double)S.groups.size() + 1e-3 * swapped;
     std::vector<double> LU((size_t)S.lu_size + 1, 0.0), CB((size_t)S.cb_size + 1, 0.0), upd((size_t)S.upd_size + 1, 0.0);
     std::vector<double> y((size_t)n);
     int fail = 0;
@@ -51,7 +63,7 @@ extern "C" int mfemu_solve(int32_t n, const int32_t *outer, const int32_t *inner
     // ---------------------------------------------------------------- factorisation
     for (size_t q = 0; q < S.big_u.size(); ++q) LU[S.big_dst[q]] += vals[S.big_u[q]];
     std::vector<double> W;
-    for (const LaunchGroup &g : S.groups)
+    for (const LaunchGroup &g : order)
     {
         if (g.kind == 0)
         {
@@ -128,7 +140,7 @@ extern "C" int mfemu_solve(int32_t n, const int32_t *outer, const int32_t *inner
     // ---------------------------------------------------------------- forward sweep
     for (int32_t k = 0; k < n; ++k) y[k] = b[S.row_src.empty() ? S.perm[k] : S.row_src[(size_t)S.perm[k]]]; // Q A x = Q b
     std::vector<double> Y, U, X;
-    for (const LaunchGroup &g : S.groups)
+    for (const LaunchGroup &g : order)
     {
         if (g.kind == 0)
         {
@@ -183,9 +195,9 @@ extern "C" int mfemu_solve(int32_t n, const int32_t *outer, const int32_t *inner
     }
 
     // ---------------------------------------------------------------- backward sweep
-    for (size_t gi = S.groups.size(); gi-- > 0;)
+    for (size_t gi = order.size(); gi-- > 0;)
     {
-        const LaunchGroup &g = S.groups[gi];
+        const LaunchGroup &g = order[gi];
         if (g.kind == 0)
         {
             for (int32_t t = g.end - 1; t >= g.begin; --t)

@@ -56,6 +56,17 @@ def test_grid2d_units_and_big_fronts(emu, m, leaf, budget):
         assert st["n_big"] > 0 and st["n_units"] > 0 and st["n_groups"] >= 2  # mixed schedule
 
 
+@pytest.mark.parametrize("m,budget", [(96, 4096), (128, 2048), (160, 8192), (200, -1)])
+def test_units_beside_big_fronts_of_their_stage_are_independent(emu, m, budget):
+    """The CUDA path runs a launch of units beside the level of big fronts behind it when the schedule flags the pair
+    (LaunchGroup::same_stage).  The scalar walk takes every flagged pair in the opposite order, in the factorisation and
+    in both sweeps: the answer must not care.  (n_groups carries the number of swapped pairs in its fraction.)"""
+    st = _check(emu, m * m, P.grid2d_probe_matrix(m), EMPTY, 0.0, budget)
+    swapped = round((st["n_groups"] - int(st["n_groups"])) * 1000)
+    if budget >= 0:
+        assert st["n_big"] > 0 and swapped >= 1, st
+
+
 @pytest.mark.parametrize("budget", [0, 1024, 96 * 1024])
 def test_disconnected_and_dense_blocks(emu, budget):
     r = np.random.default_rng(3)
